@@ -1,0 +1,163 @@
+/*
+ * vhmm.h -- C ABI of libvhmm.so: the B200 (sm_100a) implementation of the VAE_HMM hot path
+ * of yashnaray/VQ-VAE-HMM-model.
+ *
+ * The reference has no FFI / plugin layer: the path sits behind Python classes
+ * (VQ_VAE_HMM_fixed.py:31-143).  Each entry point below states the reference lines it
+ * replaces; the Python host (vq-vae-hmm-model_b200/) binds them with ctypes and wraps them in
+ * torch.autograd.Function objects behind the reference's own class / method names.
+ *
+ * Conventions
+ *   - Every pointer is a DEVICE pointer unless the name ends in _host.  The library allocates
+ *     nothing and keeps no pointer after a call returns: the caller owns inputs, outputs and
+ *     workspace (size from vhmm_workspace_bytes).  All work is enqueued on `stream`
+ *     (a cudaStream_t passed as void*); no call synchronises the device.
+ *   - Tensors are contiguous fp32 in the reference's layouts: x (B,C,T), u (B,U,T),
+ *     logits/q (B,K,T), mu/logvar (B,C,T), log_A (B,T,K,K), log_b/gamma (B,T,K), xi (B,T,K,K);
+ *     lengths is int64 (B,) on the device.
+ *   - Return value: 0 ok; <0 invalid argument (VHMM_E_*); >0 a cudaError_t.  vhmm_last_error()
+ *     returns a thread-local description of the last failure.  Nothing throws.
+ *   - Parameters: 18 device pointers in state_dict order:
+ *       0 encoder.conv1.weight (H,C,3)   1 encoder.conv1.bias (H)
+ *       2 encoder.conv2.weight (H2,H,3)  3 encoder.conv2.bias (H2)
+ *       4 encoder.to_logits.weight (K,H2,1) 5 encoder.to_logits.bias (K)
+ *       6 prior.log_prior (K)
+ *       7 prior.transition_net.0.weight (TH,U) 8 prior.transition_net.0.bias (TH)
+ *       9 prior.transition_net.2.weight (K*K,TH) 10 prior.transition_net.2.bias (K*K)
+ *      11 decoder.embeddings.weight (K,H)
+ *      12 decoder.conv1.weight (H,H,3)  13 decoder.conv1.bias (H)
+ *      14 decoder.conv2.weight (H,H,3)  15 decoder.conv2.bias (H)
+ *      16 decoder.to_params.weight (2C,H,1) 17 decoder.to_params.bias (2C)
+ *     The flat gradient buffer uses the same order, tensors back to back (vhmm_param_count).
+ */
+#ifndef VHMM_H_
+#define VHMM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VHMM_VERSION 100 /* major*100 + minor */
+#define VHMM_NUM_PARAMS 18
+#define VHMM_PAD_STATE 255 /* Viterbi path value for t >= lengths[b] */
+
+enum {
+  VHMM_E_ARG = -1,       /* null pointer / non-positive size */
+  VHMM_E_DIMS = -2,      /* unsupported model dimensions for this entry point */
+  VHMM_E_WORKSPACE = -3, /* workspace too small */
+  VHMM_E_ALIGN = -4      /* pointer not 16-byte aligned */
+};
+
+/* model dimensions: VAE_HMM(input_dim=C, hidden_dim=H, K, hidden_dim2=H2, u_dim=U,
+ * trans_hidden=TH), VQ_VAE_HMM_fixed.py:93 */
+typedef struct vhmm_dims {
+  int32_t C, H, K, H2, U, TH;
+} vhmm_dims;
+
+typedef struct vhmm_params {
+  const float* p[VHMM_NUM_PARAMS];
+} vhmm_params;
+
+/* ops for vhmm_workspace_bytes */
+enum {
+  VHMM_OP_ENCODER_FWD = 1,
+  VHMM_OP_PRIOR_FWD = 2,
+  VHMM_OP_DECODER_FWD = 3,
+  VHMM_OP_ELBO = 4,
+  VHMM_OP_HMM_FORWARD = 5,
+  VHMM_OP_HMM_POSTERIOR = 6,
+  VHMM_OP_VITERBI = 7,
+  VHMM_OP_HMM_DECODE = 8,
+  VHMM_OP_HMM_SCAN = 9,
+  VHMM_OP_EMISSION_TABLE = 10
+};
+
+int vhmm_version(void);
+const char* vhmm_last_error(void);
+/* kernels launched by this library in this process so far (bench.py gpu_launches) */
+int64_t vhmm_launch_count(void);
+/* number of floats in the flat parameter / gradient buffer for `dims` */
+int64_t vhmm_param_count(const vhmm_dims* dims);
+/* offsets (in floats) of the 18 tensors inside the flat buffer; out has 19 entries (last=total) */
+int vhmm_param_offsets(const vhmm_dims* dims, int64_t* out_host);
+/* minimum workspace for `op`; for VHMM_OP_ELBO any larger workspace lets the library process
+ * more sequences per pass (it chunks the batch to fit). */
+size_t vhmm_workspace_bytes(int op, const vhmm_dims* dims, int64_t B, int64_t T);
+
+/* Encoder.forward, VQ_VAE_HMM_fixed.py:38-41 (+ softmax of :114/:141 when q != NULL).
+ * x (B,C,T) -> logits (B,K,T) [, q (B,K,T)].  Either output may be NULL (not both). */
+int vhmm_encoder_fwd(const vhmm_dims* dims, const vhmm_params* params, const float* x,
+                     int64_t B, int64_t T, float* logits, float* q, void* workspace,
+                     size_t workspace_bytes, void* stream);
+
+/* Prior.forward, VQ_VAE_HMM_fixed.py:59-71.  u (B,U,T) (the layout collate_fn produces; the
+ * Python wrapper applies the permute rule of :64-65) -> log_pi (K), log_A (B,T,K,K). */
+int vhmm_prior_fwd(const vhmm_dims* dims, const vhmm_params* params, const float* u, int64_t B,
+                   int64_t T, float* log_pi, float* log_A, void* workspace,
+                   size_t workspace_bytes, void* stream);
+
+/* Decoder.forward, VQ_VAE_HMM_fixed.py:81-90.  q (B,K,T) -> mu (B,C,T), logvar (B,C,T). */
+int vhmm_decoder_fwd(const vhmm_dims* dims, const vhmm_params* params, const float* q, int64_t B,
+                     int64_t T, float* mu, float* logvar, void* workspace,
+                     size_t workspace_bytes, void* stream);
+
+/* VAE_HMM.compute_loss forward (+ its autograd backward when grads != NULL),
+ * VQ_VAE_HMM_fixed.py:106-137 and loss.backward() at :156.
+ *   norms      device double[2] = { max(N_valid_global*C, 1), B_global }: the reference's
+ *              normalisers (:120, :131, :135); under batch sharding they are the GLOBAL values.
+ *   beta       the KL weight (:137)
+ *   sums       device double[4] out: { sum nll*mask, sum_b(init+trans), sum entropy*mask,
+ *              valid steps } over THIS call's sequences (un-normalised).
+ *              loss = sums[0]/norms[0] + beta*(-sums[1]/norms[1] - sums[2]/norms[1]).
+ *   grads      device float[vhmm_param_count] out or NULL: d loss / d params for this call's
+ *              sequences with the global normalisers applied (sum over ranks = full gradient).
+ */
+int vhmm_elbo(const vhmm_dims* dims, const vhmm_params* params, const float* x, const float* u,
+              const int64_t* lengths, int64_t B, int64_t T, const double* norms, double beta,
+              double* sums, float* grads, void* workspace, size_t workspace_bytes, void* stream);
+
+/* argmax regime decoding (backtesting.py:155, src/backtesting.py:107): q or logits (B,K,T) ->
+ * regimes int64 (B,T), lowest index on ties. */
+int vhmm_argmax_regimes(const float* q, int64_t B, int64_t K, int64_t T, int64_t* regimes,
+                        void* stream);
+
+/* ---- exact-HMM stages: extensions, absent from the reference ---- */
+
+/* B.1: decoder on the K one-hot sequences of length T -> mu_tab (K,C,T), logvar_tab (K,C,T). */
+int vhmm_emission_table(const vhmm_dims* dims, const vhmm_params* params, int64_t T,
+                        float* mu_tab, float* logvar_tab, void* workspace, size_t workspace_bytes,
+                        void* stream);
+/* B.1: log_b[b,t,k] = -0.5 sum_c [log(2 pi v) + (x-mu)^2/v], v = max(exp(logvar),1e-8). */
+int vhmm_emission_logprob(const float* x, const float* mu_tab, const float* logvar_tab, int64_t B,
+                          int64_t C, int64_t T, int64_t K, float* log_b, void* stream);
+/* B.2: forward recursion.  loglik (B); alpha (B,T,K) log-space or NULL. */
+int vhmm_hmm_forward(const float* log_pi, const float* log_A, const float* log_b,
+                     const int64_t* lengths, int64_t B, int64_t T, int64_t K, float* loglik,
+                     float* alpha, void* stream);
+/* B.3: forward + backward recursion = gradient of loglik: gamma (B,T,K), xi (B,T,K,K) or NULL. */
+int vhmm_hmm_posterior(const float* log_pi, const float* log_A, const float* log_b,
+                       const int64_t* lengths, int64_t B, int64_t T, int64_t K, float* loglik,
+                       float* gamma, float* xi, void* workspace, size_t workspace_bytes,
+                       void* stream);
+/* B.4: Viterbi, uint8 back-pointers, lowest-index tie-break.  path (B,T) uint8, score (B). */
+int vhmm_viterbi(const float* log_pi, const float* log_A, const float* log_b,
+                 const int64_t* lengths, int64_t B, int64_t T, int64_t K, uint8_t* path,
+                 float* score, void* workspace, size_t workspace_bytes, void* stream);
+/* cfg 3: Viterbi path + posterior gamma from one read of the inputs. */
+int vhmm_hmm_decode(const float* log_pi, const float* log_A, const float* log_b,
+                    const int64_t* lengths, int64_t B, int64_t T, int64_t K, uint8_t* path,
+                    float* gamma, float* loglik, void* workspace, size_t workspace_bytes,
+                    void* stream);
+/* B.5: log-semiring parallel scan over T (long sequences, small batch).  loglik (B);
+ * alpha (B,T,K) all-prefix forward variables or NULL. */
+int vhmm_hmm_scan(const float* log_pi, const float* log_A, const float* log_b,
+                  const int64_t* lengths, int64_t B, int64_t T, int64_t K, float* loglik,
+                  float* alpha, void* workspace, size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VHMM_H_ */

@@ -1,0 +1,178 @@
+"""GPU tests of the exact-HMM stages against the CPU oracle (oracle/hmm.py; 'parity unpinned'
+vs the reference, which has no such code).  log-lik / gamma / xi within 1e-5 of the float64
+restatement, Viterbi paths bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import hmm as H
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+def rand_hmm(B, T, K, seed, lb_scale=3.0):
+    r = np.random.default_rng(seed)
+    lp = r.normal(size=K); lp -= np.log(np.exp(lp).sum())
+    la = r.normal(size=(B, T, K, K)); la -= np.log(np.exp(la).sum(-1, keepdims=True))
+    lb = r.normal(size=(B, T, K)) * lb_scale
+    L = r.integers(1, T + 1, size=B); L[0] = T
+    return lp.astype(np.float32), la.astype(np.float32), lb.astype(np.float32), L.astype(np.int64)
+
+
+def dev(*a):
+    return [torch.from_numpy(np.ascontiguousarray(v)).cuda() for v in a]
+
+
+CASES = [(2, 1, 4), (3, 1, 1), (3, 7, 9), (3, 50, 33), (3, 256, 130), (3, 257, 5), (3, 1000, 3), (4, 64, 17),
+         (5, 20, 6), (8, 31, 4), (32, 12, 3)]
+
+
+@pytest.mark.parametrize("K,T,B", CASES)
+def test_forward_posterior_vs_oracle(K, T, B):
+    import vhmm_b200.functional as Fn
+    lp, la, lb, L = rand_hmm(B, T, K, seed=K * 7 + T)
+    gamma64, xi64, ll64 = H.posteriors(lp, la, lb, L)
+    alpha64, _ = H.forward(lp, la, lb, L)
+    d = dev(lp, la, lb, L)
+    ll, alpha = Fn.hmm_forward(*d, want_alpha=True)
+    assert np.allclose(ll.cpu().numpy(), ll64, rtol=TOL, atol=1e-5)
+    a = alpha.cpu().numpy()
+    valid = np.arange(T)[None, :] < L[:, None]
+    assert np.abs(a - alpha64)[valid].max() <= TOL * max(1.0, np.abs(alpha64).max())
+    # carried alpha for t >= L
+    assert np.abs(a - alpha64).max() <= 2e-5 * max(1.0, np.abs(alpha64).max())
+    ll2, gamma, xi = Fn.hmm_posterior(*d)
+    assert np.allclose(ll2.cpu().numpy(), ll64, rtol=TOL, atol=1e-5)
+    assert np.abs(gamma.cpu().numpy() - gamma64).max() <= TOL
+    assert np.abs(xi.cpu().numpy() - xi64).max() <= TOL
+    ll3 = Fn.hmm_scan(*d)
+    assert np.allclose(ll3.cpu().numpy(), ll64, rtol=TOL, atol=1e-5)
+    ll4, alpha4 = Fn.hmm_scan(*d, want_alpha=True)
+    assert np.abs(alpha4.cpu().numpy() - alpha64)[valid].max() <= 2e-5 * max(1.0, np.abs(alpha64).max())
+
+
+@pytest.mark.parametrize("K,T,B", CASES)
+def test_viterbi_bit_exact(K, T, B):
+    import vhmm_b200.functional as Fn
+    lp, la, lb, L = rand_hmm(B, T, K, seed=K * 13 + T)
+    # quantise so that exact ties occur regularly
+    la = np.round(la * 2) / 2
+    lb = np.round(lb * 2) / 2
+    lp = np.round(lp * 2) / 2
+    path64, score = H.viterbi(lp, la, lb, L, dtype=np.float32)
+    d = dev(lp.astype(np.float32), la.astype(np.float32), lb.astype(np.float32), L)
+    path, sc = Fn.viterbi(*d)
+    assert np.array_equal(path.cpu().numpy(), path64)
+    assert np.array_equal(sc.cpu().numpy(), score)
+    p2, gamma, ll = Fn.hmm_decode(*d)
+    assert np.array_equal(p2.cpu().numpy(), path64)
+    g64, _, ll64 = H.posteriors(lp, la, lb, L)
+    assert np.abs(gamma.cpu().numpy() - g64).max() <= TOL
+    assert np.allclose(ll.cpu().numpy(), ll64, rtol=TOL, atol=1e-5)
+
+
+def test_viterbi_all_ties_lowest_index():
+    import vhmm_b200.functional as Fn
+    K, T = 3, 40
+    lp = np.full(K, -np.log(K), np.float32)
+    la = np.full((2, T, K, K), -np.log(K), np.float32)
+    lb = np.zeros((2, T, K), np.float32)
+    lb[1, T - 1] = [-5.0, 1.0, 1.0]
+    path, _ = Fn.viterbi(*dev(lp, la, lb, np.array([T, T], np.int64)))
+    p = path.cpu().numpy()
+    assert (p[0] == 0).all()
+    assert p[1, -1] == 1 and (p[1, :-1] == 0).all()
+
+
+def test_loglik_autograd_is_beta_recursion():
+    import vhmm_b200.functional as Fn
+    lp, la, lb, L = rand_hmm(6, 37, 3, seed=5)
+    gamma64, xi64, ll64 = H.posteriors(lp, la, lb, L)
+    tlp, tla, tlb, tL = dev(lp, la, lb, L)
+    tlp.requires_grad_(True); tla.requires_grad_(True); tlb.requires_grad_(True)
+    ll = Fn.HmmLogLikFunction.apply(tlp, tla, tlb, tL)
+    w = torch.arange(1, 7, device="cuda", dtype=torch.float32)
+    (ll * w).sum().backward()
+    wn = np.arange(1, 7)[:, None, None]
+    assert np.abs(tlb.grad.cpu().numpy() - gamma64 * wn).max() <= 1e-4
+    assert np.abs(tla.grad.cpu().numpy() - xi64 * wn[..., None]).max() <= 1e-4
+    assert np.abs(tlp.grad.cpu().numpy() - (gamma64[:, 0] * wn[:, 0]).sum(0)).max() <= 1e-4
+
+
+def test_emissions_and_model_level_api():
+    import vhmm_b200 as V
+    from oracle import elbo as O
+    C, Hd, K, H2, U, TH = 5, 64, 3, 32, 4, 128
+    p = O.init_params(C, Hd, K, H2, U, TH, seed=2)
+    x, u, L = O.synth_batch(9, C, U, 48, seed=8)
+    m = V.VAE_HMM(C, Hd, K, H2, u_dim=U)
+    m.load_state_dict(p)
+    m = m.cuda()
+    mu_t, lv_t = H.emission_table({k: v.double() for k, v in p.items()}, 48, O.decode)
+    lb64 = H.emission_logprob(x.numpy(), mu_t.numpy(), lv_t.numpy())
+    with torch.no_grad():
+        log_pi, log_A, log_b = m.hmm_inputs(x.cuda(), u.cuda())
+    assert np.abs(log_b.cpu().numpy() - lb64).max() <= TOL * np.abs(lb64).max()
+    lp64, lA64 = O.prior({k: v.double() for k, v in p.items()}, u.double(), U)
+    g64, _, ll64 = H.posteriors(lp64.numpy(), lA64.numpy(), lb64, L.numpy())
+    with torch.no_grad():
+        probs = m.get_regime_probs(x.cuda(), u.cuda(), L)
+        ll = m.hmm_log_likelihood(x.cuda(), u.cuda(), L)
+        path, score = m.viterbi(x.cuda(), u.cuda(), L)
+    assert probs.shape == (9, K, 48)
+    assert np.abs(probs.permute(0, 2, 1).cpu().numpy() - g64).max() <= 1e-4
+    assert np.allclose(ll.cpu().numpy(), ll64, rtol=TOL)
+    # Viterbi on the device's own fp32 inputs must equal the oracle on those same inputs
+    p_or, _ = H.viterbi(log_pi.cpu().numpy(), log_A.cpu().numpy(), log_b.cpu().numpy(), L.numpy())
+    assert np.array_equal(path.cpu().numpy(), p_or)
+
+
+def test_large_batch_properties():
+    """cfg-3-shaped (B reduced): gamma rows sum to 1 on valid steps and are 0 beyond; scan ==
+    sequential forward; decode's path == viterbi's path; permutation invariance."""
+    import vhmm_b200.functional as Fn
+    B, T, K = 20000, 256, 3
+    g = torch.Generator(device="cuda").manual_seed(0)
+    la = torch.log_softmax(torch.randn(B, T, K, K, device="cuda", generator=g), dim=-1)
+    lb = torch.randn(B, T, K, device="cuda", generator=g) * 3
+    lp = torch.log_softmax(torch.randn(K, device="cuda", generator=g), dim=-1)
+    L = torch.randint(1, T + 1, (B,), device="cuda", generator=g)
+    ll, gamma, xi = Fn.hmm_posterior(lp, la, lb, L)
+    valid = torch.arange(T, device="cuda")[None, :] < L[:, None]
+    s = gamma.sum(-1)
+    assert float((s[valid] - 1).abs().max()) < 1e-5 and float(s[~valid].abs().max()) == 0
+    xs = xi.sum((-1, -2))
+    v1 = valid.clone(); v1[:, 0] = False
+    assert float((xs[v1] - 1).abs().max()) < 1e-5
+    assert float((xi.sum(-2) - gamma)[v1].abs().max()) < 1e-5
+    ll2 = Fn.hmm_scan(lp, la, lb, L)
+    assert torch.allclose(ll, ll2, rtol=1e-5, atol=1e-4)
+    p1, sc = Fn.viterbi(lp, la, lb, L)
+    p2, g2, ll3 = Fn.hmm_decode(lp, la, lb, L)
+    assert torch.equal(p1, p2) and torch.allclose(g2, gamma, atol=1e-6) and torch.equal(ll3, ll)
+    assert bool(((p1 == 255) == ~valid).all())
+    assert bool((sc <= ll + 1e-3).all())   # best path score <= total log-likelihood
+    # check a slice against the oracle
+    n = 64
+    po, so = H.viterbi(lp.cpu().numpy(), la[:n].cpu().numpy(), lb[:n].cpu().numpy(), L[:n].cpu().numpy())
+    assert np.array_equal(p1[:n].cpu().numpy(), po)
+
+
+def test_long_sequence_scan():
+    """cfg-4-shaped: T=65536 (B reduced to 8): scan log-lik equals the sequential kernel and
+    the float64 oracle on one sequence."""
+    import vhmm_b200.functional as Fn
+    B, T, K = 8, 65536, 3
+    g = torch.Generator(device="cuda").manual_seed(1)
+    la = torch.log_softmax(torch.randn(B, T, K, K, device="cuda", generator=g), dim=-1)
+    lb = torch.randn(B, T, K, device="cuda", generator=g)
+    lp = torch.log_softmax(torch.randn(K, device="cuda", generator=g), dim=-1)
+    L = torch.tensor([T, T - 1, 40000, 129, 128, 1, 65000, 2], device="cuda")
+    ll_seq = Fn.hmm_forward(lp, la, lb, L)
+    ll_scan, alpha = Fn.hmm_scan(lp, la, lb, L, want_alpha=True)
+    assert torch.allclose(ll_seq, ll_scan, rtol=1e-6, atol=1e-2)
+    _, ll64 = H.forward(lp.cpu().numpy(), la[:1].cpu().numpy(), lb[:1].cpu().numpy(), np.array([T]))
+    assert abs(float(ll_scan[0]) - ll64[0]) <= TOL * abs(ll64[0])
+    a_last = torch.logsumexp(alpha[0, T - 1], dim=0)
+    assert abs(float(a_last) - ll64[0]) <= 2e-5 * abs(ll64[0])

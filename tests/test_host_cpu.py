@@ -1,0 +1,78 @@
+"""CPU-side checks of the host package: the C-ABI library builds/loads and exports every symbol
+declared in include/vhmm.h (no compute calls without a GPU), the module mirrors the reference
+interface, collate semantics."""
+import os
+import re
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    import vhmm_b200 as V
+    L = V.lib()
+    hdr = open(os.path.join(ROOT, "include", "vhmm.h")).read()
+    declared = set(re.findall(r"\b(vhmm_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 17
+    from vhmm_b200 import _lib
+    assert declared == set(_lib.PROTOTYPES), declared ^ set(_lib.PROTOTYPES)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert L.vhmm_version() == 100
+
+
+def test_param_layout_matches_state_dict():
+    import vhmm_b200 as V
+    from vhmm_b200 import functional as Fn
+    m = V.VAE_HMM(5, 64, 3, 32, u_dim=4)
+    assert list(m.state_dict().keys()) == list(Fn.PARAM_ORDER)
+    off = Fn.param_offsets(m._dims)
+    sizes = [m.state_dict()[k].numel() for k in Fn.PARAM_ORDER]
+    assert [off[i + 1] - off[i] for i in range(18)] == sizes
+    assert Fn.param_count(m._dims) == 34649
+
+
+def test_same_init_as_reference_golden():
+    """Default-initialised weights equal the reference's for the same seed (same RNG order)."""
+    import vhmm_b200 as V
+    from conftest import load_golden
+    g = load_golden("base_fresh")
+    torch.manual_seed(0)
+    m = V.VAE_HMM(5, 64, 3, 32, u_dim=4)
+    for k, v in m.state_dict().items():
+        assert torch.equal(v, g["params"][k]), k
+
+
+def test_no_cpu_fallback_and_reference_errors():
+    import vhmm_b200 as V
+    m = V.VAE_HMM(5, 8, 3, 4, u_dim=2, trans_hidden=8)
+    with pytest.raises(ValueError):
+        m.compute_loss(torch.zeros(1, 5, 4), torch.zeros(1, 2, 4), None)
+    with pytest.raises(ValueError):
+        V.VAE_HMM(5, 8, 3, 4)
+    if not torch.cuda.is_available():
+        with pytest.raises(V.VhmmError):
+            m.encode(torch.zeros(1, 5, 4))
+
+
+def test_collate_contract():
+    import random
+    import vhmm_b200 as V
+    random.seed(1)
+    xs = torch.randn(4, 5, 90)
+    us = torch.randn(4, 4, 90)
+    ds = V.RandomChunkDataset(xs, us, min_len=20, max_len=50)
+    assert len(ds) == 1000
+    batch = [ds[i] for i in range(6)]
+    x, u, L = V.collate_fn(batch, "cpu")
+    assert L.dtype == torch.int64 and L.device.type == "cpu"
+    T = int(L.max())
+    assert x.shape == (6, 5, T) and u.shape == (6, 4, T)
+    for i, (xi, ui, n) in enumerate(batch):
+        assert torch.equal(x[i, :, :n], xi) and float(x[i, :, n:].abs().sum()) == 0
+        assert torch.equal(u[i, :, :n], ui) and float(u[i, :, n:].abs().sum()) == 0
+    import src.utils
+    import VQ_VAE_HMM_fixed as R
+    assert R.VAE_HMM is V.VAE_HMM and R.collate_fn is V.collate_fn

@@ -1,0 +1,128 @@
+"""ctypes binding of libvhmm.so (include/vhmm.h) + the in-tree nvcc build.
+
+The library is plain CUDA-runtime C ABI (no torch types in any signature).  It is built
+in-tree (``libvhmm.so`` next to this file) so that it travels to the GPU box with the repo
+snapshot and shows up in the loaded-library list of every process that uses the product.
+There is no CPU fallback: if the library cannot be loaded, every op raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import shutil
+import subprocess
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(_HERE, "csrc")
+LIB_PATH = os.path.join(_HERE, "libvhmm.so")
+SOURCES = ("api.cu", "elbo_layerwise.cu", "hmm.cu", "elbo_fused.cu", "train_ops.cu")
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-shared"]
+
+# op codes (include/vhmm.h)
+OP_ENCODER_FWD, OP_PRIOR_FWD, OP_DECODER_FWD, OP_ELBO = 1, 2, 3, 4
+OP_HMM_FORWARD, OP_HMM_POSTERIOR, OP_VITERBI, OP_HMM_DECODE, OP_HMM_SCAN, OP_EMISSION_TABLE = 5, 6, 7, 8, 9, 10
+NUM_PARAMS = 18
+PAD_STATE = 255
+
+
+class Dims(ctypes.Structure):
+    _fields_ = [("C", ctypes.c_int32), ("H", ctypes.c_int32), ("K", ctypes.c_int32),
+                ("H2", ctypes.c_int32), ("U", ctypes.c_int32), ("TH", ctypes.c_int32)]
+
+
+class Params(ctypes.Structure):
+    _fields_ = [("p", ctypes.c_void_p * NUM_PARAMS)]
+
+
+class VhmmError(RuntimeError):
+    pass
+
+
+def _sources():
+    return [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
+
+
+def needs_build() -> bool:
+    if not os.path.exists(LIB_PATH):
+        return True
+    t = os.path.getmtime(LIB_PATH)
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(_HERE, "..", "include", "vhmm.h")]
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile every CUDA source for sm_100a into libvhmm.so (nvcc cross-compiles without a GPU)."""
+    if not force and not needs_build():
+        return LIB_PATH
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        raise VhmmError("nvcc not found: cannot build libvhmm.so")
+    tmp = LIB_PATH + ".tmp.%d" % os.getpid()
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", tmp] + _sources()
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise VhmmError("nvcc failed:\n" + res.stdout + res.stderr)
+    os.replace(tmp, LIB_PATH)
+    if verbose:
+        print(res.stderr)
+    return LIB_PATH
+
+
+_lock = threading.Lock()
+_lib = None
+
+_P, _I64, _SZ, _DBL = ctypes.c_void_p, ctypes.c_int64, ctypes.c_size_t, ctypes.c_double
+_DP, _PP = ctypes.POINTER(Dims), ctypes.POINTER(Params)
+
+# name -> (restype, argtypes); must list every symbol declared in include/vhmm.h
+PROTOTYPES = {
+    "vhmm_version": (ctypes.c_int, []),
+    "vhmm_last_error": (ctypes.c_char_p, []),
+    "vhmm_launch_count": (_I64, []),
+    "vhmm_param_count": (_I64, [_DP]),
+    "vhmm_param_offsets": (ctypes.c_int, [_DP, ctypes.POINTER(_I64)]),
+    "vhmm_workspace_bytes": (_SZ, [ctypes.c_int, _DP, _I64, _I64]),
+    "vhmm_encoder_fwd": (ctypes.c_int, [_DP, _PP, _P, _I64, _I64, _P, _P, _P, _SZ, _P]),
+    "vhmm_prior_fwd": (ctypes.c_int, [_DP, _PP, _P, _I64, _I64, _P, _P, _P, _SZ, _P]),
+    "vhmm_decoder_fwd": (ctypes.c_int, [_DP, _PP, _P, _I64, _I64, _P, _P, _P, _SZ, _P]),
+    "vhmm_elbo": (ctypes.c_int, [_DP, _PP, _P, _P, _P, _I64, _I64, _P, _DBL, _P, _P, _P, _SZ, _P]),
+    "vhmm_argmax_regimes": (ctypes.c_int, [_P, _I64, _I64, _I64, _P, _P]),
+    "vhmm_emission_table": (ctypes.c_int, [_DP, _PP, _I64, _P, _P, _P, _SZ, _P]),
+    "vhmm_emission_logprob": (ctypes.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P, _P]),
+    "vhmm_hmm_forward": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P]),
+    "vhmm_hmm_posterior": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _SZ, _P]),
+    "vhmm_viterbi": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _SZ, _P]),
+    "vhmm_hmm_decode": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _SZ, _P]),
+    "vhmm_hmm_scan": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _SZ, _P]),
+}
+
+
+def lib() -> ctypes.CDLL:
+    """Load (building first if the sources are newer) and return the bound library."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if needs_build():
+            build()
+        try:
+            L = ctypes.CDLL(LIB_PATH)
+        except OSError as e:  # no fallback: fail loudly
+            raise VhmmError(f"cannot load {LIB_PATH}: {e}") from e
+        for name, (res, args) in PROTOTYPES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        msg = lib().vhmm_last_error().decode("utf-8", "replace")
+        kind = "invalid argument" if rc < 0 else "CUDA error"
+        raise VhmmError(f"{what} failed ({kind} {rc}): {msg}")

@@ -1,0 +1,175 @@
+// api.cu -- extern "C" entry points of libvhmm.so (include/vhmm.h).  Argument validation and
+// dispatch only; kernels live in the other translation units.
+#include <atomic>
+
+#include "common.cuh"
+
+namespace vhmm {
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+// elbo_layerwise.cu
+size_t layerwise_workspace_bytes(int op, const vhmm_dims& d, int64_t B, int64_t T);
+int layerwise_encoder_fwd(const vhmm_dims&, const vhmm_params&, const float*, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
+int layerwise_prior_fwd(const vhmm_dims&, const vhmm_params&, const float*, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
+int layerwise_decoder_fwd(const vhmm_dims&, const vhmm_params&, const float*, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
+int layerwise_elbo(const vhmm_dims&, const vhmm_params&, const float*, const float*, const int64_t*, int64_t, int64_t, const double*, double, double*, float*, void*, size_t, cudaStream_t);
+int layerwise_emission_table(const vhmm_dims&, const vhmm_params&, int64_t, float*, float*, void*, size_t, cudaStream_t);
+int launch_argmax(const float* q, int64_t B, int64_t K, int64_t T, int64_t* out, cudaStream_t st);
+// hmm.cu
+size_t hmm_workspace_bytes(int op, int64_t B, int64_t T, int64_t K);
+int hmm_emission_logprob(const float*, const float*, const float*, int64_t, int64_t, int64_t, int64_t, float*, cudaStream_t);
+int hmm_forward(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, float*, float*, cudaStream_t);
+int hmm_posterior(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, float*, float*, float*, void*, size_t, cudaStream_t);
+int hmm_viterbi(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, void*, size_t, cudaStream_t);
+int hmm_decode(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, float*, void*, size_t, cudaStream_t);
+int hmm_scan(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
+
+static bool params_ok(const vhmm_params* p) {
+  if (!p) return false;
+  for (int i = 0; i < VHMM_NUM_PARAMS; ++i)
+    if (!p->p[i]) return false;
+  return true;
+}
+
+}  // namespace vhmm
+
+using namespace vhmm;
+
+#define ARG(cond, what) VHMM_REQUIRE((cond), VHMM_E_ARG, "%s: invalid argument: %s", __func__, what)
+
+extern "C" {
+
+int vhmm_version(void) { return VHMM_VERSION; }
+
+const char* vhmm_last_error(void) { return g_err; }
+
+int64_t vhmm_launch_count(void) { return (int64_t)g_launches.load(); }
+
+int64_t vhmm_param_count(const vhmm_dims* dims) {
+  if (!dims_ok(dims)) return -1;
+  int64_t off[VHMM_NUM_PARAMS + 1];
+  param_offsets(*dims, off);
+  return off[VHMM_NUM_PARAMS];
+}
+
+int vhmm_param_offsets(const vhmm_dims* dims, int64_t* out_host) {
+  ARG(dims_ok(dims), "dims");
+  ARG(out_host, "out_host");
+  param_offsets(*dims, out_host);
+  return 0;
+}
+
+size_t vhmm_workspace_bytes(int op, const vhmm_dims* dims, int64_t B, int64_t T) {
+  if (B <= 0 || T <= 0) return 0;
+  switch (op) {
+    case VHMM_OP_HMM_FORWARD: case VHMM_OP_HMM_POSTERIOR: case VHMM_OP_VITERBI:
+    case VHMM_OP_HMM_DECODE: case VHMM_OP_HMM_SCAN:
+      return hmm_workspace_bytes(op, B, T, dims ? dims->K : 0);
+    default:
+      if (!dims_ok(dims)) return 0;
+      return layerwise_workspace_bytes(op, *dims, B, T);
+  }
+}
+
+int vhmm_encoder_fwd(const vhmm_dims* dims, const vhmm_params* params, const float* x, int64_t B,
+                     int64_t T, float* logits, float* q, void* workspace, size_t workspace_bytes,
+                     void* stream) {
+  ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(x, "x");
+  ARG(B > 0 && T > 0, "B,T"); ARG(logits || q, "logits and q both NULL"); ARG(workspace, "workspace");
+  return layerwise_encoder_fwd(*dims, *params, x, B, T, logits, q, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int vhmm_prior_fwd(const vhmm_dims* dims, const vhmm_params* params, const float* u, int64_t B,
+                   int64_t T, float* log_pi, float* log_A, void* workspace, size_t workspace_bytes,
+                   void* stream) {
+  ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(u, "u");
+  ARG(B > 0 && T > 0, "B,T"); ARG(log_pi && log_A, "outputs"); ARG(workspace, "workspace");
+  return layerwise_prior_fwd(*dims, *params, u, B, T, log_pi, log_A, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int vhmm_decoder_fwd(const vhmm_dims* dims, const vhmm_params* params, const float* q, int64_t B,
+                     int64_t T, float* mu, float* logvar, void* workspace, size_t workspace_bytes,
+                     void* stream) {
+  ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(q, "q");
+  ARG(B > 0 && T > 0, "B,T"); ARG(mu && logvar, "outputs"); ARG(workspace, "workspace");
+  return layerwise_decoder_fwd(*dims, *params, q, B, T, mu, logvar, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int vhmm_elbo(const vhmm_dims* dims, const vhmm_params* params, const float* x, const float* u,
+              const int64_t* lengths, int64_t B, int64_t T, const double* norms, double beta,
+              double* sums, float* grads, void* workspace, size_t workspace_bytes, void* stream) {
+  ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(x && u && lengths, "x/u/lengths");
+  ARG(B > 0 && T > 0, "B,T"); ARG(norms && sums, "norms/sums"); ARG(workspace, "workspace");
+  return layerwise_elbo(*dims, *params, x, u, lengths, B, T, norms, beta, sums, grads, workspace,
+                        workspace_bytes, (cudaStream_t)stream);
+}
+
+int vhmm_argmax_regimes(const float* q, int64_t B, int64_t K, int64_t T, int64_t* regimes, void* stream) {
+  ARG(q && regimes, "q/regimes"); ARG(B > 0 && K > 0 && T > 0, "B,K,T");
+  return launch_argmax(q, B, K, T, regimes, (cudaStream_t)stream);
+}
+
+int vhmm_emission_table(const vhmm_dims* dims, const vhmm_params* params, int64_t T, float* mu_tab,
+                        float* logvar_tab, void* workspace, size_t workspace_bytes, void* stream) {
+  ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(T > 0, "T");
+  ARG(mu_tab && logvar_tab, "outputs"); ARG(workspace, "workspace");
+  return layerwise_emission_table(*dims, *params, T, mu_tab, logvar_tab, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int vhmm_emission_logprob(const float* x, const float* mu_tab, const float* logvar_tab, int64_t B,
+                          int64_t C, int64_t T, int64_t K, float* log_b, void* stream) {
+  ARG(x && mu_tab && logvar_tab && log_b, "pointers"); ARG(B > 0 && C > 0 && T > 0 && K > 0, "sizes");
+  return hmm_emission_logprob(x, mu_tab, logvar_tab, B, C, T, K, log_b, (cudaStream_t)stream);
+}
+
+#define HMM_ARGS_OK()                                                                   \
+  ARG(log_pi && log_A && log_b && lengths, "inputs");                                   \
+  ARG(B > 0 && T > 0, "B,T");                                                           \
+  VHMM_REQUIRE(K >= 1 && K <= 32, VHMM_E_DIMS, "%s: K=%lld outside [1,32]", __func__, (long long)K)
+
+int vhmm_hmm_forward(const float* log_pi, const float* log_A, const float* log_b,
+                     const int64_t* lengths, int64_t B, int64_t T, int64_t K, float* loglik,
+                     float* alpha, void* stream) {
+  HMM_ARGS_OK(); ARG(loglik, "loglik");
+  return hmm_forward(log_pi, log_A, log_b, lengths, B, T, K, loglik, alpha, (cudaStream_t)stream);
+}
+
+int vhmm_hmm_posterior(const float* log_pi, const float* log_A, const float* log_b,
+                       const int64_t* lengths, int64_t B, int64_t T, int64_t K, float* loglik,
+                       float* gamma, float* xi, void* workspace, size_t workspace_bytes, void* stream) {
+  HMM_ARGS_OK(); ARG(loglik && gamma, "loglik/gamma"); ARG(workspace, "workspace");
+  return hmm_posterior(log_pi, log_A, log_b, lengths, B, T, K, loglik, gamma, xi, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int vhmm_viterbi(const float* log_pi, const float* log_A, const float* log_b, const int64_t* lengths,
+                 int64_t B, int64_t T, int64_t K, uint8_t* path, float* score, void* workspace,
+                 size_t workspace_bytes, void* stream) {
+  HMM_ARGS_OK(); ARG(path, "path"); ARG(workspace, "workspace");
+  return hmm_viterbi(log_pi, log_A, log_b, lengths, B, T, K, path, score, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int vhmm_hmm_decode(const float* log_pi, const float* log_A, const float* log_b,
+                    const int64_t* lengths, int64_t B, int64_t T, int64_t K, uint8_t* path,
+                    float* gamma, float* loglik, void* workspace, size_t workspace_bytes, void* stream) {
+  HMM_ARGS_OK(); ARG(path && gamma && loglik, "outputs"); ARG(workspace, "workspace");
+  return hmm_decode(log_pi, log_A, log_b, lengths, B, T, K, path, gamma, loglik, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int vhmm_hmm_scan(const float* log_pi, const float* log_A, const float* log_b, const int64_t* lengths,
+                  int64_t B, int64_t T, int64_t K, float* loglik, float* alpha, void* workspace,
+                  size_t workspace_bytes, void* stream) {
+  HMM_ARGS_OK(); ARG(loglik, "loglik"); ARG(workspace, "workspace");
+  return hmm_scan(log_pi, log_A, log_b, lengths, B, T, K, loglik, alpha, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+}  // extern "C"

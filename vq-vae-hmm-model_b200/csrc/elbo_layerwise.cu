@@ -1,0 +1,291 @@
+// elbo_layerwise.cu -- the layer-wise (activation-stashing) implementation of the pinned path
+// for ARBITRARY model dimensions: Encoder / Prior / Decoder forward and the mean-field ELBO
+// with its full backward.  The batch is processed in chunks that fit the caller's workspace.
+// Reference: VQ_VAE_HMM_fixed.py:31-143; maths in SURVEY.md Appendix A.2.
+#include "conv_generic.cuh"
+#include "pointwise.cuh"
+
+namespace vhmm {
+
+static const int64_t kMaxChunk = 32768;  // gridDim.y/z limit is 65535
+
+struct LayerwiseSizes {
+  int64_t per_step_fwd;   // floats per (sequence, step) kept by the forward pass
+  int64_t per_step_bwd;   // extra floats per step for the backward pass
+  int64_t scratch;        // wgrad partial scratch (floats), independent of the chunk size
+};
+
+static LayerwiseSizes layerwise_sizes(const vhmm_dims& d) {
+  LayerwiseSizes s;
+  const int64_t K2 = (int64_t)d.K * d.K;
+  s.per_step_fwd = d.H + d.H2 + 3 * (int64_t)d.K + d.TH + K2 + 3 * (int64_t)d.H + 2 * d.C;
+  s.per_step_bwd = 2 * d.C + d.K + K2 + 3 * (int64_t)d.H + 2 * (int64_t)d.K + d.H2 + d.H + d.TH;
+  const int64_t BIG = 1 << 20;
+  int64_t m = 0, v;
+  v = wgrad_scratch_floats(d.C, d.H, 3, BIG); m = v > m ? v : m;
+  v = wgrad_scratch_floats(d.H, d.H2, 3, BIG); m = v > m ? v : m;
+  v = wgrad_scratch_floats(d.H2, d.K, 1, BIG); m = v > m ? v : m;
+  v = wgrad_scratch_floats(d.U, d.TH, 1, BIG); m = v > m ? v : m;
+  v = wgrad_scratch_floats(d.TH, d.K * d.K, 1, BIG); m = v > m ? v : m;
+  v = wgrad_scratch_floats(d.K, d.H, 1, BIG); m = v > m ? v : m;
+  v = wgrad_scratch_floats(d.H, d.H, 3, BIG); m = v > m ? v : m;
+  v = wgrad_scratch_floats(d.H, 2 * d.C, 1, BIG); m = v > m ? v : m;
+  s.scratch = m;
+  return s;
+}
+
+static size_t fixed_bytes(const vhmm_dims& d, int64_t T) {
+  LayerwiseSizes s = layerwise_sizes(d);
+  size_t bytes = 0;
+  bytes += align_up(sizeof(float) * KMAX, 256);                        // log_pi
+  bytes += align_up(sizeof(double) * KMAX, 256);                       // qsum
+  bytes += align_up(sizeof(float) * (size_t)s.scratch, 256);
+  return bytes + 4096;
+}
+
+size_t layerwise_workspace_bytes(int op, const vhmm_dims& d, int64_t B, int64_t T) {
+  LayerwiseSizes s = layerwise_sizes(d);
+  const int64_t Bc = B < 1024 ? B : 1024;
+  const size_t slack = 64 * 256;
+  switch (op) {
+    case VHMM_OP_ENCODER_FWD:
+      return (size_t)B * T * (d.H + d.H2 + d.K) * 4 + slack;
+    case VHMM_OP_PRIOR_FWD:
+      return (size_t)B * T * (d.TH + (int64_t)d.K * d.K) * 4 + slack;
+    case VHMM_OP_DECODER_FWD:
+      return (size_t)B * T * (3 * (int64_t)d.H) * 4 + slack;
+    case VHMM_OP_EMISSION_TABLE:
+      return (size_t)d.K * T * (3 * (int64_t)d.H + d.K + 2 * d.C) * 4 + slack;
+    case VHMM_OP_ELBO:
+      return fixed_bytes(d, T) + (size_t)Bc * T * (s.per_step_fwd + s.per_step_bwd) * 4 +
+             (size_t)Bc * cdiv(T, 256) * 32 + slack;
+    default:
+      return 0;
+  }
+}
+
+// ---- forward building blocks (whole-tensor, caller provides scratch) -------------------
+static int encoder_chain(const vhmm_dims& d, const vhmm_params& P, const float* x, int64_t B,
+                         int64_t T, float* h1, float* h2, float* logits, cudaStream_t st) {
+  int rc;
+  if ((rc = launch_conv(x, wview_fwd(P.p[P_E1W], d.C, 3), P.p[P_E1B], nullptr, h1, B, d.C, d.H, T, 3, EPI_RELU, st))) return rc;
+  if ((rc = launch_conv(h1, wview_fwd(P.p[P_E2W], d.H, 3), P.p[P_E2B], nullptr, h2, B, d.H, d.H2, T, 3, EPI_RELU, st))) return rc;
+  return launch_conv(h2, wview_fwd(P.p[P_E3W], d.H2, 1), P.p[P_E3B], nullptr, logits, B, d.H2, d.K, T, 1, EPI_NONE, st);
+}
+
+// e (B,H,T) = E^T q ; g1, g2 ; out rows [row0,row0+nrows) of to_params into `out`
+static int decoder_chain(const vhmm_dims& d, const vhmm_params& P, const float* q, int64_t B,
+                         int64_t T, float* e, float* g1, float* g2, cudaStream_t st) {
+  int rc;
+  WView emb{P.p[P_EMB], 0, 1, d.H, 0};  // W(o=d, c=k) = E[k*H + d]   (VQ_VAE_HMM_fixed.py:83)
+  if ((rc = launch_conv(q, emb, nullptr, nullptr, e, B, d.K, d.H, T, 1, EPI_NONE, st))) return rc;
+  if ((rc = launch_conv(e, wview_fwd(P.p[P_D1W], d.H, 3), P.p[P_D1B], nullptr, g1, B, d.H, d.H, T, 3, EPI_RELU, st))) return rc;
+  return launch_conv(g1, wview_fwd(P.p[P_D2W], d.H, 3), P.p[P_D2B], nullptr, g2, B, d.H, d.H, T, 3, EPI_RELU, st);
+}
+
+int layerwise_encoder_fwd(const vhmm_dims& d, const vhmm_params& P, const float* x, int64_t B,
+                          int64_t T, float* logits, float* q, void* ws, size_t ws_bytes,
+                          cudaStream_t st) {
+  Arena A(ws, ws_bytes);
+  float* h1 = A.take<float>((size_t)B * d.H * T);
+  float* h2 = A.take<float>((size_t)B * d.H2 * T);
+  float* lg = logits ? logits : A.take<float>((size_t)B * d.K * T);
+  VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "encoder_fwd: workspace %zu < %zu", ws_bytes, A.used);
+  for (int64_t b0 = 0; b0 < B; b0 += kMaxChunk) {
+    int64_t nb = B - b0 < kMaxChunk ? B - b0 : kMaxChunk;
+    int rc = encoder_chain(d, P, x + b0 * d.C * T, nb, T, h1 + b0 * d.H * T, h2 + b0 * d.H2 * T,
+                           lg + b0 * d.K * T, st);
+    if (rc) return rc;
+    if (q) {
+      dim3 g((unsigned)cdiv(T, 256), (unsigned)nb);
+      softmax_kernel<<<g, 256, 0, st>>>(lg + b0 * d.K * T, q + b0 * d.K * T, nullptr, d.K, (int)T);
+      VHMM_LAUNCH_CHECK();
+    }
+  }
+  return 0;
+}
+
+int layerwise_prior_fwd(const vhmm_dims& d, const vhmm_params& P, const float* u, int64_t B,
+                        int64_t T, float* log_pi, float* log_A, void* ws, size_t ws_bytes,
+                        cudaStream_t st) {
+  VHMM_REQUIRE(d.K <= KMAX, VHMM_E_DIMS, "prior_fwd: K=%d > %d", d.K, KMAX);
+  Arena A(ws, ws_bytes);
+  const int K2 = d.K * d.K;
+  float* a = A.take<float>((size_t)B * d.TH * T);
+  float* M = A.take<float>((size_t)B * K2 * T);
+  VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "prior_fwd: workspace %zu < %zu", ws_bytes, A.used);
+  log_pi_kernel<<<1, 32, 0, st>>>(P.p[P_LOGPRIOR], log_pi, d.K);
+  VHMM_LAUNCH_CHECK();
+  int rc;
+  if ((rc = launch_conv(u, wview_fwd(P.p[P_T0W], d.U, 1), P.p[P_T0B], nullptr, a, B, d.U, d.TH, T, 1, EPI_RELU, st))) return rc;
+  if ((rc = launch_conv(a, wview_fwd(P.p[P_T2W], d.TH, 1), P.p[P_T2B], nullptr, M, B, d.TH, K2, T, 1, EPI_NONE, st))) return rc;
+  for (int64_t b0 = 0; b0 < B; b0 += kMaxChunk) {
+    int64_t nb = B - b0 < kMaxChunk ? B - b0 : kMaxChunk;
+    dim3 g((unsigned)cdiv(T, 128), (unsigned)d.K, (unsigned)nb);
+    logA_out_kernel<<<g, 128, 0, st>>>(M + b0 * K2 * T, log_A + b0 * T * K2, d.K, (int)T);
+    VHMM_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+int layerwise_decoder_fwd(const vhmm_dims& d, const vhmm_params& P, const float* q, int64_t B,
+                          int64_t T, float* mu, float* logvar, void* ws, size_t ws_bytes,
+                          cudaStream_t st) {
+  Arena A(ws, ws_bytes);
+  float* e = A.take<float>((size_t)B * d.H * T);
+  float* g1 = A.take<float>((size_t)B * d.H * T);
+  float* g2 = A.take<float>((size_t)B * d.H * T);
+  VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "decoder_fwd: workspace %zu < %zu", ws_bytes, A.used);
+  int rc;
+  if ((rc = decoder_chain(d, P, q, B, T, e, g1, g2, st))) return rc;
+  // to_params rows [0,C) -> mu, rows [C,2C) -> logvar (VQ_VAE_HMM_fixed.py:87-90)
+  if ((rc = launch_conv(g2, wview_fwd(P.p[P_DPW], d.H, 1), P.p[P_DPB], nullptr, mu, B, d.H, d.C, T, 1, EPI_NONE, st))) return rc;
+  return launch_conv(g2, wview_fwd(P.p[P_DPW] + (int64_t)d.C * d.H, d.H, 1), P.p[P_DPB] + d.C, nullptr, logvar, B, d.H, d.C, T, 1, EPI_NONE, st);
+}
+
+// ---- ELBO forward + backward ------------------------------------------------------------
+int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, const float* u,
+                   const int64_t* lengths, int64_t B, int64_t T, const double* norms, double beta,
+                   double* sums, float* grads, void* ws, size_t ws_bytes, cudaStream_t st) {
+  VHMM_REQUIRE(d.K <= KMAX, VHMM_E_DIMS, "elbo: K=%d > %d", d.K, KMAX);
+  const LayerwiseSizes S = layerwise_sizes(d);
+  const int K = d.K, K2 = d.K * d.K, C = d.C, H = d.H, H2 = d.H2, U = d.U, TH = d.TH;
+  int64_t off[VHMM_NUM_PARAMS + 1];
+  param_offsets(d, off);
+
+  Arena A(ws, ws_bytes);
+  float* log_pi = A.take<float>(KMAX);
+  double* qsum = A.take<double>(KMAX);
+  float* scratch = A.take<float>((size_t)S.scratch);
+  VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "elbo: workspace %zu too small (fixed part %zu)", ws_bytes, A.used);
+  const int64_t per_step = S.per_step_fwd + (grads ? S.per_step_bwd : 0);
+  const size_t left = (ws_bytes - A.used > 64 * 256) ? ws_bytes - A.used - 64 * 256 : 0;
+  int64_t Bc = (int64_t)(left / ((size_t)per_step * T * 4 + (size_t)cdiv(T, 256) * 32));
+  if (Bc > B) Bc = B;
+  if (Bc > kMaxChunk) Bc = kMaxChunk;
+  VHMM_REQUIRE(Bc >= 1, VHMM_E_WORKSPACE, "elbo: workspace %zu cannot hold one sequence (T=%lld)", ws_bytes, (long long)T);
+  const size_t n = (size_t)Bc * T;
+  double* partial = A.take<double>(4 * (size_t)(Bc * cdiv(T, 256)));
+  float* h1 = A.take<float>(n * H);   float* h2 = A.take<float>(n * H2);
+  float* lg = A.take<float>(n * K);   float* q = A.take<float>(n * K);   float* lq = A.take<float>(n * K);
+  float* a = A.take<float>(n * TH);   float* M = A.take<float>(n * K2);
+  float* e = A.take<float>(n * H);    float* g1 = A.take<float>(n * H);  float* g2 = A.take<float>(n * H);
+  float* p = A.take<float>(n * 2 * C);
+  float *dp = nullptr, *dqp = nullptr, *dM = nullptr, *dg2 = nullptr, *dg1 = nullptr, *de = nullptr,
+        *dqd = nullptr, *dl = nullptr, *dh2 = nullptr, *dh1 = nullptr, *da = nullptr;
+  if (grads) {
+    dp = A.take<float>(n * 2 * C); dqp = A.take<float>(n * K); dM = A.take<float>(n * K2);
+    dg2 = A.take<float>(n * H); dg1 = A.take<float>(n * H); de = A.take<float>(n * H);
+    dqd = A.take<float>(n * K); dl = A.take<float>(n * K);
+    dh2 = A.take<float>(n * H2); dh1 = A.take<float>(n * H); da = A.take<float>(n * TH);
+  }
+  VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "elbo: internal workspace accounting error (%zu > %zu)", A.used, ws_bytes);
+
+  VHMM_CUDA_CHECK(cudaMemsetAsync(sums, 0, 4 * sizeof(double), st));
+  VHMM_CUDA_CHECK(cudaMemsetAsync(qsum, 0, KMAX * sizeof(double), st));
+  if (grads) VHMM_CUDA_CHECK(cudaMemsetAsync(grads, 0, off[VHMM_NUM_PARAMS] * sizeof(float), st));
+  log_pi_kernel<<<1, 32, 0, st>>>(P.p[P_LOGPRIOR], log_pi, K);
+  VHMM_LAUNCH_CHECK();
+  const float betaf = (float)beta;
+  int rc;
+#define RC(call) do { if ((rc = (call))) return rc; } while (0)
+  for (int64_t b0 = 0; b0 < B; b0 += Bc) {
+    const int64_t nb = B - b0 < Bc ? B - b0 : Bc;
+    const float* xc = x + b0 * C * T;
+    const float* uc = u + b0 * U * T;
+    const int64_t* Lc = lengths + b0;
+    // ---------------- forward ----------------
+    RC(encoder_chain(d, P, xc, nb, T, h1, h2, lg, st));
+    {
+      dim3 g((unsigned)cdiv(T, 256), (unsigned)nb);
+      softmax_kernel<<<g, 256, 0, st>>>(lg, q, lq, K, (int)T);
+      VHMM_LAUNCH_CHECK();
+    }
+    RC(launch_conv(uc, wview_fwd(P.p[P_T0W], U, 1), P.p[P_T0B], nullptr, a, nb, U, TH, T, 1, EPI_RELU, st));
+    RC(launch_conv(a, wview_fwd(P.p[P_T2W], TH, 1), P.p[P_T2B], nullptr, M, nb, TH, K2, T, 1, EPI_NONE, st));
+    {
+      dim3 g((unsigned)cdiv(T, 256), (unsigned)K, (unsigned)nb);
+      row_logsoftmax_kernel<<<g, 256, 0, st>>>(M, K, (int)T);
+      VHMM_LAUNCH_CHECK();
+    }
+    RC(decoder_chain(d, P, q, nb, T, e, g1, g2, st));
+    RC(launch_conv(g2, wview_fwd(P.p[P_DPW], H, 1), P.p[P_DPB], nullptr, p, nb, H, 2 * C, T, 1, EPI_NONE, st));
+    {
+      dim3 g((unsigned)cdiv(T, 256), (unsigned)nb);
+      loss_seed_kernel<<<g, 256, 0, st>>>(xc, p, q, lq, M, log_pi, Lc, norms, betaf, C, K, (int)T,
+                                          partial, dp, dqp, dM);
+      VHMM_LAUNCH_CHECK();
+      sum_partials_kernel<<<1, 1024, 0, st>>>(partial, (int64_t)g.x * g.y, sums);
+      VHMM_LAUNCH_CHECK();
+      q0_sum_kernel<<<1, 1024, 0, st>>>(q, nb, K, (int)T, qsum);
+      VHMM_LAUNCH_CHECK();
+    }
+    if (!grads) continue;
+    // ---------------- backward: decoder ----------------
+    RC(launch_wgrad(dp, g2, grads + off[P_DPW], grads + off[P_DPB], wview_fwd(nullptr, H, 1), nb, H, 2 * C, T, 1, scratch, st));
+    RC(launch_conv(dp, wview_dgrad(P.p[P_DPW], H, 1), nullptr, g2, dg2, nb, 2 * C, H, T, 1, EPI_MASK, st));
+    RC(launch_wgrad(dg2, g1, grads + off[P_D2W], grads + off[P_D2B], wview_fwd(nullptr, H, 3), nb, H, H, T, 3, scratch, st));
+    RC(launch_conv(dg2, wview_dgrad(P.p[P_D2W], H, 3), nullptr, g1, dg1, nb, H, H, T, 3, EPI_MASK, st));
+    RC(launch_wgrad(dg1, e, grads + off[P_D1W], grads + off[P_D1B], wview_fwd(nullptr, H, 3), nb, H, H, T, 3, scratch, st));
+    RC(launch_conv(dg1, wview_dgrad(P.p[P_D1W], H, 3), nullptr, nullptr, de, nb, H, H, T, 3, EPI_NONE, st));
+    {
+      WView embL{nullptr, 0, 1, H, 0};  // dE[k,d] stored at k*H + d  with (o=d, c=k)
+      RC(launch_wgrad(de, q, grads + off[P_EMB], nullptr, embL, nb, K, H, T, 1, scratch, st));
+      WView embT{P.p[P_EMB], 0, H, 1, 0};  // dq[k,t] = sum_d E[k,d] de[d,t]: W(o=k, c=d)
+      RC(launch_conv(de, embT, nullptr, nullptr, dqd, nb, H, K, T, 1, EPI_NONE, st));
+    }
+    {
+      dim3 g((unsigned)cdiv(T, 256), (unsigned)nb);
+      dlogits_kernel<<<g, 256, 0, st>>>(q, lq, dqd, dqp, Lc, norms, betaf, K, (int)T, dl);
+      VHMM_LAUNCH_CHECK();
+    }
+    // ---------------- backward: encoder ----------------
+    RC(launch_wgrad(dl, h2, grads + off[P_E3W], grads + off[P_E3B], wview_fwd(nullptr, H2, 1), nb, H2, K, T, 1, scratch, st));
+    RC(launch_conv(dl, wview_dgrad(P.p[P_E3W], H2, 1), nullptr, h2, dh2, nb, K, H2, T, 1, EPI_MASK, st));
+    RC(launch_wgrad(dh2, h1, grads + off[P_E2W], grads + off[P_E2B], wview_fwd(nullptr, H, 3), nb, H, H2, T, 3, scratch, st));
+    RC(launch_conv(dh2, wview_dgrad(P.p[P_E2W], H, 3), nullptr, h1, dh1, nb, H2, H, T, 3, EPI_MASK, st));
+    RC(launch_wgrad(dh1, xc, grads + off[P_E1W], grads + off[P_E1B], wview_fwd(nullptr, C, 3), nb, C, H, T, 3, scratch, st));
+    // ---------------- backward: prior ----------------
+    RC(launch_wgrad(dM, a, grads + off[P_T2W], grads + off[P_T2B], wview_fwd(nullptr, TH, 1), nb, TH, K2, T, 1, scratch, st));
+    RC(launch_conv(dM, wview_dgrad(P.p[P_T2W], TH, 1), nullptr, a, da, nb, K2, TH, T, 1, EPI_MASK, st));
+    RC(launch_wgrad(da, uc, grads + off[P_T0W], grads + off[P_T0B], wview_fwd(nullptr, U, 1), nb, U, TH, T, 1, scratch, st));
+  }
+#undef RC
+  finalize_prior_kernel<<<1, 32, 0, st>>>(log_pi, qsum, norms, betaf, K, sums,
+                                          grads ? grads + off[P_LOGPRIOR] : nullptr);
+  VHMM_LAUNCH_CHECK();
+  return 0;
+}
+
+// per-state emission table: decoder on the K one-hot sequences.
+__global__ void onehot_kernel(float* __restrict__ q, int K, int T) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= (int64_t)K * K * T) return;
+  const int64_t row = i / T;        // row = s*K + k
+  q[i] = (row / K == row % K) ? 1.f : 0.f;
+}
+
+int layerwise_emission_table(const vhmm_dims& d, const vhmm_params& P, int64_t T, float* mu_tab,
+                             float* logvar_tab, void* ws, size_t ws_bytes, cudaStream_t st) {
+  Arena A(ws, ws_bytes);
+  float* q = A.take<float>((size_t)d.K * d.K * T);
+  VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "emission_table: workspace too small");
+  onehot_kernel<<<(unsigned)cdiv((int64_t)d.K * d.K * T, 256), 256, 0, st>>>(q, d.K, (int)T);
+  VHMM_LAUNCH_CHECK();
+  return layerwise_decoder_fwd(d, P, q, d.K, T, mu_tab, logvar_tab, (char*)ws + A.used,
+                               ws_bytes - A.used, st);
+}
+
+}  // namespace vhmm
+
+namespace vhmm {
+int launch_argmax(const float* q, int64_t B, int64_t K, int64_t T, int64_t* out, cudaStream_t st) {
+  for (int64_t b0 = 0; b0 < B; b0 += kMaxChunk) {
+    int64_t nb = B - b0 < kMaxChunk ? B - b0 : kMaxChunk;
+    dim3 g((unsigned)cdiv(T, 256), (unsigned)nb);
+    argmax_kernel<<<g, 256, 0, st>>>(q + b0 * K * T, (int)K, (int)T, out + b0 * T);
+    VHMM_LAUNCH_CHECK();
+  }
+  return 0;
+}
+}  // namespace vhmm

@@ -1,0 +1,235 @@
+// hmm.cu -- host side of the exact-HMM stages (extensions): dispatch
+// between the tuned small-K kernels (hmm_small.cuh, hmm_scan.cuh) and the any-K warp kernels
+// (hmm_generic.cuh), workspace carving, emission log-probabilities.
+#include "hmm_generic.cuh"
+#include "hmm_scan.cuh"
+
+namespace vhmm {
+
+static inline bool small_k(int64_t K) { return K >= 2 && K <= 4; }
+static inline bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
+
+constexpr int HS_TC = 8;     // steps per staged slab
+constexpr int HS_NT = 128;   // rows (threads) per CTA
+constexpr int SCAN_CH = 128; // steps per scan chunk
+
+static int64_t psi_bytes(int64_t K) { return K <= 4 ? 1 : K; }
+
+size_t hmm_workspace_bytes(int op, int64_t B, int64_t T, int64_t K) {
+  if (K <= 0) K = 32;
+  const size_t stash = align_up((size_t)B * T * K * sizeof(float), 256);
+  const size_t psi = align_up((size_t)B * T * psi_bytes(K), 256);
+  const int64_t nck = cdiv(T, SCAN_CH);
+  switch (op) {
+    case VHMM_OP_HMM_FORWARD: return 0;
+    case VHMM_OP_HMM_POSTERIOR: return stash + 256;
+    case VHMM_OP_VITERBI: return psi + 256;
+    case VHMM_OP_HMM_DECODE: return stash + psi + 512;
+    case VHMM_OP_HMM_SCAN:
+      return align_up((size_t)B * nck * K * K * 4, 256) + 2 * align_up((size_t)B * nck * 8, 256) +
+             align_up((size_t)B * nck * K * 4, 256) + 1024;
+    default: return 0;
+  }
+}
+
+// ---- emission log-probabilities (B.1) -----------------------------------------------------
+// log_b[b,t,k] = -0.5 sum_c [ log(2 pi v) + (x - mu)^2 / v ],  v = max(exp(logvar), 1e-8)
+__global__ void __launch_bounds__(256)
+emission_kernel(const float* __restrict__ x, const float* __restrict__ mu, const float* __restrict__ lv,
+                int C, int T, int K, float* __restrict__ log_b) {
+  const int t = blockIdx.x * 256 + threadIdx.x;
+  if (t >= T) return;
+  const int64_t b = blockIdx.y;
+  for (int k = 0; k < K; ++k) {
+    float acc = 0.f;
+    for (int c = 0; c < C; ++c) {
+      const float xv = x[(b * C + c) * (int64_t)T + t];
+      const float m = mu[((int64_t)k * C + c) * T + t];
+      const float v = fmaxf(expf(lv[((int64_t)k * C + c) * T + t]), 1e-8f);
+      const float d = xv - m;
+      acc += logf(6.283185307179586f * v) + d * d / v;
+    }
+    log_b[(b * T + t) * K + k] = -0.5f * acc;
+  }
+}
+
+int hmm_emission_logprob(const float* x, const float* mu_tab, const float* logvar_tab, int64_t B,
+                         int64_t C, int64_t T, int64_t K, float* log_b, cudaStream_t st) {
+  for (int64_t b0 = 0; b0 < B; b0 += 32768) {
+    const int64_t nb = B - b0 < 32768 ? B - b0 : 32768;
+    dim3 g((unsigned)cdiv(T, 256), (unsigned)nb);
+    emission_kernel<<<g, 256, 0, st>>>(x + b0 * C * T, mu_tab, logvar_tab, (int)C, (int)T, (int)K,
+                                       log_b + b0 * T * K);
+    VHMM_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+// ---- small-K launch helpers ---------------------------------------------------------------
+template <int K, bool SP, bool VIT>
+static int launch_fwd_small(const hs::Args& a, cudaStream_t st) {
+  using TL = hs::Tile<K, HS_TC, HS_NT>;
+  auto kern = hs::fwd_kernel<K, HS_TC, HS_NT, SP, VIT>;
+  VHMM_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TL::SMEM));
+  kern<<<(unsigned)cdiv(a.nrows, HS_NT), HS_NT, TL::SMEM, st>>>(a);
+  VHMM_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int K>
+static int launch_bwd_small(const hs::Args& a, cudaStream_t st) {
+  using TL = hs::Tile<K, HS_TC, HS_NT>;
+  auto kern = hs::bwd_kernel<K, HS_TC, HS_NT>;
+  VHMM_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TL::SMEM));
+  kern<<<(unsigned)cdiv(a.nrows, HS_NT), HS_NT, TL::SMEM, st>>>(a);
+  VHMM_LAUNCH_CHECK();
+  return 0;
+}
+
+#define DISPATCH_K(K, CALL)                                  \
+  switch ((int)(K)) {                                        \
+    case 2: { constexpr int KK = 2; CALL; break; }           \
+    case 3: { constexpr int KK = 3; CALL; break; }           \
+    case 4: { constexpr int KK = 4; CALL; break; }           \
+    default: rc = VHMM_E_DIMS;                               \
+  }
+
+static hs::Args base_args(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths,
+                          int64_t B, int64_t T, int64_t K) {
+  hs::Args a{};
+  a.log_pi = log_pi; a.A = A; a.Bm = Bm; a.lengths = lengths;
+  a.nrows = B; a.T = T; a.rows_per_seq = 1; a.CH = (int)T;
+  const bool tk4 = ((T * K) & 3) == 0;
+  a.vec_in = tk4 && aligned16(A) && aligned16(Bm);
+  a.vec_out = tk4;
+  a.vec_xi = tk4;
+  a.full = 0;
+  return a;
+}
+
+int hmm_forward(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B,
+                int64_t T, int64_t K, float* loglik, float* alpha, cudaStream_t st) {
+  if (small_k(K)) {
+    hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
+    a.loglik = loglik; a.alpha_log = alpha;
+    a.vec_out = a.vec_out && (!alpha || aligned16(alpha));
+    a.full = alpha ? 1 : 0;
+    int rc = 0;
+    DISPATCH_K(K, (rc = launch_fwd_small<KK, true, false>(a, st)));
+    return rc;
+  }
+  const int wpb = 4;
+  hg::fwd_kernel<false><<<(unsigned)cdiv(B, wpb), wpb * 32, 0, st>>>(log_pi, A, Bm, lengths, B, (int)T, (int)K,
+                                                                     loglik, alpha, nullptr, nullptr, nullptr);
+  VHMM_LAUNCH_CHECK();
+  return 0;
+}
+
+int hmm_posterior(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B,
+                  int64_t T, int64_t K, float* loglik, float* gamma, float* xi, void* ws, size_t ws_bytes,
+                  cudaStream_t st) {
+  Arena ar(ws, ws_bytes);
+  float* stash = ar.take<float>((size_t)B * T * K);
+  VHMM_REQUIRE(ar.ok, VHMM_E_WORKSPACE, "hmm_posterior: workspace %zu < %zu", ws_bytes, ar.used);
+  if (small_k(K)) {
+    hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
+    a.loglik = loglik; a.ahat = stash; a.gamma = gamma; a.xi = xi;
+    a.vec_out = a.vec_out && aligned16(stash) && aligned16(gamma);
+    a.vec_xi = a.vec_xi && (!xi || aligned16(xi));
+    int rc = 0;
+    DISPATCH_K(K, (rc = launch_fwd_small<KK, true, false>(a, st)));
+    if (rc) return rc;
+    DISPATCH_K(K, (rc = launch_bwd_small<KK>(a, st)));
+    return rc;
+  }
+  const int wpb = 4;
+  hg::fwd_kernel<false><<<(unsigned)cdiv(B, wpb), wpb * 32, 0, st>>>(log_pi, A, Bm, lengths, B, (int)T, (int)K,
+                                                                     loglik, stash, nullptr, nullptr, nullptr);
+  VHMM_LAUNCH_CHECK();
+  hg::bwd_kernel<<<(unsigned)cdiv(B, wpb), wpb * 32, 0, st>>>(A, Bm, lengths, B, (int)T, (int)K, stash, loglik, gamma, xi);
+  VHMM_LAUNCH_CHECK();
+  return 0;
+}
+
+int hmm_viterbi(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B,
+                int64_t T, int64_t K, uint8_t* path, float* score, void* ws, size_t ws_bytes,
+                cudaStream_t st) {
+  Arena ar(ws, ws_bytes);
+  uint8_t* psi = ar.take<uint8_t>((size_t)B * T * psi_bytes(K));
+  VHMM_REQUIRE(ar.ok, VHMM_E_WORKSPACE, "viterbi: workspace %zu < %zu", ws_bytes, ar.used);
+  if (small_k(K)) {
+    hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
+    a.psi = psi; a.path = path; a.score = score;
+    int rc = 0;
+    DISPATCH_K(K, (rc = launch_fwd_small<KK, false, true>(a, st)));
+    return rc;
+  }
+  const int wpb = 4;
+  hg::fwd_kernel<true><<<(unsigned)cdiv(B, wpb), wpb * 32, 0, st>>>(log_pi, A, Bm, lengths, B, (int)T, (int)K,
+                                                                    nullptr, nullptr, psi, path, score);
+  VHMM_LAUNCH_CHECK();
+  return 0;
+}
+
+int hmm_decode(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B,
+               int64_t T, int64_t K, uint8_t* path, float* gamma, float* loglik, void* ws, size_t ws_bytes,
+               cudaStream_t st) {
+  Arena ar(ws, ws_bytes);
+  float* stash = ar.take<float>((size_t)B * T * K);
+  uint8_t* psi = ar.take<uint8_t>((size_t)B * T * psi_bytes(K));
+  VHMM_REQUIRE(ar.ok, VHMM_E_WORKSPACE, "hmm_decode: workspace %zu < %zu", ws_bytes, ar.used);
+  if (small_k(K)) {
+    // one forward sweep computes alpha_hat AND the Viterbi back-pointers from the same staged
+    // inputs; the backward sweep then produces gamma.
+    hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
+    a.loglik = loglik; a.ahat = stash; a.gamma = gamma; a.xi = nullptr;
+    a.psi = psi; a.path = path; a.score = nullptr;
+    a.vec_out = a.vec_out && aligned16(stash) && aligned16(gamma);
+    int rc = 0;
+    DISPATCH_K(K, (rc = launch_fwd_small<KK, true, true>(a, st)));
+    if (rc) return rc;
+    DISPATCH_K(K, (rc = launch_bwd_small<KK>(a, st)));
+    return rc;
+  }
+  int rc = hmm_viterbi(log_pi, A, Bm, lengths, B, T, K, path, nullptr, psi, (size_t)B * T * psi_bytes(K), st);
+  if (rc) return rc;
+  return hmm_posterior(log_pi, A, Bm, lengths, B, T, K, loglik, gamma, nullptr, stash, (size_t)B * T * K * 4, st);
+}
+
+template <int K>
+static int scan_small(hs::Args a, hs::ScanArgs sa, float* alpha, int64_t B, cudaStream_t st) {
+  using TL = hs::Tile<K, HS_TC, HS_NT>;
+  auto k1 = hs::scan_local_kernel<K, HS_TC, HS_NT>;
+  VHMM_CUDA_CHECK(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TL::SMEM));
+  k1<<<(unsigned)cdiv(a.nrows, HS_NT), HS_NT, TL::SMEM, st>>>(a, sa);
+  VHMM_LAUNCH_CHECK();
+  hs::scan_carry_kernel<K><<<(unsigned)B, 32, 0, st>>>(a, sa);
+  VHMM_LAUNCH_CHECK();
+  if (alpha) {
+    a.vin = sa.vin; a.ll_in = sa.ll_in; a.alpha_log = alpha; a.full = 1; a.loglik = nullptr;
+    return launch_fwd_small<K, true, false>(a, st);
+  }
+  return 0;
+}
+
+int hmm_scan(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B,
+             int64_t T, int64_t K, float* loglik, float* alpha, void* ws, size_t ws_bytes, cudaStream_t st) {
+  if (!small_k(K)) return hmm_forward(log_pi, A, Bm, lengths, B, T, K, loglik, alpha, st);
+  const int64_t nck = cdiv(T, SCAN_CH);
+  Arena ar(ws, ws_bytes);
+  hs::ScanArgs sa{};
+  sa.Pmat = ar.take<float>((size_t)B * nck * K * K);
+  sa.Pscale = ar.take<double>((size_t)B * nck);
+  sa.vin = ar.take<float>((size_t)B * nck * K);
+  sa.ll_in = ar.take<double>((size_t)B * nck);
+  sa.loglik = loglik;
+  VHMM_REQUIRE(ar.ok, VHMM_E_WORKSPACE, "hmm_scan: workspace %zu < %zu", ws_bytes, ar.used);
+  hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
+  a.nrows = B * nck; a.rows_per_seq = (int)nck; a.CH = SCAN_CH;
+  a.vec_out = a.vec_out && (!alpha || aligned16(alpha));
+  int rc = 0;
+  DISPATCH_K(K, (rc = scan_small<KK>(a, sa, alpha, B, st)));
+  return rc;
+}
+
+}  // namespace vhmm

@@ -1,0 +1,216 @@
+// hmm_scan.cuh -- parallel scan over T for long sequences with a small batch.
+//
+// The scan element of step t is the K x K transfer matrix M_t[i,j] = A_t[i,j] * b_t[j]; the
+// log-semiring product (P (x) Q)[i,j] = logsumexp_k(P[i,k] + Q[k,j]) is carried in the scaled
+// representation (P / s, log s): an ordinary matrix product of the normalised factors plus a
+// sum of log-scales -- the same semiring element, but 27 FMA per combine instead of
+// 27 exp + 9 log.  Three phases:
+//   1. scan_local_kernel : one thread per chunk of CH steps -> chunk product (matrix, log-scale)
+//   2. scan_carry_kernel : one warp per sequence: exclusive scan of the chunk products applied
+//                          to alpha_0 -> incoming vector + log-scale of every chunk, loglik
+//   3. hs::fwd_kernel    : (only if all-prefix alpha is requested) re-run each chunk from its
+//                          incoming vector
+#pragma once
+#include "hmm_small.cuh"
+
+namespace vhmm {
+namespace hs {
+
+struct ScanArgs {
+  float* Pmat;       // (nrows, K*K) normalised chunk products
+  double* Pscale;    // (nrows)
+  float* vin;        // (nrows, K)
+  double* ll_in;     // (nrows)
+  float* loglik;     // (B)
+};
+
+// P <- normalise(P * M), *scale += log(sum)
+template <int K>
+__device__ __forceinline__ void matmul_norm(float* P, const float* M, double* scale) {
+  float R[K * K], s = 0.f;
+#pragma unroll
+  for (int i = 0; i < K; ++i)
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+      float acc = 0.f;
+#pragma unroll
+      for (int k = 0; k < K; ++k) acc = fmaf(P[i * K + k], M[k * K + j], acc);
+      R[i * K + j] = acc;
+      s += acc;
+    }
+  const float inv = 1.f / s;
+#pragma unroll
+  for (int i = 0; i < K * K; ++i) P[i] = R[i] * inv;
+  *scale += (double)logf(s);
+}
+
+template <int K, int TC, int NT>
+__global__ void __launch_bounds__(NT) scan_local_kernel(Args a, ScanArgs sa) {
+  using TL = Tile<K, TC, NT>;
+  extern __shared__ __align__(16) float smem[];
+  __shared__ int64_t row_step0[NT];
+  __shared__ int row_n[NT];
+  __shared__ int max_n;
+  const int tid = threadIdx.x;
+  const int64_t r = (int64_t)blockIdx.x * NT + tid;
+  int64_t b = 0;
+  int t_start = 0, n = 0;
+  if (tid == 0) max_n = 0;
+  if (r < a.nrows) {
+    b = r / a.rows_per_seq;
+    t_start = (int)(r - b * a.rows_per_seq) * a.CH;
+    const int cap = (int)min((int64_t)a.CH, a.T - t_start);
+    int64_t L = a.lengths[b];
+    L = L < 0 ? 0 : (L > a.T ? a.T : L);
+    n = (int)max((int64_t)0, min((int64_t)cap, L - t_start));
+  }
+  row_step0[tid] = b * a.T + t_start;
+  row_n[tid] = n;
+  __syncthreads();
+  atomicMax(&max_n, n);
+  __syncthreads();
+  const int nch = (max_n + TC - 1) / TC;
+  float P[K * K];
+#pragma unroll
+  for (int i = 0; i < K * K; ++i) P[i] = (i / K == i % K) ? 1.f / K : 0.f;  // identity / K (sum 1)
+  double scale = 0.0;
+  if (nch > 0) {
+    stage_slab<K, TC, NT>(smem, a, row_step0, row_n, 0);
+    cp_commit();
+  }
+  for (int c = 0; c < nch; ++c) {
+    float* cur = smem + (c & 1) * TL::STAGE;
+    if (c + 1 < nch) stage_slab<K, TC, NT>(smem + ((c + 1) & 1) * TL::STAGE, a, row_step0, row_n, c + 1);
+    cp_commit();
+    cp_wait<1>();
+    __syncthreads();
+    if (r < a.nrows) {
+#pragma unroll
+      for (int g = 0; g < TC / 4; ++g) {
+        const int tl0 = c * TC + g * 4;
+        if (tl0 >= n) break;
+        float Av[4 * K * K], Bv[4 * K];
+        load4<K>(cur + tid * TL::ROW, cur + tid * TL::ROW + TL::PA, g, Av, Bv);
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+          const int tl = tl0 + s;
+          if (tl >= n || (t_start == 0 && tl == 0)) continue;   // step 0 is alpha_0, not a transfer
+          const float* la = Av + s * K * K;
+          const float* lb = Bv + s * K;
+          float mb = lb[0];
+#pragma unroll
+          for (int j = 1; j < K; ++j) mb = fmaxf(mb, lb[j]);
+          float M[K * K];
+#pragma unroll
+          for (int j = 0; j < K; ++j) {
+            const float bj = __expf(lb[j] - mb);
+#pragma unroll
+            for (int i = 0; i < K; ++i) M[i * K + j] = __expf(la[i * K + j]) * bj;
+          }
+          matmul_norm<K>(P, M, &scale);
+          scale += (double)mb;
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (r < a.nrows) {
+#pragma unroll
+    for (int i = 0; i < K * K; ++i) sa.Pmat[r * K * K + i] = P[i];
+    sa.Pscale[r] = scale + log((double)K);  // undo the 1/K of the initial identity
+  }
+}
+
+// one warp per sequence.  Lane l owns chunks [l*per, (l+1)*per).
+template <int K>
+__global__ void __launch_bounds__(32) scan_carry_kernel(Args a, ScanArgs sa) {
+  const int64_t b = blockIdx.x;
+  const int lane = threadIdx.x;
+  const int nck = a.rows_per_seq;
+  const int per = (nck + 31) / 32;
+  const int c_lo = min(lane * per, nck), c_hi = min(c_lo + per, nck);
+  const int64_t row0 = b * nck;
+  // (1) lane-local product of this lane's chunk matrices
+  float Q[K * K];
+#pragma unroll
+  for (int i = 0; i < K * K; ++i) Q[i] = (i / K == i % K) ? 1.f / K : 0.f;
+  double qs = log((double)K);
+  for (int c = c_lo; c < c_hi; ++c) {
+    float M[K * K];
+#pragma unroll
+    for (int i = 0; i < K * K; ++i) M[i] = sa.Pmat[(row0 + c) * K * K + i];
+    matmul_norm<K>(Q, M, &qs);
+    qs += sa.Pscale[row0 + c];
+  }
+  // (2) inclusive Kogge-Stone scan of (Q, qs) across lanes: X_l = Q_0 * ... * Q_l
+  for (int d = 1; d < 32; d <<= 1) {
+    float Pm[K * K];
+#pragma unroll
+    for (int i = 0; i < K * K; ++i) Pm[i] = __shfl_up_sync(0xffffffffu, Q[i], d);
+    const double ps = __shfl_up_sync(0xffffffffu, qs, d);
+    if (lane >= d) {
+      double sc = ps + qs;
+      matmul_norm<K>(Pm, Q, &sc);   // Pm <- Pm * Q  (earlier factors on the left)
+#pragma unroll
+      for (int i = 0; i < K * K; ++i) Q[i] = Pm[i];
+      qs = sc;
+    }
+  }
+  // exclusive prefix for this lane = inclusive of lane-1
+  float X[K * K];
+#pragma unroll
+  for (int i = 0; i < K * K; ++i) X[i] = __shfl_up_sync(0xffffffffu, Q[i], 1);
+  double xs = __shfl_up_sync(0xffffffffu, qs, 1);
+  // alpha_0 (normalised) and its log-scale
+  float v[K];
+  double ll;
+  {
+    float m = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < K; ++j) { v[j] = a.log_pi[j] + a.Bm[b * a.T * K + j]; m = fmaxf(m, v[j]); }
+    float cs = 0.f;
+#pragma unroll
+    for (int j = 0; j < K; ++j) { v[j] = __expf(v[j] - m); cs += v[j]; }
+#pragma unroll
+    for (int j = 0; j < K; ++j) v[j] /= cs;
+    ll = (double)(logf(cs) + m);
+  }
+  const int64_t L = a.lengths[b];
+  if (L <= 0) { if (lane == 0) sa.loglik[b] = 0.f; return; }
+  if (lane > 0) {
+    float w[K], cs = 0.f;
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+      float acc = 0.f;
+#pragma unroll
+      for (int i = 0; i < K; ++i) acc = fmaf(v[i], X[i * K + j], acc);
+      w[j] = acc; cs += acc;
+    }
+#pragma unroll
+    for (int j = 0; j < K; ++j) v[j] = w[j] / cs;
+    ll += xs + (double)logf(cs);
+  }
+  // (3) walk this lane's chunks: record the incoming vector, then apply the chunk product
+  for (int c = c_lo; c < c_hi; ++c) {
+#pragma unroll
+    for (int j = 0; j < K; ++j) sa.vin[(row0 + c) * K + j] = v[j];
+    sa.ll_in[row0 + c] = ll;
+    float w[K], cs = 0.f;
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+      float acc = 0.f;
+#pragma unroll
+      for (int i = 0; i < K; ++i) acc = fmaf(v[i], sa.Pmat[(row0 + c) * K * K + i * K + j], acc);
+      w[j] = acc; cs += acc;
+    }
+#pragma unroll
+    for (int j = 0; j < K; ++j) v[j] = w[j] / cs;
+    ll += sa.Pscale[row0 + c] + (double)logf(cs);
+  }
+  // the lane that owns the last chunk holds the total
+  const int last_lane = (nck - 1) / per;
+  if (lane == last_lane) sa.loglik[b] = (float)ll;
+}
+
+}  // namespace hs
+}  // namespace vhmm

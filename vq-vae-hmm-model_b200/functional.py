@@ -1,0 +1,352 @@
+"""Tensor-level wrappers around the C ABI: pointer plumbing, workspace reuse, and the
+torch.autograd.Function objects (ELBO; exact-HMM log-likelihood whose backward is the
+beta-recursion kernel).  PyTorch is used for device memory, streams and autograd bookkeeping
+only -- every number is produced by libvhmm.so.  No CPU fallback: non-CUDA tensors raise.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import Dims, Params, VhmmError, check
+
+PARAM_ORDER = (
+    "encoder.conv1.weight", "encoder.conv1.bias",
+    "encoder.conv2.weight", "encoder.conv2.bias",
+    "encoder.to_logits.weight", "encoder.to_logits.bias",
+    "prior.log_prior",
+    "prior.transition_net.0.weight", "prior.transition_net.0.bias",
+    "prior.transition_net.2.weight", "prior.transition_net.2.bias",
+    "decoder.embeddings.weight",
+    "decoder.conv1.weight", "decoder.conv1.bias",
+    "decoder.conv2.weight", "decoder.conv2.bias",
+    "decoder.to_params.weight", "decoder.to_params.bias",
+)
+
+_workspaces: Dict[Tuple[int, int], torch.Tensor] = {}
+ELBO_WORKSPACE_CAP = 12 << 30  # bytes: upper bound for the layer-wise path's activation stash
+
+
+def _require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise VhmmError("vhmm ops run on CUDA tensors only (no CPU fallback); got a "
+                            f"{t.device} tensor")
+
+
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _stream(dev) -> ctypes.c_void_p:
+    return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+
+
+def workspace(dev: torch.device, nbytes: int) -> torch.Tensor:
+    """Per-(device, stream) scratch buffer, grown on demand and reused across calls."""
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(),
+           torch.cuda.current_stream(dev).cuda_stream)
+    nbytes = max(int(nbytes), 256)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        _workspaces.pop(key, None)
+        ws = None
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        _workspaces[key] = ws
+    return ws
+
+
+def release_workspaces():
+    _workspaces.clear()
+
+
+def make_dims(C, H, K, H2, U, TH) -> Dims:
+    return Dims(int(C), int(H), int(K), int(H2), int(U), int(TH))
+
+
+def pack_params(tensors: Sequence[torch.Tensor]) -> Tuple[Params, list]:
+    """18 tensors in PARAM_ORDER -> (struct of device pointers, keep-alive list)."""
+    if len(tensors) != _lib.NUM_PARAMS:
+        raise VhmmError(f"expected {_lib.NUM_PARAMS} parameter tensors, got {len(tensors)}")
+    keep = [_f32c(t.detach()) for t in tensors]
+    _require_cuda(*keep)
+    P = Params()
+    for i, t in enumerate(keep):
+        P.p[i] = t.data_ptr()
+    return P, keep
+
+
+def param_count(d: Dims) -> int:
+    return int(_lib.lib().vhmm_param_count(ctypes.byref(d)))
+
+
+def param_offsets(d: Dims):
+    out = (ctypes.c_int64 * (_lib.NUM_PARAMS + 1))()
+    check(_lib.lib().vhmm_param_offsets(ctypes.byref(d), out), "vhmm_param_offsets")
+    return list(out)
+
+
+def _ws_bytes(op, d, B, T) -> int:
+    return int(_lib.lib().vhmm_workspace_bytes(op, ctypes.byref(d) if d is not None else None, B, T))
+
+
+# ---------------------------------------------------------------------------------------
+# pinned path
+# ---------------------------------------------------------------------------------------
+def encoder_fwd(d: Dims, params, x, want_q=False, want_logits=True):
+    x = _f32c(x); _require_cuda(x)
+    B, C, T = x.shape
+    if C != d.C:
+        raise VhmmError(f"encode: expected {d.C} input channels, got {C}")
+    P, keep = pack_params(params)
+    logits = torch.empty(B, d.K, T, device=x.device, dtype=torch.float32) if want_logits else None
+    q = torch.empty(B, d.K, T, device=x.device, dtype=torch.float32) if want_q else None
+    with torch.cuda.device(x.device):
+        ws = workspace(x.device, _ws_bytes(_lib.OP_ENCODER_FWD, d, B, T))
+        check(_lib.lib().vhmm_encoder_fwd(ctypes.byref(d), ctypes.byref(P), _ptr(x), B, T, _ptr(logits), _ptr(q),
+                                          _ptr(ws), ws.numel(), _stream(x.device)), "vhmm_encoder_fwd")
+    return logits, q
+
+
+def prior_fwd(d: Dims, params, u):
+    """u in the (B,U,T) layout."""
+    u = _f32c(u); _require_cuda(u)
+    B, U, T = u.shape
+    if U != d.U:
+        raise VhmmError(f"prior: expected u_dim {d.U}, got {U}")
+    P, keep = pack_params(params)
+    log_pi = torch.empty(d.K, device=u.device, dtype=torch.float32)
+    log_A = torch.empty(B, T, d.K, d.K, device=u.device, dtype=torch.float32)
+    with torch.cuda.device(u.device):
+        ws = workspace(u.device, _ws_bytes(_lib.OP_PRIOR_FWD, d, B, T))
+        check(_lib.lib().vhmm_prior_fwd(ctypes.byref(d), ctypes.byref(P), _ptr(u), B, T, _ptr(log_pi), _ptr(log_A),
+                                        _ptr(ws), ws.numel(), _stream(u.device)), "vhmm_prior_fwd")
+    return log_pi, log_A
+
+
+def decoder_fwd(d: Dims, params, q):
+    q = _f32c(q); _require_cuda(q)
+    B, K, T = q.shape
+    if K != d.K:
+        raise VhmmError(f"decode: expected K={d.K} rows, got {K}")
+    P, keep = pack_params(params)
+    mu = torch.empty(B, d.C, T, device=q.device, dtype=torch.float32)
+    logvar = torch.empty(B, d.C, T, device=q.device, dtype=torch.float32)
+    with torch.cuda.device(q.device):
+        ws = workspace(q.device, _ws_bytes(_lib.OP_DECODER_FWD, d, B, T))
+        check(_lib.lib().vhmm_decoder_fwd(ctypes.byref(d), ctypes.byref(P), _ptr(q), B, T, _ptr(mu), _ptr(logvar),
+                                          _ptr(ws), ws.numel(), _stream(q.device)), "vhmm_decoder_fwd")
+    return mu, logvar
+
+
+def elbo_norms(lengths_dev: torch.Tensor, B: int, C: int, T: int) -> torch.Tensor:
+    """device double[2] = {max(N_valid*C, 1), B}: the reference's normalisers
+    (VQ_VAE_HMM_fixed.py:120, :131, :135) for THIS process's sequences."""
+    nv = lengths_dev.clamp(min=0, max=T).sum().to(torch.float64)
+    return torch.stack([(nv * C).clamp(min=1.0), torch.tensor(float(B), dtype=torch.float64, device=lengths_dev.device)])
+
+
+def elbo_raw(d: Dims, params, x, u, lengths_dev, norms, beta: float, want_grads: bool):
+    """One call of vhmm_elbo.  Returns (sums double[4] on device, flat grads or None)."""
+    x = _f32c(x); u = _f32c(u); _require_cuda(x, u, lengths_dev, norms)
+    B, C, T = x.shape
+    if C != d.C or u.shape != (B, d.U, T):
+        raise VhmmError(f"compute_loss: shape mismatch x{tuple(x.shape)} u{tuple(u.shape)} for dims C={d.C} U={d.U}")
+    if lengths_dev.dtype != torch.int64 or lengths_dev.numel() != B:
+        raise VhmmError("compute_loss: lengths must be int64 of shape (B,)")
+    P, keep = pack_params(params)
+    sums = torch.empty(4, device=x.device, dtype=torch.float64)
+    grads = torch.empty(param_count(d), device=x.device, dtype=torch.float32) if want_grads else None
+    with torch.cuda.device(x.device):
+        need = _ws_bytes(_lib.OP_ELBO, d, B, T)          # enough for min(B,1024) sequences
+        per_seq = max(1, (need // max(1, min(B, 1024))))
+        want = min(ELBO_WORKSPACE_CAP, per_seq * B + (64 << 20))
+        ws = workspace(x.device, max(need, want))
+        check(_lib.lib().vhmm_elbo(ctypes.byref(d), ctypes.byref(P), _ptr(x), _ptr(u), _ptr(lengths_dev), B, T,
+                                   _ptr(norms), float(beta), _ptr(sums), _ptr(grads), _ptr(ws), ws.numel(),
+                                   _stream(x.device)), "vhmm_elbo")
+    return sums, grads
+
+
+def loss_from_sums(sums: torch.Tensor, norms: torch.Tensor, beta: float) -> torch.Tensor:
+    """recon + beta*(prior_loss - entropy) from un-normalised sums (VQ_VAE_HMM_fixed.py:137)."""
+    recon = sums[0] / norms[0]
+    prior_loss = -sums[1] / norms[1]
+    ent = sums[2] / norms[1]
+    return (recon + beta * (prior_loss - ent)).to(torch.float32)
+
+
+class ElboFunction(torch.autograd.Function):
+    """loss = ELBO(x,u,lengths,beta; 18 params).  The gradient is produced by the same
+    library call as the loss (fused forward+backward); backward() only scales it."""
+
+    @staticmethod
+    def forward(ctx, d, x, u, lengths_dev, beta, norms, *params):
+        want = any(p.requires_grad for p in params) and torch.is_grad_enabled()
+        sums, grads = elbo_raw(d, params, x, u, lengths_dev, norms, beta, want)
+        ctx.has_grads = grads is not None
+        ctx.shapes = [tuple(p.shape) for p in params]
+        ctx.offsets = param_offsets(d)
+        ctx.save_for_backward(grads if grads is not None else sums)
+        ctx.mark_non_differentiable(sums)
+        return loss_from_sums(sums, norms, beta), sums
+
+    @staticmethod
+    def backward(ctx, gout, _gsums):
+        if not ctx.has_grads:
+            raise VhmmError("ELBO gradients were not computed (forward ran without grad)")
+        (flat,) = ctx.saved_tensors
+        flat = flat * gout.to(flat.dtype)
+        outs = []
+        for i, shp in enumerate(ctx.shapes):
+            outs.append(flat[ctx.offsets[i]:ctx.offsets[i + 1]].view(shp))
+        return (None, None, None, None, None, None, *outs)
+
+
+def argmax_regimes(q):
+    q = _f32c(q); _require_cuda(q)
+    B, K, T = q.shape
+    out = torch.empty(B, T, device=q.device, dtype=torch.int64)
+    with torch.cuda.device(q.device):
+        check(_lib.lib().vhmm_argmax_regimes(_ptr(q), B, K, T, _ptr(out), _stream(q.device)), "vhmm_argmax_regimes")
+    return out
+
+
+# ---------------------------------------------------------------------------------------
+# exact-HMM stages (extensions)
+# ---------------------------------------------------------------------------------------
+def emission_table(d: Dims, params, T: int, device):
+    P, keep = pack_params(params)
+    mu = torch.empty(d.K, d.C, T, device=device, dtype=torch.float32)
+    lv = torch.empty(d.K, d.C, T, device=device, dtype=torch.float32)
+    with torch.cuda.device(device):
+        ws = workspace(mu.device, _ws_bytes(_lib.OP_EMISSION_TABLE, d, d.K, T))
+        check(_lib.lib().vhmm_emission_table(ctypes.byref(d), ctypes.byref(P), T, _ptr(mu), _ptr(lv), _ptr(ws),
+                                             ws.numel(), _stream(mu.device)), "vhmm_emission_table")
+    return mu, lv
+
+
+def emission_logprob(x, mu_tab, logvar_tab):
+    x = _f32c(x); mu_tab = _f32c(mu_tab); logvar_tab = _f32c(logvar_tab); _require_cuda(x, mu_tab, logvar_tab)
+    B, C, T = x.shape
+    K = mu_tab.shape[0]
+    out = torch.empty(B, T, K, device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device):
+        check(_lib.lib().vhmm_emission_logprob(_ptr(x), _ptr(mu_tab), _ptr(logvar_tab), B, C, T, K, _ptr(out),
+                                               _stream(x.device)), "vhmm_emission_logprob")
+    return out
+
+
+def _hmm_inputs(log_pi, log_A, log_b, lengths):
+    log_pi = _f32c(log_pi); log_A = _f32c(log_A); log_b = _f32c(log_b)
+    _require_cuda(log_pi, log_A, log_b)
+    B, T, K = log_b.shape
+    if log_A.shape != (B, T, K, K) or log_pi.shape != (K,):
+        raise VhmmError(f"hmm: shape mismatch log_pi{tuple(log_pi.shape)} log_A{tuple(log_A.shape)} log_b{tuple(log_b.shape)}")
+    if lengths is None:
+        lengths = torch.full((B,), T, dtype=torch.int64, device=log_b.device)
+    lengths = lengths.to(device=log_b.device, dtype=torch.int64).contiguous()
+    return log_pi, log_A, log_b, lengths, B, T, K
+
+
+def hmm_forward(log_pi, log_A, log_b, lengths=None, want_alpha=False):
+    log_pi, log_A, log_b, lengths, B, T, K = _hmm_inputs(log_pi, log_A, log_b, lengths)
+    ll = torch.empty(B, device=log_b.device, dtype=torch.float32)
+    alpha = torch.empty(B, T, K, device=log_b.device, dtype=torch.float32) if want_alpha else None
+    with torch.cuda.device(log_b.device):
+        check(_lib.lib().vhmm_hmm_forward(_ptr(log_pi), _ptr(log_A), _ptr(log_b), _ptr(lengths), B, T, K, _ptr(ll),
+                                          _ptr(alpha), _stream(log_b.device)), "vhmm_hmm_forward")
+    return (ll, alpha) if want_alpha else ll
+
+
+def hmm_posterior(log_pi, log_A, log_b, lengths=None, want_xi=True):
+    log_pi, log_A, log_b, lengths, B, T, K = _hmm_inputs(log_pi, log_A, log_b, lengths)
+    dev = log_b.device
+    ll = torch.empty(B, device=dev, dtype=torch.float32)
+    gamma = torch.empty(B, T, K, device=dev, dtype=torch.float32)
+    xi = torch.empty(B, T, K, K, device=dev, dtype=torch.float32) if want_xi else None
+    dk = Dims(1, 1, K, 1, 1, 1)
+    with torch.cuda.device(dev):
+        ws = workspace(dev, _ws_bytes(_lib.OP_HMM_POSTERIOR, dk, B, T))
+        check(_lib.lib().vhmm_hmm_posterior(_ptr(log_pi), _ptr(log_A), _ptr(log_b), _ptr(lengths), B, T, K, _ptr(ll),
+                                            _ptr(gamma), _ptr(xi), _ptr(ws), ws.numel(), _stream(dev)),
+              "vhmm_hmm_posterior")
+    return ll, gamma, xi
+
+
+def viterbi(log_pi, log_A, log_b, lengths=None):
+    log_pi, log_A, log_b, lengths, B, T, K = _hmm_inputs(log_pi, log_A, log_b, lengths)
+    dev = log_b.device
+    path = torch.empty(B, T, device=dev, dtype=torch.uint8)
+    score = torch.empty(B, device=dev, dtype=torch.float32)
+    dk = Dims(1, 1, K, 1, 1, 1)
+    with torch.cuda.device(dev):
+        ws = workspace(dev, _ws_bytes(_lib.OP_VITERBI, dk, B, T))
+        check(_lib.lib().vhmm_viterbi(_ptr(log_pi), _ptr(log_A), _ptr(log_b), _ptr(lengths), B, T, K, _ptr(path),
+                                      _ptr(score), _ptr(ws), ws.numel(), _stream(dev)), "vhmm_viterbi")
+    return path, score
+
+
+def hmm_decode(log_pi, log_A, log_b, lengths=None):
+    """Viterbi path + posterior gamma + loglik from one forward sweep (cfg 3)."""
+    log_pi, log_A, log_b, lengths, B, T, K = _hmm_inputs(log_pi, log_A, log_b, lengths)
+    dev = log_b.device
+    path = torch.empty(B, T, device=dev, dtype=torch.uint8)
+    gamma = torch.empty(B, T, K, device=dev, dtype=torch.float32)
+    ll = torch.empty(B, device=dev, dtype=torch.float32)
+    dk = Dims(1, 1, K, 1, 1, 1)
+    with torch.cuda.device(dev):
+        ws = workspace(dev, _ws_bytes(_lib.OP_HMM_DECODE, dk, B, T))
+        check(_lib.lib().vhmm_hmm_decode(_ptr(log_pi), _ptr(log_A), _ptr(log_b), _ptr(lengths), B, T, K, _ptr(path),
+                                         _ptr(gamma), _ptr(ll), _ptr(ws), ws.numel(), _stream(dev)), "vhmm_hmm_decode")
+    return path, gamma, ll
+
+
+def hmm_scan(log_pi, log_A, log_b, lengths=None, want_alpha=False):
+    log_pi, log_A, log_b, lengths, B, T, K = _hmm_inputs(log_pi, log_A, log_b, lengths)
+    dev = log_b.device
+    ll = torch.empty(B, device=dev, dtype=torch.float32)
+    alpha = torch.empty(B, T, K, device=dev, dtype=torch.float32) if want_alpha else None
+    dk = Dims(1, 1, K, 1, 1, 1)
+    with torch.cuda.device(dev):
+        ws = workspace(dev, _ws_bytes(_lib.OP_HMM_SCAN, dk, B, T))
+        check(_lib.lib().vhmm_hmm_scan(_ptr(log_pi), _ptr(log_A), _ptr(log_b), _ptr(lengths), B, T, K, _ptr(ll),
+                                       _ptr(alpha), _ptr(ws), ws.numel(), _stream(dev)), "vhmm_hmm_scan")
+    return (ll, alpha) if want_alpha else ll
+
+
+class HmmLogLikFunction(torch.autograd.Function):
+    """loglik[b] of the exact HMM (B.2); backward is the beta-recursion kernel (B.3):
+    d loglik / d log_b = gamma, d loglik / d log_A = xi, d loglik / d log_pi = sum_b gamma[b,0]."""
+
+    @staticmethod
+    def forward(ctx, log_pi, log_A, log_b, lengths):
+        need = log_pi.requires_grad or log_A.requires_grad or log_b.requires_grad
+        if need and torch.is_grad_enabled():
+            ll, gamma, xi = hmm_posterior(log_pi, log_A, log_b, lengths, want_xi=True)
+            ctx.save_for_backward(gamma, xi)
+            ctx.ok = True
+        else:
+            ll = hmm_forward(log_pi, log_A, log_b, lengths)
+            ctx.ok = False
+        return ll
+
+    @staticmethod
+    def backward(ctx, g):
+        if not ctx.ok:
+            raise VhmmError("hmm log-likelihood gradients were not computed")
+        gamma, xi = ctx.saved_tensors
+        g = g.to(gamma.dtype)
+        g_b = gamma * g[:, None, None]
+        g_A = xi * g[:, None, None, None]
+        g_pi = g_b[:, 0, :].sum(dim=0)
+        return g_pi, g_A, g_b, None

@@ -1,0 +1,65 @@
+"""Batch sharding across the GPUs of one box: one process per GPU, sequences
+partitioned, parameters replicated, NO communication inside any kernel, and exactly one NCCL
+all-reduce per step over [flat gradients || loss sums] after a tiny all-reduce of the two
+normalisers.  The sharded loss equals the un-sharded loss of the concatenated batch (the
+reference divides the reconstruction term by the GLOBAL valid count, VQ_VAE_HMM_fixed.py:120)."""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from . import functional as Fn
+
+
+class _ShardedElbo(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, model, x, u, lengths_dev, beta, norms_local, group, *params):
+        d = model._dims
+        # global normalisers: sum of valid steps * C and of batch sizes over ranks
+        C = x.shape[1]
+        nv = lengths_dev.clamp(min=0, max=x.shape[2]).sum().to(torch.float64)
+        cnt = torch.stack([nv * C, norms_local[1]])
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
+        norms = torch.stack([cnt[0].clamp(min=1.0), cnt[1]])
+        want = any(p.requires_grad for p in params) and torch.is_grad_enabled()
+        sums, grads = Fn.elbo_raw(d, params, x, u, lengths_dev, norms, beta, want)
+        # one all-reduce: grads (fp32) followed by the sums split into hi/lo floats
+        hi = sums.to(torch.float32)
+        lo = (sums - hi.to(torch.float64)).to(torch.float32)
+        parts = ([grads] if grads is not None else []) + [hi, lo]
+        flat = torch.cat(parts)
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+        n = grads.numel() if grads is not None else 0
+        gsums = flat[n:n + 4].to(torch.float64) + flat[n + 4:n + 8].to(torch.float64)
+        ctx.has_grads = grads is not None
+        ctx.shapes = [tuple(p.shape) for p in params]
+        ctx.offsets = Fn.param_offsets(d)
+        ctx.save_for_backward(flat[:n] if n else gsums)
+        return Fn.loss_from_sums(gsums, norms, beta)
+
+    @staticmethod
+    def backward(ctx, gout):
+        (flat,) = ctx.saved_tensors
+        if not ctx.has_grads:
+            raise Fn.VhmmError("ELBO gradients were not computed")
+        flat = flat * gout.to(flat.dtype)
+        outs = [flat[ctx.offsets[i]:ctx.offsets[i + 1]].view(s) for i, s in enumerate(ctx.shapes)]
+        return (None, None, None, None, None, None, None, *outs)
+
+
+def sharded_elbo(model, x, u, lengths_dev, beta, norms_local, group=None):
+    """Global loss (identical on every rank) whose backward leaves the GLOBAL gradient in .grad."""
+    return _ShardedElbo.apply(model, x, u, lengths_dev, beta, norms_local, group, *model._params())
+
+
+def shard_batch(x, u, lengths, rank, world):
+    """Contiguous split of the batch dimension: rank g gets [g*B/G, (g+1)*B/G)."""
+    B = x.shape[0]
+    lo, hi = (B * rank) // world, (B * (rank + 1)) // world
+    return x[lo:hi], u[lo:hi], lengths[lo:hi]
+
+
+def enable_sharding(model, group=None):
+    """After this, model.compute_loss() returns the global loss / leaves global gradients."""
+    model.shard_group = group if group is not None else dist.group.WORLD
+    return model
