@@ -1,0 +1,261 @@
+#!/usr/bin/env python3
+"""bench.py -- sequence-steps/s of the VAE_HMM ELBO forward+backward (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo (CUDA, sm_100a)
+    python bench.py --impl reference --steps K --warmup W    # the reference's CPU PyTorch path
+                                                             # (oracle port) on the host cores
+Under torchrun (N>1) every rank runs the same per-GPU workload (weak scaling: the batch is
+sharded, B_local sequences per GPU) and the step contains the one NCCL all-reduce of
+[gradients || loss sums]; rank 0 prints ONE JSON line.
+
+Workload = BASELINE.json configs[1]: VAE_HMM(input_dim=5, hidden_dim=64, K=3, hidden_dim2=32,
+u_dim=4), synthetic B=65536 T=512 fp32, one step = compute_loss(...).backward() over the batch.
+`value` is measured with inputs resident in HBM; `e2e` through the public API from pinned HOST
+buffers (H2D of x,u,lengths and D2H of the loss inside the timed region).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+MODEL = dict(C=5, H=64, K=3, H2=32, U=4, TH=128)
+FLOP_PER_STEP = 205740          # algorithmic fwd+bwd FLOPs per sequence-step (base)
+BYTES_PER_STEP = 72             # x,u read once forward and once backward
+FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12   # FFMA peak at max SM clock (derived)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], bf16=d.get("bf16_tflops_sustained", d["bf16_tflops"]), src="measured")
+    return dict(hbm=6650.0, bf16=1400.0, src="fallback")
+
+
+class ClockSampler:
+    """samples SM clock / throttle reasons of one GPU during the timed region"""
+
+    def __init__(self, index):
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40,
+                 "sw_thermal_slowdown": 0x20, "hw_power_brake": 0x80}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def start(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join()
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def cpu_reference_step_rate(B_cpu, T, steps, warmup, threads=None):
+    """The reference's CPU PyTorch path (oracle/elbo.py restates it op for op) timed on the host
+    cores: compute_loss + backward on a bounded sample of the workload."""
+    import torch
+    from oracle import elbo as O
+    n = threads or os.cpu_count() or 1
+    torch.set_num_threads(n)
+    p = O.init_params(MODEL["C"], MODEL["H"], MODEL["K"], MODEL["H2"], MODEL["U"], MODEL["TH"], seed=0)
+    x, u, L = O.synth_batch(B_cpu, MODEL["C"], MODEL["U"], T, seed=1234, ragged=False)
+    for _ in range(warmup):
+        O.loss_and_grads(p, x, u, L, MODEL["U"], 1.0)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        O.loss_and_grads(p, x, u, L, MODEL["U"], 1.0)
+    dt = (time.perf_counter() - t0) / steps
+    return B_cpu * T / dt, dt, n
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    B_cpu, T = args.cpu_batch, args.T
+    rate, dt, n = cpu_reference_step_rate(B_cpu, T, args.steps, args.warmup)
+    sample = f"B={B_cpu} of {args.B} sequences, T={T}, compute_loss+backward, torch CPU fp32"
+    line = {
+        "impl": "reference", "metric": "sequence-steps/sec for ELBO fwd+bwd", "value": rate,
+        "unit": "sequence-steps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"cfg2: VAE_HMM(5,64,K=3,32,u_dim=4) ELBO fwd+bwd B={args.B} T={T} (CPU sample B={B_cpu})"},
+        "cpu_baseline": {"value": rate, "unit": "sequence-steps/s", "cores": n, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": "sequence-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--B", type=int, default=65536, help="sequences per GPU")
+    ap.add_argument("--T", type=int, default=512)
+    ap.add_argument("--cpu-batch", type=int, default=512, help="sequences in the CPU baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    import vhmm_b200 as V
+    from vhmm_b200 import functional as Fn
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, T, W, K = args.B, args.T, max(args.warmup, 3), args.steps
+
+    torch.manual_seed(0)
+    model = V.VAE_HMM(MODEL["C"], MODEL["H"], MODEL["K"], MODEL["H2"], u_dim=MODEL["U"]).to(dev)
+    if world > 1:
+        V.parallel.enable_sharding(model)
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    x = torch.randn(B, MODEL["C"], T, device=dev, generator=g)
+    u = torch.randn(B, MODEL["U"], T, device=dev, generator=g)
+    lengths_cpu = torch.full((B,), T, dtype=torch.int64)
+    lengths = lengths_cpu.to(dev)
+    xh = torch.empty(x.shape, pin_memory=True); xh.copy_(x)
+    uh = torch.empty(u.shape, pin_memory=True); uh.copy_(u)
+    lh = lengths_cpu.pin_memory()
+    beta = 1.0
+
+    def step_resident():
+        model.zero_grad(set_to_none=True)
+        loss = model.compute_loss(x, u, lengths, beta)
+        loss.backward()
+        return loss
+
+    xd, ud = torch.empty_like(x), torch.empty_like(u)
+
+    def step_e2e():
+        xd.copy_(xh, non_blocking=True)
+        ud.copy_(uh, non_blocking=True)
+        ld = lh.to(dev, non_blocking=True)
+        model.zero_grad(set_to_none=True)
+        loss = model.compute_loss(xd, ud, ld, beta)
+        loss.backward()
+        return loss.item()            # D2H of the step's result, every step
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            out = fn()
+        e1.record()
+        sync_all()
+        ms = e0.elapsed_time(e1) / steps
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        return ms, out
+
+    for _ in range(W):
+        step_resident()
+    launches0 = V.lib().vhmm_launch_count()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms, loss = timed(step_resident, K)
+    clocks = sampler.stop()
+    launches = (V.lib().vhmm_launch_count() - launches0) // K
+    value = world * B * T / (ms * 1e-3)
+
+    for _ in range(2):
+        step_e2e()
+    ms_e2e, _ = timed(step_e2e, K)
+    e2e_value = world * B * T / (ms_e2e * 1e-3)
+    h2d = xh.numel() * 4 + uh.numel() * 4 + lh.numel() * 8
+    loss_val = float(loss)
+
+    pk = peaks()
+    per_gpu_steps = B * T
+    tfl = per_gpu_steps * FLOP_PER_STEP / (ms * 1e-3) / 1e12
+    gbs = per_gpu_steps * BYTES_PER_STEP / (ms * 1e-3) / 1e9
+    roofline = {
+        "kernel": "ELBO fwd+bwd step (all launches of one vhmm_elbo call)",
+        "bound": "fp32", "achieved": tfl, "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s",
+        "frac": tfl / FP32_PEAK_TFLOPS, "traffic": None,
+        "peak_source": "derived FFMA peak 148 SM x 128 lanes x 2 x 1.965 GHz; path computes in fp32 FFMA",
+        "flop_per_step": FLOP_PER_STEP,
+        "hbm": {"achieved": gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
+                "bytes_per_step": BYTES_PER_STEP, "peak_source": pk["src"]},
+        "tensor": {"achieved": tfl, "peak": pk["bf16"], "unit": "TFLOP/s", "frac": tfl / pk["bf16"],
+                   "peak_source": pk["src"] + " bf16 dense (context only; path is fp32)"},
+    }
+    line = {
+        "metric": "sequence-steps/sec for ELBO fwd+bwd", "value": value, "unit": "sequence-steps/s",
+        "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"cfg2: VAE_HMM(5,64,K=3,32,u_dim=4) ELBO fwd+bwd, B={B} per GPU x {world} GPU, T={T}, lengths=T",
+                   "parallelism": f"batch-sharded x{world}, 1 NCCL all-reduce/step" if world > 1 else "single GPU",
+                   "l2": "inputs (1.2 GB/GPU) larger than L2; no flush needed"},
+        "e2e": {"value": e2e_value, "unit": "sequence-steps/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
+        "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "loss": loss_val,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        rate, dt, n = cpu_reference_step_rate(args.cpu_batch, T, 3, 1)
+        line["cpu_baseline"] = {"value": rate, "unit": "sequence-steps/s", "cores": n, "kind": "port",
+                                "sample": f"B={args.cpu_batch} of {B} sequences, T={T}, 3 timed iterations of the oracle port (torch CPU fp32) of compute_loss+backward"}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

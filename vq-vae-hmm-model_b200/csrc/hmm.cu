@@ -120,7 +120,7 @@ int hmm_forward(const float* log_pi, const float* A, const float* Bm, const int6
   }
   const int wpb = 4;
   hg::fwd_kernel<false><<<(unsigned)cdiv(B, wpb), wpb * 32, 0, st>>>(log_pi, A, Bm, lengths, B, (int)T, (int)K,
-                                                                     loglik, alpha, nullptr, nullptr, nullptr);
+                                                                     loglik, alpha, 0, nullptr, nullptr, nullptr);
   VHMM_LAUNCH_CHECK();
   return 0;
 }
@@ -144,9 +144,9 @@ int hmm_posterior(const float* log_pi, const float* A, const float* Bm, const in
   }
   const int wpb = 4;
   hg::fwd_kernel<false><<<(unsigned)cdiv(B, wpb), wpb * 32, 0, st>>>(log_pi, A, Bm, lengths, B, (int)T, (int)K,
-                                                                     loglik, stash, nullptr, nullptr, nullptr);
+                                                                     loglik, stash, 1, nullptr, nullptr, nullptr);
   VHMM_LAUNCH_CHECK();
-  hg::bwd_kernel<<<(unsigned)cdiv(B, wpb), wpb * 32, 0, st>>>(A, Bm, lengths, B, (int)T, (int)K, stash, loglik, gamma, xi);
+  hg::bwd_kernel<<<(unsigned)cdiv(B, wpb), wpb * 32, 0, st>>>(A, Bm, lengths, B, (int)T, (int)K, stash, gamma, xi);
   VHMM_LAUNCH_CHECK();
   return 0;
 }
@@ -166,7 +166,7 @@ int hmm_viterbi(const float* log_pi, const float* A, const float* Bm, const int6
   }
   const int wpb = 4;
   hg::fwd_kernel<true><<<(unsigned)cdiv(B, wpb), wpb * 32, 0, st>>>(log_pi, A, Bm, lengths, B, (int)T, (int)K,
-                                                                    nullptr, nullptr, psi, path, score);
+                                                                    nullptr, nullptr, 0, psi, path, score);
   VHMM_LAUNCH_CHECK();
   return 0;
 }
@@ -191,9 +191,11 @@ int hmm_decode(const float* log_pi, const float* A, const float* Bm, const int64
     DISPATCH_K(K, (rc = launch_bwd_small<KK>(a, st)));
     return rc;
   }
-  int rc = hmm_viterbi(log_pi, A, Bm, lengths, B, T, K, path, nullptr, psi, (size_t)B * T * psi_bytes(K), st);
+  int rc = hmm_viterbi(log_pi, A, Bm, lengths, B, T, K, path, nullptr, psi,
+                       align_up((size_t)B * T * psi_bytes(K), 256), st);
   if (rc) return rc;
-  return hmm_posterior(log_pi, A, Bm, lengths, B, T, K, loglik, gamma, nullptr, stash, (size_t)B * T * K * 4, st);
+  return hmm_posterior(log_pi, A, Bm, lengths, B, T, K, loglik, gamma, nullptr, stash,
+                       align_up((size_t)B * T * K * 4, 256), st);
 }
 
 template <int K>

@@ -28,7 +28,7 @@ template <bool VIT>
 __global__ void __launch_bounds__(128)
 fwd_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const float* __restrict__ Bm,
            const int64_t* __restrict__ lengths, int64_t nB, int T, int K, float* __restrict__ loglik,
-           float* __restrict__ alpha, uint8_t* __restrict__ psi, uint8_t* __restrict__ path,
+           float* __restrict__ alpha, int stash, uint8_t* __restrict__ psi, uint8_t* __restrict__ path,
            float* __restrict__ score) {
   const int lane = threadIdx.x & 31;
   const int64_t b = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -38,9 +38,18 @@ fwd_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const 
   const bool on = lane < K;
   const float* Ab = A + b * (int64_t)T * K * K;
   const float* Bb = Bm + b * (int64_t)T * K;
+  // sum-product: `al` holds the NORMALISED log forward variable (logsumexp_k al = 0) and `ll`
+  // the running log normaliser in double, so magnitudes stay O(10) and fp32 keeps ~1e-7.
+  // `stash` != 0 stores the normalised values (for bwd_kernel), else alpha = al + ll (B.2).
   float al = -INFINITY;
+  double ll = 0.0;
   if (L > 0 && on) al = log_pi[lane] + Bb[lane];
-  if (!VIT && alpha && on && L > 0) alpha[(b * T) * K + lane] = al;
+  if (!VIT && L > 0) {
+    const float z = warp_lse(on ? al : -INFINITY);
+    al -= z;
+    ll = (double)z;
+    if (alpha && on) alpha[(b * T) * K + lane] = stash ? al : al + z;
+  }
   for (int t = 1; t < L; ++t) {
     const float* At = Ab + (int64_t)t * K * K;
     float nv;
@@ -57,7 +66,10 @@ fwd_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const 
         if (on) s += expf(ai + At[i * K + lane] - mm);
       }
       nv = on ? Bb[(int64_t)t * K + lane] + mm + logf(s) : -INFINITY;
-      if (alpha && on) alpha[(b * T + t) * K + lane] = nv;
+      const float z = warp_lse(nv);
+      nv -= z;
+      ll += (double)z;
+      if (alpha && on) alpha[(b * T + t) * K + lane] = stash ? nv : nv + (float)ll;
     } else {
       float best = -INFINITY;
       int arg = 0;
@@ -74,11 +86,10 @@ fwd_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const 
     al = nv;
   }
   if (!VIT) {
-    const float ll = warp_lse(on ? al : -INFINITY);
-    if (lane == 0 && loglik) loglik[b] = (L > 0) ? ll : 0.f;
+    if (lane == 0 && loglik) loglik[b] = (L > 0) ? (float)ll : 0.f;
     // carried values for t >= L (oracle.forward keeps alpha unchanged)
-    if (alpha && on)
-      for (int t = (L > 0 ? L : 0); t < T; ++t) alpha[(b * T + t) * K + lane] = al;
+    if (alpha && on && !stash)
+      for (int t = (L > 0 ? L : 0); t < T; ++t) alpha[(b * T + t) * K + lane] = al + (float)ll;
   } else {
     // final state: lowest index attaining the max
     const float v = on ? al : -INFINITY;
@@ -102,7 +113,7 @@ fwd_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const 
 // backward recursion with gamma / xi from the log-space alpha stash
 __global__ void __launch_bounds__(128)
 bwd_kernel(const float* __restrict__ A, const float* __restrict__ Bm, const int64_t* __restrict__ lengths,
-           int64_t nB, int T, int K, const float* __restrict__ alpha, const float* __restrict__ loglik,
+           int64_t nB, int T, int K, const float* __restrict__ alpha /* normalised stash */,
            float* __restrict__ gamma, float* __restrict__ xi) {
   const int lane = threadIdx.x & 31;
   const int64_t b = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -112,7 +123,6 @@ bwd_kernel(const float* __restrict__ A, const float* __restrict__ Bm, const int6
   const bool on = lane < K;
   const float* Ab = A + b * (int64_t)T * K * K;
   const float* Bb = Bm + b * (int64_t)T * K;
-  const float ll = loglik[b];
   for (int t = T - 1; t >= L; --t) {
     if (on) gamma[(b * T + t) * K + lane] = 0.f;
     if (xi) for (int e = lane; e < K * K; e += 32) xi[(b * T + t) * (int64_t)K * K + e] = 0.f;
@@ -120,7 +130,11 @@ bwd_kernel(const float* __restrict__ A, const float* __restrict__ Bm, const int6
   float be = on ? 0.f : -INFINITY;   // beta_{L-1} = 0
   for (int t = L - 1; t >= 0; --t) {
     const float at = on ? alpha[(b * T + t) * K + lane] : -INFINITY;
-    if (on) gamma[(b * T + t) * K + lane] = expf(at + be - ll);
+    {
+      const float gl = on ? at + be : -INFINITY;
+      const float zg = warp_lse(gl);
+      if (on) gamma[(b * T + t) * K + lane] = expf(gl - zg);
+    }
     if (t == 0) {
       if (xi) for (int e = lane; e < K * K; e += 32) xi[(b * T) * (int64_t)K * K + e] = 0.f;
       break;
@@ -130,9 +144,21 @@ bwd_kernel(const float* __restrict__ A, const float* __restrict__ Bm, const int6
     const float ap = on ? alpha[(b * T + t - 1) * K + lane] : -INFINITY;  // alpha_{t-1}[i], lane = i
     // xi_t[i,j]: lane = j, loop i
     if (xi) {
+      float mx = -INFINITY;
       for (int i = 0; i < K; ++i) {
         const float ai = __shfl_sync(0xffffffffu, ap, i);
-        if (on) xi[((b * T + t) * (int64_t)K + i) * K + lane] = expf(ai + At[i * K + lane] + w - ll);
+        if (on) mx = fmaxf(mx, ai + At[i * K + lane]);
+      }
+      const float mmx = (mx == -INFINITY) ? 0.f : mx;
+      float sx = 0.f;
+      for (int i = 0; i < K; ++i) {
+        const float ai = __shfl_sync(0xffffffffu, ap, i);
+        if (on) sx += expf(ai + At[i * K + lane] - mmx);
+      }
+      const float zx = warp_lse(on ? mmx + logf(sx) + w : -INFINITY);   // log sum_ij of xi terms
+      for (int i = 0; i < K; ++i) {
+        const float ai = __shfl_sync(0xffffffffu, ap, i);
+        if (on) xi[((b * T + t) * (int64_t)K + i) * K + lane] = expf(ai + At[i * K + lane] + w - zx);
       }
     }
     // beta_{t-1}[i] = lse_j(A[i,j] + w[j]): lane = i reads row i
@@ -148,6 +174,7 @@ bwd_kernel(const float* __restrict__ A, const float* __restrict__ Bm, const int6
       if (on) s += expf(At[lane * K + j] + wj - mm);
     }
     be = on ? mm + logf(s) : -INFINITY;
+    be -= warp_lse(be);   // keep beta normalised too (gamma / xi are renormalised per step)
   }
 }
 

@@ -191,7 +191,7 @@ class ElboFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, d, x, u, lengths_dev, beta, norms, *params):
-        want = any(p.requires_grad for p in params) and torch.is_grad_enabled()
+        want = any(ctx.needs_input_grad)   # (grad mode is always off inside forward)
         sums, grads = elbo_raw(d, params, x, u, lengths_dev, norms, beta, want)
         ctx.has_grads = grads is not None
         ctx.shapes = [tuple(p.shape) for p in params]
@@ -330,8 +330,7 @@ class HmmLogLikFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, log_pi, log_A, log_b, lengths):
-        need = log_pi.requires_grad or log_A.requires_grad or log_b.requires_grad
-        if need and torch.is_grad_enabled():
+        if any(ctx.needs_input_grad):
             ll, gamma, xi = hmm_posterior(log_pi, log_A, log_b, lengths, want_xi=True)
             ctx.save_for_backward(gamma, xi)
             ctx.ok = True

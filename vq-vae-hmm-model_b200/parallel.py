@@ -21,7 +21,7 @@ class _ShardedElbo(torch.autograd.Function):
         cnt = torch.stack([nv * C, norms_local[1]])
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
         norms = torch.stack([cnt[0].clamp(min=1.0), cnt[1]])
-        want = any(p.requires_grad for p in params) and torch.is_grad_enabled()
+        want = any(ctx.needs_input_grad)
         sums, grads = Fn.elbo_raw(d, params, x, u, lengths_dev, norms, beta, want)
         # one all-reduce: grads (fp32) followed by the sums split into hi/lo floats
         hi = sums.to(torch.float32)
