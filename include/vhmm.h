@@ -119,6 +119,19 @@ int vhmm_elbo(const vhmm_dims* dims, const vhmm_params* params, const float* x, 
               const int64_t* lengths, int64_t B, int64_t T, const double* norms, double beta,
               double* sums, float* grads, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Two implementations of vhmm_elbo share the signature above:
+ *   VHMM_ELBO_LAYERWISE  one kernel per layer, activations stashed in the workspace; any dims.
+ *   VHMM_ELBO_FUSED      three recompute-in-tile tensor-core kernels, no activation in HBM; needs
+ *                        H%32==0, H2%16==0, TH%32==0, C,U,K<=8 (instantiated for the reference's
+ *                        base config C=5,H=64,H2=32,K=3,U=4,TH=128).
+ * VHMM_ELBO_AUTO (default) picks FUSED when the dims allow it; the environment variable
+ * VHMM_ELBO_IMPL=layerwise|fused overrides AUTO.  vhmm_workspace_bytes(VHMM_OP_ELBO, ...) follows
+ * the active choice; for FUSED it is an exact requirement (a larger workspace is not used). */
+enum { VHMM_ELBO_AUTO = 0, VHMM_ELBO_LAYERWISE = 1, VHMM_ELBO_FUSED = 2 };
+int vhmm_elbo_select(int impl);
+/* the implementation vhmm_elbo would run for `dims` now (VHMM_ELBO_LAYERWISE / VHMM_ELBO_FUSED) */
+int vhmm_elbo_active_impl(const vhmm_dims* dims);
+
 /* argmax regime decoding (backtesting.py:155, src/backtesting.py:107): q or logits (B,K,T) ->
  * regimes int64 (B,T), lowest index on ties. */
 int vhmm_argmax_regimes(const float* q, int64_t B, int64_t K, int64_t T, int64_t* regimes,

@@ -116,7 +116,7 @@ def loss_terms(p, x, u, lengths, U: int) -> Tuple[torch.Tensor, torch.Tensor, to
     B, C, T = x.shape
     if lengths is None:
         raise ValueError("lengths required")
-    valid = torch.arange(T)[None, :] < lengths[:, None]                      # :111
+    valid = torch.arange(T, device=x.device)[None, :] < lengths.to(x.device)[:, None]   # :111
     log_pi, log_A = prior(p, u, U)                                           # :112
     logits = encode(p, x)                                                    # :113
     q = F.softmax(logits, dim=1)                                             # :114

@@ -13,6 +13,16 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-5
 
 
+@pytest.fixture(autouse=True, scope="module", params=["fused", "layerwise"])
+def elbo_impl(request):
+    """Every test of this module runs against both vhmm_elbo implementations (include/vhmm.h):
+    the fused tensor-core kernels (base config; other dims fall back) and the layer-wise path."""
+    import vhmm_b200.functional as Fn
+    Fn.elbo_select(request.param)
+    yield request.param
+    Fn.elbo_select("auto")
+
+
 def _model(dims, params):
     import vhmm_b200 as V
     m = V.VAE_HMM(dims["C"], dims["H"], dims["K"], dims["H2"], u_dim=dims["U"], trans_hidden=dims["TH"])
@@ -100,9 +110,11 @@ def test_loss_and_gradients_vs_oracle(B, T, ragged):
             assert float(sd[k].grad.abs().max()) == 0.0, k
 
 
-def test_chunked_batch_equals_single_pass():
-    """The library chunks the batch to fit the workspace; results must not depend on it."""
+def test_chunked_batch_equals_single_pass(elbo_impl):
+    """The layer-wise path chunks the batch to fit the workspace; results must not depend on it."""
     import vhmm_b200.functional as Fn
+    if elbo_impl != "layerwise":
+        pytest.skip("the fused path keeps no activation stash: nothing to chunk")
     from oracle import elbo as O
     C, H, K, H2, U, TH = 5, 64, 3, 32, 4, 128
     p = O.init_params(C, H, K, H2, U, TH, seed=3)
@@ -175,6 +187,32 @@ def test_train_model_and_state_dict_roundtrip(tmp_path):
     m2 = m2.cuda()
     with torch.no_grad():
         assert float(m2.compute_loss(xb, ub, Lb, 1.0)) == l1
+
+
+def test_fused_is_active_for_base_config(elbo_impl):
+    import vhmm_b200.functional as Fn
+    assert Fn.elbo_active_impl(Fn.make_dims(5, 64, 3, 32, 4, 128)) == elbo_impl
+    assert Fn.elbo_active_impl(Fn.make_dims(5, 8, 3, 4, 2, 8)) == "layerwise"   # dims the MMA tiling cannot take
+
+
+def test_large_batch_vs_float64_oracle_on_gpu():
+    """Accumulation over many tiles: B=1024, T=512 against the float64 oracle evaluated with torch
+    on the same GPU (the oracle is plain torch code; float64 on the device is only the checker)."""
+    from oracle import elbo as O
+    C, H, K, H2, U, TH = 5, 64, 3, 32, 4, 128
+    p = O.init_params(C, H, K, H2, U, TH, seed=5)
+    B, T = 1024, 512
+    x, u, L = O.synth_batch(B, C, U, T, seed=9, ragged=True, min_len=100)
+    m = _model(dict(C=C, H=H, K=K, H2=H2, U=U, TH=TH), p)
+    loss = m.compute_loss(x.cuda(), u.cuda(), L, 0.9)
+    loss.backward()
+    p64 = {k: v.double().cuda() for k, v in p.items()}
+    loss64, _, g64 = O.loss_and_grads(p64, x.double().cuda(), u.double().cuda(), L, U, 0.9)
+    assert abs(float(loss) - float(loss64)) <= TOL * abs(float(loss64))
+    sd = dict(m.named_parameters())
+    bad = {k: rel_err(sd[k].grad.cpu(), g64[k].cpu()) for k in O.PARAM_ORDER}
+    bad = {k: v for k, v in bad.items() if v > TOL}
+    assert not bad, bad
 
 
 def test_full_size_properties():

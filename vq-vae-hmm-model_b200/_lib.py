@@ -15,8 +15,8 @@ import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-LIB_PATH = os.path.join(_HERE, "libvhmm.so")
-SOURCES = ("api.cu", "elbo_layerwise.cu", "hmm.cu", "elbo_fused.cu", "train_ops.cu")
+LIB_PATH = os.environ.get("VHMM_LIB") or os.path.join(_HERE, "libvhmm.so")   # VHMM_LIB: an instrumented build (tools/)
+SOURCES = ("api.cu", "elbo_layerwise.cu", "hmm.cu", "elbo_fused.cu")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
 
@@ -25,6 +25,7 @@ OP_ENCODER_FWD, OP_PRIOR_FWD, OP_DECODER_FWD, OP_ELBO = 1, 2, 3, 4
 OP_HMM_FORWARD, OP_HMM_POSTERIOR, OP_VITERBI, OP_HMM_DECODE, OP_HMM_SCAN, OP_EMISSION_TABLE = 5, 6, 7, 8, 9, 10
 NUM_PARAMS = 18
 PAD_STATE = 255
+ELBO_AUTO, ELBO_LAYERWISE, ELBO_FUSED = 0, 1, 2
 
 
 class Dims(ctypes.Structure):
@@ -45,6 +46,8 @@ def _sources():
 
 
 def needs_build() -> bool:
+    if os.environ.get("VHMM_LIB"):
+        return False
     if not os.path.exists(LIB_PATH):
         return True
     t = os.path.getmtime(LIB_PATH)
@@ -88,6 +91,8 @@ PROTOTYPES = {
     "vhmm_prior_fwd": (ctypes.c_int, [_DP, _PP, _P, _I64, _I64, _P, _P, _P, _SZ, _P]),
     "vhmm_decoder_fwd": (ctypes.c_int, [_DP, _PP, _P, _I64, _I64, _P, _P, _P, _SZ, _P]),
     "vhmm_elbo": (ctypes.c_int, [_DP, _PP, _P, _P, _P, _I64, _I64, _P, _DBL, _P, _P, _P, _SZ, _P]),
+    "vhmm_elbo_select": (ctypes.c_int, [ctypes.c_int]),
+    "vhmm_elbo_active_impl": (ctypes.c_int, [_DP]),
     "vhmm_argmax_regimes": (ctypes.c_int, [_P, _I64, _I64, _I64, _P, _P]),
     "vhmm_emission_table": (ctypes.c_int, [_DP, _PP, _I64, _P, _P, _P, _SZ, _P]),
     "vhmm_emission_logprob": (ctypes.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P, _P]),

@@ -1,6 +1,8 @@
 // api.cu -- extern "C" entry points of libvhmm.so (include/vhmm.h).  Argument validation and
 // dispatch only; kernels live in the other translation units.
 #include <atomic>
+#include <stdlib.h>
+#include <string.h>
 
 #include "common.cuh"
 
@@ -25,6 +27,10 @@ int layerwise_decoder_fwd(const vhmm_dims&, const vhmm_params&, const float*, in
 int layerwise_elbo(const vhmm_dims&, const vhmm_params&, const float*, const float*, const int64_t*, int64_t, int64_t, const double*, double, double*, float*, void*, size_t, cudaStream_t);
 int layerwise_emission_table(const vhmm_dims&, const vhmm_params&, int64_t, float*, float*, void*, size_t, cudaStream_t);
 int launch_argmax(const float* q, int64_t B, int64_t K, int64_t T, int64_t* out, cudaStream_t st);
+// elbo_fused.cu
+bool fused_supported(const vhmm_dims& d);
+size_t fused_workspace_bytes(const vhmm_dims& d, int64_t B, int64_t T);
+int fused_elbo(const vhmm_dims&, const vhmm_params&, const float*, const float*, const int64_t*, int64_t, int64_t, const double*, double, double*, float*, void*, size_t, cudaStream_t);
 // hmm.cu
 size_t hmm_workspace_bytes(int op, int64_t B, int64_t T, int64_t K);
 int hmm_emission_logprob(const float*, const float*, const float*, int64_t, int64_t, int64_t, int64_t, float*, cudaStream_t);
@@ -33,6 +39,18 @@ int hmm_posterior(const float*, const float*, const float*, const int64_t*, int6
 int hmm_viterbi(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, void*, size_t, cudaStream_t);
 int hmm_decode(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, float*, void*, size_t, cudaStream_t);
 int hmm_scan(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
+
+static std::atomic<int> g_elbo_impl{VHMM_ELBO_AUTO};
+static int elbo_impl_for(const vhmm_dims& d) {
+  int sel = g_elbo_impl.load();
+  if (sel == VHMM_ELBO_AUTO) {
+    const char* e = getenv("VHMM_ELBO_IMPL");
+    if (e && !strcmp(e, "layerwise")) sel = VHMM_ELBO_LAYERWISE;
+    if (e && !strcmp(e, "fused")) sel = VHMM_ELBO_FUSED;
+  }
+  if (sel == VHMM_ELBO_LAYERWISE) return VHMM_ELBO_LAYERWISE;
+  return fused_supported(d) ? VHMM_ELBO_FUSED : VHMM_ELBO_LAYERWISE;
+}
 
 static bool params_ok(const vhmm_params* p) {
   if (!p) return false;
@@ -77,6 +95,7 @@ size_t vhmm_workspace_bytes(int op, const vhmm_dims* dims, int64_t B, int64_t T)
       return hmm_workspace_bytes(op, B, T, dims ? dims->K : 0);
     default:
       if (!dims_ok(dims)) return 0;
+      if (op == VHMM_OP_ELBO && elbo_impl_for(*dims) == VHMM_ELBO_FUSED) return fused_workspace_bytes(*dims, B, T);
       return layerwise_workspace_bytes(op, *dims, B, T);
   }
 }
@@ -110,8 +129,22 @@ int vhmm_elbo(const vhmm_dims* dims, const vhmm_params* params, const float* x, 
               double* sums, float* grads, void* workspace, size_t workspace_bytes, void* stream) {
   ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(x && u && lengths, "x/u/lengths");
   ARG(B > 0 && T > 0, "B,T"); ARG(norms && sums, "norms/sums"); ARG(workspace, "workspace");
+  if (elbo_impl_for(*dims) == VHMM_ELBO_FUSED)
+    return fused_elbo(*dims, *params, x, u, lengths, B, T, norms, beta, sums, grads, workspace,
+                      workspace_bytes, (cudaStream_t)stream);
   return layerwise_elbo(*dims, *params, x, u, lengths, B, T, norms, beta, sums, grads, workspace,
                         workspace_bytes, (cudaStream_t)stream);
+}
+
+int vhmm_elbo_select(int impl) {
+  ARG(impl == VHMM_ELBO_AUTO || impl == VHMM_ELBO_LAYERWISE || impl == VHMM_ELBO_FUSED, "impl");
+  g_elbo_impl.store(impl);
+  return 0;
+}
+
+int vhmm_elbo_active_impl(const vhmm_dims* dims) {
+  if (!dims_ok(dims)) return VHMM_E_ARG;
+  return elbo_impl_for(*dims);
 }
 
 int vhmm_argmax_regimes(const float* q, int64_t B, int64_t K, int64_t T, int64_t* regimes, void* stream) {

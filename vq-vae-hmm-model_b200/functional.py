@@ -167,14 +167,27 @@ def elbo_raw(d: Dims, params, x, u, lengths_dev, norms, beta: float, want_grads:
     sums = torch.empty(4, device=x.device, dtype=torch.float64)
     grads = torch.empty(param_count(d), device=x.device, dtype=torch.float32) if want_grads else None
     with torch.cuda.device(x.device):
-        need = _ws_bytes(_lib.OP_ELBO, d, B, T)          # enough for min(B,1024) sequences
-        per_seq = max(1, (need // max(1, min(B, 1024))))
-        want = min(ELBO_WORKSPACE_CAP, per_seq * B + (64 << 20))
-        ws = workspace(x.device, max(need, want))
+        need = _ws_bytes(_lib.OP_ELBO, d, B, T)
+        if _lib.lib().vhmm_elbo_active_impl(ctypes.byref(d)) == _lib.ELBO_FUSED:
+            ws = workspace(x.device, need)               # exact: no activation stash
+        else:                                            # layer-wise: enough for min(B,1024) sequences,
+            per_seq = max(1, (need // max(1, min(B, 1024))))   # more lets it chunk the batch less
+            want = min(ELBO_WORKSPACE_CAP, per_seq * B + (64 << 20))
+            ws = workspace(x.device, max(need, want))
         check(_lib.lib().vhmm_elbo(ctypes.byref(d), ctypes.byref(P), _ptr(x), _ptr(u), _ptr(lengths_dev), B, T,
                                    _ptr(norms), float(beta), _ptr(sums), _ptr(grads), _ptr(ws), ws.numel(),
                                    _stream(x.device)), "vhmm_elbo")
     return sums, grads
+
+
+def elbo_select(impl: str = "auto"):
+    """Choose the vhmm_elbo implementation: "auto" | "layerwise" | "fused" (include/vhmm.h)."""
+    code = {"auto": _lib.ELBO_AUTO, "layerwise": _lib.ELBO_LAYERWISE, "fused": _lib.ELBO_FUSED}[impl]
+    check(_lib.lib().vhmm_elbo_select(code), "vhmm_elbo_select")
+
+
+def elbo_active_impl(d: Dims) -> str:
+    return {_lib.ELBO_LAYERWISE: "layerwise", _lib.ELBO_FUSED: "fused"}[int(_lib.lib().vhmm_elbo_active_impl(ctypes.byref(d)))]
 
 
 def loss_from_sums(sums: torch.Tensor, norms: torch.Tensor, beta: float) -> torch.Tensor:
