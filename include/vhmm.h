@@ -132,6 +132,13 @@ int vhmm_elbo_select(int impl);
 /* the implementation vhmm_elbo would run for `dims` now (VHMM_ELBO_LAYERWISE / VHMM_ELBO_FUSED) */
 int vhmm_elbo_active_impl(const vhmm_dims* dims);
 
+/* Measurement hook for bench.py (roofline of the dominant kernel): while enabled, the FUSED path
+ * records CUDA events on the caller's stream around its three tile kernels (up to 64 calls).
+ * vhmm_elbo_timing_read waits for those events and returns the summed milliseconds of
+ * {enc_prior, decoder, enc_bwd} and the number of calls recorded. */
+int vhmm_elbo_timing(int enable);
+int vhmm_elbo_timing_read(double* ms_sum_host /*[3]*/, int* ncalls_host);
+
 /* argmax regime decoding (backtesting.py:155, src/backtesting.py:107): q or logits (B,K,T) ->
  * regimes int64 (B,T), lowest index on ties. */
 int vhmm_argmax_regimes(const float* q, int64_t B, int64_t K, int64_t T, int64_t* regimes,

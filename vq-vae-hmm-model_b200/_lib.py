@@ -93,6 +93,8 @@ PROTOTYPES = {
     "vhmm_elbo": (ctypes.c_int, [_DP, _PP, _P, _P, _P, _I64, _I64, _P, _DBL, _P, _P, _P, _SZ, _P]),
     "vhmm_elbo_select": (ctypes.c_int, [ctypes.c_int]),
     "vhmm_elbo_active_impl": (ctypes.c_int, [_DP]),
+    "vhmm_elbo_timing": (ctypes.c_int, [ctypes.c_int]),
+    "vhmm_elbo_timing_read": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int)]),
     "vhmm_argmax_regimes": (ctypes.c_int, [_P, _I64, _I64, _I64, _P, _P]),
     "vhmm_emission_table": (ctypes.c_int, [_DP, _PP, _I64, _P, _P, _P, _SZ, _P]),
     "vhmm_emission_logprob": (ctypes.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P, _P]),

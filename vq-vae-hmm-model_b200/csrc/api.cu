@@ -31,6 +31,8 @@ int launch_argmax(const float* q, int64_t B, int64_t K, int64_t T, int64_t* out,
 bool fused_supported(const vhmm_dims& d);
 size_t fused_workspace_bytes(const vhmm_dims& d, int64_t B, int64_t T);
 int fused_elbo(const vhmm_dims&, const vhmm_params&, const float*, const float*, const int64_t*, int64_t, int64_t, const double*, double, double*, float*, void*, size_t, cudaStream_t);
+int fused_timing_enable(int enable);
+int fused_timing_read(double* ms_sum, int* ncalls);
 // hmm.cu
 size_t hmm_workspace_bytes(int op, int64_t B, int64_t T, int64_t K);
 int hmm_emission_logprob(const float*, const float*, const float*, int64_t, int64_t, int64_t, int64_t, float*, cudaStream_t);
@@ -140,6 +142,13 @@ int vhmm_elbo_select(int impl) {
   ARG(impl == VHMM_ELBO_AUTO || impl == VHMM_ELBO_LAYERWISE || impl == VHMM_ELBO_FUSED, "impl");
   g_elbo_impl.store(impl);
   return 0;
+}
+
+int vhmm_elbo_timing(int enable) { return fused_timing_enable(enable); }
+
+int vhmm_elbo_timing_read(double* ms_sum_host, int* ncalls_host) {
+  ARG(ms_sum_host && ncalls_host, "outputs");
+  return fused_timing_read(ms_sum_host, ncalls_host);
 }
 
 int vhmm_elbo_active_impl(const vhmm_dims* dims) {

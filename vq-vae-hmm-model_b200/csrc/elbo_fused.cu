@@ -698,6 +698,18 @@ __global__ void finish_kernel(const float* __restrict__ red, const double* __res
 }
 
 // ---- host side ---------------------------------------------------------------------------------
+// optional per-kernel timing (vhmm_elbo_timing): CUDA events recorded on the caller's stream
+// around the three tile kernels of up to TIMING_SLOTS consecutive calls
+constexpr int TIMING_SLOTS = 64;
+struct TimingState {
+  bool enabled = false;
+  int ncalls = 0;
+  cudaEvent_t ev[TIMING_SLOTS][4] = {};
+  bool created = false;
+};
+static TimingState g_timing_;
+#define g_timing ::vhmm::fz::g_timing_
+
 template <typename CF>
 struct Launcher {
   static size_t workspace_bytes(int64_t B, int64_t T, int ncta) {
@@ -746,13 +758,19 @@ struct Launcher {
     VHMM_LAUNCH_CHECK();
     fold_kernel<CF><<<(unsigned)cdiv(3 * CF::H * 8, 128), 128, 0, st>>>(P.p[P_D1W], P.p[P_EMB], wfold);
     VHMM_LAUNCH_CHECK();
+    cudaEvent_t* tev = nullptr;
+    if (g_timing.enabled && grads && g_timing.ncalls < TIMING_SLOTS) tev = g_timing.ev[g_timing.ncalls++];
+    if (tev) VHMM_CUDA_CHECK(cudaEventRecord(tev[0], st));
     kA<<<ncta, NTH, CF::SM_A * 4, st>>>(cm, P);
     VHMM_LAUNCH_CHECK();
+    if (tev) VHMM_CUDA_CHECK(cudaEventRecord(tev[1], st));
     if (grads) {
       kB<<<ncta, NTH, CF::SM_B * 4, st>>>(cm, P);
       VHMM_LAUNCH_CHECK();
+      if (tev) VHMM_CUDA_CHECK(cudaEventRecord(tev[2], st));
       kC<<<ncta, NTH, CF::SM_C * 4, st>>>(cm, P);
       VHMM_LAUNCH_CHECK();
+      if (tev) VHMM_CUDA_CHECK(cudaEventRecord(tev[3], st));
       reduce_acc_kernel<<<(unsigned)cdiv(CF::ACC_ALL, 256), 256, 0, st>>>(cm.acc_part, ncta, CF::ACC_ALL, red);
       VHMM_LAUNCH_CHECK();
     } else {
@@ -785,6 +803,32 @@ static int fused_sm_count() {
       n = 148;
   }
   return n;
+}
+
+int fused_timing_enable(int enable) {
+  if (enable && !g_timing.created) {
+    for (int i = 0; i < fz::TIMING_SLOTS; ++i)
+      for (int j = 0; j < 4; ++j) VHMM_CUDA_CHECK(cudaEventCreate(&g_timing.ev[i][j]));
+    g_timing.created = true;
+  }
+  g_timing.enabled = enable != 0;
+  g_timing.ncalls = 0;
+  return 0;
+}
+
+// ms_sum[0..2] = total milliseconds of kernels A, B, C over the recorded calls (waits for them)
+int fused_timing_read(double* ms_sum, int* ncalls) {
+  ms_sum[0] = ms_sum[1] = ms_sum[2] = 0.0;
+  *ncalls = g_timing.ncalls;
+  for (int i = 0; i < g_timing.ncalls; ++i) {
+    VHMM_CUDA_CHECK(cudaEventSynchronize(g_timing.ev[i][3]));
+    for (int j = 0; j < 3; ++j) {
+      float ms = 0.f;
+      VHMM_CUDA_CHECK(cudaEventElapsedTime(&ms, g_timing.ev[i][j], g_timing.ev[i][j + 1]));
+      ms_sum[j] += ms;
+    }
+  }
+  return 0;
 }
 
 bool fused_supported(const vhmm_dims& d) {

@@ -9,8 +9,14 @@ namespace vhmm {
 static inline bool small_k(int64_t K) { return K >= 2 && K <= 4; }
 static inline bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 
-constexpr int HS_TC = 8;     // steps per staged slab
-constexpr int HS_NT = 128;   // rows (threads) per CTA
+#ifndef VHMM_HS_TC
+#define VHMM_HS_TC 4   /* 4 steps x 2 stages = 416 B of smem per row -> 512 rows resident per SM (measured best) */
+#endif
+#ifndef VHMM_HS_NT
+#define VHMM_HS_NT 64
+#endif
+constexpr int HS_TC = VHMM_HS_TC;   // steps per staged slab
+constexpr int HS_NT = VHMM_HS_NT;   // rows (threads) per CTA
 constexpr int SCAN_CH = 128; // steps per scan chunk
 
 static int64_t psi_bytes(int64_t K) { return K <= 4 ? 1 : K; }
