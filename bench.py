@@ -243,22 +243,27 @@ def main():
         n = ktimes[3]
         kms = [t / n for t in ktimes[:3]]
         dec_tfl = per_gpu_steps * DEC_FLOP_PER_STEP / (kms[1] * 1e-3) / 1e12
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", "r1_fused_decoder_traffic.json")
+        dec = Fn.elbo_decoder_active()
+        traffic = None   # dram bytes per launch of the active decoder kernel from its committed ncu --set full capture
+        tp = os.path.join(ROOT, "profiles", "r1_tc5_decoder_traffic.json" if dec == "tc5" else "r1_fused_decoder_traffic.json")
         if os.path.exists(tp):
             tj = json.load(open(tp))
             if tj.get("B") == B and tj.get("T") == T:
                 traffic = tj["dram_bytes_per_launch"]
         roofline = {
-            "kernel": "vhmm::fz::decoder_kernel (decoder fwd+bwd + NLL, 3xTF32 mma.sync)",
+            "kernel": ("vhmm::fz::decoder_tc5_kernel (decoder fwd+bwd + NLL; 64x64 k=3 GEMMs on tcgen05, 2xFP16 split)"
+                       if dec == "tc5" else "vhmm::fz::decoder_kernel (decoder fwd+bwd + NLL, 3xTF32 mma.sync)"),
             "bound": "tensor", "achieved": dec_tfl, "peak": pk["bf16"], "unit": "TFLOP/s",
             "frac": dec_tfl / pk["bf16"], "traffic": traffic,
             "peak_source": pk["src"] + " bf16 dense cuBLAS, sustained (kernel timed inside a long step)",
             "algorithmic_flop_per_step": DEC_FLOP_PER_STEP, "ms_per_launch": kms[1],
             "share_of_step": kms[1] / ms,
             "kernels_ms": {"enc_prior": kms[0], "decoder": kms[1], "enc_bwd": kms[2]},
-            "note": "fp32-parity path: every product is 3 TF32 MMAs (hi*hi, lo*hi, hi*lo); legacy mma.sync TF32 "
-                    "peaks at 512 MAC/clk/SM on B200 (tools/microbench.cu), i.e. 93 TFLOP/s of fp32-equivalent work",
+            "note": ("fp32-parity path: every product of the three big GEMMs is 3 fp16 tcgen05 MMAs (h*h, h*m, m*h) with "
+                     "fp32 accumulate in TMEM, so at most 1/3 of the bf16 peak is reachable; the small layers run on mma.sync"
+                     if dec == "tc5" else
+                     "fp32-parity path: every product is 3 TF32 MMAs (hi*hi, lo*hi, hi*lo); legacy mma.sync TF32 "
+                     "peaks at 512 MAC/clk/SM on B200 (tools/microbench.cu), i.e. 93 TFLOP/s of fp32-equivalent work"),
             "step": step_ctx,
         }
     else:
@@ -272,7 +277,7 @@ def main():
         "config": {"workload": f"cfg2: VAE_HMM(5,64,K=3,32,u_dim=4) ELBO fwd+bwd, B={B} per GPU x {world} GPU, T={T}, lengths=T",
                    "parallelism": f"batch-sharded x{world}, 1 NCCL all-reduce/step" if world > 1 else "single GPU",
                    "l2": f"inputs ({(B * T * 36) / 1e9:.2f} GB/GPU) larger than the 126 MB L2; no flush needed",
-                   "elbo_impl": Fn.elbo_active_impl(model._dims)},
+                   "elbo_impl": Fn.elbo_active_impl(model._dims), "decoder_kernel": Fn.elbo_decoder_active()},
         "e2e": {"value": e2e_value, "unit": "sequence-steps/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "loss": loss_val,

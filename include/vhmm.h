@@ -132,6 +132,16 @@ int vhmm_elbo_select(int impl);
 /* the implementation vhmm_elbo would run for `dims` now (VHMM_ELBO_LAYERWISE / VHMM_ELBO_FUSED) */
 int vhmm_elbo_active_impl(const vhmm_dims* dims);
 
+/* The FUSED path has two builds of its decoder kernel (decoder forward + backward + NLL):
+ *   VHMM_DECODER_TC5  the three 64x64 k=3 GEMM families on the 5th-generation tensor core
+ *                     (tcgen05.mma, TMEM accumulators, 2 x fp16 split operands, fp32 accumulate)
+ *   VHMM_DECODER_MMA  the same GEMMs on mma.sync with the 3 x TF32 split
+ * Both meet the 1e-5 parity bar; AUTO (default) = TC5; environment VHMM_FUSED_DECODER=mma|tc5
+ * overrides AUTO. */
+enum { VHMM_DECODER_AUTO = 0, VHMM_DECODER_MMA = 1, VHMM_DECODER_TC5 = 2 };
+int vhmm_elbo_decoder_select(int variant);
+int vhmm_elbo_decoder_active(void);
+
 /* Measurement hook for bench.py (roofline of the dominant kernel): while enabled, the FUSED path
  * records CUDA events on the caller's stream around its three tile kernels (up to 64 calls).
  * vhmm_elbo_timing_read waits for those events and returns the summed milliseconds of

@@ -13,14 +13,18 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-5
 
 
-@pytest.fixture(autouse=True, scope="module", params=["fused", "layerwise"])
+@pytest.fixture(autouse=True, scope="module", params=["fused", "fused-mma", "layerwise"])
 def elbo_impl(request):
-    """Every test of this module runs against both vhmm_elbo implementations (include/vhmm.h):
-    the fused tensor-core kernels (base config; other dims fall back) and the layer-wise path."""
+    """Every test of this module runs against all vhmm_elbo implementations (include/vhmm.h): the
+    fused tile kernels with the tcgen05 decoder ("fused") and with the mma.sync decoder
+    ("fused-mma") -- base config; other dims fall back -- and the layer-wise path."""
     import vhmm_b200.functional as Fn
-    Fn.elbo_select(request.param)
-    yield request.param
+    impl, _, dec = request.param.partition("-")
+    Fn.elbo_select(impl)
+    Fn.elbo_decoder_select(dec or "tc5")
+    yield impl
     Fn.elbo_select("auto")
+    Fn.elbo_decoder_select("auto")
 
 
 def _model(dims, params):

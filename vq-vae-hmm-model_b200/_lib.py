@@ -26,6 +26,7 @@ OP_HMM_FORWARD, OP_HMM_POSTERIOR, OP_VITERBI, OP_HMM_DECODE, OP_HMM_SCAN, OP_EMI
 NUM_PARAMS = 18
 PAD_STATE = 255
 ELBO_AUTO, ELBO_LAYERWISE, ELBO_FUSED = 0, 1, 2
+DECODER_AUTO, DECODER_MMA, DECODER_TC5 = 0, 1, 2
 
 
 class Dims(ctypes.Structure):
@@ -93,6 +94,8 @@ PROTOTYPES = {
     "vhmm_elbo": (ctypes.c_int, [_DP, _PP, _P, _P, _P, _I64, _I64, _P, _DBL, _P, _P, _P, _SZ, _P]),
     "vhmm_elbo_select": (ctypes.c_int, [ctypes.c_int]),
     "vhmm_elbo_active_impl": (ctypes.c_int, [_DP]),
+    "vhmm_elbo_decoder_select": (ctypes.c_int, [ctypes.c_int]),
+    "vhmm_elbo_decoder_active": (ctypes.c_int, []),
     "vhmm_elbo_timing": (ctypes.c_int, [ctypes.c_int]),
     "vhmm_elbo_timing_read": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int)]),
     "vhmm_argmax_regimes": (ctypes.c_int, [_P, _I64, _I64, _I64, _P, _P]),

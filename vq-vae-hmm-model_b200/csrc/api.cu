@@ -32,6 +32,8 @@ bool fused_supported(const vhmm_dims& d);
 size_t fused_workspace_bytes(const vhmm_dims& d, int64_t B, int64_t T);
 int fused_elbo(const vhmm_dims&, const vhmm_params&, const float*, const float*, const int64_t*, int64_t, int64_t, const double*, double, double*, float*, void*, size_t, cudaStream_t);
 int fused_timing_enable(int enable);
+int fused_decoder_select(int variant);
+int fused_decoder_active();
 int fused_timing_read(double* ms_sum, int* ncalls);
 // hmm.cu
 size_t hmm_workspace_bytes(int op, int64_t B, int64_t T, int64_t K);
@@ -143,6 +145,12 @@ int vhmm_elbo_select(int impl) {
   g_elbo_impl.store(impl);
   return 0;
 }
+
+int vhmm_elbo_decoder_select(int variant) {
+  ARG(variant == VHMM_DECODER_AUTO || variant == VHMM_DECODER_MMA || variant == VHMM_DECODER_TC5, "variant");
+  return fused_decoder_select(variant);
+}
+int vhmm_elbo_decoder_active(void) { return fused_decoder_active(); }
 
 int vhmm_elbo_timing(int enable) { return fused_timing_enable(enable); }
 

@@ -23,8 +23,11 @@
 // padded batch; activations are zero only outside [0,T) (conv zero padding); `lengths` masks the
 // loss terms only.  Tiles beyond the dependency cone of the valid steps are skipped (their
 // gradients are exactly zero) and the consumers substitute zeros for what was not written.
+#include <stdlib.h>
+#include <string.h>
 #include "common.cuh"
 #include "mma_tf32.cuh"
+#include "tc5.cuh"
 
 namespace vhmm {
 namespace fz {
@@ -488,6 +491,9 @@ __global__ void __launch_bounds__(NTH, 1) decoder_kernel(Common cm, vhmm_params 
   if (tid == 0) cm.loss_part[(int64_t)blockIdx.x * LP + 0] = v;
 }
 
+// kernel B on the 5th-generation tensor core (tcgen05): same interface and results as decoder_kernel
+#include "decoder_tc5.cuh"
+
 // =============================================================================================
 // kernel C: encoder backward (forward recomputed in the tile)
 // =============================================================================================
@@ -710,6 +716,19 @@ struct TimingState {
 static TimingState g_timing_;
 #define g_timing ::vhmm::fz::g_timing_
 
+// which decoder kernel the fused path launches: 0 = auto (tcgen05), 1 = mma.sync 3xTF32, 2 = tcgen05 2xFP16
+static int g_decoder_variant_ = 0;
+inline int decoder_variant() {
+  int v = g_decoder_variant_;
+  if (v == 0) {
+    const char* e = getenv("VHMM_FUSED_DECODER");
+    if (e && !strcmp(e, "mma")) v = 1;
+    else if (e && !strcmp(e, "tc5")) v = 2;
+    else v = 2;
+  }
+  return v;
+}
+
 template <typename CF>
 struct Launcher {
   static size_t workspace_bytes(int64_t B, int64_t T, int ncta) {
@@ -743,12 +762,15 @@ struct Launcher {
     if (cm.ntiles < ncta) ncta = (int)cm.ntiles;
 
     auto kA = enc_prior_kernel<CF>;
-    auto kB = decoder_kernel<CF>;
+    const bool tc5v = decoder_variant() == 2;
+    auto kB = tc5v ? decoder_tc5_kernel<CF> : decoder_kernel<CF>;
+    const size_t smB = tc5v ? t5::Lay<CF>::BYTES : (size_t)CF::SM_B * 4;
     auto kC = enc_bwd_kernel<CF>;
     static bool attr_done = false;   // idempotent: a racing second caller sets the same values
     if (!attr_done) {
       VHMM_CUDA_CHECK(cudaFuncSetAttribute(kA, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SM_A * 4));
-      VHMM_CUDA_CHECK(cudaFuncSetAttribute(kB, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SM_B * 4));
+      VHMM_CUDA_CHECK(cudaFuncSetAttribute(decoder_kernel<CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SM_B * 4));
+      VHMM_CUDA_CHECK(cudaFuncSetAttribute(decoder_tc5_kernel<CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5::Lay<CF>::BYTES));
       VHMM_CUDA_CHECK(cudaFuncSetAttribute(kC, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SM_C * 4));
       attr_done = true;
     }
@@ -765,7 +787,7 @@ struct Launcher {
     VHMM_LAUNCH_CHECK();
     if (tev) VHMM_CUDA_CHECK(cudaEventRecord(tev[1], st));
     if (grads) {
-      kB<<<ncta, NTH, CF::SM_B * 4, st>>>(cm, P);
+      kB<<<ncta, NTH, smB, st>>>(cm, P);
       VHMM_LAUNCH_CHECK();
       if (tev) VHMM_CUDA_CHECK(cudaEventRecord(tev[2], st));
       kC<<<ncta, NTH, CF::SM_C * 4, st>>>(cm, P);
@@ -775,7 +797,7 @@ struct Launcher {
       VHMM_LAUNCH_CHECK();
     } else {
       // loss only: the decoder kernel still evaluates the NLL (its backward half is cheap to keep)
-      kB<<<ncta, NTH, CF::SM_B * 4, st>>>(cm, P);
+      kB<<<ncta, NTH, smB, st>>>(cm, P);
       VHMM_LAUNCH_CHECK();
     }
     vhmm_dims d{CF::C, CF::H, CF::K, CF::H2, CF::U, CF::TH};
@@ -804,6 +826,9 @@ static int fused_sm_count() {
   }
   return n;
 }
+
+int fused_decoder_select(int variant) { fz::g_decoder_variant_ = variant; return 0; }
+int fused_decoder_active() { return fz::decoder_variant(); }
 
 int fused_timing_enable(int enable) {
   if (enable && !g_timing.created) {

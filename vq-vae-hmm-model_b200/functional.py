@@ -186,6 +186,16 @@ def elbo_select(impl: str = "auto"):
     check(_lib.lib().vhmm_elbo_select(code), "vhmm_elbo_select")
 
 
+def elbo_decoder_select(variant: str = "auto"):
+    """Decoder kernel of the fused path: "auto" | "mma" (mma.sync 3xTF32) | "tc5" (tcgen05 2xFP16)."""
+    code = {"auto": _lib.DECODER_AUTO, "mma": _lib.DECODER_MMA, "tc5": _lib.DECODER_TC5}[variant]
+    check(_lib.lib().vhmm_elbo_decoder_select(code), "vhmm_elbo_decoder_select")
+
+
+def elbo_decoder_active() -> str:
+    return {_lib.DECODER_MMA: "mma", _lib.DECODER_TC5: "tc5"}[int(_lib.lib().vhmm_elbo_decoder_active())]
+
+
 def elbo_active_impl(d: Dims) -> str:
     return {_lib.ELBO_LAYERWISE: "layerwise", _lib.ELBO_FUSED: "fused"}[int(_lib.lib().vhmm_elbo_active_impl(ctypes.byref(d)))]
 
