@@ -174,14 +174,12 @@ def main():
         loss.backward()
         return loss
 
-    xd, ud = torch.empty_like(x), torch.empty_like(u)
-
     def step_e2e():
-        xd.copy_(xh, non_blocking=True)
-        ud.copy_(uh, non_blocking=True)
-        ld = lh.to(dev, non_blocking=True)
+        # the public API call with HOST buffers (pinned): compute_loss streams the batch to the device
+        # chunk by chunk underneath the kernels (functional.elbo_raw_streamed); lengths are a CPU
+        # tensor exactly as the reference's collate_fn produces them
         model.zero_grad(set_to_none=True)
-        loss = model.compute_loss(xd, ud, ld, beta)
+        loss = model.compute_loss(xh, uh, lh, beta)
         loss.backward()
         return loss.item()            # D2H of the step's result, every step
 

@@ -242,3 +242,30 @@ def test_full_size_properties():
     sp, _ = Fn.elbo_raw(m._dims, m._params(), xs[perm].contiguous(), us[perm].contiguous(), Ls[perm].contiguous(), norms, 1.0, False)
     assert torch.allclose(s, sp, rtol=1e-9)
     assert float(s[3]) == float(L.sum())
+
+
+def test_host_resident_batch_is_streamed(elbo_impl):
+    """compute_loss on (pinned) HOST tensors streams the batch chunk by chunk (functional.
+    elbo_raw_streamed); loss and gradients equal the device-resident call."""
+    import vhmm_b200.functional as Fn
+    from oracle import elbo as O
+    C, H, K, H2, U, TH = 5, 64, 3, 32, 4, 128
+    p = O.init_params(C, H, K, H2, U, TH, seed=11)
+    x, u, L = O.synth_batch(70, C, U, 96, seed=12)
+    m = _model(dict(C=C, H=H, K=K, H2=H2, U=U, TH=TH), p)
+    m.zero_grad(set_to_none=True)
+    l0 = m.compute_loss(x.cuda(), u.cuda(), L, 0.6)
+    l0.backward()
+    g0 = {k: v.grad.detach().clone() for k, v in m.named_parameters()}
+    Ld = L.cuda()
+    norms = Fn.elbo_norms(Ld, 70, C, 96)
+    s1, gr1 = Fn.elbo_raw_streamed(m._dims, m._params(), x.pin_memory(), u.pin_memory(), Ld, norms, 0.6, True, chunk=16)
+    s0, gr0 = Fn.elbo_raw(m._dims, m._params(), x.cuda(), u.cuda(), Ld, norms, 0.6, True)
+    assert rel_err(s1, s0) <= 1e-9
+    assert rel_err(gr1, gr0) <= 2e-6
+    m.zero_grad(set_to_none=True)
+    l1 = m.compute_loss(x.pin_memory(), u.pin_memory(), L, 0.6)     # public API, host tensors
+    l1.backward()
+    assert abs(float(l1) - float(l0)) <= 1e-6 * abs(float(l0))
+    for k, v in m.named_parameters():
+        assert rel_err(v.grad, g0[k]) <= 2e-6, k

@@ -62,7 +62,8 @@ struct Lay {
   static constexpr int PB = S + CF::H * PT;                     // [16][PT]
   static constexpr int ACC = PB + 16 * PT;                      // small gradient accumulators: layout of Cfg::B_* minus B_WF
   static constexpr int NACC = CF::ACC_B - CF::B_WF;
-  static constexpr int FLOATS = ACC + NACC;
+  static constexpr int QX1 = ACC + NACC;                        // second input buffer (prefetch of the next tile)
+  static constexpr int FLOATS = QX1 + 16 * PT;
   static constexpr size_t BYTES = (size_t)OP_BYTES + (size_t)FLOATS * 4;
 };
 }  // namespace t5
@@ -86,7 +87,8 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
   float* bd1s = fl + L::BD1;
   float* bd2s = fl + L::BD2;
   float* bps = fl + L::BP;
-  float* QX = fl + L::QX;
+  float* QX0 = fl + L::QX;
+  float* QX1 = fl + L::QX1;
   float* S = fl + L::S;
   float* Pb = fl + L::PB;
   float* acc = fl + L::ACC;                                // acc[i] <-> Cfg::B_WF + i
@@ -194,14 +196,24 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
       tc5::fence_after_sync();
     }
   };
-  for (int64_t tile = blockIdx.x; tile < cm.ntiles; tile += gridDim.x) {
-    const TileInfo ti = tile_info(cm, tile);
-    if (ti.t0 >= ti.Leff + 2) continue;
+  TileInfo ti, tn;
+  int buf = 0;
+  auto fetch = [&](const TileInfo& t_, float* dst) {
+    const int qmax = (t_.Leff + 6 < cm.T) ? t_.Leff + 6 : cm.T;
+    prefetch_rows(dst, cm.q, K, t_.b, cm.T, t_.t0, qmax);
+    prefetch_rows(dst + 8 * PT, cm.x, C, t_.b, cm.T, t_.t0, cm.T);
+  };
+  int64_t tile = next_tile<2>(cm, blockIdx.x, ti);
+  if (tile >= 0) fetch(ti, QX0);
+  cp_async_commit();
+  while (tile >= 0) {
+    const int64_t nxt = next_tile<2>(cm, tile + gridDim.x, tn);
+    if (nxt >= 0) fetch(tn, buf ? QX0 : QX1);
+    cp_async_commit();
+    cp_async_wait_prev();
+    const float* QX = buf ? QX1 : QX0;
     const int t0 = ti.t0, T = cm.T, Lb = ti.L;
     const int64_t b = ti.b;
-    const int qmax = (ti.Leff + 6 < T) ? ti.Leff + 6 : T;
-    load_rows(QX, cm.q, K, b, T, t0, qmax);
-    load_rows(QX + 8 * PT, cm.x, C, b, T, t0, T);
     if (tid == 0) amax_sh = 0u;
     __syncthreads(); PROF(0);
     // ---- g1 = relu(conv3'(q) + b1) -> S (fp32), then its fp16 parts -> RA   (:83-85)
@@ -412,6 +424,7 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     }
     PROF(10);
     if (++ndone % FLUSH == 0) flush_all();
+    tile = nxt; ti = tn; buf ^= 1;
   }
   PROF_DUMP("decoder_tc5", 11);
   flush_all();

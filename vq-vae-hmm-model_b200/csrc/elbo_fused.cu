@@ -76,9 +76,9 @@ struct Cfg {
   // shared memory (floats)
   static constexpr int R1 = (H + H2 > TH) ? H + H2 : TH;   // h1|h2 region, reused for the prior's hidden layer
   static constexpr int SM_A = 3 * H * 8 + 3 * H2 * PW_H + 16 * PW_H2 + TH * 8 + 16 * PW_TH + (H + H2 + 16 + TH + 16 + 8) +
-                              (16 + R1 + 16 + 16 + 16) * PT + ACC_A;
+                              (16 + R1 + 16 + 16 + 16) * PT + ACC_A + 16 * PT;   // + second input buffer (prefetch)
   static constexpr int SM_B = 3 * H * 8 + 3 * H * PW_H + 16 * PW_H + (H + H + 16) + (16 + H + H + 16) * PT + ACC_B;
-  static constexpr int SM_C = 3 * H * 8 + 3 * H2 * PW_H + 16 * PW_H2 + (H + H2 + 16) + (16 + H + H2 + 16 + 16) * PT + ACC_C;
+  static constexpr int SM_C = 3 * H * 8 + 3 * H2 * PW_H + 16 * PW_H2 + (H + H2 + 16) + (16 + H + H2 + 16 + 16) * PT + ACC_C + 32 * PT;   // + second input buffers (prefetch)
 };
 
 // ---- helpers --------------------------------------------------------------------------------
@@ -135,6 +135,32 @@ __device__ __forceinline__ void load_rows(float* dst, const float* __restrict__ 
     const int r = i / NC, j = i - r * NC, t = t0 - HL + j;
     dst[r * PT + j] = (t >= 0 && t < tmax) ? src[(b * nrows + r) * (int64_t)T + t] : 0.f;
   }
+}
+
+// asynchronous variant (cp.async, 4-byte granules so that any T / alignment works; columns outside
+// [0, tmax) are zero-filled): used to fetch the NEXT tile's inputs while the current tile computes
+__device__ __forceinline__ void prefetch_rows(float* dst, const float* __restrict__ src, int nrows, int64_t b, int T,
+                                              int t0, int tmax) {
+  for (int i = threadIdx.x; i < nrows * NC; i += NTH) {
+    const int r = i / NC, j = i - r * NC, t = t0 - HL + j;
+    const bool ok = (t >= 0 && t < tmax);
+    const float* g = src + (b * nrows + r) * (int64_t)T + (ok ? t : 0);
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst + r * PT + j);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" :: "r"(d), "l"(g), "r"(ok ? 4 : 0) : "memory");
+  }
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_prev() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+// first tile >= `tile` of this CTA's round-robin sequence that is inside the dependency cone of
+// its sequence's valid steps (t0 < Leff + SKIP); -1 when there is none
+template <int SKIP>
+__device__ __forceinline__ int64_t next_tile(const Common& cm, int64_t tile, TileInfo& ti) {
+  for (; tile < cm.ntiles; tile += gridDim.x) {
+    ti = tile_info(cm, tile);
+    if (ti.t0 < ti.Leff + SKIP) return tile;
+  }
+  return -1;
 }
 
 __device__ __forceinline__ double block_sum_d(double v, double* sh) {
@@ -235,8 +261,8 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_kernel(Common cm, vhmm_param
   float* bt0s = b3s + 16;
   float* bt2s = bt0s + TH;                // [16]
   float* lps = bt2s + 16;                 // [8]
-  float* XU = lps + 8;                    // rows 0..7 x, rows 8..15 u
-  float* R1 = XU + 16 * PT;               // h1 | h2, later the prior's hidden layer a
+  float* XU0 = lps + 8;                   // rows 0..7 x, rows 8..15 u (buffer 0; buffer 1 at the end)
+  float* R1 = XU0 + 16 * PT;               // h1 | h2, later the prior's hidden layer a
   float* H1 = R1;
   float* H2b = R1 + H * PT;
   float* Ab = R1;
@@ -244,6 +270,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_kernel(Common cm, vhmm_param
   float* Mb = LQ + 16 * PT;               // transition logits -> log_A, row i*K+j
   float* dMb = Mb + 16 * PT;
   float* acc = dMb + 16 * PT;             // ACC_A
+  float* XU1 = acc + CF::ACC_A;
   for (int i = threadIdx.x; i < CF::SM_A; i += NTH) sm[i] = 0.f;
   __syncthreads();
   stage_conv_w(W1s, P.p[P_E1W], H, C, 3, H, 8);
@@ -258,19 +285,30 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_kernel(Common cm, vhmm_param
 #pragma unroll
   for (int k = 0; k < K; ++k) s_q0[k] = 0.0;
   const int tid = threadIdx.x, w = tid >> 5;
+  PROF_DECL
   __syncthreads();
 
   double* part = cm.acc_part + (int64_t)blockIdx.x * CF::ACC_ALL;
   int ndone = 0;
-  for (int64_t tile = blockIdx.x; tile < cm.ntiles; tile += gridDim.x) {
-    const TileInfo ti = tile_info(cm, tile);
-    if (ti.t0 >= ti.Leff + 6) continue;
+  TileInfo ti, tn;
+  int buf = 0;
+  auto fetch = [&](const TileInfo& t_, float* dst) {
+    prefetch_rows(dst, cm.x, C, t_.b, cm.T, t_.t0, cm.T);
+    prefetch_rows(dst + 8 * PT, cm.u, U, t_.b, cm.T, t_.t0, cm.T);
+  };
+  int64_t tile = next_tile<6>(cm, blockIdx.x, ti);
+  if (tile >= 0) fetch(ti, XU0);
+  cp_async_commit();
+  while (tile >= 0) {
+    const int64_t nxt = next_tile<6>(cm, tile + gridDim.x, tn);
+    if (nxt >= 0) fetch(tn, buf ? XU0 : XU1);
+    cp_async_commit();
+    cp_async_wait_prev();
+    const float* XU = buf ? XU1 : XU0;
     const int t0 = ti.t0, T = cm.T, L = ti.L;
     const int64_t b = ti.b;
-    load_rows(XU, cm.x, C, b, T, t0, T);
-    load_rows(XU + 8 * PT, cm.u, U, b, T, t0, T);
-    __syncthreads();
-    encoder_forward<CF>(W1s, b1s, W2s, b2s, W3s, b3s, XU, H1, H2b, LQ, t0, T);
+    __syncthreads(); PROF(0);
+    encoder_forward<CF>(W1s, b1s, W2s, b2s, W3s, b3s, XU, H1, H2b, LQ, t0, T); PROF(1);
     // softmax, entropy, init term, q -> HBM
     if (tid < NC) {
       const int j = tid, t = t0 - HL + j;
@@ -297,12 +335,13 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_kernel(Common cm, vhmm_param
       }
       if (own && t < L) { s_ent += (double)ent; s_valid += 1.0; }                     // :134-135
     }
-    __syncthreads();   // h1/h2 are dead from here: R1 becomes the prior's hidden layer
+    __syncthreads(); PROF(2);   // h1/h2 are dead from here: R1 becomes the prior's hidden layer
     // a = relu(W0 u + b0) on every column (VQ_VAE_HMM_fixed.py:68)
     cols_op<TH, 2, 2, 1, 1, false>(Wt0s, 0, 8, XU + 8 * PT, EpiReluZero{Ab, bt0s, t0, T});
     __syncthreads();
+    PROF(3);
     cols_op<16, 1, 1, TH / 8, 1, false>(Wt2s, 0, CF::PW_TH, Ab, EpiBiasRows{Mb, bt2s, K2});
-    __syncthreads();
+    __syncthreads(); PROF(4);
     if (tid < NC) {    // row log-softmax -> log_A (:69)
       const int j = tid;
 #pragma unroll
@@ -354,21 +393,24 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_kernel(Common cm, vhmm_param
         for (int k = 0; k < K; ++k) cm.dq_prior[(b * K + k) * (int64_t)T + t] = aP * dq[k];
     }
     __syncthreads();
+    PROF(5);
     // gradients of transition_net.2: dWt2[r][h] += sum_t dM[r][t] a[h][t]
     for (int unit = w; unit < TH / 8; unit += NW)
       gemm_time<1, 1, KST, J0, PT>(dMb, Ab + unit * 8 * PT, acc + CF::A_WT2 + unit * 8, 0, CF::PW_TH);
     row_sums<J0, TT / 4, PT, NW>(dMb, K2, acc + CF::A_BT2);
-    __syncthreads();
+    __syncthreads(); PROF(6);
     // da = relu'(a) * Wt2^T dM, in place over a
     cols_op<TH, 2, 2, 2, 1, true>(Wt2s, 0, CF::PW_TH, dMb, EpiReluMask{Ab});
-    __syncthreads();
+    __syncthreads(); PROF(7);
     // gradients of transition_net.0: dWt0[h][c] += sum_t da[h][t] u[c][t]
     for (int unit = w; unit < TH / 16; unit += NW)
       gemm_time<1, 1, KST, J0, PT>(Ab + unit * 16 * PT, XU + 8 * PT, acc + CF::A_WT0 + unit * 16 * 8, 0, 8);
     row_sums<J0, TT / 4, PT, NW>(Ab, TH, acc + CF::A_BT0);
-    __syncthreads();
+    __syncthreads(); PROF(8);
     if (++ndone % FLUSH == 0) flush_acc(part, acc, CF::ACC_A);
+    tile = nxt; ti = tn; buf ^= 1;
   }
+  PROF_DUMP("enc_prior", 9);
   // per-CTA partials
   flush_acc(part, acc, CF::ACC_A);
   double* lp = cm.loss_part + (int64_t)blockIdx.x * LP;
@@ -507,12 +549,14 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_kernel(Common cm, vhmm_params 
   float* b1s = W3s + 16 * CF::PW_H2;
   float* b2s = b1s + H;
   float* b3s = b2s + H2;                  // [16]
-  float* XU = b3s + 16;                   // rows 0..7 x
-  float* H1 = XU + 16 * PT;
+  float* XU0 = b3s + 16;                  // rows 0..7 x (buffer 0)
+  float* H1 = XU0 + 16 * PT;
   float* H2b = H1 + H * PT;
   float* LQ = H2b + H2 * PT;              // logits, then d loss / d logits (rows >= K stay zero)
-  float* DQ = LQ + 16 * PT;               // d loss / d q from the decoder and the prior
-  float* acc = DQ + 16 * PT;              // ACC_C
+  float* DQ0 = LQ + 16 * PT;              // d loss / d q: rows 0.. from the decoder, rows 8.. from the prior (buffer 0)
+  float* acc = DQ0 + 16 * PT;             // ACC_C
+  float* XU1 = acc + CF::ACC_C;
+  float* DQ1 = XU1 + 16 * PT;
   for (int i = threadIdx.x; i < CF::SM_C; i += NTH) sm[i] = 0.f;
   __syncthreads();
   stage_conv_w(W1s, P.p[P_E1W], H, C, 3, H, 8);
@@ -521,24 +565,32 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_kernel(Common cm, vhmm_params 
   stage_vec(b1s, P.p[P_E1B], H); stage_vec(b2s, P.p[P_E2B], H2); stage_vec(b3s, P.p[P_E3B], K);
   const float aE = (float)((double)cm.beta / cm.norms[1]);
   const int tid = threadIdx.x, w = tid >> 5;
+  PROF_DECL
   __syncthreads();
 
   double* part = cm.acc_part + (int64_t)blockIdx.x * CF::ACC_ALL + CF::ACC_A + CF::ACC_B;
   int ndone = 0;
-  for (int64_t tile = blockIdx.x; tile < cm.ntiles; tile += gridDim.x) {
-    const TileInfo ti = tile_info(cm, tile);
-    if (ti.t0 >= ti.Leff + 3) continue;
+  TileInfo ti, tn;
+  int buf = 0;
+  auto fetch = [&](const TileInfo& t_, float* xu, float* dq) {
+    const int dmax = (t_.Leff + 2 < cm.T) ? t_.Leff + 2 : cm.T;
+    prefetch_rows(xu, cm.x, C, t_.b, cm.T, t_.t0, cm.T);
+    prefetch_rows(dq, cm.dq_dec, K, t_.b, cm.T, t_.t0, dmax);
+    prefetch_rows(dq + 8 * PT, cm.dq_prior, K, t_.b, cm.T, t_.t0, dmax);
+  };
+  int64_t tile = next_tile<3>(cm, blockIdx.x, ti);
+  if (tile >= 0) fetch(ti, XU0, DQ0);
+  cp_async_commit();
+  while (tile >= 0) {
+    const int64_t nxt = next_tile<3>(cm, tile + gridDim.x, tn);
+    if (nxt >= 0) fetch(tn, buf ? XU0 : XU1, buf ? DQ0 : DQ1);
+    cp_async_commit();
+    cp_async_wait_prev();
+    const float* XU = buf ? XU1 : XU0;
+    const float* DQ = buf ? DQ1 : DQ0;
     const int t0 = ti.t0, T = cm.T, L = ti.L;
-    const int64_t b = ti.b;
-    const int dmax = (ti.Leff + 2 < T) ? ti.Leff + 2 : T;
-    load_rows(XU, cm.x, C, b, T, t0, T);
-    for (int i = tid; i < K * NC; i += NTH) {
-      const int r = i / NC, j = i - r * NC, t = t0 - HL + j;
-      const int64_t o = (b * K + r) * (int64_t)T + t;
-      DQ[r * PT + j] = (t >= 0 && t < dmax) ? cm.dq_dec[o] + cm.dq_prior[o] : 0.f;
-    }
-    __syncthreads();
-    encoder_forward<CF>(W1s, b1s, W2s, b2s, W3s, b3s, XU, H1, H2b, LQ, t0, T);
+    __syncthreads(); PROF(0);
+    encoder_forward<CF>(W1s, b1s, W2s, b2s, W3s, b3s, XU, H1, H2b, LQ, t0, T); PROF(1);
     if (tid < NC) {    // d loss / d logits: softmax backward of dq plus the entropy term (:134-137)
       const int j = tid, t = t0 - HL + j;
       const bool inr = (j >= 2 && j < NC - 2 && t >= 0 && t < T);
@@ -553,7 +605,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_kernel(Common cm, vhmm_params 
 #pragma unroll
       for (int k = 0; k < K; ++k) {
         const float z = lg[k] - m;
-        qv[k] = expf(z) * inv; lq[k] = z - ls; dq[k] = DQ[k * PT + j];
+        qv[k] = expf(z) * inv; lq[k] = z - ls; dq[k] = DQ[k * PT + j] + DQ[(8 + k) * PT + j];
         sd += qv[k] * dq[k];
         Hh -= qv[k] * lq[k];
       }
@@ -564,15 +616,15 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_kernel(Common cm, vhmm_params 
         LQ[k * PT + j] = inr ? gk : 0.f;
       }
     }
-    __syncthreads();
+    __syncthreads(); PROF(2);
     // to_logits gradients: dW3[k][c] += sum_t dl[k][t] h2[c][t]
     for (int unit = w; unit < H2 / 8; unit += NW)
       gemm_time<1, 1, KST, J0, PT>(LQ, H2b + unit * 8 * PT, acc + CF::C_W3 + unit * 8, 0, CF::PW_H2);
     row_sums<J0, TT / 4, PT, NW>(LQ, K, acc + CF::C_B3);
-    __syncthreads();
+    __syncthreads(); PROF(3);
     // dh2 = relu'(h2) * W3^T dl, in place
     cols_op<H2, 1, 2, 1, 1, true>(W3s, 0, CF::PW_H2, LQ, EpiReluMask{H2b});
-    __syncthreads();
+    __syncthreads(); PROF(4);
     // conv2 gradients: dW2[tau][o][c] += sum_t dh2[o][t] h1[c][t+tau-1]
     for (int unit = w; unit < (H / 8) * (H2 / 16); unit += NW) {
       const int nt = unit % (H / 8), mh = unit / (H / 8);
@@ -580,19 +632,21 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_kernel(Common cm, vhmm_params 
                                    H2 * CF::PW_H, CF::PW_H);
     }
     row_sums<J0, TT / 4, PT, NW>(H2b, H2, acc + CF::C_B2);
-    __syncthreads();
+    __syncthreads(); PROF(5);
     // dh1 = relu'(h1) * conv3^T(dh2), in place
     cols_op<H, 2, 2, H2 / 8, 3, true>(W2s, H2 * CF::PW_H, CF::PW_H, H2b, EpiReluMask{H1});
-    __syncthreads();
+    __syncthreads(); PROF(6);
     // conv1 gradients: dW1[tau][o][c] += sum_t dh1[o][t] x[c][t+tau-1]
     for (int unit = w; unit < 3 * (H / 16); unit += NW) {
       const int mt = unit % (H / 16), tap = unit / (H / 16);
       gemm_time<1, 1, KST, J0, PT>(H1 + mt * 16 * PT, XU + tap - 1, acc + CF::C_W1 + tap * H * 8 + mt * 16 * 8, 0, 8);
     }
     row_sums<J0, TT / 4, PT, NW>(H1, H, acc + CF::C_B1);
-    __syncthreads();
+    __syncthreads(); PROF(7);
     if (++ndone % FLUSH == 0) flush_acc(part, acc, CF::ACC_C);
+    tile = nxt; ti = tn; buf ^= 1;
   }
+  PROF_DUMP("enc_bwd", 8);
   flush_acc(part, acc, CF::ACC_C);
 }
 

@@ -155,8 +155,58 @@ def elbo_norms(lengths_dev: torch.Tensor, B: int, C: int, T: int) -> torch.Tenso
     return torch.stack([(nv * C).clamp(min=1.0), torch.tensor(float(B), dtype=torch.float64, device=lengths_dev.device)])
 
 
+_stream_state = {}
+
+
+def elbo_raw_streamed(d: Dims, params, x, u, lengths_dev, norms, beta: float, want_grads: bool, chunk: int = 0):
+    """vhmm_elbo over a HOST-resident batch (pinned memory recommended): the batch is cut into
+    chunks of sequences that are copied host->device on a side stream while the previous chunk
+    computes (double-buffered staging, events both ways).  Sequences are independent and the
+    normalisers are global, so the un-normalised sums and the gradients of the chunks add up to
+    exactly the single-call result (up to fp32 summation order).  Chunks run in a fixed order."""
+    dev = lengths_dev.device
+    B, C, T = x.shape
+    U = u.shape[1]
+    if chunk <= 0:
+        chunk = max(1024, -(-B // 16))
+    chunk = min(chunk, B)
+    key = (dev.index, chunk, C, U, T)
+    st = _stream_state.get(key)
+    if st is None:
+        _stream_state.clear()           # one staging set at a time (it is hundreds of MB)
+        st = {"copy": torch.cuda.Stream(device=dev),
+              "buf": [(torch.empty(chunk, C, T, device=dev), torch.empty(chunk, U, T, device=dev)) for _ in range(2)],
+              "copied": [torch.cuda.Event(), torch.cuda.Event()], "done": [torch.cuda.Event(), torch.cuda.Event()]}
+        _stream_state[key] = st
+    cs = torch.cuda.current_stream(dev)
+    copy_s = st["copy"]
+    copy_s.wait_stream(cs)              # staging buffers may still be read by earlier work on the compute stream
+    sums_t = torch.zeros(4, device=dev, dtype=torch.float64)
+    grads_t = torch.zeros(param_count(d), device=dev, dtype=torch.float32) if want_grads else None
+    for i, b0 in enumerate(range(0, B, chunk)):
+        b1 = min(B, b0 + chunk)
+        n, k = b1 - b0, i % 2
+        xb, ub = st["buf"][k]
+        with torch.cuda.stream(copy_s):
+            if i >= 2:
+                copy_s.wait_event(st["done"][k])
+            xb[:n].copy_(x[b0:b1], non_blocking=True)
+            ub[:n].copy_(u[b0:b1], non_blocking=True)
+            st["copied"][k].record(copy_s)
+        cs.wait_event(st["copied"][k])
+        sums, grads = elbo_raw(d, params, xb[:n], ub[:n], lengths_dev[b0:b1], norms, beta, want_grads)
+        sums_t += sums
+        if want_grads:
+            grads_t += grads
+        st["done"][k].record(cs)
+    return sums_t, grads_t
+
+
 def elbo_raw(d: Dims, params, x, u, lengths_dev, norms, beta: float, want_grads: bool):
-    """One call of vhmm_elbo.  Returns (sums double[4] on device, flat grads or None)."""
+    """One call of vhmm_elbo.  Returns (sums double[4] on device, flat grads or None).
+    Host-resident x/u (CPU tensors, the model on a GPU) are streamed: elbo_raw_streamed."""
+    if x.device.type == "cpu" and u.device.type == "cpu" and lengths_dev.is_cuda:
+        return elbo_raw_streamed(d, params, _f32c(x), _f32c(u), lengths_dev, norms, beta, want_grads)
     x = _f32c(x); u = _f32c(u); _require_cuda(x, u, lengths_dev, norms)
     B, C, T = x.shape
     if C != d.C or u.shape != (B, d.U, T):

@@ -126,7 +126,10 @@ class VAE_HMM(nn.Module):
             raise ValueError('u required for non-stationary transitions')
         if u.dim() == 3 and u.shape[1] != self._dims.U and u.shape[2] == self._dims.U:
             u = u.permute(0, 2, 1)
-        lengths_dev = lengths.to(device=x.device, dtype=torch.int64)
+        # x, u may live in (pinned) host memory while the model is on a GPU: the batch is then streamed
+        # to the device chunk by chunk underneath the kernels (functional.elbo_raw_streamed)
+        dev = x.device if x.is_cuda else self.prior.log_prior.device
+        lengths_dev = lengths.to(device=dev, dtype=torch.int64)
         norms = Fn.elbo_norms(lengths_dev, B, C, T)
         if self.shard_group is not None:
             from . import parallel
