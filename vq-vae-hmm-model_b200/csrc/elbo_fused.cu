@@ -650,6 +650,9 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_kernel(Common cm, vhmm_params 
   flush_acc(part, acc, CF::ACC_C);
 }
 
+// kernels A and C with the encoder's 64->32 convolution on tcgen05: same interfaces and results
+#include "encoder_tc5.cuh"
+
 // =============================================================================================
 // small kernels around the three tile kernels
 // =============================================================================================
@@ -815,17 +818,22 @@ struct Launcher {
     cm.norms = norms; cm.beta = (float)beta; cm.log_pi = log_pi; cm.wfold = wfold;
     if (cm.ntiles < ncta) ncta = (int)cm.ntiles;
 
-    auto kA = enc_prior_kernel<CF>;
+    const bool tc5e = decoder_variant() == 2;
+    auto kA = tc5e ? enc_prior_tc5_kernel<CF> : enc_prior_kernel<CF>;
+    const size_t smA = tc5e ? t5e::Sz<CF>::A : (size_t)CF::SM_A * 4;
     const bool tc5v = decoder_variant() == 2;
     auto kB = tc5v ? decoder_tc5_kernel<CF> : decoder_kernel<CF>;
     const size_t smB = tc5v ? t5::Lay<CF>::BYTES : (size_t)CF::SM_B * 4;
-    auto kC = enc_bwd_kernel<CF>;
+    auto kC = tc5e ? enc_bwd_tc5_kernel<CF> : enc_bwd_kernel<CF>;
+    const size_t smC = tc5e ? t5e::Sz<CF>::C : (size_t)CF::SM_C * 4;
     static bool attr_done = false;   // idempotent: a racing second caller sets the same values
     if (!attr_done) {
-      VHMM_CUDA_CHECK(cudaFuncSetAttribute(kA, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SM_A * 4));
+      VHMM_CUDA_CHECK(cudaFuncSetAttribute(enc_prior_kernel<CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SM_A * 4));
+      VHMM_CUDA_CHECK(cudaFuncSetAttribute(enc_prior_tc5_kernel<CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5e::Sz<CF>::A));
+      VHMM_CUDA_CHECK(cudaFuncSetAttribute(enc_bwd_tc5_kernel<CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5e::Sz<CF>::C));
       VHMM_CUDA_CHECK(cudaFuncSetAttribute(decoder_kernel<CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SM_B * 4));
       VHMM_CUDA_CHECK(cudaFuncSetAttribute(decoder_tc5_kernel<CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5::Lay<CF>::BYTES));
-      VHMM_CUDA_CHECK(cudaFuncSetAttribute(kC, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SM_C * 4));
+      VHMM_CUDA_CHECK(cudaFuncSetAttribute(enc_bwd_kernel<CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SM_C * 4));
       attr_done = true;
     }
     VHMM_CUDA_CHECK(cudaMemsetAsync(cm.loss_part, 0, (size_t)ncta * LP * 8, st));
@@ -837,14 +845,14 @@ struct Launcher {
     cudaEvent_t* tev = nullptr;
     if (g_timing.enabled && grads && g_timing.ncalls < TIMING_SLOTS) tev = g_timing.ev[g_timing.ncalls++];
     if (tev) VHMM_CUDA_CHECK(cudaEventRecord(tev[0], st));
-    kA<<<ncta, NTH, CF::SM_A * 4, st>>>(cm, P);
+    kA<<<ncta, NTH, smA, st>>>(cm, P);
     VHMM_LAUNCH_CHECK();
     if (tev) VHMM_CUDA_CHECK(cudaEventRecord(tev[1], st));
     if (grads) {
       kB<<<ncta, NTH, smB, st>>>(cm, P);
       VHMM_LAUNCH_CHECK();
       if (tev) VHMM_CUDA_CHECK(cudaEventRecord(tev[2], st));
-      kC<<<ncta, NTH, CF::SM_C * 4, st>>>(cm, P);
+      kC<<<ncta, NTH, smC, st>>>(cm, P);
       VHMM_LAUNCH_CHECK();
       if (tev) VHMM_CUDA_CHECK(cudaEventRecord(tev[3], st));
       reduce_acc_kernel<<<(unsigned)cdiv(CF::ACC_ALL, 256), 256, 0, st>>>(cm.acc_part, ncta, CF::ACC_ALL, red);
