@@ -172,6 +172,16 @@ int vhmm_hmm_posterior(const float* log_pi, const float* log_A, const float* log
                        const int64_t* lengths, int64_t B, int64_t T, int64_t K, float* loglik,
                        float* gamma, float* xi, void* workspace, size_t workspace_bytes,
                        void* stream);
+/* vhmm_hmm_posterior / vhmm_hmm_decode have two builds for K <= 4:
+ *   VHMM_POSTERIOR_ONEPASS  one warp per sequence, the sequence resident in shared memory, time
+ *                           parallelised over the lanes (chunk products + warp scan): inputs and
+ *                           outputs cross HBM once (60 B/step for gamma, 96 with xi).  Needs
+ *                           T*K % 4 == 0, 16-byte aligned tensors and T <= 512 (K=3).
+ *   VHMM_POSTERIOR_SWEEP    forward sweep (alpha_hat stash) + backward sweep, one thread per
+ *                           sequence: any T, 132 B/step of traffic.
+ * AUTO (default) = ONEPASS when it applies; environment VHMM_POSTERIOR=sweep overrides AUTO. */
+enum { VHMM_POSTERIOR_AUTO = 0, VHMM_POSTERIOR_SWEEP = 1 };
+int vhmm_hmm_posterior_select(int variant);
 /* B.4: Viterbi, uint8 back-pointers, lowest-index tie-break.  path (B,T) uint8, score (B). */
 int vhmm_viterbi(const float* log_pi, const float* log_A, const float* log_b,
                  const int64_t* lengths, int64_t B, int64_t T, int64_t K, uint8_t* path,

@@ -43,6 +43,7 @@ int hmm_posterior(const float*, const float*, const float*, const int64_t*, int6
 int hmm_viterbi(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, void*, size_t, cudaStream_t);
 int hmm_decode(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, float*, void*, size_t, cudaStream_t);
 int hmm_scan(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
+int hmm_posterior_select(int mode);
 
 static std::atomic<int> g_elbo_impl{VHMM_ELBO_AUTO};
 static int elbo_impl_for(const vhmm_dims& d) {
@@ -149,6 +150,10 @@ int vhmm_elbo_select(int impl) {
 int vhmm_elbo_decoder_select(int variant) {
   ARG(variant == VHMM_DECODER_AUTO || variant == VHMM_DECODER_MMA || variant == VHMM_DECODER_TC5, "variant");
   return fused_decoder_select(variant);
+}
+int vhmm_hmm_posterior_select(int variant) {
+  ARG(variant == VHMM_POSTERIOR_AUTO || variant == VHMM_POSTERIOR_SWEEP, "variant");
+  return hmm_posterior_select(variant);
 }
 int vhmm_elbo_decoder_active(void) { return fused_decoder_active(); }
 

@@ -3,6 +3,8 @@
 // (hmm_generic.cuh), workspace carving, emission log-probabilities.
 #include "hmm_generic.cuh"
 #include "hmm_scan.cuh"
+#include "hmm_warp.cuh"
+#include <stdlib.h>
 
 namespace vhmm {
 
@@ -100,6 +102,68 @@ static int launch_bwd_small(const hs::Args& a, cudaStream_t st) {
     default: rc = VHMM_E_DIMS;                               \
   }
 
+
+// ---- one-pass posterior (hmm_warp.cuh): whole sequence in shared memory, one warp each ------
+static int g_posterior_mode = -1;   // -1: from env VHMM_POSTERIOR (onepass|sweep), 0 auto, 1 sweep only
+int hmm_posterior_select(int mode) { g_posterior_mode = mode; return 0; }
+static bool onepass_allowed() {
+  if (g_posterior_mode < 0) {
+    const char* e = getenv("VHMM_POSTERIOR");
+    g_posterior_mode = (e && e[0] == 's') ? 1 : 0;
+  }
+  return g_posterior_mode == 0;
+}
+constexpr size_t HW_MAX_WARP_BYTES = 28 * 1024;   // >= 8 resident warps per SM
+static bool onepass_fits(int64_t T, int64_t K, const void* A, const void* Bm, const void* gamma, const void* xi) {
+  if (!small_k(K) || T < 1 || ((T * K) & 3) != 0) return false;
+  if (!aligned16(A) || !aligned16(Bm) || !aligned16(gamma) || (xi && !aligned16(xi))) return false;
+  const int S = 4 * (int)cdiv(T, 128);
+  const size_t wb = 32 * (size_t)(hw::pitch_odd16(S * (int)(K * K)) + hw::pitch_odd16(S * (int)K)) * 4;
+  return wb <= HW_MAX_WARP_BYTES;
+}
+template <int K, bool XI>
+static int launch_onepass(hw::Args a, cudaStream_t st) {
+  auto kern = hw::posterior_kernel<K, XI>;
+  const size_t wb = 32 * (size_t)(a.SA + a.SB) * 4;
+  int wpb = (int)((56 * 1024) / wb);
+  wpb = wpb < 1 ? 1 : (wpb > 4 ? 4 : wpb);
+  const size_t smem = wb * wpb;
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    VHMM_CUDA_CHECK(cudaGetDevice(&dev));
+    VHMM_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  VHMM_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  VHMM_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+  int per_sm = 0;
+  VHMM_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, wpb * 32, smem));
+  if (per_sm < 1) per_sm = 1;
+  int64_t grid = (int64_t)sms * per_sm;
+  const int64_t need = cdiv(a.B, wpb);
+  if (grid > need) grid = need;
+  kern<<<(unsigned)grid, wpb * 32, smem, st>>>(a);
+  VHMM_LAUNCH_CHECK();
+  return 0;
+}
+static int hmm_posterior_onepass(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths,
+                                 int64_t B, int64_t T, int64_t K, float* loglik, float* gamma, float* xi,
+                                 cudaStream_t st) {
+  hw::Args a{};
+  a.log_pi = log_pi; a.A = A; a.Bm = Bm; a.lengths = lengths; a.B = B; a.T = T;
+  a.S = 4 * (int)cdiv(T, 128);
+  a.SA = hw::pitch_odd16(a.S * (int)(K * K));
+  a.SB = hw::pitch_odd16(a.S * (int)K);
+  const uint64_t ga = (uint64_t)a.S * K * K / 4, gb = (uint64_t)a.S * K / 4;
+  a.magicA = (unsigned)(((1ull << 32) + ga - 1) / ga);
+  a.magicB = (unsigned)(((1ull << 32) + gb - 1) / gb);
+  a.loglik = loglik; a.gamma = gamma; a.xi = xi;
+  int rc = 0;
+  if (xi) { DISPATCH_K(K, (rc = launch_onepass<KK, true>(a, st))); }
+  else    { DISPATCH_K(K, (rc = launch_onepass<KK, false>(a, st))); }
+  return rc;
+}
+
 static hs::Args base_args(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths,
                           int64_t B, int64_t T, int64_t K) {
   hs::Args a{};
@@ -134,6 +198,8 @@ int hmm_forward(const float* log_pi, const float* A, const float* Bm, const int6
 int hmm_posterior(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B,
                   int64_t T, int64_t K, float* loglik, float* gamma, float* xi, void* ws, size_t ws_bytes,
                   cudaStream_t st) {
+  if (onepass_allowed() && onepass_fits(T, K, A, Bm, gamma, xi))
+    return hmm_posterior_onepass(log_pi, A, Bm, lengths, B, T, K, loglik, gamma, xi, st);
   Arena ar(ws, ws_bytes);
   float* stash = ar.take<float>((size_t)B * T * K);
   VHMM_REQUIRE(ar.ok, VHMM_E_WORKSPACE, "hmm_posterior: workspace %zu < %zu", ws_bytes, ar.used);
@@ -184,6 +250,16 @@ int hmm_decode(const float* log_pi, const float* A, const float* Bm, const int64
   float* stash = ar.take<float>((size_t)B * T * K);
   uint8_t* psi = ar.take<uint8_t>((size_t)B * T * psi_bytes(K));
   VHMM_REQUIRE(ar.ok, VHMM_E_WORKSPACE, "hmm_decode: workspace %zu < %zu", ws_bytes, ar.used);
+  if (small_k(K) && onepass_allowed() && onepass_fits(T, K, A, Bm, gamma, nullptr)) {
+    // Viterbi sweep (49 B/step) + one-pass posterior (60 B/step): 109 B/step of traffic against
+    // 181 B/step for the fused forward sweep + backward sweep below
+    hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
+    a.psi = psi; a.path = path; a.score = nullptr;
+    int rc = 0;
+    DISPATCH_K(K, (rc = launch_fwd_small<KK, false, true>(a, st)));
+    if (rc) return rc;
+    return hmm_posterior_onepass(log_pi, A, Bm, lengths, B, T, K, loglik, gamma, nullptr, st);
+  }
   if (small_k(K)) {
     // one forward sweep computes alpha_hat AND the Viterbi back-pointers from the same staged
     // inputs; the backward sweep then produces gamma.

@@ -1,0 +1,452 @@
+// hmm_warp.cuh -- one-pass posteriors (gamma, xi, log-likelihood) for small K: one WARP per
+// sequence, the whole sequence resident in shared memory, time parallelised over the lanes.
+//
+// Why: the two-sweep kernels of hmm_small.cuh move 132 B per step for 60 algorithmic bytes
+// (inputs read twice, alpha_hat stash written and read).  Here every input byte crosses HBM
+// once and every output byte once (gamma 60 B/step, gamma+xi 96 B/step).
+//
+// Lane l owns the S consecutive steps [l*S, l*S+S), S = 4*ceil(T/128).  Per sequence:
+//   load   cp.async (16 B, coalesced over the warp) of log_A / log_b into per-lane chunks whose
+//          pitches are odd multiples of 16 B, so that each lane reads its own chunk back with
+//          conflict-free LDS.128.
+//   pass 1 P_t[i,j] = exp(log_A_t[i,j] + log_b_t[j] - max_j log_b_t) written back in place
+//          (the exps are paid once); chunk product M_l = prod_t P_t, rescaled by powers of two.
+//          Step 0 has no transition: P_0 = I and v0 = pi * b~_0 enters as the start vector.
+//   scan   Kogge-Stone over the lanes: prefix products (forward start vector of every chunk,
+//          log-likelihood from the tracked exponents) and suffix products (backward start vector).
+//   pass 2 forward sweep inside the chunk: alpha_hat_t stored over the log_b slots.
+//   pass 3 backward sweep: gamma_t (over the alpha_hat slot), xi_t (over the P_t slot), beta_hat.
+//   store  coalesced 16-byte stores of the gamma / xi rows (zeros for t >= L).
+// All arithmetic is on non-negative numbers (no cancellation); rescaling is by exact powers of
+// two.  Maths: SURVEY.md Appendix B.2/B.3; conventions of oracle/hmm.py:posteriors.
+#pragma once
+#include "hmm_small.cuh"
+
+namespace vhmm {
+namespace hw {
+
+struct Args {
+  const float* log_pi;
+  const float* A;          // (B,T,K,K)
+  const float* Bm;         // (B,T,K)
+  const int64_t* lengths;  // (B)
+  int64_t B, T;
+  int S;                   // steps per lane, multiple of 4, 32*S >= T
+  int SA, SB;              // per-lane chunk pitches (floats) of the A / b regions
+  unsigned magicA, magicB; // ceil(2^32 / granules per chunk)
+  float* loglik;           // (B) or null
+  float* gamma;            // (B,T,K)
+  float* xi;               // (B,T,K,K) or null (XI kernels only)
+};
+
+__host__ __device__ constexpr int pitch_odd16(int n) { return (((n >> 2) & 1) == 0) ? n + 4 : n; }
+
+// 2^-e with e = floor(log2(m)) (m > 0, finite, < 2^127); *ex += e
+__device__ __forceinline__ float pow2_rescale(float m, int* ex) {
+  const unsigned b = __float_as_uint(m) & 0x7f800000u;
+  *ex += (int)(b >> 23) - 127;
+  return __uint_as_float(0x7f000000u - b);
+}
+__device__ __forceinline__ float pow2_rescale(float m) {
+  const unsigned b = __float_as_uint(m) & 0x7f800000u;
+  return __uint_as_float(0x7f000000u - b);
+}
+template <int N>
+__device__ __forceinline__ float max_of(const float* v) {
+  float m = v[0];
+#pragma unroll
+  for (int i = 1; i < N; ++i) m = fmaxf(m, v[i]);
+  return m;
+}
+__device__ __forceinline__ float ex2f(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// R = X * Y (K x K)
+template <int K>
+__device__ __forceinline__ void mat_mul(float* R, const float* X, const float* Y) {
+#pragma unroll
+  for (int i = 0; i < K; ++i)
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+      float acc = X[i * K] * Y[j];
+#pragma unroll
+      for (int k = 1; k < K; ++k) acc = fmaf(X[i * K + k], Y[k * K + j], acc);
+      R[i * K + j] = acc;
+    }
+}
+
+template <int N>
+__device__ __forceinline__ void lds4(const float* p, float* v) {
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    const float4 q = *reinterpret_cast<const float4*>(p + i * 4);
+    v[i * 4 + 0] = q.x; v[i * 4 + 1] = q.y; v[i * 4 + 2] = q.z; v[i * 4 + 3] = q.w;
+  }
+}
+template <int N>
+__device__ __forceinline__ void sts4(float* p, const float* v) {
+#pragma unroll
+  for (int i = 0; i < N; ++i)
+    *reinterpret_cast<float4*>(p + i * 4) = make_float4(v[i * 4], v[i * 4 + 1], v[i * 4 + 2], v[i * 4 + 3]);
+}
+
+template <int K, bool XI>
+__global__ void __launch_bounds__(128) posterior_kernel(Args a) {
+  constexpr int KK = K * K;
+  constexpr float LOG2E = 1.4426950408889634f, LN2 = 0.6931471805599453f;
+  extern __shared__ __align__(16) float smem[];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  const int S = a.S, SA = a.SA, SB = a.SB;
+  float* regA = smem + (size_t)wib * 32 * (SA + SB);
+  float* regB = regA + 32 * SA;
+  float* myA = regA + lane * SA;
+  float* myB = regB + lane * SB;
+  const int T = (int)a.T;
+  const int t0 = lane * S;
+  const int GA = S * KK / 4, GB = S * K / 4;   // 16-byte granules per chunk
+  const int rowGA = T * KK / 4, rowGB = T * K / 4;
+  float pi[K];
+#pragma unroll
+  for (int j = 0; j < K; ++j) pi[j] = a.log_pi[j] * LOG2E;
+
+  const int64_t nwarps = (int64_t)gridDim.x * wpb;
+  for (int64_t b = (int64_t)blockIdx.x * wpb + wib; b < a.B; b += nwarps) {
+    int64_t Ll = a.lengths[b];
+    const int L = (int)(Ll < 0 ? 0 : (Ll > a.T ? a.T : Ll));
+    const int nv = max(0, min(S, L - t0));          // valid steps of my chunk
+    // ---- load: granules that hold a valid step --------------------------------------
+    {
+      const float* gA = a.A + b * (int64_t)T * KK;
+      const float* gB = a.Bm + b * (int64_t)T * K;
+      const int nA = (L * KK + 3) >> 2, nB = (L * K + 3) >> 2;
+      for (int g = lane; g < nA; g += 32) {
+        const int c = (int)__umulhi((unsigned)g, a.magicA);
+        hs::cp_async16(regA + c * SA + (g - c * GA) * 4, gA + (int64_t)g * 4);
+      }
+      for (int g = lane; g < nB; g += 32) {
+        const int c = (int)__umulhi((unsigned)g, a.magicB);
+        hs::cp_async16(regB + c * SB + (g - c * GB) * 4, gB + (int64_t)g * 4);
+      }
+      hs::cp_commit();
+      hs::cp_wait<0>();
+      __syncwarp();
+    }
+    // ---- pass 1: P_t in place, chunk product ----------------------------------------
+    float M[KK];
+#pragma unroll
+    for (int i = 0; i < KK; ++i) M[i] = (i / K == i % K) ? 1.f : 0.f;
+    int ex = 0;
+    float mbsum = 0.f;
+    float v0[K];
+#pragma unroll
+    for (int j = 0; j < K; ++j) v0[j] = 0.f;
+    for (int g = 0; g * 4 < nv; ++g) {
+      float Av[4 * KK], Bv[4 * K];
+      lds4<KK>(myA + g * 4 * KK, Av);
+      lds4<K>(myB + g * 4 * K, Bv);
+#pragma unroll
+      for (int s = 0; s < 4; ++s) {
+        float* la = Av + s * KK;
+        const float* lb = Bv + s * K;
+        if (g * 4 + s < nv) {
+          const float mb = max_of<K>(lb);
+          mbsum += mb;
+          float cj[K];
+#pragma unroll
+          for (int j = 0; j < K; ++j) cj[j] = (lb[j] - mb) * LOG2E;
+          if (t0 + g * 4 + s == 0) {
+#pragma unroll
+            for (int j = 0; j < K; ++j) v0[j] = ex2f(pi[j] + cj[j]);
+#pragma unroll
+            for (int i = 0; i < KK; ++i) la[i] = (i / K == i % K) ? 1.f : 0.f;
+          } else {
+#pragma unroll
+            for (int i = 0; i < K; ++i)
+#pragma unroll
+              for (int j = 0; j < K; ++j) la[i * K + j] = ex2f(fmaf(la[i * K + j], LOG2E, cj[j]));
+            float R[KK];
+            mat_mul<K>(R, M, la);
+#pragma unroll
+            for (int i = 0; i < KK; ++i) M[i] = R[i];
+          }
+        }
+        if (s & 1) {
+          const float sc = pow2_rescale(max_of<KK>(M), &ex);
+#pragma unroll
+          for (int i = 0; i < KK; ++i) M[i] *= sc;
+        }
+      }
+      sts4<KK>(myA + g * 4 * KK, Av);
+    }
+    // ---- scan over the lanes ---------------------------------------------------------
+    // prefix: lane 0 contributes the rank-one matrix 1 * (v0 M_0), so that every prefix has
+    // identical rows = v0 M_0 ... M_l; only row 0 is carried.
+    float pre[K];
+    int pex = ex;
+    {
+      float Pm[KK];
+      if (lane == 0) {
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+          float acc = v0[0] * M[j];
+#pragma unroll
+          for (int k = 1; k < K; ++k) acc = fmaf(v0[k], M[k * K + j], acc);
+          pre[j] = acc;
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < KK; ++i) Pm[i] = M[i];
+      // vector-times-matrix scan: lane l holds (pre_l, Pm_l); combining the segment ending at
+      // l-d with the segment ending at l: pre <- pre_other * Pm_l, Pm <- Pm_other * Pm_l.
+      // Lanes whose segment already starts at lane 0 (lane < d) are final.
+      bool has = (lane == 0);   // 'pre' valid (segment reaches lane 0)
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        float opre[K], oPm[KK];
+#pragma unroll
+        for (int j = 0; j < K; ++j) opre[j] = __shfl_up_sync(0xffffffffu, pre[j], d);
+#pragma unroll
+        for (int i = 0; i < KK; ++i) oPm[i] = __shfl_up_sync(0xffffffffu, Pm[i], d);
+        const int oex = __shfl_up_sync(0xffffffffu, pex, d);
+        const bool ohas = __shfl_up_sync(0xffffffffu, (int)has, d) != 0;
+        if (lane >= d && !has) {
+          pex += oex;
+          if (ohas) {
+#pragma unroll
+            for (int j = 0; j < K; ++j) {
+              float acc = opre[0] * Pm[j];
+#pragma unroll
+              for (int k = 1; k < K; ++k) acc = fmaf(opre[k], Pm[k * K + j], acc);
+              pre[j] = acc;
+            }
+            has = true;
+            const float sc = pow2_rescale(fmaxf(max_of<K>(pre), 1e-37f), &pex);
+#pragma unroll
+            for (int j = 0; j < K; ++j) pre[j] *= sc;
+          } else {
+            float R[KK];
+            mat_mul<K>(R, oPm, Pm);
+            const float sc = pow2_rescale(fmaxf(max_of<KK>(R), 1e-37f), &pex);
+#pragma unroll
+            for (int i = 0; i < KK; ++i) Pm[i] = R[i] * sc;
+          }
+        }
+      }
+    }
+    // suffix: only the row sums (suffix product applied to the all-ones vector) are needed:
+    // w_l = M_l M_{l+1} ... M_31 1.  Carry (w, Sm) with Sm the segment product.
+    float suf[K];
+    {
+      float Sm[KK];
+#pragma unroll
+      for (int i = 0; i < KK; ++i) Sm[i] = M[i];
+      bool has = (lane == 31);
+#pragma unroll
+      for (int i = 0; i < K; ++i) {
+        float acc = M[i * K];
+#pragma unroll
+        for (int j = 1; j < K; ++j) acc += M[i * K + j];
+        suf[i] = acc;
+      }
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        float osuf[K], oSm[KK];
+#pragma unroll
+        for (int j = 0; j < K; ++j) osuf[j] = __shfl_down_sync(0xffffffffu, suf[j], d);
+#pragma unroll
+        for (int i = 0; i < KK; ++i) oSm[i] = __shfl_down_sync(0xffffffffu, Sm[i], d);
+        const bool ohas = __shfl_down_sync(0xffffffffu, (int)has, d) != 0;
+        if (lane + d < 32 && !has) {
+          if (ohas) {
+#pragma unroll
+            for (int i = 0; i < K; ++i) {
+              float acc = Sm[i * K] * osuf[0];
+#pragma unroll
+              for (int k = 1; k < K; ++k) acc = fmaf(Sm[i * K + k], osuf[k], acc);
+              suf[i] = acc;
+            }
+            has = true;
+            const float sc = pow2_rescale(fmaxf(max_of<K>(suf), 1e-37f));
+#pragma unroll
+            for (int j = 0; j < K; ++j) suf[j] *= sc;
+          } else {
+            float R[KK];
+            mat_mul<K>(R, Sm, oSm);
+            const float sc = pow2_rescale(fmaxf(max_of<KK>(R), 1e-37f));
+#pragma unroll
+            for (int i = 0; i < KK; ++i) Sm[i] = R[i] * sc;
+          }
+        }
+      }
+    }
+    // log-likelihood: lane 31 holds v0 M_0 ... M_31 (scaled by 2^-pex)
+    if (a.loglik) {
+      double ms = warp_sum((double)mbsum);
+      if (lane == 31) {
+        float s = pre[0];
+#pragma unroll
+        for (int j = 1; j < K; ++j) s += pre[j];
+        a.loglik[b] = (L > 0) ? (float)((double)logf(s) + (double)pex * (double)LN2 + ms) : 0.f;
+      }
+    }
+    // start vectors of my chunk
+    float fin[K], bin[K];
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+      const float f = __shfl_up_sync(0xffffffffu, pre[j], 1);
+      const float w = __shfl_down_sync(0xffffffffu, suf[j], 1);
+      fin[j] = (lane == 0) ? v0[j] : f;
+      bin[j] = (lane == 31) ? 1.f : w;
+    }
+    {
+      const float sf = pow2_rescale(fmaxf(max_of<K>(fin), 1e-37f));
+      const float sb = pow2_rescale(fmaxf(max_of<K>(bin), 1e-37f));
+#pragma unroll
+      for (int j = 0; j < K; ++j) { fin[j] *= sf; bin[j] *= sb; }
+    }
+    // ---- pass 2: forward sweep, alpha_hat over the log_b slots -------------------------
+    {
+      float al[K];
+#pragma unroll
+      for (int j = 0; j < K; ++j) al[j] = fin[j];
+      for (int g = 0; g * 4 < nv; ++g) {
+        float Av[4 * KK], Ov[4 * K];
+        lds4<KK>(myA + g * 4 * KK, Av);
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+          const float* P = Av + s * KK;
+          if (g * 4 + s < nv) {
+            float n[K];
+#pragma unroll
+            for (int j = 0; j < K; ++j) {
+              float acc = al[0] * P[j];
+#pragma unroll
+              for (int k = 1; k < K; ++k) acc = fmaf(al[k], P[k * K + j], acc);
+              n[j] = acc;
+            }
+            const float sc = pow2_rescale(fmaxf(max_of<K>(n), 1e-37f));
+#pragma unroll
+            for (int j = 0; j < K; ++j) al[j] = n[j] * sc;
+          }
+#pragma unroll
+          for (int j = 0; j < K; ++j) Ov[s * K + j] = al[j];
+        }
+        sts4<K>(myB + g * 4 * K, Ov);
+      }
+    }
+    // ---- pass 3: backward sweep: gamma, xi, beta_hat ------------------------------------
+    {
+      float bh[K];
+#pragma unroll
+      for (int j = 0; j < K; ++j) bh[j] = bin[j];
+      const int cap = max(0, min(S, T - t0));        // steps of my chunk that exist
+      for (int g = (cap + 3) / 4 - 1; g >= 0; --g) {
+        float Gv[4 * K];
+        if (g * 4 >= nv) {
+          // group entirely beyond the sequence length: zeros
+#pragma unroll
+          for (int i = 0; i < 4 * K; ++i) Gv[i] = 0.f;
+          sts4<K>(myB + g * 4 * K, Gv);
+          if (XI) {
+            float Z[4 * KK];
+#pragma unroll
+            for (int i = 0; i < 4 * KK; ++i) Z[i] = 0.f;
+            sts4<KK>(myA + g * 4 * KK, Z);
+          }
+          continue;
+        }
+        float Av[4 * KK], Hv[4 * K], prev[K];
+        lds4<KK>(myA + g * 4 * KK, Av);
+        lds4<K>(myB + g * 4 * K, Hv);
+        if (XI) {
+          // alpha_hat of the step before this group
+          if (g == 0) {
+#pragma unroll
+            for (int j = 0; j < K; ++j) prev[j] = fin[j];
+          } else {
+#pragma unroll
+            for (int j = 0; j < K; ++j) prev[j] = myB[g * 4 * K - K + j];
+          }
+        }
+#pragma unroll
+        for (int s = 3; s >= 0; --s) {
+          float* P = Av + s * KK;
+          float* gm = Gv + s * K;
+          if (g * 4 + s >= nv) {
+#pragma unroll
+            for (int j = 0; j < K; ++j) gm[j] = 0.f;
+            if (XI) {
+#pragma unroll
+              for (int i = 0; i < KK; ++i) P[i] = 0.f;
+            }
+            continue;
+          }
+          const float* ah = Hv + s * K;
+          float gs = 0.f;
+#pragma unroll
+          for (int j = 0; j < K; ++j) { gm[j] = ah[j] * bh[j]; gs += gm[j]; }
+          const float ginv = __frcp_rn(gs);
+#pragma unroll
+          for (int j = 0; j < K; ++j) gm[j] *= ginv;
+          float nb[K];
+#pragma unroll
+          for (int i = 0; i < K; ++i) {
+            float acc = P[i * K] * bh[0];
+#pragma unroll
+            for (int j = 1; j < K; ++j) acc = fmaf(P[i * K + j], bh[j], acc);
+            nb[i] = acc;
+          }
+          if (XI) {
+            if (t0 + g * 4 + s == 0) {
+#pragma unroll
+              for (int i = 0; i < KK; ++i) P[i] = 0.f;
+            } else {
+              const float* ap = (s == 0) ? prev : (Hv + (s - 1) * K);
+              float xs = 0.f;
+#pragma unroll
+              for (int i = 0; i < K; ++i)
+#pragma unroll
+                for (int j = 0; j < K; ++j) {
+                  P[i * K + j] = ap[i] * P[i * K + j] * bh[j];
+                  xs += P[i * K + j];
+                }
+              const float xinv = __frcp_rn(xs);
+#pragma unroll
+              for (int i = 0; i < KK; ++i) P[i] *= xinv;
+            }
+          }
+          const float sc = pow2_rescale(fmaxf(max_of<K>(nb), 1e-37f));
+#pragma unroll
+          for (int j = 0; j < K; ++j) bh[j] = nb[j] * sc;
+        }
+        sts4<K>(myB + g * 4 * K, Gv);
+        if (XI) sts4<KK>(myA + g * 4 * KK, Av);
+      }
+    }
+    __syncwarp();
+    // ---- store: coalesced rows ------------------------------------------------------
+    {
+      float* gG = a.gamma + b * (int64_t)T * K;
+      for (int g = lane; g < rowGB; g += 32) {
+        const int c = (int)__umulhi((unsigned)g, a.magicB);
+        const float4 v = *reinterpret_cast<const float4*>(regB + c * SB + (g - c * GB) * 4);
+        __stcs(reinterpret_cast<float4*>(gG) + g, v);
+      }
+      if (XI) {
+        float* gX = a.xi + b * (int64_t)T * KK;
+        for (int g = lane; g < rowGA; g += 32) {
+          const int c = (int)__umulhi((unsigned)g, a.magicA);
+          const float4 v = *reinterpret_cast<const float4*>(regA + c * SA + (g - c * GA) * 4);
+          __stcs(reinterpret_cast<float4*>(gX) + g, v);
+        }
+      }
+    }
+    __syncwarp();
+  }
+}
+
+}  // namespace hw
+}  // namespace vhmm

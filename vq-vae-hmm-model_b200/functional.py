@@ -242,6 +242,13 @@ def elbo_decoder_select(variant: str = "auto"):
     check(_lib.lib().vhmm_elbo_decoder_select(code), "vhmm_elbo_decoder_select")
 
 
+def hmm_posterior_select(variant: str = "auto"):
+    """Posterior kernels for K <= 4: "auto" (one-pass warp kernel when it applies) | "sweep"
+    (forward + backward sweep, one thread per sequence).  include/vhmm.h."""
+    code = {"auto": 0, "sweep": 1}[variant]
+    check(_lib.lib().vhmm_hmm_posterior_select(code), "vhmm_hmm_posterior_select")
+
+
 def elbo_decoder_active() -> str:
     return {_lib.DECODER_MMA: "mma", _lib.DECODER_TC5: "tc5"}[int(_lib.lib().vhmm_elbo_decoder_active())]
 
