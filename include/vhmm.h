@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define VHMM_VERSION 100 /* major*100 + minor */
+#define VHMM_VERSION 101 /* major*100 + minor */
 #define VHMM_NUM_PARAMS 18
 #define VHMM_PAD_STATE 255 /* Viterbi path value for t >= lengths[b] */
 
@@ -153,6 +153,34 @@ int vhmm_elbo_timing_read(double* ms_sum_host /*[3]*/, int* ncalls_host);
  * regimes int64 (B,T), lowest index on ties. */
 int vhmm_argmax_regimes(const float* q, int64_t B, int64_t K, int64_t T, int64_t* regimes,
                         void* stream);
+
+/* ---- callers either side of the ELBO path ---- */
+
+/* f1: device-side batching.  Replaces RandomChunkDataset.__getitem__'s slicing and collate_fn's
+ * 2B slice copies (VQ_VAE_HMM_fixed.py:20-29, :164-179; src/utils/data.py:7-44) by one gather from
+ * a corpus resident in HBM: x_cat (C,S_tot), u_cat (U,S_tot) = the sequences concatenated along
+ * time.  col0[b] = absolute first column of item b (sequence offset + start), lengths[b] its
+ * length; T = max length (the caller knows it: lengths are produced on the host, :165).
+ * x_out (B,C,T), u_out (B,U,T): out[b,r,t] = t < lengths[b] ? cat[r, col0[b]+t] : 0. */
+int vhmm_gather_chunks(const float* x_cat, const float* u_cat, int64_t S_tot, int64_t C, int64_t U,
+                       const int64_t* col0, const int64_t* lengths, int64_t B, int64_t T,
+                       float* x_out, float* u_out, void* stream);
+
+/* f2: optimiser tail of train_model (VQ_VAE_HMM_fixed.py:146,:155-157) and Trainer.train_epoch
+ * (src/training/trainer.py:24-34): torch.optim.Adam (no weight decay, no amsgrad) over the 18
+ * parameter tensors from the FLAT gradient buffer of vhmm_elbo, optionally preceded by
+ * clip_grad_norm_(max_norm) (trainer.py:31; max_norm <= 0: none).  grads are multiplied by
+ * *grad_scale first when grad_scale != NULL (device float; the upstream d loss).  exp_avg /
+ * exp_avg_sq: flat fp32 state, same layout as grads.  step = 1 for the first update.
+ * grad_norm_out (device float, or NULL) receives the global L2 norm before clipping.  scratch:
+ * 8 bytes of device memory (needed when clipping or grad_norm_out is requested). */
+typedef struct vhmm_params_mut {
+  float* p[VHMM_NUM_PARAMS];
+} vhmm_params_mut;
+int vhmm_adam_step(const vhmm_dims* dims, const vhmm_params_mut* params, const float* grads,
+                   float* exp_avg, float* exp_avg_sq, double lr, double beta1, double beta2,
+                   double eps, int64_t step, const float* grad_scale, double max_norm,
+                   float* grad_norm_out, double* scratch, void* stream);
 
 /* ---- exact-HMM stages: extensions, absent from the reference ---- */
 

@@ -1,0 +1,166 @@
+"""GPU tests of the callers either side of the path: f1 device-side batching
+(vhmm_gather_chunks) bit-exact against batches the real reference RandomChunkDataset + collate_fn
+produced (tests/golden/collate_stream.npz, base_collate.npz), f2 the fused Adam / clip step
+(vhmm_adam_step) against parameters the reference's own training loop produced
+(tests/golden/train_adam.npz, train_clip.npz) and against torch.optim.Adam on the same gradients."""
+import os
+import random
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN, load_golden, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def _stream_corpus():
+    z = np.load(os.path.join(GOLDEN, "collate_stream.npz"))
+    g = torch.Generator().manual_seed(77)
+    lens = [int(n) for n in z["lens"]]
+    xs = [torch.randn(5, n, generator=g) for n in lens]
+    us = [torch.randn(4, n, generator=g) for n in lens]
+    return z, xs, us
+
+
+def test_gather_matches_reference_collate_stream_bit_exact():
+    import vhmm_b200 as V
+    z, xs, us = _stream_corpus()
+    corpus = V.DeviceCorpus(xs, us)
+    random.seed(5)
+    for i in range(3):
+        x, u, L = corpus.sample_batch(16, min_len=20, max_len=50)
+        assert L.dtype == torch.int64 and L.device.type == "cpu"
+        assert np.array_equal(L.numpy(), z[f"L{i}"])
+        assert np.array_equal(x.cpu().numpy(), z[f"x{i}"])
+        assert np.array_equal(u.cpu().numpy(), z[f"u{i}"])
+
+
+def test_gather_matches_base_collate_fixture_unaligned_T():
+    """base_collate.npz: reference dataset + collate with T not a multiple of 4 (scalar store path)."""
+    import vhmm_b200 as V
+    g0 = load_golden("base_collate")
+    g = torch.Generator().manual_seed(1234)
+    xs = torch.randn(10, 5, 120, generator=g)
+    us = torch.randn(10, 4, 120, generator=g)
+    corpus = V.DeviceCorpus(list(xs), list(us))
+    random.seed(0)
+    x, u, L = corpus.sample_batch(8, min_len=20, max_len=60)
+    assert torch.equal(L, g0["lengths"])
+    assert torch.equal(x.cpu(), g0["x"]) and torch.equal(u.cpu(), g0["u"])
+
+
+def test_gather_loader_equals_host_collate_and_edge_cases():
+    import vhmm_b200 as V
+    r = np.random.default_rng(0)
+    lens = [33, 200, 57, 400]
+    xs = [torch.from_numpy(r.normal(size=(5, n)).astype(np.float32)) for n in lens]
+    us = [torch.from_numpy(r.normal(size=(4, n)).astype(np.float32)) for n in lens]
+    corpus = V.DeviceCorpus(xs, us)
+    # same random stream through the host dataset + collate_fn and through the device loader
+    random.seed(11)
+    ds = V.RandomChunkDataset(xs, us, min_len=20, max_len=200)
+    ref_batches = []
+    for n in (64, 64, 7):
+        ref_batches.append(V.collate_fn([ds[i] for i in range(n)], "cpu"))
+    random.seed(11)
+    loader = V.DeviceChunkLoader(corpus, 64, min_len=20, max_len=200, items_per_epoch=135)
+    assert len(loader) == 3
+    for (x, u, L), (xr, ur, Lr) in zip(loader, ref_batches):
+        assert torch.equal(L, Lr) and torch.equal(x.cpu(), xr) and torch.equal(u.cpu(), ur)
+    # explicit triples: whole sequence, last column, padded T, length 1
+    x, u, L = corpus.gather([3, 0, 1], [400, 1, 5], [0, 32, 195], T=404)
+    assert x.shape == (3, 5, 404) and torch.equal(x[0, :, :400].cpu(), xs[3]) and float(x[0, :, 400:].abs().max()) == 0
+    assert torch.equal(x[1, :, :1].cpu(), xs[0][:, 32:33]) and float(x[1, :, 1:].abs().max()) == 0
+    assert torch.equal(u[2, :, :5].cpu(), us[1][:, 195:200])
+    with pytest.raises(V.VhmmError):
+        corpus.gather([0], [10], [30])          # runs past the end of its sequence
+    # the vectorised sampler draws valid triples with the reference's ranges
+    idx, ln, st = V.training.sample_triples_fast(lens, 5000, 20, 200, np.random.default_rng(1))
+    sl = np.asarray(lens)[idx]
+    assert (ln >= 20).all() and (ln <= np.minimum(200, sl)).all() and (st >= 0).all() and (st + ln <= sl).all()
+    assert set(np.unique(idx)) == {0, 1, 2, 3} and ln.max() == 200 and ln.min() == 20
+
+
+def _fresh_model():
+    import vhmm_b200 as V
+    torch.manual_seed(0)
+    return V.VAE_HMM(5, 64, 3, 32, u_dim=4).cuda()
+
+
+@pytest.mark.parametrize("name,clip", [("train_adam", 0.0), ("train_clip", 1.0)])
+def test_fused_step_matches_reference_training_loop(name, clip):
+    """4 steps of the reference's loop (CPU, unmodified reference) vs 4 fused steps on the GPU."""
+    import vhmm_b200 as V
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    g = load_golden("base_fresh")
+    m = _fresh_model()
+    opt = V.FusedAdam(m, lr=1e-3)
+    x, u, L = g["x"].cuda(), g["u"].cuda(), g["lengths"]
+    for i in range(4):
+        loss, flat = m.loss_and_flat_grads(x, u, L, 0.7)
+        opt.step(flat, max_norm=clip)
+        assert abs(float(loss) - z["losses64"][i]) <= 2e-5 * abs(z["losses64"][i]), (i, float(loss))
+        if clip:
+            assert abs(float(opt.grad_norm) - z["norms64"][i]) <= 1e-4 * z["norms64"][i]
+    # Adam normalises every coordinate to ~lr per step, so parameters are compared in absolute terms:
+    # 4 steps move a weight by <= 4e-3; agreement to 2e-6 is 5e-4 of the movement (fp32 reference run
+    # vs its own float64 run differs by about as much: checked below).
+    worst = 0.0
+    for k, p in m.named_parameters():
+        d = float((p.detach().double().cpu() - torch.from_numpy(z["param64:" + k])).abs().max())
+        d32 = float((torch.from_numpy(z["param:" + k]).double() - torch.from_numpy(z["param64:" + k])).abs().max())
+        worst = max(worst, d)
+        assert d <= max(2e-6, 4 * d32), (k, d, d32)
+    assert worst > 0.0
+
+
+def test_fused_adam_equals_torch_adam_on_same_gradients():
+    """Same flat gradients into torch.optim.Adam (+ clip_grad_norm_) and into vhmm_adam_step."""
+    import vhmm_b200 as V
+    from vhmm_b200 import functional as Fn
+    g = load_golden("base_fresh")
+    x, u, L = g["x"].cuda(), g["u"].cuda(), g["lengths"]
+    for clip in (0.0, 1.0):
+        a, b = _fresh_model(), _fresh_model()
+        topt = torch.optim.Adam(a.parameters(), lr=3e-3)
+        fopt = V.FusedAdam(b, lr=3e-3)
+        off = Fn.param_offsets(a._dims)
+        for _ in range(5):
+            _, flat = b.loss_and_flat_grads(x, u, L, 1.0)
+            for i, p in enumerate(a._params()):
+                p.grad = flat[off[i]:off[i + 1]].view_as(p).clone()
+            if clip:
+                torch.nn.utils.clip_grad_norm_(a.parameters(), clip)
+            topt.step()
+            fopt.step(flat, max_norm=clip)
+            for (k, pa), (_, pb) in zip(a.named_parameters(), b.named_parameters()):
+                assert float((pa - pb).abs().max()) <= 1e-7 + 1e-6 * float(pa.abs().max()), k
+        # optimiser state interchanges with torch.optim.Adam's format
+        sd = fopt.state_dict()
+        t2 = torch.optim.Adam(b.parameters(), lr=3e-3)
+        t2.load_state_dict(sd)
+        f2 = V.FusedAdam(b, lr=1.0)
+        f2.load_state_dict(topt.state_dict())
+        assert f2.step_count == 5 and f2.lr == 3e-3
+        assert rel_err(f2.exp_avg, fopt.exp_avg) <= 1e-5 and rel_err(f2.exp_avg_sq, fopt.exp_avg_sq) <= 1e-5
+
+
+def test_trainer_and_train_model_fused_reduce_the_loss(capsys):
+    import vhmm_b200 as V
+    r = np.random.default_rng(3)
+    xs = [torch.from_numpy(r.normal(size=(5, 300)).astype(np.float32)) for _ in range(6)]
+    us = [torch.from_numpy(r.normal(size=(4, 300)).astype(np.float32)) for _ in range(6)]
+    corpus = V.DeviceCorpus(xs, us)
+    random.seed(2)
+    loader = V.DeviceChunkLoader(corpus, 64, items_per_epoch=256)
+    tr = V.Trainer(_fresh_model(), lr=1e-3, device="cuda")
+    l0 = tr.train_epoch(loader, beta=0.5)
+    for _ in range(3):
+        l1 = tr.train_epoch(loader, beta=0.5)
+    assert np.isfinite(l0) and l1 < l0
+    m = V.train_model_fused(_fresh_model(), loader, num_epochs=2, lr=1e-3)
+    out = capsys.readouterr().out
+    assert "Epoch 1/2, Loss:" in out and "Epoch 2/2, Loss:" in out
+    assert all(torch.isfinite(p).all() for p in m.parameters())

@@ -20,7 +20,7 @@ def test_library_exports_every_declared_symbol():
     assert declared == set(_lib.PROTOTYPES), declared ^ set(_lib.PROTOTYPES)
     for name in declared:
         assert hasattr(L, name), name
-    assert L.vhmm_version() == 100
+    assert L.vhmm_version() == 101
 
 
 def test_param_layout_matches_state_dict():
@@ -76,3 +76,28 @@ def test_collate_contract():
     import src.utils
     import VQ_VAE_HMM_fixed as R
     assert R.VAE_HMM is V.VAE_HMM and R.collate_fn is V.collate_fn
+
+
+def test_sample_triples_consumes_random_like_the_reference_dataset():
+    """training.sample_triples + plain slicing reproduces, on the CPU, the batches the real reference
+    RandomChunkDataset + collate_fn produced (tests/golden/collate_stream.npz): same three
+    random.randint calls per item in the same order."""
+    import random
+    import numpy as np
+    from conftest import GOLDEN
+    from vhmm_b200.training import sample_triples
+    z = np.load(os.path.join(GOLDEN, "collate_stream.npz"))
+    g = torch.Generator().manual_seed(77)
+    lens = [int(n) for n in z["lens"]]
+    xs = [torch.randn(5, n, generator=g) for n in lens]
+    us = [torch.randn(4, n, generator=g) for n in lens]
+    random.seed(5)
+    for i in range(3):
+        idx, ln, st = sample_triples(lens, 16, 20, 50)
+        assert np.array_equal(ln, z[f"L{i}"])
+        T = int(ln.max())
+        x = np.zeros((16, 5, T), np.float32); u = np.zeros((16, 4, T), np.float32)
+        for b in range(16):
+            x[b, :, :ln[b]] = xs[idx[b]][:, st[b]:st[b] + ln[b]].numpy()
+            u[b, :, :ln[b]] = us[idx[b]][:, st[b]:st[b] + ln[b]].numpy()
+        assert np.array_equal(x, z[f"x{i}"]) and np.array_equal(u, z[f"u{i}"])

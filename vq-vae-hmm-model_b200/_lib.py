@@ -16,7 +16,7 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.environ.get("VHMM_LIB") or os.path.join(_HERE, "libvhmm.so")   # VHMM_LIB: an instrumented build (tools/)
-SOURCES = ("api.cu", "elbo_layerwise.cu", "hmm.cu", "elbo_fused.cu")
+SOURCES = ("api.cu", "elbo_layerwise.cu", "hmm.cu", "elbo_fused.cu", "batch_train.cu")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
 
@@ -99,6 +99,8 @@ PROTOTYPES = {
     "vhmm_elbo_timing": (ctypes.c_int, [ctypes.c_int]),
     "vhmm_elbo_timing_read": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int)]),
     "vhmm_argmax_regimes": (ctypes.c_int, [_P, _I64, _I64, _I64, _P, _P]),
+    "vhmm_gather_chunks": (ctypes.c_int, [_P, _P, _I64, _I64, _I64, _P, _P, _I64, _I64, _P, _P, _P]),
+    "vhmm_adam_step": (ctypes.c_int, [_DP, _PP, _P, _P, _P, _DBL, _DBL, _DBL, _DBL, _I64, _P, _DBL, _P, _P, _P]),
     "vhmm_emission_table": (ctypes.c_int, [_DP, _PP, _I64, _P, _P, _P, _SZ, _P]),
     "vhmm_emission_logprob": (ctypes.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P, _P]),
     "vhmm_hmm_forward": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P]),

@@ -44,6 +44,9 @@ int hmm_viterbi(const float*, const float*, const float*, const int64_t*, int64_
 int hmm_decode(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, float*, void*, size_t, cudaStream_t);
 int hmm_scan(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
 int hmm_posterior_select(int mode);
+// batch_train.cu
+int gather_chunks(const float*, const float*, int64_t, int64_t, int64_t, const int64_t*, const int64_t*, int64_t, int64_t, float*, float*, cudaStream_t);
+int adam_step(const vhmm_dims&, float* const*, const float*, float*, float*, double, double, double, double, int64_t, const float*, double, float*, double*, cudaStream_t);
 
 static std::atomic<int> g_elbo_impl{VHMM_ELBO_AUTO};
 static int elbo_impl_for(const vhmm_dims& d) {
@@ -172,6 +175,24 @@ int vhmm_elbo_active_impl(const vhmm_dims* dims) {
 int vhmm_argmax_regimes(const float* q, int64_t B, int64_t K, int64_t T, int64_t* regimes, void* stream) {
   ARG(q && regimes, "q/regimes"); ARG(B > 0 && K > 0 && T > 0, "B,K,T");
   return launch_argmax(q, B, K, T, regimes, (cudaStream_t)stream);
+}
+
+int vhmm_gather_chunks(const float* x_cat, const float* u_cat, int64_t S_tot, int64_t C, int64_t U,
+                       const int64_t* col0, const int64_t* lengths, int64_t B, int64_t T, float* x_out,
+                       float* u_out, void* stream) {
+  ARG(x_cat && u_cat && col0 && lengths && x_out && u_out, "pointers");
+  ARG(S_tot > 0 && C > 0 && U > 0 && B >= 0 && T >= 0, "sizes");
+  return gather_chunks(x_cat, u_cat, S_tot, C, U, col0, lengths, B, T, x_out, u_out, (cudaStream_t)stream);
+}
+
+int vhmm_adam_step(const vhmm_dims* dims, const vhmm_params_mut* params, const float* grads, float* exp_avg,
+                   float* exp_avg_sq, double lr, double beta1, double beta2, double eps, int64_t step,
+                   const float* grad_scale, double max_norm, float* grad_norm_out, double* scratch, void* stream) {
+  ARG(dims_ok(dims), "dims"); ARG(params && grads && exp_avg && exp_avg_sq, "pointers");
+  for (int i = 0; i < VHMM_NUM_PARAMS; ++i) ARG(params->p[i], "params");
+  ARG(step >= 1, "step"); ARG(beta1 >= 0 && beta1 < 1 && beta2 >= 0 && beta2 < 1 && eps >= 0, "hyper-parameters");
+  return adam_step(*dims, params->p, grads, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, step, grad_scale, max_norm,
+                   grad_norm_out, scratch, (cudaStream_t)stream);
 }
 
 int vhmm_emission_table(const vhmm_dims* dims, const vhmm_params* params, int64_t T, float* mu_tab,

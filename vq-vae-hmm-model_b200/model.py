@@ -137,6 +137,27 @@ class VAE_HMM(nn.Module):
         loss, _ = Fn.ElboFunction.apply(self._dims, x, u, lengths_dev, float(beta), norms, *self._params())
         return loss
 
+    def loss_and_flat_grads(self, x, u, lengths, beta=1.0):
+        """compute_loss and its gradient without an autograd graph: (loss 0-d fp32 on the device,
+        flat fp32 gradient buffer in state_dict order).  This is what vhmm_elbo produces in one call;
+        training.FusedAdam consumes the buffer directly."""
+        B, C, T = x.shape
+        if lengths is None:
+            raise ValueError('lengths required')
+        if u is None:
+            raise ValueError('u required for non-stationary transitions')
+        if u.dim() == 3 and u.shape[1] != self._dims.U and u.shape[2] == self._dims.U:
+            u = u.permute(0, 2, 1)
+        dev = x.device if x.is_cuda else self.prior.log_prior.device
+        lengths_dev = lengths.to(device=dev, dtype=torch.int64)
+        norms = Fn.elbo_norms(lengths_dev, B, C, T)
+        with torch.no_grad():
+            if self.shard_group is not None:
+                from . import parallel
+                return parallel.sharded_loss_and_flat_grads(self, x, u, lengths_dev, float(beta), norms, self.shard_group)
+            sums, grads = Fn.elbo_raw(self._dims, self._params(), x, u, lengths_dev, norms, float(beta), True)
+            return Fn.loss_from_sums(sums, norms, float(beta)), grads
+
     def loss_terms(self, x, u, lengths):
         """(recon_loss, prior_loss, entropy) as normalised by the reference (:120, :131, :135)."""
         B, C, T = x.shape

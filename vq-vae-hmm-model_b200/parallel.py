@@ -47,6 +47,24 @@ class _ShardedElbo(torch.autograd.Function):
         return (None, None, None, None, None, None, None, *outs)
 
 
+def sharded_loss_and_flat_grads(model, x, u, lengths_dev, beta, norms_local, group=None):
+    """The exchange of _ShardedElbo without autograd: (global loss, GLOBAL flat gradient buffer)."""
+    d = model._dims
+    C = x.shape[1]
+    nv = lengths_dev.clamp(min=0, max=x.shape[2]).sum().to(torch.float64)
+    cnt = torch.stack([nv * C, norms_local[1]])
+    dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
+    norms = torch.stack([cnt[0].clamp(min=1.0), cnt[1]])
+    sums, grads = Fn.elbo_raw(d, model._params(), x, u, lengths_dev, norms, beta, True)
+    hi = sums.to(torch.float32)
+    lo = (sums - hi.to(torch.float64)).to(torch.float32)
+    flat = torch.cat([grads, hi, lo])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    n = grads.numel()
+    gsums = flat[n:n + 4].to(torch.float64) + flat[n + 4:n + 8].to(torch.float64)
+    return Fn.loss_from_sums(gsums, norms, beta), flat[:n]
+
+
 def sharded_elbo(model, x, u, lengths_dev, beta, norms_local, group=None):
     """Global loss (identical on every rank) whose backward leaves the GLOBAL gradient in .grad."""
     return _ShardedElbo.apply(model, x, u, lengths_dev, beta, norms_local, group, *model._params())
