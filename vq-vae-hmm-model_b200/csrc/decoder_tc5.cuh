@@ -31,6 +31,7 @@
 // accumulators of the mma.sync kernel, no shared memory spent.
 #pragma once
 #include "tc5.cuh"
+#include "skinny.cuh"
 
 namespace t5 {
 constexpr int ROWS = 130;                 // rows of an activation plane: row r <-> window column r-1
@@ -63,7 +64,8 @@ struct Lay {
   static constexpr int ACC = PB + 16 * PT;                      // small gradient accumulators: layout of Cfg::B_* minus B_WF
   static constexpr int NACC = CF::ACC_B - CF::B_WF;
   static constexpr int QX1 = ACC + NACC;                        // second input buffer (prefetch of the next tile)
-  static constexpr int FLOATS = QX1 + 16 * PT;
+  static constexpr int SCR = QX1 + 16 * PT;                     // slice partials of the folded conv1 weight gradient (skinny.cuh)
+  static constexpr int FLOATS = SCR + SkTaps<CF::K, CF::H>::FLOATS;
   static constexpr size_t BYTES = (size_t)OP_BYTES + (size_t)FLOATS * 4;
 };
 }  // namespace t5
@@ -97,6 +99,7 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
   float* accBD2 = acc + (CF::B_BD2 - CF::B_WF);
   float* accBD1 = acc + (CF::B_BD1 - CF::B_WF);
   float* accBP = acc + (CF::B_BP - CF::B_WF);
+  float* scrW = fl + L::SCR;
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
 
   for (int i = tid; i < (int)(L::BYTES / 4); i += NTH) reinterpret_cast<uint32_t*>(smraw)[i] = 0u;
@@ -186,7 +189,7 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
           tc5::tmem_ld16(tmem + lane_base + t5::TACC + 64 * tau + 16 * cg, a);
           double* dst = part + CF::B_W2 + (tau * H + (jrow & 63)) * CF::PW_H + 16 * cg;
 #pragma unroll
-          for (int e = 0; e < 16; ++e) { dst[e] += (double)a[e]; a[e] = 0.f; }
+          for (int e = 0; e < 16; ++e) { atomicAdd(dst + e, (double)a[e]); a[e] = 0.f; }
           tc5::tmem_st16(tmem + lane_base + t5::TACC + 64 * tau + 16 * cg, a);
         }
         tc5::tmem_st_wait();
@@ -208,9 +211,11 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
   cp_async_commit();
   while (tile >= 0) {
     const int64_t nxt = next_tile<2>(cm, tile + gridDim.x, tn);
+    PROF(12);
     if (nxt >= 0) fetch(tn, buf ? QX0 : QX1);
     cp_async_commit();
     cp_async_wait_prev();
+    PROF(13);
     const float* QX = buf ? QX1 : QX0;
     const int t0 = ti.t0, T = cm.T, Lb = ti.L;
     const int64_t b = ti.b;
@@ -381,22 +386,13 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     }
     tc5::fence_before_sync();
     __syncthreads(); PROF(8);
-    // ---- folded conv1 gradients dW'[tau][o][k] += sum_t dg1[o][t] q[k][t+tau-1], bias, d loss / d q -> HBM
-    for (int unit = w; unit < 3 * (H / 16); unit += NW) {
-      const int mt = unit % (H / 16), tap = unit / (H / 16);
-      gemm_time<1, 1, KST, J0, PT>(S + mt * 16 * PT, QX + tap - 1, accWF + tap * H * 8 + mt * 16 * 8, 0, 8);
-    }
-    row_sums<J0, TT / 4, PT, NW>(S, H, accBD1);
-    {
-      float* dq = cm.dq_dec;
-      cols_op<16, 1, 1, H / 8, 3, true>(WFs, H * 8, 8, S, [=](int r, int c, float v0, float v1) {
-        if (r < K) {
-          const int t = t0 - HL + c;
-          if (c >= J0 && c < J0 + TT && t < T) dq[(b * K + r) * (int64_t)T + t] = v0;
-          if (c + 1 >= J0 && c + 1 < J0 + TT && t + 1 < T) dq[(b * K + r) * (int64_t)T + t + 1] = v1;
-        }
-      });
-    }
+    // ---- folded conv1 gradients dW'[tau][o][k] += sum_t dg1[o][t] q[k][t+tau-1], bias, d loss / d q -> HBM:
+    // register-blocked FFMA (skinny.cuh): slice partials -> scrW / Pb, one barrier, ordered reduction
+    sk_wgrad_taps<K, H>(S, QX, scrW);
+    sk_dgrad_taps<K, H, 4>(WFs, S, Pb);
+    __syncthreads();
+    sk_wgrad_taps_reduce<K, H>(scrW, accWF, accBD1);
+    sk_dgrad_taps_store<K, 4>(Pb, cm.dq_dec + b * K * (int64_t)T, t0, T);
     PROF(9);
     // ---- conv2 weight gradient: drain each tap's tile sum into the persistent TMEM accumulators
     {
@@ -424,9 +420,10 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     }
     PROF(10);
     if (++ndone % FLUSH == 0) flush_all();
+    PROF(11);
     tile = nxt; ti = tn; buf ^= 1;
   }
-  PROF_DUMP("decoder_tc5", 11);
+  PROF_DUMP("decoder_tc5", 14);
   flush_all();
   const double v = block_sum_d(s_nll, red);
   if (tid == 0) cm.loss_part[(int64_t)blockIdx.x * LP + 0] = v;

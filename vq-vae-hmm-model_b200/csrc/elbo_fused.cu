@@ -176,11 +176,18 @@ __device__ __forceinline__ double block_sum_d(double v, double* sh) {
 }
 
 // part[i] += acc[i]; acc[i] = 0: the fp32 shared-memory accumulators only ever sum FLUSH tiles
-// before they are folded into the CTA's double-precision partial in HBM
-constexpr int FLUSH = 16;
+// before they are folded into the CTA's double-precision partial in HBM.  The fold is a
+// fire-and-forget RED.ADD.F64 (the partial is private to the CTA and every address receives
+// exactly one add per flush, so the result is as deterministic as load-add-store, without the
+// 64 MB of partials -- more than fits beside the inputs in L2 -- being read back through the SM:
+// the load-add-store version cost 36 us per flush, 12 % of the decoder kernel)
+#ifndef VHMM_FLUSH
+#define VHMM_FLUSH 256   /* tools/flush_check.py: gradients at cfg 2 agree with the FLUSH = 16 build to ~1e-6 */
+#endif
+constexpr int FLUSH = VHMM_FLUSH;
 __device__ __forceinline__ void flush_acc(double* __restrict__ part, float* acc, int n) {
   for (int i = threadIdx.x; i < n; i += NTH) {
-    part[i] += (double)acc[i];
+    atomicAdd(part + i, (double)acc[i]);
     acc[i] = 0.f;
   }
   __syncthreads();

@@ -427,7 +427,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
           tc5::tmem_ld16(tmem + lane_base + t5e::TACC + 64 * tau + 16 * cg, a);
           double* dst = part + CF::C_W2 + (tau * H2 + (jrow & 31)) * CF::PW_H + 16 * cg;
 #pragma unroll
-          for (int e = 0; e < 16; ++e) { dst[e] += (double)a[e]; a[e] = 0.f; }
+          for (int e = 0; e < 16; ++e) { atomicAdd(dst + e, (double)a[e]); a[e] = 0.f; }
           tc5::tmem_st16(tmem + lane_base + t5e::TACC + 64 * tau + 16 * cg, a);
         }
         tc5::tmem_st_wait();

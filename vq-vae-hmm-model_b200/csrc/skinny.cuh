@@ -22,3 +22,105 @@ __device__ __forceinline__ void sk_wgrad_in4(const float* __restrict__ act, cons
   acc[h * 8 + c] += s;
   if (c == 0) bsum[h] += sb;
 }
+
+// ---- "skinny" k=3 conv gradients with K_Q <= 5 input rows (folded decoder conv1: 3 -> 64, encoder
+// conv1: 5 -> 64).  On the padded mma.sync helpers these are latency-bound (rows padded 3 -> 8/16, a
+// 15-step dependent MMA chain per warp); as register-blocked FFMA they are ~4x shorter.
+//
+// sk_wgrad_taps: thread (o = tid % HH, s = tid / HH) sums its slice of the owned columns
+//   part[s][o][tau*KQ + k] = sum_{j in slice s} dY[o][j] * X[k][j + tau - 1],  part[s][o][3 KQ] = sum_j dY[o][j]
+// into scr[(s*HH + o)*PS + .] (PS odd: conflict-free); after a __syncthreads sk_wgrad_taps_reduce adds
+// the NTH/HH slices in a fixed order into accW[(tau*HH + o)*8 + k] and accB[o] (deterministic).
+template <int KQ, int HH>
+struct SkTaps {
+  static constexpr int NS = NTH / HH;            // time slices
+  static constexpr int NO = 3 * KQ + 1;          // outputs per (o, slice)
+  static constexpr int PS = NO | 1;              // odd pitch
+  static constexpr int FLOATS = NS * HH * PS;
+};
+
+template <int KQ, int HH>
+__device__ __forceinline__ void sk_wgrad_taps(const float* __restrict__ dY, const float* __restrict__ X,
+                                              float* __restrict__ scr) {
+  using SK = SkTaps<KQ, HH>;
+  const int o = threadIdx.x % HH, s = threadIdx.x / HH;
+  float a0[KQ], a1[KQ], a2[KQ], sb = 0.f;
+#pragma unroll
+  for (int k = 0; k < KQ; ++k) a0[k] = a1[k] = a2[k] = 0.f;
+  for (int q = s; q < TT / 4; q += SK::NS) {
+    const int j = J0 + 4 * q;
+    const float4 d = *reinterpret_cast<const float4*>(dY + o * PT + j);
+    sb += (d.x + d.y) + (d.z + d.w);
+#pragma unroll
+    for (int k = 0; k < KQ; ++k) {
+      const float* xr = X + k * PT + j;
+      const float xm = xr[-1], xp = xr[4];
+      const float4 xv = *reinterpret_cast<const float4*>(xr);
+      a0[k] = fmaf(d.w, xv.z, fmaf(d.z, xv.y, fmaf(d.y, xv.x, fmaf(d.x, xm, a0[k]))));
+      a1[k] = fmaf(d.w, xv.w, fmaf(d.z, xv.z, fmaf(d.y, xv.y, fmaf(d.x, xv.x, a1[k]))));
+      a2[k] = fmaf(d.w, xp, fmaf(d.z, xv.w, fmaf(d.y, xv.z, fmaf(d.x, xv.y, a2[k]))));
+    }
+  }
+  float* p = scr + (s * HH + o) * SK::PS;
+#pragma unroll
+  for (int k = 0; k < KQ; ++k) { p[k] = a0[k]; p[KQ + k] = a1[k]; p[2 * KQ + k] = a2[k]; }
+  p[3 * KQ] = sb;
+}
+
+template <int KQ, int HH>
+__device__ __forceinline__ void sk_wgrad_taps_reduce(const float* __restrict__ scr, float* __restrict__ accW,
+                                                     float* __restrict__ accB) {
+  using SK = SkTaps<KQ, HH>;
+  for (int i = threadIdx.x; i < HH * SK::NO; i += NTH) {
+    const int o = i / SK::NO, c = i - o * SK::NO;
+    float sum = 0.f;
+#pragma unroll
+    for (int s = 0; s < SK::NS; ++s) sum += scr[(s * HH + o) * SK::PS + c];
+    if (c < 3 * KQ) accW[((c / KQ) * HH + o) * 8 + (c % KQ)] += sum;
+    else accB[o] += sum;
+  }
+}
+
+// sk_dgrad_taps: input gradient of the same conv, out[k][j] = sum_tau sum_o W[tau][o][k] * dY[o][j + 1 - tau]
+// (W as [3][HH][8] floats, k < KQ <= 4).  Thread (p = tid % 64 < TT/2, g = tid / 64 < NG) handles the
+// column pair j = J0 + 2p, j+1 over the HH/NG rows of group g -> scr[(g*KQ + k)*NC + j]; threads with
+// g >= NG skip.  sk_dgrad_taps_store (after a __syncthreads) adds the groups and writes the owned
+// columns with t < T to dq[k*T + t] (dq already offset to the sequence).
+template <int KQ, int HH, int NG>
+__device__ __forceinline__ void sk_dgrad_taps(const float* __restrict__ Wf, const float* __restrict__ dY,
+                                              float* __restrict__ scr) {
+  static_assert(KQ <= 4, "weights are read as one float4 per (tau, o)");
+  const int p = threadIdx.x & 63, g = threadIdx.x >> 6;
+  if (g >= NG || p >= TT / 2) return;
+  const int j = J0 + 2 * p;
+  float o0[4] = {0.f, 0.f, 0.f, 0.f}, o1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+  for (int o = g * (HH / NG); o < (g + 1) * (HH / NG); ++o) {
+    const float* r = dY + o * PT + j;
+    const float dm = r[-1], dp = r[2];
+    const float2 d = *reinterpret_cast<const float2*>(r);
+    const float4 w0 = *reinterpret_cast<const float4*>(Wf + o * 8);
+    const float4 w1 = *reinterpret_cast<const float4*>(Wf + (HH + o) * 8);
+    const float4 w2 = *reinterpret_cast<const float4*>(Wf + (2 * HH + o) * 8);
+    const float a0[4] = {w0.x, w0.y, w0.z, w0.w}, a1[4] = {w1.x, w1.y, w1.z, w1.w}, a2[4] = {w2.x, w2.y, w2.z, w2.w};
+#pragma unroll
+    for (int k = 0; k < KQ; ++k) {
+      o0[k] = fmaf(a2[k], dm, fmaf(a1[k], d.x, fmaf(a0[k], d.y, o0[k])));
+      o1[k] = fmaf(a2[k], d.x, fmaf(a1[k], d.y, fmaf(a0[k], dp, o1[k])));
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < KQ; ++k) *reinterpret_cast<float2*>(scr + (g * KQ + k) * NC + j) = make_float2(o0[k], o1[k]);
+}
+
+template <int KQ, int NG>
+__device__ __forceinline__ void sk_dgrad_taps_store(const float* __restrict__ scr, float* __restrict__ dq, int t0, int T) {
+  for (int i = threadIdx.x; i < KQ * TT; i += NTH) {
+    const int k = i / TT, c = J0 + (i - k * TT);
+    float sum = 0.f;
+#pragma unroll
+    for (int g = 0; g < NG; ++g) sum += scr[(g * KQ + k) * NC + c];
+    const int t = t0 - HL + c;
+    if (t < T) dq[(int64_t)k * T + t] = sum;
+  }
+}
