@@ -572,12 +572,12 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
     }
     tc5::fence_before_sync();
     __syncthreads(); PROF(6);
-    // conv1 gradients: dW1[tau][o][c] += sum_t dh1[o][t] x[c][t+tau-1]
-    for (int unit = w; unit < 3 * (H / 16); unit += NW) {
-      const int mt = unit % (H / 16), tap = unit / (H / 16);
-      gemm_time<1, 1, KST, J0, PT>(H1 + mt * 16 * PT, XU + tap - 1, acc + CF::C_W1 + tap * H * 8 + mt * 16 * 8, 0, 8);
-    }
-    row_sums<J0, TT / 4, PT, NW>(H1, H, acc + CF::C_B1);
+    // conv1 gradients: dW1[tau][o][c] += sum_t dh1[o][t] x[c][t+tau-1], bias: register-blocked FFMA (skinny.cuh);
+    // slice partials go to the C_W2 block of acc, which this build never uses (dW2 accumulates in TMEM)
+    static_assert(SkTaps<C, H, 4>::FLOATS <= 3 * H2 * CF::PW_H, "conv1 gradient scratch must fit the unused C_W2 block");
+    sk_wgrad_taps<C, H, 4>(H1, XU, acc + CF::C_W2);
+    __syncthreads();
+    sk_wgrad_taps_reduce<C, H, 4>(acc + CF::C_W2, acc + CF::C_W1, acc + CF::C_B1);
     PROF(7);
     {   // conv2 weight gradient: drain each tap's tile sum into the persistent TMEM accumulators
       const float inv_w = 1.f / (sD * sH);

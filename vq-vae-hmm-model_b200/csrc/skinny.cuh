@@ -31,19 +31,20 @@ __device__ __forceinline__ void sk_wgrad_in4(const float* __restrict__ act, cons
 //   part[s][o][tau*KQ + k] = sum_{j in slice s} dY[o][j] * X[k][j + tau - 1],  part[s][o][3 KQ] = sum_j dY[o][j]
 // into scr[(s*HH + o)*PS + .] (PS odd: conflict-free); after a __syncthreads sk_wgrad_taps_reduce adds
 // the NTH/HH slices in a fixed order into accW[(tau*HH + o)*8 + k] and accB[o] (deterministic).
-template <int KQ, int HH>
+template <int KQ, int HH, int NS_ = NTH / HH>
 struct SkTaps {
-  static constexpr int NS = NTH / HH;            // time slices
+  static constexpr int NS = NS_;                 // time slices (threads with tid / HH >= NS idle)
   static constexpr int NO = 3 * KQ + 1;          // outputs per (o, slice)
   static constexpr int PS = NO | 1;              // odd pitch
   static constexpr int FLOATS = NS * HH * PS;
 };
 
-template <int KQ, int HH>
+template <int KQ, int HH, int NS = NTH / HH>
 __device__ __forceinline__ void sk_wgrad_taps(const float* __restrict__ dY, const float* __restrict__ X,
                                               float* __restrict__ scr) {
-  using SK = SkTaps<KQ, HH>;
+  using SK = SkTaps<KQ, HH, NS>;
   const int o = threadIdx.x % HH, s = threadIdx.x / HH;
+  if (s >= NS) return;
   float a0[KQ], a1[KQ], a2[KQ], sb = 0.f;
 #pragma unroll
   for (int k = 0; k < KQ; ++k) a0[k] = a1[k] = a2[k] = 0.f;
@@ -67,10 +68,10 @@ __device__ __forceinline__ void sk_wgrad_taps(const float* __restrict__ dY, cons
   p[3 * KQ] = sb;
 }
 
-template <int KQ, int HH>
+template <int KQ, int HH, int NS = NTH / HH>
 __device__ __forceinline__ void sk_wgrad_taps_reduce(const float* __restrict__ scr, float* __restrict__ accW,
                                                      float* __restrict__ accB) {
-  using SK = SkTaps<KQ, HH>;
+  using SK = SkTaps<KQ, HH, NS>;
   for (int i = threadIdx.x; i < HH * SK::NO; i += NTH) {
     const int o = i / SK::NO, c = i - o * SK::NO;
     float sum = 0.f;
