@@ -225,7 +225,7 @@ def main():
     ms_e2e, _ = timed(step_e2e, K)
     e2e_value = world * B * T / (ms_e2e * 1e-3)
     h2d = xh.numel() * 4 + uh.numel() * 4 + lh.numel() * 8
-    loss_val = float(loss)
+    loss_val = float(loss.detach())
 
     pk = peaks()
     per_gpu_steps = B * T
