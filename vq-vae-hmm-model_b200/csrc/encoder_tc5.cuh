@@ -319,16 +319,15 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
     }
     __syncthreads();
     PROF(5);
-    // gradients of transition_net.2: dWt2[r][h] += sum_t dM[r][t] a[h][t]
-    for (int unit = w; unit < TH / 8; unit += NW)
-      gemm_time<1, 1, KST, J0, PT>(dMb, Ab + unit * 8 * PT, acc + CF::A_WT2 + unit * 8, 0, CF::PW_TH);
+    // gradients of transition_net.{2,0}: dWt2[r][h] += sum_t dM[r][t] a[h][t]; da = relu'(a) * Wt2^T dM (kept in
+    // registers); dWt0[h][c] += sum_t da[h][t] u[c][t] and its bias -- one register-blocked FFMA pass
+    // (skinny.cuh: sk_prior_bwd).  Slice partials go to LQ|Mb (q, log q and log_A are dead after the pair term).
+    static_assert(SkPrior<K2, U, TH, 2>::FLOATS <= 32 * PT, "prior gradient scratch must fit LQ|Mb");
+    sk_prior_bwd<K2, U, TH, 2, CF::PW_TH>(Ab, dMb, Wt2s, XU + 8 * PT, LQ);
     row_sums<J0, TT / 4, PT, NW>(dMb, K2, acc + CF::A_BT2);
     __syncthreads(); PROF(6);
-    // da = relu'(a) * Wt2^T dM, in place over a
-    cols_op<TH, 2, 2, 2, 1, true>(Wt2s, 0, CF::PW_TH, dMb, EpiReluMask{Ab});
-    __syncthreads(); PROF(7);
-    // gradients of transition_net.0: dWt0[h][c] += sum_t da[h][t] u[c][t], bias (FP32 FFMA, one thread per output: skinny.cuh)
-    sk_wgrad_in4(Ab, XU + 8 * PT, acc + CF::A_WT0, acc + CF::A_BT0);
+    sk_prior_bwd_reduce<K2, U, TH, 2, CF::PW_TH>(LQ, acc + CF::A_WT2, acc + CF::A_WT0, acc + CF::A_BT0);
+    PROF(7);
     __syncthreads(); PROF(8);
     if (++ndone % FLUSH == 0) flush_acc(part, acc, CF::ACC_A);
     tile = nxt; ti = tn; buf ^= 1;

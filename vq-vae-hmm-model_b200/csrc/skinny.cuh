@@ -125,3 +125,86 @@ __device__ __forceinline__ void sk_dgrad_taps_store(const float* __restrict__ sc
     if (t < T) dq[(int64_t)k * T + t] = sum;
   }
 }
+
+// ---- prior MLP backward (transition_net: U -> TH -> K2 logits), all three gradients in one pass.
+// Given dM[r][j] (d loss / d transition logits, zero outside the owned columns), a[h][j] (hidden
+// activations) and u[c][j]:
+//   da[h][j]    = relu'(a[h][j]) * sum_r W2[r][h] dM[r][j]          (never stored: u is data)
+//   dW2[r][h]  += sum_j dM[r][j] a[h][j]
+//   dW0[h][c]  += sum_j da[h][j] u[c][j],   db0[h] += sum_j da[h][j]
+// Thread (h = tid % THH, s = tid / THH < NS) walks the 4-column groups q = s, s+NS, ... of the owned
+// columns: per group 1 + K2 + U 16-byte loads (all but the first are warp broadcasts) feed
+// 4 (2 K2 + U) FMAs.  Slice partials -> scr[(s*THH + h)*PS + .]; sk_prior_bwd_reduce adds the slices in
+// a fixed order.  Replaces three padded 3xTF32 mma.sync phases (37 % of kernel A).
+template <int KK2, int UU, int THH, int NS>
+struct SkPrior {
+  static constexpr int NO = KK2 + UU + 1;
+  static constexpr int PS = NO | 1;
+  static constexpr int FLOATS = NS * THH * PS;
+};
+
+template <int KK2, int UU, int THH, int NS, int PW2>
+__device__ __forceinline__ void sk_prior_bwd(const float* __restrict__ a, const float* __restrict__ dM,
+                                             const float* __restrict__ W2, const float* __restrict__ u,
+                                             float* __restrict__ scr) {
+  using SK = SkPrior<KK2, UU, THH, NS>;
+  // 2 NS time slices are computed; the two slices of a warp (lanes 0..15 / 16..31, 16 hidden rows each)
+  // are combined with one shuffle before the store, so only NS partials per row reach the scratch.
+  static_assert(THH * NS * 2 == NTH && THH % 16 == 0, "thread mapping: NTH = 2 NS THH");
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+  const int h = (wp % (THH / 16)) * 16 + (lane & 15);
+  const int sg = wp / (THH / 16);                 // slice pair kept in the scratch
+  const int s = 2 * sg + (lane >> 4);             // time slice of this thread, < 2 NS
+  float w2[KK2], g2[KK2], g0[UU], sb = 0.f;
+#pragma unroll
+  for (int r = 0; r < KK2; ++r) { w2[r] = W2[r * PW2 + h]; g2[r] = 0.f; }
+#pragma unroll
+  for (int c = 0; c < UU; ++c) g0[c] = 0.f;
+#pragma unroll 1
+  for (int q = s; q < TT / 4; q += 2 * NS) {
+    const int j = J0 + 4 * q;
+    const float4 av = *reinterpret_cast<const float4*>(a + h * PT + j);
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int r = 0; r < KK2; ++r) {
+      const float4 d = *reinterpret_cast<const float4*>(dM + r * PT + j);
+      t.x = fmaf(w2[r], d.x, t.x); t.y = fmaf(w2[r], d.y, t.y); t.z = fmaf(w2[r], d.z, t.z); t.w = fmaf(w2[r], d.w, t.w);
+      g2[r] = fmaf(d.w, av.w, fmaf(d.z, av.z, fmaf(d.y, av.y, fmaf(d.x, av.x, g2[r]))));
+    }
+    t.x = av.x > 0.f ? t.x : 0.f; t.y = av.y > 0.f ? t.y : 0.f; t.z = av.z > 0.f ? t.z : 0.f; t.w = av.w > 0.f ? t.w : 0.f;
+    sb += (t.x + t.y) + (t.z + t.w);
+#pragma unroll
+    for (int c = 0; c < UU; ++c) {
+      const float4 v = *reinterpret_cast<const float4*>(u + c * PT + j);
+      g0[c] = fmaf(t.w, v.w, fmaf(t.z, v.z, fmaf(t.y, v.y, fmaf(t.x, v.x, g0[c]))));
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < KK2; ++r) g2[r] += __shfl_xor_sync(0xffffffffu, g2[r], 16);
+#pragma unroll
+  for (int c = 0; c < UU; ++c) g0[c] += __shfl_xor_sync(0xffffffffu, g0[c], 16);
+  sb += __shfl_xor_sync(0xffffffffu, sb, 16);
+  if (lane < 16) {
+    float* p = scr + (sg * THH + h) * SK::PS;
+#pragma unroll
+    for (int r = 0; r < KK2; ++r) p[r] = g2[r];
+#pragma unroll
+    for (int c = 0; c < UU; ++c) p[KK2 + c] = g0[c];
+    p[KK2 + UU] = sb;
+  }
+}
+
+template <int KK2, int UU, int THH, int NS, int PW2>
+__device__ __forceinline__ void sk_prior_bwd_reduce(const float* __restrict__ scr, float* __restrict__ accW2,
+                                                    float* __restrict__ accW0, float* __restrict__ accB0) {
+  using SK = SkPrior<KK2, UU, THH, NS>;
+  for (int i = threadIdx.x; i < THH * SK::NO; i += NTH) {
+    const int h = i / SK::NO, c = i - h * SK::NO;
+    float sum = 0.f;
+#pragma unroll
+    for (int s = 0; s < NS; ++s) sum += scr[(s * THH + h) * SK::PS + c];
+    if (c < KK2) accW2[c * PW2 + h] += sum;
+    else if (c < KK2 + UU) accW0[h * 8 + (c - KK2)] += sum;
+    else accB0[h] += sum;
+  }
+}
