@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
   using L = t5::Lay<CF>;
   extern __shared__ __align__(1024) uint8_t smraw[];
   __shared__ double red[NW];
-  __shared__ __align__(8) uint64_t bar_f, bar_d, bar_w;
+  __shared__ __align__(8) uint64_t bar_f, bar_d, bar_w, bar_w2;
   __shared__ uint32_t tmem_sh, amax_sh;
   uint8_t* W2h = smraw;                                   // fp16 weights
   uint8_t* RA = W2h + t5::W_BYTES;                         // g1 parts
@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
 
   for (int i = tid; i < (int)(L::BYTES / 4); i += NTH) reinterpret_cast<uint32_t*>(smraw)[i] = 0u;
   if (tid == 0) {
-    tc5::mbar_init(&bar_f, 1); tc5::mbar_init(&bar_d, 1); tc5::mbar_init(&bar_w, 1);
+    tc5::mbar_init(&bar_f, 1); tc5::mbar_init(&bar_d, 1); tc5::mbar_init(&bar_w, 1); tc5::mbar_init(&bar_w2, 1);
     tc5::mbar_init_fence();
     amax_sh = 0u;
   }
@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
   const float inv_f = 1.f / (sA * sW);
   const float aR = (float)(1.0 / cm.norms[0]);
   double s_nll = 0.0;
-  uint32_t par_f = 0, par_d = 0, par_w = 0;               // mbarrier phase parities
+  uint32_t par_f = 0, par_d = 0, par_w = 0, par_w2 = 0;   // mbarrier phase parities
   const uint32_t lane_base = (uint32_t)(32 * (w & 3)) << 16;   // this warp's TMEM lane quadrant
   const int jrow = 32 * (w & 3) + lane;                    // TMEM lane == window column (time GEMMs) or stacked channel (dW2)
   const int cg = w >> 2;                                    // 16-column group this warp reads
@@ -209,11 +209,11 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
   int64_t tile = next_tile<2>(cm, blockIdx.x, ti);
   if (tile >= 0) fetch(ti, QX0);
   cp_async_commit();
+  int64_t nxt = (tile >= 0) ? next_tile<2>(cm, tile + gridDim.x, tn) : -1;
   while (tile >= 0) {
-    const int64_t nxt = next_tile<2>(cm, tile + gridDim.x, tn);
-    PROF(12);
     if (nxt >= 0) fetch(tn, buf ? QX0 : QX1);
     cp_async_commit();
+    const TilePre pre = tile_pre(cm, nxt >= 0 ? nxt + gridDim.x : cm.ntiles);   // consumed after the tile
     cp_async_wait_prev();
     PROF(13);
     const float* QX = buf ? QX1 : QX0;
@@ -281,14 +281,13 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     // ---- p = Wp g2 + bp, Gaussian NLL and its gradient (:87-90, :118-120)
     cols_op<16, 1, 1, H / 8, 1, false>(WPs, 0, CF::PW_H, S, EpiBiasRows{Pb, bps, 2 * C});
     __syncthreads(); PROF(3);
-    if (tid < NC) {
-      const int j = tid, t = t0 - HL + j;
+    {   // all 512 threads: thread (column j, channel group): channels c = tid/NC, tid/NC + 4, ...
+      const int j = tid & (NC - 1), t = t0 - HL + j;
       const bool inr = (j >= 2 && j < NC - 2 && t >= 0 && t < T);
       const bool mk = inr && t < Lb;
       const bool own = mk && j >= J0 && j < J0 + TT;
       float nll = 0.f;
-#pragma unroll
-      for (int c = 0; c < C; ++c) {
+      for (int c = tid / NC; c < C; c += NTH / NC) {
         const float mu = Pb[c * PT + j], lv = Pb[(C + c) * PT + j], xv = QX[(8 + c) * PT + j];
         const float ev = expf(lv), v = fmaxf(ev, 1e-8f), d = mu - xv, r = d * d / v;
         nll += 0.5f * (logf(6.283185307179586f * v) + r);
@@ -299,10 +298,11 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     }
     __syncthreads(); PROF(4);
     // ---- to_params gradients, then dg2 = relu'(g2) * Wp^T dp in place over S
-    for (int unit = w; unit < H / 8; unit += NW)
-      gemm_time<1, 1, KST, J0, PT>(Pb, S + unit * 8 * PT, accWP + unit * 8, 0, CF::PW_H);
+    static_assert(SkRows<2 * C, H>::FLOATS <= SkTaps<CF::K, CF::H>::FLOATS, "to_params gradient partials share the scratch of phase 9");
+    sk_wgrad_rows<2 * C, H>(Pb, S, scrW);             // dWp[p][o] += sum_t dp[p][t] g2[o][t] as FFMA (skinny.cuh)
     row_sums<J0, TT / 4, PT, NW>(Pb, 2 * C, accBP);
     __syncthreads(); PROF(5);
+    sk_wgrad_rows_reduce<2 * C, H>(scrW, accWP, CF::PW_H);
     cols_op<H, 2, 2, 2, 1, true>(WPs, 0, CF::PW_H, Pb, EpiReluMask{S});
     __syncthreads(); PROF(6);
     {   // conv2 bias gradient and the tile maximum of |dg2| (scale of its fp16 parts)
@@ -337,15 +337,17 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     tc5::fence_before_sync();
     __syncthreads(); PROF(7);
     // ---- tensor core: dg1 pre-mask (input gradient of conv2) and the weight gradient of tap 0
-    auto issue_wgrad = [&](int tau, bool lead) {   // WACC = [dg2_h; dg2_m] x [g1_h; g1_m](shifted by tau) over the 120 owned columns
+    // weight-gradient tile sum of one tap: acc = [dg2_h; dg2_m] x [g1_h; g1_m](shifted by tau) over the 120 owned
+    // columns, into 128 TMEM columns at `acc_col`; completion on `bar`
+    auto issue_wgrad = [&](int tau, bool lead, uint32_t acc_col, uint64_t* bar) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const uint64_t a = (i < 7) ? tc5::make_desc(sRB + (J0 + 1 + 16 * i) * 16, 128, t5::PLANE)
                                    : tc5::make_desc(sSB, 128, t5::SB_PLANE);
         const uint64_t bq = tc5::make_desc(sRA + (J0 + 16 * i + tau) * 16, 128, t5::PLANE);
-        if (lead) tc5::mma_f16(tmem + t5::WACC, a, bq, ID_W128, i ? 1u : 0u);
+        if (lead) tc5::mma_f16(tmem + acc_col, a, bq, ID_W128, i ? 1u : 0u);
       }
-      if (lead) tc5::commit(&bar_w);
+      if (lead) tc5::commit(bar);
     };
     if (w == 0) {
       tc5::fence_after_sync();
@@ -365,7 +367,7 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
           }
         }
       if (lead) tc5::commit(&bar_d);
-      issue_wgrad(0, lead);
+      issue_wgrad(0, lead, t5::WACC, &bar_w);
       __syncwarp();
     }
     tc5::mbar_wait(&bar_d, par_d); par_d ^= 1u;
@@ -386,6 +388,11 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     }
     tc5::fence_before_sync();
     __syncthreads(); PROF(8);
+    if (w == 0) {   // the forward / input-gradient accumulator is free now: tap 1 runs there under the FFMA phase below
+      tc5::fence_after_sync();
+      issue_wgrad(1, tc5::elect_one(), t5::ACC_F, &bar_w2);
+      __syncwarp();
+    }
     // ---- folded conv1 gradients dW'[tau][o][k] += sum_t dg1[o][t] q[k][t+tau-1], bias, d loss / d q -> HBM:
     // register-blocked FFMA (skinny.cuh): slice partials -> scrW / Pb, one barrier, ordered reduction
     sk_wgrad_taps<K, H>(S, QX, scrW);
@@ -394,26 +401,29 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     sk_wgrad_taps_reduce<K, H>(scrW, accWF, accBD1);
     sk_dgrad_taps_store<K, 4>(Pb, cm.dq_dec + b * K * (int64_t)T, t0, T);
     PROF(9);
-    // ---- conv2 weight gradient: drain each tap's tile sum into the persistent TMEM accumulators
+    // ---- conv2 weight gradient: drain each tap's tile sum into the persistent TMEM accumulators.  Tap 0 (WACC) and
+    // tap 1 (ACC_F) were issued under the previous phases; tap 2 reuses WACC as soon as tap 0 is drained.
     {
       const float inv_w = 1.f / (sA * sB);
 #pragma unroll 1
       for (int tau = 0; tau < 3; ++tau) {
-        tc5::mbar_wait(&bar_w, par_w); par_w ^= 1u;
+        const uint32_t col = (tau == 1) ? t5::ACC_F : t5::WACC;
+        if (tau == 1) { tc5::mbar_wait(&bar_w2, par_w2); par_w2 ^= 1u; }
+        else          { tc5::mbar_wait(&bar_w, par_w); par_w ^= 1u; }
         tc5::fence_after_sync();
         float v0[16], v1[16], a[16];
-        tc5::tmem_ld16(tmem + lane_base + t5::WACC + 16 * cg, v0);        // x g1_h
-        tc5::tmem_ld16(tmem + lane_base + t5::WACC + 64 + 16 * cg, v1);   // x g1_m
+        tc5::tmem_ld16(tmem + lane_base + col + 16 * cg, v0);        // x g1_h
+        tc5::tmem_ld16(tmem + lane_base + col + 64 + 16 * cg, v1);   // x g1_m
         tc5::tmem_ld16(tmem + lane_base + t5::TACC + 64 * tau + 16 * cg, a);
 #pragma unroll
         for (int e = 0; e < 16; ++e) a[e] += (v0[e] + v1[e]) * inv_w;
         tc5::tmem_st16(tmem + lane_base + t5::TACC + 64 * tau + 16 * cg, a);
         tc5::tmem_st_wait();
         tc5::fence_before_sync();
-        __syncthreads();
-        if (tau < 2 && w == 0) {
+        if (tau != 1) __syncthreads();
+        if (tau == 0 && w == 0) {
           tc5::fence_after_sync();
-          issue_wgrad(tau + 1, tc5::elect_one());
+          issue_wgrad(2, tc5::elect_one(), t5::WACC, &bar_w);
           __syncwarp();
         }
       }
@@ -422,6 +432,8 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     if (++ndone % FLUSH == 0) flush_all();
     PROF(11);
     tile = nxt; ti = tn; buf ^= 1;
+    nxt = (tile >= 0) ? tile_resolve<2>(cm, pre, tn) : -1;
+    PROF(12);
   }
   PROF_DUMP("decoder_tc5", 14);
   flush_all();

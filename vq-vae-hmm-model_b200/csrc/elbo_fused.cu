@@ -141,6 +141,19 @@ __device__ __forceinline__ void load_rows(float* dst, const float* __restrict__ 
 // [0, tmax) are zero-filled): used to fetch the NEXT tile's inputs while the current tile computes
 __device__ __forceinline__ void prefetch_rows(float* dst, const float* __restrict__ src, int nrows, int64_t b, int T,
                                               int t0, int tmax) {
+  if (((T & 3) == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
+    // 16-byte granules: t0 - HL is a multiple of 4 (TT and HL are), rows start 16-byte aligned when T % 4 == 0;
+    // a granule that straddles tmax is zero-filled beyond it through the src-size operand
+    for (int i = threadIdx.x; i < nrows * (NC / 4); i += NTH) {
+      const int r = i / (NC / 4), j = (i - r * (NC / 4)) * 4, t = t0 - HL + j;
+      int nval = (t < 0) ? 0 : (tmax - t);
+      nval = nval < 0 ? 0 : (nval > 4 ? 4 : nval);
+      const float* g = src + (b * nrows + r) * (int64_t)T + (nval ? t : 0);
+      const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst + r * PT + j);
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(d), "l"(g), "r"(4 * nval) : "memory");
+    }
+    return;
+  }
   for (int i = threadIdx.x; i < nrows * NC; i += NTH) {
     const int r = i / NC, j = i - r * NC, t = t0 - HL + j;
     const bool ok = (t >= 0 && t < tmax);
@@ -161,6 +174,40 @@ __device__ __forceinline__ int64_t next_tile(const Common& cm, int64_t tile, Til
     if (ti.t0 < ti.Leff + SKIP) return tile;
   }
   return -1;
+}
+
+// Software-pipelined tile selection for the persistent tile kernels: the length of the candidate tile
+// AFTER the next one is loaded at the top of an iteration (tile_pre) and only looked at once the
+// current tile is done (tile_resolve), so the dependent global load -- and the index division -- are
+// off the critical path of every tile (they were 3-6 % of the three kernels).
+struct TilePre {
+  int64_t cand, b, L;
+  int t0;
+};
+__device__ __forceinline__ TilePre tile_pre(const Common& cm, int64_t cand) {
+  TilePre p;
+  p.cand = cand; p.b = 0; p.L = 0; p.t0 = 0;
+  if (cand < cm.ntiles) {
+    if (cm.ntiles <= 0x7fffffffLL) {       // 32-bit division whenever the tile count allows it
+      const unsigned bb = (unsigned)cand / (unsigned)cm.tiles_per_seq;
+      p.b = bb;
+      p.t0 = (int)((unsigned)cand - bb * (unsigned)cm.tiles_per_seq) * TT;
+    } else {
+      p.b = cand / cm.tiles_per_seq;
+      p.t0 = (int)(cand - p.b * cm.tiles_per_seq) * TT;
+    }
+    p.L = cm.lengths[p.b];
+  }
+  return p;
+}
+template <int SKIP>
+__device__ __forceinline__ int64_t tile_resolve(const Common& cm, const TilePre& p, TileInfo& ti) {
+  if (p.cand >= cm.ntiles) return -1;
+  ti.b = p.b; ti.t0 = p.t0;
+  ti.L = (int)(p.L < 0 ? 0 : (p.L > cm.T ? cm.T : p.L));
+  ti.Leff = ti.L < 1 ? 1 : ti.L;
+  if (ti.t0 < ti.Leff + SKIP) return p.cand;
+  return next_tile<SKIP>(cm, p.cand + gridDim.x, ti);   // ragged batch: this tile is outside the dependency cone
 }
 
 __device__ __forceinline__ double block_sum_d(double v, double* sh) {

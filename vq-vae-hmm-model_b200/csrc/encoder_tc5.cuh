@@ -221,11 +221,16 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
   int64_t tile = next_tile<6>(cm, blockIdx.x, ti);
   if (tile >= 0) fetch(ti, XU0);
   cp_async_commit();
+  int64_t nxt = (tile >= 0) ? next_tile<6>(cm, tile + gridDim.x, tn) : -1;
   while (tile >= 0) {
-    const int64_t nxt = next_tile<6>(cm, tile + gridDim.x, tn);
+    PROF(12);
     if (nxt >= 0) fetch(tn, buf ? XU0 : XU1);
     cp_async_commit();
+    PROF(9);
+    const TilePre pre = tile_pre(cm, nxt >= 0 ? nxt + gridDim.x : cm.ntiles);   // consumed after the tile
+    PROF(10);
     cp_async_wait_prev();
+    PROF(11);
     const float* XU = buf ? XU1 : XU0;
     const int t0 = ti.t0, T = cm.T, L = ti.L;
     const int64_t b = ti.b;
@@ -331,8 +336,9 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
     __syncthreads(); PROF(8);
     if (++ndone % FLUSH == 0) flush_acc(part, acc, CF::ACC_A);
     tile = nxt; ti = tn; buf ^= 1;
+    nxt = (tile >= 0) ? tile_resolve<6>(cm, pre, tn) : -1;
   }
-  PROF_DUMP("enc_prior", 9);
+  PROF_DUMP("enc_prior", 13);
   // per-CTA partials
   flush_acc(part, acc, CF::ACC_A);
   double* lp = cm.loss_part + (int64_t)blockIdx.x * LP;
@@ -447,10 +453,11 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
   int64_t tile = next_tile<3>(cm, blockIdx.x, ti);
   if (tile >= 0) fetch(ti, XU0, DQ0);
   cp_async_commit();
+  int64_t nxt = (tile >= 0) ? next_tile<3>(cm, tile + gridDim.x, tn) : -1;
   while (tile >= 0) {
-    const int64_t nxt = next_tile<3>(cm, tile + gridDim.x, tn);
     if (nxt >= 0) fetch(tn, buf ? XU0 : XU1, buf ? DQ0 : DQ1);
     cp_async_commit();
+    const TilePre pre = tile_pre(cm, nxt >= 0 ? nxt + gridDim.x : cm.ntiles);   // consumed after the tile
     cp_async_wait_prev();
     const float* XU = buf ? XU1 : XU0;
     const float* DQ = buf ? DQ1 : DQ0;
@@ -606,6 +613,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
     PROF(8);
     if (++ndone % FLUSH == 0) flush_all();
     tile = nxt; ti = tn; buf ^= 1;
+    nxt = (tile >= 0) ? tile_resolve<3>(cm, pre, tn) : -1;
   }
   PROF_DUMP("enc_bwd_tc5", 9);
   flush_all();

@@ -208,3 +208,47 @@ __device__ __forceinline__ void sk_prior_bwd_reduce(const float* __restrict__ sc
     else accB0[h] += sum;
   }
 }
+
+// ---- weight gradient of a 1x1 layer with few output rows (decoder.to_params: 2C = 10 rows):
+//   acc[p*PA + o] += sum_{j owned} dP[p][j] * Y[o][j],  p < NP, o < HH
+// thread (o = tid % HH, s = tid / HH): 1 + NP 16-byte loads (the dP ones are warp broadcasts) per 4 NP FMAs.
+template <int NP, int HH, int NS = NTH / HH>
+struct SkRows {
+  static constexpr int PS = NP | 1;
+  static constexpr int FLOATS = NS * HH * PS;
+};
+
+template <int NP, int HH, int NS = NTH / HH>
+__device__ __forceinline__ void sk_wgrad_rows(const float* __restrict__ dP, const float* __restrict__ Y,
+                                              float* __restrict__ scr) {
+  using SK = SkRows<NP, HH, NS>;
+  const int o = threadIdx.x % HH, s = threadIdx.x / HH;
+  if (s >= NS) return;
+  float g[NP];
+#pragma unroll
+  for (int p = 0; p < NP; ++p) g[p] = 0.f;
+  for (int q = s; q < TT / 4; q += NS) {
+    const int j = J0 + 4 * q;
+    const float4 y = *reinterpret_cast<const float4*>(Y + o * PT + j);
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+      const float4 d = *reinterpret_cast<const float4*>(dP + p * PT + j);
+      g[p] = fmaf(d.w, y.w, fmaf(d.z, y.z, fmaf(d.y, y.y, fmaf(d.x, y.x, g[p]))));
+    }
+  }
+  float* dst = scr + (s * HH + o) * SK::PS;
+#pragma unroll
+  for (int p = 0; p < NP; ++p) dst[p] = g[p];
+}
+
+template <int NP, int HH, int NS = NTH / HH>
+__device__ __forceinline__ void sk_wgrad_rows_reduce(const float* __restrict__ scr, float* __restrict__ accW, int PA) {
+  using SK = SkRows<NP, HH, NS>;
+  for (int i = threadIdx.x; i < HH * NP; i += NTH) {
+    const int o = i / NP, p = i - o * NP;
+    float sum = 0.f;
+#pragma unroll
+    for (int s = 0; s < NS; ++s) sum += scr[(s * HH + o) * SK::PS + p];
+    accW[p * PA + o] += sum;
+  }
+}
