@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
   constexpr int C = CF::C, H = CF::H, H2 = CF::H2, K = CF::K;
   static_assert(H == 64 && H2 == 32, "the tcgen05 encoder tiling is written for hidden_dim = 64, hidden_dim2 = 32");
   extern __shared__ __align__(1024) uint8_t smraw[];
-  __shared__ __align__(8) uint64_t bar_f, bar_d, bar_w;
+  __shared__ __align__(8) uint64_t bar_f, bar_d, bar_w, bar_w2;
   __shared__ uint32_t tmem_sh, amax_sh, amax2_sh;
   uint8_t* W2h = smraw;                   // fp16 conv2 weights
   uint8_t* RA = W2h + t5e::W_BYTES;       // h1 parts
@@ -385,7 +385,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   for (int i = tid; i < (int)(t5e::Sz<CF>::C / 4); i += NTH) reinterpret_cast<uint32_t*>(smraw)[i] = 0u;
   if (tid == 0) {
-    tc5::mbar_init(&bar_f, 1); tc5::mbar_init(&bar_d, 1); tc5::mbar_init(&bar_w, 1);
+    tc5::mbar_init(&bar_f, 1); tc5::mbar_init(&bar_d, 1); tc5::mbar_init(&bar_w, 1); tc5::mbar_init(&bar_w2, 1);
     tc5::mbar_init_fence();
     amax_sh = 0u;
   }
@@ -403,7 +403,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
   tc5::fence_after_sync();
   const uint32_t tmem = tmem_sh, sRA = tc5::smem_u32(RA), sRB = tc5::smem_u32(RB), sSB = tc5::smem_u32(SBf),
                  sW2 = tc5::smem_u32(W2h);
-  uint32_t par_f = 0, par_d = 0, par_w = 0;
+  uint32_t par_f = 0, par_d = 0, par_w = 0, par_w2 = 0;
   const uint32_t lane_base = (uint32_t)(32 * (w & 3)) << 16;
   const int jrow = 32 * (w & 3) + lane, cg = w >> 2;
   constexpr uint32_t ID_D64 = tc5::idesc_f16(64, 0, 1), ID_W128 = tc5::idesc_f16(128, 1, 1);
@@ -532,15 +532,15 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
     tc5::fence_before_sync();
     __syncthreads(); PROF(5);
     // ---- tensor core: dh1 pre-mask (input gradient of conv2) and the weight gradient of tap 0
-    auto issue_wgrad = [&](int tau, bool lead) {   // WACC = [dh2_h; dh2_m; -] x [h1_h; h1_m](shifted by tau) over the 120 owned columns
+    auto issue_wgrad = [&](int tau, bool lead, uint32_t acc_col, uint64_t* bar) {   // acc = [dh2_h; dh2_m; -] x [h1_h; h1_m](shifted by tau) over the 120 owned columns
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const uint64_t a = (i < 7) ? tc5::make_desc(sRB + (J0 + 1 + 16 * i) * 16, 128, t5e::PLANE)
                                    : tc5::make_desc(sSB, 128, t5e::SB_PLANE);
         const uint64_t bq = tc5::make_desc(sRA + (J0 + 16 * i + tau) * 16, 128, t5e::PLANE);
-        if (lead) tc5::mma_f16(tmem + t5e::WACC, a, bq, ID_W128, i ? 1u : 0u);
+        if (lead) tc5::mma_f16(tmem + acc_col, a, bq, ID_W128, i ? 1u : 0u);
       }
-      if (lead) tc5::commit(&bar_w);
+      if (lead) tc5::commit(bar);
     };
     if (w == 0) {
       tc5::fence_after_sync();
@@ -560,7 +560,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
           }
         }
       if (lead) tc5::commit(&bar_d);
-      issue_wgrad(0, lead);
+      issue_wgrad(0, lead, t5e::WACC, &bar_w);
       __syncwarp();
     }
     tc5::mbar_wait(&bar_d, par_d); par_d ^= 1u;
@@ -578,6 +578,11 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
     }
     tc5::fence_before_sync();
     __syncthreads(); PROF(6);
+    if (w == 0) {   // the input-gradient accumulator is free now: tap 1 runs there under the FFMA phase below
+      tc5::fence_after_sync();
+      issue_wgrad(1, tc5::elect_one(), t5e::ACC, &bar_w2);
+      __syncwarp();
+    }
     // conv1 gradients: dW1[tau][o][c] += sum_t dh1[o][t] x[c][t+tau-1], bias: register-blocked FFMA (skinny.cuh);
     // slice partials go to the C_W2 block of acc, which this build never uses (dW2 accumulates in TMEM)
     static_assert(SkTaps<C, H, 4>::FLOATS <= 3 * H2 * CF::PW_H, "conv1 gradient scratch must fit the unused C_W2 block");
@@ -585,16 +590,19 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
     __syncthreads();
     sk_wgrad_taps_reduce<C, H, 4>(acc + CF::C_W2, acc + CF::C_W1, acc + CF::C_B1);
     PROF(7);
-    {   // conv2 weight gradient: drain each tap's tile sum into the persistent TMEM accumulators
+    {   // conv2 weight gradient: drain each tap's tile sum into the persistent TMEM accumulators.  Tap 0 (WACC) and
+        // tap 1 (ACC) were issued under the previous phases; tap 2 reuses WACC as soon as tap 0 is drained.
       const float inv_w = 1.f / (sD * sH);
 #pragma unroll 1
       for (int tau = 0; tau < 3; ++tau) {
-        tc5::mbar_wait(&bar_w, par_w); par_w ^= 1u;
+        const uint32_t col = (tau == 1) ? t5e::ACC : t5e::WACC;
+        if (tau == 1) { tc5::mbar_wait(&bar_w2, par_w2); par_w2 ^= 1u; }
+        else          { tc5::mbar_wait(&bar_w, par_w); par_w ^= 1u; }
         tc5::fence_after_sync();
         if ((w & 3) < 2) {   // lanes 0..63 carry data
           float v0[16], v1[16], a[16];
-          tc5::tmem_ld16(tmem + lane_base + t5e::WACC + 16 * cg, v0);        // x h1_h
-          tc5::tmem_ld16(tmem + lane_base + t5e::WACC + 64 + 16 * cg, v1);   // x h1_m
+          tc5::tmem_ld16(tmem + lane_base + col + 16 * cg, v0);        // x h1_h
+          tc5::tmem_ld16(tmem + lane_base + col + 64 + 16 * cg, v1);   // x h1_m
           tc5::tmem_ld16(tmem + lane_base + t5e::TACC + 64 * tau + 16 * cg, a);
 #pragma unroll
           for (int e = 0; e < 16; ++e) a[e] += (v0[e] + v1[e]) * inv_w;
@@ -602,10 +610,10 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
           tc5::tmem_st_wait();
         }
         tc5::fence_before_sync();
-        __syncthreads();
-        if (tau < 2 && w == 0) {
+        if (tau != 1) __syncthreads();
+        if (tau == 0 && w == 0) {
           tc5::fence_after_sync();
-          issue_wgrad(tau + 1, tc5::elect_one());
+          issue_wgrad(2, tc5::elect_one(), t5e::WACC, &bar_w);
           __syncwarp();
         }
       }
