@@ -492,11 +492,12 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
       }
     }
     __syncthreads(); PROF(2);
-    // to_logits gradients: dW3[k][c] += sum_t dl[k][t] h2[c][t]
-    for (int unit = w; unit < H2 / 8; unit += NW)
-      gemm_time<1, 1, KST, J0, PT>(LQ, H2b + unit * 8 * PT, acc + CF::C_W3 + unit * 8, 0, CF::PW_H2);
+    // to_logits gradients: dW3[k][c] += sum_t dl[k][t] h2[c][t] as FFMA (skinny.cuh; slice partials in the unused C_W2 block)
+    static_assert(SkRows<K, H2>::FLOATS <= 3 * H2 * CF::PW_H, "to_logits gradient scratch must fit the unused C_W2 block");
+    sk_wgrad_rows<K, H2>(LQ, H2b, acc + CF::C_W2);
     row_sums<J0, TT / 4, PT, NW>(LQ, K, acc + CF::C_B3);
     __syncthreads(); PROF(3);
+    sk_wgrad_rows_reduce<K, H2>(acc + CF::C_W2, acc + CF::C_W3, CF::PW_H2);
     // dh2 = relu'(h2) * W3^T dl, in place
     cols_op<H2, 1, 2, 1, 1, true>(W3s, 0, CF::PW_H2, LQ, EpiReluMask{H2b});
     __syncthreads(); PROF(4);
