@@ -72,9 +72,11 @@ def test_posterior_variants_vs_oracle(K, T, B, variant):
         ll, gamma, xi = Fn.hmm_posterior(*d)
         ll1, gamma1, _ = Fn.hmm_posterior(*d, want_xi=False)
         path, gamma2, ll2 = Fn.hmm_decode(*d)
+        ll0 = Fn.hmm_forward(*d)            # log-likelihood only: the one-pass kernel without its sweeps ("auto")
     finally:
         Fn.hmm_posterior_select("auto")
     assert np.allclose(ll.cpu().numpy(), ll64, rtol=TOL, atol=1e-5)
+    assert np.allclose(ll0.cpu().numpy(), ll64, rtol=TOL, atol=1e-5)
     assert np.abs(gamma.cpu().numpy() - gamma64).max() <= TOL
     assert np.abs(xi.cpu().numpy() - xi64).max() <= TOL
     assert torch.allclose(gamma, gamma1, atol=2e-6) and torch.allclose(ll, ll1, rtol=1e-6)

@@ -121,9 +121,9 @@ static bool onepass_fits(int64_t T, int64_t K, const void* A, const void* Bm, co
   const size_t wb = 32 * (size_t)(hw::pitch_odd16(S * (int)(K * K)) + hw::pitch_odd16(S * (int)K)) * 4;
   return wb <= HW_MAX_WARP_BYTES;
 }
-template <int K, bool XI>
+template <int K, bool XI, bool LL_ONLY = false>
 static int launch_onepass(hw::Args a, cudaStream_t st) {
-  auto kern = hw::posterior_kernel<K, XI>;
+  auto kern = hw::posterior_kernel<K, XI, LL_ONLY>;
   const size_t wb = 32 * (size_t)(a.SA + a.SB) * 4;
   int wpb = (int)((56 * 1024) / wb);
   wpb = wpb < 1 ? 1 : (wpb > 4 ? 4 : wpb);
@@ -159,8 +159,9 @@ static int hmm_posterior_onepass(const float* log_pi, const float* A, const floa
   a.magicB = (unsigned)(((1ull << 32) + gb - 1) / gb);
   a.loglik = loglik; a.gamma = gamma; a.xi = xi;
   int rc = 0;
-  if (xi) { DISPATCH_K(K, (rc = launch_onepass<KK, true>(a, st))); }
-  else    { DISPATCH_K(K, (rc = launch_onepass<KK, false>(a, st))); }
+  if (!gamma) { DISPATCH_K(K, (rc = launch_onepass<KK, false, true>(a, st))); }   // log-likelihood only
+  else if (xi) { DISPATCH_K(K, (rc = launch_onepass<KK, true>(a, st))); }
+  else         { DISPATCH_K(K, (rc = launch_onepass<KK, false>(a, st))); }
   return rc;
 }
 
@@ -179,6 +180,9 @@ static hs::Args base_args(const float* log_pi, const float* A, const float* Bm, 
 
 int hmm_forward(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B,
                 int64_t T, int64_t K, float* loglik, float* alpha, cudaStream_t st) {
+  // log-likelihood only: the time-parallel warp kernel (hmm_warp.cuh) without its sweeps
+  if (!alpha && loglik && onepass_allowed() && onepass_fits(T, K, A, Bm, A, nullptr))
+    return hmm_posterior_onepass(log_pi, A, Bm, lengths, B, T, K, loglik, nullptr, nullptr, st);
   if (small_k(K)) {
     hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
     a.loglik = loglik; a.alpha_log = alpha;

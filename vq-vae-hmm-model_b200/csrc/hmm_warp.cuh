@@ -93,7 +93,9 @@ __device__ __forceinline__ void sts4(float* p, const float* v) {
     *reinterpret_cast<float4*>(p + i * 4) = make_float4(v[i * 4], v[i * 4 + 1], v[i * 4 + 2], v[i * 4 + 3]);
 }
 
-template <int K, bool XI>
+// LL_ONLY: forward log-likelihood only (hmm_forward without all-prefix alpha): load, pass 1 without the
+// write-back of P_t, prefix scan, log-likelihood -- no suffix scan, no sweeps, no stores.
+template <int K, bool XI, bool LL_ONLY = false>
 __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
   constexpr int KK = K * K;
   constexpr float LOG2E = 1.4426950408889634f, LN2 = 0.6931471805599453f;
@@ -179,7 +181,7 @@ __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
           for (int i = 0; i < KK; ++i) M[i] *= sc;
         }
       }
-      sts4<KK>(myA + g * 4 * KK, Av);
+      if (!LL_ONLY) sts4<KK>(myA + g * 4 * KK, Av);
     }
     // ---- scan over the lanes ---------------------------------------------------------
     // prefix: lane 0 contributes the rank-one matrix 1 * (v0 M_0), so that every prefix has
@@ -202,9 +204,12 @@ __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
       // vector-times-matrix scan: lane l holds (pre_l, Pm_l); combining the segment ending at
       // l-d with the segment ending at l: pre <- pre_other * Pm_l, Pm <- Pm_other * Pm_l.
       // Lanes whose segment already starts at lane 0 (lane < d) are final.
+      // Three Kogge-Stone rounds inside groups of 8 lanes (matrix products), then the carry vector of each
+      // group is handed to the next one serially (3 cheap vector x matrix steps instead of 2 matrix rounds).
       bool has = (lane == 0);   // 'pre' valid (segment reaches lane 0)
+      const int li = lane & 7;
 #pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
+      for (int d = 1; d < 8; d <<= 1) {
         float opre[K], oPm[KK];
 #pragma unroll
         for (int j = 0; j < K; ++j) opre[j] = __shfl_up_sync(0xffffffffu, pre[j], d);
@@ -212,7 +217,7 @@ __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
         for (int i = 0; i < KK; ++i) oPm[i] = __shfl_up_sync(0xffffffffu, Pm[i], d);
         const int oex = __shfl_up_sync(0xffffffffu, pex, d);
         const bool ohas = __shfl_up_sync(0xffffffffu, (int)has, d) != 0;
-        if (lane >= d && !has) {
+        if (li >= d && !has) {
           pex += oex;
           if (ohas) {
 #pragma unroll
@@ -235,11 +240,32 @@ __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
           }
         }
       }
+#pragma unroll
+      for (int g = 1; g < 4; ++g) {
+        float vpre[K];
+#pragma unroll
+        for (int j = 0; j < K; ++j) vpre[j] = __shfl_sync(0xffffffffu, pre[j], 8 * g - 1);
+        const int vex = __shfl_sync(0xffffffffu, pex, 8 * g - 1);
+        if ((lane >> 3) == g) {
+          float n[K];
+#pragma unroll
+          for (int j = 0; j < K; ++j) {
+            float acc = vpre[0] * Pm[j];
+#pragma unroll
+            for (int k = 1; k < K; ++k) acc = fmaf(vpre[k], Pm[k * K + j], acc);
+            n[j] = acc;
+          }
+          pex += vex;
+          const float sc = pow2_rescale(fmaxf(max_of<K>(n), 1e-37f), &pex);
+#pragma unroll
+          for (int j = 0; j < K; ++j) pre[j] = n[j] * sc;
+        }
+      }
     }
     // suffix: only the row sums (suffix product applied to the all-ones vector) are needed:
     // w_l = M_l M_{l+1} ... M_31 1.  Carry (w, Sm) with Sm the segment product.
     float suf[K];
-    {
+    if (!LL_ONLY) {
       float Sm[KK];
 #pragma unroll
       for (int i = 0; i < KK; ++i) Sm[i] = M[i];
@@ -251,15 +277,16 @@ __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
         for (int j = 1; j < K; ++j) acc += M[i * K + j];
         suf[i] = acc;
       }
+      const int li = lane & 7;
 #pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
+      for (int d = 1; d < 8; d <<= 1) {
         float osuf[K], oSm[KK];
 #pragma unroll
         for (int j = 0; j < K; ++j) osuf[j] = __shfl_down_sync(0xffffffffu, suf[j], d);
 #pragma unroll
         for (int i = 0; i < KK; ++i) oSm[i] = __shfl_down_sync(0xffffffffu, Sm[i], d);
         const bool ohas = __shfl_down_sync(0xffffffffu, (int)has, d) != 0;
-        if (lane + d < 32 && !has) {
+        if (li + d < 8 && !has) {
           if (ohas) {
 #pragma unroll
             for (int i = 0; i < K; ++i) {
@@ -281,6 +308,25 @@ __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
           }
         }
       }
+#pragma unroll
+      for (int g = 2; g >= 0; --g) {   // hand the carry of group g+1 (its first lane) to group g
+        float vs[K];
+#pragma unroll
+        for (int j = 0; j < K; ++j) vs[j] = __shfl_sync(0xffffffffu, suf[j], 8 * g + 8);
+        if ((lane >> 3) == g) {
+          float n[K];
+#pragma unroll
+          for (int i = 0; i < K; ++i) {
+            float acc = Sm[i * K] * vs[0];
+#pragma unroll
+            for (int k = 1; k < K; ++k) acc = fmaf(Sm[i * K + k], vs[k], acc);
+            n[i] = acc;
+          }
+          const float sc = pow2_rescale(fmaxf(max_of<K>(n), 1e-37f));
+#pragma unroll
+          for (int j = 0; j < K; ++j) suf[j] = n[j] * sc;
+        }
+      }
     }
     // log-likelihood: lane 31 holds v0 M_0 ... M_31 (scaled by 2^-pex)
     if (a.loglik) {
@@ -292,6 +338,7 @@ __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
         a.loglik[b] = (L > 0) ? (float)((double)logf(s) + (double)pex * (double)LN2 + ms) : 0.f;
       }
     }
+    if (LL_ONLY) { __syncwarp(); continue; }
     // start vectors of my chunk
     float fin[K], bin[K];
 #pragma unroll
