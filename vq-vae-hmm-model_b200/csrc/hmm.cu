@@ -19,7 +19,10 @@ static inline bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 #endif
 constexpr int HS_TC = VHMM_HS_TC;   // steps per staged slab
 constexpr int HS_NT = VHMM_HS_NT;   // rows (threads) per CTA
-constexpr int SCAN_CH = 128; // steps per scan chunk
+#ifndef VHMM_SCAN_CH
+#define VHMM_SCAN_CH 64   /* measured at cfg 4 (B=64, T=65536): 32 -> 0.160 ms, 64 -> 0.110 ms, 128 -> 0.117 ms (log-lik) */
+#endif
+constexpr int SCAN_CH = VHMM_SCAN_CH; // steps per scan chunk
 
 static int64_t psi_bytes(int64_t K) { return K <= 4 ? 1 : K; }
 

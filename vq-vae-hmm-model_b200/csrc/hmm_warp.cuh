@@ -21,6 +21,7 @@
 // two.  Maths: SURVEY.md Appendix B.2/B.3; conventions of oracle/hmm.py:posteriors.
 #pragma once
 #include "hmm_small.cuh"
+#pragma nv_diag_suppress 128   // LL_ONLY instantiations leave the sweeps unreachable on purpose
 
 namespace vhmm {
 namespace hw {

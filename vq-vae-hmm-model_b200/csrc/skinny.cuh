@@ -252,3 +252,8 @@ __device__ __forceinline__ void sk_wgrad_rows_reduce(const float* __restrict__ s
     accW[p * PA + o] += sum;
   }
 }
+
+// (Measured and dropped: the input gradients of the same 1x1 layers, dg2 = relu'(g2) * Wp^T dp and
+// dh2 = relu'(h2) * W3^T dl, as FFMA over all 128 columns were not faster than the mma.sync helper --
+// 35.99 vs 35.57 ms for the decoder kernel -- because there every output column is needed, so the
+// tensor-core tile is not padded in the long dimension.)
