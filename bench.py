@@ -243,7 +243,7 @@ def main():
         dec_tfl = per_gpu_steps * DEC_FLOP_PER_STEP / (kms[1] * 1e-3) / 1e12
         dec = Fn.elbo_decoder_active()
         traffic = None   # dram bytes per launch of the active decoder kernel from its committed ncu --set full capture
-        tp = os.path.join(ROOT, "profiles", "r1b_decoder_traffic.json" if dec == "tc5" else "r1_fused_decoder_traffic.json")
+        tp = os.path.join(ROOT, "profiles", "r1c_decoder_traffic.json" if dec == "tc5" else "r1_fused_decoder_traffic.json")
         if os.path.exists(tp):
             tj = json.load(open(tp))
             if tj.get("B") == B and tj.get("T") == T:
@@ -258,7 +258,7 @@ def main():
             "share_of_step": kms[1] / ms,
             "kernels_ms": {"enc_prior": kms[0], "decoder": kms[1], "enc_bwd": kms[2]},
             "note": ("fp32-parity path: every product of the three big GEMMs is 3 fp16 tcgen05 MMAs (h*h, h*m, m*h) with "
-                     "fp32 accumulate in TMEM, so at most 1/3 of the bf16 peak is reachable; the small layers run on mma.sync"
+                     "fp32 accumulate in TMEM, so at most 1/3 of the bf16 peak is reachable; the skinny layers run as FP32 FFMA, the remaining small ones on mma.sync"
                      if dec == "tc5" else
                      "fp32-parity path: every product is 3 TF32 MMAs (hi*hi, lo*hi, hi*lo); legacy mma.sync TF32 "
                      "peaks at 512 MAC/clk/SM on B200 (tools/microbench.cu), i.e. 93 TFLOP/s of fp32-equivalent work"),

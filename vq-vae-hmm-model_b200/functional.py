@@ -167,15 +167,33 @@ def elbo_raw_streamed(d: Dims, params, x, u, lengths_dev, norms, beta: float, wa
     dev = lengths_dev.device
     B, C, T = x.shape
     U = u.shape[1]
-    if chunk <= 0:
-        chunk = max(1024, -(-B // 16))
-    chunk = min(chunk, B)
-    key = (dev.index, chunk, C, U, T)
+    # chunk schedule.  Explicit ``chunk``: uniform.  Default: geometric -- B/32, B/32, B/16, B/8, then B/4 --
+    # so that only a small first chunk's copy is exposed (the kernels are ~4x slower per byte than the copy,
+    # a chunk twice the size of its predecessor still arrives in time) while the per-call cost (kernel
+    # prologues, the 64 MB partial reduction of the finish kernel: ~0.19 ms) is paid 7 times, not 16-32.
+    # Measured at cfg 2 (tools/stream_chunk_probe.py): uniform 8 / 16 / 32 chunks = 97.0 / 97.8 / 99.2 ms.
+    if chunk > 0:
+        chunk = min(chunk, B)
+        sizes = [min(chunk, B - b0) for b0 in range(0, B, chunk)]
+    else:
+        cap = max(1024, -(-B // 4))
+        cur = max(1024, -(-B // 32))
+        sizes, left, first = [], B, True
+        while left > 0:
+            n = min(cur, left)
+            sizes.append(n)
+            left -= n
+            if first:
+                first = False          # the first size is used twice
+            else:
+                cur = min(cap, cur * 2)
+    big = max(sizes)
+    key = (dev.index, big, C, U, T)
     st = _stream_state.get(key)
     if st is None:
         _stream_state.clear()           # one staging set at a time (it is hundreds of MB)
         st = {"copy": torch.cuda.Stream(device=dev),
-              "buf": [(torch.empty(chunk, C, T, device=dev), torch.empty(chunk, U, T, device=dev)) for _ in range(2)],
+              "buf": [(torch.empty(big, C, T, device=dev), torch.empty(big, U, T, device=dev)) for _ in range(2)],
               "copied": [torch.cuda.Event(), torch.cuda.Event()], "done": [torch.cuda.Event(), torch.cuda.Event()]}
         _stream_state[key] = st
     cs = torch.cuda.current_stream(dev)
@@ -183,9 +201,9 @@ def elbo_raw_streamed(d: Dims, params, x, u, lengths_dev, norms, beta: float, wa
     copy_s.wait_stream(cs)              # staging buffers may still be read by earlier work on the compute stream
     sums_t = torch.zeros(4, device=dev, dtype=torch.float64)
     grads_t = torch.zeros(param_count(d), device=dev, dtype=torch.float32) if want_grads else None
-    for i, b0 in enumerate(range(0, B, chunk)):
-        b1 = min(B, b0 + chunk)
-        n, k = b1 - b0, i % 2
+    b0 = 0
+    for i, n in enumerate(sizes):
+        b1, k = b0 + n, i % 2
         xb, ub = st["buf"][k]
         with torch.cuda.stream(copy_s):
             if i >= 2:
@@ -199,6 +217,7 @@ def elbo_raw_streamed(d: Dims, params, x, u, lengths_dev, norms, beta: float, wa
         if want_grads:
             grads_t += grads
         st["done"][k].record(cs)
+        b0 = b1
     return sums_t, grads_t
 
 
