@@ -164,3 +164,30 @@ def test_trainer_and_train_model_fused_reduce_the_loss(capsys):
     out = capsys.readouterr().out
     assert "Epoch 1/2, Loss:" in out and "Epoch 2/2, Loss:" in out
     assert all(torch.isfinite(p).all() for p in m.parameters())
+
+
+def test_serving_infer_matches_reference_outputs():
+    """/infer body (inference_api/app.py:57-77) on the shipped checkpoint: each sequence of the golden batch
+    (outputs produced by the unmodified reference) as one request; equal-length requests fused into one
+    launch give bit-identical results to single calls."""
+    import vhmm_b200 as V
+    g = load_golden("base_ckpt")
+    d = g["dims"]
+    m = V.VAE_HMM(d["C"], d["H"], d["K"], d["H2"], u_dim=d["U"], trans_hidden=d["TH"])
+    m.load_state_dict(g["params"])
+    m = m.cuda().eval()
+    x = g["x"]
+    # the fixture ran the whole (B,C,T) batch through the reference; rows are independent, so row b as a
+    # single (1,C,T) request must reproduce row b of the reference's outputs
+    reqs = [x[b].tolist() for b in range(x.shape[0])]
+    one = V.serving.infer(m, reqs[0])
+    assert set(one) == {"mu", "logvar", "regime_probs"}
+    many = V.serving.infer_many(m, reqs + [x[0, :, :17].tolist()])
+    assert len(many) == len(reqs) + 1 and len(many[-1]["mu"][0]) == 17
+    for b in range(len(reqs)):
+        for key, ref in (("mu", g["raw"]["mu"]), ("logvar", g["raw"]["logvar"]), ("regime_probs", g["raw"]["q"])):
+            got = np.asarray(many[b][key], np.float64)
+            assert np.abs(got - ref[b]).max() <= 1e-5 * max(1.0, np.abs(ref[b]).max()), (b, key)
+    assert one == many[0]
+    single_last = V.serving.infer(m, x[0, :, :17].tolist())
+    assert single_last == many[-1]

@@ -13,9 +13,10 @@ from .data import (RandomChunkDataset, collate_fn, train_model, device,  # noqa:
                    save_checkpoint, load_checkpoint)
 from . import parallel  # noqa: F401
 from . import training  # noqa: F401
+from . import serving  # noqa: F401
 from .training import DeviceCorpus, DeviceChunkLoader, FusedAdam, Trainer, train_model_fused  # noqa: F401
 
 __all__ = ["VAE_HMM", "Encoder", "Prior", "Decoder", "RandomChunkDataset", "collate_fn",
            "train_model", "device", "save_checkpoint", "load_checkpoint", "functional",
-           "parallel", "training", "DeviceCorpus", "DeviceChunkLoader", "FusedAdam", "Trainer",
+           "parallel", "training", "serving", "DeviceCorpus", "DeviceChunkLoader", "FusedAdam", "Trainer",
            "train_model_fused", "build", "lib", "VhmmError"]
