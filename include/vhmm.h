@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define VHMM_VERSION 101 /* major*100 + minor */
+#define VHMM_VERSION 102 /* major*100 + minor */
 #define VHMM_NUM_PARAMS 18
 #define VHMM_PAD_STATE 255 /* Viterbi path value for t >= lengths[b] */
 
@@ -72,7 +72,8 @@ enum {
   VHMM_OP_VITERBI = 7,
   VHMM_OP_HMM_DECODE = 8,
   VHMM_OP_HMM_SCAN = 9,
-  VHMM_OP_EMISSION_TABLE = 10
+  VHMM_OP_EMISSION_TABLE = 10,
+  VHMM_OP_HMM_INPUTS = 11
 };
 
 int vhmm_version(void);
@@ -191,6 +192,15 @@ int vhmm_emission_table(const vhmm_dims* dims, const vhmm_params* params, int64_
 /* B.1: log_b[b,t,k] = -0.5 sum_c [log(2 pi v) + (x-mu)^2/v], v = max(exp(logvar),1e-8). */
 int vhmm_emission_logprob(const float* x, const float* mu_tab, const float* logvar_tab, int64_t B,
                           int64_t C, int64_t T, int64_t K, float* log_b, void* stream);
+/* Front end of the recursion stages, fused (one FFMA kernel, no activation traffic): log_A (B,T,K,K) =
+ * Prior.forward(u) (VQ_VAE_HMM_fixed.py:59-71: Linear-ReLU-Linear on u[b,:,t], row log-softmax) and
+ * log_b (B,T,K) = the per-state emission log-probabilities of B.1 from the emission table.  Same results
+ * as vhmm_prior_fwd + vhmm_emission_logprob.  Instantiated for C=5, K=3, U=4, TH=128 and T % 4 == 0
+ * (vhmm_hmm_inputs_supported); x, u, log_A, log_b 16-byte aligned. */
+int vhmm_hmm_inputs_supported(const vhmm_dims* dims, int64_t T);
+int vhmm_hmm_inputs(const vhmm_dims* dims, const vhmm_params* params, const float* x, const float* u,
+                    int64_t B, int64_t T, const float* mu_tab, const float* logvar_tab, float* log_A,
+                    float* log_b, void* workspace, size_t workspace_bytes, void* stream);
 /* B.2: forward recursion.  loglik (B); alpha (B,T,K) log-space or NULL. */
 int vhmm_hmm_forward(const float* log_pi, const float* log_A, const float* log_b,
                      const int64_t* lengths, int64_t B, int64_t T, int64_t K, float* loglik,

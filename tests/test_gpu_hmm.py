@@ -228,3 +228,34 @@ def test_long_sequence_scan():
     assert abs(float(ll_scan[0]) - ll64[0]) <= TOL * abs(ll64[0])
     a_last = torch.logsumexp(alpha[0, T - 1], dim=0)
     assert abs(float(a_last) - ll64[0]) <= 2e-5 * abs(ll64[0])
+
+
+def test_fused_hmm_inputs_match_layerwise_and_oracle():
+    """vhmm_hmm_inputs (one FFMA kernel from raw x,u) against the float64 oracle prior / emission and against
+    vhmm_prior_fwd + vhmm_emission_logprob; T % 4 != 0 falls back to the latter."""
+    import vhmm_b200 as V
+    from vhmm_b200 import functional as Fn
+    from oracle import elbo as O
+    C, Hd, K, H2, U, TH = 5, 64, 3, 32, 4, 128
+    p = O.init_params(C, Hd, K, H2, U, TH, seed=4)
+    m = V.VAE_HMM(C, Hd, K, H2, u_dim=U)
+    m.load_state_dict(p)
+    m = m.cuda()
+    p64 = {k: v.double() for k, v in p.items()}
+    for (B, T) in ((37, 64), (5, 300), (3, 50)):
+        x, u, L = O.synth_batch(B, C, U, T, seed=B + T)
+        x, u = x * 2.0, u * 1.5
+        lp64, lA64 = O.prior(p64, u.double(), U)
+        mu_t, lv_t = H.emission_table(p64, T, O.decode)
+        lb64 = H.emission_logprob(x.numpy(), mu_t.numpy(), lv_t.numpy())
+        with torch.no_grad():
+            log_pi, log_A, log_b = m.hmm_inputs(x.cuda(), u.cuda())
+            mu_tab, lv_tab = Fn.emission_table(m._dims, m._params(), T, torch.device("cuda"))
+            fused = Fn.hmm_inputs_fused(m._dims, m._params(), x.cuda(), u.cuda(), mu_tab, lv_tab)
+            _, log_A_lw = m.prior(u.cuda())
+            log_b_lw = Fn.emission_logprob(x.cuda(), mu_tab, lv_tab)
+        assert (fused is not None) == (T % 4 == 0)
+        assert np.abs(log_pi.cpu().numpy() - lp64.numpy()).max() <= TOL
+        assert np.abs(log_A.cpu().numpy() - lA64.numpy()).max() <= TOL * max(1.0, np.abs(lA64.numpy()).max())
+        assert np.abs(log_b.cpu().numpy() - lb64).max() <= TOL * np.abs(lb64).max()
+        assert float((log_A - log_A_lw).abs().max()) <= 2e-5 and float((log_b - log_b_lw).abs().max()) <= 2e-5 * float(log_b_lw.abs().max())

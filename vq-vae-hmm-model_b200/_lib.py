@@ -16,13 +16,14 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.environ.get("VHMM_LIB") or os.path.join(_HERE, "libvhmm.so")   # VHMM_LIB: an instrumented build (tools/)
-SOURCES = ("api.cu", "elbo_layerwise.cu", "hmm.cu", "elbo_fused.cu", "batch_train.cu")
+SOURCES = ("api.cu", "elbo_layerwise.cu", "hmm.cu", "elbo_fused.cu", "batch_train.cu", "hmm_inputs.cu")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
 
 # op codes (include/vhmm.h)
 OP_ENCODER_FWD, OP_PRIOR_FWD, OP_DECODER_FWD, OP_ELBO = 1, 2, 3, 4
 OP_HMM_FORWARD, OP_HMM_POSTERIOR, OP_VITERBI, OP_HMM_DECODE, OP_HMM_SCAN, OP_EMISSION_TABLE = 5, 6, 7, 8, 9, 10
+OP_HMM_INPUTS = 11
 NUM_PARAMS = 18
 PAD_STATE = 255
 ELBO_AUTO, ELBO_LAYERWISE, ELBO_FUSED = 0, 1, 2
@@ -103,6 +104,8 @@ PROTOTYPES = {
     "vhmm_adam_step": (ctypes.c_int, [_DP, _PP, _P, _P, _P, _DBL, _DBL, _DBL, _DBL, _I64, _P, _DBL, _P, _P, _P]),
     "vhmm_emission_table": (ctypes.c_int, [_DP, _PP, _I64, _P, _P, _P, _SZ, _P]),
     "vhmm_emission_logprob": (ctypes.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P, _P]),
+    "vhmm_hmm_inputs_supported": (ctypes.c_int, [_DP, _I64]),
+    "vhmm_hmm_inputs": (ctypes.c_int, [_DP, _PP, _P, _P, _I64, _I64, _P, _P, _P, _P, _P, _SZ, _P]),
     "vhmm_hmm_forward": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P]),
     "vhmm_hmm_posterior": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _SZ, _P]),
     "vhmm_hmm_posterior_select": (ctypes.c_int, [ctypes.c_int]),

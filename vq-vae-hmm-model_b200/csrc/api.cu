@@ -44,6 +44,10 @@ int hmm_viterbi(const float*, const float*, const float*, const int64_t*, int64_
 int hmm_decode(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, float*, void*, size_t, cudaStream_t);
 int hmm_scan(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
 int hmm_posterior_select(int mode);
+// hmm_inputs.cu
+bool hmm_inputs_supported(const vhmm_dims& d, int64_t T);
+size_t hmm_inputs_workspace_bytes(const vhmm_dims& d, int64_t T);
+int hmm_inputs(const vhmm_dims&, const vhmm_params&, const float*, const float*, int64_t, int64_t, const float*, const float*, float*, float*, void*, size_t, cudaStream_t);
 // batch_train.cu
 int gather_chunks(const float*, const float*, int64_t, int64_t, int64_t, const int64_t*, const int64_t*, int64_t, int64_t, float*, float*, cudaStream_t);
 int adam_step(const vhmm_dims&, float* const*, const float*, float*, float*, double, double, double, double, int64_t, const float*, double, float*, double*, cudaStream_t);
@@ -101,6 +105,8 @@ size_t vhmm_workspace_bytes(int op, const vhmm_dims* dims, int64_t B, int64_t T)
     case VHMM_OP_HMM_FORWARD: case VHMM_OP_HMM_POSTERIOR: case VHMM_OP_VITERBI:
     case VHMM_OP_HMM_DECODE: case VHMM_OP_HMM_SCAN:
       return hmm_workspace_bytes(op, B, T, dims ? dims->K : 0);
+    case VHMM_OP_HMM_INPUTS:
+      return dims_ok(dims) ? hmm_inputs_workspace_bytes(*dims, T) : 0;
     default:
       if (!dims_ok(dims)) return 0;
       if (op == VHMM_OP_ELBO && elbo_impl_for(*dims) == VHMM_ELBO_FUSED) return fused_workspace_bytes(*dims, B, T);
@@ -175,6 +181,16 @@ int vhmm_elbo_active_impl(const vhmm_dims* dims) {
 int vhmm_argmax_regimes(const float* q, int64_t B, int64_t K, int64_t T, int64_t* regimes, void* stream) {
   ARG(q && regimes, "q/regimes"); ARG(B > 0 && K > 0 && T > 0, "B,K,T");
   return launch_argmax(q, B, K, T, regimes, (cudaStream_t)stream);
+}
+
+int vhmm_hmm_inputs_supported(const vhmm_dims* dims, int64_t T) { return dims_ok(dims) && T > 0 && hmm_inputs_supported(*dims, T) ? 1 : 0; }
+
+int vhmm_hmm_inputs(const vhmm_dims* dims, const vhmm_params* params, const float* x, const float* u, int64_t B, int64_t T,
+                    const float* mu_tab, const float* logvar_tab, float* log_A, float* log_b, void* workspace,
+                    size_t workspace_bytes, void* stream) {
+  ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(x && u && mu_tab && logvar_tab && log_A && log_b, "pointers");
+  ARG(B > 0 && T > 0, "B,T"); ARG(workspace, "workspace");
+  return hmm_inputs(*dims, *params, x, u, B, T, mu_tab, logvar_tab, log_A, log_b, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 int vhmm_gather_chunks(const float* x_cat, const float* u_cat, int64_t S_tot, int64_t C, int64_t U,

@@ -345,6 +345,24 @@ def emission_logprob(x, mu_tab, logvar_tab):
     return out
 
 
+def hmm_inputs_fused(d: Dims, params, x, u, mu_tab, logvar_tab):
+    """(log_A (B,T,K,K), log_b (B,T,K)) from raw x, u in one kernel (vhmm_hmm_inputs), or None when the
+    dims / T are outside its instantiation (the caller then uses prior_fwd + emission_logprob)."""
+    x = _f32c(x); u = _f32c(u); _require_cuda(x, u, mu_tab, logvar_tab)
+    B, C, T = x.shape
+    if not _lib.lib().vhmm_hmm_inputs_supported(ctypes.byref(d), T) or u.shape != (B, d.U, T):
+        return None
+    log_A = torch.empty(B, T, d.K, d.K, device=x.device, dtype=torch.float32)
+    log_b = torch.empty(B, T, d.K, device=x.device, dtype=torch.float32)
+    P, keep = pack_params(params)
+    with torch.cuda.device(x.device):
+        ws = workspace(x.device, _ws_bytes(_lib.OP_HMM_INPUTS, d, B, T))
+        check(_lib.lib().vhmm_hmm_inputs(ctypes.byref(d), ctypes.byref(P), _ptr(x), _ptr(u), B, T, _ptr(_f32c(mu_tab)),
+                                         _ptr(_f32c(logvar_tab)), _ptr(log_A), _ptr(log_b), _ptr(ws), ws.numel(),
+                                         _stream(x.device)), "vhmm_hmm_inputs")
+    return log_A, log_b
+
+
 def _hmm_inputs(log_pi, log_A, log_b, lengths):
     log_pi = _f32c(log_pi); log_A = _f32c(log_A); log_b = _f32c(log_b)
     _require_cuda(log_pi, log_A, log_b)

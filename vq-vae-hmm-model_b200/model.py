@@ -183,8 +183,13 @@ class VAE_HMM(nn.Module):
     def hmm_inputs(self, x, u):
         """(log_pi (K), log_A (B,T,K,K), log_b (B,T,K)) with the per-state emission table of B.1."""
         B, C, T = x.shape
-        log_pi, log_A = self.prior(u)
         mu_tab, lv_tab = Fn.emission_table(self._dims, self._params(), T, x.device)
+        if u.dim() == 3 and u.shape[1] == self._dims.U:
+            fused = Fn.hmm_inputs_fused(self._dims, self._params(), x, u, mu_tab, lv_tab)   # one FFMA kernel
+            if fused is not None:
+                log_pi = torch.log_softmax(self.prior.log_prior.detach().float(), dim=0)    # :54 (K values)
+                return log_pi, fused[0], fused[1]
+        log_pi, log_A = self.prior(u)
         log_b = Fn.emission_logprob(x, mu_tab, lv_tab)
         return log_pi, log_A, log_b
 
