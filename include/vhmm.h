@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define VHMM_VERSION 102 /* major*100 + minor */
+#define VHMM_VERSION 103 /* major*100 + minor */
 #define VHMM_NUM_PARAMS 18
 #define VHMM_PAD_STATE 255 /* Viterbi path value for t >= lengths[b] */
 
@@ -201,6 +201,15 @@ int vhmm_hmm_inputs_supported(const vhmm_dims* dims, int64_t T);
 int vhmm_hmm_inputs(const vhmm_dims* dims, const vhmm_params* params, const float* x, const float* u,
                     int64_t B, int64_t T, const float* mu_tab, const float* logvar_tab, float* log_A,
                     float* log_b, void* workspace, size_t workspace_bytes, void* stream);
+/* The whole log-likelihood path in one kernel: transition softmax + emission log-probabilities + forward
+ * recursion, one warp per sequence, alpha in registers, log_A / log_b never materialised (HBM traffic = x and
+ * u only).  loglik (B) = vhmm_hmm_forward(log_pi, vhmm_hmm_inputs(x, u)) to fp32 rounding.  log_pi: K
+ * normalised log-probabilities on the device.  Same instantiation and workspace (VHMM_OP_HMM_INPUTS) as
+ * vhmm_hmm_inputs.  Replaces the method api.py:18 / SURVEY B.2 reach through model.hmm_log_likelihood. */
+int vhmm_hmm_loglik_fused(const vhmm_dims* dims, const vhmm_params* params, const float* log_pi, const float* x,
+                          const float* u, const int64_t* lengths, int64_t B, int64_t T, const float* mu_tab,
+                          const float* logvar_tab, float* loglik, void* workspace, size_t workspace_bytes,
+                          void* stream);
 /* B.2: forward recursion.  loglik (B); alpha (B,T,K) log-space or NULL. */
 int vhmm_hmm_forward(const float* log_pi, const float* log_A, const float* log_b,
                      const int64_t* lengths, int64_t B, int64_t T, int64_t K, float* loglik,

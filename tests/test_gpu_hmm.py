@@ -259,3 +259,42 @@ def test_fused_hmm_inputs_match_layerwise_and_oracle():
         assert np.abs(log_A.cpu().numpy() - lA64.numpy()).max() <= TOL * max(1.0, np.abs(lA64.numpy()).max())
         assert np.abs(log_b.cpu().numpy() - lb64).max() <= TOL * np.abs(lb64).max()
         assert float((log_A - log_A_lw).abs().max()) <= 2e-5 and float((log_b - log_b_lw).abs().max()) <= 2e-5 * float(log_b_lw.abs().max())
+
+
+def test_fused_loglik_from_raw_inputs():
+    """vhmm_hmm_loglik_fused (transition softmax + emissions + forward recursion in one kernel, nothing
+    materialised) against the float64 oracle forward on the oracle's own prior / emissions, and against the
+    two-stage device path; ragged lengths incl. 0 and 1, T not a multiple of 128, scaled inputs."""
+    import vhmm_b200 as V
+    from vhmm_b200 import functional as Fn
+    from oracle import elbo as O
+    C, Hd, K, H2, U, TH = 5, 64, 3, 32, 4, 128
+    p = O.init_params(C, Hd, K, H2, U, TH, seed=6)
+    m = V.VAE_HMM(C, Hd, K, H2, u_dim=U)
+    m.load_state_dict(p)
+    m = m.cuda()
+    p64 = {k: v.double() for k, v in p.items()}
+    for (B, T, sx) in ((41, 64, 1.0), (7, 300, 2.0), (19, 512, 3.0), (3, 1028, 1.0)):
+        x, u, L = O.synth_batch(B, C, U, T, seed=3 * B + T)
+        x, u = x * sx, u * 1.5
+        L[0] = T
+        if B > 4:
+            L[1], L[2] = 1, 0
+        lp64, lA64 = O.prior(p64, u.double(), U)
+        mu_t, lv_t = H.emission_table(p64, T, O.decode)
+        lb64 = H.emission_logprob(x.numpy(), mu_t.numpy(), lv_t.numpy())
+        ll64 = H.forward(lp64.numpy(), lA64.numpy(), lb64, np.maximum(L.numpy(), 1))[1]
+        live = L.numpy() > 0   # a zero-length sequence has no oracle value; the device paths must agree on it
+        with torch.no_grad():
+            mu_tab, lv_tab = Fn.emission_table(m._dims, m._params(), T, torch.device("cuda"))
+            ll = Fn.hmm_loglik_fused(m._dims, m._params(), lp64.float().cuda(), x.cuda(), u.cuda(), L.cuda(), mu_tab, lv_tab)
+            assert ll is not None
+            ll_m = m.hmm_log_likelihood(x.cuda(), u.cuda(), L)
+            log_pi, log_A, log_b = m.hmm_inputs(x.cuda(), u.cuda())
+            ll_2 = Fn.hmm_forward(log_pi, log_A, log_b, L.cuda())
+            ll_full = m.hmm_log_likelihood(x.cuda(), u.cuda())
+            ll_full2 = Fn.hmm_forward(log_pi, log_A, log_b, None)
+        assert torch.equal(ll, ll_m)
+        assert np.allclose(ll.cpu().numpy()[live], ll64[live], rtol=TOL, atol=1e-6)
+        assert torch.allclose(ll, ll_2, rtol=TOL, atol=1e-6)
+        assert torch.allclose(ll_full, ll_full2, rtol=TOL, atol=1e-6)

@@ -23,6 +23,10 @@ with torch.no_grad():
     log_pi, log_A, log_b = m.hmm_inputs(x, u)
     t_dec = timed(lambda: Fn.hmm_decode(log_pi, log_A, log_b, L), iters=3, warmup=1)
     t_all = timed(lambda: m.decode_regimes(x, u, L), iters=3, warmup=1)
+    t_ll2 = timed(lambda: Fn.hmm_forward(*m.hmm_inputs(x, u), L), iters=3, warmup=1)       # front end + recursion
+    t_ll1 = timed(lambda: m.hmm_log_likelihood(x, u, L), iters=3, warmup=1)                 # one fused kernel
+    d = float((m.hmm_log_likelihood(x, u, L) - Fn.hmm_forward(*m.hmm_inputs(x, u), L)).abs().max())
 steps = B * T
 print(json.dumps({"config": f"cfg3 pipeline B={B} T={T} K=3 from raw x,u", "prior_ms": t_prior, "emission_logprob_ms": t_emis,
-                  "hmm_inputs_ms": t_inputs, "decode_ms": t_dec, "decode_regimes_ms": t_all, "steps_per_s_end_to_end": steps / (t_all * 1e-3)}))
+                  "hmm_inputs_ms": t_inputs, "decode_ms": t_dec, "decode_regimes_ms": t_all, "loglik_two_stage_ms": t_ll2,
+                  "loglik_fused_ms": t_ll1, "loglik_fused_steps_per_s": B * T / (t_ll1 * 1e-3), "loglik_max_abs_diff": d, "steps_per_s_end_to_end": steps / (t_all * 1e-3)}))

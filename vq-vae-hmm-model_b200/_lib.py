@@ -106,6 +106,7 @@ PROTOTYPES = {
     "vhmm_emission_logprob": (ctypes.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P, _P]),
     "vhmm_hmm_inputs_supported": (ctypes.c_int, [_DP, _I64]),
     "vhmm_hmm_inputs": (ctypes.c_int, [_DP, _PP, _P, _P, _I64, _I64, _P, _P, _P, _P, _P, _SZ, _P]),
+    "vhmm_hmm_loglik_fused": (ctypes.c_int, [_DP, _PP, _P, _P, _P, _P, _I64, _I64, _P, _P, _P, _P, _SZ, _P]),
     "vhmm_hmm_forward": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P]),
     "vhmm_hmm_posterior": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _SZ, _P]),
     "vhmm_hmm_posterior_select": (ctypes.c_int, [ctypes.c_int]),

@@ -48,6 +48,7 @@ int hmm_posterior_select(int mode);
 bool hmm_inputs_supported(const vhmm_dims& d, int64_t T);
 size_t hmm_inputs_workspace_bytes(const vhmm_dims& d, int64_t T);
 int hmm_inputs(const vhmm_dims&, const vhmm_params&, const float*, const float*, int64_t, int64_t, const float*, const float*, float*, float*, void*, size_t, cudaStream_t);
+int hmm_loglik_fused(const vhmm_dims&, const vhmm_params&, const float*, const float*, const float*, const int64_t*, int64_t, int64_t, const float*, const float*, float*, void*, size_t, cudaStream_t);
 // batch_train.cu
 int gather_chunks(const float*, const float*, int64_t, int64_t, int64_t, const int64_t*, const int64_t*, int64_t, int64_t, float*, float*, cudaStream_t);
 int adam_step(const vhmm_dims&, float* const*, const float*, float*, float*, double, double, double, double, int64_t, const float*, double, float*, double*, cudaStream_t);
@@ -191,6 +192,15 @@ int vhmm_hmm_inputs(const vhmm_dims* dims, const vhmm_params* params, const floa
   ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(x && u && mu_tab && logvar_tab && log_A && log_b, "pointers");
   ARG(B > 0 && T > 0, "B,T"); ARG(workspace, "workspace");
   return hmm_inputs(*dims, *params, x, u, B, T, mu_tab, logvar_tab, log_A, log_b, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int vhmm_hmm_loglik_fused(const vhmm_dims* dims, const vhmm_params* params, const float* log_pi, const float* x, const float* u,
+                          const int64_t* lengths, int64_t B, int64_t T, const float* mu_tab, const float* logvar_tab,
+                          float* loglik, void* workspace, size_t workspace_bytes, void* stream) {
+  ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(log_pi && x && u && mu_tab && logvar_tab && loglik, "pointers");
+  ARG(B > 0 && T > 0, "B,T"); ARG(workspace, "workspace");
+  return hmm_loglik_fused(*dims, *params, log_pi, x, u, lengths, B, T, mu_tab, logvar_tab, loglik, workspace, workspace_bytes,
+                          (cudaStream_t)stream);
 }
 
 int vhmm_gather_chunks(const float* x_cat, const float* u_cat, int64_t S_tot, int64_t C, int64_t U,

@@ -94,6 +94,89 @@ __device__ __forceinline__ void sts4(float* p, const float* v) {
     *reinterpret_cast<float4*>(p + i * 4) = make_float4(v[i * 4], v[i * 4 + 1], v[i * 4 + 2], v[i * 4 + 3]);
 }
 
+// Prefix scan over the lanes of the chunk products M_l (scaled by 2^-ex_l) applied to the start vector v0 of
+// lane 0: on return lane l holds pre = v0 M_0 ... M_l scaled by 2^-pex.  Lane 0 contributes the rank-one matrix
+// 1 * (v0 M_0), so that every prefix has identical rows; only that row is carried once a segment reaches lane 0.
+template <int K>
+__device__ __forceinline__ void warp_prefix_scan(const float* M, int ex, const float* v0, int lane, float* pre, int& pex) {
+  constexpr int KK = K * K;
+  pex = ex;
+  {
+    float Pm[KK];
+    if (lane == 0) {
+#pragma unroll
+      for (int j = 0; j < K; ++j) {
+        float acc = v0[0] * M[j];
+#pragma unroll
+        for (int k = 1; k < K; ++k) acc = fmaf(v0[k], M[k * K + j], acc);
+        pre[j] = acc;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < KK; ++i) Pm[i] = M[i];
+    // vector-times-matrix scan: lane l holds (pre_l, Pm_l); combining the segment ending at
+    // l-d with the segment ending at l: pre <- pre_other * Pm_l, Pm <- Pm_other * Pm_l.
+    // Lanes whose segment already starts at lane 0 (lane < d) are final.
+    // Three Kogge-Stone rounds inside groups of 8 lanes (matrix products), then the carry vector of each
+    // group is handed to the next one serially (3 cheap vector x matrix steps instead of 2 matrix rounds).
+    bool has = (lane == 0);   // 'pre' valid (segment reaches lane 0)
+    const int li = lane & 7;
+#pragma unroll
+    for (int d = 1; d < 8; d <<= 1) {
+      float opre[K], oPm[KK];
+#pragma unroll
+      for (int j = 0; j < K; ++j) opre[j] = __shfl_up_sync(0xffffffffu, pre[j], d);
+#pragma unroll
+      for (int i = 0; i < KK; ++i) oPm[i] = __shfl_up_sync(0xffffffffu, Pm[i], d);
+      const int oex = __shfl_up_sync(0xffffffffu, pex, d);
+      const bool ohas = __shfl_up_sync(0xffffffffu, (int)has, d) != 0;
+      if (li >= d && !has) {
+        pex += oex;
+        if (ohas) {
+#pragma unroll
+          for (int j = 0; j < K; ++j) {
+            float acc = opre[0] * Pm[j];
+#pragma unroll
+            for (int k = 1; k < K; ++k) acc = fmaf(opre[k], Pm[k * K + j], acc);
+            pre[j] = acc;
+          }
+          has = true;
+          const float sc = pow2_rescale(fmaxf(max_of<K>(pre), 1e-37f), &pex);
+#pragma unroll
+          for (int j = 0; j < K; ++j) pre[j] *= sc;
+        } else {
+          float R[KK];
+          mat_mul<K>(R, oPm, Pm);
+          const float sc = pow2_rescale(fmaxf(max_of<KK>(R), 1e-37f), &pex);
+#pragma unroll
+          for (int i = 0; i < KK; ++i) Pm[i] = R[i] * sc;
+        }
+      }
+    }
+#pragma unroll
+    for (int g = 1; g < 4; ++g) {
+      float vpre[K];
+#pragma unroll
+      for (int j = 0; j < K; ++j) vpre[j] = __shfl_sync(0xffffffffu, pre[j], 8 * g - 1);
+      const int vex = __shfl_sync(0xffffffffu, pex, 8 * g - 1);
+      if ((lane >> 3) == g) {
+        float n[K];
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+          float acc = vpre[0] * Pm[j];
+#pragma unroll
+          for (int k = 1; k < K; ++k) acc = fmaf(vpre[k], Pm[k * K + j], acc);
+          n[j] = acc;
+        }
+        pex += vex;
+        const float sc = pow2_rescale(fmaxf(max_of<K>(n), 1e-37f), &pex);
+#pragma unroll
+        for (int j = 0; j < K; ++j) pre[j] = n[j] * sc;
+      }
+    }
+  }
+}
+
 // LL_ONLY: forward log-likelihood only (hmm_forward without all-prefix alpha): load, pass 1 without the
 // write-back of P_t, prefix scan, log-likelihood -- no suffix scan, no sweeps, no stores.
 template <int K, bool XI, bool LL_ONLY = false>
@@ -185,84 +268,9 @@ __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
       if (!LL_ONLY) sts4<KK>(myA + g * 4 * KK, Av);
     }
     // ---- scan over the lanes ---------------------------------------------------------
-    // prefix: lane 0 contributes the rank-one matrix 1 * (v0 M_0), so that every prefix has
-    // identical rows = v0 M_0 ... M_l; only row 0 is carried.
     float pre[K];
-    int pex = ex;
-    {
-      float Pm[KK];
-      if (lane == 0) {
-#pragma unroll
-        for (int j = 0; j < K; ++j) {
-          float acc = v0[0] * M[j];
-#pragma unroll
-          for (int k = 1; k < K; ++k) acc = fmaf(v0[k], M[k * K + j], acc);
-          pre[j] = acc;
-        }
-      }
-#pragma unroll
-      for (int i = 0; i < KK; ++i) Pm[i] = M[i];
-      // vector-times-matrix scan: lane l holds (pre_l, Pm_l); combining the segment ending at
-      // l-d with the segment ending at l: pre <- pre_other * Pm_l, Pm <- Pm_other * Pm_l.
-      // Lanes whose segment already starts at lane 0 (lane < d) are final.
-      // Three Kogge-Stone rounds inside groups of 8 lanes (matrix products), then the carry vector of each
-      // group is handed to the next one serially (3 cheap vector x matrix steps instead of 2 matrix rounds).
-      bool has = (lane == 0);   // 'pre' valid (segment reaches lane 0)
-      const int li = lane & 7;
-#pragma unroll
-      for (int d = 1; d < 8; d <<= 1) {
-        float opre[K], oPm[KK];
-#pragma unroll
-        for (int j = 0; j < K; ++j) opre[j] = __shfl_up_sync(0xffffffffu, pre[j], d);
-#pragma unroll
-        for (int i = 0; i < KK; ++i) oPm[i] = __shfl_up_sync(0xffffffffu, Pm[i], d);
-        const int oex = __shfl_up_sync(0xffffffffu, pex, d);
-        const bool ohas = __shfl_up_sync(0xffffffffu, (int)has, d) != 0;
-        if (li >= d && !has) {
-          pex += oex;
-          if (ohas) {
-#pragma unroll
-            for (int j = 0; j < K; ++j) {
-              float acc = opre[0] * Pm[j];
-#pragma unroll
-              for (int k = 1; k < K; ++k) acc = fmaf(opre[k], Pm[k * K + j], acc);
-              pre[j] = acc;
-            }
-            has = true;
-            const float sc = pow2_rescale(fmaxf(max_of<K>(pre), 1e-37f), &pex);
-#pragma unroll
-            for (int j = 0; j < K; ++j) pre[j] *= sc;
-          } else {
-            float R[KK];
-            mat_mul<K>(R, oPm, Pm);
-            const float sc = pow2_rescale(fmaxf(max_of<KK>(R), 1e-37f), &pex);
-#pragma unroll
-            for (int i = 0; i < KK; ++i) Pm[i] = R[i] * sc;
-          }
-        }
-      }
-#pragma unroll
-      for (int g = 1; g < 4; ++g) {
-        float vpre[K];
-#pragma unroll
-        for (int j = 0; j < K; ++j) vpre[j] = __shfl_sync(0xffffffffu, pre[j], 8 * g - 1);
-        const int vex = __shfl_sync(0xffffffffu, pex, 8 * g - 1);
-        if ((lane >> 3) == g) {
-          float n[K];
-#pragma unroll
-          for (int j = 0; j < K; ++j) {
-            float acc = vpre[0] * Pm[j];
-#pragma unroll
-            for (int k = 1; k < K; ++k) acc = fmaf(vpre[k], Pm[k * K + j], acc);
-            n[j] = acc;
-          }
-          pex += vex;
-          const float sc = pow2_rescale(fmaxf(max_of<K>(n), 1e-37f), &pex);
-#pragma unroll
-          for (int j = 0; j < K; ++j) pre[j] = n[j] * sc;
-        }
-      }
-    }
+    int pex;
+    warp_prefix_scan<K>(M, ex, v0, lane, pre, pex);
     // suffix: only the row sums (suffix product applied to the all-ones vector) are needed:
     // w_l = M_l M_{l+1} ... M_31 1.  Carry (w, Sm) with Sm the segment product.
     float suf[K];

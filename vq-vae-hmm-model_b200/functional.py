@@ -363,6 +363,27 @@ def hmm_inputs_fused(d: Dims, params, x, u, mu_tab, logvar_tab):
     return log_A, log_b
 
 
+def hmm_loglik_fused(d: Dims, params, log_pi, x, u, lengths, mu_tab, logvar_tab):
+    """loglik (B) straight from raw x, u: transition softmax + emission log-probabilities + forward recursion
+    in ONE kernel (vhmm_hmm_loglik_fused), or None when the dims / T are outside its instantiation."""
+    x = _f32c(x); u = _f32c(u); _require_cuda(x, u, mu_tab, logvar_tab)
+    B, C, T = x.shape
+    if not _lib.lib().vhmm_hmm_inputs_supported(ctypes.byref(d), T) or u.shape != (B, d.U, T):
+        return None
+    log_pi = _f32c(log_pi.to(x.device))
+    if lengths is not None:
+        lengths = lengths.to(device=x.device, dtype=torch.int64).contiguous()
+    out = torch.empty(B, device=x.device, dtype=torch.float32)
+    P, keep = pack_params(params)
+    with torch.cuda.device(x.device):
+        ws = workspace(x.device, _ws_bytes(_lib.OP_HMM_INPUTS, d, B, T))
+        check(_lib.lib().vhmm_hmm_loglik_fused(ctypes.byref(d), ctypes.byref(P), _ptr(log_pi), _ptr(x), _ptr(u),
+                                               _ptr(lengths) if lengths is not None else None, B, T,
+                                               _ptr(_f32c(mu_tab)), _ptr(_f32c(logvar_tab)), _ptr(out), _ptr(ws),
+                                               ws.numel(), _stream(x.device)), "vhmm_hmm_loglik_fused")
+    return out
+
+
 def _hmm_inputs(log_pi, log_A, log_b, lengths):
     log_pi = _f32c(log_pi); log_A = _f32c(log_A); log_b = _f32c(log_b)
     _require_cuda(log_pi, log_A, log_b)

@@ -194,6 +194,14 @@ class VAE_HMM(nn.Module):
         return log_pi, log_A, log_b
 
     def hmm_log_likelihood(self, x, u, lengths=None):
+        """log p(x | u) per sequence (B.2).  One fused kernel from raw (x, u) when the dims allow
+        (nothing materialised), else front end + forward recursion."""
+        if u.dim() == 3 and u.shape[1] == self._dims.U and x.numel() > 0:
+            mu_tab, lv_tab = Fn.emission_table(self._dims, self._params(), x.shape[2], x.device)
+            log_pi = torch.log_softmax(self.prior.log_prior.detach().float(), dim=0)
+            ll = Fn.hmm_loglik_fused(self._dims, self._params(), log_pi, x, u, lengths, mu_tab, lv_tab)
+            if ll is not None:
+                return ll
         log_pi, log_A, log_b = self.hmm_inputs(x, u)
         return Fn.hmm_forward(log_pi, log_A, log_b, lengths)
 
