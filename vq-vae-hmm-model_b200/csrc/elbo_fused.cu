@@ -49,10 +49,14 @@ constexpr int LP = 16;     // doubles of loss partials per CTA
 #define PROF(id) do { if (threadIdx.x == 0) { long long n_ = clock64(); prof_t[id] += n_ - prof_prev; prof_prev = n_; } } while (0)
 #define PROF_DUMP(name, n) do { if (threadIdx.x == 0 && blockIdx.x == 0) { long long tot_ = 0; for (int i_ = 0; i_ < n; ++i_) tot_ += prof_t[i_]; \
   printf("%s phases (%% of %lld cyc):", name, tot_); for (int i_ = 0; i_ < n; ++i_) printf(" %d:%.1f", i_, 100.0 * prof_t[i_] / tot_); printf("\n"); } } while (0)
+#define PROF_PARAMS , long long* prof_t, long long& prof_prev
+#define PROF_ARGS , prof_t, prof_prev
 #else
 #define PROF_DECL
 #define PROF(id)
 #define PROF_DUMP(name, n)
+#define PROF_PARAMS
+#define PROF_ARGS
 #endif
 
 template <int C_, int H_, int H2_, int K_, int U_, int TH_>
@@ -88,6 +92,14 @@ __device__ __forceinline__ void stage_conv_w(float* dst, const float* __restrict
   for (int i = threadIdx.x; i < O * Cin * KW; i += NTH) {
     const int tau = i % KW, c = (i / KW) % Cin, o = i / (KW * Cin);
     dst[(tau * Opad + o) * PW + c] = src[i];
+  }
+}
+// conv weight (O, Cin, 3) -> dst[tau][c][O] (8 input rows per tap, rows [Cin, 8) stay zero): the layout
+// sk_conv_taps_fwd reads with lane <-> o, bank-conflict free
+__device__ __forceinline__ void stage_conv_w_T(float* dst, const float* __restrict__ src, int O, int Cin) {
+  for (int i = threadIdx.x; i < O * Cin * 3; i += NTH) {
+    const int tau = i % 3, c = (i / 3) % Cin, o = i / (3 * Cin);
+    dst[(tau * 8 + c) * O + o] = src[i];
   }
 }
 __device__ __forceinline__ void stage_vec(float* dst, const float* __restrict__ src, int n) {

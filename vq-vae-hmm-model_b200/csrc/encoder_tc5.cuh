@@ -75,29 +75,21 @@ template <typename CF>
 __device__ __forceinline__ void encoder_forward_tc5(const float* W1s, const float* b1s, const float* b2s, const float* W3s,
                                                     const float* b3s, const float* XU, float* H1, float* H2b, float* LQ,
                                                     uint8_t* RA, uint32_t sRA, uint32_t sW2, uint32_t tmem, uint64_t* bar,
-                                                    uint32_t& par, uint32_t* amax_sh, float sW, float& sH, int t0, int T) {
+                                                    uint32_t& par, uint32_t* amax_sh, float sW, float& sH, int t0, int T PROF_PARAMS) {
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   {
-    float lm = 0.f;
-    cols_op<CF::H, 2, 2, 1, 3, false>(W1s, CF::H * 8, 8, XU, [&](int r, int c, float v0, float v1) {
-      const int t = t0 - HL + c;
-      const float bb = b1s[r];
-      float2 o;
-      o.x = (t >= 0 && t < T) ? fmaxf(v0 + bb, 0.f) : 0.f;
-      o.y = (t + 1 >= 0 && t + 1 < T) ? fmaxf(v1 + bb, 0.f) : 0.f;
-      *reinterpret_cast<float2*>(H1 + r * PT + c) = o;
-      lm = fmaxf(lm, fmaxf(o.x, o.y));
-    });
+    float lm = sk_conv_taps_fwd<CF::C, CF::H>(W1s, b1s, XU, H1, t0, T);   // conv1 + ReLU as FFMA (skinny.cuh)
+    PROF(18);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) lm = fmaxf(lm, __shfl_xor_sync(0xffffffffu, lm, o));
     if (lane == 0) atomicMax(amax_sh, __float_as_uint(lm));
   }
-  __syncthreads();
+  __syncthreads(); PROF(14);
   sH = tc5::pow2_scale(__uint_as_float(*amax_sh));
   act_to_parts<CF::H>(H1, sH, RA, t5e::H1_PART);
   tc5::fence_async_smem();
   tc5::fence_before_sync();
-  __syncthreads();
+  __syncthreads(); PROF(15);
   if (w == 0) {   // h2 pre-activation: per accumulator set [0,32) = h1_h*W_h, [32,64) = h1_h*W_m + h1_m*W_h
     tc5::fence_after_sync();
     const bool lead = tc5::elect_one();
@@ -118,7 +110,7 @@ __device__ __forceinline__ void encoder_forward_tc5(const float* W1s, const floa
     if (lead) tc5::commit(bar);
     __syncwarp();
   }
-  tc5::mbar_wait(bar, par); par ^= 1u;
+  tc5::mbar_wait(bar, par); par ^= 1u; PROF(16);
   tc5::fence_after_sync();
   {
     const uint32_t lane_base = (uint32_t)(32 * (w & 3)) << 16;
@@ -138,8 +130,8 @@ __device__ __forceinline__ void encoder_forward_tc5(const float* W1s, const floa
     }
   }
   tc5::fence_before_sync();
-  __syncthreads();
-  cols_op<16, 1, 1, CF::H2 / 8, 1, false>(W3s, 0, CF::PW_H2, H2b, EpiBiasRows{LQ, b3s, CF::K});
+  __syncthreads(); PROF(17);
+  sk_rows_fwd<CF::K, CF::H2>(W3s, CF::PW_H2, b3s, H2b, LQ);   // logits layer as FFMA
   __syncthreads();
 }
 
@@ -191,7 +183,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
   if (threadIdx.x < 32) tc5::tmem_alloc512(&tmem_sh);
   __syncthreads();
   const float sW = stage_w2e_f16<CF>(W2h, P.p[P_E2W], &amax_sh);
-  stage_conv_w(W1s, P.p[P_E1W], H, C, 3, H, 8);
+  stage_conv_w_T(W1s, P.p[P_E1W], H, C);   // [tau][c][H]: lane <-> output row reads are conflict-free
   stage_conv_w(W3s, P.p[P_E3W], K, H2, 1, 16, CF::PW_H2);
   stage_conv_w(Wt0s, P.p[P_T0W], TH, U, 1, TH, 8);
   stage_conv_w(Wt2s, P.p[P_T2W], K2, TH, 1, 16, CF::PW_TH);
@@ -238,7 +230,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
     __syncthreads(); PROF(0);
     float sH;
     (void)sizeof(sH);
-    encoder_forward_tc5<CF>(W1s, b1s, b2s, W3s, b3s, XU, H1, H2b, LQ, RA, sRA, sW2, tmem, &bar_f, par_f, &amax_sh, sW, sH, t0, T); PROF(1);
+    encoder_forward_tc5<CF>(W1s, b1s, b2s, W3s, b3s, XU, H1, H2b, LQ, RA, sRA, sW2, tmem, &bar_f, par_f, &amax_sh, sW, sH, t0, T PROF_ARGS); PROF(1);
     // softmax, entropy, init term, q -> HBM
     if (tid < NC) {
       const int j = tid, t = t0 - HL + j;
@@ -338,7 +330,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
     tile = nxt; ti = tn; buf ^= 1;
     nxt = (tile >= 0) ? tile_resolve<6>(cm, pre, tn) : -1;
   }
-  PROF_DUMP("enc_prior", 13);
+  PROF_DUMP("enc_prior", 19);
   // per-CTA partials
   flush_acc(part, acc, CF::ACC_A);
   double* lp = cm.loss_part + (int64_t)blockIdx.x * LP;
@@ -392,7 +384,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
   if (w == 0) tc5::tmem_alloc512(&tmem_sh);
   __syncthreads();
   const float sW = stage_w2e_f16<CF>(W2h, P.p[P_E2W], &amax_sh);
-  stage_conv_w(W1s, P.p[P_E1W], H, C, 3, H, 8);
+  stage_conv_w_T(W1s, P.p[P_E1W], H, C);   // [tau][c][H]: lane <-> output row reads are conflict-free
   stage_conv_w(W3s, P.p[P_E3W], K, H2, 1, 16, CF::PW_H2);
   stage_vec(b1s, P.p[P_E1B], H); stage_vec(b2s, P.p[P_E2B], H2); stage_vec(b3s, P.p[P_E3B], K);
   const float aE = (float)((double)cm.beta / cm.norms[1]);
@@ -465,7 +457,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
     if (tid == 0) { amax_sh = 0u; amax2_sh = 0u; }
     __syncthreads(); PROF(0);
     float sH;
-    encoder_forward_tc5<CF>(W1s, b1s, b2s, W3s, b3s, XU, H1, H2b, LQ, RA, sRA, sW2, tmem, &bar_f, par_f, &amax_sh, sW, sH, t0, T); PROF(1);
+    encoder_forward_tc5<CF>(W1s, b1s, b2s, W3s, b3s, XU, H1, H2b, LQ, RA, sRA, sW2, tmem, &bar_f, par_f, &amax_sh, sW, sH, t0, T PROF_ARGS); PROF(1);
     if (tid < NC) {    // d loss / d logits: softmax backward of dq plus the entropy term (:134-137)
       const int j = tid, t = t0 - HL + j;
       const bool inr = (j >= 2 && j < NC - 2 && t >= 0 && t < T);
@@ -624,7 +616,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
     tile = nxt; ti = tn; buf ^= 1;
     nxt = (tile >= 0) ? tile_resolve<3>(cm, pre, tn) : -1;
   }
-  PROF_DUMP("enc_bwd_tc5", 9);
+  PROF_DUMP("enc_bwd_tc5", 19);
   flush_all();
   tc5::fence_before_sync();
   __syncthreads();

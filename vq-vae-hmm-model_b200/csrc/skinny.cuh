@@ -257,3 +257,78 @@ __device__ __forceinline__ void sk_wgrad_rows_reduce(const float* __restrict__ s
 // dh2 = relu'(h2) * W3^T dl, as FFMA over all 128 columns were not faster than the mma.sync helper --
 // 35.99 vs 35.57 ms for the decoder kernel -- because there every output column is needed, so the
 // tensor-core tile is not padded in the long dimension.)
+
+// ---- forward "skinny" layers (few input rows, or few output rows) as FP32 FFMA -----------------
+// On the padded mma.sync helper these are one long dependent MMA chain per warp (3xTF32, rows padded to
+// 8/16): 3.2 k cycles per tile for encoder conv1 (5 -> 64, k = 3) and 1.3 k for the 32 -> K logits layer.
+//
+// sk_conv_taps_fwd: out[r][c] = relu(bias[r] + sum_{tau,k} W[(tau*8 + k)*HH + r] * X[k][c + tau - 1]) for
+// columns [1, NC-1) inside the sequence, 0 elsewhere.  Lane <-> output row (its 3 KQ weights live in
+// registers), warp <-> 16-column slice, so every X load is a warp broadcast and the float4 stores of rows
+// r..r+7 tile the banks (PT == 4 mod 32).  Returns this thread's max output (for the fp16 scale).
+template <int KQ, int HH>
+__device__ __forceinline__ float sk_conv_taps_fwd(const float* __restrict__ W, const float* __restrict__ bias,
+                                                  const float* __restrict__ X, float* __restrict__ out, int t0, int T) {
+  constexpr int RW = HH / 32, NSL = NW / RW, CS = NC / NSL;
+  static_assert(HH % 32 == 0 && NW % RW == 0 && NC % NSL == 0 && CS % 4 == 0, "row / slice split");
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r = 32 * (w % RW) + lane, c0 = CS * (w / RW);
+  float wt[3][KQ];
+#pragma unroll
+  for (int tau = 0; tau < 3; ++tau)
+#pragma unroll
+    for (int k = 0; k < KQ; ++k) wt[tau][k] = W[(tau * 8 + k) * HH + r];
+  float acc[CS];
+  const float bb = bias[r];
+#pragma unroll
+  for (int j = 0; j < CS; ++j) acc[j] = bb;
+#pragma unroll
+  for (int k = 0; k < KQ; ++k) {
+    const float* xr = X + k * PT + c0;
+    float xv[CS + 2];
+    xv[0] = xr[-1];                     // column -1 of slice 0 only feeds the (zeroed) edge column
+    xv[CS + 1] = xr[CS];                // column NC of the last slice likewise (row padding)
+#pragma unroll
+    for (int q = 0; q < CS / 4; ++q) {
+      const float4 v = *reinterpret_cast<const float4*>(xr + 4 * q);
+      xv[4 * q + 1] = v.x; xv[4 * q + 2] = v.y; xv[4 * q + 3] = v.z; xv[4 * q + 4] = v.w;
+    }
+#pragma unroll
+    for (int tau = 0; tau < 3; ++tau)
+#pragma unroll
+      for (int j = 0; j < CS; ++j) acc[j] = fmaf(wt[tau][k], xv[j + tau], acc[j]);
+  }
+  float lm = 0.f;
+#pragma unroll
+  for (int q = 0; q < CS / 4; ++q) {
+    float o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int c = c0 + 4 * q + e, t = t0 - HL + c;
+      o[e] = (c >= 1 && c < NC - 1 && t >= 0 && t < T) ? fmaxf(acc[4 * q + e], 0.f) : 0.f;
+      lm = fmaxf(lm, o[e]);
+    }
+    *reinterpret_cast<float4*>(out + r * PT + c0 + 4 * q) = make_float4(o[0], o[1], o[2], o[3]);
+  }
+  return lm;
+}
+
+// sk_rows_fwd: out[k][c] = bias[k] + sum_{o < KK} W[k*PW + o] * In[o][c] for k < NR (NR * NC <= NTH threads,
+// thread = (column, output row); weights are warp broadcasts, In reads run along the lanes).
+template <int NR, int KK>
+__device__ __forceinline__ void sk_rows_fwd(const float* __restrict__ W, int PW, const float* __restrict__ bias,
+                                            const float* __restrict__ In, float* __restrict__ out) {
+  static_assert(NR * NC <= NTH && KK % 4 == 0, "one thread per output");
+  const int c = threadIdx.x % NC, k = threadIdx.x / NC;
+  if (k >= NR) return;
+  float a0 = bias[k], a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+  for (int q = 0; q < KK / 4; ++q) {
+    const float4 wv = *reinterpret_cast<const float4*>(W + k * PW + 4 * q);
+    a0 = fmaf(wv.x, In[(4 * q + 0) * PT + c], a0);
+    a1 = fmaf(wv.y, In[(4 * q + 1) * PT + c], a1);
+    a2 = fmaf(wv.z, In[(4 * q + 2) * PT + c], a2);
+    a3 = fmaf(wv.w, In[(4 * q + 3) * PT + c], a3);
+  }
+  out[k * PT + c] = (a0 + a1) + (a2 + a3);
+}
