@@ -80,7 +80,7 @@ struct Cfg {
   // shared memory (floats)
   static constexpr int R1 = (H + H2 > TH) ? H + H2 : TH;   // h1|h2 region, reused for the prior's hidden layer
   static constexpr int SM_A = 3 * H * 8 + 3 * H2 * PW_H + 16 * PW_H2 + TH * 8 + 16 * PW_TH + (H + H2 + 16 + TH + 16 + 8) +
-                              (16 + R1 + 16 + 16 + 16) * PT + ACC_A + 16 * PT;   // + second input buffer (prefetch)
+                              (16 + R1 + 16 + 16 + 16) * PT + ACC_A + 16 * PT + H2 * PT;   // + second input buffer (prefetch) + h2 (tcgen05 build)
   static constexpr int SM_B = 3 * H * 8 + 3 * H * PW_H + 16 * PW_H + (H + H + 16) + (16 + H + H + 16) * PT + ACC_B;
   static constexpr int SM_C = 3 * H * 8 + 3 * H2 * PW_H + 16 * PW_H2 + (H + H2 + 16) + (16 + H + H2 + 16 + 16) * PT + ACC_C + 32 * PT;   // + second input buffers (prefetch)
 };

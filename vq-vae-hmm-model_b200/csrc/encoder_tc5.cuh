@@ -71,11 +71,11 @@ __device__ __forceinline__ void act_to_parts(const float* __restrict__ A, float 
 // encoder forward with conv2 on the tensor core (kernels A and C).  XU rows [0,8) hold x.
 // h1 (fp32) -> H1 and its fp16 parts -> RA (scale returned in sH); h2 -> H2b; logits -> LQ.
 // *amax_sh must be 0 on entry.  Ends with a __syncthreads().
-template <typename CF>
+template <typename CF, typename Mid>
 __device__ __forceinline__ void encoder_forward_tc5(const float* W1s, const float* b1s, const float* b2s, const float* W3s,
                                                     const float* b3s, const float* XU, float* H1, float* H2b, float* LQ,
                                                     uint8_t* RA, uint32_t sRA, uint32_t sW2, uint32_t tmem, uint64_t* bar,
-                                                    uint32_t& par, uint32_t* amax_sh, float sW, float& sH, int t0, int T PROF_PARAMS) {
+                                                    uint32_t& par, uint32_t* amax_sh, float sW, float& sH, int t0, int T, Mid mid PROF_PARAMS) {
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   {
     float lm = sk_conv_taps_fwd<CF::C, CF::H>(W1s, b1s, XU, H1, t0, T);   // conv1 + ReLU as FFMA (skinny.cuh)
@@ -110,6 +110,7 @@ __device__ __forceinline__ void encoder_forward_tc5(const float* W1s, const floa
     if (lead) tc5::commit(bar);
     __syncwarp();
   }
+  mid();   // work that does not depend on h2 runs under the tensor-core latency (may use __syncthreads)
   tc5::mbar_wait(bar, par); par ^= 1u; PROF(16);
   tc5::fence_after_sync();
   {
@@ -171,13 +172,13 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
   float* XU0 = lps + 8;                   // rows 0..7 x, rows 8..15 u (buffer 0; buffer 1 at the end)
   float* R1 = XU0 + 16 * PT;               // h1 | h2, later the prior's hidden layer a
   float* H1 = R1;
-  float* H2b = R1 + H * PT;
   float* Ab = R1;
   float* LQ = R1 + CF::R1 * PT;           // rows 0..K-1 logits -> q, rows 8.. log q
   float* Mb = LQ + 16 * PT;               // transition logits -> log_A, row i*K+j
   float* dMb = Mb + 16 * PT;
   float* acc = dMb + 16 * PT;             // ACC_A
   float* XU1 = acc + CF::ACC_A;
+  float* H2b = XU1 + 16 * PT;             // h2 has its own rows: R1 holds the prior's hidden layer a by the time it is written
   for (int i = threadIdx.x; i < (int)(t5e::Sz<CF>::A / 4); i += NTH) reinterpret_cast<uint32_t*>(smraw)[i] = 0u;
   if (threadIdx.x == 0) { tc5::mbar_init(&bar_f, 1); tc5::mbar_init_fence(); amax_sh = 0u; }
   if (threadIdx.x < 32) tc5::tmem_alloc512(&tmem_sh);
@@ -230,7 +231,31 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
     __syncthreads(); PROF(0);
     float sH;
     (void)sizeof(sH);
-    encoder_forward_tc5<CF>(W1s, b1s, b2s, W3s, b3s, XU, H1, H2b, LQ, RA, sRA, sW2, tmem, &bar_f, par_f, &amax_sh, sW, sH, t0, T PROF_ARGS); PROF(1);
+    // The transition MLP depends on u only: it runs between the issue of the conv2 MMAs and the wait for them
+    // (h1 is dead once its fp16 parts are staged, so its rows become the hidden layer a; h2 has rows of its own).
+    auto prior_fwd = [&]() {
+      PROF(13);
+      cols_op<TH, 2, 2, 1, 1, false>(Wt0s, 0, 8, XU + 8 * PT, EpiReluZero{Ab, bt0s, t0, T});   // a = relu(W0 u + b0) (:68)
+      __syncthreads();
+      PROF(3);
+      cols_op<16, 1, 1, TH / 8, 1, false>(Wt2s, 0, CF::PW_TH, Ab, EpiBiasRows{Mb, bt2s, K2});
+      __syncthreads(); PROF(4);
+      if (tid < NC) {    // row log-softmax -> log_A (:69)
+        const int j = tid;
+#pragma unroll
+        for (int i = 0; i < K; ++i) {
+          float v[K], m = -INFINITY, s = 0.f;
+#pragma unroll
+          for (int jj = 0; jj < K; ++jj) { v[jj] = Mb[(i * K + jj) * PT + j]; m = fmaxf(m, v[jj]); }
+#pragma unroll
+          for (int jj = 0; jj < K; ++jj) s += expf(v[jj] - m);
+          const float lse = m + logf(s);
+#pragma unroll
+          for (int jj = 0; jj < K; ++jj) Mb[(i * K + jj) * PT + j] = v[jj] - lse;
+        }
+      }
+    };
+    encoder_forward_tc5<CF>(W1s, b1s, b2s, W3s, b3s, XU, H1, H2b, LQ, RA, sRA, sW2, tmem, &bar_f, par_f, &amax_sh, sW, sH, t0, T, prior_fwd PROF_ARGS); PROF(1);
     // softmax, entropy, init term, q -> HBM
     if (tid < NC) {
       const int j = tid, t = t0 - HL + j;
@@ -257,28 +282,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
       }
       if (own && t < L) { s_ent += (double)ent; s_valid += 1.0; }                     // :134-135
     }
-    __syncthreads(); PROF(2);   // h1/h2 are dead from here: R1 becomes the prior's hidden layer
-    // a = relu(W0 u + b0) on every column (VQ_VAE_HMM_fixed.py:68)
-    cols_op<TH, 2, 2, 1, 1, false>(Wt0s, 0, 8, XU + 8 * PT, EpiReluZero{Ab, bt0s, t0, T});
-    __syncthreads();
-    PROF(3);
-    cols_op<16, 1, 1, TH / 8, 1, false>(Wt2s, 0, CF::PW_TH, Ab, EpiBiasRows{Mb, bt2s, K2});
-    __syncthreads(); PROF(4);
-    if (tid < NC) {    // row log-softmax -> log_A (:69)
-      const int j = tid;
-#pragma unroll
-      for (int i = 0; i < K; ++i) {
-        float v[K], m = -INFINITY, s = 0.f;
-#pragma unroll
-        for (int jj = 0; jj < K; ++jj) { v[jj] = Mb[(i * K + jj) * PT + j]; m = fmaxf(m, v[jj]); }
-#pragma unroll
-        for (int jj = 0; jj < K; ++jj) s += expf(v[jj] - m);
-        const float lse = m + logf(s);
-#pragma unroll
-        for (int jj = 0; jj < K; ++jj) Mb[(i * K + jj) * PT + j] = v[jj] - lse;
-      }
-    }
-    __syncthreads();
+    __syncthreads(); PROF(2);
     if (tid < NC) {    // pair term (:125-131), d/dM, d/dq of the prior
       const int j = tid, t = t0 - HL + j;
       const bool own = (j >= J0 && j < J0 + TT && t < T);
@@ -457,7 +461,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
     if (tid == 0) { amax_sh = 0u; amax2_sh = 0u; }
     __syncthreads(); PROF(0);
     float sH;
-    encoder_forward_tc5<CF>(W1s, b1s, b2s, W3s, b3s, XU, H1, H2b, LQ, RA, sRA, sW2, tmem, &bar_f, par_f, &amax_sh, sW, sH, t0, T PROF_ARGS); PROF(1);
+    encoder_forward_tc5<CF>(W1s, b1s, b2s, W3s, b3s, XU, H1, H2b, LQ, RA, sRA, sW2, tmem, &bar_f, par_f, &amax_sh, sW, sH, t0, T, [] {} PROF_ARGS); PROF(1);
     if (tid < NC) {    // d loss / d logits: softmax backward of dq plus the entropy term (:134-137)
       const int j = tid, t = t0 - HL + j;
       const bool inr = (j >= 2 && j < NC - 2 && t >= 0 && t < T);
