@@ -65,7 +65,8 @@ struct Lay {
   static constexpr int NACC = CF::ACC_B - CF::B_WF;
   static constexpr int QX1 = ACC + NACC;                        // second input buffer (prefetch of the next tile)
   static constexpr int SCR = QX1 + 16 * PT;                     // slice partials of the folded conv1 weight gradient (skinny.cuh)
-  static constexpr int FLOATS = SCR + SkTaps<CF::K, CF::H>::FLOATS;
+  static constexpr int WFT = SCR + SkTaps<CF::K, CF::H>::FLOATS;  // [3][K][H] folded conv1, transposed for the FFMA forward
+  static constexpr int FLOATS = WFT + 3 * CF::K * CF::H;
   static constexpr size_t BYTES = (size_t)OP_BYTES + (size_t)FLOATS * 4;
 };
 }  // namespace t5
@@ -100,6 +101,7 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
   float* accBD1 = acc + (CF::B_BD1 - CF::B_WF);
   float* accBP = acc + (CF::B_BP - CF::B_WF);
   float* scrW = fl + L::SCR;
+  float* WFT = fl + L::WFT;
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
 
   for (int i = tid; i < (int)(L::BYTES / 4); i += NTH) reinterpret_cast<uint32_t*>(smraw)[i] = 0u;
@@ -111,6 +113,10 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
   if (w == 0) tc5::tmem_alloc512(&tmem_sh);
   __syncthreads();
   stage_vec(WFs, cm.wfold, 3 * H * 8);
+  for (int i = tid; i < 3 * K * H; i += NTH) {   // WFT[tau][k][o] = wfold[tau][o][k]
+    const int o = i % H, k = (i / H) % K, tau = i / (H * K);
+    WFT[i] = cm.wfold[(tau * H + o) * 8 + k];
+  }
   stage_conv_w(WPs, P.p[P_DPW], 2 * C, H, 1, 16, CF::PW_H);
   stage_vec(bd1s, P.p[P_D1B], H); stage_vec(bd2s, P.p[P_D2B], H); stage_vec(bps, P.p[P_DPB], 2 * C);
   // weight scale: max |W2| -> power of two
@@ -222,7 +228,7 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     if (tid == 0) amax_sh = 0u;
     __syncthreads(); PROF(0);
     // ---- g1 = relu(conv3'(q) + b1) -> S (fp32), then its fp16 parts -> RA   (:83-85)
-    cols_op<H, 2, 2, 1, 3, false>(WFs, H * 8, 8, QX, EpiReluZero{S, bd1s, t0, T});
+    (void)sk_conv_taps_fwd<K, H, K>(WFT, bd1s, QX, S, t0, T);   // FFMA (skinny.cuh); edge columns 0, NC-1 are zero
     __syncthreads();
     for (int i = tid; i < t5::NPL * NC; i += NTH) {
       const int pl = i / NC, j = i - pl * NC;

@@ -262,11 +262,11 @@ __device__ __forceinline__ void sk_wgrad_rows_reduce(const float* __restrict__ s
 // On the padded mma.sync helper these are one long dependent MMA chain per warp (3xTF32, rows padded to
 // 8/16): 3.2 k cycles per tile for encoder conv1 (5 -> 64, k = 3) and 1.3 k for the 32 -> K logits layer.
 //
-// sk_conv_taps_fwd: out[r][c] = relu(bias[r] + sum_{tau,k} W[(tau*8 + k)*HH + r] * X[k][c + tau - 1]) for
+// sk_conv_taps_fwd: out[r][c] = relu(bias[r] + sum_{tau,k} W[(tau*KR + k)*HH + r] * X[k][c + tau - 1]) for
 // columns [1, NC-1) inside the sequence, 0 elsewhere.  Lane <-> output row (its 3 KQ weights live in
 // registers), warp <-> 16-column slice, so every X load is a warp broadcast and the float4 stores of rows
 // r..r+7 tile the banks (PT == 4 mod 32).  Returns this thread's max output (for the fp16 scale).
-template <int KQ, int HH>
+template <int KQ, int HH, int KR = 8>
 __device__ __forceinline__ float sk_conv_taps_fwd(const float* __restrict__ W, const float* __restrict__ bias,
                                                   const float* __restrict__ X, float* __restrict__ out, int t0, int T) {
   constexpr int RW = HH / 32, NSL = NW / RW, CS = NC / NSL;
@@ -277,7 +277,7 @@ __device__ __forceinline__ float sk_conv_taps_fwd(const float* __restrict__ W, c
 #pragma unroll
   for (int tau = 0; tau < 3; ++tau)
 #pragma unroll
-    for (int k = 0; k < KQ; ++k) wt[tau][k] = W[(tau * 8 + k) * HH + r];
+    for (int k = 0; k < KQ; ++k) wt[tau][k] = W[(tau * KR + k) * HH + r];
   float acc[CS];
   const float bb = bias[r];
 #pragma unroll
@@ -298,14 +298,17 @@ __device__ __forceinline__ float sk_conv_taps_fwd(const float* __restrict__ W, c
 #pragma unroll
       for (int j = 0; j < CS; ++j) acc[j] = fmaf(wt[tau][k], xv[j + tau], acc[j]);
   }
+  // live columns: [max(1, HL - t0), min(NC - 1, T - t0 + HL)) -- one unsigned compare per element
+  const int lo = max(1, HL - t0), hi = min(NC - 1, T - t0 + HL);
+  const unsigned span = (unsigned)max(hi - lo, 0);
+  const int d0 = c0 - lo;
   float lm = 0.f;
 #pragma unroll
   for (int q = 0; q < CS / 4; ++q) {
     float o[4];
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
-      const int c = c0 + 4 * q + e, t = t0 - HL + c;
-      o[e] = (c >= 1 && c < NC - 1 && t >= 0 && t < T) ? fmaxf(acc[4 * q + e], 0.f) : 0.f;
+      o[e] = ((unsigned)(d0 + 4 * q + e) < span) ? fmaxf(acc[4 * q + e], 0.f) : 0.f;
       lm = fmaxf(lm, o[e]);
     }
     *reinterpret_cast<float4*>(out + r * PT + c0 + 4 * q) = make_float4(o[0], o[1], o[2], o[3]);
