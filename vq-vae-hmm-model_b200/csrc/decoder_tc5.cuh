@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     tc5::fence_before_sync();
     __syncthreads(); PROF(2);
     // ---- p = Wp g2 + bp, Gaussian NLL and its gradient (:87-90, :118-120)
-    cols_op<16, 1, 1, H / 8, 1, false>(WPs, 0, CF::PW_H, S, EpiBiasRows{Pb, bps, 2 * C});
+    cols_op<16, 1, 1, H / 8, 1, false>(WPs, 0, CF::PW_H, S, EpiBiasRows{Pb, bps, 2 * C});   // (an FFMA form split over 4 thread groups measured 12 % slower)
     __syncthreads(); PROF(3);
     {   // all 512 threads: thread (column j, channel group): channels c = tid/NC, tid/NC + 4, ...
       const int j = tid & (NC - 1), t = t0 - HL + j;
@@ -309,7 +309,7 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     row_sums<J0, TT / 4, PT, NW>(Pb, 2 * C, accBP);
     __syncthreads(); PROF(5);
     sk_wgrad_rows_reduce<2 * C, H>(scrW, accWP, CF::PW_H);
-    cols_op<H, 2, 2, 2, 1, true>(WPs, 0, CF::PW_H, Pb, EpiReluMask{S});
+    cols_op<H, 2, 2, 2, 1, true>(WPs, 0, CF::PW_H, Pb, EpiReluMask{S});   // (the FFMA form, sk_rowsT_mask, is slower here)
     __syncthreads(); PROF(6);
     {   // conv2 bias gradient and the tile maximum of |dg2| (scale of its fp16 parts)
       row_sums<J0, TT / 4, PT, NW>(S, H, accBD2);

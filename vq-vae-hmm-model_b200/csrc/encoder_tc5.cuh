@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
     // (h1 is dead once its fp16 parts are staged, so its rows become the hidden layer a; h2 has rows of its own).
     auto prior_fwd = [&]() {
       PROF(13);
-      cols_op<TH, 2, 2, 1, 1, false>(Wt0s, 0, 8, XU + 8 * PT, EpiReluZero{Ab, bt0s, t0, T});   // a = relu(W0 u + b0) (:68)
+      sk_rows_in_fwd<U, TH>(Wt0s, bt0s, XU + 8 * PT, Ab, t0, T);   // a = relu(W0 u + b0) (:68) as FFMA
       __syncthreads();
       PROF(3);
       cols_op<16, 1, 1, TH / 8, 1, false>(Wt2s, 0, CF::PW_TH, Ab, EpiBiasRows{Mb, bt2s, K2});
@@ -495,7 +495,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
     __syncthreads(); PROF(3);
     sk_wgrad_rows_reduce<K, H2>(acc + CF::C_W2, acc + CF::C_W3, CF::PW_H2);
     // dh2 = relu'(h2) * W3^T dl, in place
-    cols_op<H2, 1, 2, 1, 1, true>(W3s, 0, CF::PW_H2, LQ, EpiReluMask{H2b});
+    sk_rowsT_mask<K, H2>(W3s, CF::PW_H2, LQ, H2b);   // dh2 = relu'(h2) * W3^T dlogits as FFMA
     __syncthreads(); PROF(4);
     {   // conv2 bias gradient and the tile maximum of |dh2| (scale of its fp16 parts)
       row_sums<J0, TT / 4, PT, NW>(H2b, H2, acc + CF::C_B2);

@@ -335,3 +335,78 @@ __device__ __forceinline__ void sk_rows_fwd(const float* __restrict__ W, int PW,
   }
   out[k * PT + c] = (a0 + a1) + (a2 + a3);
 }
+
+// sk_rowsT_mask: input gradient of a layer with few output rows, fused with the ReLU mask of the activation
+// it flows into:  buf[o][c] = buf[o][c] > 0 ? sum_{p < NP} W[p*PW + o] * D[p][c] : 0   (o < HH, every column).
+// Lane <-> o (its NP weights in registers, read along the lanes), warp <-> column slice, D loads are broadcasts.
+template <int NP, int HH>
+__device__ __forceinline__ void sk_rowsT_mask(const float* __restrict__ W, int PW, const float* __restrict__ D,
+                                              float* __restrict__ buf) {
+  constexpr int RW = HH / 32, NSL = NW / RW, CS = NC / NSL;
+  static_assert(HH % 32 == 0 && NW % RW == 0 && NC % NSL == 0 && CS % 4 == 0, "row / slice split");
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int o = 32 * (w % RW) + lane, c0 = CS * (w / RW);
+  float wt[NP];
+#pragma unroll
+  for (int p = 0; p < NP; ++p) wt[p] = W[p * PW + o];
+  float acc[CS];
+#pragma unroll
+  for (int j = 0; j < CS; ++j) acc[j] = 0.f;
+#pragma unroll
+  for (int p = 0; p < NP; ++p)
+#pragma unroll
+    for (int q = 0; q < CS / 4; ++q) {
+      const float4 d = *reinterpret_cast<const float4*>(D + p * PT + c0 + 4 * q);
+      acc[4 * q + 0] = fmaf(wt[p], d.x, acc[4 * q + 0]);
+      acc[4 * q + 1] = fmaf(wt[p], d.y, acc[4 * q + 1]);
+      acc[4 * q + 2] = fmaf(wt[p], d.z, acc[4 * q + 2]);
+      acc[4 * q + 3] = fmaf(wt[p], d.w, acc[4 * q + 3]);
+    }
+#pragma unroll
+  for (int q = 0; q < CS / 4; ++q) {
+    float4* pb = reinterpret_cast<float4*>(buf + o * PT + c0 + 4 * q);
+    const float4 a = *pb;
+    *pb = make_float4(a.x > 0.f ? acc[4 * q] : 0.f, a.y > 0.f ? acc[4 * q + 1] : 0.f, a.z > 0.f ? acc[4 * q + 2] : 0.f,
+                      a.w > 0.f ? acc[4 * q + 3] : 0.f);
+  }
+}
+
+// sk_rows_in_fwd: a layer with few INPUT rows and no taps:  out[h][c] = relu(bias[h] + sum_{k < KQ} W[h*8 + k] * X[k][c])
+// inside the sequence, 0 outside (every column).  Lane <-> h, warp <-> column slice, processed 16 columns at a time.
+template <int KQ, int HH>
+__device__ __forceinline__ void sk_rows_in_fwd(const float* __restrict__ W, const float* __restrict__ bias,
+                                               const float* __restrict__ X, float* __restrict__ out, int t0, int T) {
+  constexpr int RW = HH / 32, NSL = NW / RW, CS = NC / NSL;
+  static_assert(HH % 32 == 0 && NW % RW == 0 && NC % NSL == 0 && CS % 16 == 0 && KQ <= 4, "row / slice split");
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int h = 32 * (w % RW) + lane, c0 = CS * (w / RW);
+  const float4 w4 = *reinterpret_cast<const float4*>(W + h * 8);
+  const float wt[4] = {w4.x, w4.y, w4.z, w4.w};
+  const float bb = bias[h];
+  const int lo = max(0, HL - t0), hi = min(NC, T - t0 + HL);
+  const unsigned span = (unsigned)max(hi - lo, 0);
+#pragma unroll
+  for (int cb = 0; cb < CS; cb += 16) {
+    float acc[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) acc[j] = bb;
+#pragma unroll
+    for (int k = 0; k < KQ; ++k)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float4 v = *reinterpret_cast<const float4*>(X + k * PT + c0 + cb + 4 * q);
+        acc[4 * q + 0] = fmaf(wt[k], v.x, acc[4 * q + 0]);
+        acc[4 * q + 1] = fmaf(wt[k], v.y, acc[4 * q + 1]);
+        acc[4 * q + 2] = fmaf(wt[k], v.z, acc[4 * q + 2]);
+        acc[4 * q + 3] = fmaf(wt[k], v.w, acc[4 * q + 3]);
+      }
+    const int d0 = c0 + cb - lo;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float o[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) o[e] = ((unsigned)(d0 + 4 * q + e) < span) ? fmaxf(acc[4 * q + e], 0.f) : 0.f;
+      *reinterpret_cast<float4*>(out + h * PT + c0 + cb + 4 * q) = make_float4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
