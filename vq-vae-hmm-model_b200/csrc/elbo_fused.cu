@@ -120,6 +120,7 @@ struct Common {
   const float* wfold;      // (3,H,8) folded decoder.conv1 weights, staged layout
   float* q;                // (B,K,T)  written by A
   float* dq_prior;         // (B,K,T)  written by A
+  float* lg;               // (B,K,T)  encoder logits, written by A (tcgen05 build) so that C need not recompute them
   float* dq_dec;           // (B,K,T)  written by B
   double* loss_part;       // [grid][LP]: 0 nll (B); 1 init+trans, 2 entropy, 3 valid steps, 4.. sum_b q[b,k,0] (A)
   double* acc_part;        // [grid][ACC_ALL], zeroed by the host; each CTA adds its smem accumulators every FLUSH tiles
@@ -856,7 +857,7 @@ template <typename CF>
 struct Launcher {
   static size_t workspace_bytes(int64_t B, int64_t T, int ncta) {
     size_t s = 0;
-    s += 3 * align_up((size_t)B * CF::K * T * 4, 256);             // q, dq_prior, dq_dec
+    s += 4 * align_up((size_t)B * CF::K * T * 4, 256);             // q, dq_prior, dq_dec, logits
     s += align_up((size_t)ncta * CF::ACC_ALL * 8, 256);            // per-CTA gradient partials (double)
     s += align_up((size_t)CF::ACC_ALL * 4, 256);                   // reduced
     s += align_up((size_t)ncta * LP * 8, 256);                     // loss partials
@@ -872,6 +873,7 @@ struct Launcher {
     cm.q = A.take<float>((size_t)B * CF::K * T);
     cm.dq_prior = A.take<float>((size_t)B * CF::K * T);
     cm.dq_dec = A.take<float>((size_t)B * CF::K * T);
+    cm.lg = A.take<float>((size_t)B * CF::K * T);
     cm.acc_part = A.take<double>((size_t)ncta * CF::ACC_ALL);
     float* red = A.take<float>(CF::ACC_ALL);
     cm.loss_part = A.take<double>((size_t)ncta * LP);

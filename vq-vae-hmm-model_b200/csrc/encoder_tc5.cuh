@@ -71,7 +71,7 @@ __device__ __forceinline__ void act_to_parts(const float* __restrict__ A, float 
 // encoder forward with conv2 on the tensor core (kernels A and C).  XU rows [0,8) hold x.
 // h1 (fp32) -> H1 and its fp16 parts -> RA (scale returned in sH); h2 -> H2b; logits -> LQ.
 // *amax_sh must be 0 on entry.  Ends with a __syncthreads().
-template <typename CF, typename Mid>
+template <typename CF, bool LOGITS, typename Mid>
 __device__ __forceinline__ void encoder_forward_tc5(const float* W1s, const float* b1s, const float* b2s, const float* W3s,
                                                     const float* b3s, const float* XU, float* H1, float* H2b, float* LQ,
                                                     uint8_t* RA, uint32_t sRA, uint32_t sW2, uint32_t tmem, uint64_t* bar,
@@ -132,8 +132,10 @@ __device__ __forceinline__ void encoder_forward_tc5(const float* W1s, const floa
   }
   tc5::fence_before_sync();
   __syncthreads(); PROF(17);
-  sk_rows_fwd<CF::K, CF::H2>(W3s, CF::PW_H2, b3s, H2b, LQ);   // logits layer as FFMA
-  __syncthreads();
+  if (LOGITS) {
+    sk_rows_fwd<CF::K, CF::H2>(W3s, CF::PW_H2, b3s, H2b, LQ);   // logits layer as FFMA
+    __syncthreads();
+  }
 }
 
 namespace t5e {
@@ -255,7 +257,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
         }
       }
     };
-    encoder_forward_tc5<CF>(W1s, b1s, b2s, W3s, b3s, XU, H1, H2b, LQ, RA, sRA, sW2, tmem, &bar_f, par_f, &amax_sh, sW, sH, t0, T, prior_fwd PROF_ARGS); PROF(1);
+    encoder_forward_tc5<CF, true>(W1s, b1s, b2s, W3s, b3s, XU, H1, H2b, LQ, RA, sRA, sW2, tmem, &bar_f, par_f, &amax_sh, sW, sH, t0, T, prior_fwd PROF_ARGS); PROF(1);
     // softmax, entropy, init term, q -> HBM
     if (tid < NC) {
       const int j = tid, t = t0 - HL + j;
@@ -277,6 +279,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
         ent -= qv * lq;
         if (own) {
           cm.q[(b * K + k) * (int64_t)T + t] = qv;
+          cm.lg[(b * K + k) * (int64_t)T + t] = lg[k];   // kernel C reads the logits instead of recomputing conv3
           if (t == 0) { s_q0[k] += (double)qv; s_trans += (double)(qv * lps[k]); }   // :123 (not masked)
         }
       }
@@ -357,6 +360,7 @@ template <typename CF>
 __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_params P) {
   constexpr int C = CF::C, H = CF::H, H2 = CF::H2, K = CF::K;
   static_assert(H == 64 && H2 == 32, "the tcgen05 encoder tiling is written for hidden_dim = 64, hidden_dim2 = 32");
+  static_assert(K <= 4, "the stored logits ride in rows 4..7 of the dq_dec input group");
   extern __shared__ __align__(1024) uint8_t smraw[];
   __shared__ __align__(8) uint64_t bar_f, bar_d, bar_w, bar_w2;
   __shared__ uint32_t tmem_sh, amax_sh, amax2_sh;
@@ -445,6 +449,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
     prefetch_rows(xu, cm.x, C, t_.b, cm.T, t_.t0, cm.T);
     prefetch_rows(dq, cm.dq_dec, K, t_.b, cm.T, t_.t0, dmax);
     prefetch_rows(dq + 8 * PT, cm.dq_prior, K, t_.b, cm.T, t_.t0, dmax);
+    prefetch_rows(dq + 4 * PT, cm.lg, K, t_.b, cm.T, t_.t0, dmax);   // rows 4.. of the dq_dec group are free (K <= 4)
   };
   int64_t tile = next_tile<3>(cm, blockIdx.x, ti);
   if (tile >= 0) fetch(ti, XU0, DQ0);
@@ -461,32 +466,36 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
     if (tid == 0) { amax_sh = 0u; amax2_sh = 0u; }
     __syncthreads(); PROF(0);
     float sH;
-    encoder_forward_tc5<CF>(W1s, b1s, b2s, W3s, b3s, XU, H1, H2b, LQ, RA, sRA, sW2, tmem, &bar_f, par_f, &amax_sh, sW, sH, t0, T, [] {} PROF_ARGS); PROF(1);
-    if (tid < NC) {    // d loss / d logits: softmax backward of dq plus the entropy term (:134-137)
-      const int j = tid, t = t0 - HL + j;
-      const bool inr = (j >= 2 && j < NC - 2 && t >= 0 && t < T);
-      const bool mk = inr && t < L;
-      float lg[K], m = -INFINITY, s = 0.f;
+    // d loss / d logits needs only the logits kernel A stored and the two dq streams: it runs while the tensor
+    // core works on conv2 (the logits layer itself is not recomputed here)
+    auto dlogits = [&]() {
+      if (tid < NC) {    // softmax backward of dq plus the entropy term (:134-137)
+        const int j = tid, t = t0 - HL + j;
+        const bool inr = (j >= 2 && j < NC - 2 && t >= 0 && t < T);
+        const bool mk = inr && t < L;
+        float lg[K], m = -INFINITY, s = 0.f;
 #pragma unroll
-      for (int k = 0; k < K; ++k) { lg[k] = LQ[k * PT + j]; m = fmaxf(m, lg[k]); }
+        for (int k = 0; k < K; ++k) { lg[k] = DQ[(4 + k) * PT + j]; m = fmaxf(m, lg[k]); }
 #pragma unroll
-      for (int k = 0; k < K; ++k) s += expf(lg[k] - m);
-      const float ls = logf(s), inv = 1.f / s;
-      float qv[K], lq[K], dq[K], sd = 0.f, Hh = 0.f;
+        for (int k = 0; k < K; ++k) s += expf(lg[k] - m);
+        const float ls = logf(s), inv = 1.f / s;
+        float qv[K], lq[K], dq[K], sd = 0.f, Hh = 0.f;
 #pragma unroll
-      for (int k = 0; k < K; ++k) {
-        const float z = lg[k] - m;
-        qv[k] = expf(z) * inv; lq[k] = z - ls; dq[k] = DQ[k * PT + j] + DQ[(8 + k) * PT + j];
-        sd += qv[k] * dq[k];
-        Hh -= qv[k] * lq[k];
+        for (int k = 0; k < K; ++k) {
+          const float z = lg[k] - m;
+          qv[k] = expf(z) * inv; lq[k] = z - ls; dq[k] = DQ[k * PT + j] + DQ[(8 + k) * PT + j];
+          sd += qv[k] * dq[k];
+          Hh -= qv[k] * lq[k];
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          float gk = qv[k] * (dq[k] - sd);
+          if (mk) gk += aE * qv[k] * (lq[k] + Hh);
+          LQ[k * PT + j] = inr ? gk : 0.f;
+        }
       }
-#pragma unroll
-      for (int k = 0; k < K; ++k) {
-        float gk = qv[k] * (dq[k] - sd);
-        if (mk) gk += aE * qv[k] * (lq[k] + Hh);
-        LQ[k * PT + j] = inr ? gk : 0.f;
-      }
-    }
+    };
+    encoder_forward_tc5<CF, false>(W1s, b1s, b2s, W3s, b3s, XU, H1, H2b, LQ, RA, sRA, sW2, tmem, &bar_f, par_f, &amax_sh, sW, sH, t0, T, dlogits PROF_ARGS); PROF(1);
     __syncthreads(); PROF(2);
     // to_logits gradients: dW3[k][c] += sum_t dl[k][t] h2[c][t] as FFMA (skinny.cuh; slice partials in the unused C_W2 block)
     static_assert(SkRows<K, H2>::FLOATS <= 3 * H2 * CF::PW_H, "to_logits gradient scratch must fit the unused C_W2 block");
