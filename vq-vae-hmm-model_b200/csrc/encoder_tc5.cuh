@@ -469,8 +469,8 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
     // d loss / d logits needs only the logits kernel A stored and the two dq streams: it runs while the tensor
     // core works on conv2 (the logits layer itself is not recomputed here)
     auto dlogits = [&]() {
-      if (tid < NC) {    // softmax backward of dq plus the entropy term (:134-137)
-        const int j = tid, t = t0 - HL + j;
+      if (tid >= NTH - NC) {    // softmax backward of dq plus the entropy term (:134-137); the last 4 warps: warp 0 is issuing MMAs
+        const int j = tid - (NTH - NC), t = t0 - HL + j;
         const bool inr = (j >= 2 && j < NC - 2 && t >= 0 && t < T);
         const bool mk = inr && t < L;
         float lg[K], m = -INFINITY, s = 0.f;
