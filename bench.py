@@ -243,7 +243,7 @@ def main():
         dec_tfl = per_gpu_steps * DEC_FLOP_PER_STEP / (kms[1] * 1e-3) / 1e12
         dec = Fn.elbo_decoder_active()
         traffic = None   # dram bytes per launch of the active decoder kernel from its committed ncu --set full capture
-        tp = os.path.join(ROOT, "profiles", "r1c_decoder_traffic.json" if dec == "tc5" else "r1_fused_decoder_traffic.json")
+        tp = os.path.join(ROOT, "profiles", "r1d_decoder_traffic.json" if dec == "tc5" else "r1_fused_decoder_traffic.json")
         if os.path.exists(tp):
             tj = json.load(open(tp))
             if tj.get("B") == B and tj.get("T") == T:
