@@ -309,21 +309,15 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     row_sums<J0, TT / 4, PT, NW>(Pb, 2 * C, accBP);
     __syncthreads(); PROF(5);
     sk_wgrad_rows_reduce<2 * C, H>(scrW, accWP, CF::PW_H);
-    cols_op<H, 2, 2, 2, 1, true>(WPs, 0, CF::PW_H, Pb, EpiReluMask{S});   // (the FFMA form, sk_rowsT_mask, is slower here)
-    __syncthreads(); PROF(6);
-    {   // conv2 bias gradient and the tile maximum of |dg2| (scale of its fp16 parts)
-      row_sums<J0, TT / 4, PT, NW>(S, H, accBD2);
+    {   // dg2 in place over S (mma.sync: the FFMA form, sk_rowsT_mask, is slower here) + the tile maximum of |dg2|
       float m = 0.f;
-      for (int i = tid; i < H * (NC / 4); i += NTH) {
-        const int r = i / (NC / 4), q4 = i - r * (NC / 4);
-        const float4 v = *reinterpret_cast<const float4*>(S + r * PT + 4 * q4);
-        m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
-      }
+      cols_op<H, 2, 2, 2, 1, true>(WPs, 0, CF::PW_H, Pb, EpiReluMaskMax{S, &m});
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
       if (lane == 0) atomicMax(&amax_sh, __float_as_uint(m));
     }
-    __syncthreads();
+    __syncthreads(); PROF(6);
+    row_sums<J0, TT / 4, PT, NW>(S, H, accBD2);   // conv2 bias gradient
     const float sB = tc5::pow2_scale(__uint_as_float(amax_sh));
     for (int i = tid; i < t5::NPL * NC; i += NTH) {   // dg2 parts -> RB (+ the tail chunk with columns >= J0+TT zeroed)
       const int pl = i / NC, j = i - pl * NC;

@@ -285,6 +285,18 @@ struct EpiReluMask {
   }
 };
 
+// EpiReluMask that also tracks the thread's max |value written| (scale of the fp16 parts that follow)
+struct EpiReluMaskMax {
+  float* buf; float* lm;
+  __device__ __forceinline__ void operator()(int r, int c, float v0, float v1) const {
+    float2* p = reinterpret_cast<float2*>(buf + r * PT + c);
+    const float2 a = *p;
+    const float2 o = make_float2(a.x > 0.f ? v0 : 0.f, a.y > 0.f ? v1 : 0.f);
+    *p = o;
+    *lm = fmaxf(*lm, fmaxf(fabsf(o.x), fabsf(o.y)));
+  }
+};
+
 // out rows [0,M) x the 128 columns of the tile, split into (16*MT) x (8*NT) warp work units
 template <int M, int MT, int NT, int KSTEPS, int TAPS, bool TRANS, typename Epi>
 __device__ __forceinline__ void cols_op(const float* W, int tapStride, int PW, const float* In, Epi epi) {

@@ -504,21 +504,14 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
     __syncthreads(); PROF(3);
     sk_wgrad_rows_reduce<K, H2>(acc + CF::C_W2, acc + CF::C_W3, CF::PW_H2);
     // dh2 = relu'(h2) * W3^T dl, in place
-    sk_rowsT_mask<K, H2>(W3s, CF::PW_H2, LQ, H2b);   // dh2 = relu'(h2) * W3^T dlogits as FFMA
-    __syncthreads(); PROF(4);
-    {   // conv2 bias gradient and the tile maximum of |dh2| (scale of its fp16 parts)
-      row_sums<J0, TT / 4, PT, NW>(H2b, H2, acc + CF::C_B2);
-      float m = 0.f;
-      for (int i = tid; i < H2 * (NC / 4); i += NTH) {
-        const int r = i / (NC / 4), q4 = i - r * (NC / 4);
-        const float4 v = *reinterpret_cast<const float4*>(H2b + r * PT + 4 * q4);
-        m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
-      }
+    {   // dh2 = relu'(h2) * W3^T dlogits as FFMA, with the tile maximum of |dh2| (scale of its fp16 parts)
+      float m = sk_rowsT_mask<K, H2>(W3s, CF::PW_H2, LQ, H2b);
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
       if (lane == 0) atomicMax(&amax2_sh, __float_as_uint(m));
     }
-    __syncthreads();
+    __syncthreads(); PROF(4);
+    row_sums<J0, TT / 4, PT, NW>(H2b, H2, acc + CF::C_B2);   // conv2 bias gradient
     const float sD = tc5::pow2_scale(__uint_as_float(amax2_sh));
     for (int i = tid; i < (H2 / 8) * NC; i += NTH) {   // dh2 parts -> RB (+ the tail chunk with columns >= J0+TT zeroed)
       const int pl = i / NC, j = i - pl * NC;

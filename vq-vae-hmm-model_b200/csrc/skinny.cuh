@@ -337,11 +337,12 @@ __device__ __forceinline__ void sk_rows_fwd(const float* __restrict__ W, int PW,
 }
 
 // sk_rowsT_mask: input gradient of a layer with few output rows, fused with the ReLU mask of the activation
-// it flows into:  buf[o][c] = buf[o][c] > 0 ? sum_{p < NP} W[p*PW + o] * D[p][c] : 0   (o < HH, every column).
+// it flows into:  buf[o][c] = buf[o][c] > 0 ? sum_{p < NP} W[p*PW + o] * D[p][c] : 0   (o < HH, every column);
+// returns the thread's max |buf|.
 // Lane <-> o (its NP weights in registers, read along the lanes), warp <-> column slice, D loads are broadcasts.
 template <int NP, int HH>
-__device__ __forceinline__ void sk_rowsT_mask(const float* __restrict__ W, int PW, const float* __restrict__ D,
-                                              float* __restrict__ buf) {
+__device__ __forceinline__ float sk_rowsT_mask(const float* __restrict__ W, int PW, const float* __restrict__ D,
+                                               float* __restrict__ buf) {
   constexpr int RW = HH / 32, NSL = NW / RW, CS = NC / NSL;
   static_assert(HH % 32 == 0 && NW % RW == 0 && NC % NSL == 0 && CS % 4 == 0, "row / slice split");
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -362,13 +363,17 @@ __device__ __forceinline__ void sk_rowsT_mask(const float* __restrict__ W, int P
       acc[4 * q + 2] = fmaf(wt[p], d.z, acc[4 * q + 2]);
       acc[4 * q + 3] = fmaf(wt[p], d.w, acc[4 * q + 3]);
     }
+  float lm = 0.f;
 #pragma unroll
   for (int q = 0; q < CS / 4; ++q) {
     float4* pb = reinterpret_cast<float4*>(buf + o * PT + c0 + 4 * q);
     const float4 a = *pb;
-    *pb = make_float4(a.x > 0.f ? acc[4 * q] : 0.f, a.y > 0.f ? acc[4 * q + 1] : 0.f, a.z > 0.f ? acc[4 * q + 2] : 0.f,
-                      a.w > 0.f ? acc[4 * q + 3] : 0.f);
+    const float4 o = make_float4(a.x > 0.f ? acc[4 * q] : 0.f, a.y > 0.f ? acc[4 * q + 1] : 0.f, a.z > 0.f ? acc[4 * q + 2] : 0.f,
+                                 a.w > 0.f ? acc[4 * q + 3] : 0.f);
+    *pb = o;
+    lm = fmaxf(fmaxf(lm, fmaxf(fabsf(o.x), fabsf(o.y))), fmaxf(fabsf(o.z), fabsf(o.w)));
   }
+  return lm;   // this thread's max |out| (scale of the fp16 parts)
 }
 
 // sk_rows_in_fwd: a layer with few INPUT rows and no taps:  out[h][c] = relu(bias[h] + sum_{k < KQ} W[h*8 + k] * X[k][c])
