@@ -198,6 +198,34 @@ def test_fused_is_active_for_base_config(elbo_impl):
     assert Fn.elbo_active_impl(Fn.make_dims(5, 64, 3, 32, 4, 128)) == elbo_impl
     assert Fn.elbo_active_impl(Fn.make_dims(5, 8, 3, 4, 2, 8)) == "layerwise"   # dims the MMA tiling cannot take
 
+@pytest.mark.parametrize("T", [512, 362])
+def test_tile_boundaries_and_skipped_tiles_vs_oracle(T):
+    """Lengths at and around the 120-step tile boundaries, and sequences so short that most of their tiles are
+    skipped (kernel C reads logits / dq streams that kernel A and B wrote only inside the dependency cone);
+    T = 362 takes the 4-byte input prefetch path (T % 4 != 0)."""
+    from oracle import elbo as O
+    C, H, K, H2, U, TH = 5, 64, 3, 32, 4, 128
+    p = O.init_params(C, H, K, H2, U, TH, seed=77)
+    Ls = [T, 1, 2, 3, 4, 5, 6, 7, 117, 118, 119, 120, 121, 122, 123, 124, 125, 126, 239, 240, 241, 242, 245, 359, 360, 361, T - 1]
+    Ls = [min(l, T) for l in Ls]
+    B = len(Ls)
+    x, u, _ = O.synth_batch(B, C, U, T, seed=T, ragged=False)
+    L = torch.tensor(Ls, dtype=torch.long)
+    keep = (torch.arange(T)[None, :] < L[:, None]).unsqueeze(1)
+    x, u = x * keep, u * keep
+    p64 = {k: v.double() for k, v in p.items()}
+    loss64, _, g64 = O.loss_and_grads(p64, x.double(), u.double(), L, U, 0.8)
+    m = _model(dict(C=C, H=H, K=K, H2=H2, U=U, TH=TH), p)
+    for rep in range(2):   # the second pass runs on a workspace holding the first pass's values
+        m.zero_grad()
+        loss = m.compute_loss(x.cuda(), u.cuda(), L, 0.8)
+        loss.backward()
+        assert abs(float(loss) - float(loss64)) <= TOL * abs(float(loss64))
+        sd = dict(m.named_parameters())
+        bad = {k: rel_err(sd[k].grad.cpu(), g64[k]) for k in O.PARAM_ORDER}
+        bad = {k: v for k, v in bad.items() if v > TOL}
+        assert not bad, bad
+
 
 def test_large_batch_vs_float64_oracle_on_gpu():
     """Accumulation over many tiles: B=1024, T=512 against the float64 oracle evaluated with torch
