@@ -126,11 +126,13 @@ __device__ __forceinline__ void split_f16(float xs, __half& h, __half& m) {
 
 // power-of-two scale that maps |x| <= bound into [2^13, 2^14) (fp16 max = 65504); 1 for bound == 0
 __device__ __forceinline__ float pow2_scale(float bound) {
-  if (!(bound > 0.f) || !isfinite(bound)) return 1.f;
-  int e = ilogbf(bound);           // bound in [2^e, 2^(e+1))
+  // integer form (this runs on every thread after each per-tile maximum): exponent field -> 2^(13 - e)
+  const uint32_t bits = __float_as_uint(bound) & 0x7fffffffu;
+  if (bits == 0u || bits >= 0x7f800000u) return 1.f;        // 0, inf, nan
+  int e = (int)(bits >> 23) - 127;                            // bound in [2^e, 2^(e+1)); subnormals read as -127
   int k = 13 - e;
   k = k > 40 ? 40 : (k < -40 ? -40 : k);   // products of two scales stay far inside fp32's range
-  return ldexpf(1.f, k);
+  return __uint_as_float((uint32_t)(k + 127) << 23);
 }
 
 }  // namespace tc5
