@@ -228,16 +228,11 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     if (tid == 0) amax_sh = 0u;
     __syncthreads(); PROF(0);
     // ---- g1 = relu(conv3'(q) + b1) -> S (fp32), then its fp16 parts -> RA   (:83-85)
-    (void)sk_conv_taps_fwd<K, H, K>(WFT, bd1s, QX, S, t0, T);   // FFMA (skinny.cuh); edge columns 0, NC-1 are zero
-    __syncthreads();
-    for (int i = tid; i < t5::NPL * NC; i += NTH) {
-      const int pl = i / NC, j = i - pl * NC;
-      __align__(16) __half hh[8], mm[8];
-#pragma unroll
-      for (int e = 0; e < 8; ++e) tc5::split_f16(S[(pl * 8 + e) * PT + j] * sA, hh[e], mm[e]);
-      uint8_t* p = RA + pl * t5::PLANE + (j + 1) * 16;
-      *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(hh);
-      *reinterpret_cast<uint4*>(p + t5::PART) = *reinterpret_cast<const uint4*>(mm);
+    {   // FFMA (skinny.cuh) straight into the fp16 parts: the scale of g1 is static and nothing reads g1 in fp32
+      float g1v[SkConv<H>::CS];
+      int r, c0;
+      (void)sk_conv_taps_regs<K, H, K>(WFT, bd1s, QX, t0, T, g1v, r, c0);   // edge columns 0, NC-1 are zero
+      sk_store_parts(g1v, sA, RA, t5::PLANE, t5::PART, r, c0);
     }
     tc5::fence_async_smem();
     tc5::fence_before_sync();

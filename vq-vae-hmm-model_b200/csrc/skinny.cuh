@@ -266,9 +266,15 @@ __device__ __forceinline__ void sk_wgrad_rows_reduce(const float* __restrict__ s
 // columns [1, NC-1) inside the sequence, 0 elsewhere.  Lane <-> output row (its 3 KQ weights live in
 // registers), warp <-> 16-column slice, so every X load is a warp broadcast and the float4 stores of rows
 // r..r+7 tile the banks (PT == 4 mod 32).  Returns this thread's max output (for the fp16 scale).
+template <int HH>
+struct SkConv {
+  static constexpr int RW = HH / 32, NSL = NW / RW, CS = NC / NSL;   // row warps, column slices, columns per slice
+};
+// core: the masked outputs of this thread's (row r, columns c0..c0+CS) stay in registers (o[]); returns their max
 template <int KQ, int HH, int KR = 8>
-__device__ __forceinline__ float sk_conv_taps_fwd(const float* __restrict__ W, const float* __restrict__ bias,
-                                                  const float* __restrict__ X, float* __restrict__ out, int t0, int T) {
+__device__ __forceinline__ float sk_conv_taps_regs(const float* __restrict__ W, const float* __restrict__ bias,
+                                                   const float* __restrict__ X, int t0, int T,
+                                                   float (&o)[SkConv<HH>::CS], int& r_out, int& c0_out) {
   constexpr int RW = HH / 32, NSL = NW / RW, CS = NC / NSL;
   static_assert(HH % 32 == 0 && NW % RW == 0 && NC % NSL == 0 && CS % 4 == 0, "row / slice split");
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -304,16 +310,39 @@ __device__ __forceinline__ float sk_conv_taps_fwd(const float* __restrict__ W, c
   const int d0 = c0 - lo;
   float lm = 0.f;
 #pragma unroll
-  for (int q = 0; q < CS / 4; ++q) {
-    float o[4];
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      o[e] = ((unsigned)(d0 + 4 * q + e) < span) ? fmaxf(acc[4 * q + e], 0.f) : 0.f;
-      lm = fmaxf(lm, o[e]);
-    }
-    *reinterpret_cast<float4*>(out + r * PT + c0 + 4 * q) = make_float4(o[0], o[1], o[2], o[3]);
+  for (int j = 0; j < CS; ++j) {
+    o[j] = ((unsigned)(d0 + j) < span) ? fmaxf(acc[j], 0.f) : 0.f;
+    lm = fmaxf(lm, o[j]);
   }
+  r_out = r; c0_out = c0;
   return lm;
+}
+// the same, stored as fp32 out[r][c]
+template <int KQ, int HH, int KR = 8>
+__device__ __forceinline__ float sk_conv_taps_fwd(const float* __restrict__ W, const float* __restrict__ bias,
+                                                  const float* __restrict__ X, float* __restrict__ out, int t0, int T) {
+  constexpr int CS = SkConv<HH>::CS;
+  float o[CS];
+  int r, c0;
+  const float lm = sk_conv_taps_regs<KQ, HH, KR>(W, bias, X, t0, T, o, r, c0);
+#pragma unroll
+  for (int q = 0; q < CS / 4; ++q)
+    *reinterpret_cast<float4*>(out + r * PT + c0 + 4 * q) = make_float4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+  return lm;
+}
+// registers -> the two fp16 parts of the tcgen05 operand layout act[part][r/8][col+1][8]: 2-byte stores; the lanes of
+// a warp (32 rows = 4 planes x 8 channels) hit 16 distinct words in 16 distinct banks (plane pitch == 8 words mod 32)
+template <int CS>
+__device__ __forceinline__ void sk_store_parts(const float (&o)[CS], float scale, uint8_t* __restrict__ dst, int plane_bytes,
+                                               int part_bytes, int r, int c0) {
+  uint8_t* p = dst + (r >> 3) * plane_bytes + (c0 + 1) * 16 + (r & 7) * 2;
+#pragma unroll
+  for (int j = 0; j < CS; ++j) {
+    __half h, m;
+    tc5::split_f16(o[j] * scale, h, m);
+    *reinterpret_cast<__half*>(p + j * 16) = h;
+    *reinterpret_cast<__half*>(p + part_bytes + j * 16) = m;
+  }
 }
 
 // sk_rows_fwd: out[k][c] = bias[k] + sum_{o < KK} W[k*PW + o] * In[o][c] for k < NR (NR * NC <= NTH threads,
