@@ -1,10 +1,14 @@
-// skinny.cuh -- FP32-FFMA version of the one "skinny" weight gradient where it beats the padded
-// tensor-core helper of mma_tf32.cuh: dWt0 (128 x 4 outputs, K = the 120 owned columns), one thread
-// per output with 16-byte operand loads.  (Measured on B200: the same treatment of the 128 -> 9
-// layer and its gradients is shared-memory-bandwidth bound -- ~1.7 FMA per LDS wavefront -- and
-// SLOWER than the mma.sync path, so those stay on the tensor core.)  Buffers are act[row][PT] fp32
+// skinny.cuh -- register-blocked FP32-FFMA forms of the "skinny" layers of the fused ELBO kernels: layers with
+// 3..10 rows on one side (encoder conv1 5 -> 64, folded decoder conv1 3 -> 64, to_logits 32 -> 3, to_params
+// 64 -> 10, the transition MLP 4 -> 128 -> 9) and their gradients.  On the padded mma.sync helpers of
+// mma_tf32.cuh these are latency- or issue-bound (rows padded to 8/16, operands split on the fly, one dependent
+// MMA chain per warp).  Common scheme: thread = (the long-side row, a time slice), the few short-side values in
+// registers, 16-byte operand loads of which all but one are warp broadcasts, slice partials in a scratch region
+// that is dead at that point, one barrier, an ordered (deterministic) reduction.  Buffers are act[row][PT] fp32
 // with PT == 4 mod 32: a 16-byte piece of 8 consecutive rows is bank-conflict free.
-// Included inside namespace vhmm::fz.
+// What stays on mma.sync after measurement (B200): the 128 -> 9 transition logits forward (kernel A) and the
+// to_params forward / input gradient (decoder) -- long contraction with BOTH operands in shared memory, ~1.7 FMA
+// per LDS wavefront as FFMA.  Included inside namespace vhmm::fz.
 #pragma once
 
 // acc[h*8 + c] += sum_{j owned} act[h][j] * in[c][j] for c < 4, h < 128; bsum[h] += sum_{j owned} act[h][j]
