@@ -229,6 +229,28 @@ def test_long_sequence_scan():
     a_last = torch.logsumexp(alpha[0, T - 1], dim=0)
     assert abs(float(a_last) - ll64[0]) <= 2e-5 * abs(ll64[0])
 
+@pytest.mark.parametrize("K", [2, 3, 4])
+def test_scan_loglik_by_segment_products(K):
+    """Log-likelihood-only scan on long sequences takes the segment-product path (one warp per 256-step segment in
+    the one-pass kernel + per-sequence carry scan): equal to the sequential forward kernel and to the float64
+    oracle; ragged lengths around the segment boundaries, incl. 0 and 1; want_alpha=True still takes the chunk path."""
+    import vhmm_b200.functional as Fn
+    for (B, T) in ((12, 1024), (4, 65536)):
+        g = torch.Generator(device="cuda").manual_seed(K * 7 + B)
+        la = torch.log_softmax(torch.randn(B, T, K, K, device="cuda", generator=g) * 1.5, dim=-1)
+        lb = torch.randn(B, T, K, device="cuda", generator=g) * 2 - 3
+        lp = torch.log_softmax(torch.randn(K, device="cuda", generator=g), dim=-1)
+        Ls = [T, T - 1, 1, 0, 255, 256, 257, 511, 512, 513, 700, 2][:B]
+        L = torch.tensor(Ls, device="cuda")
+        ll_seq = Fn.hmm_forward(lp, la, lb, L)
+        ll_seg = Fn.hmm_scan(lp, la, lb, L)
+        ll_chk, _ = Fn.hmm_scan(lp, la, lb, L, want_alpha=True)
+        assert torch.allclose(ll_seg, ll_seq, rtol=2e-6, atol=1e-3), (ll_seg, ll_seq)
+        assert torch.allclose(ll_seg, ll_chk, rtol=2e-6, atol=1e-3)
+        n = 3
+        _, ll64 = H.forward(lp.cpu().numpy(), la[:n].cpu().numpy(), lb[:n].cpu().numpy(), np.maximum(L[:n].cpu().numpy(), 1))
+        assert np.allclose(ll_seg[:n].cpu().numpy(), ll64, rtol=TOL, atol=1e-6)
+
 
 def test_fused_hmm_inputs_match_layerwise_and_oracle():
     """vhmm_hmm_inputs (one FFMA kernel from raw x,u) against the float64 oracle prior / emission and against

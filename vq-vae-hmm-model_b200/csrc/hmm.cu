@@ -124,9 +124,9 @@ static bool onepass_fits(int64_t T, int64_t K, const void* A, const void* Bm, co
   const size_t wb = 32 * (size_t)(hw::pitch_odd16(S * (int)(K * K)) + hw::pitch_odd16(S * (int)K)) * 4;
   return wb <= HW_MAX_WARP_BYTES;
 }
-template <int K, bool XI, bool LL_ONLY = false>
+template <int K, bool XI, bool LL_ONLY = false, bool SEG = false>
 static int launch_onepass(hw::Args a, cudaStream_t st) {
-  auto kern = hw::posterior_kernel<K, XI, LL_ONLY>;
+  auto kern = hw::posterior_kernel<K, XI, LL_ONLY, SEG>;
   const size_t wb = 32 * (size_t)(a.SA + a.SB) * 4;
   int wpb = (int)((56 * 1024) / wb);
   wpb = wpb < 1 ? 1 : (wpb > 4 ? 4 : wpb);
@@ -315,6 +315,30 @@ int hmm_scan(const float* log_pi, const float* A, const float* Bm, const int64_t
   sa.ll_in = ar.take<double>((size_t)B * nck);
   sa.loglik = loglik;
   VHMM_REQUIRE(ar.ok, VHMM_E_WORKSPACE, "hmm_scan: workspace %zu < %zu", ws_bytes, ar.used);
+  // log-likelihood only, T a multiple of the segment length: segment products by the one-pass kernel (one warp per
+  // 256-step segment, inputs resident in shared memory, ~HBM speed), then the per-sequence carry scan
+  constexpr int64_t SEG_T = 256;
+  if (!alpha && onepass_allowed() && T % SEG_T == 0 && T >= 2 * SEG_T && B * (T / SEG_T) < (1ll << 31) &&
+      onepass_fits(SEG_T, K, A, Bm, nullptr, nullptr)) {
+    const int64_t nseg = T / SEG_T;
+    hw::Args w{};
+    w.log_pi = log_pi; w.A = A; w.Bm = Bm; w.lengths = lengths; w.B = B * nseg; w.T = SEG_T;
+    w.S = 4 * (int)cdiv(SEG_T, 128);
+    w.SA = hw::pitch_odd16(w.S * (int)(K * K));
+    w.SB = hw::pitch_odd16(w.S * (int)K);
+    const uint64_t ga = (uint64_t)w.S * K * K / 4, gb = (uint64_t)w.S * K / 4;
+    w.magicA = (unsigned)(((1ull << 32) + ga - 1) / ga);
+    w.magicB = (unsigned)(((1ull << 32) + gb - 1) / gb);
+    w.nseg = (int)nseg; w.Pmat = sa.Pmat; w.Pscale = sa.Pscale;
+    int rc = 0;
+    DISPATCH_K(K, (rc = launch_onepass<KK, false, true, true>(w, st)));
+    if (rc) return rc;
+    hs::Args c = base_args(log_pi, A, Bm, lengths, B, T, K);
+    c.nrows = B * nseg; c.rows_per_seq = (int)nseg; c.CH = (int)SEG_T;
+    DISPATCH_K(K, (hs::scan_carry_kernel<KK><<<(unsigned)B, 32, 0, st>>>(c, sa), rc = 0));
+    VHMM_LAUNCH_CHECK();
+    return rc;
+  }
   hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
   a.nrows = B * nck; a.rows_per_seq = (int)nck; a.CH = SCAN_CH;
   a.vec_out = a.vec_out && (!alpha || aligned16(alpha));

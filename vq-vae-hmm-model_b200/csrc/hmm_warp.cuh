@@ -38,6 +38,10 @@ struct Args {
   float* loglik;           // (B) or null
   float* gamma;            // (B,T,K)
   float* xi;               // (B,T,K,K) or null (XI kernels only)
+  // SEG kernels (long sequences cut into segments of T steps; B = sequences * nseg rows, `lengths` per SEQUENCE):
+  int nseg;                // segments per sequence
+  float* Pmat;             // (rows, K*K) segment transfer products, scaled
+  double* Pscale;          // (rows) natural-log scale: true product = Pmat * exp(Pscale)
 };
 
 __host__ __device__ constexpr int pitch_odd16(int n) { return (((n >> 2) & 1) == 0) ? n + 4 : n; }
@@ -179,8 +183,12 @@ __device__ __forceinline__ void warp_prefix_scan(const float* M, int ex, const f
 
 // LL_ONLY: forward log-likelihood only (hmm_forward without all-prefix alpha): load, pass 1 without the
 // write-back of P_t, prefix scan, log-likelihood -- no suffix scan, no sweeps, no stores.
-template <int K, bool XI, bool LL_ONLY = false>
+// SEG (with LL_ONLY): the row is one T-step segment of a longer sequence; instead of a log-likelihood the kernel
+// emits the segment's transfer-matrix product (conventions of hmm_scan.cuh: step 0 of a SEQUENCE is alpha_0, not a
+// transfer) for the per-sequence carry scan -- the time-parallel scan of hmm_scan at one-pass bandwidth.
+template <int K, bool XI, bool LL_ONLY = false, bool SEG = false>
 __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
+  static_assert(!SEG || LL_ONLY, "segment products come from the log-likelihood-only pass");
   constexpr int KK = K * K;
   constexpr float LOG2E = 1.4426950408889634f, LN2 = 0.6931471805599453f;
   extern __shared__ __align__(16) float smem[];
@@ -200,7 +208,16 @@ __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
 
   const int64_t nwarps = (int64_t)gridDim.x * wpb;
   for (int64_t b = (int64_t)blockIdx.x * wpb + wib; b < a.B; b += nwarps) {
-    int64_t Ll = a.lengths[b];
+    int64_t Ll;
+    bool first = true;                               // row starts at step 0 of its sequence
+    if (SEG) {
+      const int64_t seq = b / a.nseg;
+      const int seg = (int)(b - seq * a.nseg);
+      first = (seg == 0);
+      Ll = a.lengths[seq] - (int64_t)seg * a.T;
+    } else {
+      Ll = a.lengths[b];
+    }
     const int L = (int)(Ll < 0 ? 0 : (Ll > a.T ? a.T : Ll));
     const int nv = max(0, min(S, L - t0));          // valid steps of my chunk
     // ---- load: granules that hold a valid step --------------------------------------
@@ -239,11 +256,12 @@ __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
         const float* lb = Bv + s * K;
         if (g * 4 + s < nv) {
           const float mb = max_of<K>(lb);
-          mbsum += mb;
+          const bool is0 = (t0 + g * 4 + s == 0) && first;
+          if (!(SEG && is0)) mbsum += mb;            // (SEG: the emission of step 0 belongs to alpha_0)
           float cj[K];
 #pragma unroll
           for (int j = 0; j < K; ++j) cj[j] = (lb[j] - mb) * LOG2E;
-          if (t0 + g * 4 + s == 0) {
+          if (is0) {
 #pragma unroll
             for (int j = 0; j < K; ++j) v0[j] = ex2f(pi[j] + cj[j]);
 #pragma unroll
@@ -266,6 +284,31 @@ __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
         }
       }
       if (!LL_ONLY) sts4<KK>(myA + g * 4 * KK, Av);
+    }
+    if (SEG) {   // ordered product of the 32 chunk products (tree over the lanes), then out
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        float O[KK];
+#pragma unroll
+        for (int i = 0; i < KK; ++i) O[i] = __shfl_down_sync(0xffffffffu, M[i], d);
+        const int oex = __shfl_down_sync(0xffffffffu, ex, d);
+        if ((lane & (2 * d - 1)) == 0) {
+          float R[KK];
+          mat_mul<K>(R, M, O);
+          ex += oex;
+          const float sc = pow2_rescale(fmaxf(max_of<KK>(R), 1e-37f), &ex);
+#pragma unroll
+          for (int i = 0; i < KK; ++i) M[i] = R[i] * sc;
+        }
+      }
+      const double ms = warp_sum((double)mbsum);
+      if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < KK; ++i) a.Pmat[b * KK + i] = M[i];
+        a.Pscale[b] = (double)ex * (double)LN2 + ms;
+      }
+      __syncwarp();
+      continue;
     }
     // ---- scan over the lanes ---------------------------------------------------------
     float pre[K];
