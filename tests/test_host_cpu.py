@@ -101,3 +101,61 @@ def test_sample_triples_consumes_random_like_the_reference_dataset():
             x[b, :, :ln[b]] = xs[idx[b]][:, st[b]:st[b] + ln[b]].numpy()
             u[b, :, :ln[b]] = us[idx[b]][:, st[b]:st[b] + ln[b]].numpy()
         assert np.array_equal(x, z[f"x{i}"]) and np.array_equal(u, z[f"u{i}"])
+
+
+# every ``from VQ_VAE_HMM_fixed import`` / ``from src... import`` line of the reference tree (grep of the checkout;
+# the files are cited so the list can be re-derived)
+REFERENCE_IMPORT_LINES = [
+    "from VQ_VAE_HMM_fixed import VAE_HMM",                                                   # api.py:4, app.py:5, inference_api/app.py:10, tests/smoke_test.py:11
+    "from VQ_VAE_HMM_fixed import VAE_HMM, RandomChunkDataset, collate_fn",                   # evaluation/evaluate.py:19, training_pipeline/train.py:16
+    "from VQ_VAE_HMM_fixed import RandomChunkDataset, collate_fn",                            # data_loader.py:6
+    "from VQ_VAE_HMM_fixed import VAE_HMM, train_model, RegimePortfolioOptimizer, sharpe_loss",   # train.py:4
+    "from src.models import VAE_HMM",                                                         # examples/train_example.py:5
+    "from src.portfolio import RegimePortfolioOptimizer, sharpe_loss",                        # examples/train_example.py:6
+    "from src.training import Trainer",                                                       # examples/train_example.py:7
+    "from src.utils import RandomChunkDataset, collate_fn",                                   # examples/train_example.py:8
+    "from src.models.vae_hmm import VAE_HMM, Encoder, Decoder, Prior",                        # src/__init__.py:11
+    "from src.portfolio.optimizers import RegimePortfolioOptimizer, AttentionPortfolioOptimizer, TransformerPortfolioOptimizer, BayesianPortfolioOptimizer",  # src/__init__.py:12
+    "from src.portfolio.hedging import RegimeDeltaHedger, DynamicDeltaHedger",                # src/__init__.py:18
+    "from src.training.trainer import Trainer, MetaTrainer, WalkForwardTrainer",              # src/__init__.py:19
+    "from src.utils.data import RandomChunkDataset, collate_fn, save_checkpoint, load_checkpoint",  # src/utils/__init__.py:3
+]
+OUT_OF_SCOPE = ("RegimePortfolioOptimizer", "sharpe_loss", "src.portfolio", "MetaTrainer", "WalkForwardTrainer")
+
+
+def _run_import_lines(lines, pythonpath):
+    import subprocess
+    import sys
+    code = "import vhmm_b200\n" + "\n".join(lines) + "\nprint('IMPORTS_OK')\n"
+    env = dict(os.environ, PYTHONPATH=pythonpath, PYTHONDONTWRITEBYTECODE="1")
+    env.pop("VHMM_REFERENCE_ROOT", None)
+    return subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, cwd="/tmp")
+
+
+def test_every_reference_import_site_resolves():
+    """With this repo AHEAD of a reference checkout on PYTHONPATH every import line of the reference tree works:
+    hot-path names come from this repo, out-of-scope names from the reference's own files."""
+    ref = "/root/reference"
+    if not os.path.isdir(ref):
+        pytest.skip("no reference checkout on this machine (the GPU box)")
+    r = _run_import_lines(REFERENCE_IMPORT_LINES + [
+        "import vhmm_b200, VQ_VAE_HMM_fixed, src.models, src.training",
+        "assert VQ_VAE_HMM_fixed.VAE_HMM is vhmm_b200.VAE_HMM and src.models.VAE_HMM is vhmm_b200.VAE_HMM",
+        "assert src.training.Trainer is vhmm_b200.Trainer",
+        "assert RegimePortfolioOptimizer.__module__.startswith('src.portfolio')",
+    ], ROOT + os.pathsep + ref)
+    assert r.returncode == 0 and "IMPORTS_OK" in r.stdout, r.stderr[-2000:]
+
+
+def test_import_sites_without_reference_checkout():
+    """Without a reference checkout the hot-path names still import; out-of-scope names raise ImportError."""
+    inscope = [l for l in REFERENCE_IMPORT_LINES if not any(k in l for k in OUT_OF_SCOPE)]
+    r = _run_import_lines(inscope, ROOT)
+    assert r.returncode == 0 and "IMPORTS_OK" in r.stdout, r.stderr[-2000:]
+    rest = [l for l in REFERENCE_IMPORT_LINES if l not in inscope]
+    body = ["bad = []"]
+    for l in rest:
+        body += ["try:", "    " + l, "    bad.append(%r)" % l, "except ImportError:", "    pass"]
+    body.append("assert not bad, bad")
+    r = _run_import_lines(body, ROOT)
+    assert r.returncode == 0 and "IMPORTS_OK" in r.stdout, r.stderr[-2000:]
