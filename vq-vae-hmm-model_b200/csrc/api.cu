@@ -10,6 +10,23 @@ namespace vhmm {
 
 static thread_local char g_err[512] = "";
 static std::atomic<long long> g_launches{0};
+
+int current_device() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) dev = 0;
+  return dev < VHMM_MAX_DEVICES ? dev : VHMM_MAX_DEVICES - 1;
+}
+int device_sm_count() {
+  static std::atomic<int> sms[VHMM_MAX_DEVICES];
+  const int dev = current_device();
+  int n = sms[dev].load(std::memory_order_relaxed);
+  if (n == 0) {
+    int v = 0;
+    n = (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) ? v : 148;
+    sms[dev].store(n, std::memory_order_relaxed);
+  }
+  return n;
+}
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 void set_error(const char* fmt, ...) {

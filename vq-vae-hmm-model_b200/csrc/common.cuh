@@ -12,6 +12,20 @@ namespace vhmm {
 void set_error(const char* fmt, ...);
 void count_launch();  // process-wide kernel launch counter (vhmm_launch_count)
 
+// Per-DEVICE cached state (api.cu).  Function attributes (cudaFuncSetAttribute) and SM counts belong to a
+// device/context, not to the process: a process that drives several GPUs (model.to('cuda:1'), one thread per
+// GPU) must see each device's own values.  Slots are indexed by cudaGetDevice(); entries are written with the
+// same idempotent values by racing first callers.
+constexpr int VHMM_MAX_DEVICES = 64;
+int current_device();                 // cudaGetDevice(), 0 on failure; clamped to [0, VHMM_MAX_DEVICES)
+int device_sm_count();                // multiprocessors of the CURRENT device (cached per device)
+// once-per-device flag: returns true exactly when `slot` has not been marked for the current device yet
+struct PerDeviceOnce {
+  unsigned char done[VHMM_MAX_DEVICES] = {};
+  bool pending() const { return !done[current_device()]; }
+  void mark() { done[current_device()] = 1; }
+};
+
 #define VHMM_CUDA_CHECK(expr)                                                            \
   do {                                                                                   \
     cudaError_t e__ = (expr);                                                            \

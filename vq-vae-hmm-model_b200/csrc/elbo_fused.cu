@@ -23,6 +23,7 @@
 // padded batch; activations are zero only outside [0,T) (conv zero padding); `lengths` masks the
 // loss terms only.  Tiles beyond the dependency cone of the valid steps are skipped (their
 // gradients are exactly zero) and the consumers substitute zeros for what was not written.
+#include <atomic>
 #include <stdlib.h>
 #include <string.h>
 #include "common.cuh"
@@ -853,7 +854,7 @@ static TimingState g_timing_;
 #define g_timing ::vhmm::fz::g_timing_
 
 // which decoder kernel the fused path launches: 0 = auto (tcgen05), 1 = mma.sync 3xTF32, 2 = tcgen05 2xFP16
-static int g_decoder_variant_ = 0;
+static std::atomic<int> g_decoder_variant_{0};
 inline int decoder_variant() {
   int v = g_decoder_variant_;
   if (v == 0) {
@@ -906,15 +907,15 @@ struct Launcher {
     const size_t smB = tc5v ? t5::Lay<CF>::BYTES : (size_t)CF::SM_B * 4;
     auto kC = tc5e ? enc_bwd_tc5_kernel<CF> : enc_bwd_kernel<CF>;
     const size_t smC = tc5e ? t5e::Sz<CF>::C : (size_t)CF::SM_C * 4;
-    static bool attr_done = false;   // idempotent: a racing second caller sets the same values
-    if (!attr_done) {
+    static PerDeviceOnce attr_done;   // per device (the attribute belongs to the context); idempotent under a race
+    if (attr_done.pending()) {
       VHMM_CUDA_CHECK(cudaFuncSetAttribute(enc_prior_kernel<CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SM_A * 4));
       VHMM_CUDA_CHECK(cudaFuncSetAttribute(enc_prior_tc5_kernel<CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5e::Sz<CF>::A));
       VHMM_CUDA_CHECK(cudaFuncSetAttribute(enc_bwd_tc5_kernel<CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5e::Sz<CF>::C));
       VHMM_CUDA_CHECK(cudaFuncSetAttribute(decoder_kernel<CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SM_B * 4));
       VHMM_CUDA_CHECK(cudaFuncSetAttribute(decoder_tc5_kernel<CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5::Lay<CF>::BYTES));
       VHMM_CUDA_CHECK(cudaFuncSetAttribute(enc_bwd_kernel<CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SM_C * 4));
-      attr_done = true;
+      attr_done.mark();
     }
     VHMM_CUDA_CHECK(cudaMemsetAsync(cm.loss_part, 0, (size_t)ncta * LP * 8, st));
     if (grads) VHMM_CUDA_CHECK(cudaMemsetAsync(cm.acc_part, 0, (size_t)ncta * CF::ACC_ALL * 8, st));
@@ -956,18 +957,7 @@ using CfgBase = Cfg<5, 64, 32, 3, 4, 128>;   // BASELINE.json configs[0..1]
 
 }  // namespace fz
 
-static int fused_sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0, v = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess &&
-        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
-      n = v;
-    else
-      n = 148;
-  }
-  return n;
-}
+static int fused_sm_count() { return device_sm_count(); }   // of the CURRENT device
 
 int fused_decoder_select(int variant) { fz::g_decoder_variant_ = variant; return 0; }
 int fused_decoder_active() { return fz::decoder_variant(); }

@@ -4,6 +4,7 @@
 #include "hmm_generic.cuh"
 #include "hmm_scan.cuh"
 #include "hmm_warp.cuh"
+#include <atomic>
 #include <stdlib.h>
 
 namespace vhmm {
@@ -107,7 +108,7 @@ static int launch_bwd_small(const hs::Args& a, cudaStream_t st) {
 
 
 // ---- one-pass posterior (hmm_warp.cuh): whole sequence in shared memory, one warp each ------
-static int g_posterior_mode = -1;   // -1: from env VHMM_POSTERIOR (onepass|sweep), 0 auto, 1 sweep only
+static std::atomic<int> g_posterior_mode{-1};   // -1: from env VHMM_POSTERIOR (onepass|sweep), 0 auto, 1 sweep only
 int hmm_posterior_select(int mode) { g_posterior_mode = mode; return 0; }
 static bool onepass_allowed() {
   if (g_posterior_mode < 0) {
@@ -131,12 +132,7 @@ static int launch_onepass(hw::Args a, cudaStream_t st) {
   int wpb = (int)((56 * 1024) / wb);
   wpb = wpb < 1 ? 1 : (wpb > 4 ? 4 : wpb);
   const size_t smem = wb * wpb;
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    VHMM_CUDA_CHECK(cudaGetDevice(&dev));
-    VHMM_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  }
+  const int sms = device_sm_count();   // current device
   VHMM_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   VHMM_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
   int per_sm = 0;
@@ -238,7 +234,7 @@ int hmm_viterbi(const float* log_pi, const float* A, const float* Bm, const int6
   VHMM_REQUIRE(ar.ok, VHMM_E_WORKSPACE, "viterbi: workspace %zu < %zu", ws_bytes, ar.used);
   if (small_k(K)) {
     hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
-    a.psi = psi; a.path = path; a.score = score;
+    a.psi = psi; a.path = path; a.vec_path = ((T & 3) == 0) && (((uintptr_t)path & 3) == 0); a.score = score;
     int rc = 0;
     DISPATCH_K(K, (rc = launch_fwd_small<KK, false, true>(a, st)));
     return rc;
@@ -261,7 +257,7 @@ int hmm_decode(const float* log_pi, const float* A, const float* Bm, const int64
     // Viterbi sweep (49 B/step) + one-pass posterior (60 B/step): 109 B/step of traffic against
     // 181 B/step for the fused forward sweep + backward sweep below
     hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
-    a.psi = psi; a.path = path; a.score = nullptr;
+    a.psi = psi; a.path = path; a.vec_path = ((T & 3) == 0) && (((uintptr_t)path & 3) == 0); a.score = nullptr;
     int rc = 0;
     DISPATCH_K(K, (rc = launch_fwd_small<KK, false, true>(a, st)));
     if (rc) return rc;
@@ -272,7 +268,7 @@ int hmm_decode(const float* log_pi, const float* A, const float* Bm, const int64
     // inputs; the backward sweep then produces gamma.
     hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
     a.loglik = loglik; a.ahat = stash; a.gamma = gamma; a.xi = nullptr;
-    a.psi = psi; a.path = path; a.score = nullptr;
+    a.psi = psi; a.path = path; a.vec_path = ((T & 3) == 0) && (((uintptr_t)path & 3) == 0); a.score = nullptr;
     a.vec_out = a.vec_out && aligned16(stash) && aligned16(gamma);
     int rc = 0;
     DISPATCH_K(K, (rc = launch_fwd_small<KK, true, true>(a, st)));

@@ -11,6 +11,7 @@
 // consumed by the K*K logits, so per hidden unit 2 + PK2/4 broadcast LDS.128 feed 4 (U + 1 + K*K) FP32
 // operations -- FFMA bound (1,664 MAC per step), no activation traffic at all.  The emission term reads a
 // pre-reduced table (mu, 1/v, log(2 pi v)) built once per call by a tiny kernel.
+#include <atomic>
 #include "common.cuh"
 #include "hmm_warp.cuh"
 
@@ -298,14 +299,14 @@ int hmm_loglik_fused(const vhmm_dims& d, const vhmm_params& P, const float* log_
   emission_tab3_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(mu_tab, logvar_tab, n, tab3);
   VHMM_LAUNCH_CHECK();
   // persistent grid = exactly the resident CTAs (a partial second wave of equal-work CTAs would double the time)
-  static int per_sm = 0, sms = 0;
+  static std::atomic<int> per_sm_dev[VHMM_MAX_DEVICES];   // resident CTAs per SM, per device
+  const int sms = device_sm_count();
+  int per_sm = per_sm_dev[current_device()].load(std::memory_order_relaxed);
   if (!per_sm) {
-    int dev = 0, n_sm = 0, n_cta = 0;
-    VHMM_CUDA_CHECK(cudaGetDevice(&dev));
-    VHMM_CUDA_CHECK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+    int n_cta = 0;
     VHMM_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n_cta, hmm_loglik_fused_kernel<3, 5, 4, 128>, 128, 0));
-    sms = n_sm;
     per_sm = n_cta < 1 ? 1 : n_cta;
+    per_sm_dev[current_device()].store(per_sm, std::memory_order_relaxed);
   }
   int64_t grid = cdiv(B, 4);
   if (grid > (int64_t)sms * per_sm) grid = (int64_t)sms * per_sm;

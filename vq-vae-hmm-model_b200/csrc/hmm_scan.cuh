@@ -38,6 +38,7 @@ __device__ __forceinline__ void matmul_norm(float* P, const float* M, double* sc
       R[i * K + j] = acc;
       s += acc;
     }
+  s = fmaxf(s, 1.17549435e-38f);   // a vanished product (structural zeros / underflow) must not turn into NaN
   const float inv = 1.f / s;
 #pragma unroll
   for (int i = 0; i < K * K; ++i) P[i] = R[i] * inv;
@@ -186,6 +187,7 @@ __global__ void __launch_bounds__(32) scan_carry_kernel(Args a, ScanArgs sa) {
       for (int i = 0; i < K; ++i) acc = fmaf(v[i], X[i * K + j], acc);
       w[j] = acc; cs += acc;
     }
+    cs = fmaxf(cs, 1.17549435e-38f);
 #pragma unroll
     for (int j = 0; j < K; ++j) v[j] = w[j] / cs;
     ll += xs + (double)logf(cs);
@@ -203,6 +205,7 @@ __global__ void __launch_bounds__(32) scan_carry_kernel(Args a, ScanArgs sa) {
       for (int i = 0; i < K; ++i) acc = fmaf(v[i], sa.Pmat[(row0 + c) * K * K + i * K + j], acc);
       w[j] = acc; cs += acc;
     }
+    cs = fmaxf(cs, 1.17549435e-38f);
 #pragma unroll
     for (int j = 0; j < K; ++j) v[j] = w[j] / cs;
     ll += sa.Pscale[row0 + c] + (double)logf(cs);

@@ -57,6 +57,7 @@ struct Args {
   int vec_out;             // 16-byte stores allowed for (B,T,K) outputs / stash
   int vec_xi;              // 16-byte stores allowed for xi
   int full;                // visit every step (outputs are defined for t >= L too)
+  int vec_path;            // 4-byte stores into `path` allowed (T % 4 == 0 and the caller's pointer is 4-byte aligned)
   // forward outputs
   float* loglik;           // (B)            plain rows only
   float* alpha_log;        // (B,T,K) or null
@@ -326,11 +327,12 @@ __global__ void __launch_bounds__(NT) fwd_kernel(Args a) {
     if (a.score) a.score[b] = (n > 0) ? best : 0.f;
     uint8_t* prow = a.path + b * a.T;
     const uint8_t* psirow = a.psi + b * a.T * Psi<K>::BYTES;
-    const bool v4 = ((a.T & 3) == 0);
+    const bool v4 = ((a.T & 3) == 0);          // psi rows (library workspace, 256-byte aligned)
+    const bool p4 = v4 && a.vec_path;          // path rows (caller's pointer)
     const int T = (int)a.T;
     // pad region
     for (int t = T - 1; t >= n; --t) {
-      if (v4 && (t & 3) == 3 && t - 3 >= n) { *reinterpret_cast<uint32_t*>(prow + t - 3) = 0xFFFFFFFFu; t -= 3; }
+      if (p4 && (t & 3) == 3 && t - 3 >= n) { *reinterpret_cast<uint32_t*>(prow + t - 3) = 0xFFFFFFFFu; t -= 3; }
       else prow[t] = VHMM_PAD_STATE;
     }
     int t = n - 1;
@@ -343,7 +345,8 @@ __global__ void __launch_bounds__(NT) fwd_kernel(Args a) {
           out |= (uint32_t)state << (8 * s);
           if (t - 3 + s >= 1) state = (int)((w >> (8 * s + 2 * state)) & 3u);
         }
-        *reinterpret_cast<uint32_t*>(prow + t - 3) = out;
+        if (p4) *reinterpret_cast<uint32_t*>(prow + t - 3) = out;
+        else { prow[t - 3] = (uint8_t)out; prow[t - 2] = (uint8_t)(out >> 8); prow[t - 1] = (uint8_t)(out >> 16); prow[t] = (uint8_t)(out >> 24); }
         t -= 4;
       } else {
         prow[t] = (uint8_t)state;
