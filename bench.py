@@ -26,6 +26,7 @@ sys.path.insert(0, ROOT)
 MODEL = dict(C=5, H=64, K=3, H2=32, U=4, TH=128)
 FLOP_PER_STEP = 205740          # algorithmic fwd+bwd FLOPs per sequence-step (base)
 BYTES_PER_STEP = 72             # x,u read once forward and once backward
+TRAFFIC_FILE = "r1d_decoder_traffic.json"   # latest committed ncu --set full capture of the decoder tile kernel
 DEC_FLOP_PER_STEP = 3 * 50816   # decoder forward 50,816 FLOP/step; fwd+bwd = 3x
 FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12   # FFMA peak at max SM clock (derived)
 
@@ -41,8 +42,9 @@ def peaks():
 class ClockSampler:
     """samples SM clock / throttle reasons of one GPU during the timed region"""
 
-    def __init__(self, index):
+    def __init__(self, index, interval=0.05):
         self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self.interval = interval
         self._stop = threading.Event()
         self._thr = None
         try:
@@ -70,7 +72,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            time.sleep(0.05)
+            time.sleep(self.interval)
 
     def start(self):
         if self.nv is not None:
@@ -87,21 +89,45 @@ class ClockSampler:
 
 
 def cpu_reference_step_rate(B_cpu, T, steps, warmup, threads=None):
-    """The reference's CPU PyTorch path (oracle/elbo.py restates it op for op) timed on the host
-    cores: compute_loss + backward on a bounded sample of the workload."""
+    """The reference's CPU PyTorch path timed on the host cores: compute_loss + backward on a bounded sample of
+    the workload.  kind "reference": the UNMODIFIED reference module (oracle/_ref/VQ_VAE_HMM_fixed.py, placed
+    there by oracle/build_ref.py; it travels to the GPU box like the built library); kind "port": the pinned
+    op-for-op restatement oracle/elbo.py when the copy is absent.  Returns (steps/s, s/step, threads, kind)."""
     import torch
     from oracle import elbo as O
+    from oracle import build_ref
     n = threads or os.cpu_count() or 1
     torch.set_num_threads(n)
-    p = O.init_params(MODEL["C"], MODEL["H"], MODEL["K"], MODEL["H2"], MODEL["U"], MODEL["TH"], seed=0)
     x, u, L = O.synth_batch(B_cpu, MODEL["C"], MODEL["U"], T, seed=1234, ragged=False)
+    R = build_ref.load()
+    if R is not None:
+        torch.manual_seed(0)
+        m = R.VAE_HMM(MODEL["C"], MODEL["H"], MODEL["K"], MODEL["H2"], u_dim=MODEL["U"])   # stays on the CPU
+        m.train()
+
+        def step():
+            m.zero_grad(set_to_none=True)
+            loss = m.compute_loss(x, u, L, 1.0)      # VQ_VAE_HMM_fixed.py:106-137
+            loss.backward()                          # :156
+            return loss
+        kind = "reference"
+    else:
+        p = O.init_params(MODEL["C"], MODEL["H"], MODEL["K"], MODEL["H2"], MODEL["U"], MODEL["TH"], seed=0)
+
+        def step():
+            return O.loss_and_grads(p, x, u, L, MODEL["U"], 1.0)
+        kind = "port"
     for _ in range(warmup):
-        O.loss_and_grads(p, x, u, L, MODEL["U"], 1.0)
+        step()
     t0 = time.perf_counter()
     for _ in range(steps):
-        O.loss_and_grads(p, x, u, L, MODEL["U"], 1.0)
+        step()
     dt = (time.perf_counter() - t0) / steps
-    return B_cpu * T / dt, dt, n
+    return B_cpu * T / dt, dt, n, kind
+
+
+CPU_KIND_TEXT = {"reference": "the unmodified reference module (oracle/_ref/VQ_VAE_HMM_fixed.py) on the CPU, torch fp32",
+                 "port": "oracle port (oracle/elbo.py, pinned bit for bit to the reference) on the CPU, torch fp32"}
 
 
 def run_reference(args):
@@ -109,19 +135,185 @@ def run_reference(args):
     if rank != 0:
         return
     B_cpu, T = args.cpu_batch, args.T
-    rate, dt, n = cpu_reference_step_rate(B_cpu, T, args.steps, args.warmup)
-    sample = f"B={B_cpu} of {args.B} sequences, T={T}, compute_loss+backward, torch CPU fp32"
+    rate, dt, n, kind = cpu_reference_step_rate(B_cpu, T, args.steps, args.warmup)
+    sample = f"B={B_cpu} of {args.B} sequences, T={T}, compute_loss+backward, {CPU_KIND_TEXT[kind]}"
     line = {
         "impl": "reference", "metric": "sequence-steps/sec for ELBO fwd+bwd", "value": rate,
         "unit": "sequence-steps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"cfg2: VAE_HMM(5,64,K=3,32,u_dim=4) ELBO fwd+bwd B={args.B} T={T} (CPU sample B={B_cpu})"},
-        "cpu_baseline": {"value": rate, "unit": "sequence-steps/s", "cores": n, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": rate, "unit": "sequence-steps/s", "cores": n, "kind": kind, "sample": sample},
         "e2e": {"value": rate, "unit": "sequence-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# stage lines: the HBM-bound exact-HMM kernels (and the front ends that feed them) on BASELINE.json configs
+# [2] (B=2^20, T=256, K=3), [3] (B=64, T=65536) and a K=32 case of [4], each timed with CUDA events on the
+# launch stream with its own NVML clock record.  Algorithmic bytes per step: SURVEY.md 8(d).
+# ---------------------------------------------------------------------------------------------------------
+def timed_stage(torch, fn, local, min_ms=250.0, warmup=3, max_iters=400):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); fn(); e1.record()
+    torch.cuda.synchronize()
+    one = max(e0.elapsed_time(e1), 1e-3)
+    iters = int(min(max_iters, max(5, min_ms / one)))
+    sampler = ClockSampler(local, interval=0.01)
+    sampler.start()
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    return e0.elapsed_time(e1) / iters, iters, clocks
+
+
+def stage_line(name, cfg, ms, iters, clocks, steps, bytes_per_step, pk, flop_per_step=None, note=None):
+    gbs = bytes_per_step * steps / (ms * 1e-3) / 1e9
+    d = {"stage": name, "config": cfg, "ms": ms, "iters": iters, "steps": steps, "steps_per_s": steps / (ms * 1e-3),
+         "bytes_per_step": bytes_per_step, "bound": "hbm", "achieved_gbs": gbs, "peak_gbs": pk["hbm"],
+         "frac": gbs / pk["hbm"], "clocks": clocks}
+    if flop_per_step:
+        tf = flop_per_step * steps / (ms * 1e-3) / 1e12
+        d.update({"bound": "fp32-ffma", "flop_per_step": flop_per_step, "achieved_tflops": tf,
+                  "frac_of_fp32_ffma_peak": tf / FP32_PEAK_TFLOPS, "frac_hbm": d["frac"]})
+        d["frac"] = tf / FP32_PEAK_TFLOPS
+    if note:
+        d["note"] = note
+    return d
+
+
+def synth_hmm_inputs(torch, dev, B, T, K, seed):
+    """row-normalised log_A (B,T,K,K), Gaussian-like log_b (B,T,K), log_pi -- generated in slabs"""
+    g = torch.Generator(device=dev).manual_seed(seed)
+    log_pi = torch.log_softmax(torch.randn(K, device=dev, generator=g), 0)
+    log_A = torch.empty(B, T, K, K, device=dev)
+    slab = max(1, (1 << 26) // (T * K * K))
+    for b0 in range(0, B, slab):
+        n = min(slab, B - b0)
+        log_A[b0:b0 + n] = torch.log_softmax(torch.randn(n, T, K, K, device=dev, generator=g), -1)
+    log_b = -0.5 * torch.randn(B, T, K, device=dev, generator=g) ** 2 - 1.0
+    return log_pi, log_A, log_b
+
+
+def run_stages(torch, V, Fn, model, dev, local, pk, quick=False):
+    """rank 0, single GPU.  Returns the list of stage lines."""
+    out = []
+    mn = 60.0 if quick else 250.0
+    with torch.no_grad():
+        # ---- cfg 3: B = 2^20, T = 256, K = 3; inputs produced by the pipeline from seeded x, u (SURVEY 8d)
+        B, T, K = (1 << 20), 256, 3
+        cfg = f"cfg3: B={B} T={T} K={K}, lengths=T, log_A/log_b from the model's front end on seeded x,u"
+        g = torch.Generator(device=dev).manual_seed(4321)
+        x = torch.randn(B, MODEL["C"], T, device=dev, generator=g)
+        u = torch.randn(B, MODEL["U"], T, device=dev, generator=g)
+        L = torch.full((B,), T, dtype=torch.int64, device=dev)
+        steps = B * T
+        ms, it, ck = timed_stage(torch, lambda: model.hmm_inputs(x, u), local, mn)
+        out.append(stage_line("hmm_inputs (x,u -> log_A, log_b: transition MLP + row log-softmax + emission log-prob, one kernel)",
+                              cfg, ms, it, ck, steps, 36 + 48, pk, flop_per_step=3328 + 90,
+                              note="compute-bound front end: 3,328 FLOP of the 4->128->9 MLP per 84 B"))
+        ms, it, ck = timed_stage(torch, lambda: model.hmm_log_likelihood(x, u, L), local, mn)
+        out.append(stage_line("hmm_loglik_fused (raw x,u -> log p(x|u): softmax + emission + forward recursion, one kernel)",
+                              cfg, ms, it, ck, steps, 36, pk, flop_per_step=3328 + 90,
+                              note="north-star kernel #2; nothing materialised, HBM traffic = x,u only"))
+        ms, it, ck = timed_stage(torch, lambda: model.decode_regimes(x, u, L), local, mn)
+        out.append(stage_line("decode_regimes from raw x,u (front end + Viterbi + gamma)", cfg, ms, it, ck, steps, 36 + 13, pk))
+        log_pi, log_A, log_b = model.hmm_inputs(x, u)
+        del x, u
+        inb = 4 * (K * K + K)
+        for name, bps, fn in (
+                ("hmm_forward (log-likelihood)", inb, lambda: Fn.hmm_forward(log_pi, log_A, log_b, L)),
+                ("viterbi (uint8 path)", inb + 1, lambda: Fn.viterbi(log_pi, log_A, log_b, L)),
+                ("hmm_posterior (gamma)", inb + 4 * K, lambda: Fn.hmm_posterior(log_pi, log_A, log_b, L, want_xi=False)),
+                ("hmm_posterior (gamma + xi = beta-recursion gradient)", 2 * inb, lambda: Fn.hmm_posterior(log_pi, log_A, log_b, L, want_xi=True)),
+                ("hmm_decode (Viterbi path + gamma)", inb + 4 * K + 1, lambda: Fn.hmm_decode(log_pi, log_A, log_b, L))):
+            ms, it, ck = timed_stage(torch, fn, local, mn)
+            out.append(stage_line(name, cfg, ms, it, ck, steps, bps, pk))
+        del log_A, log_b
+        Fn.release_workspaces()
+        torch.cuda.empty_cache()
+        # ---- cfg 4: B = 64, T = 65536 (long sequences, small batch): log-semiring scan over T
+        B, T = 64, 65536
+        cfg = f"cfg4: B={B} T={T} K={K} (201 MB job: launch/latency-bound)"
+        log_pi, log_A, log_b = synth_hmm_inputs(torch, dev, B, T, K, 11)
+        L = torch.full((B,), T, dtype=torch.int64, device=dev)
+        ms, it, ck = timed_stage(torch, lambda: Fn.hmm_scan(log_pi, log_A, log_b, L), local, mn, max_iters=4000)
+        out.append(stage_line("hmm_scan (log-likelihood)", cfg, ms, it, ck, B * T, inb, pk,
+                              note="201 MB of inputs fit the 126 MB L2 only partly; repeated launches re-read from HBM"))
+        ms, it, ck = timed_stage(torch, lambda: Fn.hmm_scan(log_pi, log_A, log_b, L, want_alpha=True), local, mn, max_iters=2000)
+        out.append(stage_line("hmm_scan (all-prefix alpha)", cfg, ms, it, ck, B * T, inb + 4 * K, pk))
+        del log_A, log_b
+        # ---- cfg 5 recursion shapes: K = 32 (warp-per-sequence kernels), T = 1024
+        B, T, K = 2048, 1024, 32
+        cfg = f"cfg5 recursion: B={B} T={T} K={K} (B bounded by the materialised log_A: 4,224 B/step)"
+        log_pi, log_A, log_b = synth_hmm_inputs(torch, dev, B, T, K, 12)
+        L = torch.full((B,), T, dtype=torch.int64, device=dev)
+        inb = 4 * (K * K + K)
+        for name, bps, fn in (
+                ("hmm_forward K=32", inb, lambda: Fn.hmm_forward(log_pi, log_A, log_b, L)),
+                ("viterbi K=32", inb + 1, lambda: Fn.viterbi(log_pi, log_A, log_b, L)),
+                ("hmm_posterior K=32 (gamma)", inb + 4 * K, lambda: Fn.hmm_posterior(log_pi, log_A, log_b, L, want_xi=False))):
+            ms, it, ck = timed_stage(torch, fn, local, mn)
+            out.append(stage_line(name, cfg, ms, it, ck, B * T, bps, pk))
+        del log_A, log_b
+        Fn.release_workspaces()
+        torch.cuda.empty_cache()
+    return out
+
+
+def run_decode_sharded(torch, dist, V, Fn, model, dev, local, world, rank, pk):
+    """BASELINE.json configs[2]: Viterbi + posterior decoding of B = 2^20 sequences (T = 256, K = 3) batch-sharded
+    over the ranks -- pure replicas over disjoint shards, no collective in the data path.  Strong
+    scaling: the 2^20 sequences are split; max-over-ranks device time; steps/s over all ranks."""
+    B_total, T, K = (1 << 20), 256, 3
+    Bl = B_total // world
+    g = torch.Generator(device=dev).manual_seed(4321 + rank)
+    res = {}
+    with torch.no_grad():
+        x = torch.randn(Bl, MODEL["C"], T, device=dev, generator=g)
+        u = torch.randn(Bl, MODEL["U"], T, device=dev, generator=g)
+        L = torch.full((Bl,), T, dtype=torch.int64, device=dev)
+        log_pi, log_A, log_b = model.hmm_inputs(x, u)
+        for key, bps, fn in (("decode_materialised", 61, lambda: Fn.hmm_decode(log_pi, log_A, log_b, L)),
+                             ("decode_from_raw", 49, lambda: model.decode_regimes(x, u, L))):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            sampler = ClockSampler(local, interval=0.01)
+            sampler.start()
+            iters = 20
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            clocks = sampler.stop()
+            ms = e0.elapsed_time(e1) / iters
+            if world > 1:
+                t = torch.tensor([ms], device=dev, dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = float(t)
+            steps = B_total * T
+            res[key] = {"ms": ms, "iters": iters, "steps_per_s": steps / (ms * 1e-3), "bytes_per_step": bps,
+                        "achieved_gbs_per_gpu": bps * (steps / world) / (ms * 1e-3) / 1e9,
+                        "frac_hbm_per_gpu": bps * (steps / world) / (ms * 1e-3) / 1e9 / pk["hbm"], "clocks": clocks}
+        del log_A, log_b, x, u
+    Fn.release_workspaces()
+    torch.cuda.empty_cache()
+    return {"workload": f"cfg3: Viterbi path + posterior gamma, B={B_total} total ({Bl} per GPU) T={T} K={K}, "
+                        f"batch-sharded x{world}, no collective", "n_gpus": world, "scaling": "strong", **res}
 
 
 def main():
@@ -132,8 +324,12 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--B", type=int, default=65536, help="sequences per GPU")
     ap.add_argument("--T", type=int, default=512)
-    ap.add_argument("--cpu-batch", type=int, default=512, help="sequences in the CPU baseline sample")
+    ap.add_argument("--cpu-batch", type=int, default=1024, help="sequences in the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-stages", action="store_true", help="skip the exact-HMM stage lines / cfg-3 decode block")
+    ap.add_argument("--quick-stages", action="store_true", help="shorter stage timings")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --B sequences per GPU (default, the contract's per-N lines); strong: --B sequences in total")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -152,7 +348,9 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    B, T, W, K = args.B, args.T, max(args.warmup, 3), args.steps
+    B, T, W, K = args.B, args.T, max(args.warmup, 3), args.steps   # timing rules: at least 3 warm-up steps ("warmup" in the line is the value used)
+    if args.scaling == "strong":
+        B = B // world
 
     torch.manual_seed(0)
     model = V.VAE_HMM(MODEL["C"], MODEL["H"], MODEL["K"], MODEL["H2"], u_dim=MODEL["U"]).to(dev)
@@ -227,6 +425,27 @@ def main():
     h2d = xh.numel() * 4 + uh.numel() * 4 + lh.numel() * 8
     loss_val = float(loss.detach())
 
+    # strong-scaling companion of the weak line (N > 1): the metric config's B sequences IN TOTAL, B/N per GPU --
+    # the per-launch prologue (weight staging, partial reduction) and the all-reduce weigh N times more here
+    strong = None
+    if world > 1 and args.scaling == "weak":
+        Bs = B // world
+        xs, us, ls = x[:Bs], u[:Bs], lengths[:Bs]
+
+        def step_strong():
+            model.zero_grad(set_to_none=True)
+            ll = model.compute_loss(xs, us, ls, beta)
+            ll.backward()
+            return ll
+        for _ in range(3):
+            step_strong()
+        ms_s, _ = timed(step_strong, K)
+        strong = {"scaling": "strong", "B_total": Bs * world, "B_per_gpu": Bs, "ms_per_step": ms_s,
+                  "value": world * Bs * T / (ms_s * 1e-3), "unit": "sequence-steps/s"}
+        xs = us = ls = None
+    xh = uh = None
+    Fn._stream_state.clear()
+
     pk = peaks()
     per_gpu_steps = B * T
     tfl = per_gpu_steps * FLOP_PER_STEP / (ms * 1e-3) / 1e12
@@ -242,17 +461,19 @@ def main():
         kms = [t / n for t in ktimes[:3]]
         dec_tfl = per_gpu_steps * DEC_FLOP_PER_STEP / (kms[1] * 1e-3) / 1e12
         dec = Fn.elbo_decoder_active()
-        traffic = None   # dram bytes per launch of the active decoder kernel from its committed ncu --set full capture
-        tp = os.path.join(ROOT, "profiles", "r1d_decoder_traffic.json" if dec == "tc5" else "r1_fused_decoder_traffic.json")
+        traffic = traffic_src = None   # dram bytes per launch of the active decoder kernel: NOT measured in this run,
+        # read back from the committed `ncu --set full` capture of the same kernel and shape
+        tp = os.path.join(ROOT, "profiles", TRAFFIC_FILE if dec == "tc5" else "r1_fused_decoder_traffic.json")
         if os.path.exists(tp):
             tj = json.load(open(tp))
             if tj.get("B") == B and tj.get("T") == T:
                 traffic = tj["dram_bytes_per_launch"]
+                traffic_src = "from committed ncu capture profiles/" + os.path.basename(tp) + " (not measured in this run)"
         roofline = {
             "kernel": ("vhmm::fz::decoder_tc5_kernel (decoder fwd+bwd + NLL; 64x64 k=3 GEMMs on tcgen05, 2xFP16 split)"
                        if dec == "tc5" else "vhmm::fz::decoder_kernel (decoder fwd+bwd + NLL, 3xTF32 mma.sync)"),
             "bound": "tensor", "achieved": dec_tfl, "peak": pk["bf16"], "unit": "TFLOP/s",
-            "frac": dec_tfl / pk["bf16"], "traffic": traffic,
+            "frac": dec_tfl / pk["bf16"], "traffic": traffic, "traffic_source": traffic_src,
             "peak_source": pk["src"] + " bf16 dense cuBLAS, sustained (kernel timed inside a long step)",
             "algorithmic_flop_per_step": DEC_FLOP_PER_STEP, "ms_per_launch": kms[1],
             "share_of_step": kms[1] / ms,
@@ -271,8 +492,9 @@ def main():
     line = {
         "metric": "sequence-steps/sec for ELBO fwd+bwd", "value": value, "unit": "sequence-steps/s",
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"cfg2: VAE_HMM(5,64,K=3,32,u_dim=4) ELBO fwd+bwd, B={B} per GPU x {world} GPU, T={T}, lengths=T",
+                   "warmup_note": "at least 3 warm-up steps are always run (timing rules); `warmup` is the count used",
                    "parallelism": f"batch-sharded x{world}, 1 NCCL all-reduce/step" if world > 1 else "single GPU",
                    "l2": f"inputs ({(B * T * 36) / 1e9:.2f} GB/GPU) larger than the 126 MB L2; no flush needed",
                    "elbo_impl": Fn.elbo_active_impl(model._dims), "decoder_kernel": Fn.elbo_decoder_active()},
@@ -280,10 +502,20 @@ def main():
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "loss": loss_val,
     }
+    if strong is not None:
+        line["strong_scaling"] = strong
+    x = u = None                      # free the cfg-2 batch before the stage workloads (cfg 3 needs ~30 GB)
+    model.zero_grad(set_to_none=True)
+    Fn.release_workspaces()
+    torch.cuda.empty_cache()
+    if not args.no_stages:
+        if world == 1:
+            line["stages"] = run_stages(torch, V, Fn, model, dev, local, pk, quick=args.quick_stages)
+        line["decode_cfg3"] = run_decode_sharded(torch, dist, V, Fn, model, dev, local, world, rank, pk)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        rate, dt, n = cpu_reference_step_rate(args.cpu_batch, T, 3, 1)
-        line["cpu_baseline"] = {"value": rate, "unit": "sequence-steps/s", "cores": n, "kind": "port",
-                                "sample": f"B={args.cpu_batch} of {B} sequences, T={T}, 3 timed iterations of the oracle port (torch CPU fp32) of compute_loss+backward"}
+        rate, dt, n, kind = cpu_reference_step_rate(args.cpu_batch, T, 3, 1)
+        line["cpu_baseline"] = {"value": rate, "unit": "sequence-steps/s", "cores": n, "kind": kind,
+                                "sample": f"B={args.cpu_batch} of {B} sequences, T={T}, 3 timed iterations of compute_loss+backward: {CPU_KIND_TEXT[kind]}"}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
