@@ -207,3 +207,26 @@ def brute_force(log_pi, log_A, log_b):
             gamma[t, z[t]] += wz
     n_best = int((scores == m).sum())
     return ll, gamma, np.array(paths[int(np.argmax(scores))]), m, n_best
+
+
+# ---------------------------------------------------------------------------------------
+# the reference tree's one HMM statement: the TFP "weather" model quoted in hmm.py:11-42
+# ---------------------------------------------------------------------------------------
+def weather_model(T=7, obs=None):
+    """hmm.py:11-42 in this file's conventions: K=2 (0 cold, 1 hot), pi=[.8,.2] (:11), A=[[.7,.3],[.2,.8]]
+    (:17-18, stationary -> broadcast over t), emissions N(0,5) / N(15,10) (:25), num_steps=7 (:34).
+    ``obs`` (T,) gives log_b[t,k] = log N(obs_t; mu_k, sigma_k); obs=None gives log_b = 0 (no evidence), for which
+    the posterior gamma is the prior state marginal pi A^t and the log-likelihood is log 1 = 0.
+    Returns (log_pi (2,), log_A (1,T,2,2), log_b (1,T,2), state means (2,)).  Closed forms the snippet states:
+    E[x_t] = 15 P(hot at t) = 9 - 6 * 2^-t  ("elements approach 9.0", :38); stationary P(hot) = .3/(.3+.2) = .6."""
+    pi = np.array([0.8, 0.2])
+    A = np.array([[0.7, 0.3], [0.2, 0.8]])
+    mu = np.array([0.0, 15.0])
+    sd = np.array([5.0, 10.0])
+    log_A = np.broadcast_to(np.log(A), (1, T, 2, 2)).copy()
+    if obs is None:
+        log_b = np.zeros((1, T, 2))
+    else:
+        o = np.asarray(obs, np.float64)[:, None]
+        log_b = (-0.5 * ((o - mu) / sd) ** 2 - np.log(sd) - 0.5 * math.log(2 * math.pi))[None]
+    return np.log(pi), log_A, log_b, mu

@@ -320,3 +320,122 @@ def test_fused_loglik_from_raw_inputs():
         assert np.allclose(ll.cpu().numpy()[live], ll64[live], rtol=TOL, atol=1e-6)
         assert torch.allclose(ll, ll_2, rtol=TOL, atol=1e-6)
         assert torch.allclose(ll_full, ll_full2, rtol=TOL, atol=1e-6)
+
+
+def test_weather_model_of_reference_hmm_py_on_the_kernels():
+    """The reference tree's only HMM statement (hmm.py:11-42, TFP weather model) on the device kernels: with no
+    evidence (log_b = 0) gamma is the prior marginal, so the daily mean temperatures are 9 - 6*2^-t ("approach 9.0",
+    hmm.py:38) and the log-likelihood is 0; log_prob(zeros(7)) (hmm.py:42) = -19.855635 (enumeration over the 2^7
+    paths, tests/test_oracle_hmm.py); every recursion kernel family is run (thread-per-sequence K=2, sweep, scan,
+    Viterbi), also on a batch of copies so that several warps / CTAs take part."""
+    import vhmm_b200.functional as Fn
+    for T in (7, 8, 64):        # 7: hmm.py's num_steps; 8 / 64: shapes the one-pass warp kernel takes (T*K % 4 == 0)
+        lp, lA, lb0, mu = H.weather_model(T)
+        rep = 37
+        L = np.full(rep, T, np.int64)
+        d = dev(lp.astype(np.float32), np.repeat(lA, rep, 0).astype(np.float32), np.repeat(lb0, rep, 0).astype(np.float32), L)
+        closed = 9.0 - 6.0 * 0.5 ** np.arange(T)
+        for variant in ("auto", "sweep"):
+            Fn.hmm_posterior_select(variant)
+            try:
+                ll, gamma, xi = Fn.hmm_posterior(*d)
+            finally:
+                Fn.hmm_posterior_select("auto")
+            means = gamma.double().cpu().numpy() @ mu
+            assert np.abs(means - closed[None]).max() <= 1e-5 * 9.0, (T, variant)
+            assert float(ll.abs().max()) <= 1e-5
+            # xi[t] = P(z_{t-1}=i) A[i,j]: rows of the joint sum to the previous marginal
+            assert np.abs(xi[:, 1:].sum(-1).cpu().numpy() - gamma[:, :-1].cpu().numpy()).max() <= 1e-5
+        obs = np.zeros(T)
+        lp, lA, lb, _ = H.weather_model(T, obs=obs)
+        g64, _, ll64 = H.posteriors(lp, lA, lb, np.array([T]))
+        if T == 7:
+            assert abs(ll64[0] - (-19.855635)) < 2e-6
+        d = dev(lp.astype(np.float32), np.repeat(lA, rep, 0).astype(np.float32), np.repeat(lb, rep, 0).astype(np.float32), L)
+        for ll in (Fn.hmm_forward(*d), Fn.hmm_scan(*d), Fn.hmm_posterior(*d)[0], Fn.hmm_decode(*d)[2]):
+            assert np.allclose(ll.cpu().numpy(), ll64[0], rtol=TOL)
+        path, score = Fn.viterbi(*d)
+        assert int(path.max()) == 0            # a week at 0 degrees decodes as all cold
+        assert np.abs(Fn.hmm_posterior(*d)[1].cpu().numpy() - g64).max() <= TOL
+
+
+@pytest.mark.parametrize("K,T,B", [(32, 300, 5), (32, 1024, 3), (16, 513, 4), (7, 128, 9)])
+def test_generic_k_kernels_long_sequences(K, T, B):
+    """hmm_generic.cuh (one warp per sequence, lane = state; the only path of the scaled config K = 32) on sequences
+    of cfg-5 length: log-lik / alpha / gamma / xi vs the float64 oracle, Viterbi bit-exact incl. quantised ties."""
+    import vhmm_b200.functional as Fn
+    lp, la, lb, L = rand_hmm(B, T, K, seed=K + T)
+    L[1] = T // 2 + 1
+    g64, x64, ll64 = H.posteriors(lp, la, lb, L)
+    d = dev(lp, la, lb, L)
+    ll, alpha = Fn.hmm_forward(*d, want_alpha=True)
+    a64, _ = H.forward(lp, la, lb, L)
+    valid = np.arange(T)[None, :] < L[:, None]
+    assert np.allclose(ll.cpu().numpy(), ll64, rtol=TOL)
+    assert np.abs(alpha.cpu().numpy() - a64)[valid].max() <= TOL * np.abs(a64).max()
+    ll2, gamma, xi = Fn.hmm_posterior(*d)
+    assert np.allclose(ll2.cpu().numpy(), ll64, rtol=TOL)
+    assert np.abs(gamma.cpu().numpy() - g64).max() <= TOL
+    assert np.abs(xi.cpu().numpy() - x64).max() <= TOL
+    ll3 = Fn.hmm_scan(*d)
+    assert np.allclose(ll3.cpu().numpy(), ll64, rtol=TOL)
+    laq, lbq, lpq = np.round(la * 2) / 2, np.round(lb * 2) / 2, np.round(lp * 2) / 2
+    po, so = H.viterbi(lpq, laq, lbq, L, dtype=np.float32)
+    dq = dev(lpq.astype(np.float32), laq.astype(np.float32), lbq.astype(np.float32), L)
+    path, sc = Fn.viterbi(*dq)
+    assert np.array_equal(path.cpu().numpy(), po) and np.array_equal(sc.cpu().numpy(), so)
+    p2, g2, _ = Fn.hmm_decode(*dq)
+    assert np.array_equal(p2.cpu().numpy(), po)
+
+
+def test_scan_with_structural_zeros_and_sticky_chains():
+    """left-to-right chains (log_A = -inf below the diagonal) and near-absorbing states with sharply
+    discriminative emissions over T >= 512: chunk / segment products lose whole rows; the scan must stay finite and
+    equal the per-step-normalised sequential kernel and the float64 oracle."""
+    import vhmm_b200.functional as Fn
+    r = np.random.default_rng(9)
+    for K, T in ((3, 1024), (4, 768), (3, 4096)):
+        B = 6
+        A = r.random((B, T, K, K)) + 0.05
+        A[:3] *= np.triu(np.ones((K, K)))[None, None]                  # left-to-right: structural zeros
+        A[3:] = 1e-6 * A[3:] + np.eye(K)[None, None]                   # sticky: stay with prob ~ 1 - 2e-6
+        A /= A.sum(-1, keepdims=True)
+        with np.errstate(divide="ignore"):
+            la = np.log(A).astype(np.float32)
+        lb = (r.normal(size=(B, T, K)) * 6.0 - 8.0).astype(np.float32)
+        lp = np.log(np.full(K, 1.0 / K)).astype(np.float32)
+        L = np.array([T, T - 3, 600, T, 513, T], np.int64)
+        _, ll64 = H.forward(lp, la, lb, L)
+        assert np.isfinite(ll64).all()
+        d = dev(lp, la, lb, L)
+        ll_seq = Fn.hmm_forward(*d).cpu().numpy()
+        ll_scan = Fn.hmm_scan(*d).cpu().numpy()
+        ll_chk = Fn.hmm_scan(*d, want_alpha=True)[0].cpu().numpy()
+        assert np.isfinite(ll_scan).all() and np.isfinite(ll_chk).all()
+        assert np.allclose(ll_seq, ll64, rtol=TOL)
+        assert np.allclose(ll_scan, ll64, rtol=TOL), (K, T, ll_scan, ll64)
+        assert np.allclose(ll_chk, ll64, rtol=TOL), (K, T, ll_chk, ll64)
+
+
+def test_viterbi_path_pointer_at_odd_offset():
+    """a C-ABI caller may pass a uint8 path pointer that is not 4-byte aligned (a slice of a larger
+    buffer) with T % 4 == 0; the kernels must fall back to byte stores instead of faulting."""
+    import ctypes
+    import vhmm_b200 as V
+    from vhmm_b200 import functional as Fn, _lib
+    K, T, B = 3, 64, 33
+    lp, la, lb, L = rand_hmm(B, T, K, seed=21)
+    tlp, tla, tlb, tL = dev(lp, la, lb, L)
+    ref_path, _ = Fn.viterbi(tlp, tla, tlb, tL)
+    big = torch.full((B * T + 8,), 7, dtype=torch.uint8, device="cuda")
+    for off in (1, 2, 3):
+        view = big[off:off + B * T]
+        score = torch.empty(B, device="cuda")
+        dk = _lib.Dims(1, 1, K, 1, 1, 1)
+        ws = Fn.workspace(tlb.device, Fn._ws_bytes(_lib.OP_VITERBI, dk, B, T))
+        _lib.check(V.lib().vhmm_viterbi(Fn._ptr(tlp), Fn._ptr(tla), Fn._ptr(tlb), Fn._ptr(tL), B, T, K,
+                                        ctypes.c_void_p(view.data_ptr()), Fn._ptr(score), Fn._ptr(ws), ws.numel(),
+                                        Fn._stream(tlb.device)), "vhmm_viterbi")
+        torch.cuda.synchronize()
+        assert torch.equal(view.view(B, T), ref_path)
+        assert int(big[off - 1]) == 7 and int(big[off + B * T]) == 7

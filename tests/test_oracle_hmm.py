@@ -91,3 +91,22 @@ def test_scan_matches_sequential():
     _, ll = H.forward(lp, la, lb, L)
     for chunk in (1, 4, 16):
         assert np.allclose(H.scan_loglik(lp, la, lb, L, chunk=chunk), ll, rtol=1e-12, atol=1e-10)
+
+
+def test_weather_model_of_reference_hmm_py():
+    """The reference's only HMM statement (hmm.py:11-42, a TFP doc snippet): marginal means 9 - 6*2^-t ("approach
+    9.0", :38) and log_prob(zeros(7)) (:42) by enumeration over the 2^7 paths."""
+    lp, lA, lb0, mu = H.weather_model(7)
+    L = np.array([7])
+    gamma, _, ll = H.posteriors(lp, lA, lb0, L)
+    assert abs(ll[0]) < 1e-14                                    # no evidence: log 1
+    means = gamma[0] @ mu
+    assert np.allclose(means, 9.0 - 6.0 * 0.5 ** np.arange(7), atol=1e-13)
+    assert np.allclose(means, [3.0, 6.0, 7.5, 8.25, 8.625, 8.8125, 8.90625])
+    lp, lA, lb, _ = H.weather_model(7, obs=np.zeros(7))
+    _, _, ll = H.posteriors(lp, lA, lb, L)
+    ll_bf, gamma_bf, path_bf, best, n_best = H.brute_force(lp, lA[0], lb[0])
+    assert abs(ll[0] - ll_bf) < 1e-13
+    assert abs(ll[0] - (-19.855635)) < 2e-6                      # value of model.log_prob(zeros(7)), checked by enumeration
+    path, score = H.viterbi(lp, lA, lb, L, dtype=np.float64)
+    assert (path[0] == 0).all() and n_best == 1 and (path_bf == 0).all()   # a week at 0 degrees is a cold week
