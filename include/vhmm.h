@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define VHMM_VERSION 103 /* major*100 + minor */
+#define VHMM_VERSION 104 /* major*100 + minor */
 #define VHMM_NUM_PARAMS 18
 #define VHMM_PAD_STATE 255 /* Viterbi path value for t >= lengths[b] */
 
@@ -73,7 +73,9 @@ enum {
   VHMM_OP_HMM_DECODE = 8,
   VHMM_OP_HMM_SCAN = 9,
   VHMM_OP_EMISSION_TABLE = 10,
-  VHMM_OP_HMM_INPUTS = 11
+  VHMM_OP_HMM_INPUTS = 11,
+  VHMM_OP_HMM_PARAM_GRADS = 12,
+  VHMM_OP_TRANSITION_PROBS = 13
 };
 
 int vhmm_version(void);
@@ -99,6 +101,15 @@ int vhmm_encoder_fwd(const vhmm_dims* dims, const vhmm_params* params, const flo
 int vhmm_prior_fwd(const vhmm_dims* dims, const vhmm_params* params, const float* u, int64_t B,
                    int64_t T, float* log_pi, float* log_A, void* workspace,
                    size_t workspace_bytes, void* stream);
+
+/* Transition PROBABILITIES A = exp(log_A) = softmax rows of Prior.forward (VQ_VAE_HMM_fixed.py:68-69): the
+ * (B,T,K,K) tensor the reference's consumers take as `transition_matrix` / `trans_matrix` / `transition_probs`
+ * and index with [:, -1] (regime_utilities.py:42-53, delta_hedger.py:167-183, loss_functions.py:128-147;
+ * VQ_VAE_HMM_fixed.py:214-228 regime_aware_sharpe_loss).  u (B,U,T) -> trans_probs (B,T,K,K), rows sum to 1.
+ * Workspace: VHMM_OP_TRANSITION_PROBS. */
+int vhmm_transition_probs(const vhmm_dims* dims, const vhmm_params* params, const float* u, int64_t B,
+                          int64_t T, float* trans_probs, void* workspace, size_t workspace_bytes,
+                          void* stream);
 
 /* Decoder.forward, VQ_VAE_HMM_fixed.py:81-90.  q (B,K,T) -> mu (B,C,T), logvar (B,C,T). */
 int vhmm_decoder_fwd(const vhmm_dims* dims, const vhmm_params* params, const float* q, int64_t B,
@@ -219,6 +230,20 @@ int vhmm_hmm_posterior(const float* log_pi, const float* log_A, const float* log
                        const int64_t* lengths, int64_t B, int64_t T, int64_t K, float* loglik,
                        float* gamma, float* xi, void* workspace, size_t workspace_bytes,
                        void* stream);
+/* B.3, last sentence: the beta-recursion gradient chained to the 18 parameters.  For
+ * loss = sum_b w[b] * loglik[b]  (w = d loss / d loglik, device float (B); the exact-HMM loss hmm_nll uses
+ * w = -1/B) and the posterior pair (gamma, xi) of vhmm_hmm_posterior on the inputs vhmm_hmm_inputs /
+ * vhmm_prior_fwd + vhmm_emission_logprob produced from (x, u):  grads (flat, vhmm_param_count floats, the layout
+ * of vhmm_elbo's) is OVERWRITTEN with d loss / d params -- through the row log-softmax and the transition MLP
+ * (VQ_VAE_HMM_fixed.py:68-69), through the per-state emission table and the decoder evaluated on the K one-hot
+ * sequences (B.1; :81-90, :118-119), and through log_pi = log_softmax(log_prior) (:54, :71).  The six encoder
+ * tensors do not enter the exact likelihood: their gradients are zero.  Any dims with K <= 32; the batch is
+ * processed in chunks that fit the workspace (minimum: VHMM_OP_HMM_PARAM_GRADS).  This is what the backward of the
+ * torch.autograd.Function behind model.hmm_nll / hmm_log_likelihood calls (train_model call shape :153-157). */
+int vhmm_hmm_param_grads(const vhmm_dims* dims, const vhmm_params* params, const float* x, const float* u,
+                         const float* log_A, const float* gamma, const float* xi, const float* w,
+                         const float* mu_tab, const float* logvar_tab, int64_t B, int64_t T, float* grads,
+                         void* workspace, size_t workspace_bytes, void* stream);
 /* vhmm_hmm_posterior / vhmm_hmm_decode have two builds for K <= 4:
  *   VHMM_POSTERIOR_ONEPASS  one warp per sequence, the sequence resident in shared memory, time
  *                           parallelised over the lanes (chunk products + warp scan): inputs and

@@ -439,3 +439,109 @@ def test_viterbi_path_pointer_at_odd_offset():
         torch.cuda.synchronize()
         assert torch.equal(view.view(B, T), ref_path)
         assert int(big[off - 1]) == 7 and int(big[off + B * T]) == 7
+
+
+def _torch_loglik64(p64, x, u, L, U):
+    """float64, differentiable restatement of oracle/hmm.py (forward recursion B.2 on the oracle's own prior and
+    per-state emission table B.1) in torch, for autograd w.r.t. the 18 parameters."""
+    import math
+    from oracle import elbo as O
+    log_pi, log_A = O.prior(p64, u, U)
+    K = log_pi.shape[0]
+    B, C, T = x.shape
+    q = torch.zeros(K, K, T, dtype=torch.float64)
+    for k in range(K):
+        q[k, k, :] = 1.0
+    mu, lv = O.decode(p64, q)                                            # (K,C,T)
+    v = lv.exp().clamp(min=1e-8)
+    dlt = x[:, None] - mu[None]
+    lb = (-0.5 * (torch.log(2 * math.pi * v)[None] + dlt * dlt / v[None]).sum(dim=2)).permute(0, 2, 1)   # (B,T,K)
+    alpha = log_pi[None] + lb[:, 0]
+    for t in range(1, T):
+        nxt = lb[:, t] + torch.logsumexp(alpha[:, :, None] + log_A[:, t], dim=1)
+        alpha = torch.where((t < L)[:, None], nxt, alpha)
+    return torch.logsumexp(alpha, dim=1)
+
+
+HMM_GRAD_TOL = 1e-5
+
+
+@pytest.mark.parametrize("dims,B,T", [((5, 64, 3, 32, 4, 128), 9, 64),      # base config, fused front end
+                                      ((5, 64, 3, 32, 4, 128), 5, 50),      # T % 4 != 0: Prior + emission kernels, sweep posterior
+                                      ((3, 8, 4, 4, 2, 16), 7, 33),         # small dims, K = 4
+                                      ((4, 16, 6, 8, 3, 32), 6, 40)])       # K = 6: warp-per-sequence recursion kernels
+def test_hmm_nll_backward_reaches_the_18_parameters(dims, B, T):
+    """model.hmm_nll(x,u,lengths).backward(): backward = gamma/xi (beta recursion) -> row log-softmax -> transition MLP
+    -> emission table -> decoder on the one-hot sequences -> log_prior.  Against float64 autograd through the oracle
+    restated in torch: every one of the 18 tensors norm-wise <= 1e-5 (the six encoder tensors are exactly zero)."""
+    import vhmm_b200 as V
+    from oracle import elbo as O
+    C, Hd, K, H2, U, TH = dims
+    p = O.init_params(C, Hd, K, H2, U, TH, seed=11)
+    x, u, L = O.synth_batch(B, C, U, T, seed=B + T, ragged=True, min_len=1)
+    L[1] = 1
+    x = x * 1.5
+    m = V.VAE_HMM(C, Hd, K, H2, u_dim=U, trans_hidden=TH)
+    m.load_state_dict(p)
+    m = m.cuda()
+    w = torch.linspace(-1.0, 2.0, B, dtype=torch.float64)
+    p64 = {k: v.double().requires_grad_(True) for k, v in p.items()}
+    ll64 = _torch_loglik64(p64, x.double(), u.double(), L, U)
+    for mode in ("nll", "weighted"):
+        loss64 = -ll64.mean() if mode == "nll" else (ll64 * w).sum()
+        g64 = torch.autograd.grad(loss64, [p64[k] for k in O.PARAM_ORDER], allow_unused=True, retain_graph=True)
+        m.zero_grad(set_to_none=True)
+        if mode == "nll":
+            loss = m.hmm_nll(x.cuda(), u.cuda(), L)
+        else:
+            ll = m.hmm_log_likelihood(x.cuda(), u.cuda(), L)
+            assert ll.grad_fn is not None
+            assert np.allclose(ll.detach().cpu().numpy(), ll64.detach().numpy(), rtol=TOL)
+            loss = (ll * w.float().cuda()).sum()
+        assert abs(float(loss) - float(loss64)) <= TOL * abs(float(loss64))
+        loss.backward()
+        sd = dict(m.named_parameters())
+        for k, g in zip(O.PARAM_ORDER, g64):
+            got = sd[k].grad
+            assert got is not None, k
+            if k.startswith("encoder."):
+                assert g is None and float(got.abs().max()) == 0.0, k
+                continue
+            den = float(g.norm())
+            err = float((got.double().cpu() - g).norm()) / den
+            assert err <= HMM_GRAD_TOL, (mode, k, err)
+    # the same loop the reference runs (VQ_VAE_HMM_fixed.py:153-157) trains on the exact likelihood
+    opt = torch.optim.Adam(m.parameters(), lr=1e-2)
+    first = None
+    for _ in range(8):
+        opt.zero_grad()
+        loss = m.hmm_nll(x.cuda(), u.cuda(), L)
+        loss.backward()
+        opt.step()
+        first = float(loss) if first is None else first
+    assert float(loss) < first
+
+
+def test_transition_probs_accessor_for_reference_consumers():
+    """(B,T,K,K) = exp(log_A): what regime_utilities.py:42-53 / delta_hedger.py:167-183 / loss_functions.py:128-147 take
+    (they read [:, -1] and torch.diagonal / bmm it with the (B,K) regime probabilities)."""
+    import vhmm_b200 as V
+    from oracle import elbo as O
+    p = O.init_params(5, 64, 3, 32, 4, 128, seed=5)
+    x, u, L = O.synth_batch(6, 5, 4, 37, seed=2)
+    m = V.VAE_HMM(5, 64, 3, 32, u_dim=4)
+    m.load_state_dict(p)
+    m = m.cuda()
+    _, lA64 = O.prior({k: v.double() for k, v in p.items()}, u.double(), 4)
+    with torch.no_grad():
+        A = m.transition_probs(u.cuda())
+        A2 = m.transition_probs(u.permute(0, 2, 1).contiguous().cuda())       # (B,T,U) layout: permute rule :64-65
+        probs = m.get_regime_probs(x.cuda(), u.cuda(), L)
+    assert A.shape == (6, 37, 3, 3) and torch.equal(A, A2)
+    assert np.abs(A.cpu().numpy() - np.exp(lA64.numpy())).max() <= 1e-6
+    assert float((A.sum(-1) - 1).abs().max()) <= 1e-6
+    # the consumer's own expressions (regime_utilities.py:46-47, loss_functions.py:134-136) on our tensors
+    self_transition = torch.diagonal(A[:, -1], dim1=-2, dim2=-1)
+    cur = probs[:, :, -1]
+    assert (cur * self_transition).sum(dim=-1, keepdim=True).shape == (6, 1)
+    assert torch.bmm(cur.unsqueeze(1), A[:, -1, :, :]).shape == (6, 1, 3)

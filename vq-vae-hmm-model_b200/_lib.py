@@ -24,6 +24,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 OP_ENCODER_FWD, OP_PRIOR_FWD, OP_DECODER_FWD, OP_ELBO = 1, 2, 3, 4
 OP_HMM_FORWARD, OP_HMM_POSTERIOR, OP_VITERBI, OP_HMM_DECODE, OP_HMM_SCAN, OP_EMISSION_TABLE = 5, 6, 7, 8, 9, 10
 OP_HMM_INPUTS = 11
+OP_HMM_PARAM_GRADS, OP_TRANSITION_PROBS = 12, 13
 NUM_PARAMS = 18
 PAD_STATE = 255
 ELBO_AUTO, ELBO_LAYERWISE, ELBO_FUSED = 0, 1, 2
@@ -107,6 +108,8 @@ PROTOTYPES = {
     "vhmm_hmm_inputs_supported": (ctypes.c_int, [_DP, _I64]),
     "vhmm_hmm_inputs": (ctypes.c_int, [_DP, _PP, _P, _P, _I64, _I64, _P, _P, _P, _P, _P, _SZ, _P]),
     "vhmm_hmm_loglik_fused": (ctypes.c_int, [_DP, _PP, _P, _P, _P, _P, _I64, _I64, _P, _P, _P, _P, _SZ, _P]),
+    "vhmm_transition_probs": (ctypes.c_int, [_DP, _PP, _P, _I64, _I64, _P, _P, _SZ, _P]),
+    "vhmm_hmm_param_grads": (ctypes.c_int, [_DP, _PP, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64, _P, _P, _SZ, _P]),
     "vhmm_hmm_forward": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P]),
     "vhmm_hmm_posterior": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _SZ, _P]),
     "vhmm_hmm_posterior_select": (ctypes.c_int, [ctypes.c_int]),

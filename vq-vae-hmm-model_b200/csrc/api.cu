@@ -39,7 +39,10 @@ void set_error(const char* fmt, ...) {
 // elbo_layerwise.cu
 size_t layerwise_workspace_bytes(int op, const vhmm_dims& d, int64_t B, int64_t T);
 int layerwise_encoder_fwd(const vhmm_dims&, const vhmm_params&, const float*, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
-int layerwise_prior_fwd(const vhmm_dims&, const vhmm_params&, const float*, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
+int layerwise_prior_fwd(const vhmm_dims&, const vhmm_params&, const float*, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t, int as_probs);
+size_t hmm_param_grads_workspace_bytes(const vhmm_dims& d, int64_t B, int64_t T);
+int hmm_param_grads(const vhmm_dims&, const vhmm_params&, const float*, const float*, const float*, const float*, const float*,
+                    const float*, const float*, const float*, int64_t, int64_t, float*, void*, size_t, cudaStream_t);
 int layerwise_decoder_fwd(const vhmm_dims&, const vhmm_params&, const float*, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
 int layerwise_elbo(const vhmm_dims&, const vhmm_params&, const float*, const float*, const int64_t*, int64_t, int64_t, const double*, double, double*, float*, void*, size_t, cudaStream_t);
 int layerwise_emission_table(const vhmm_dims&, const vhmm_params&, int64_t, float*, float*, void*, size_t, cudaStream_t);
@@ -125,6 +128,10 @@ size_t vhmm_workspace_bytes(int op, const vhmm_dims* dims, int64_t B, int64_t T)
       return hmm_workspace_bytes(op, B, T, dims ? dims->K : 0);
     case VHMM_OP_HMM_INPUTS:
       return dims_ok(dims) ? hmm_inputs_workspace_bytes(*dims, T) : 0;
+    case VHMM_OP_HMM_PARAM_GRADS:
+      return dims_ok(dims) ? hmm_param_grads_workspace_bytes(*dims, B, T) : 0;
+    case VHMM_OP_TRANSITION_PROBS:
+      return dims_ok(dims) ? layerwise_workspace_bytes(VHMM_OP_PRIOR_FWD, *dims, B, T) : 0;
     default:
       if (!dims_ok(dims)) return 0;
       if (op == VHMM_OP_ELBO && elbo_impl_for(*dims) == VHMM_ELBO_FUSED) return fused_workspace_bytes(*dims, B, T);
@@ -145,7 +152,25 @@ int vhmm_prior_fwd(const vhmm_dims* dims, const vhmm_params* params, const float
                    void* stream) {
   ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(u, "u");
   ARG(B > 0 && T > 0, "B,T"); ARG(log_pi && log_A, "outputs"); ARG(workspace, "workspace");
-  return layerwise_prior_fwd(*dims, *params, u, B, T, log_pi, log_A, workspace, workspace_bytes, (cudaStream_t)stream);
+  return layerwise_prior_fwd(*dims, *params, u, B, T, log_pi, log_A, workspace, workspace_bytes, (cudaStream_t)stream, 0);
+}
+
+int vhmm_transition_probs(const vhmm_dims* dims, const vhmm_params* params, const float* u, int64_t B, int64_t T,
+                          float* trans_probs, void* workspace, size_t workspace_bytes, void* stream) {
+  ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(u, "u");
+  ARG(B > 0 && T > 0, "B,T"); ARG(trans_probs, "trans_probs"); ARG(workspace, "workspace");
+  return layerwise_prior_fwd(*dims, *params, u, B, T, nullptr, trans_probs, workspace, workspace_bytes, (cudaStream_t)stream, 1);
+}
+
+int vhmm_hmm_param_grads(const vhmm_dims* dims, const vhmm_params* params, const float* x, const float* u,
+                         const float* log_A, const float* gamma, const float* xi, const float* w, const float* mu_tab,
+                         const float* logvar_tab, int64_t B, int64_t T, float* grads, void* workspace,
+                         size_t workspace_bytes, void* stream) {
+  ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(x && u, "x,u");
+  ARG(log_A && gamma && xi && w, "log_A,gamma,xi,w"); ARG(mu_tab && logvar_tab, "tables");
+  ARG(B > 0 && T > 0, "B,T"); ARG(grads, "grads"); ARG(workspace, "workspace");
+  return hmm_param_grads(*dims, *params, x, u, log_A, gamma, xi, w, mu_tab, logvar_tab, B, T, grads, workspace,
+                         workspace_bytes, (cudaStream_t)stream);
 }
 
 int vhmm_decoder_fwd(const vhmm_dims* dims, const vhmm_params* params, const float* q, int64_t B,

@@ -107,22 +107,24 @@ int layerwise_encoder_fwd(const vhmm_dims& d, const vhmm_params& P, const float*
 
 int layerwise_prior_fwd(const vhmm_dims& d, const vhmm_params& P, const float* u, int64_t B,
                         int64_t T, float* log_pi, float* log_A, void* ws, size_t ws_bytes,
-                        cudaStream_t st) {
+                        cudaStream_t st, int as_probs) {
   VHMM_REQUIRE(d.K <= KMAX, VHMM_E_DIMS, "prior_fwd: K=%d > %d", d.K, KMAX);
   Arena A(ws, ws_bytes);
   const int K2 = d.K * d.K;
   float* a = A.take<float>((size_t)B * d.TH * T);
   float* M = A.take<float>((size_t)B * K2 * T);
   VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "prior_fwd: workspace %zu < %zu", ws_bytes, A.used);
-  log_pi_kernel<<<1, 32, 0, st>>>(P.p[P_LOGPRIOR], log_pi, d.K);
-  VHMM_LAUNCH_CHECK();
+  if (log_pi) {
+    log_pi_kernel<<<1, 32, 0, st>>>(P.p[P_LOGPRIOR], log_pi, d.K);
+    VHMM_LAUNCH_CHECK();
+  }
   int rc;
   if ((rc = launch_conv(u, wview_fwd(P.p[P_T0W], d.U, 1), P.p[P_T0B], nullptr, a, B, d.U, d.TH, T, 1, EPI_RELU, st))) return rc;
   if ((rc = launch_conv(a, wview_fwd(P.p[P_T2W], d.TH, 1), P.p[P_T2B], nullptr, M, B, d.TH, K2, T, 1, EPI_NONE, st))) return rc;
   for (int64_t b0 = 0; b0 < B; b0 += kMaxChunk) {
     int64_t nb = B - b0 < kMaxChunk ? B - b0 : kMaxChunk;
     dim3 g((unsigned)cdiv(T, 128), (unsigned)d.K, (unsigned)nb);
-    logA_out_kernel<<<g, 128, 0, st>>>(M + b0 * K2 * T, log_A + b0 * T * K2, d.K, (int)T);
+    logA_out_kernel<<<g, 128, 0, st>>>(M + b0 * K2 * T, log_A + b0 * T * K2, d.K, (int)T, as_probs);
     VHMM_LAUNCH_CHECK();
   }
   return 0;
@@ -275,6 +277,8 @@ int layerwise_emission_table(const vhmm_dims& d, const vhmm_params& P, int64_t T
   return layerwise_decoder_fwd(d, P, q, d.K, T, mu_tab, logvar_tab, (char*)ws + A.used,
                                ws_bytes - A.used, st);
 }
+
+#include "hmm_grad.cuh"
 
 }  // namespace vhmm
 

@@ -43,7 +43,7 @@ __global__ void row_logsoftmax_kernel(float* __restrict__ M, int K, int T) {
 
 // (B,K*K,T) raw transition logits -> log_A (B,T,K,K) with row log-softmax (public prior()).
 // grid (ceil(T/128), K(i), B); block 128.
-__global__ void logA_out_kernel(const float* __restrict__ M, float* __restrict__ log_A, int K, int T) {
+__global__ void logA_out_kernel(const float* __restrict__ M, float* __restrict__ log_A, int K, int T, int as_probs) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= T) return;
   const int i = blockIdx.y;
@@ -55,7 +55,10 @@ __global__ void logA_out_kernel(const float* __restrict__ M, float* __restrict__
   for (int j = 0; j < K; ++j) s += expf(M[base + (int64_t)j * T] - m);
   const float lse = m + logf(s);
   float* o = log_A + ((b * T + t) * K + i) * (int64_t)K;
-  for (int j = 0; j < K; ++j) o[j] = M[base + (int64_t)j * T] - lse;
+  for (int j = 0; j < K; ++j) {
+    const float v = M[base + (int64_t)j * T] - lse;
+    o[j] = as_probs ? expf(v) : v;      // as_probs: A = exp(log_A), the (B,T,K,K) tensor of regime_utilities.py:42-53
+  }
 }
 
 // log_pi = log_softmax(log_prior)   (K <= KMAX; single warp)

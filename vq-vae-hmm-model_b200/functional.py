@@ -487,3 +487,88 @@ class HmmLogLikFunction(torch.autograd.Function):
         g_A = xi * g[:, None, None, None]
         g_pi = g_b[:, 0, :].sum(dim=0)
         return g_pi, g_A, g_b, None
+
+
+def transition_probs(d: Dims, params, u):
+    """A = exp(log_A) (B,T,K,K), rows summing to 1: the `transition_matrix` / `trans_matrix` / `transition_probs`
+    argument of the reference's consumers (regime_utilities.py:42-53, delta_hedger.py:167-183,
+    loss_functions.py:128-147), which index it with [:, -1].  u in the (B,U,T) layout."""
+    u = _f32c(u); _require_cuda(u)
+    B, U, T = u.shape
+    if U != d.U:
+        raise VhmmError(f"transition_probs: expected u_dim {d.U}, got {U}")
+    P, keep = pack_params(params)
+    out = torch.empty(B, T, d.K, d.K, device=u.device, dtype=torch.float32)
+    with torch.cuda.device(u.device):
+        ws = workspace(u.device, _ws_bytes(_lib.OP_TRANSITION_PROBS, d, B, T))
+        check(_lib.lib().vhmm_transition_probs(ctypes.byref(d), ctypes.byref(P), _ptr(u), B, T, _ptr(out), _ptr(ws),
+                                               ws.numel(), _stream(u.device)), "vhmm_transition_probs")
+    return out
+
+
+HMM_GRAD_WORKSPACE_CAP = 4 << 30   # bytes: the chunked transition-MLP backward takes what it gets
+
+
+def hmm_param_grads(d: Dims, params, x, u, log_A, gamma, xi, w, mu_tab, logvar_tab):
+    """Flat d(sum_b w[b] loglik[b]) / d(18 parameters) from the posterior pair (vhmm_hmm_param_grads)."""
+    x = _f32c(x); u = _f32c(u); w = _f32c(w)
+    _require_cuda(x, u, log_A, gamma, xi, w, mu_tab, logvar_tab)
+    B, C, T = x.shape
+    P, keep = pack_params(params)
+    grads = torch.empty(param_count(d), device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device):
+        need = _ws_bytes(_lib.OP_HMM_PARAM_GRADS, d, B, T)
+        per_seq = T * (2 * d.TH + d.K * d.K) * 4
+        ws = workspace(x.device, max(need, min(HMM_GRAD_WORKSPACE_CAP, need + per_seq * B)))
+        check(_lib.lib().vhmm_hmm_param_grads(ctypes.byref(d), ctypes.byref(P), _ptr(x), _ptr(u), _ptr(_f32c(log_A)),
+                                              _ptr(_f32c(gamma)), _ptr(_f32c(xi)), _ptr(w), _ptr(_f32c(mu_tab)),
+                                              _ptr(_f32c(logvar_tab)), B, T, _ptr(grads), _ptr(ws), ws.numel(),
+                                              _stream(x.device)), "vhmm_hmm_param_grads")
+    return grads
+
+
+def hmm_inputs_any(d: Dims, params, x, u, mu_tab, logvar_tab):
+    """(log_A, log_b) from raw (x, u (B,U,T)): the fused front end when the dims allow, else Prior + emission kernels."""
+    fused = hmm_inputs_fused(d, params, x, u, mu_tab, logvar_tab)
+    if fused is not None:
+        return fused
+    _, log_A = prior_fwd(d, params, u)
+    return log_A, emission_logprob(x, mu_tab, logvar_tab)
+
+
+class HmmParamLogLikFunction(torch.autograd.Function):
+    """loglik (B) = log p(x_b | u_b) of the exact HMM as a function of the 18 PARAMETERS: forward =
+    front end + forward/backward recursion; backward = the beta-recursion gradient (gamma, xi: already produced by the
+    forward pass) chained through the row log-softmax, the transition MLP, the emission table / decoder and log_pi to
+    the parameters (vhmm_hmm_param_grads).  This is north_star's "torch.autograd.Function whose backward is the
+    beta-recursion gradient kernel"; model.hmm_nll(...).backward() and train_model-style loops go through it."""
+
+    @staticmethod
+    def forward(ctx, d, x, u, lengths, *params):
+        x = _f32c(x); u = _f32c(u)
+        B, C, T = x.shape
+        want = any(ctx.needs_input_grad)
+        mu_tab, lv_tab = emission_table(d, params, T, x.device)
+        log_pi = torch.log_softmax(params[6].detach().float(), dim=0)        # VQ_VAE_HMM_fixed.py:54 (K values)
+        log_A, log_b = hmm_inputs_any(d, params, x, u, mu_tab, lv_tab)
+        ctx.want = want
+        if want:
+            ll, gamma, xi = hmm_posterior(log_pi, log_A, log_b, lengths, want_xi=True)
+            del log_b
+            ctx.d = d
+            ctx.params = [p.detach() for p in params]
+            ctx.shapes = [tuple(p.shape) for p in params]
+            ctx.offsets = param_offsets(d)
+            ctx.save_for_backward(x, u, log_A, gamma, xi, mu_tab, lv_tab)
+        else:
+            ll = hmm_forward(log_pi, log_A, log_b, lengths)
+        return ll
+
+    @staticmethod
+    def backward(ctx, g):
+        if not ctx.want:
+            raise VhmmError("hmm log-likelihood gradients were not computed (forward ran without grad)")
+        x, u, log_A, gamma, xi, mu_tab, lv_tab = ctx.saved_tensors
+        flat = hmm_param_grads(ctx.d, ctx.params, x, u, log_A, gamma, xi, g.to(torch.float32).contiguous(), mu_tab, lv_tab)
+        outs = [flat[ctx.offsets[i]:ctx.offsets[i + 1]].view(shp) for i, shp in enumerate(ctx.shapes)]
+        return (None, None, None, None, *outs)

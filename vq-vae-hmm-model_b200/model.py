@@ -88,8 +88,9 @@ class VAE_HMM(nn.Module):
     ``compute_loss`` is differentiable w.r.t. the 18 parameters (fused forward+backward kernel
     behind a torch.autograd.Function).  ``encode/decode/prior/forward`` are inference ops and
     return tensors without grad_fn.  Additions (absent from the reference):
-    ``hmm_inputs``, ``hmm_log_likelihood``, ``hmm_nll``, ``get_regime_probs`` (the method
-    api.py:18 calls), ``viterbi``, ``decode_regimes``, ``argmax_regimes``.
+    ``hmm_inputs``, ``hmm_log_likelihood``, ``hmm_nll`` (differentiable w.r.t. the 18 parameters),
+    ``get_regime_probs`` (the method api.py:18 calls), ``transition_probs``, ``viterbi``, ``decode_regimes``,
+    ``argmax_regimes``.
     """
 
     def __init__(self, input_dim, hidden_dim, K, hidden_dim2, u_dim=None, trans_hidden=128):
@@ -193,10 +194,29 @@ class VAE_HMM(nn.Module):
         log_b = Fn.emission_logprob(x, mu_tab, lv_tab)
         return log_pi, log_A, log_b
 
+    def _u_layout(self, u):
+        """(B,U,T) view of u under the permute rule of VQ_VAE_HMM_fixed.py:64-65"""
+        if u is None:
+            raise ValueError('u required for non-stationary transitions')
+        if u.dim() != 3:
+            raise VhmmError(f"expected a 3-d u, got {tuple(u.shape)}")
+        if u.shape[1] != self._dims.U:
+            if u.shape[2] != self._dims.U:
+                raise VhmmError(f"no axis of u{tuple(u.shape)} equals u_dim={self._dims.U}")
+            u = u.permute(0, 2, 1)
+        return u
+
     def hmm_log_likelihood(self, x, u, lengths=None):
-        """log p(x | u) per sequence (B.2).  One fused kernel from raw (x, u) when the dims allow
-        (nothing materialised), else front end + forward recursion."""
-        if u.dim() == 3 and u.shape[1] == self._dims.U and x.numel() > 0:
+        """log p(x | u) per sequence (B.2).  With autograd enabled and parameters that require grad the result is
+        differentiable w.r.t. the 18 parameters: backward = the beta-recursion gradient kernel chained to the
+        parameters (functional.HmmParamLogLikFunction).  Without grad: one fused kernel from raw (x, u) when the dims
+        allow (nothing materialised), else front end + forward recursion."""
+        u = self._u_layout(u)
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()) and x.numel() > 0:
+            if lengths is not None:
+                lengths = lengths.to(device=x.device, dtype=torch.int64)
+            return Fn.HmmParamLogLikFunction.apply(self._dims, x, u, lengths, *self._params())
+        if x.numel() > 0:
             mu_tab, lv_tab = Fn.emission_table(self._dims, self._params(), x.shape[2], x.device)
             log_pi = torch.log_softmax(self.prior.log_prior.detach().float(), dim=0)
             ll = Fn.hmm_loglik_fused(self._dims, self._params(), log_pi, x, u, lengths, mu_tab, lv_tab)
@@ -206,8 +226,15 @@ class VAE_HMM(nn.Module):
         return Fn.hmm_forward(log_pi, log_A, log_b, lengths)
 
     def hmm_nll(self, x, u, lengths=None):
-        """-mean_b loglik[b] (B.2)."""
+        """-mean_b loglik[b] (B.2): the exact-HMM training loss.  ``model.hmm_nll(x, u, lengths).backward()`` leaves
+        the gradients of all 18 parameters in ``.grad`` (the six encoder tensors get zeros: the exact likelihood
+        does not use the encoder), so the reference's loop (VQ_VAE_HMM_fixed.py:153-157) can train on it."""
         return -self.hmm_log_likelihood(x, u, lengths).mean()
+
+    def transition_probs(self, u):
+        """exp(log_A) as (B,T,K,K) -- the transition tensor regime_utilities.py:42-53, delta_hedger.py:167-183 and
+        loss_functions.py:128-147 take next to the (B,K,T) regime probabilities (they read [:, -1])."""
+        return Fn.transition_probs(self._dims, self._params(), self._u_layout(u))
 
     def get_regime_probs(self, x, u, lengths=None):
         """Smoothed posteriors gamma as (B,K,T) -- the layout every reference consumer of
