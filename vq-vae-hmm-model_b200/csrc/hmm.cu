@@ -2,6 +2,7 @@
 // between the tuned small-K kernels (hmm_small.cuh, hmm_scan.cuh) and the any-K warp kernels
 // (hmm_generic.cuh), workspace carving, emission log-probabilities.
 #include "hmm_generic.cuh"
+#include "hmm_wide.cuh"
 #include "hmm_scan.cuh"
 #include "hmm_warp.cuh"
 #include <atomic>
@@ -39,7 +40,7 @@ size_t hmm_workspace_bytes(int op, int64_t B, int64_t T, int64_t K) {
     case VHMM_OP_HMM_DECODE: return stash + psi + 512;
     case VHMM_OP_HMM_SCAN:
       return align_up((size_t)B * nck * K * K * 4, 256) + 2 * align_up((size_t)B * nck * 8, 256) +
-             align_up((size_t)B * nck * K * 4, 256) + 1024;
+             align_up((size_t)B * nck * K * 4, 256) + align_up((size_t)B * 4, 256) + 1024;
     default: return 0;
   }
 }
@@ -177,6 +178,19 @@ static hs::Args base_args(const float* log_pi, const float* A, const float* Bm, 
   return a;
 }
 
+// K > 4: the warp-per-sequence kernels of hmm_wide.cuh, instantiated for lane counts 8 / 16 / 32
+// (VHMM_WIDE=generic selects the first-round log-space kernels of hmm_generic.cuh, kept for comparison)
+static bool wide_allowed() {
+  static const int v = [] { const char* e = getenv("VHMM_WIDE"); return (e && e[0] == 'g') ? 0 : 1; }();
+  return v != 0;
+}
+#define DISPATCH_KP(K, expr)                                         \
+  do {                                                               \
+    if ((K) <= 8) { constexpr int KP = 8; expr; }                    \
+    else if ((K) <= 16) { constexpr int KP = 16; expr; }             \
+    else { constexpr int KP = 32; expr; }                            \
+  } while (0)
+
 int hmm_forward(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B,
                 int64_t T, int64_t K, float* loglik, float* alpha, cudaStream_t st) {
   // log-likelihood only: the time-parallel warp kernel (hmm_warp.cuh) without its sweeps
@@ -191,7 +205,14 @@ int hmm_forward(const float* log_pi, const float* A, const float* Bm, const int6
     DISPATCH_K(K, (rc = launch_fwd_small<KK, true, false>(a, st)));
     return rc;
   }
+  VHMM_REQUIRE(K <= 32, VHMM_E_DIMS, "hmm_forward: K=%lld > 32", (long long)K);
   const int wpb = 4;
+  if (wide_allowed()) {
+    DISPATCH_KP(K, (hx::fwd_kernel<KP><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
+                       log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, alpha, nullptr)));
+    VHMM_LAUNCH_CHECK();
+    return 0;
+  }
   hg::fwd_kernel<false><<<(unsigned)cdiv(B, wpb), wpb * 32, 0, st>>>(log_pi, A, Bm, lengths, B, (int)T, (int)K,
                                                                      loglik, alpha, 0, nullptr, nullptr, nullptr);
   VHMM_LAUNCH_CHECK();
@@ -217,7 +238,22 @@ int hmm_posterior(const float* log_pi, const float* A, const float* Bm, const in
     DISPATCH_K(K, (rc = launch_bwd_small<KK>(a, st)));
     return rc;
   }
+  VHMM_REQUIRE(K <= 32, VHMM_E_DIMS, "hmm_posterior: K=%lld > 32", (long long)K);
   const int wpb = 4;
+  if (wide_allowed()) {
+    DISPATCH_KP(K, (hx::fwd_kernel<KP><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
+                       log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, nullptr, stash)));
+    VHMM_LAUNCH_CHECK();
+    if (xi) {
+      DISPATCH_KP(K, (hx::bwd_kernel<KP, true><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
+                         A, Bm, lengths, B, (int)T, (int)K, stash, gamma, xi)));
+    } else {
+      DISPATCH_KP(K, (hx::bwd_kernel<KP, false><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
+                         A, Bm, lengths, B, (int)T, (int)K, stash, gamma, nullptr)));
+    }
+    VHMM_LAUNCH_CHECK();
+    return 0;
+  }
   hg::fwd_kernel<false><<<(unsigned)cdiv(B, wpb), wpb * 32, 0, st>>>(log_pi, A, Bm, lengths, B, (int)T, (int)K,
                                                                      loglik, stash, 1, nullptr, nullptr, nullptr);
   VHMM_LAUNCH_CHECK();
@@ -239,7 +275,14 @@ int hmm_viterbi(const float* log_pi, const float* A, const float* Bm, const int6
     DISPATCH_K(K, (rc = launch_fwd_small<KK, false, true>(a, st)));
     return rc;
   }
+  VHMM_REQUIRE(K <= 32, VHMM_E_DIMS, "hmm_viterbi: K=%lld > 32", (long long)K);
   const int wpb = 4;
+  if (wide_allowed()) {
+    DISPATCH_KP(K, (hx::vit_kernel<KP><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
+                       log_pi, A, Bm, lengths, B, (int)T, (int)K, psi, path, score)));
+    VHMM_LAUNCH_CHECK();
+    return 0;
+  }
   hg::fwd_kernel<true><<<(unsigned)cdiv(B, wpb), wpb * 32, 0, st>>>(log_pi, A, Bm, lengths, B, (int)T, (int)K,
                                                                     nullptr, nullptr, 0, psi, path, score);
   VHMM_LAUNCH_CHECK();
@@ -293,9 +336,13 @@ static int scan_small(hs::Args a, hs::ScanArgs sa, float* alpha, int64_t B, cuda
   hs::scan_carry_kernel<K><<<(unsigned)B, 32, 0, st>>>(a, sa);
   VHMM_LAUNCH_CHECK();
   if (alpha) {
-    a.vin = sa.vin; a.ll_in = sa.ll_in; a.alpha_log = alpha; a.full = 1; a.loglik = nullptr;
-    return launch_fwd_small<K, true, false>(a, st);
+    hs::Args a3 = a;
+    a3.vin = sa.vin; a3.ll_in = sa.ll_in; a3.alpha_log = alpha; a3.full = 1; a3.loglik = nullptr;
+    int rc = launch_fwd_small<K, true, false>(a3, st);
+    if (rc) return rc;
   }
+  hs::scan_fixup_kernel<K><<<(unsigned)B, 32, 0, st>>>(a, sa, alpha);   // sequences whose products vanished only
+  VHMM_LAUNCH_CHECK();
   return 0;
 }
 
@@ -309,6 +356,7 @@ int hmm_scan(const float* log_pi, const float* A, const float* Bm, const int64_t
   sa.Pscale = ar.take<double>((size_t)B * nck);
   sa.vin = ar.take<float>((size_t)B * nck * K);
   sa.ll_in = ar.take<double>((size_t)B * nck);
+  sa.suspect = ar.take<int>((size_t)B);
   sa.loglik = loglik;
   VHMM_REQUIRE(ar.ok, VHMM_E_WORKSPACE, "hmm_scan: workspace %zu < %zu", ws_bytes, ar.used);
   // log-likelihood only, T a multiple of the segment length: segment products by the one-pass kernel (one warp per
@@ -332,6 +380,8 @@ int hmm_scan(const float* log_pi, const float* A, const float* Bm, const int64_t
     hs::Args c = base_args(log_pi, A, Bm, lengths, B, T, K);
     c.nrows = B * nseg; c.rows_per_seq = (int)nseg; c.CH = (int)SEG_T;
     DISPATCH_K(K, (hs::scan_carry_kernel<KK><<<(unsigned)B, 32, 0, st>>>(c, sa), rc = 0));
+    VHMM_LAUNCH_CHECK();
+    DISPATCH_K(K, (hs::scan_fixup_kernel<KK><<<(unsigned)B, 32, 0, st>>>(c, sa, nullptr), rc = 0));   // vanished products only
     VHMM_LAUNCH_CHECK();
     return rc;
   }

@@ -22,7 +22,17 @@ struct ScanArgs {
   float* vin;        // (nrows, K)
   double* ll_in;     // (nrows)
   float* loglik;     // (B)
+  int* suspect;      // (B) set to 1 by the carry scan when a product it needed had vanished (see scan_fixup_kernel)
 };
+
+// A product of transfer matrices is carried with ONE scale for the whole K x K matrix.  With structural zeros
+// (log_A = -inf: left-to-right chains) or near-absorbing states under sharply discriminative emissions the ROWS of
+// a long product differ by more than fp32's range, and the rows that matter for a given start vector can underflow
+// while the largest row stays O(1).  Everything the scan does is exact up to powers of two until a value drops below
+// 2^-126 of the largest entry, so the condition is detectable: the row-weighted sum `cs` the carry scan divides by
+// falls below 2^-100.  Such sequences are marked and recomputed by scan_fixup_kernel with the per-step-normalised
+// sequential recursion (which only ever carries a vector).
+constexpr float SCAN_VANISH = 7.8886090522101181e-31f;   // 2^-100
 
 // P <- normalise(P * M), *scale += log(sum)
 template <int K>
@@ -177,7 +187,8 @@ __global__ void __launch_bounds__(32) scan_carry_kernel(Args a, ScanArgs sa) {
     ll = (double)(logf(cs) + m);
   }
   const int64_t L = a.lengths[b];
-  if (L <= 0) { if (lane == 0) sa.loglik[b] = 0.f; return; }
+  if (L <= 0) { if (lane == 0) { sa.loglik[b] = 0.f; if (sa.suspect) sa.suspect[b] = 0; } return; }
+  bool vanished = false;
   if (lane > 0) {
     float w[K], cs = 0.f;
 #pragma unroll
@@ -187,6 +198,7 @@ __global__ void __launch_bounds__(32) scan_carry_kernel(Args a, ScanArgs sa) {
       for (int i = 0; i < K; ++i) acc = fmaf(v[i], X[i * K + j], acc);
       w[j] = acc; cs += acc;
     }
+    vanished |= (c_lo < c_hi) && !(cs >= SCAN_VANISH);
     cs = fmaxf(cs, 1.17549435e-38f);
 #pragma unroll
     for (int j = 0; j < K; ++j) v[j] = w[j] / cs;
@@ -205,14 +217,93 @@ __global__ void __launch_bounds__(32) scan_carry_kernel(Args a, ScanArgs sa) {
       for (int i = 0; i < K; ++i) acc = fmaf(v[i], sa.Pmat[(row0 + c) * K * K + i * K + j], acc);
       w[j] = acc; cs += acc;
     }
+    // (only chunks that hold a valid transition count: beyond the length the products are identities)
+    vanished |= ((int64_t)c * a.CH < L) && !(cs >= SCAN_VANISH);
     cs = fmaxf(cs, 1.17549435e-38f);
 #pragma unroll
     for (int j = 0; j < K; ++j) v[j] = w[j] / cs;
     ll += sa.Pscale[row0 + c] + (double)logf(cs);
   }
+  const bool any_vanished = __any_sync(0xffffffffu, vanished);
+  if (lane == 0 && sa.suspect) sa.suspect[b] = any_vanished ? 1 : 0;
   // the lane that owns the last chunk holds the total
   const int last_lane = (nck - 1) / per;
   if (lane == last_lane) sa.loglik[b] = (float)ll;
+}
+
+
+// Sequences marked by the carry scan: per-step-normalised forward recursion (B.2), one warp per sequence.  The lanes
+// form the transfer matrices of 32 consecutive steps (coalesced loads, exps in parallel), lane 0 applies them in
+// order.  Writes loglik and, if requested, the log-space alpha rows (carried unchanged beyond the length).
+template <int K>
+__global__ void __launch_bounds__(32) scan_fixup_kernel(Args a, ScanArgs sa, float* __restrict__ alpha) {
+  const int64_t b = blockIdx.x;
+  if (!sa.suspect[b]) return;
+  __shared__ float Pm[32][K * K + 1];
+  __shared__ float mb[32];
+  const int lane = threadIdx.x;
+  const int T = (int)a.T;
+  int64_t L64 = a.lengths[b];
+  const int L = (int)(L64 < 0 ? 0 : (L64 > T ? T : L64));
+  const float* Ab = a.A + b * (int64_t)T * K * K;
+  const float* Bb = a.Bm + b * (int64_t)T * K;
+  float v[K];
+  double ll = 0.0;
+  if (lane == 0) {
+    float m = -INFINITY, cs = 0.f;
+#pragma unroll
+    for (int j = 0; j < K; ++j) { v[j] = a.log_pi[j] + Bb[j]; m = fmaxf(m, v[j]); }
+#pragma unroll
+    for (int j = 0; j < K; ++j) { v[j] = expf(v[j] - m); cs += v[j]; }
+#pragma unroll
+    for (int j = 0; j < K; ++j) v[j] /= cs;
+    ll = (double)m + (double)logf(cs);
+    if (alpha)
+#pragma unroll
+      for (int j = 0; j < K; ++j) alpha[(b * T) * K + j] = logf(v[j]) + (float)ll;
+  }
+  for (int tb = 1; tb < L; tb += 32) {
+    const int t = tb + lane;
+    if (t < L) {
+      float lb[K], m = -INFINITY;
+#pragma unroll
+      for (int j = 0; j < K; ++j) { lb[j] = Bb[(int64_t)t * K + j]; m = fmaxf(m, lb[j]); }
+#pragma unroll
+      for (int i = 0; i < K; ++i)
+#pragma unroll
+        for (int j = 0; j < K; ++j) Pm[lane][i * K + j] = expf(Ab[(int64_t)t * K * K + i * K + j] + lb[j] - m);
+      mb[lane] = m;
+    }
+    __syncwarp();
+    if (lane == 0) {
+      const int n = min(32, L - tb);
+      for (int s = 0; s < n; ++s) {
+        float w[K], cs = 0.f;
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+          float acc = 0.f;
+#pragma unroll
+          for (int i = 0; i < K; ++i) acc = fmaf(v[i], Pm[s][i * K + j], acc);
+          w[j] = acc; cs += acc;
+        }
+        const float inv = 1.f / cs;          // cs == 0: the data has probability zero -> -inf, as the oracle gives
+#pragma unroll
+        for (int j = 0; j < K; ++j) v[j] = w[j] * inv;
+        ll += (double)mb[s] + (double)logf(cs);
+        if (alpha)
+#pragma unroll
+          for (int j = 0; j < K; ++j) alpha[(b * T + tb + s) * K + j] = logf(v[j]) + (float)ll;
+      }
+    }
+    __syncwarp();
+  }
+  if (lane == 0) {
+    sa.loglik[b] = (L > 0) ? (float)ll : 0.f;
+    if (alpha)
+      for (int t = (L > 0 ? L : 1); t < T; ++t)
+#pragma unroll
+        for (int j = 0; j < K; ++j) alpha[(b * T + t) * K + j] = logf(v[j]) + (float)ll;
+  }
 }
 
 }  // namespace hs

@@ -1,0 +1,289 @@
+// hmm_wide.cuh -- exact-HMM recursions for 4 < K <= 32 (the scaled config's K = 32): one WARP per sequence,
+// lane = state, HBM-bound by design (4(K^2+K) = 4,224 B per step at K = 32).
+//
+// Replaces the first-round correctness kernels of hmm_generic.cuh, which walked log-space recursions straight out
+// of global memory (two dependent sweeps over the K rows per step, no prefetch: 13 us per step and warp at K = 32,
+// 4..10 % of the HBM roofline).  Here:
+//   * lane j reads COLUMN j of log_A_t (row i = 32 consecutive floats over the lanes: every load is one coalesced
+//     128-byte line) into registers, one step AHEAD of the recursion (register double buffer), so the recursion's
+//     dependent chain never waits for HBM;
+//   * sum-product runs in scaled linear space exactly like the small-K kernels: P_t[i,j] = exp(log_A_t[i,j] +
+//     log_b_t[j] - max_j log_b_t) (the K exps per lane are independent of the recursion), alpha_hat_t =
+//     normalise(alpha_hat_{t-1} P_t) with K shuffle-broadcasts + FMAs on four accumulators, log-normalisers summed
+//     in double.  No logsumexp chain, no cancellation (all terms non-negative);
+//   * backward: beta_hat_{t-1}[i] = sum_j P_t[i,j] beta_hat_t[j] needs ROW sums of what the lanes hold as columns:
+//     each lane scales its column by beta_hat_t[j], the warp writes the K x K tile to shared memory (pitch K+1) and
+//     lane i sums row i -- conflict-free both ways; xi_t[i,j] = alpha_hat_{t-1}[i] P_t[i,j] beta_hat_t[j] / Z is
+//     formed in the column layout, i.e. stored with coalesced 128-byte rows;
+//   * Viterbi keeps the oracle's operation order (one rounded add per candidate, strict '>' scanning i upwards, one
+//     rounded add of log_b): bit-exact paths; back-pointers one byte per state, back-tracking in blocks of 32 steps
+//     staged through shared memory (the dependent chain runs on LDS latency, not on HBM latency).
+// Maths: SURVEY.md Appendix B.2-B.4; conventions of oracle/hmm.py.
+#pragma once
+#include "common.cuh"
+
+namespace vhmm {
+namespace hx {
+
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr int WPB = 4;   // warps per CTA
+
+__device__ __forceinline__ float wmax(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float wsum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// column `lane` of log_A_t (K x K row-major at At) -> a[i], i < K; -inf for i >= K or lanes >= K
+template <int KP>
+__device__ __forceinline__ void load_col(const float* __restrict__ At, int K, int lane, bool on, float (&a)[KP]) {
+#pragma unroll
+  for (int i = 0; i < KP; ++i) a[i] = (on && i < K) ? __ldcs(At + i * K + lane) : -INFINITY;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// forward: loglik (B); optional log-space alpha (B,T,K) (carried unchanged for t >= L, B.2) and/or the
+// normalised linear alpha_hat (B,T,K) (stash for bwd_kernel)
+// ---------------------------------------------------------------------------------------------------------
+template <int KP>
+__global__ void __launch_bounds__(WPB * 32)
+fwd_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const float* __restrict__ Bm,
+           const int64_t* __restrict__ lengths, int64_t nB, int T, int K, float* __restrict__ loglik,
+           float* __restrict__ alpha, float* __restrict__ ahat) {
+  const int lane = threadIdx.x & 31;
+  const int64_t b = (int64_t)blockIdx.x * WPB + (threadIdx.x >> 5);
+  if (b >= nB) return;
+  const int64_t L64 = lengths[b];
+  const int L = (int)(L64 < 0 ? 0 : (L64 > T ? T : L64));
+  const bool on = lane < K;
+  const int KK = K * K;
+  const float* Ab = A + b * (int64_t)T * KK;
+  const float* Bb = Bm + b * (int64_t)T * K;
+  float v = 0.f;
+  double ll = 0.0;
+  if (L > 0) {
+    const float x = on ? log_pi[lane] + Bb[lane] : -INFINITY;
+    const float m = wmax(x);
+    v = on ? ex2((x - m) * LOG2E) : 0.f;
+    const float s = wsum(v);
+    v *= 1.f / s;
+    ll = (double)m + (double)logf(s);
+    if (on) {
+      if (alpha) alpha[(b * T) * K + lane] = logf(v) + (float)ll;
+      if (ahat) ahat[(b * T) * K + lane] = v;
+    }
+  }
+  float an[KP], bn = -INFINITY;
+  if (L > 1) {
+    load_col<KP>(Ab + KK, K, lane, on, an);
+    bn = on ? __ldcs(Bb + K + lane) : -INFINITY;
+  }
+  for (int t = 1; t < L; ++t) {
+    float ac[KP];
+#pragma unroll
+    for (int i = 0; i < KP; ++i) ac[i] = an[i];
+    const float bc = bn;
+    if (t + 1 < L) {   // next step's inputs are in flight while this step computes
+      load_col<KP>(Ab + (int64_t)(t + 1) * KK, K, lane, on, an);
+      bn = on ? __ldcs(Bb + (int64_t)(t + 1) * K + lane) : -INFINITY;
+    }
+    const float mb = wmax(bc);
+    const float cj = on ? (bc - mb) * LOG2E : -INFINITY;
+    float w0 = 0.f, w1 = 0.f, w2 = 0.f, w3 = 0.f;
+#pragma unroll
+    for (int i = 0; i < KP; ++i) {
+      const float p = ex2(fmaf(ac[i], LOG2E, cj));          // 0 for i >= K, lanes >= K and structural zeros
+      const float vi = __shfl_sync(0xffffffffu, v, i);
+      if ((i & 3) == 0) w0 = fmaf(vi, p, w0);
+      else if ((i & 3) == 1) w1 = fmaf(vi, p, w1);
+      else if ((i & 3) == 2) w2 = fmaf(vi, p, w2);
+      else w3 = fmaf(vi, p, w3);
+    }
+    const float w = on ? (w0 + w1) + (w2 + w3) : 0.f;
+    const float s = wsum(w);
+    v = w * (1.f / s);
+    ll += (double)mb + (double)logf(s);
+    if (on) {
+      if (alpha) alpha[(b * T + t) * K + lane] = logf(v) + (float)ll;
+      if (ahat) ahat[(b * T + t) * K + lane] = v;
+    }
+  }
+  if (lane == 0 && loglik) loglik[b] = (L > 0) ? (float)ll : 0.f;
+  if (alpha && on) {
+    const float carried = logf(v) + (float)ll;
+    for (int t = (L > 0 ? L : 0); t < T; ++t) alpha[(b * T + t) * K + lane] = carried;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// backward: gamma (B,T,K) and, if XI, xi (B,T,K,K) from the alpha_hat stash (zeros for t >= L; xi[:,0] = 0)
+// ---------------------------------------------------------------------------------------------------------
+template <int KP, bool XI>
+__global__ void __launch_bounds__(WPB * 32)
+bwd_kernel(const float* __restrict__ A, const float* __restrict__ Bm, const int64_t* __restrict__ lengths,
+           int64_t nB, int T, int K, const float* __restrict__ ahat, float* __restrict__ gamma,
+           float* __restrict__ xi) {
+  __shared__ float tr[WPB][KP][KP + 1];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int64_t b = (int64_t)blockIdx.x * WPB + wib;
+  if (b >= nB) return;
+  const int64_t L64 = lengths[b];
+  const int L = (int)(L64 < 0 ? 0 : (L64 > T ? T : L64));
+  const bool on = lane < K;
+  const int KK = K * K;
+  const float* Ab = A + b * (int64_t)T * KK;
+  const float* Bb = Bm + b * (int64_t)T * K;
+  const float* ah = ahat + b * (int64_t)T * K;
+  float* gm = gamma + b * (int64_t)T * K;
+  float* xb = XI ? xi + b * (int64_t)T * KK : nullptr;
+  // steps beyond the length (and xi of step 0): zeros
+  for (int64_t e = (int64_t)L * K + lane; e < (int64_t)T * K; e += 32) gm[e] = 0.f;
+  if (XI) {
+    for (int64_t e = (int64_t)L * KK + lane; e < (int64_t)T * KK; e += 32) xb[e] = 0.f;
+    if (L > 0) for (int e = lane; e < KK; e += 32) xb[e] = 0.f;
+  }
+  if (L <= 0) return;
+  float (*mytr)[KP + 1] = tr[wib];
+  float be = on ? 1.f : 0.f;                      // beta_hat_{L-1} (any positive scale: gamma / xi are normalised per step)
+  float an[KP], bn = -INFINITY, apn = 0.f;
+  float at = on ? ah[(int64_t)(L - 1) * K + lane] : 0.f;
+  if (L > 1) {
+    load_col<KP>(Ab + (int64_t)(L - 1) * KK, K, lane, on, an);
+    bn = on ? __ldcs(Bb + (int64_t)(L - 1) * K + lane) : -INFINITY;
+    apn = on ? ah[(int64_t)(L - 2) * K + lane] : 0.f;
+  }
+  for (int t = L - 1; t >= 0; --t) {
+    {
+      const float g = at * be;
+      const float sg = wsum(g);
+      if (on) gm[(int64_t)t * K + lane] = g * (1.f / sg);
+    }
+    if (t == 0) break;
+    float ac[KP];
+#pragma unroll
+    for (int i = 0; i < KP; ++i) ac[i] = an[i];
+    const float bc = bn, ap = apn;
+    if (t >= 2) {
+      load_col<KP>(Ab + (int64_t)(t - 1) * KK, K, lane, on, an);
+      bn = on ? __ldcs(Bb + (int64_t)(t - 1) * K + lane) : -INFINITY;
+      apn = on ? ah[(int64_t)(t - 2) * K + lane] : 0.f;
+    }
+    const float mb = wmax(bc);
+    const float cj = on ? (bc - mb) * LOG2E : -INFINITY;
+    float q[KP];                                   // q[i] = P_t[i, lane] * beta_hat_t[lane]
+#pragma unroll
+    for (int i = 0; i < KP; ++i) q[i] = ex2(fmaf(ac[i], LOG2E, cj)) * be;
+    if (XI) {
+      float zs = 0.f;
+#pragma unroll
+      for (int i = 0; i < KP; ++i) zs = fmaf(__shfl_sync(0xffffffffu, ap, i), q[i], zs);
+      const float iz = 1.f / wsum(zs);
+      float* xr = xb + (int64_t)t * KK;
+#pragma unroll
+      for (int i = 0; i < KP; ++i) {
+        const float ai = __shfl_sync(0xffffffffu, ap, i);
+        if (on && i < K) xr[i * K + lane] = ai * q[i] * iz;
+      }
+    }
+    // row sums through shared memory: tile[i][j] = q_j[i]; lane i sums row i
+    __syncwarp();
+    if (lane < KP) {
+#pragma unroll
+      for (int i = 0; i < KP; ++i) mytr[i][lane] = q[i];
+    }
+    __syncwarp();
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    if (lane < KP) {
+#pragma unroll
+      for (int j = 0; j < KP; j += 4) {
+        s0 += mytr[lane][j]; s1 += mytr[lane][j + 1]; s2 += mytr[lane][j + 2]; s3 += mytr[lane][j + 3];
+      }
+    }
+    const float bs = on ? (s0 + s1) + (s2 + s3) : 0.f;
+    be = bs * (1.f / wmax(bs));                    // keep beta_hat in range (power-free rescale; any positive factor)
+    at = ap;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Viterbi (B.4): psi (B,T,K) uint8 workspace, path (B,T) uint8 (255 for t >= L), score (B) or null
+// ---------------------------------------------------------------------------------------------------------
+template <int KP>
+__global__ void __launch_bounds__(WPB * 32)
+vit_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const float* __restrict__ Bm,
+           const int64_t* __restrict__ lengths, int64_t nB, int T, int K, uint8_t* __restrict__ psi,
+           uint8_t* __restrict__ path, float* __restrict__ score) {
+  __shared__ uint8_t pb[WPB][32 * KP];
+  __shared__ uint8_t ob[WPB][32];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int64_t b = (int64_t)blockIdx.x * WPB + wib;
+  if (b >= nB) return;
+  const int64_t L64 = lengths[b];
+  const int L = (int)(L64 < 0 ? 0 : (L64 > T ? T : L64));
+  const bool on = lane < K;
+  const int KK = K * K;
+  const float* Ab = A + b * (int64_t)T * KK;
+  const float* Bb = Bm + b * (int64_t)T * K;
+  uint8_t* ps = psi + b * (int64_t)T * K;
+  uint8_t* pr = path + b * (int64_t)T;
+  for (int t = L + lane; t < T; t += 32) pr[t] = VHMM_PAD_STATE;
+  float dl = (L > 0 && on) ? __fadd_rn(log_pi[lane], Bb[lane]) : -INFINITY;
+  float an[KP], bn = -INFINITY;
+  if (L > 1) {
+    load_col<KP>(Ab + KK, K, lane, on, an);
+    bn = on ? __ldcs(Bb + K + lane) : -INFINITY;
+  }
+  for (int t = 1; t < L; ++t) {
+    float ac[KP];
+#pragma unroll
+    for (int i = 0; i < KP; ++i) ac[i] = an[i];
+    const float bc = bn;
+    if (t + 1 < L) {
+      load_col<KP>(Ab + (int64_t)(t + 1) * KK, K, lane, on, an);
+      bn = on ? __ldcs(Bb + (int64_t)(t + 1) * K + lane) : -INFINITY;
+    }
+    float best = __fadd_rn(__shfl_sync(0xffffffffu, dl, 0), ac[0]);
+    int arg = 0;
+#pragma unroll
+    for (int i = 1; i < KP; ++i) {
+      const float c = __fadd_rn(__shfl_sync(0xffffffffu, dl, i), ac[i]);
+      if (i < K && c > best) { best = c; arg = i; }      // strict: the lowest i wins ties
+    }
+    dl = on ? __fadd_rn(bc, best) : -INFINITY;
+    if (on) ps[(int64_t)t * K + lane] = (uint8_t)arg;
+  }
+  const float m = wmax(dl);
+  const unsigned ball = __ballot_sync(0xffffffffu, on && dl == m);
+  int state = ball ? __ffs(ball) - 1 : 0;             // lowest index attaining the max
+  if (lane == 0 && score) score[b] = (L > 0) ? m : 0.f;
+  __syncwarp();                                        // psi written by the lanes is visible to the warp
+  for (int hi = L - 1; hi >= 0; hi -= 32) {
+    const int lo = hi - 31 > 0 ? hi - 31 : 0;
+    const int n = hi - lo + 1;
+    for (int e = lane; e < n * K; e += 32) pb[wib][e] = ps[(int64_t)lo * K + e];
+    __syncwarp();
+    if (lane == 0) {
+      for (int t = hi; t >= lo; --t) {
+        ob[wib][t - lo] = (uint8_t)state;
+        if (t >= 1) state = pb[wib][(t - lo) * K + state];
+      }
+    }
+    __syncwarp();
+    state = __shfl_sync(0xffffffffu, state, 0);
+    if (lane < n) pr[lo + lane] = ob[wib][lane];
+    __syncwarp();
+  }
+}
+
+}  // namespace hx
+}  // namespace vhmm
