@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define VHMM_VERSION 104 /* major*100 + minor */
+#define VHMM_VERSION 105 /* major*100 + minor */
 #define VHMM_NUM_PARAMS 18
 #define VHMM_PAD_STATE 255 /* Viterbi path value for t >= lengths[b] */
 
@@ -75,7 +75,8 @@ enum {
   VHMM_OP_EMISSION_TABLE = 10,
   VHMM_OP_HMM_INPUTS = 11,
   VHMM_OP_HMM_PARAM_GRADS = 12,
-  VHMM_OP_TRANSITION_PROBS = 13
+  VHMM_OP_TRANSITION_PROBS = 13,
+  VHMM_OP_FORWARD = 14
 };
 
 int vhmm_version(void);
@@ -95,6 +96,15 @@ size_t vhmm_workspace_bytes(int op, const vhmm_dims* dims, int64_t B, int64_t T)
 int vhmm_encoder_fwd(const vhmm_dims* dims, const vhmm_params* params, const float* x,
                      int64_t B, int64_t T, float* logits, float* q, void* workspace,
                      size_t workspace_bytes, void* stream);
+
+/* VAE_HMM.forward, VQ_VAE_HMM_fixed.py:139-143: x (B,C,T) -> q = softmax(encoder(x)) (B,K,T), (mu, logvar) =
+ * decoder(q) (B,C,T) each [, logits (B,K,T) when non-NULL].  For the dims of the FUSED path (see vhmm_elbo_select)
+ * this -- and vhmm_encoder_fwd / vhmm_decoder_fwd -- is ONE persistent tile kernel (conv2 layers on tcgen05, every
+ * activation on chip: 20 B/step read, 52 B/step written for forward()); other dims run the layer kernels.
+ * Workspace: VHMM_OP_FORWARD. */
+int vhmm_forward(const vhmm_dims* dims, const vhmm_params* params, const float* x, int64_t B, int64_t T,
+                 float* logits, float* q, float* mu, float* logvar, void* workspace, size_t workspace_bytes,
+                 void* stream);
 
 /* Prior.forward, VQ_VAE_HMM_fixed.py:59-71.  u (B,U,T) (the layout collate_fn produces; the
  * Python wrapper applies the permute rule of :64-65) -> log_pi (K), log_A (B,T,K,K). */

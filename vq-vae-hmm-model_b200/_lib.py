@@ -24,7 +24,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 OP_ENCODER_FWD, OP_PRIOR_FWD, OP_DECODER_FWD, OP_ELBO = 1, 2, 3, 4
 OP_HMM_FORWARD, OP_HMM_POSTERIOR, OP_VITERBI, OP_HMM_DECODE, OP_HMM_SCAN, OP_EMISSION_TABLE = 5, 6, 7, 8, 9, 10
 OP_HMM_INPUTS = 11
-OP_HMM_PARAM_GRADS, OP_TRANSITION_PROBS = 12, 13
+OP_HMM_PARAM_GRADS, OP_TRANSITION_PROBS, OP_FORWARD = 12, 13, 14
 NUM_PARAMS = 18
 PAD_STATE = 255
 ELBO_AUTO, ELBO_LAYERWISE, ELBO_FUSED = 0, 1, 2
@@ -91,6 +91,7 @@ PROTOTYPES = {
     "vhmm_param_offsets": (ctypes.c_int, [_DP, ctypes.POINTER(_I64)]),
     "vhmm_workspace_bytes": (_SZ, [ctypes.c_int, _DP, _I64, _I64]),
     "vhmm_encoder_fwd": (ctypes.c_int, [_DP, _PP, _P, _I64, _I64, _P, _P, _P, _SZ, _P]),
+    "vhmm_forward": (ctypes.c_int, [_DP, _PP, _P, _I64, _I64, _P, _P, _P, _P, _P, _SZ, _P]),
     "vhmm_prior_fwd": (ctypes.c_int, [_DP, _PP, _P, _I64, _I64, _P, _P, _P, _SZ, _P]),
     "vhmm_decoder_fwd": (ctypes.c_int, [_DP, _PP, _P, _I64, _I64, _P, _P, _P, _SZ, _P]),
     "vhmm_elbo": (ctypes.c_int, [_DP, _PP, _P, _P, _P, _I64, _I64, _P, _DBL, _P, _P, _P, _SZ, _P]),

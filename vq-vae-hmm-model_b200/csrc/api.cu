@@ -51,6 +51,9 @@ int launch_argmax(const float* q, int64_t B, int64_t K, int64_t T, int64_t* out,
 bool fused_supported(const vhmm_dims& d);
 size_t fused_workspace_bytes(const vhmm_dims& d, int64_t B, int64_t T);
 int fused_elbo(const vhmm_dims&, const vhmm_params&, const float*, const float*, const int64_t*, int64_t, int64_t, const double*, double, double*, float*, void*, size_t, cudaStream_t);
+size_t fused_forward_workspace_bytes(const vhmm_dims& d);
+int fused_forward(const vhmm_dims&, const vhmm_params&, const float*, const float*, int64_t, int64_t, float*, float*, float*, float*,
+                  void*, size_t, cudaStream_t);
 int fused_timing_enable(int enable);
 int fused_decoder_select(int variant);
 int fused_decoder_active();
@@ -135,6 +138,11 @@ size_t vhmm_workspace_bytes(int op, const vhmm_dims* dims, int64_t B, int64_t T)
     default:
       if (!dims_ok(dims)) return 0;
       if (op == VHMM_OP_ELBO && elbo_impl_for(*dims) == VHMM_ELBO_FUSED) return fused_workspace_bytes(*dims, B, T);
+      if ((op == VHMM_OP_ENCODER_FWD || op == VHMM_OP_DECODER_FWD || op == VHMM_OP_FORWARD) &&
+          elbo_impl_for(*dims) == VHMM_ELBO_FUSED)
+        return fused_forward_workspace_bytes(*dims);   // the fused tile kernel keeps every activation on chip
+      if (op == VHMM_OP_FORWARD)
+        return layerwise_workspace_bytes(VHMM_OP_ENCODER_FWD, *dims, B, T) + layerwise_workspace_bytes(VHMM_OP_DECODER_FWD, *dims, B, T);
       return layerwise_workspace_bytes(op, *dims, B, T);
   }
 }
@@ -144,7 +152,26 @@ int vhmm_encoder_fwd(const vhmm_dims* dims, const vhmm_params* params, const flo
                      void* stream) {
   ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(x, "x");
   ARG(B > 0 && T > 0, "B,T"); ARG(logits || q, "logits and q both NULL"); ARG(workspace, "workspace");
+  if (elbo_impl_for(*dims) == VHMM_ELBO_FUSED)
+    return fused_forward(*dims, *params, x, nullptr, B, T, logits, q, nullptr, nullptr, workspace, workspace_bytes,
+                         (cudaStream_t)stream);
   return layerwise_encoder_fwd(*dims, *params, x, B, T, logits, q, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int vhmm_forward(const vhmm_dims* dims, const vhmm_params* params, const float* x, int64_t B, int64_t T,
+                 float* logits, float* q, float* mu, float* logvar, void* workspace, size_t workspace_bytes,
+                 void* stream) {
+  ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(x, "x");
+  ARG(B > 0 && T > 0, "B,T"); ARG(q && mu && logvar, "q, mu, logvar"); ARG(workspace, "workspace");
+  if (elbo_impl_for(*dims) == VHMM_ELBO_FUSED)
+    return fused_forward(*dims, *params, x, nullptr, B, T, logits, q, mu, logvar, workspace, workspace_bytes,
+                         (cudaStream_t)stream);
+  const size_t we = layerwise_workspace_bytes(VHMM_OP_ENCODER_FWD, *dims, B, T);
+  VHMM_REQUIRE(workspace_bytes >= we, VHMM_E_WORKSPACE, "vhmm_forward: workspace %zu < %zu", workspace_bytes, we);
+  int rc = layerwise_encoder_fwd(*dims, *params, x, B, T, logits, q, workspace, we, (cudaStream_t)stream);
+  if (rc) return rc;
+  return layerwise_decoder_fwd(*dims, *params, q, B, T, mu, logvar, (char*)workspace + we, workspace_bytes - we,
+                               (cudaStream_t)stream);
 }
 
 int vhmm_prior_fwd(const vhmm_dims* dims, const vhmm_params* params, const float* u, int64_t B,
@@ -178,6 +205,9 @@ int vhmm_decoder_fwd(const vhmm_dims* dims, const vhmm_params* params, const flo
                      void* stream) {
   ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(q, "q");
   ARG(B > 0 && T > 0, "B,T"); ARG(mu && logvar, "outputs"); ARG(workspace, "workspace");
+  if (elbo_impl_for(*dims) == VHMM_ELBO_FUSED)
+    return fused_forward(*dims, *params, nullptr, q, B, T, nullptr, nullptr, mu, logvar, workspace, workspace_bytes,
+                         (cudaStream_t)stream);
   return layerwise_decoder_fwd(*dims, *params, q, B, T, mu, logvar, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 

@@ -955,6 +955,48 @@ struct Launcher {
 
 using CfgBase = Cfg<5, 64, 32, 3, 4, 128>;   // BASELINE.json configs[0..1]
 
+#include "forward_tc5.cuh"
+
+// host side of the fused forward-only kernel: x != null -> encoder half, mu != null -> decoder half
+template <typename CF>
+struct FwdLauncher {
+  static size_t workspace_bytes() { return align_up((size_t)3 * CF::H * 8 * 4, 256) + 256; }
+  template <bool ENC, bool DEC>
+  static int launch(const FwdArgs& fa, const vhmm_params& P, int ncta, cudaStream_t st) {
+    auto k = forward_tc5_kernel<CF, ENC, DEC>;
+    constexpr size_t sm = t5f::Lay<CF, ENC, DEC>::BYTES;
+    static_assert(sm <= 227 * 1024, "forward tile kernel exceeds the shared memory of an SM");
+    static PerDeviceOnce attr_done;
+    if (attr_done.pending()) {
+      VHMM_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+      attr_done.mark();
+    }
+    k<<<ncta, NTH, sm, st>>>(fa, P);
+    VHMM_LAUNCH_CHECK();
+    return 0;
+  }
+  static int run(const vhmm_params& P, const float* x, const float* q_in, int64_t B, int64_t T, float* logits, float* q,
+                 float* mu, float* logvar, void* ws, size_t ws_bytes, int ncta, cudaStream_t st) {
+    Arena A(ws, ws_bytes);
+    float* wfold = A.take<float>(3 * CF::H * 8);
+    VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "fused forward: workspace %zu < %zu", ws_bytes, A.used);
+    FwdArgs fa{};
+    fa.x = x; fa.q_in = q_in; fa.B = B; fa.T = (int)T;
+    fa.tiles_per_seq = (int)cdiv(T, TT);
+    fa.ntiles = B * fa.tiles_per_seq;
+    fa.wfold = wfold; fa.logits = logits; fa.q = q; fa.mu = mu; fa.logvar = logvar;
+    if (fa.ntiles < ncta) ncta = (int)fa.ntiles;
+    const bool enc = x != nullptr, dec = mu != nullptr;
+    if (dec) {
+      fold_kernel<CF><<<(unsigned)cdiv(3 * CF::H * 8, 128), 128, 0, st>>>(P.p[P_D1W], P.p[P_EMB], wfold);
+      VHMM_LAUNCH_CHECK();
+    }
+    if (enc && dec) return launch<true, true>(fa, P, ncta, st);
+    if (enc) return launch<true, false>(fa, P, ncta, st);
+    return launch<false, true>(fa, P, ncta, st);
+  }
+};
+
 }  // namespace fz
 
 static int fused_sm_count() { return device_sm_count(); }   // of the CURRENT device
@@ -995,6 +1037,19 @@ bool fused_supported(const vhmm_dims& d) {
 size_t fused_workspace_bytes(const vhmm_dims& d, int64_t B, int64_t T) {
   if (!fused_supported(d)) return 0;
   return fz::Launcher<fz::CfgBase>::workspace_bytes(B, T, fused_sm_count());
+}
+
+size_t fused_forward_workspace_bytes(const vhmm_dims& d) {
+  return fused_supported(d) ? fz::FwdLauncher<fz::CfgBase>::workspace_bytes() : 0;
+}
+
+// x (B,C,T) -> logits / q (either may be null) [-> mu, logvar]; or q_in (B,K,T) -> mu, logvar when x is null
+int fused_forward(const vhmm_dims& d, const vhmm_params& P, const float* x, const float* q_in, int64_t B, int64_t T,
+                  float* logits, float* q, float* mu, float* logvar, void* ws, size_t ws_bytes, cudaStream_t st) {
+  VHMM_REQUIRE(fused_supported(d), VHMM_E_DIMS, "fused forward: unsupported dims");
+  VHMM_REQUIRE((x != nullptr) != (q_in != nullptr), VHMM_E_ARG, "fused forward: exactly one of x, q_in");
+  VHMM_REQUIRE((mu != nullptr) == (logvar != nullptr), VHMM_E_ARG, "fused forward: mu and logvar come together");
+  return fz::FwdLauncher<fz::CfgBase>::run(P, x, q_in, B, T, logits, q, mu, logvar, ws, ws_bytes, fused_sm_count(), st);
 }
 
 int fused_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, const float* u, const int64_t* lengths,

@@ -117,6 +117,24 @@ def encoder_fwd(d: Dims, params, x, want_q=False, want_logits=True):
     return logits, q
 
 
+def forward_fwd(d: Dims, params, x, want_logits=False):
+    """VAE_HMM.forward (VQ_VAE_HMM_fixed.py:139-143) in one library call: ((mu, logvar), q[, logits])."""
+    x = _f32c(x); _require_cuda(x)
+    B, C, T = x.shape
+    if C != d.C:
+        raise VhmmError(f"forward: expected {d.C} input channels, got {C}")
+    P, keep = pack_params(params)
+    q = torch.empty(B, d.K, T, device=x.device, dtype=torch.float32)
+    logits = torch.empty(B, d.K, T, device=x.device, dtype=torch.float32) if want_logits else None
+    mu = torch.empty(B, d.C, T, device=x.device, dtype=torch.float32)
+    logvar = torch.empty(B, d.C, T, device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device):
+        ws = workspace(x.device, _ws_bytes(_lib.OP_FORWARD, d, B, T))
+        check(_lib.lib().vhmm_forward(ctypes.byref(d), ctypes.byref(P), _ptr(x), B, T, _ptr(logits), _ptr(q), _ptr(mu),
+                                      _ptr(logvar), _ptr(ws), ws.numel(), _stream(x.device)), "vhmm_forward")
+    return (mu, logvar), q, logits
+
+
 def prior_fwd(d: Dims, params, u):
     """u in the (B,U,T) layout."""
     u = _f32c(u); _require_cuda(u)

@@ -168,8 +168,7 @@ class VAE_HMM(nn.Module):
         return sums[0] / norms[0], -sums[1] / norms[1], sums[2] / norms[1]
 
     def forward(self, x):
-        logits, q = Fn.encoder_fwd(self._dims, self._params(), x, want_q=True, want_logits=False)
-        mu, logvar = Fn.decoder_fwd(self._dims, self._params(), q)
+        (mu, logvar), q, _ = Fn.forward_fwd(self._dims, self._params(), x)   # one fused tile kernel for the base dims
         return (mu, logvar), q
 
     # -- regime decoding used all over the reference (backtesting.py:155 etc.) -------------
