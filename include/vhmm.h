@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define VHMM_VERSION 105 /* major*100 + minor */
+#define VHMM_VERSION 106 /* major*100 + minor */
 #define VHMM_NUM_PARAMS 18
 #define VHMM_PAD_STATE 255 /* Viterbi path value for t >= lengths[b] */
 
@@ -76,7 +76,8 @@ enum {
   VHMM_OP_HMM_INPUTS = 11,
   VHMM_OP_HMM_PARAM_GRADS = 12,
   VHMM_OP_TRANSITION_PROBS = 13,
-  VHMM_OP_FORWARD = 14
+  VHMM_OP_FORWARD = 14,
+  VHMM_OP_TRAIN_STEP = 15
 };
 
 int vhmm_version(void);
@@ -203,6 +204,28 @@ int vhmm_adam_step(const vhmm_dims* dims, const vhmm_params_mut* params, const f
                    float* exp_avg, float* exp_avg_sq, double lr, double beta1, double beta2,
                    double eps, int64_t step, const float* grad_scale, double max_norm,
                    float* grad_norm_out, double* scratch, void* stream);
+
+/* f2: ONE whole training step of train_model (VQ_VAE_HMM_fixed.py:153-157) / Trainer.train_epoch (trainer.py:24-34) for the
+ * small-batch regime of BASELINE.json configs[0] (batch 64, T <= 200), where the step is launch-bound: batch assembly
+ * from the resident corpus (vhmm_gather_chunks) + normalisers + ELBO forward/backward (FUSED path) + loss + optional
+ * clip_grad_norm_ + Adam, enqueued by a single call in which EVERY scalar that changes from step to step lives in
+ * DEVICE memory -- so the call can be captured once per (B, T) into a CUDA graph and replayed (the host then issues
+ * one memcpy of (col0, lengths) and one graph launch per step).  `state`: device double[VHMM_TS_COUNT]:
+ *   in : BETA (KL weight of this step), LR, BETA1, BETA2, STEP (number of updates done so far; incremented here)
+ *   out: NORM0/NORM1 (the normalisers :120/:131), SUMS[4] (as vhmm_elbo), LOSS (this step, fp32-rounded like the
+ *        reference's loss tensor), LOSS_SUM / BATCHES (running totals for the epoch mean the reference prints :160;
+ *        the host resets them), STEP_SIZE / BC2_SQRT (Adam bias corrections of this step).
+ * beta1 / beta2 / eps / max_norm are constants of a run (host arguments; beta1/beta2 must equal state[BETA1/2]).
+ * x_buf (B,C,T), u_buf (B,U,T), grads (vhmm_param_count): caller-owned scratch.  Workspace: VHMM_OP_TRAIN_STEP. */
+enum {
+  VHMM_TS_NORM0 = 0, VHMM_TS_NORM1 = 1, VHMM_TS_BETA = 2, VHMM_TS_STEP = 3, VHMM_TS_LR = 4, VHMM_TS_BETA1 = 5,
+  VHMM_TS_BETA2 = 6, VHMM_TS_LOSS = 7, VHMM_TS_LOSS_SUM = 8, VHMM_TS_BATCHES = 9, VHMM_TS_STEP_SIZE = 10,
+  VHMM_TS_BC2_SQRT = 11, VHMM_TS_SUMS = 12, VHMM_TS_COUNT = 16
+};
+int vhmm_train_step(const vhmm_dims* dims, const vhmm_params_mut* params, const float* x_cat, const float* u_cat,
+                    int64_t S_tot, const int64_t* col0, const int64_t* lengths, int64_t B, int64_t T, double* state,
+                    float* exp_avg, float* exp_avg_sq, double beta1, double beta2, double eps, double max_norm,
+                    float* x_buf, float* u_buf, float* grads, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- exact-HMM stages: extensions, absent from the reference ---- */
 

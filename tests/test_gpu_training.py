@@ -191,3 +191,70 @@ def test_serving_infer_matches_reference_outputs():
     assert one == many[0]
     single_last = V.serving.infer(m, x[0, :, :17].tolist())
     assert single_last == many[-1]
+
+
+def test_graphed_train_step_equals_the_eager_fused_step():
+    """f2: the CUDA-graph replay of vhmm_train_step (gather + normalisers + ELBO fwd/bwd + loss + clip + Adam, scalars in
+    device memory) against the eager path (DeviceCorpus.gather + loss_and_flat_grads + FusedAdam.step) for the same
+    `random` stream: same batches, same per-batch losses and the same parameters after an epoch with beta warm-up."""
+    import random
+    import vhmm_b200 as V
+    g = torch.Generator().manual_seed(5)
+    xs = [torch.randn(5, 300, generator=g) for _ in range(12)]
+    us = [torch.randn(4, 300, generator=g) for _ in range(12)]
+    res = {}
+    for mode in ("eager", "graph"):
+        torch.manual_seed(0)
+        m = V.VAE_HMM(5, 64, 3, 32, u_dim=4).cuda()
+        corpus = V.DeviceCorpus(xs, us)
+        loader = V.DeviceChunkLoader(corpus, 16, min_len=20, max_len=120, items_per_epoch=200)   # 13 batches, the last of 8 items
+        random.seed(3)
+        opt = V.FusedAdam(m, lr=2e-3)
+        losses = []
+        if mode == "eager":
+            for ep, beta in enumerate((0.25, 1.0)):
+                for x, u, L in loader:
+                    loss, flat = m.loss_and_flat_grads(x, u, L, beta)
+                    opt.step(flat, max_norm=1.0)
+                    losses.append(float(loss))
+        else:
+            gs = V.training.GraphedTrainStep(m, corpus, 16, max_norm=1.0, optimizer=opt)
+            for ep, beta in enumerate((0.25, 1.0)):
+                gs.reset_epoch_totals()
+                ep_losses = []
+                for tr in loader.iter_triples():
+                    gs.step(*tr, beta=beta)
+                    ep_losses.append(gs.last_loss())
+                assert abs(gs.epoch_mean_loss() - sum(ep_losses) / len(ep_losses)) <= 1e-6 * abs(sum(ep_losses) / len(ep_losses))
+                losses += ep_losses
+            assert len(gs.graphs) >= 2 and opt.step_count == 26
+        res[mode] = (losses, {k: v.detach().clone() for k, v in m.state_dict().items()})
+    le, lg = res["eager"][0], res["graph"][0]
+    assert len(le) == len(lg) == 26
+    assert max(abs(a - b) / abs(a) for a, b in zip(le, lg)) <= 2e-6
+    for k, v in res["eager"][1].items():
+        assert float((v - res["graph"][1][k]).abs().max()) <= 2e-6 * max(1.0, float(v.abs().max())), k
+
+
+def test_train_model_fused_takes_the_graph_path_and_trainer_too(capsys):
+    import random
+    import vhmm_b200 as V
+    g = torch.Generator().manual_seed(6)
+    xs = [torch.randn(5, 250, generator=g) for _ in range(8)]
+    us = [torch.randn(4, 250, generator=g) for _ in range(8)]
+    torch.manual_seed(0)
+    m = V.VAE_HMM(5, 64, 3, 32, u_dim=4).cuda()
+    loader = V.DeviceChunkLoader(V.DeviceCorpus(xs, us), 32, min_len=20, max_len=100, items_per_epoch=320)
+    random.seed(0)
+    n0 = V.lib().vhmm_launch_count()
+    V.train_model_fused(m, loader, num_epochs=3, lr=1e-3)
+    out = capsys.readouterr().out
+    assert out.count("Epoch") == 3 and "Loss:" in out
+    first, last = [float(l.split("Loss:")[1]) for l in out.strip().splitlines()][::2]
+    assert last < first + 1.0
+    # kernels are launched at capture time only: 30 steps replayed from <= ~30 distinct-T graphs
+    assert V.lib().vhmm_launch_count() - n0 <= 30 * 16
+    tr = V.Trainer(m, lr=1e-3, device="cuda")
+    random.seed(1)
+    avg = tr.train_epoch(loader, beta=0.5)
+    assert np.isfinite(avg) and tr._graphed is not None

@@ -24,7 +24,10 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 OP_ENCODER_FWD, OP_PRIOR_FWD, OP_DECODER_FWD, OP_ELBO = 1, 2, 3, 4
 OP_HMM_FORWARD, OP_HMM_POSTERIOR, OP_VITERBI, OP_HMM_DECODE, OP_HMM_SCAN, OP_EMISSION_TABLE = 5, 6, 7, 8, 9, 10
 OP_HMM_INPUTS = 11
-OP_HMM_PARAM_GRADS, OP_TRANSITION_PROBS, OP_FORWARD = 12, 13, 14
+OP_HMM_PARAM_GRADS, OP_TRANSITION_PROBS, OP_FORWARD, OP_TRAIN_STEP = 12, 13, 14, 15
+# vhmm_train_step state slots (include/vhmm.h)
+TS_NORM0, TS_NORM1, TS_BETA, TS_STEP, TS_LR, TS_BETA1, TS_BETA2, TS_LOSS, TS_LOSS_SUM, TS_BATCHES, TS_STEP_SIZE, TS_BC2_SQRT, TS_SUMS, TS_COUNT = \
+    0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 16
 NUM_PARAMS = 18
 PAD_STATE = 255
 ELBO_AUTO, ELBO_LAYERWISE, ELBO_FUSED = 0, 1, 2
@@ -103,6 +106,8 @@ PROTOTYPES = {
     "vhmm_elbo_timing_read": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int)]),
     "vhmm_argmax_regimes": (ctypes.c_int, [_P, _I64, _I64, _I64, _P, _P]),
     "vhmm_gather_chunks": (ctypes.c_int, [_P, _P, _I64, _I64, _I64, _P, _P, _I64, _I64, _P, _P, _P]),
+    "vhmm_train_step": (ctypes.c_int, [_DP, _PP, _P, _P, _I64, _P, _P, _I64, _I64, _P, _P, _P, _DBL, _DBL, _DBL, _DBL, _P, _P, _P, _P,
+                                       _SZ, _P]),
     "vhmm_adam_step": (ctypes.c_int, [_DP, _PP, _P, _P, _P, _DBL, _DBL, _DBL, _DBL, _I64, _P, _DBL, _P, _P, _P]),
     "vhmm_emission_table": (ctypes.c_int, [_DP, _PP, _I64, _P, _P, _P, _SZ, _P]),
     "vhmm_emission_logprob": (ctypes.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P, _P]),

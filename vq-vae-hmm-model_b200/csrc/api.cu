@@ -50,7 +50,7 @@ int launch_argmax(const float* q, int64_t B, int64_t K, int64_t T, int64_t* out,
 // elbo_fused.cu
 bool fused_supported(const vhmm_dims& d);
 size_t fused_workspace_bytes(const vhmm_dims& d, int64_t B, int64_t T);
-int fused_elbo(const vhmm_dims&, const vhmm_params&, const float*, const float*, const int64_t*, int64_t, int64_t, const double*, double, double*, float*, void*, size_t, cudaStream_t);
+int fused_elbo(const vhmm_dims&, const vhmm_params&, const float*, const float*, const int64_t*, int64_t, int64_t, const double*, double, double*, float*, void*, size_t, cudaStream_t, const double* beta_dev);
 size_t fused_forward_workspace_bytes(const vhmm_dims& d);
 int fused_forward(const vhmm_dims&, const vhmm_params&, const float*, const float*, int64_t, int64_t, float*, float*, float*, float*,
                   void*, size_t, cudaStream_t);
@@ -75,6 +75,9 @@ int hmm_loglik_fused(const vhmm_dims&, const vhmm_params&, const float*, const f
 // batch_train.cu
 int gather_chunks(const float*, const float*, int64_t, int64_t, int64_t, const int64_t*, const int64_t*, int64_t, int64_t, float*, float*, cudaStream_t);
 int adam_step(const vhmm_dims&, float* const*, const float*, float*, float*, double, double, double, double, int64_t, const float*, double, float*, double*, cudaStream_t);
+size_t train_step_workspace_bytes(const vhmm_dims& d, int64_t B, int64_t T);
+int train_step(const vhmm_dims&, float* const*, const float*, const float*, int64_t, const int64_t*, const int64_t*, int64_t, int64_t,
+               double*, float*, float*, double, double, double, double, float*, float*, float*, void*, size_t, cudaStream_t);
 
 static std::atomic<int> g_elbo_impl{VHMM_ELBO_AUTO};
 static int elbo_impl_for(const vhmm_dims& d) {
@@ -133,6 +136,8 @@ size_t vhmm_workspace_bytes(int op, const vhmm_dims* dims, int64_t B, int64_t T)
       return dims_ok(dims) ? hmm_inputs_workspace_bytes(*dims, T) : 0;
     case VHMM_OP_HMM_PARAM_GRADS:
       return dims_ok(dims) ? hmm_param_grads_workspace_bytes(*dims, B, T) : 0;
+    case VHMM_OP_TRAIN_STEP:
+      return dims_ok(dims) ? train_step_workspace_bytes(*dims, B, T) : 0;
     case VHMM_OP_TRANSITION_PROBS:
       return dims_ok(dims) ? layerwise_workspace_bytes(VHMM_OP_PRIOR_FWD, *dims, B, T) : 0;
     default:
@@ -218,7 +223,7 @@ int vhmm_elbo(const vhmm_dims* dims, const vhmm_params* params, const float* x, 
   ARG(B > 0 && T > 0, "B,T"); ARG(norms && sums, "norms/sums"); ARG(workspace, "workspace");
   if (elbo_impl_for(*dims) == VHMM_ELBO_FUSED)
     return fused_elbo(*dims, *params, x, u, lengths, B, T, norms, beta, sums, grads, workspace,
-                      workspace_bytes, (cudaStream_t)stream);
+                      workspace_bytes, (cudaStream_t)stream, nullptr);
   return layerwise_elbo(*dims, *params, x, u, lengths, B, T, norms, beta, sums, grads, workspace,
                         workspace_bytes, (cudaStream_t)stream);
 }
@@ -281,6 +286,18 @@ int vhmm_gather_chunks(const float* x_cat, const float* u_cat, int64_t S_tot, in
   ARG(x_cat && u_cat && col0 && lengths && x_out && u_out, "pointers");
   ARG(S_tot > 0 && C > 0 && U > 0 && B >= 0 && T >= 0, "sizes");
   return gather_chunks(x_cat, u_cat, S_tot, C, U, col0, lengths, B, T, x_out, u_out, (cudaStream_t)stream);
+}
+
+int vhmm_train_step(const vhmm_dims* dims, const vhmm_params_mut* params, const float* x_cat, const float* u_cat,
+                    int64_t S_tot, const int64_t* col0, const int64_t* lengths, int64_t B, int64_t T, double* state,
+                    float* exp_avg, float* exp_avg_sq, double beta1, double beta2, double eps, double max_norm,
+                    float* x_buf, float* u_buf, float* grads, void* workspace, size_t workspace_bytes, void* stream) {
+  ARG(dims_ok(dims), "dims"); ARG(params, "params");
+  for (int i = 0; i < VHMM_NUM_PARAMS; ++i) ARG(params->p[i], "params->p[i]");
+  ARG(x_cat && u_cat && S_tot > 0, "corpus"); ARG(col0 && lengths, "col0/lengths"); ARG(B > 0 && T > 0, "B,T");
+  ARG(state && exp_avg && exp_avg_sq, "state"); ARG(x_buf && u_buf && grads, "buffers"); ARG(workspace, "workspace");
+  return train_step(*dims, params->p, x_cat, u_cat, S_tot, col0, lengths, B, T, state, exp_avg, exp_avg_sq, beta1, beta2,
+                    eps, max_norm, x_buf, u_buf, grads, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 int vhmm_adam_step(const vhmm_dims* dims, const vhmm_params_mut* params, const float* grads, float* exp_avg,

@@ -88,7 +88,11 @@ __global__ void __launch_bounds__(256)
 adam_kernel(ParamTable tab, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, int64_t n,
             float step_size /* lr / (1 - beta1^t) */, float w1 /* 1 - beta1 */, float beta2, float w2 /* 1 - beta2 */,
             float bc2_sqrt, float eps, const float* __restrict__ scale, const double* __restrict__ sqnorm,
-            float max_norm, float* __restrict__ gnorm_out) {
+            float max_norm, float* __restrict__ gnorm_out, const double* __restrict__ dyn /* train state or null */) {
+  if (dyn) {   // graph-replayed step: lr / (1 - beta1^t) and sqrt(1 - beta2^t) of THIS step come from device memory
+    step_size = (float)dyn[VHMM_TS_STEP_SIZE];
+    bc2_sqrt = (float)dyn[VHMM_TS_BC2_SQRT];
+  }
   const float s = scale ? *scale : 1.f;
   float coef = 1.f;
   if (sqnorm) {
@@ -131,7 +135,89 @@ int adam_step(const vhmm_dims& d, float* const* params, const float* grads, floa
   if (blocks > 1184) blocks = 1184;
   adam_kernel<<<(unsigned)blocks, 256, 0, st>>>(tab, grads, m, v, n, step_size, (float)(1.0 - beta1), (float)beta2,
                                                (float)(1.0 - beta2), bc2_sqrt, (float)eps, grad_scale,
-                                               need_norm ? scratch : nullptr, (float)max_norm, gnorm_out);
+                                               need_norm ? scratch : nullptr, (float)max_norm, gnorm_out, nullptr);
+  VHMM_LAUNCH_CHECK();
+  return 0;
+}
+
+// ---- f2: the whole small-batch training step with device-resident scalars (graph capture) -------------------
+// one block: normalisers of this batch (VQ_VAE_HMM_fixed.py:120, :131, :135), step counter, Adam bias corrections
+// computed as torch computes them (python floats = double)
+__global__ void __launch_bounds__(256) train_prep_kernel(const int64_t* __restrict__ lengths, int64_t B, int C, int T,
+                                                         double* __restrict__ st) {
+  __shared__ double sh[32];
+  double acc = 0.0;
+  for (int64_t b = threadIdx.x; b < B; b += 256) {
+    int64_t L = lengths[b];
+    L = L < 0 ? 0 : (L > T ? T : L);
+    acc += (double)L;
+  }
+  acc = block_sum(acc, sh);
+  if (threadIdx.x == 0) {
+    const double n0 = acc * (double)C;
+    st[VHMM_TS_NORM0] = n0 < 1.0 ? 1.0 : n0;
+    st[VHMM_TS_NORM1] = (double)B;
+    const double step = st[VHMM_TS_STEP] + 1.0;
+    st[VHMM_TS_STEP] = step;
+    const double bc1 = 1.0 - pow(st[VHMM_TS_BETA1], step), bc2 = 1.0 - pow(st[VHMM_TS_BETA2], step);
+    st[VHMM_TS_STEP_SIZE] = st[VHMM_TS_LR] / bc1;
+    st[VHMM_TS_BC2_SQRT] = sqrt(bc2);
+  }
+}
+// loss = recon + beta (prior - entropy) from the un-normalised sums (:137); fp32 like the reference's loss tensor
+__global__ void train_loss_kernel(double* __restrict__ st) {
+  if (threadIdx.x || blockIdx.x) return;
+  const double* sums = st + VHMM_TS_SUMS;
+  const double recon = sums[0] / st[VHMM_TS_NORM0], prior = -sums[1] / st[VHMM_TS_NORM1], ent = sums[2] / st[VHMM_TS_NORM1];
+  const double loss = (double)(float)(recon + st[VHMM_TS_BETA] * (prior - ent));
+  st[VHMM_TS_LOSS] = loss;
+  st[VHMM_TS_LOSS_SUM] += loss;
+  st[VHMM_TS_BATCHES] += 1.0;
+}
+
+int fused_elbo(const vhmm_dims&, const vhmm_params&, const float*, const float*, const int64_t*, int64_t, int64_t, const double*,
+               double, double*, float*, void*, size_t, cudaStream_t, const double* beta_dev);
+bool fused_supported(const vhmm_dims& d);
+size_t fused_workspace_bytes(const vhmm_dims& d, int64_t B, int64_t T);
+
+size_t train_step_workspace_bytes(const vhmm_dims& d, int64_t B, int64_t T) {
+  return fused_supported(d) ? fused_workspace_bytes(d, B, T) + 256 : 0;
+}
+
+int train_step(const vhmm_dims& d, float* const* params, const float* x_cat, const float* u_cat, int64_t S_tot,
+               const int64_t* col0, const int64_t* lengths, int64_t B, int64_t T, double* state, float* exp_avg,
+               float* exp_avg_sq, double beta1, double beta2, double eps, double max_norm, float* x_buf, float* u_buf,
+               float* grads, void* ws, size_t ws_bytes, cudaStream_t st) {
+  VHMM_REQUIRE(fused_supported(d), VHMM_E_DIMS, "train_step: needs the dims of the fused ELBO path");
+  int rc = gather_chunks(x_cat, u_cat, S_tot, d.C, d.U, col0, lengths, B, T, x_buf, u_buf, st);
+  if (rc) return rc;
+  train_prep_kernel<<<1, 256, 0, st>>>(lengths, B, d.C, (int)T, state);
+  VHMM_LAUNCH_CHECK();
+  vhmm_params P;
+  for (int i = 0; i < VHMM_NUM_PARAMS; ++i) P.p[i] = params[i];
+  Arena ar(ws, ws_bytes);
+  double* sq = ar.take<double>(1);
+  VHMM_REQUIRE(ar.ok, VHMM_E_WORKSPACE, "train_step: workspace too small");
+  rc = fused_elbo(d, P, x_buf, u_buf, lengths, B, T, state + VHMM_TS_NORM0, 0.0, state + VHMM_TS_SUMS, grads,
+                  (char*)ws + ar.used, ws_bytes - ar.used, st, state + VHMM_TS_BETA);
+  if (rc) return rc;
+  train_loss_kernel<<<1, 32, 0, st>>>(state);
+  VHMM_LAUNCH_CHECK();
+  ParamTable tab;
+  param_offsets(d, tab.off);
+  for (int i = 0; i < VHMM_NUM_PARAMS; ++i) tab.p[i] = params[i];
+  const int64_t n = tab.off[VHMM_NUM_PARAMS];
+  if (max_norm > 0.0) {
+    grad_sqnorm_kernel<<<1, 1024, 0, st>>>(grads, n, nullptr, sq);
+    VHMM_LAUNCH_CHECK();
+  }
+  int64_t blocks = cdiv(n, 256);
+  if (blocks > 1184) blocks = 1184;
+  // beta1 / beta2 are constants of a run (host arguments, also stored in the state for the bias corrections); the
+  // step-dependent scalars (step size, sqrt of the second bias correction) are read from the state by the kernel
+  adam_kernel<<<(unsigned)blocks, 256, 0, st>>>(tab, grads, exp_avg, exp_avg_sq, n, 0.f, (float)(1.0 - beta1), (float)beta2,
+                                               (float)(1.0 - beta2), 1.f, (float)eps, nullptr,
+                                               max_norm > 0.0 ? sq : nullptr, (float)max_norm, nullptr, state);
   VHMM_LAUNCH_CHECK();
   return 0;
 }

@@ -117,6 +117,7 @@ struct Common {
   int64_t ntiles;
   const double* norms;     // {max(N_valid*C,1), B}
   float beta;
+  const double* beta_dev;  // when non-null the KL weight is read from device memory (graph-replayed training step)
   const float* log_pi;     // (K) log_softmax(log_prior)
   const float* wfold;      // (3,H,8) folded decoder.conv1 weights, staged layout
   float* q;                // (B,K,T)  written by A
@@ -126,6 +127,8 @@ struct Common {
   double* loss_part;       // [grid][LP]: 0 nll (B); 1 init+trans, 2 entropy, 3 valid steps, 4.. sum_b q[b,k,0] (A)
   double* acc_part;        // [grid][ACC_ALL], zeroed by the host; each CTA adds its smem accumulators every FLUSH tiles
 };
+
+__device__ __forceinline__ double beta_of(const Common& cm) { return cm.beta_dev ? *cm.beta_dev : (double)cm.beta; }
 
 struct TileInfo {
   int64_t b;
@@ -360,7 +363,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_kernel(Common cm, vhmm_param
   stage_conv_w(Wt2s, P.p[P_T2W], K2, TH, 1, 16, CF::PW_TH);
   stage_vec(b1s, P.p[P_E1B], H); stage_vec(b2s, P.p[P_E2B], H2); stage_vec(b3s, P.p[P_E3B], K);
   stage_vec(bt0s, P.p[P_T0B], TH); stage_vec(bt2s, P.p[P_T2B], K2); stage_vec(lps, cm.log_pi, K);
-  const float aP = (float)(-(double)cm.beta / cm.norms[1]);
+  const float aP = (float)(-beta_of(cm) / cm.norms[1]);
   double s_trans = 0.0, s_ent = 0.0, s_valid = 0.0, s_q0[K];
 #pragma unroll
   for (int k = 0; k < K; ++k) s_q0[k] = 0.0;
@@ -643,7 +646,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_kernel(Common cm, vhmm_params 
   stage_conv_w(W2s, P.p[P_E2W], H2, H, 3, H2, CF::PW_H);
   stage_conv_w(W3s, P.p[P_E3W], K, H2, 1, 16, CF::PW_H2);
   stage_vec(b1s, P.p[P_E1B], H); stage_vec(b2s, P.p[P_E2B], H2); stage_vec(b3s, P.p[P_E3B], K);
-  const float aE = (float)((double)cm.beta / cm.norms[1]);
+  const float aE = (float)(beta_of(cm) / cm.norms[1]);
   const int tid = threadIdx.x, w = tid >> 5;
   PROF_DECL
   __syncthreads();
@@ -772,7 +775,8 @@ __global__ void reduce_acc_kernel(const double* __restrict__ part, int ncta, int
 template <typename CF>
 __global__ void finish_kernel(const float* __restrict__ red, const double* __restrict__ loss_part, int ncta,
                               const float* __restrict__ log_pi, const double* __restrict__ norms, float beta,
-                              vhmm_params P, double* __restrict__ sums, float* __restrict__ grads) {
+                              const double* __restrict__ beta_dev, vhmm_params P, double* __restrict__ sums,
+                              float* __restrict__ grads) {
   constexpr int C = CF::C, H = CF::H, H2 = CF::H2, K = CF::K, U = CF::U, TH = CF::TH, K2 = CF::K2;
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
   if (tid == 0) {
@@ -784,7 +788,7 @@ __global__ void finish_kernel(const float* __restrict__ red, const double* __res
     }
     for (int i = 0; i < 4; ++i) sums[i] = s[i];
     if (grads) {   // log_prior through log_softmax (:71): g = aP*q0 - softmax * sum(aP*q0)
-      const double aP = -(double)beta / norms[1];
+      const double aP = -(beta_dev ? *beta_dev : (double)beta) / norms[1];
       double gs = 0.0;
       for (int k = 0; k < K; ++k) gs += aP * q0[k];
       constexpr int off_lp = H * C * 3 + H + H2 * H * 3 + H2 + K * H2 + K;   // offset of prior.log_prior
@@ -880,7 +884,7 @@ struct Launcher {
 
   static int run(const vhmm_params& P, const float* x, const float* u, const int64_t* lengths, int64_t B, int64_t T,
                  const double* norms, double beta, double* sums, float* grads, void* ws, size_t ws_bytes, int ncta,
-                 cudaStream_t st) {
+                 cudaStream_t st, const double* beta_dev = nullptr) {
     Arena A(ws, ws_bytes);
     Common cm{};
     cm.q = A.take<float>((size_t)B * CF::K * T);
@@ -896,7 +900,7 @@ struct Launcher {
     cm.x = x; cm.u = u; cm.lengths = lengths; cm.B = B; cm.T = (int)T;
     cm.tiles_per_seq = (int)cdiv(T, TT);
     cm.ntiles = B * cm.tiles_per_seq;
-    cm.norms = norms; cm.beta = (float)beta; cm.log_pi = log_pi; cm.wfold = wfold;
+    cm.norms = norms; cm.beta = (float)beta; cm.beta_dev = beta_dev; cm.log_pi = log_pi; cm.wfold = wfold;
     if (cm.ntiles < ncta) ncta = (int)cm.ntiles;
 
     const bool tc5e = decoder_variant() == 2;
@@ -947,7 +951,7 @@ struct Launcher {
     int64_t off[VHMM_NUM_PARAMS + 1];
     param_offsets(d, off);
     finish_kernel<CF><<<(unsigned)cdiv(off[VHMM_NUM_PARAMS], 256), 256, 0, st>>>(red, cm.loss_part, ncta, log_pi, norms,
-                                                                                (float)beta, P, sums, grads);
+                                                                                (float)beta, beta_dev, P, sums, grads);
     VHMM_LAUNCH_CHECK();
     return 0;
   }
@@ -1054,10 +1058,10 @@ int fused_forward(const vhmm_dims& d, const vhmm_params& P, const float* x, cons
 
 int fused_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, const float* u, const int64_t* lengths,
                int64_t B, int64_t T, const double* norms, double beta, double* sums, float* grads, void* ws,
-               size_t ws_bytes, cudaStream_t st) {
+               size_t ws_bytes, cudaStream_t st, const double* beta_dev) {
   VHMM_REQUIRE(fused_supported(d), VHMM_E_DIMS, "fused elbo: unsupported dims");
   return fz::Launcher<fz::CfgBase>::run(P, x, u, lengths, B, T, norms, beta, sums, grads, ws, ws_bytes,
-                                        fused_sm_count(), st);
+                                        fused_sm_count(), st, beta_dev);
 }
 
 }  // namespace vhmm

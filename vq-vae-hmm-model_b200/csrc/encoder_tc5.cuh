@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
   stage_conv_w(Wt2s, P.p[P_T2W], K2, TH, 1, 16, CF::PW_TH);
   stage_vec(b1s, P.p[P_E1B], H); stage_vec(b2s, P.p[P_E2B], H2); stage_vec(b3s, P.p[P_E3B], K);
   stage_vec(bt0s, P.p[P_T0B], TH); stage_vec(bt2s, P.p[P_T2B], K2); stage_vec(lps, cm.log_pi, K);
-  const float aP = (float)(-(double)cm.beta / cm.norms[1]);
+  const float aP = (float)(-beta_of(cm) / cm.norms[1]);
   double s_trans = 0.0, s_ent = 0.0, s_valid = 0.0, s_q0[K];
 #pragma unroll
   for (int k = 0; k < K; ++k) s_q0[k] = 0.0;
@@ -395,7 +395,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
   stage_conv_w_T(W1s, P.p[P_E1W], H, C);   // [tau][c][H]: lane <-> output row reads are conflict-free
   stage_conv_w(W3s, P.p[P_E3W], K, H2, 1, 16, CF::PW_H2);
   stage_vec(b1s, P.p[P_E1B], H); stage_vec(b2s, P.p[P_E2B], H2); stage_vec(b3s, P.p[P_E3B], K);
-  const float aE = (float)((double)cm.beta / cm.norms[1]);
+  const float aE = (float)(beta_of(cm) / cm.norms[1]);
   PROF_DECL
   tc5::fence_async_smem();
   tc5::fence_before_sync();

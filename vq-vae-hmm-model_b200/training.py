@@ -127,15 +127,20 @@ class DeviceChunkLoader:
     def __len__(self):
         return -(-self.items // self.batch_size)
 
-    def __iter__(self):
+    def iter_triples(self):
+        """the (seq_idx, chunk_len, start) draws of one epoch, consuming the RNG exactly like __iter__"""
         left = self.items
         while left > 0:
             n = min(self.batch_size, left)
             left -= n
             if self.fast:
-                yield self.corpus.sample_batch_fast(n, self.min_len, self.max_len, self.generator)
+                yield sample_triples_fast(self.corpus.seq_lens, n, self.min_len, self.max_len, self.generator)
             else:
-                yield self.corpus.sample_batch(n, self.min_len, self.max_len, self.rng)
+                yield sample_triples(self.corpus.seq_lens, n, self.min_len, self.max_len, self.rng)
+
+    def __iter__(self):
+        for triples in self.iter_triples():
+            yield self.corpus.gather(*triples)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -173,6 +178,7 @@ class FusedAdam:
         applies clip_grad_norm_(parameters, max_norm) first (src/training/trainer.py:31)."""
         if flat_grads.numel() != self.exp_avg.numel() or flat_grads.dtype != torch.float32 or not flat_grads.is_cuda:
             raise VhmmError("FusedAdam.step: flat fp32 CUDA gradient buffer of param_count elements expected")
+        self._check_params()
         self.step_count += 1
         dev = flat_grads.device
         with torch.cuda.device(dev):
@@ -181,6 +187,15 @@ class FusedAdam:
                                             self.betas[1], self.eps, self.step_count, Fn._ptr(grad_scale),
                                             float(max_norm), Fn._ptr(self.grad_norm), Fn._ptr(self.scratch),
                                             Fn._stream(dev)), "vhmm_adam_step")
+
+    def _check_params(self):
+        """The pointer table was taken at construction: a later model.to(...) / .half() / param.data = ... would leave
+        the kernel writing into freed memory.  Fail loudly instead."""
+        for i, p in enumerate(self.params):
+            if p.data_ptr() != self.table.p[i] or p.dtype != torch.float32 or not p.is_contiguous() or \
+                    p.device != self.exp_avg.device:
+                raise VhmmError("FusedAdam: a parameter tensor was moved, re-typed or re-assigned after the optimiser was "
+                                "built; construct a new FusedAdam for the new tensors")
 
     def zero_grad(self, set_to_none: bool = True):   # API parity; the flat buffer is rewritten every step
         self.model.zero_grad(set_to_none=set_to_none)
@@ -212,10 +227,143 @@ class FusedAdam:
             self.step_count = int(float(st["step"]))
 
 
+class GraphedTrainStep:
+    """The small-batch training step (BASELINE.json configs[0]: batch 64, chunks of 20..200 steps) as a CUDA graph.
+
+    One step = batch assembly from the resident corpus + normalisers + ELBO forward/backward + loss + optional
+    clip_grad_norm_ + Adam = ``vhmm_train_step``, a single library call whose step-dependent scalars (KL weight,
+    learning rate, step counter, bias corrections, normalisers, loss totals) live in a device ``state`` vector.  The call
+    is captured ONCE per padded length T (the batch is padded to its own maximum length exactly as collate_fn does,
+    VQ_VAE_HMM_fixed.py:166 -- padding further would change the result, SURVEY.md finding 4) and replayed: per step
+    the host draws the (sequence, length, start) triples, issues ONE pinned H2D copy of (col0, lengths) and ONE graph
+    launch.  No ATen kernel, no allocation, no sync inside an epoch; the epoch loss is read from ``state`` once.
+
+    Semantics: torch.optim.Adam(lr, betas, eps) over the 18 tensors (no weight decay / amsgrad), optional
+    clip_grad_norm_(max_norm) first, exactly like FusedAdam.step (pinned to the reference's own loop by
+    tests/golden/train_adam.npz / train_clip.npz)."""
+
+    RING = 4   # pinned staging buffers in flight
+
+    def __init__(self, model, corpus: DeviceCorpus, batch_size: int, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 max_norm: float = 0.0, optimizer: Optional[FusedAdam] = None):
+        self.model, self.corpus, self.B = model, corpus, int(batch_size)
+        self.opt = optimizer if optimizer is not None else FusedAdam(model, lr=lr, betas=betas, eps=eps)
+        self.max_norm = float(max_norm)
+        self.d = model._dims
+        dev = corpus.device
+        if _lib.lib().vhmm_elbo_active_impl(ctypes.byref(self.d)) != _lib.ELBO_FUSED:
+            raise VhmmError("GraphedTrainStep: needs the model dimensions of the fused ELBO path")
+        if self.opt.exp_avg.device != dev:
+            raise VhmmError("GraphedTrainStep: model and corpus live on different devices")
+        self.dev = dev
+        self.state = torch.zeros(_lib.TS_COUNT, device=dev, dtype=torch.float64)
+        self._host_state = torch.zeros(_lib.TS_COUNT, dtype=torch.float64).pin_memory()
+        self.both = torch.zeros(2, self.B, device=dev, dtype=torch.int64)           # [col0; lengths], graph input
+        self.stage = [torch.zeros(2, self.B, dtype=torch.int64).pin_memory() for _ in range(self.RING)]
+        self.stage_ev = [None] * self.RING
+        self.k = 0
+        self.graphs = {}
+        self.grads = torch.empty(Fn.param_count(self.d), device=dev)
+        self.stream = torch.cuda.Stream(device=dev)
+        self._beta = None
+        self._push_constants(beta=1.0)
+
+    # -- device state -------------------------------------------------------------------------------
+    def _push_constants(self, beta: float):
+        """(re)write the host-controlled slots: KL weight, learning rate, Adam betas, step counter."""
+        with torch.cuda.stream(self.stream):
+            st = self.state
+            st[_lib.TS_BETA] = float(beta)
+            st[_lib.TS_LR] = self.opt.lr
+            st[_lib.TS_BETA1] = self.opt.betas[0]
+            st[_lib.TS_BETA2] = self.opt.betas[1]
+            st[_lib.TS_STEP] = float(self.opt.step_count)
+        self._beta = float(beta)
+
+    def set_beta(self, beta: float):
+        if self._beta != float(beta):
+            with torch.cuda.stream(self.stream):
+                self.state[_lib.TS_BETA] = float(beta)
+            self._beta = float(beta)
+
+    def reset_epoch_totals(self):
+        with torch.cuda.stream(self.stream):
+            self.state[_lib.TS_LOSS_SUM:_lib.TS_BATCHES + 1] = 0.0
+
+    def epoch_mean_loss(self) -> float:
+        """mean batch loss since reset_epoch_totals() -- the one device->host sync of an epoch"""
+        self.stream.synchronize()
+        st = self.state.cpu()
+        return float(st[_lib.TS_LOSS_SUM]) / max(float(st[_lib.TS_BATCHES]), 1.0)
+
+    def last_loss(self) -> float:
+        self.stream.synchronize()
+        return float(self.state[_lib.TS_LOSS])
+
+    # -- capture / replay ---------------------------------------------------------------------------
+    def _call(self, B: int, T: int, x_buf, u_buf, ws):
+        c = self.corpus
+        check(_lib.lib().vhmm_train_step(ctypes.byref(self.d), ctypes.byref(self.opt.table), Fn._ptr(c.x_cat), Fn._ptr(c.u_cat),
+                                         c.S_tot, Fn._ptr(self.both[0]), Fn._ptr(self.both[1]), B, T, Fn._ptr(self.state),
+                                         Fn._ptr(self.opt.exp_avg), Fn._ptr(self.opt.exp_avg_sq), self.opt.betas[0],
+                                         self.opt.betas[1], self.opt.eps, self.max_norm, Fn._ptr(x_buf), Fn._ptr(u_buf),
+                                         Fn._ptr(self.grads), Fn._ptr(ws), ws.numel(),
+                                         ctypes.c_void_p(torch.cuda.current_stream(self.dev).cuda_stream)), "vhmm_train_step")
+
+    def _graph(self, B: int, T: int):
+        key = (B, T)
+        g = self.graphs.get(key)
+        if g is None:
+            c = self.corpus
+            x_buf = torch.empty(B, c.C, T, device=self.dev)
+            u_buf = torch.empty(B, c.U, T, device=self.dev)
+            ws = torch.empty(max(Fn._ws_bytes(_lib.OP_TRAIN_STEP, self.d, B, T), 256), dtype=torch.uint8, device=self.dev)
+            graph = torch.cuda.CUDAGraph()
+            self.stream.synchronize()
+            with torch.cuda.device(self.dev), torch.cuda.graph(graph, stream=self.stream):
+                self._call(B, T, x_buf, u_buf, ws)
+            g = (graph, x_buf, u_buf, ws)
+            self.graphs[key] = g
+        return g
+
+    def step(self, seq_idx, chunk_len, start, beta: float = 1.0):
+        """one training step on the items (sequence, length, start) -- what DeviceCorpus.gather + loss_and_flat_grads +
+        FusedAdam.step do, replayed from the graph of this batch's (B, T)"""
+        c = self.corpus
+        seq_idx = np.asarray(seq_idx, np.int64); chunk_len = np.asarray(chunk_len, np.int64); start = np.asarray(start, np.int64)
+        B = int(seq_idx.shape[0])
+        if B == 0 or B > self.B:
+            raise VhmmError(f"GraphedTrainStep.step: batch of {B} items (capacity {self.B})")
+        sl = np.asarray(c.seq_lens, np.int64)[seq_idx]
+        if (chunk_len < 0).any() or (start < 0).any() or (start + chunk_len > sl).any():
+            raise VhmmError("GraphedTrainStep.step: chunk outside its sequence")
+        T = int(chunk_len.max())
+        self.opt._check_params()
+        self.set_beta(beta)
+        graph = self._graph(B, T)[0]
+        k = self.k
+        self.k = (k + 1) % self.RING
+        if self.stage_ev[k] is not None:
+            self.stage_ev[k].synchronize()          # the copy that last read this pinned buffer has run
+        hb = self.stage[k]
+        hb[0, :B] = torch.from_numpy(c.offsets[seq_idx] + start)
+        hb[1, :B] = torch.from_numpy(chunk_len)
+        with torch.cuda.stream(self.stream):
+            self.both[:, :B].copy_(hb[:, :B], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+            self.stage_ev[k] = ev
+            graph.replay()
+        self.opt.step_count += 1
+        return T
+
+
 class Trainer:
     """src/training/trainer.py:9-43 with the fused step: same constructor, ``train_epoch`` (returns the
     mean batch loss, clips the gradient norm to 1.0 like :31) and ``train`` (beta warm-up :38).
-    A custom ``loss_fn`` falls back to autograd + torch.optim.Adam exactly as the reference does."""
+    A custom ``loss_fn`` runs under autograd + torch.optim.Adam as in the reference -- it must be built on
+    ``model.compute_loss`` / ``model.hmm_nll`` / ``model.hmm_log_likelihood``, the differentiable entry points
+    (encode / decode / forward return inference tensors without grad_fn)."""
 
     def __init__(self, model, lr: float = 1e-3, device: str = 'cuda', max_norm: float = 1.0):
         self.model = model.to(device)
@@ -223,9 +371,21 @@ class Trainer:
         self.max_norm = max_norm
         self.opt = FusedAdam(self.model, lr=lr)
         self._torch_opt = None
+        self._graphed = None
 
     def train_epoch(self, dataloader, loss_fn=None, beta: float = 1.0) -> float:
         self.model.train()
+        if loss_fn is None and isinstance(dataloader, DeviceChunkLoader) and \
+                _lib.lib().vhmm_elbo_active_impl(ctypes.byref(self.model._dims)) == _lib.ELBO_FUSED:
+            # launch-bound small-batch regime: one pinned H2D copy + one CUDA-graph launch per step
+            gs = self._graphed
+            if gs is None or gs.corpus is not dataloader.corpus or gs.B < dataloader.batch_size:
+                gs = self._graphed = GraphedTrainStep(self.model, dataloader.corpus, dataloader.batch_size,
+                                                      max_norm=self.max_norm, optimizer=self.opt)
+            gs.reset_epoch_totals()
+            for triples in dataloader.iter_triples():
+                gs.step(*triples, beta=beta)
+            return gs.epoch_mean_loss()
         total = torch.zeros((), device=self.opt.exp_avg.device, dtype=torch.float64)
         nb = 0
         for batch in dataloader:
@@ -258,6 +418,17 @@ def train_model_fused(model, dataloader, num_epochs=10, lr=1e-3):
     min(1, 2(ep+1)/E), no gradient clipping, the same line printed per epoch."""
     opt = FusedAdam(model, lr=lr)
     model.train()
+    if isinstance(dataloader, DeviceChunkLoader) and \
+            _lib.lib().vhmm_elbo_active_impl(ctypes.byref(model._dims)) == _lib.ELBO_FUSED:
+        # launch-bound regime: every step is one pinned H2D copy + one CUDA-graph launch (GraphedTrainStep)
+        gs = GraphedTrainStep(model, dataloader.corpus, dataloader.batch_size, optimizer=opt)
+        for ep in range(num_epochs):
+            beta = min(1.0, 2.0 * (ep + 1) / num_epochs)
+            gs.reset_epoch_totals()
+            for triples in dataloader.iter_triples():
+                gs.step(*triples, beta=beta)
+            print(f"Epoch {ep+1}/{num_epochs}, Loss: {gs.epoch_mean_loss():.4f}")
+        return model
     for ep in range(num_epochs):
         beta = min(1.0, 2.0 * (ep + 1) / num_epochs)
         total = torch.zeros((), device=opt.exp_avg.device, dtype=torch.float64)
