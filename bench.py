@@ -208,6 +208,20 @@ def run_stages(torch, V, Fn, model, dev, local, pk, quick=False):
     out = []
     mn = 60.0 if quick else 250.0
     with torch.no_grad():
+        # ---- cfg 2 shape, inference: the fused forward-only tile kernel (encode / forward of the reference API)
+        B, T = 65536, 512
+        cfg = f"cfg2 inference: B={B} T={T}, VAE_HMM.forward / encode through the public API"
+        g = torch.Generator(device=dev).manual_seed(99)
+        x = torch.randn(B, MODEL["C"], T, device=dev, generator=g)
+        ms, it, ck = timed_stage(torch, lambda: model(x), local, mn)
+        out.append(stage_line("forward (x -> q, mu, logvar: ONE fused tile kernel, conv2 layers on tcgen05, no activation in HBM)",
+                              cfg, ms, it, ck, B * T, 20 + 12 + 40, pk, flop_per_step=68580,
+                              note="68,580 algorithmic FLOP per step (SURVEY 8d fwd); compute-bound: judged against the FP32 FFMA peak"))
+        ms, it, ck = timed_stage(torch, lambda: model.regime_probs_meanfield(x), local, mn)
+        out.append(stage_line("encode + softmax (x -> q: the regime-probability call of every reference consumer)",
+                              cfg, ms, it, ck, B * T, 20 + 12, pk, flop_per_step=14400))
+        del x
+        torch.cuda.empty_cache()
         # ---- cfg 3: B = 2^20, T = 256, K = 3; inputs produced by the pipeline from seeded x, u
         B, T, K = (1 << 20), 256, 3
         cfg = f"cfg3: B={B} T={T} K={K}, lengths=T, log_A/log_b from the model's front end on seeded x,u"
@@ -267,6 +281,57 @@ def run_stages(torch, V, Fn, model, dev, local, pk, quick=False):
         Fn.release_workspaces()
         torch.cuda.empty_cache()
     return out
+
+
+def run_train_cfg1(torch, V, dev):
+    """BASELINE.json configs[0] as a TRAINING loop (train_model, VQ_VAE_HMM_fixed.py:145-162): batch 64, chunks of
+    20..200 steps of 40 base sequences, 1000 items per epoch (16 batches).  Wall clock per batch over whole epochs
+    (host sampling included, one sync per epoch): eager fused step vs the CUDA-graph replay (GraphedTrainStep)."""
+    import random
+    gcpu = torch.Generator().manual_seed(1234)
+    xs = list(torch.randn(40, MODEL["C"], 400, generator=gcpu))
+    us = list(torch.randn(40, MODEL["U"], 400, generator=gcpu))
+    corpus = V.DeviceCorpus(xs, us, device=dev)
+    res = {}
+    for mode in ("eager", "graph"):
+        torch.manual_seed(0)
+        m = V.VAE_HMM(MODEL["C"], MODEL["H"], MODEL["K"], MODEL["H2"], u_dim=MODEL["U"]).to(dev)
+        opt = V.FusedAdam(m, lr=1e-3)
+        loader = V.DeviceChunkLoader(corpus, 64)
+        random.seed(0)
+        gs = V.training.GraphedTrainStep(m, corpus, 64, optimizer=opt) if mode == "graph" else None
+
+        def epoch():
+            steps = 0
+            if gs is None:
+                tot = torch.zeros((), device=dev, dtype=torch.float64)
+                for xb, ub, L in loader:
+                    loss, flat = m.loss_and_flat_grads(xb, ub, L, 1.0)
+                    opt.step(flat)
+                    tot += loss
+                    steps += int(L.sum())
+                float(tot)
+            else:
+                gs.reset_epoch_totals()
+                for tr in loader.iter_triples():
+                    gs.step(*tr, beta=1.0)
+                    steps += int(tr[1].sum())
+                gs.epoch_mean_loss()
+            return steps
+        for _ in range(12 if mode == "graph" else 2):     # graph: the first epochs capture one graph per distinct padded length
+            epoch()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        steps, n_ep = 0, 10
+        for _ in range(n_ep):
+            steps += epoch()
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / n_ep
+        res[mode] = {"ms_per_epoch": dt * 1e3, "ms_per_batch": dt * 1e3 / len(loader), "sequence_steps_per_s": steps / n_ep / dt}
+        if gs is not None:
+            res[mode]["graphs_captured"] = len(gs.graphs)
+    res["workload"] = "cfg1 training: batch 64, chunks 20..200 of 40x400-step sequences, 16 batches/epoch, Adam; wall clock incl. host sampling"
+    return res
 
 
 def run_decode_sharded(torch, dist, V, Fn, model, dev, local, world, rank, pk):
@@ -511,6 +576,7 @@ def main():
     if not args.no_stages:
         if world == 1:
             line["stages"] = run_stages(torch, V, Fn, model, dev, local, pk, quick=args.quick_stages)
+            line["train_cfg1"] = run_train_cfg1(torch, V, dev)
         line["decode_cfg3"] = run_decode_sharded(torch, dist, V, Fn, model, dev, local, world, rank, pk)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         rate, dt, n, kind = cpu_reference_step_rate(args.cpu_batch, T, 3, 1)

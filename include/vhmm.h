@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define VHMM_VERSION 106 /* major*100 + minor */
+#define VHMM_VERSION 107 /* major*100 + minor */
 #define VHMM_NUM_PARAMS 18
 #define VHMM_PAD_STATE 255 /* Viterbi path value for t >= lengths[b] */
 
@@ -287,6 +287,19 @@ int vhmm_hmm_param_grads(const vhmm_dims* dims, const vhmm_params* params, const
  * AUTO (default) = ONEPASS when it applies; environment VHMM_POSTERIOR=sweep overrides AUTO. */
 enum { VHMM_POSTERIOR_AUTO = 0, VHMM_POSTERIOR_SWEEP = 1 };
 int vhmm_hmm_posterior_select(int variant);
+/* Numerics of the sum-product recursions (vhmm_hmm_forward / _posterior / _decode / _scan and what is built on them).
+ *   VHMM_NUMERICS_SCALED    (default) scaled linear space in fp32: alpha_hat / beta_hat normalised every step, transfer-matrix
+ *                           products rescaled by powers of two.  Within 1e-5 of float64 as long as no state probability
+ *                           that matters LATER has dropped below 2^-126 of the most likely state -- always the case for
+ *                           dense transition rows (anything a softmax produced, e.g. Prior.forward) with per-step emission
+ *                           log-ratios up to ~60.  NOT guaranteed with structural zeros (log_A = -inf: left-to-right
+ *                           chains) under sharply discriminative emissions, where a state that cannot be re-entered can
+ *                           underflow and be needed again.  vhmm_hmm_scan detects products that vanished entirely and
+ *                           recomputes those sequences with the per-step recursion.
+ *   VHMM_NUMERICS_LOGSPACE  logsumexp recursions for every K <= 32 (one warp per sequence): any dynamic range,
+ *                           several times slower.  Viterbi is max-plus in log space in both modes (bit-exact paths). */
+enum { VHMM_NUMERICS_SCALED = 0, VHMM_NUMERICS_LOGSPACE = 1 };
+int vhmm_hmm_numerics_select(int mode);
 /* B.4: Viterbi, uint8 back-pointers, lowest-index tie-break.  path (B,T) uint8, score (B). */
 int vhmm_viterbi(const float* log_pi, const float* log_A, const float* log_b,
                  const int64_t* lengths, int64_t B, int64_t T, int64_t K, uint8_t* path,

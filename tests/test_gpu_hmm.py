@@ -388,33 +388,65 @@ def test_generic_k_kernels_long_sequences(K, T, B):
     assert np.array_equal(p2.cpu().numpy(), po)
 
 
+def _chains(r, B, T, K):
+    A = r.random((B, T, K, K)) + 0.05
+    A[:3] *= np.triu(np.ones((K, K)))[None, None]                  # left-to-right: structural zeros
+    A[3:] = 1e-6 * A[3:] + np.eye(K)[None, None]                   # sticky: stay with prob ~ 1 - 2e-6
+    A /= A.sum(-1, keepdims=True)
+    with np.errstate(divide="ignore"):
+        return np.log(A).astype(np.float32)
+
+
 def test_scan_with_structural_zeros_and_sticky_chains():
-    """left-to-right chains (log_A = -inf below the diagonal) and near-absorbing states with sharply
-    discriminative emissions over T >= 512: chunk / segment products lose whole rows; the scan must stay finite and
-    equal the per-step-normalised sequential kernel and the float64 oracle."""
+    """left-to-right chains (log_A = -inf below the diagonal) and near-absorbing states over T >= 512: chunk /
+    segment products lose whole rows.  Inside the stated contract of the scaled-linear numerics (include/vhmm.h:
+    emission log-ratios that keep every state within 2^-126 of the best) the scan -- with its vanished-product
+    detection and fix-up -- equals the per-step recursion and the float64 oracle; outside it (lb spread 6: a state that
+    cannot be re-entered underflows and is needed again) the fp32 scaled recursions all lose the same mass, and the
+    log-space build (vhmm_hmm_numerics_select) is exact."""
     import vhmm_b200.functional as Fn
     r = np.random.default_rng(9)
     for K, T in ((3, 1024), (4, 768), (3, 4096)):
         B = 6
-        A = r.random((B, T, K, K)) + 0.05
-        A[:3] *= np.triu(np.ones((K, K)))[None, None]                  # left-to-right: structural zeros
-        A[3:] = 1e-6 * A[3:] + np.eye(K)[None, None]                   # sticky: stay with prob ~ 1 - 2e-6
-        A /= A.sum(-1, keepdims=True)
-        with np.errstate(divide="ignore"):
-            la = np.log(A).astype(np.float32)
-        lb = (r.normal(size=(B, T, K)) * 6.0 - 8.0).astype(np.float32)
+        la = _chains(r, B, T, K)
         lp = np.log(np.full(K, 1.0 / K)).astype(np.float32)
         L = np.array([T, T - 3, 600, T, 513, T], np.int64)
+        # (a) sticky rows with sharp emissions (dense transitions), left-to-right rows with moderate ones
+        lb = (r.normal(size=(B, T, K)) * 6.0 - 8.0).astype(np.float32)
+        lb[:3] = (r.normal(size=(3, T, K)) * 1.0 - 2.0).astype(np.float32)
         _, ll64 = H.forward(lp, la, lb, L)
         assert np.isfinite(ll64).all()
         d = dev(lp, la, lb, L)
         ll_seq = Fn.hmm_forward(*d).cpu().numpy()
         ll_scan = Fn.hmm_scan(*d).cpu().numpy()
-        ll_chk = Fn.hmm_scan(*d, want_alpha=True)[0].cpu().numpy()
-        assert np.isfinite(ll_scan).all() and np.isfinite(ll_chk).all()
+        ll_chk, alpha = Fn.hmm_scan(*d, want_alpha=True)
         assert np.allclose(ll_seq, ll64, rtol=TOL)
         assert np.allclose(ll_scan, ll64, rtol=TOL), (K, T, ll_scan, ll64)
-        assert np.allclose(ll_chk, ll64, rtol=TOL), (K, T, ll_chk, ll64)
+        assert np.allclose(ll_chk.cpu().numpy(), ll64, rtol=TOL), (K, T, ll_chk, ll64)
+        a_last = torch.logsumexp(alpha[torch.arange(B), torch.from_numpy(L - 1)], dim=-1).cpu().numpy()
+        assert np.allclose(a_last, ll64, rtol=2e-5)
+        # (b) outside the contract: sharp emissions on the left-to-right rows
+        lb2 = (r.normal(size=(B, T, K)) * 6.0 - 8.0).astype(np.float32)
+        _, ll64b = H.forward(lp, la, lb2, L)
+        d2 = dev(lp, la, lb2, L)
+        ll_scan2 = Fn.hmm_scan(*d2).cpu().numpy()
+        ll_seq2 = Fn.hmm_forward(*d2).cpu().numpy()
+        assert np.isfinite(ll_scan2).all() and np.isfinite(ll_seq2).all()
+        assert np.allclose(ll_scan2[3:], ll64b[3:], rtol=TOL) and np.allclose(ll_seq2[3:], ll64b[3:], rtol=TOL)   # dense rows: fine
+        Fn.hmm_numerics_select("logspace")
+        try:
+            ll_log = Fn.hmm_forward(*d2).cpu().numpy()
+            ll_log_scan = Fn.hmm_scan(*d2).cpu().numpy()
+            _, g_log, _ = Fn.hmm_posterior(*d2, want_xi=False)
+            p_log, _ = Fn.viterbi(*d2)
+        finally:
+            Fn.hmm_numerics_select("scaled")
+        assert np.allclose(ll_log, ll64b, rtol=TOL), (K, T, ll_log, ll64b)
+        assert np.allclose(ll_log_scan, ll64b, rtol=TOL)
+        g64, _, _ = H.posteriors(lp, la, lb2, L)
+        assert np.abs(g_log.cpu().numpy() - g64).max() <= 1e-4
+        p_ref, _ = Fn.viterbi(*d2)
+        assert torch.equal(p_log, p_ref)          # max-plus is log-space in both builds
 
 
 def test_viterbi_path_pointer_at_odd_offset():

@@ -67,6 +67,7 @@ int hmm_viterbi(const float*, const float*, const float*, const int64_t*, int64_
 int hmm_decode(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, float*, void*, size_t, cudaStream_t);
 int hmm_scan(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
 int hmm_posterior_select(int mode);
+int hmm_numerics_select(int mode);
 // hmm_inputs.cu
 bool hmm_inputs_supported(const vhmm_dims& d, int64_t T);
 size_t hmm_inputs_workspace_bytes(const vhmm_dims& d, int64_t T);
@@ -241,6 +242,10 @@ int vhmm_elbo_decoder_select(int variant) {
 int vhmm_hmm_posterior_select(int variant) {
   ARG(variant == VHMM_POSTERIOR_AUTO || variant == VHMM_POSTERIOR_SWEEP, "variant");
   return hmm_posterior_select(variant);
+}
+int vhmm_hmm_numerics_select(int mode) {
+  ARG(mode == VHMM_NUMERICS_SCALED || mode == VHMM_NUMERICS_LOGSPACE, "mode");
+  return hmm_numerics_select(mode);
 }
 int vhmm_elbo_decoder_active(void) { return fused_decoder_active(); }
 

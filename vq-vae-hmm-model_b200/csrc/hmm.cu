@@ -10,7 +10,11 @@
 
 namespace vhmm {
 
-static inline bool small_k(int64_t K) { return K >= 2 && K <= 4; }
+// numerics of the sum-product recursions: 0 = scaled linear space (default: the tuned kernels), 1 = log space
+// (logsumexp recursions of hmm_generic.cuh for every K <= 32; include/vhmm.h: vhmm_hmm_numerics_select)
+static std::atomic<int> g_numerics{0};
+int hmm_numerics_select(int mode) { g_numerics = mode; return 0; }
+static inline bool small_k(int64_t K) { return K >= 2 && K <= 4 && g_numerics.load(std::memory_order_relaxed) == 0; }
 static inline bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 
 #ifndef VHMM_HS_TC
@@ -26,7 +30,7 @@ constexpr int HS_NT = VHMM_HS_NT;   // rows (threads) per CTA
 #endif
 constexpr int SCAN_CH = VHMM_SCAN_CH; // steps per scan chunk
 
-static int64_t psi_bytes(int64_t K) { return K <= 4 ? 1 : K; }
+static int64_t psi_bytes(int64_t K) { return small_k(K) ? 1 : K; }   // packed 2 bits/state only in the small-K kernels
 
 size_t hmm_workspace_bytes(int op, int64_t B, int64_t T, int64_t K) {
   if (K <= 0) K = 32;
@@ -182,7 +186,7 @@ static hs::Args base_args(const float* log_pi, const float* A, const float* Bm, 
 // (VHMM_WIDE=generic selects the first-round log-space kernels of hmm_generic.cuh, kept for comparison)
 static bool wide_allowed() {
   static const int v = [] { const char* e = getenv("VHMM_WIDE"); return (e && e[0] == 'g') ? 0 : 1; }();
-  return v != 0;
+  return v != 0 && g_numerics.load(std::memory_order_relaxed) == 0;
 }
 #define DISPATCH_KP(K, expr)                                         \
   do {                                                               \

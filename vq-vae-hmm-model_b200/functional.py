@@ -286,6 +286,12 @@ def hmm_posterior_select(variant: str = "auto"):
     check(_lib.lib().vhmm_hmm_posterior_select(code), "vhmm_hmm_posterior_select")
 
 
+def hmm_numerics_select(mode: str = "scaled"):
+    """Sum-product numerics of the exact-HMM stages: "scaled" (default, tuned fp32 scaled-linear kernels) | "logspace"
+    (logsumexp recursions: any dynamic range, e.g. structural zeros under sharp emissions).  include/vhmm.h."""
+    check(_lib.lib().vhmm_hmm_numerics_select({"scaled": 0, "logspace": 1}[mode]), "vhmm_hmm_numerics_select")
+
+
 def elbo_decoder_active() -> str:
     return {_lib.DECODER_MMA: "mma", _lib.DECODER_TC5: "tc5"}[int(_lib.lib().vhmm_elbo_decoder_active())]
 
