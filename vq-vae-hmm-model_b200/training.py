@@ -17,6 +17,7 @@ from __future__ import annotations
 
 import ctypes
 import random
+import random as _pyrandom
 from typing import Optional, Sequence
 
 import numpy as np
@@ -37,6 +38,26 @@ def sample_triples(seq_lens: Sequence[int], n_items: int, min_len: int = 20, max
     ln = np.empty(n_items, np.int64)
     st = np.empty(n_items, np.int64)
     n_seq = len(seq_lens)
+    grb = getattr(rng, "getrandbits", None)
+    if grb is not None and (rng is _pyrandom or isinstance(rng, _pyrandom.Random)):
+        # Same draws as rng.randint(a, b), three call layers cheaper (the step is launch-bound: at batch 64 the 192
+        # randint calls were as long as the GPU work).  CPython's randint(a, b) is a + _randbelow(b - a + 1) with
+        # _randbelow(n): k = n.bit_length(); r = getrandbits(k) until r < n  (Lib/random.py, unchanged since 3.2);
+        # tests/golden/collate_stream.npz pins the equivalence to batches the real reference dataset produced.
+        def below(n):
+            k = n.bit_length()
+            r = grb(k)
+            while r >= n:
+                r = grb(k)
+            return r
+        li, ll, ls = [0] * n_items, [0] * n_items, [0] * n_items
+        for k in range(n_items):
+            i = below(n_seq)
+            S = int(seq_lens[i])
+            hi = max_len if max_len < S else S
+            n = min_len + below(hi - min_len + 1)
+            li[k], ll[k], ls[k] = i, n, below(S - n + 1)
+        return np.array(li, np.int64), np.array(ll, np.int64), np.array(ls, np.int64)
     for k in range(n_items):
         i = rng.randint(0, n_seq - 1)
         S = int(seq_lens[i])
