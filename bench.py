@@ -26,7 +26,7 @@ sys.path.insert(0, ROOT)
 MODEL = dict(C=5, H=64, K=3, H2=32, U=4, TH=128)
 FLOP_PER_STEP = 205740          # algorithmic fwd+bwd FLOPs per sequence-step (base)
 BYTES_PER_STEP = 72             # x,u read once forward and once backward
-TRAFFIC_FILE = "r1d_decoder_traffic.json"   # latest committed ncu --set full capture of the decoder tile kernel
+TRAFFIC_FILE = "r2_decoder_traffic.json"   # latest committed ncu --set full capture of the decoder tile kernel
 DEC_FLOP_PER_STEP = 3 * 50816   # decoder forward 50,816 FLOP/step; fwd+bwd = 3x
 FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12   # FFMA peak at max SM clock (derived)
 
