@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define VHMM_VERSION 107 /* major*100 + minor */
+#define VHMM_VERSION 108 /* major*100 + minor */
 #define VHMM_NUM_PARAMS 18
 #define VHMM_PAD_STATE 255 /* Viterbi path value for t >= lengths[b] */
 
@@ -171,6 +171,20 @@ int vhmm_elbo_decoder_active(void);
  * {enc_prior, decoder, enc_bwd} and the number of calls recorded. */
 int vhmm_elbo_timing(int enable);
 int vhmm_elbo_timing_read(double* ms_sum_host /*[3]*/, int* ncalls_host);
+
+/* Layer kernels of the LAYER-WISE path (any model dims; what runs BASELINE.json configs[4], hidden_dim 256).  Every layer
+ * of the reference is an nn.Conv1d of width 3 (padding 1) or 1 -- or an nn.Linear applied per time step, the same thing
+ * (VQ_VAE_HMM_fixed.py:34-36, :53-57, :77-79).  Two builds:
+ *   VHMM_CONV_TC5   tcgen05.mma GEMM-convolutions (M = 128 time steps, N = 128 channels, fp32 parity through the
+ *                   2 x fp16 split with fp32 TMEM accumulators): needs Cin % 16 == 0, Cout % 128 == 0, T % 4 == 0
+ *   VHMM_CONV_FFMA  FP32 FFMA kernels, any shape
+ * AUTO (default) picks TC5 per layer where the shape allows; environment VHMM_CONV=ffma|tc5 seeds the choice.
+ * vhmm_conv1d_fwd is one such layer on its own: y (B,Cout,T) = [relu](bias + conv_kw(x (B,Cin,T), weight (Cout,Cin,kw))). */
+enum { VHMM_CONV_AUTO = 0, VHMM_CONV_FFMA = 1, VHMM_CONV_TC5 = 2 };
+int vhmm_conv_select(int impl);
+size_t vhmm_conv1d_workspace_bytes(int64_t Cin, int64_t Cout, int64_t kw);
+int vhmm_conv1d_fwd(const float* x, const float* weight, const float* bias, int64_t B, int64_t Cin, int64_t Cout,
+                    int64_t T, int64_t kw, int relu, float* y, void* workspace, size_t workspace_bytes, void* stream);
 
 /* argmax regime decoding (backtesting.py:155, src/backtesting.py:107): q or logits (B,K,T) ->
  * regimes int64 (B,T), lowest index on ties. */

@@ -104,6 +104,9 @@ PROTOTYPES = {
     "vhmm_elbo_decoder_active": (ctypes.c_int, []),
     "vhmm_elbo_timing": (ctypes.c_int, [ctypes.c_int]),
     "vhmm_elbo_timing_read": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int)]),
+    "vhmm_conv_select": (ctypes.c_int, [ctypes.c_int]),
+    "vhmm_conv1d_workspace_bytes": (_SZ, [_I64, _I64, _I64]),
+    "vhmm_conv1d_fwd": (ctypes.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _I64, ctypes.c_int, _P, _P, _SZ, _P]),
     "vhmm_argmax_regimes": (ctypes.c_int, [_P, _I64, _I64, _I64, _P, _P]),
     "vhmm_gather_chunks": (ctypes.c_int, [_P, _P, _I64, _I64, _I64, _P, _P, _I64, _I64, _P, _P, _P]),
     "vhmm_train_step": (ctypes.c_int, [_DP, _PP, _P, _P, _I64, _P, _P, _I64, _I64, _P, _P, _P, _DBL, _DBL, _DBL, _DBL, _P, _P, _P, _P,

@@ -47,6 +47,9 @@ int layerwise_decoder_fwd(const vhmm_dims&, const vhmm_params&, const float*, in
 int layerwise_elbo(const vhmm_dims&, const vhmm_params&, const float*, const float*, const int64_t*, int64_t, int64_t, const double*, double, double*, float*, void*, size_t, cudaStream_t);
 int layerwise_emission_table(const vhmm_dims&, const vhmm_params&, int64_t, float*, float*, void*, size_t, cudaStream_t);
 int launch_argmax(const float* q, int64_t B, int64_t K, int64_t T, int64_t* out, cudaStream_t st);
+int conv_impl_select(int mode);
+size_t conv1d_workspace_bytes(int Cin, int Cout, int kw);
+int conv1d_fwd(const float*, const float*, const float*, int64_t, int, int, int64_t, int, int, float*, void*, size_t, cudaStream_t);
 // elbo_fused.cu
 bool fused_supported(const vhmm_dims& d);
 size_t fused_workspace_bytes(const vhmm_dims& d, int64_t B, int64_t T);
@@ -242,6 +245,18 @@ int vhmm_elbo_decoder_select(int variant) {
 int vhmm_hmm_posterior_select(int variant) {
   ARG(variant == VHMM_POSTERIOR_AUTO || variant == VHMM_POSTERIOR_SWEEP, "variant");
   return hmm_posterior_select(variant);
+}
+int vhmm_conv_select(int impl) {
+  ARG(impl == VHMM_CONV_AUTO || impl == VHMM_CONV_FFMA || impl == VHMM_CONV_TC5, "impl");
+  return conv_impl_select(impl);
+}
+size_t vhmm_conv1d_workspace_bytes(int64_t Cin, int64_t Cout, int64_t kw) {
+  return (Cin > 0 && Cout > 0 && (kw == 1 || kw == 3)) ? conv1d_workspace_bytes((int)Cin, (int)Cout, (int)kw) : 0;
+}
+int vhmm_conv1d_fwd(const float* x, const float* weight, const float* bias, int64_t B, int64_t Cin, int64_t Cout, int64_t T,
+                    int64_t kw, int relu, float* y, void* workspace, size_t workspace_bytes, void* stream) {
+  ARG(x && weight && y, "x/weight/y"); ARG(B > 0 && Cin > 0 && Cout > 0 && T > 0, "sizes"); ARG(kw == 1 || kw == 3, "kw");
+  return conv1d_fwd(x, weight, bias, B, (int)Cin, (int)Cout, T, (int)kw, relu, y, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 int vhmm_hmm_numerics_select(int mode) {
   ARG(mode == VHMM_NUMERICS_SCALED || mode == VHMM_NUMERICS_LOGSPACE, "mode");

@@ -1,0 +1,324 @@
+// conv_tc5.cuh -- layer kernels on the 5th-generation tensor core (tcgen05.mma, TMEM accumulators) for the
+// LAYER-WISE path at widths where the convolutions are compute-bound GEMMs (north_star: "tensor cores ... at
+// hidden_dim >= 128"; BASELINE.json configs[4]: hidden_dim 256, hidden_dim2 128, K 32 -> K*K = 1024 transition
+// logits).  Every layer of the model is a 1-D cross-correlation of width 3 (pad 1) or 1 over (B,C,T) tensors
+// (VQ_VAE_HMM_fixed.py:34-36, :53-57, :77-79), i.e. per tap a GEMM  Y[t, o] += X[t + tau - pad, c] W[o, c, tau]:
+//
+//   conv_tc5_kernel   forward AND input gradient (the latter through the transposed / tap-flipped weight view, as in
+//                     conv_generic.cuh):  M = 128 time steps, N = 128 output channels, K = Cin in chunks of 16
+//   wgrad_tc5_kernel  weight gradient  dW[o, c, tau] = sum_{b,t} dY[b,o,t] X[b,c,t+tau-pad]:
+//                     M = 64 out channels x 2 parts, N = 64 in channels x 2 parts, K = time
+//
+// Arithmetic: the fp32-parity scheme of the fused tile kernels (decoder_tc5.cuh): every fp32 operand is scaled by a
+// power of two and split into two fp16 parts, x*s = h + m; a product is h*h + h*m + m*h with fp32 accumulation in
+// TMEM.  The tensor core's accumulate truncates toward zero, so the h*h terms are spread round-robin over THREE
+// accumulator sets (chains of K/48 instead of K/16 accumulations) and the small terms go to a fourth; the sets meet in
+// fp32 FADDs in the epilogue.  Scales: one power of two per TENSOR (device-side abs-max, absmax_kernel) -- fp16 is a
+// floating format, the scale only has to keep the largest element below 2^14.
+//
+// Operand layouts are the no-swizzle canonical ones of tc5.cuh: activations act[part][ch/8][row][8] (row = time,
+// K-major; a conv tap is a +16-byte shift of the descriptor start), weights W[tau][ch/8][part*128 + o][8], prepared
+// ONCE per call in global memory in exactly the shared-memory image of a (128-out-channel, 16-in-channel) chunk, so
+// that a chunk is one contiguous block fetched with 16-byte cp.async.  Four-stage cp.async pipeline over the K
+// chunks; the fp32 -> fp16-parts conversion of chunk k+1 runs under the MMAs of chunk k.
+#pragma once
+#include "conv_generic.cuh"
+#include "tc5.cuh"
+
+namespace vhmm {
+namespace ct5 {
+
+constexpr int NT = 256;                 // threads per CTA
+constexpr int TM = 128;                 // time steps per tile (MMA M)
+constexpr int TN = 128;                 // output channels per tile (MMA N)
+constexpr int KC = 16;                  // input channels per chunk (one MMA K step = 2 planes of 8)
+constexpr int ROWS = 130;               // rows of an activation plane: row r <-> t = t0 - 1 + r
+constexpr int PLANE = ROWS * 16;        // bytes of one 8-channel plane
+constexpr int APART = 2 * PLANE;        // one part (h or m) of a chunk
+constexpr int ABYTES = 2 * APART;       // h and m
+constexpr int WPLANE = 2 * TN * 16;     // rows = part*128 + o
+constexpr int XW = 136;                 // staged fp32 columns: t0-4 .. t0+131 (16-byte aligned start)
+constexpr int XP = 140;                 // pitch (floats)
+constexpr int XBYTES = KC * XP * 4;
+constexpr int STAGES = 4;
+constexpr uint32_t HH0 = 0, SMALL = 384;   // TMEM columns: three h*h sets at 0 / 128 / 256, the small terms at 384
+
+template <int KW>
+struct Sm {
+  static constexpr int WBYTES = KW * 2 * WPLANE;          // weights of one chunk: [tau][plane][256 rows][16 B]
+  static constexpr int STAGE = WBYTES + XBYTES;
+  static constexpr int TOTAL = STAGES * STAGE + 2 * ABYTES;
+};
+
+// |x| max of a tensor -> *out (float bits; non-negative floats order like unsigned integers).  *out zeroed by the host.
+__global__ void __launch_bounds__(256) absmax_kernel(const float* __restrict__ x, int64_t n, uint32_t* __restrict__ out) {
+  float m = 0.f;
+  const int64_t n4 = n >> 2;
+  const float4* x4 = reinterpret_cast<const float4*>(x);
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (int64_t)gridDim.x * 256) {
+    const float4 v = x4[i];
+    m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+  }
+  for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) m = fmaxf(m, fabsf(x[i]));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(out, __float_as_uint(m));
+}
+
+// W(o,c,tau) of a weight view -> fp16 parts in the chunk image Wg[ct][kc][tau][plane][part*128 + o%128][c%8]
+__global__ void __launch_bounds__(256) prep_weights_kernel(WView wv, int Cin, int Cout, int KW, const uint32_t* __restrict__ amax,
+                                                           uint8_t* __restrict__ Wg) {
+  const int64_t n = (int64_t)Cout * Cin * KW;
+  const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  const int tau = (int)(i % KW), c = (int)((i / KW) % Cin), o = (int)(i / ((int64_t)KW * Cin));
+  const float s = tc5::pow2_scale(__uint_as_float(*amax));
+  const float v = wv.w[wv.base + (int64_t)o * wv.so + (int64_t)c * wv.sc + (int64_t)tau * wv.st] * s;
+  __half h, m;
+  tc5::split_f16(v, h, m);
+  const int nkc = Cin / KC;
+  const int ct = o / TN, ol = o % TN, kc = c / KC, pl = (c % KC) / 8, e = c % 8;
+  uint8_t* p = Wg + ((((int64_t)(ct * nkc + kc) * KW + tau) * 2 + pl) * (2 * TN) + ol) * 16 + e * 2;
+  *reinterpret_cast<__half*>(p) = h;
+  *reinterpret_cast<__half*>(p + TN * 16) = m;
+}
+
+__device__ __forceinline__ void cp16(void* smem, const void* g, int bytes) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(d), "l"(g), "r"(bytes) : "memory");
+}
+
+struct ConvArgs {
+  const float* x;          // (B,Cin,T)
+  const uint8_t* Wg;       // prepared weights
+  const float* bias;       // (Cout) or null
+  const float* act;        // (B,Cout,T) ReLU mask source for EPI_MASK, or null
+  float* y;                // (B,Cout,T)
+  const uint32_t* amax_x;  // device: |x| max (float bits)
+  const uint32_t* amax_w;  // device: |W| max
+  int64_t B;
+  int Cin, Cout, T, epi;
+  int ntt, nct;            // time tiles per sequence, out-channel tiles
+  int64_t nitems;
+};
+
+// y = epi(bias + conv_KW(x, W)); requires Cin % 16 == 0, Cout % 128 == 0, T % 4 == 0, x 16-byte aligned
+template <int KW>
+__global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
+  constexpr int PAD = KW / 2;
+  using S = Sm<KW>;
+  extern __shared__ __align__(1024) uint8_t sm[];
+  // one mbarrier per parts buffer: chunk k commits to bar[k & 1] and is waited for before chunk k + 2 reuses the buffer, so a
+  // waiter is never more than one phase behind (a single barrier would alias phases k and k + 2 of the same parity)
+  __shared__ __align__(8) uint64_t bar[2];
+  __shared__ uint32_t tmem_sh;
+  uint8_t* parts = sm + STAGES * S::STAGE;
+  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < 2 * ABYTES / 4; i += NT) reinterpret_cast<uint32_t*>(parts)[i] = 0u;
+  if (tid == 0) { tc5::mbar_init(&bar[0], 1); tc5::mbar_init(&bar[1], 1); tc5::mbar_init_fence(); }
+  if (w == 0) tc5::tmem_alloc512(&tmem_sh);
+  tc5::fence_before_sync();
+  __syncthreads();
+  tc5::fence_after_sync();
+  const uint32_t tmem = tmem_sh;
+  const float sx = tc5::pow2_scale(__uint_as_float(*a.amax_x));
+  const float sw = tc5::pow2_scale(__uint_as_float(*a.amax_w));
+  const float inv = 1.f / (sx * sw);
+  const int nkc = a.Cin / KC;
+  const int T = a.T;
+  uint32_t par[2] = {0u, 0u};
+  constexpr uint32_t IDESC = tc5::idesc_f16(TN, 0, 0);
+
+  for (int64_t item = blockIdx.x; item < a.nitems; item += gridDim.x) {
+    const int ct = (int)(item % a.nct);
+    const int64_t bt = item / a.nct;
+    const int tt = (int)(bt % a.ntt);
+    const int64_t b = bt / a.ntt;
+    const int t0 = tt * TM;
+    const float* xb = a.x + b * (int64_t)a.Cin * T;
+    const uint8_t* wct = a.Wg + (int64_t)ct * nkc * S::WBYTES;
+
+    auto issue_loads = [&](int kc) {
+      uint8_t* st = sm + (kc % STAGES) * S::STAGE;
+      const uint8_t* wsrc = wct + (int64_t)kc * S::WBYTES;
+      for (int i = tid; i < S::WBYTES / 16; i += NT) cp16(st + i * 16, wsrc + i * 16, 16);
+      float* xs = reinterpret_cast<float*>(st + S::WBYTES);
+      for (int i = tid; i < KC * (XW / 4); i += NT) {
+        const int c = i / (XW / 4), j = (i - c * (XW / 4)) * 4, t = t0 - 4 + j;
+        const bool ok = (t >= 0 && t < T);               // T % 4 == 0: a granule is inside or outside as a whole
+        cp16(xs + c * XP + j, xb + (int64_t)(kc * KC + c) * T + (ok ? t : 0), ok ? 16 : 0);
+      }
+    };
+    issue_loads(0);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    if (nkc > 1) issue_loads(1);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    for (int kc = 0; kc < nkc; ++kc) {
+      // the stage about to be refilled and the parts buffer about to be rewritten were last read by the MMAs of chunk kc-2
+      if (kc >= 2) { tc5::mbar_wait(&bar[kc & 1], par[kc & 1]); par[kc & 1] ^= 1u; }
+      if (kc + 2 < nkc) issue_loads(kc + 2);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group 2;" ::: "memory");
+      __syncthreads();
+      {   // fp32 -> fp16 parts of chunk kc: item (plane, row) = 8 channels of one time step
+        const float* xs = reinterpret_cast<const float*>(sm + (kc % STAGES) * S::STAGE + S::WBYTES);
+        uint8_t* pb = parts + (kc & 1) * ABYTES;
+        for (int i = tid; i < 2 * ROWS; i += NT) {
+          const int pl = i / ROWS, r = i - pl * ROWS;
+          __align__(16) __half hh[8], mm[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) tc5::split_f16(xs[(pl * 8 + e) * XP + r + 3] * sx, hh[e], mm[e]);
+          uint8_t* p = pb + pl * PLANE + r * 16;
+          *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(hh);
+          *reinterpret_cast<uint4*>(p + APART) = *reinterpret_cast<const uint4*>(mm);
+        }
+      }
+      tc5::fence_async_smem();
+      tc5::fence_before_sync();
+      __syncthreads();
+      if (w == 0) {
+        tc5::fence_after_sync();
+        const bool lead = tc5::elect_one();
+        const uint32_t sA = tc5::smem_u32(parts + (kc & 1) * ABYTES);
+        const uint32_t sW = tc5::smem_u32(sm + (kc % STAGES) * S::STAGE);
+#pragma unroll
+        for (int tau = 0; tau < KW; ++tau) {
+          const int step = kc * KW + tau;
+          const uint64_t ah = tc5::make_desc(sA + (tau - PAD + 1) * 16, PLANE, 128);
+          const uint64_t am = tc5::make_desc(sA + APART + (tau - PAD + 1) * 16, PLANE, 128);
+          const uint64_t bh = tc5::make_desc(sW + tau * 2 * WPLANE, WPLANE, 128);
+          const uint64_t bm = tc5::make_desc(sW + tau * 2 * WPLANE + TN * 16, WPLANE, 128);
+          if (lead) {
+            tc5::mma_f16(tmem + HH0 + 128u * (uint32_t)(step % 3), ah, bh, IDESC, step >= 3 ? 1u : 0u);
+            tc5::mma_f16(tmem + SMALL, ah, bm, IDESC, step >= 1 ? 1u : 0u);
+            tc5::mma_f16(tmem + SMALL, am, bh, IDESC, 1u);
+          }
+        }
+        if (lead) tc5::commit(&bar[kc & 1]);
+        __syncwarp();
+      }
+    }
+    for (int kc = (nkc >= 2 ? nkc - 2 : 0); kc < nkc; ++kc) { tc5::mbar_wait(&bar[kc & 1], par[kc & 1]); par[kc & 1] ^= 1u; }
+    tc5::fence_after_sync();
+    {   // epilogue: TMEM lane = time row; warp w reads lane quadrant w & 3, columns [64 (w >> 2), +64)
+      const uint32_t lane_base = (uint32_t)(32 * (w & 3)) << 16;
+      const int t = t0 + 32 * (w & 3) + lane;
+      const int nsets = (nkc * KW < 3) ? nkc * KW : 3;
+#pragma unroll 1
+      for (int cgp = 0; cgp < 4; ++cgp) {
+        const int col = 64 * (w >> 2) + 16 * cgp;
+        float v[16], s[16];
+        tc5::tmem_ld16(tmem + lane_base + SMALL + col, s);
+        tc5::tmem_ld16(tmem + lane_base + HH0 + col, v);
+        if (nsets > 1) {
+          float v1[16];
+          tc5::tmem_ld16(tmem + lane_base + HH0 + 128 + col, v1);
+#pragma unroll
+          for (int e = 0; e < 16; ++e) v[e] += v1[e];
+        }
+        if (nsets > 2) {
+          float v2[16];
+          tc5::tmem_ld16(tmem + lane_base + HH0 + 256 + col, v2);
+#pragma unroll
+          for (int e = 0; e < 16; ++e) v[e] += v2[e];
+        }
+        if (t < T) {
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            const int o = ct * TN + col + e;
+            const int64_t off = (b * a.Cout + o) * (int64_t)T + t;
+            float r = (v[e] + s[e]) * inv + (a.bias ? a.bias[o] : 0.f);
+            if (a.epi == EPI_RELU) r = fmaxf(r, 0.f);
+            else if (a.epi == EPI_MASK) r = a.act[off] > 0.f ? r : 0.f;
+            a.y[off] = r;
+          }
+        }
+      }
+    }
+    tc5::fence_before_sync();
+    __syncthreads();
+    tc5::fence_after_sync();
+  }
+  tc5::fence_before_sync();
+  __syncthreads();
+  if (w == 0) tc5::tmem_free512(tmem);
+}
+
+}  // namespace ct5
+}  // namespace vhmm
+
+namespace vhmm {
+
+// ---- host side -------------------------------------------------------------------------------------------
+// 0 = auto (tensor cores when the shape allows), 1 = FP32 FFMA layer kernels only, 2 = tensor cores required
+int conv_impl_mode();
+
+static inline bool conv_tc5_ok(int Cin, int Cout, int64_t T, int kw, const void* x, const void* y) {
+  return (kw == 1 || kw == 3) && Cin % ct5::KC == 0 && Cout % ct5::TN == 0 && (T & 3) == 0 && T >= 4 &&
+         (((uintptr_t)x | (uintptr_t)y) & 15) == 0;
+}
+// bytes of prepared weights (+ two abs-max words) for one (layer, view)
+static inline size_t conv_tc5_weight_bytes(int Cin, int Cout, int kw) {
+  return align_up((size_t)Cin * Cout * kw * 4, 256) + 256;
+}
+
+struct Tc5Weights {        // a weight view prepared for conv_tc5_kernel
+  const uint8_t* Wg = nullptr;
+  const uint32_t* amax_w = nullptr;
+  uint32_t* amax_x = nullptr;      // scratch word for the activation abs-max of the launch that uses these weights
+};
+
+// prepare one weight view into `buf` (conv_tc5_weight_bytes); n_w = number of floats of the underlying tensor
+static inline int conv_tc5_prepare(WView wv, int64_t n_w, int Cin, int Cout, int kw, void* buf, Tc5Weights* out, cudaStream_t st) {
+  uint8_t* base = (uint8_t*)buf;
+  const size_t wb = align_up((size_t)Cin * Cout * kw * 4, 256);
+  uint32_t* words = (uint32_t*)(base + wb);
+  VHMM_CUDA_CHECK(cudaMemsetAsync(words, 0, 8, st));
+  int64_t blocks = cdiv(n_w, 1024);
+  if (blocks > 1184) blocks = 1184;
+  ct5::absmax_kernel<<<(unsigned)blocks, 256, 0, st>>>(wv.w, n_w, words);
+  VHMM_LAUNCH_CHECK();
+  const int64_t n = (int64_t)Cin * Cout * kw;
+  ct5::prep_weights_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(wv, Cin, Cout, kw, words, base);
+  VHMM_LAUNCH_CHECK();
+  out->Wg = base; out->amax_w = words; out->amax_x = words + 1;
+  return 0;
+}
+
+static inline int launch_conv_tc5(const float* x, const Tc5Weights& W, const float* bias, const float* act, float* y,
+                                  int64_t B, int Cin, int Cout, int64_t T, int kw, int epi, cudaStream_t st) {
+  if (B <= 0 || T <= 0) return 0;
+  VHMM_CUDA_CHECK(cudaMemsetAsync(W.amax_x, 0, 4, st));
+  const int64_t nx = B * (int64_t)Cin * T;
+  int64_t blocks = cdiv(nx, 1024 * 8);
+  if (blocks > 1184) blocks = 1184;
+  if (blocks < 1) blocks = 1;
+  ct5::absmax_kernel<<<(unsigned)blocks, 256, 0, st>>>(x, nx, W.amax_x);
+  VHMM_LAUNCH_CHECK();
+  ct5::ConvArgs a{};
+  a.x = x; a.Wg = W.Wg; a.bias = bias; a.act = act; a.y = y; a.amax_x = W.amax_x; a.amax_w = W.amax_w;
+  a.B = B; a.Cin = Cin; a.Cout = Cout; a.T = (int)T; a.epi = epi;
+  a.ntt = (int)cdiv(T, ct5::TM); a.nct = Cout / ct5::TN;
+  a.nitems = B * a.ntt * a.nct;
+  int64_t grid = device_sm_count();
+  if (grid > a.nitems) grid = a.nitems;
+  if (kw == 3) {
+    static PerDeviceOnce once;
+    if (once.pending()) {
+      VHMM_CUDA_CHECK(cudaFuncSetAttribute(ct5::conv_tc5_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ct5::Sm<3>::TOTAL));
+      once.mark();
+    }
+    ct5::conv_tc5_kernel<3><<<(unsigned)grid, ct5::NT, ct5::Sm<3>::TOTAL, st>>>(a);
+  } else {
+    static PerDeviceOnce once;
+    if (once.pending()) {
+      VHMM_CUDA_CHECK(cudaFuncSetAttribute(ct5::conv_tc5_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ct5::Sm<1>::TOTAL));
+      once.mark();
+    }
+    ct5::conv_tc5_kernel<1><<<(unsigned)grid, ct5::NT, ct5::Sm<1>::TOTAL, st>>>(a);
+  }
+  VHMM_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace vhmm

@@ -2,12 +2,47 @@
 // for ARBITRARY model dimensions: Encoder / Prior / Decoder forward and the mean-field ELBO
 // with its full backward.  The batch is processed in chunks that fit the caller's workspace.
 // Reference: VQ_VAE_HMM_fixed.py:31-143; maths in SURVEY.md Appendix A.2.
+#include <atomic>
+#include <stdlib.h>
 #include "conv_generic.cuh"
+#include "conv_tc5.cuh"
 #include "pointwise.cuh"
 
 namespace vhmm {
 
 static const int64_t kMaxChunk = 32768;  // gridDim.y/z limit is 65535
+
+// layer kernels of the layer-wise path: 0 auto (tcgen05 where the layer shape allows: Cin % 16 == 0, Cout % 128 == 0,
+// T % 4 == 0), 1 FP32 FFMA only, 2 tcgen05 required (error otherwise); environment VHMM_CONV=ffma|tc5 seeds the default
+static std::atomic<int> g_conv_impl{-1};
+int conv_impl_mode() {
+  int v = g_conv_impl.load(std::memory_order_relaxed);
+  if (v < 0) {
+    const char* e = getenv("VHMM_CONV");
+    v = (e && e[0] == 'f') ? 1 : ((e && e[0] == 't') ? 2 : 0);
+    g_conv_impl.store(v, std::memory_order_relaxed);
+  }
+  return v;
+}
+int conv_impl_select(int mode) { g_conv_impl.store(mode, std::memory_order_relaxed); return 0; }
+
+size_t conv1d_workspace_bytes(int Cin, int Cout, int kw) { return conv_tc5_weight_bytes(Cin, Cout, kw) + 256; }
+
+// one Conv1d layer (kernel width 1 or 3, padding kw/2): y = [relu](bias + conv(x, w)); w (Cout,Cin,kw)
+int conv1d_fwd(const float* x, const float* w, const float* bias, int64_t B, int Cin, int Cout, int64_t T, int kw, int relu,
+               float* y, void* ws, size_t ws_bytes, cudaStream_t st) {
+  const int mode = conv_impl_mode();
+  const bool ok = conv_tc5_ok(Cin, Cout, T, kw, x, y);
+  VHMM_REQUIRE(mode != 2 || ok, VHMM_E_DIMS, "conv1d: tensor-core layer kernel needs Cin %% 16 == 0, Cout %% 128 == 0, T %% 4 == 0");
+  if (mode != 1 && ok) {
+    VHMM_REQUIRE(ws && ws_bytes >= conv_tc5_weight_bytes(Cin, Cout, kw), VHMM_E_WORKSPACE, "conv1d: workspace too small");
+    Tc5Weights W;
+    int rc = conv_tc5_prepare(wview_fwd(w, Cin, kw), (int64_t)Cin * Cout * kw, Cin, Cout, kw, ws, &W, st);
+    if (rc) return rc;
+    return launch_conv_tc5(x, W, bias, nullptr, y, B, Cin, Cout, T, kw, relu ? EPI_RELU : EPI_NONE, st);
+  }
+  return launch_conv(x, wview_fwd(w, Cin, kw), bias, nullptr, y, B, Cin, Cout, T, kw, relu ? EPI_RELU : EPI_NONE, st);
+}
 
 struct LayerwiseSizes {
   int64_t per_step_fwd;   // floats per (sequence, step) kept by the forward pass

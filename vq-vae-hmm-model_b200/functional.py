@@ -166,6 +166,27 @@ def decoder_fwd(d: Dims, params, q):
     return mu, logvar
 
 
+def conv_select(impl: str = "auto"):
+    """Layer kernels of the layer-wise path: "auto" | "ffma" | "tc5" (include/vhmm.h: vhmm_conv_select)."""
+    check(_lib.lib().vhmm_conv_select({"auto": 0, "ffma": 1, "tc5": 2}[impl]), "vhmm_conv_select")
+
+
+def conv1d(x, weight, bias=None, relu=False):
+    """One Conv1d layer (kernel width 1 or 3, padding kw // 2) through the layer kernels of libvhmm.so."""
+    x = _f32c(x); weight = _f32c(weight); _require_cuda(x, weight)
+    B, Cin, T = x.shape
+    Cout, Cin2, kw = weight.shape
+    if Cin2 != Cin:
+        raise VhmmError(f"conv1d: weight {tuple(weight.shape)} does not match x {tuple(x.shape)}")
+    bias = _f32c(bias) if bias is not None else None
+    y = torch.empty(B, Cout, T, device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device):
+        ws = workspace(x.device, int(_lib.lib().vhmm_conv1d_workspace_bytes(Cin, Cout, kw)))
+        check(_lib.lib().vhmm_conv1d_fwd(_ptr(x), _ptr(weight), _ptr(bias), B, Cin, Cout, T, kw, int(bool(relu)), _ptr(y),
+                                         _ptr(ws), ws.numel(), _stream(x.device)), "vhmm_conv1d_fwd")
+    return y
+
+
 def elbo_norms(lengths_dev: torch.Tensor, B: int, C: int, T: int) -> torch.Tensor:
     """device double[2] = {max(N_valid*C, 1), B}: the reference's normalisers
     (VQ_VAE_HMM_fixed.py:120, :131, :135) for THIS process's sequences."""
