@@ -297,3 +297,35 @@ def test_host_resident_batch_is_streamed(elbo_impl):
     assert abs(float(l1) - float(l0)) <= 1e-6 * abs(float(l0))
     for k, v in m.named_parameters():
         assert rel_err(v.grad, g0[k]) <= 2e-6, k
+
+
+@pytest.mark.parametrize("conv", ["tc5", "ffma"])
+def test_scaled_config_cfg5_dims_vs_float64_oracle(conv):
+    """BASELINE.json configs[4] dims (hidden_dim 256, hidden_dim2 128, K 32, u_dim 16) at T = 1024 on the layer-wise path with
+    the tcgen05 layer kernels (conv_tc5.cuh: forward, input gradient and weight gradient of encoder.conv2, decoder.conv1/2,
+    transition_net.0/2) and with the FFMA ones: loss and all 18 gradient tensors against the float64 oracle, ragged lengths."""
+    import vhmm_b200 as V
+    from vhmm_b200 import functional as Fn
+    from oracle import elbo as O
+    C, H, K, H2, U, TH = 5, 256, 32, 128, 16, 128
+    p = O.init_params(C, H, K, H2, U, TH, seed=1)
+    x, u, L = O.synth_batch(6, C, U, 1024, seed=4, ragged=True, min_len=300)
+    m = V.VAE_HMM(C, H, K, H2, u_dim=U, trans_hidden=TH)
+    m.load_state_dict(p)
+    m = m.cuda()
+    p64 = {k: v.double() for k, v in p.items()}
+    ref, _, g64 = O.loss_and_grads(p64, x.double(), u.double(), L, U, 0.7)
+    Fn.conv_select(conv)
+    try:
+        loss = m.compute_loss(x.cuda(), u.cuda(), L, 0.7)
+        loss.backward()
+        with torch.no_grad():
+            (mu, lv), q = m(x.cuda())
+    finally:
+        Fn.conv_select("auto")
+    assert abs(float(loss) - float(ref)) <= TOL * abs(float(ref)), (float(loss), float(ref))
+    sd = dict(m.named_parameters())
+    for k in O.PARAM_ORDER:
+        assert rel_err(sd[k].grad.cpu(), g64[k]) <= TOL, (conv, k, rel_err(sd[k].grad.cpu(), g64[k]))
+    (mu64, lv64), q64 = O.forward(p64, x.double())
+    assert maxabs_rel(q.cpu(), q64) < TOL and maxabs_rel(mu.cpu(), mu64) < TOL and maxabs_rel(lv.cpu(), lv64) < TOL

@@ -322,3 +322,262 @@ static inline int launch_conv_tc5(const float* x, const Tc5Weights& W, const flo
 }
 
 }  // namespace vhmm
+
+// =============================================================================================================
+// weight gradient on the tensor core
+// =============================================================================================================
+namespace vhmm {
+namespace ct5 {
+
+constexpr int WNT = 512;                     // threads per CTA (16 warps: 4 TMEM lane quadrants x 4 column quarters)
+constexpr int WB = 64;                       // channels per weight block side (x 2 parts = MMA M / N of 128)
+constexpr int DY_ROWS = 128, X_ROWS = 130;   // dy row r <-> t0 + r; x row r <-> t0 - 1 + r
+constexpr int DY_PLANE = DY_ROWS * 16, X_PLANE = X_ROWS * 16;
+constexpr int DY_PARTS = 2 * 8 * DY_PLANE;   // [part][plane][row][8]: the m planes directly follow the h planes
+constexpr int X_PARTS = 2 * 8 * X_PLANE;
+constexpr int DY_P = 132, X_P = 140;         // fp32 staging pitches; x window = t0-4 .. t0+131
+constexpr int WSTAGE = (WB * DY_P + WB * X_P) * 4;
+constexpr int WSM_TOTAL = 2 * WSTAGE + DY_PARTS + X_PARTS;
+
+struct WgradArgs {
+  const float* dy;         // (B,Cout,T)
+  const float* x;          // (B,Cin,T)
+  float* part;             // [nsplit][part_stride] partial weight gradients in the PARAMETER's layout
+  int64_t part_stride;
+  int64_t w_base, w_so, w_sc, w_st;
+  const uint32_t* amax_dy;
+  const uint32_t* amax_x;
+  int64_t B;
+  int Cin, Cout, T, ntt, nbc, nsplit;
+};
+
+// part[s][W(o,c,tau)] = sum over the (b, time tile) items of split s of dy[b,o,t] x[b,c,t+tau-pad].
+// grid = (Cout/64)(Cin/64) nsplit; CTA = one 64 x 64 x KW weight block and one split of the (b, tile) items.
+// Per item: [dy_h; dy_m] (M = 128) x [x_h; x_m] (N = 128) over K = 128 time steps per tap into TMEM (all four part
+// products at once, the m*m quadrant is ignored), then drained into per-thread fp32 registers (RN adds): the TMEM
+// accumulation chains stay 8 MMAs long, whatever the batch size.
+template <int KW>
+__global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a) {
+  constexpr int PAD = KW / 2;
+  extern __shared__ __align__(1024) uint8_t sm[];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ uint32_t tmem_sh;
+  uint8_t* dyp = sm + 2 * WSTAGE;
+  uint8_t* xp = dyp + DY_PARTS;
+  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+  if (tid == 0) { tc5::mbar_init(&bar, 1); tc5::mbar_init_fence(); }
+  if (w == 0) tc5::tmem_alloc512(&tmem_sh);
+  tc5::fence_before_sync();
+  __syncthreads();
+  tc5::fence_after_sync();
+  const uint32_t tmem = tmem_sh;
+  const float sdy = tc5::pow2_scale(__uint_as_float(*a.amax_dy));
+  const float sx = tc5::pow2_scale(__uint_as_float(*a.amax_x));
+  const int s = blockIdx.x % a.nsplit;
+  const int blk = blockIdx.x / a.nsplit;
+  const int bc = blk % a.nbc, bo = blk / a.nbc;
+  const int T = a.T;
+  const int64_t nitems = a.B * a.ntt;
+  uint32_t par = 0;
+  constexpr uint32_t IDESC = tc5::idesc_f16(128, 1, 1);
+  float acc[KW][16];
+#pragma unroll
+  for (int k = 0; k < KW; ++k)
+#pragma unroll
+    for (int e = 0; e < 16; ++e) acc[k][e] = 0.f;
+  const uint32_t lane_base = (uint32_t)(32 * (w & 3)) << 16;
+  const int cq = w >> 2;
+
+  auto issue_loads = [&](int64_t item, int stage) {
+    const int64_t b = item / a.ntt;
+    const int t0 = (int)(item - b * a.ntt) * TM;
+    float* ds = reinterpret_cast<float*>(sm + stage * WSTAGE);
+    float* xs = ds + WB * DY_P;
+    const float* dyb = a.dy + (b * a.Cout + (int64_t)bo * WB) * T;
+    const float* xb = a.x + (b * a.Cin + (int64_t)bc * WB) * T;
+    for (int i = tid; i < WB * 32; i += WNT) {
+      const int c = i >> 5, j = (i & 31) * 4, t = t0 + j;
+      const bool ok = t < T;
+      cp16(ds + c * DY_P + j, dyb + (int64_t)c * T + (ok ? t : 0), ok ? 16 : 0);
+    }
+    for (int i = tid; i < WB * 34; i += WNT) {
+      const int c = i / 34, j = (i - c * 34) * 4, t = t0 - 4 + j;
+      const bool ok = (t >= 0 && t < T);
+      cp16(xs + c * X_P + j, xb + (int64_t)c * T + (ok ? t : 0), ok ? 16 : 0);
+    }
+  };
+  int64_t item = s;
+  if (item < nitems) issue_loads(item, 0);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  int stage = 0;
+  bool pending = false;     // MMAs of the previous item not yet drained
+  auto drain = [&]() {
+    tc5::mbar_wait(&bar, par); par ^= 1u;
+    tc5::fence_after_sync();
+#pragma unroll
+    for (int k = 0; k < KW; ++k) {
+      float v0[16], v1[16];
+      tc5::tmem_ld16(tmem + lane_base + 128u * k + 16 * cq, v0);
+      tc5::tmem_ld16(tmem + lane_base + 128u * k + 64 + 16 * cq, v1);
+#pragma unroll
+      for (int e = 0; e < 16; ++e) acc[k][e] += v0[e] + v1[e];
+    }
+    tc5::fence_before_sync();
+  };
+  for (; item < nitems; item += a.nsplit) {
+    const int64_t nxt = item + a.nsplit;
+    if (nxt < nitems) issue_loads(nxt, stage ^ 1);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    if (pending) drain();          // the operand parts and the TMEM accumulators are free again
+    __syncthreads();
+    {
+      const float* ds = reinterpret_cast<const float*>(sm + stage * WSTAGE);
+      const float* xs = ds + WB * DY_P;
+      for (int i = tid; i < 8 * DY_ROWS; i += WNT) {
+        const int pl = i / DY_ROWS, r = i - pl * DY_ROWS;
+        __align__(16) __half hh[8], mm[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) tc5::split_f16(ds[(pl * 8 + e) * DY_P + r] * sdy, hh[e], mm[e]);
+        uint8_t* p = dyp + pl * DY_PLANE + r * 16;
+        *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(hh);
+        *reinterpret_cast<uint4*>(p + 8 * DY_PLANE) = *reinterpret_cast<const uint4*>(mm);
+      }
+      for (int i = tid; i < 8 * X_ROWS; i += WNT) {
+        const int pl = i / X_ROWS, r = i - pl * X_ROWS;
+        __align__(16) __half hh[8], mm[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) tc5::split_f16(xs[(pl * 8 + e) * X_P + r + 3] * sx, hh[e], mm[e]);
+        uint8_t* p = xp + pl * X_PLANE + r * 16;
+        *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(hh);
+        *reinterpret_cast<uint4*>(p + 8 * X_PLANE) = *reinterpret_cast<const uint4*>(mm);
+      }
+    }
+    tc5::fence_async_smem();
+    tc5::fence_before_sync();
+    __syncthreads();
+    if (w == 0) {
+      tc5::fence_after_sync();
+      const bool lead = tc5::elect_one();
+      const uint32_t sD = tc5::smem_u32(dyp), sX = tc5::smem_u32(xp);
+#pragma unroll
+      for (int k = 0; k < KW; ++k)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint64_t da = tc5::make_desc(sD + (16 * i) * 16, 128, DY_PLANE);
+          const uint64_t db = tc5::make_desc(sX + (16 * i + k - PAD + 1) * 16, 128, X_PLANE);
+          if (lead) tc5::mma_f16(tmem + 128u * k, da, db, IDESC, i ? 1u : 0u);
+        }
+      if (lead) tc5::commit(&bar);
+      __syncwarp();
+    }
+    pending = true;
+    stage ^= 1;
+  }
+  if (pending) drain();
+  __syncthreads();
+  // lanes l and l + 64 hold the h / m rows of dy for out channel l: combine through shared memory, undo the scales
+  float* red = reinterpret_cast<float*>(sm);               // [128 rows][KW * 64 + 1]
+  constexpr int RP = KW * 64 + 1;
+  {
+    const int row = 32 * (w & 3) + lane;
+#pragma unroll
+    for (int k = 0; k < KW; ++k)
+#pragma unroll
+      for (int e = 0; e < 16; ++e) red[row * RP + k * 64 + 16 * cq + e] = acc[k][e];
+  }
+  __syncthreads();
+  const float inv = 1.f / (sdy * sx);
+  float* dst = a.part + (int64_t)s * a.part_stride;
+  for (int i = tid; i < WB * WB * KW; i += WNT) {
+    const int k = i % KW, c = (i / KW) % WB, o = i / (KW * WB);
+    const float v = (red[o * RP + k * 64 + c] + red[(o + 64) * RP + k * 64 + c]) * inv;
+    dst[a.w_base + (int64_t)(bo * WB + o) * a.w_so + (int64_t)(bc * WB + c) * a.w_sc + (int64_t)k * a.w_st] = v;
+  }
+  tc5::fence_before_sync();
+  __syncthreads();
+  if (w == 0) tc5::tmem_free512(tmem);
+}
+
+// db[o] += sum_{b,t} dy[b,o,t]: one CTA per channel, fixed-order tree (deterministic), double accumulation
+__global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict__ dy, int64_t B, int Cout, int T, float* __restrict__ gB) {
+  __shared__ double sh[32];
+  const int o = blockIdx.x;
+  double acc = 0.0;
+  const int64_t n = B * (int64_t)T;
+  for (int64_t i = threadIdx.x; i < n; i += 256) {
+    const int64_t b = i / T;
+    acc += (double)dy[(b * Cout + o) * (int64_t)T + (i - b * T)];
+  }
+  acc = block_sum(acc, sh);
+  if (threadIdx.x == 0) gB[o] = (float)((double)gB[o] + acc);
+}
+
+}  // namespace ct5
+
+static inline bool wgrad_tc5_ok(int Cin, int Cout, int64_t T, int kw, const void* dy, const void* x) {
+  return (kw == 1 || kw == 3) && Cin % ct5::WB == 0 && Cout % ct5::WB == 0 && (T & 3) == 0 && T >= 4 &&
+         (((uintptr_t)dy | (uintptr_t)x) & 15) == 0;
+}
+static inline int wgrad_tc5_nsplit(int Cin, int Cout, int64_t B, int64_t T) {
+  const int64_t blocks = (int64_t)(Cout / ct5::WB) * (Cin / ct5::WB);
+  int64_t ns = cdiv(2 * (int64_t)device_sm_count(), blocks);     // ~2 waves of CTAs: balances the (b, tile) items
+  const int64_t items = B * cdiv(T, ct5::TM);
+  if (ns > items) ns = items;
+  return (int)(ns < 1 ? 1 : ns);
+}
+// floats of scratch: partials + two abs-max words
+static inline int64_t wgrad_tc5_scratch_floats(int Cin, int Cout, int kw, int64_t B, int64_t T) {
+  return (int64_t)wgrad_tc5_nsplit(Cin, Cout, B, T) * ((int64_t)Cin * Cout * kw) + 64;
+}
+
+// gW (layer layout, +=), gB (+=, may be null)
+static inline int launch_wgrad_tc5(const float* dy, const float* x, float* gW, float* gB, WView layout, int64_t B, int Cin,
+                                   int Cout, int64_t T, int kw, float* scratch, cudaStream_t st) {
+  if (B <= 0 || T <= 0) return 0;
+  const int ns = wgrad_tc5_nsplit(Cin, Cout, B, T);
+  const int64_t nW = (int64_t)Cin * Cout * kw;
+  uint32_t* words = reinterpret_cast<uint32_t*>(scratch + (int64_t)ns * nW);
+  VHMM_CUDA_CHECK(cudaMemsetAsync(words, 0, 8, st));
+  auto amax = [&](const float* p, int64_t n, uint32_t* out) {
+    int64_t blocks = cdiv(n, 1024 * 8);
+    if (blocks > 1184) blocks = 1184;
+    if (blocks < 1) blocks = 1;
+    ct5::absmax_kernel<<<(unsigned)blocks, 256, 0, st>>>(p, n, out);
+  };
+  amax(dy, B * (int64_t)Cout * T, words);
+  VHMM_LAUNCH_CHECK();
+  amax(x, B * (int64_t)Cin * T, words + 1);
+  VHMM_LAUNCH_CHECK();
+  ct5::WgradArgs a{};
+  a.dy = dy; a.x = x; a.part = scratch; a.part_stride = nW;
+  a.w_base = layout.base; a.w_so = layout.so; a.w_sc = layout.sc; a.w_st = layout.st;
+  a.amax_dy = words; a.amax_x = words + 1;
+  a.B = B; a.Cin = Cin; a.Cout = Cout; a.T = (int)T; a.ntt = (int)cdiv(T, ct5::TM); a.nbc = Cin / ct5::WB; a.nsplit = ns;
+  const unsigned grid = (unsigned)((Cout / ct5::WB) * (Cin / ct5::WB) * ns);
+  if (kw == 3) {
+    static PerDeviceOnce once;
+    if (once.pending()) {
+      VHMM_CUDA_CHECK(cudaFuncSetAttribute(ct5::wgrad_tc5_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ct5::WSM_TOTAL));
+      once.mark();
+    }
+    ct5::wgrad_tc5_kernel<3><<<grid, ct5::WNT, ct5::WSM_TOTAL, st>>>(a);
+  } else {
+    static PerDeviceOnce once;
+    if (once.pending()) {
+      VHMM_CUDA_CHECK(cudaFuncSetAttribute(ct5::wgrad_tc5_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ct5::WSM_TOTAL));
+      once.mark();
+    }
+    ct5::wgrad_tc5_kernel<1><<<grid, ct5::WNT, ct5::WSM_TOTAL, st>>>(a);
+  }
+  VHMM_LAUNCH_CHECK();
+  reduce_partials_kernel<<<(unsigned)cdiv(nW, 256), 256, 0, st>>>(scratch, nW, ns, nW, gW);
+  VHMM_LAUNCH_CHECK();
+  if (gB) {
+    ct5::bias_grad_kernel<<<(unsigned)Cout, 256, 0, st>>>(dy, B, Cout, (int)T, gB);
+    VHMM_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+}  // namespace vhmm

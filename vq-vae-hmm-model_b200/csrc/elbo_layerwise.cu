@@ -44,6 +44,83 @@ int conv1d_fwd(const float* x, const float* w, const float* bias, int64_t B, int
   return launch_conv(x, wview_fwd(w, Cin, kw), bias, nullptr, y, B, Cin, Cout, T, kw, relu ? EPI_RELU : EPI_NONE, st);
 }
 
+// ---- tensor-core layer kernels inside the layer-wise path (conv_tc5.cuh) -------------------------------------
+// The weights of the layers whose shape the tcgen05 kernels take are prepared once per call (fp16 parts in the
+// kernel's chunk image): forward view and, where the input gradient is needed, the transposed tap-flipped view.
+struct Tc5Ctx {
+  struct Entry { const float* w; int dgrad; Tc5Weights tw; };
+  Entry e[16];
+  int n = 0;
+  const Tc5Weights* find(const float* w, int dgrad) const {
+    for (int i = 0; i < n; ++i) if (e[i].w == w && e[i].dgrad == dgrad) return &e[i].tw;
+    return nullptr;
+  }
+};
+struct Tc5Layer { int param, Cin, Cout, kw, need_dgrad; };
+// (parameter, Cin, Cout, kw, dgrad needed) of the layers that can be GEMM-shaped at large widths
+static int tc5_layers(const vhmm_dims& d, Tc5Layer* L) {
+  int n = 0;
+  L[n++] = Tc5Layer{P_E2W, d.H, d.H2, 3, 1};
+  L[n++] = Tc5Layer{P_T0W, d.U, d.TH, 1, 0};
+  L[n++] = Tc5Layer{P_T2W, d.TH, d.K * d.K, 1, 1};
+  L[n++] = Tc5Layer{P_D1W, d.H, d.H, 3, 1};
+  L[n++] = Tc5Layer{P_D2W, d.H, d.H, 3, 1};
+  return n;
+}
+static bool tc5_shape(int Cin, int Cout) { return Cin % ct5::KC == 0 && Cout % ct5::TN == 0; }
+static size_t tc5_ctx_bytes(const vhmm_dims& d) {
+  Tc5Layer L[8];
+  const int n = tc5_layers(d, L);
+  size_t b = 0;
+  for (int i = 0; i < n; ++i) {
+    if (tc5_shape(L[i].Cin, L[i].Cout)) b += conv_tc5_weight_bytes(L[i].Cin, L[i].Cout, L[i].kw);
+    if (L[i].need_dgrad && tc5_shape(L[i].Cout, L[i].Cin)) b += conv_tc5_weight_bytes(L[i].Cout, L[i].Cin, L[i].kw);
+  }
+  return b + 256;
+}
+static int tc5_ctx_prepare(const vhmm_dims& d, const vhmm_params& P, bool with_dgrad, Arena& A, Tc5Ctx* ctx, cudaStream_t st) {
+  ctx->n = 0;
+  if (conv_impl_mode() == 1) return 0;
+  Tc5Layer L[8];
+  const int n = tc5_layers(d, L);
+  for (int i = 0; i < n; ++i) {
+    const float* w = P.p[L[i].param];
+    const int64_t nw = (int64_t)L[i].Cin * L[i].Cout * L[i].kw;
+    if (tc5_shape(L[i].Cin, L[i].Cout)) {
+      void* buf = A.take<uint8_t>(conv_tc5_weight_bytes(L[i].Cin, L[i].Cout, L[i].kw));
+      if (!A.ok) return 0;     // the caller reports the workspace shortfall
+      Tc5Ctx::Entry& en = ctx->e[ctx->n++];
+      en.w = w; en.dgrad = 0;
+      int rc = conv_tc5_prepare(wview_fwd(w, L[i].Cin, L[i].kw), nw, L[i].Cin, L[i].Cout, L[i].kw, buf, &en.tw, st);
+      if (rc) return rc;
+    }
+    if (with_dgrad && L[i].need_dgrad && tc5_shape(L[i].Cout, L[i].Cin)) {
+      void* buf = A.take<uint8_t>(conv_tc5_weight_bytes(L[i].Cout, L[i].Cin, L[i].kw));
+      if (!A.ok) return 0;
+      Tc5Ctx::Entry& en = ctx->e[ctx->n++];
+      en.w = w; en.dgrad = 1;
+      int rc = conv_tc5_prepare(wview_dgrad(w, L[i].Cin, L[i].kw), nw, L[i].Cout, L[i].Cin, L[i].kw, buf, &en.tw, st);
+      if (rc) return rc;
+    }
+  }
+  return 0;
+}
+// launch_conv with the tensor-core kernel where this (weight, view) was prepared and the tensors qualify
+static int cconv(const Tc5Ctx* ctx, int dgrad, const float* x, WView wv, const float* bias, const float* act, float* y, int64_t B,
+                 int Cin, int Cout, int64_t T, int kw, int epi, cudaStream_t st) {
+  const Tc5Weights* tw = ctx ? ctx->find(wv.w, dgrad) : nullptr;
+  if (tw && conv_tc5_ok(Cin, Cout, T, kw, x, y) && (!act || (((uintptr_t)act) & 15) == 0))
+    return launch_conv_tc5(x, *tw, bias, act, y, B, Cin, Cout, T, kw, epi, st);
+  VHMM_REQUIRE(conv_impl_mode() != 2 || !tc5_shape(Cin, Cout), VHMM_E_DIMS, "conv: VHMM_CONV_TC5 selected but T %% 4 != 0 or unaligned tensors");
+  return launch_conv(x, wv, bias, act, y, B, Cin, Cout, T, kw, epi, st);
+}
+static int cwgrad(const float* dy, const float* x, float* gW, float* gB, WView layout, int64_t B, int Cin, int Cout, int64_t T,
+                  int kw, float* scratch, cudaStream_t st) {
+  if (conv_impl_mode() != 1 && wgrad_tc5_ok(Cin, Cout, T, kw, dy, x))
+    return launch_wgrad_tc5(dy, x, gW, gB, layout, B, Cin, Cout, T, kw, scratch, st);
+  return launch_wgrad(dy, x, gW, gB, layout, B, Cin, Cout, T, kw, scratch, st);
+}
+
 struct LayerwiseSizes {
   int64_t per_step_fwd;   // floats per (sequence, step) kept by the forward pass
   int64_t per_step_bwd;   // extra floats per step for the backward pass
@@ -65,6 +142,18 @@ static LayerwiseSizes layerwise_sizes(const vhmm_dims& d) {
   v = wgrad_scratch_floats(d.K, d.H, 1, BIG); m = v > m ? v : m;
   v = wgrad_scratch_floats(d.H, d.H, 3, BIG); m = v > m ? v : m;
   v = wgrad_scratch_floats(d.H, 2 * d.C, 1, BIG); m = v > m ? v : m;
+  // tensor-core weight gradients keep one partial per (weight block, split): upper bound over the batch size
+  auto tc5s = [&](int Cin, int Cout, int kw) {
+    if (Cin % ct5::WB || Cout % ct5::WB) return (int64_t)0;
+    const int64_t blocks = (int64_t)(Cout / ct5::WB) * (Cin / ct5::WB);
+    return cdiv(2 * (int64_t)device_sm_count(), blocks) * ((int64_t)Cin * Cout * kw) + 64;
+  };
+  v = tc5s(d.H, d.H2, 3); m = v > m ? v : m;
+  v = tc5s(d.TH, d.K * d.K, 1); m = v > m ? v : m;
+  v = tc5s(d.H, d.H, 3); m = v > m ? v : m;
+  v = tc5s(d.H2, d.K, 1); m = v > m ? v : m;
+  v = tc5s(d.K, d.H, 1); m = v > m ? v : m;
+  v = tc5s(d.U, d.TH, 1); m = v > m ? v : m;
   s.scratch = m;
   return s;
 }
@@ -75,6 +164,7 @@ static size_t fixed_bytes(const vhmm_dims& d, int64_t T) {
   bytes += align_up(sizeof(float) * KMAX, 256);                        // log_pi
   bytes += align_up(sizeof(double) * KMAX, 256);                       // qsum
   bytes += align_up(sizeof(float) * (size_t)s.scratch, 256);
+  bytes += tc5_ctx_bytes(d);                                           // prepared tensor-core weights
   return bytes + 4096;
 }
 
@@ -101,21 +191,21 @@ size_t layerwise_workspace_bytes(int op, const vhmm_dims& d, int64_t B, int64_t 
 
 // ---- forward building blocks (whole-tensor, caller provides scratch) -------------------
 static int encoder_chain(const vhmm_dims& d, const vhmm_params& P, const float* x, int64_t B,
-                         int64_t T, float* h1, float* h2, float* logits, cudaStream_t st) {
+                         int64_t T, float* h1, float* h2, float* logits, cudaStream_t st, const Tc5Ctx* ctx = nullptr) {
   int rc;
   if ((rc = launch_conv(x, wview_fwd(P.p[P_E1W], d.C, 3), P.p[P_E1B], nullptr, h1, B, d.C, d.H, T, 3, EPI_RELU, st))) return rc;
-  if ((rc = launch_conv(h1, wview_fwd(P.p[P_E2W], d.H, 3), P.p[P_E2B], nullptr, h2, B, d.H, d.H2, T, 3, EPI_RELU, st))) return rc;
+  if ((rc = cconv(ctx, 0, h1, wview_fwd(P.p[P_E2W], d.H, 3), P.p[P_E2B], nullptr, h2, B, d.H, d.H2, T, 3, EPI_RELU, st))) return rc;
   return launch_conv(h2, wview_fwd(P.p[P_E3W], d.H2, 1), P.p[P_E3B], nullptr, logits, B, d.H2, d.K, T, 1, EPI_NONE, st);
 }
 
 // e (B,H,T) = E^T q ; g1, g2 ; out rows [row0,row0+nrows) of to_params into `out`
 static int decoder_chain(const vhmm_dims& d, const vhmm_params& P, const float* q, int64_t B,
-                         int64_t T, float* e, float* g1, float* g2, cudaStream_t st) {
+                         int64_t T, float* e, float* g1, float* g2, cudaStream_t st, const Tc5Ctx* ctx = nullptr) {
   int rc;
   WView emb{P.p[P_EMB], 0, 1, d.H, 0};  // W(o=d, c=k) = E[k*H + d]   (VQ_VAE_HMM_fixed.py:83)
   if ((rc = launch_conv(q, emb, nullptr, nullptr, e, B, d.K, d.H, T, 1, EPI_NONE, st))) return rc;
-  if ((rc = launch_conv(e, wview_fwd(P.p[P_D1W], d.H, 3), P.p[P_D1B], nullptr, g1, B, d.H, d.H, T, 3, EPI_RELU, st))) return rc;
-  return launch_conv(g1, wview_fwd(P.p[P_D2W], d.H, 3), P.p[P_D2B], nullptr, g2, B, d.H, d.H, T, 3, EPI_RELU, st);
+  if ((rc = cconv(ctx, 0, e, wview_fwd(P.p[P_D1W], d.H, 3), P.p[P_D1B], nullptr, g1, B, d.H, d.H, T, 3, EPI_RELU, st))) return rc;
+  return cconv(ctx, 0, g1, wview_fwd(P.p[P_D2W], d.H, 3), P.p[P_D2B], nullptr, g2, B, d.H, d.H, T, 3, EPI_RELU, st);
 }
 
 int layerwise_encoder_fwd(const vhmm_dims& d, const vhmm_params& P, const float* x, int64_t B,
@@ -194,6 +284,11 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
   float* log_pi = A.take<float>(KMAX);
   double* qsum = A.take<double>(KMAX);
   float* scratch = A.take<float>((size_t)S.scratch);
+  Tc5Ctx ctx;
+  {
+    int rc0 = tc5_ctx_prepare(d, P, grads != nullptr, A, &ctx, st);
+    if (rc0) return rc0;
+  }
   VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "elbo: workspace %zu too small (fixed part %zu)", ws_bytes, A.used);
   const int64_t per_step = S.per_step_fwd + (grads ? S.per_step_bwd : 0);
   const size_t left = (ws_bytes - A.used > 64 * 256) ? ws_bytes - A.used - 64 * 256 : 0;
@@ -232,20 +327,20 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
     const float* uc = u + b0 * U * T;
     const int64_t* Lc = lengths + b0;
     // ---------------- forward ----------------
-    RC(encoder_chain(d, P, xc, nb, T, h1, h2, lg, st));
+    RC(encoder_chain(d, P, xc, nb, T, h1, h2, lg, st, &ctx));
     {
       dim3 g((unsigned)cdiv(T, 256), (unsigned)nb);
       softmax_kernel<<<g, 256, 0, st>>>(lg, q, lq, K, (int)T);
       VHMM_LAUNCH_CHECK();
     }
-    RC(launch_conv(uc, wview_fwd(P.p[P_T0W], U, 1), P.p[P_T0B], nullptr, a, nb, U, TH, T, 1, EPI_RELU, st));
-    RC(launch_conv(a, wview_fwd(P.p[P_T2W], TH, 1), P.p[P_T2B], nullptr, M, nb, TH, K2, T, 1, EPI_NONE, st));
+    RC(cconv(&ctx, 0, uc, wview_fwd(P.p[P_T0W], U, 1), P.p[P_T0B], nullptr, a, nb, U, TH, T, 1, EPI_RELU, st));
+    RC(cconv(&ctx, 0, a, wview_fwd(P.p[P_T2W], TH, 1), P.p[P_T2B], nullptr, M, nb, TH, K2, T, 1, EPI_NONE, st));
     {
       dim3 g((unsigned)cdiv(T, 256), (unsigned)K, (unsigned)nb);
       row_logsoftmax_kernel<<<g, 256, 0, st>>>(M, K, (int)T);
       VHMM_LAUNCH_CHECK();
     }
-    RC(decoder_chain(d, P, q, nb, T, e, g1, g2, st));
+    RC(decoder_chain(d, P, q, nb, T, e, g1, g2, st, &ctx));
     RC(launch_conv(g2, wview_fwd(P.p[P_DPW], H, 1), P.p[P_DPB], nullptr, p, nb, H, 2 * C, T, 1, EPI_NONE, st));
     {
       dim3 g((unsigned)cdiv(T, 256), (unsigned)nb);
@@ -259,15 +354,15 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
     }
     if (!grads) continue;
     // ---------------- backward: decoder ----------------
-    RC(launch_wgrad(dp, g2, grads + off[P_DPW], grads + off[P_DPB], wview_fwd(nullptr, H, 1), nb, H, 2 * C, T, 1, scratch, st));
+    RC(cwgrad(dp, g2, grads + off[P_DPW], grads + off[P_DPB], wview_fwd(nullptr, H, 1), nb, H, 2 * C, T, 1, scratch, st));
     RC(launch_conv(dp, wview_dgrad(P.p[P_DPW], H, 1), nullptr, g2, dg2, nb, 2 * C, H, T, 1, EPI_MASK, st));
-    RC(launch_wgrad(dg2, g1, grads + off[P_D2W], grads + off[P_D2B], wview_fwd(nullptr, H, 3), nb, H, H, T, 3, scratch, st));
-    RC(launch_conv(dg2, wview_dgrad(P.p[P_D2W], H, 3), nullptr, g1, dg1, nb, H, H, T, 3, EPI_MASK, st));
-    RC(launch_wgrad(dg1, e, grads + off[P_D1W], grads + off[P_D1B], wview_fwd(nullptr, H, 3), nb, H, H, T, 3, scratch, st));
-    RC(launch_conv(dg1, wview_dgrad(P.p[P_D1W], H, 3), nullptr, nullptr, de, nb, H, H, T, 3, EPI_NONE, st));
+    RC(cwgrad(dg2, g1, grads + off[P_D2W], grads + off[P_D2B], wview_fwd(nullptr, H, 3), nb, H, H, T, 3, scratch, st));
+    RC(cconv(&ctx, 1, dg2, wview_dgrad(P.p[P_D2W], H, 3), nullptr, g1, dg1, nb, H, H, T, 3, EPI_MASK, st));
+    RC(cwgrad(dg1, e, grads + off[P_D1W], grads + off[P_D1B], wview_fwd(nullptr, H, 3), nb, H, H, T, 3, scratch, st));
+    RC(cconv(&ctx, 1, dg1, wview_dgrad(P.p[P_D1W], H, 3), nullptr, nullptr, de, nb, H, H, T, 3, EPI_NONE, st));
     {
       WView embL{nullptr, 0, 1, H, 0};  // dE[k,d] stored at k*H + d  with (o=d, c=k)
-      RC(launch_wgrad(de, q, grads + off[P_EMB], nullptr, embL, nb, K, H, T, 1, scratch, st));
+      RC(cwgrad(de, q, grads + off[P_EMB], nullptr, embL, nb, K, H, T, 1, scratch, st));
       WView embT{P.p[P_EMB], 0, H, 1, 0};  // dq[k,t] = sum_d E[k,d] de[d,t]: W(o=k, c=d)
       RC(launch_conv(de, embT, nullptr, nullptr, dqd, nb, H, K, T, 1, EPI_NONE, st));
     }
@@ -277,15 +372,15 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
       VHMM_LAUNCH_CHECK();
     }
     // ---------------- backward: encoder ----------------
-    RC(launch_wgrad(dl, h2, grads + off[P_E3W], grads + off[P_E3B], wview_fwd(nullptr, H2, 1), nb, H2, K, T, 1, scratch, st));
+    RC(cwgrad(dl, h2, grads + off[P_E3W], grads + off[P_E3B], wview_fwd(nullptr, H2, 1), nb, H2, K, T, 1, scratch, st));
     RC(launch_conv(dl, wview_dgrad(P.p[P_E3W], H2, 1), nullptr, h2, dh2, nb, K, H2, T, 1, EPI_MASK, st));
-    RC(launch_wgrad(dh2, h1, grads + off[P_E2W], grads + off[P_E2B], wview_fwd(nullptr, H, 3), nb, H, H2, T, 3, scratch, st));
-    RC(launch_conv(dh2, wview_dgrad(P.p[P_E2W], H, 3), nullptr, h1, dh1, nb, H2, H, T, 3, EPI_MASK, st));
-    RC(launch_wgrad(dh1, xc, grads + off[P_E1W], grads + off[P_E1B], wview_fwd(nullptr, C, 3), nb, C, H, T, 3, scratch, st));
+    RC(cwgrad(dh2, h1, grads + off[P_E2W], grads + off[P_E2B], wview_fwd(nullptr, H, 3), nb, H, H2, T, 3, scratch, st));
+    RC(cconv(&ctx, 1, dh2, wview_dgrad(P.p[P_E2W], H, 3), nullptr, h1, dh1, nb, H2, H, T, 3, EPI_MASK, st));
+    RC(cwgrad(dh1, xc, grads + off[P_E1W], grads + off[P_E1B], wview_fwd(nullptr, C, 3), nb, C, H, T, 3, scratch, st));
     // ---------------- backward: prior ----------------
-    RC(launch_wgrad(dM, a, grads + off[P_T2W], grads + off[P_T2B], wview_fwd(nullptr, TH, 1), nb, TH, K2, T, 1, scratch, st));
-    RC(launch_conv(dM, wview_dgrad(P.p[P_T2W], TH, 1), nullptr, a, da, nb, K2, TH, T, 1, EPI_MASK, st));
-    RC(launch_wgrad(da, uc, grads + off[P_T0W], grads + off[P_T0B], wview_fwd(nullptr, U, 1), nb, U, TH, T, 1, scratch, st));
+    RC(cwgrad(dM, a, grads + off[P_T2W], grads + off[P_T2B], wview_fwd(nullptr, TH, 1), nb, TH, K2, T, 1, scratch, st));
+    RC(cconv(&ctx, 1, dM, wview_dgrad(P.p[P_T2W], TH, 1), nullptr, a, da, nb, K2, TH, T, 1, EPI_MASK, st));
+    RC(cwgrad(da, uc, grads + off[P_T0W], grads + off[P_T0B], wview_fwd(nullptr, U, 1), nb, U, TH, T, 1, scratch, st));
   }
 #undef RC
   finalize_prior_kernel<<<1, 32, 0, st>>>(log_pi, qsum, norms, betaf, K, sums,
