@@ -28,7 +28,7 @@
 namespace vhmm {
 namespace ct5 {
 
-constexpr int NT = 256;                 // threads per CTA
+constexpr int NT = 512;                 // threads per CTA (16 warps)
 constexpr int TM = 128;                 // time steps per tile (MMA M)
 constexpr int TN = 128;                 // output channels per tile (MMA N)
 constexpr int KC = 16;                  // input channels per chunk (one MMA K step = 2 planes of 8)
@@ -200,13 +200,13 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
     }
     for (int kc = (nkc >= 2 ? nkc - 2 : 0); kc < nkc; ++kc) { tc5::mbar_wait(&bar[kc & 1], par[kc & 1]); par[kc & 1] ^= 1u; }
     tc5::fence_after_sync();
-    {   // epilogue: TMEM lane = time row; warp w reads lane quadrant w & 3, columns [64 (w >> 2), +64)
+    {   // epilogue: TMEM lane = time row; warp w reads lane quadrant w & 3, columns [32 (w >> 2), +32)
       const uint32_t lane_base = (uint32_t)(32 * (w & 3)) << 16;
       const int t = t0 + 32 * (w & 3) + lane;
       const int nsets = (nkc * KW < 3) ? nkc * KW : 3;
 #pragma unroll 1
-      for (int cgp = 0; cgp < 4; ++cgp) {
-        const int col = 64 * (w >> 2) + 16 * cgp;
+      for (int cgp = 0; cgp < 2; ++cgp) {
+        const int col = 32 * (w >> 2) + 16 * cgp;
         float v[16], s[16];
         tc5::tmem_ld16(tmem + lane_base + SMALL + col, s);
         tc5::tmem_ld16(tmem + lane_base + HH0 + col, v);
@@ -223,14 +223,23 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
           for (int e = 0; e < 16; ++e) v[e] += v2[e];
         }
         if (t < T) {
+          // every load (bias, ReLU mask) is issued BEFORE the first store: y, act and bias are plain pointers, so a load
+          // placed after a store would have to wait for it (possible aliasing) and the 16 columns would serialise on
+          // global-memory latency
+          const int64_t off0 = (b * a.Cout + ct * TN + col) * (int64_t)T + t;
+          float bz[16], mk[16] = {};
+#pragma unroll
+          for (int e = 0; e < 16; ++e) bz[e] = a.bias ? __ldg(a.bias + ct * TN + col + e) : 0.f;
+          if (a.epi == EPI_MASK) {
+#pragma unroll
+            for (int e = 0; e < 16; ++e) mk[e] = __ldg(a.act + off0 + (int64_t)e * T);
+          }
 #pragma unroll
           for (int e = 0; e < 16; ++e) {
-            const int o = ct * TN + col + e;
-            const int64_t off = (b * a.Cout + o) * (int64_t)T + t;
-            float r = (v[e] + s[e]) * inv + (a.bias ? a.bias[o] : 0.f);
+            float r = (v[e] + s[e]) * inv + bz[e];
             if (a.epi == EPI_RELU) r = fmaxf(r, 0.f);
-            else if (a.epi == EPI_MASK) r = a.act[off] > 0.f ? r : 0.f;
-            a.y[off] = r;
+            else if (a.epi == EPI_MASK) r = mk[e] > 0.f ? r : 0.f;
+            a.y[off0 + (int64_t)e * T] = r;
           }
         }
       }
@@ -499,18 +508,25 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a) {
   if (w == 0) tc5::tmem_free512(tmem);
 }
 
-// db[o] += sum_{b,t} dy[b,o,t]: one CTA per channel, fixed-order tree (deterministic), double accumulation
-__global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict__ dy, int64_t B, int Cout, int T, float* __restrict__ gB) {
+// partial[s][o] = sum over the sequences b = s (mod nsplit) and all t of dy[b,o,t]; grid (Cout, nsplit), 128-bit loads.
+// The partials are added to gB in a fixed order by reduce_partials_kernel (deterministic).
+__global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict__ dy, int64_t B, int Cout, int T, int nsplit,
+                                                        float* __restrict__ partial) {
   __shared__ double sh[32];
-  const int o = blockIdx.x;
+  const int o = blockIdx.x, s = blockIdx.y;
+  const int T4 = T >> 2;
   double acc = 0.0;
-  const int64_t n = B * (int64_t)T;
-  for (int64_t i = threadIdx.x; i < n; i += 256) {
-    const int64_t b = i / T;
-    acc += (double)dy[(b * Cout + o) * (int64_t)T + (i - b * T)];
+  for (int64_t b = s; b < B; b += nsplit) {
+    const float4* row = reinterpret_cast<const float4*>(dy + (b * Cout + o) * (int64_t)T);
+    float a = 0.f;
+    for (int i = threadIdx.x; i < T4; i += 256) {
+      const float4 v = row[i];
+      a += (v.x + v.y) + (v.z + v.w);
+    }
+    acc += (double)a;
   }
   acc = block_sum(acc, sh);
-  if (threadIdx.x == 0) gB[o] = (float)((double)gB[o] + acc);
+  if (threadIdx.x == 0) partial[(int64_t)s * Cout + o] = (float)acc;
 }
 
 }  // namespace ct5
@@ -528,7 +544,7 @@ static inline int wgrad_tc5_nsplit(int Cin, int Cout, int64_t B, int64_t T) {
 }
 // floats of scratch: partials + two abs-max words
 static inline int64_t wgrad_tc5_scratch_floats(int Cin, int Cout, int kw, int64_t B, int64_t T) {
-  return (int64_t)wgrad_tc5_nsplit(Cin, Cout, B, T) * ((int64_t)Cin * Cout * kw) + 64;
+  return (int64_t)wgrad_tc5_nsplit(Cin, Cout, B, T) * ((int64_t)Cin * Cout * kw) + 64 + 32 * (int64_t)Cout;
 }
 
 // gW (layer layout, +=), gB (+=, may be null)
@@ -573,8 +589,12 @@ static inline int launch_wgrad_tc5(const float* dy, const float* x, float* gW, f
   VHMM_LAUNCH_CHECK();
   reduce_partials_kernel<<<(unsigned)cdiv(nW, 256), 256, 0, st>>>(scratch, nW, ns, nW, gW);
   VHMM_LAUNCH_CHECK();
-  if (gB) {
-    ct5::bias_grad_kernel<<<(unsigned)Cout, 256, 0, st>>>(dy, B, Cout, (int)T, gB);
+  if (gB) {   // (T % 4 == 0 and 16-byte alignment were checked by wgrad_tc5_ok)
+    float* bpart = scratch + (int64_t)ns * nW + 64;
+    int nb = B < 32 ? (int)B : 32;
+    ct5::bias_grad_kernel<<<dim3((unsigned)Cout, (unsigned)nb), 256, 0, st>>>(dy, B, Cout, (int)T, nb, bpart);
+    VHMM_LAUNCH_CHECK();
+    reduce_partials_kernel<<<(unsigned)cdiv(Cout, 256), 256, 0, st>>>(bpart, Cout, nb, Cout, gB);
     VHMM_LAUNCH_CHECK();
   }
   return 0;

@@ -111,7 +111,7 @@ static int cconv(const Tc5Ctx* ctx, int dgrad, const float* x, WView wv, const f
   const Tc5Weights* tw = ctx ? ctx->find(wv.w, dgrad) : nullptr;
   if (tw && conv_tc5_ok(Cin, Cout, T, kw, x, y) && (!act || (((uintptr_t)act) & 15) == 0))
     return launch_conv_tc5(x, *tw, bias, act, y, B, Cin, Cout, T, kw, epi, st);
-  VHMM_REQUIRE(conv_impl_mode() != 2 || !tc5_shape(Cin, Cout), VHMM_E_DIMS, "conv: VHMM_CONV_TC5 selected but T %% 4 != 0 or unaligned tensors");
+  VHMM_REQUIRE(conv_impl_mode() != 2 || !ctx || !tc5_shape(Cin, Cout), VHMM_E_DIMS, "conv: VHMM_CONV_TC5 selected but T %% 4 != 0 or unaligned tensors");
   return launch_conv(x, wv, bias, act, y, B, Cin, Cout, T, kw, epi, st);
 }
 static int cwgrad(const float* dy, const float* x, float* gW, float* gB, WView layout, int64_t B, int Cin, int Cout, int64_t T,
@@ -146,7 +146,7 @@ static LayerwiseSizes layerwise_sizes(const vhmm_dims& d) {
   auto tc5s = [&](int Cin, int Cout, int kw) {
     if (Cin % ct5::WB || Cout % ct5::WB) return (int64_t)0;
     const int64_t blocks = (int64_t)(Cout / ct5::WB) * (Cin / ct5::WB);
-    return cdiv(2 * (int64_t)device_sm_count(), blocks) * ((int64_t)Cin * Cout * kw) + 64;
+    return cdiv(2 * (int64_t)device_sm_count(), blocks) * ((int64_t)Cin * Cout * kw) + 64 + 32 * (int64_t)Cout;
   };
   v = tc5s(d.H, d.H2, 3); m = v > m ? v : m;
   v = tc5s(d.TH, d.K * d.K, 1); m = v > m ? v : m;
@@ -174,13 +174,13 @@ size_t layerwise_workspace_bytes(int op, const vhmm_dims& d, int64_t B, int64_t 
   const size_t slack = 64 * 256;
   switch (op) {
     case VHMM_OP_ENCODER_FWD:
-      return (size_t)B * T * (d.H + d.H2 + d.K) * 4 + slack;
+      return (size_t)B * T * (d.H + d.H2 + d.K) * 4 + slack + tc5_ctx_bytes(d);
     case VHMM_OP_PRIOR_FWD:
-      return (size_t)B * T * (d.TH + (int64_t)d.K * d.K) * 4 + slack;
+      return (size_t)B * T * (d.TH + (int64_t)d.K * d.K) * 4 + slack + tc5_ctx_bytes(d);
     case VHMM_OP_DECODER_FWD:
-      return (size_t)B * T * (3 * (int64_t)d.H) * 4 + slack;
+      return (size_t)B * T * (3 * (int64_t)d.H) * 4 + slack + tc5_ctx_bytes(d);
     case VHMM_OP_EMISSION_TABLE:
-      return (size_t)d.K * T * (3 * (int64_t)d.H + d.K + 2 * d.C) * 4 + slack;
+      return (size_t)d.K * T * (3 * (int64_t)d.H + d.K + 2 * d.C) * 4 + slack + tc5_ctx_bytes(d);
     case VHMM_OP_ELBO:
       return fixed_bytes(d, T) + (size_t)Bc * T * (s.per_step_fwd + s.per_step_bwd) * 4 +
              (size_t)Bc * cdiv(T, 256) * 32 + slack;
@@ -215,11 +215,13 @@ int layerwise_encoder_fwd(const vhmm_dims& d, const vhmm_params& P, const float*
   float* h1 = A.take<float>((size_t)B * d.H * T);
   float* h2 = A.take<float>((size_t)B * d.H2 * T);
   float* lg = logits ? logits : A.take<float>((size_t)B * d.K * T);
+  Tc5Ctx ctx;
+  { int rc0 = tc5_ctx_prepare(d, P, false, A, &ctx, st); if (rc0) return rc0; }
   VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "encoder_fwd: workspace %zu < %zu", ws_bytes, A.used);
   for (int64_t b0 = 0; b0 < B; b0 += kMaxChunk) {
     int64_t nb = B - b0 < kMaxChunk ? B - b0 : kMaxChunk;
     int rc = encoder_chain(d, P, x + b0 * d.C * T, nb, T, h1 + b0 * d.H * T, h2 + b0 * d.H2 * T,
-                           lg + b0 * d.K * T, st);
+                           lg + b0 * d.K * T, st, &ctx);
     if (rc) return rc;
     if (q) {
       dim3 g((unsigned)cdiv(T, 256), (unsigned)nb);
@@ -238,14 +240,16 @@ int layerwise_prior_fwd(const vhmm_dims& d, const vhmm_params& P, const float* u
   const int K2 = d.K * d.K;
   float* a = A.take<float>((size_t)B * d.TH * T);
   float* M = A.take<float>((size_t)B * K2 * T);
+  Tc5Ctx ctx;
+  { int rc0 = tc5_ctx_prepare(d, P, false, A, &ctx, st); if (rc0) return rc0; }
   VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "prior_fwd: workspace %zu < %zu", ws_bytes, A.used);
   if (log_pi) {
     log_pi_kernel<<<1, 32, 0, st>>>(P.p[P_LOGPRIOR], log_pi, d.K);
     VHMM_LAUNCH_CHECK();
   }
   int rc;
-  if ((rc = launch_conv(u, wview_fwd(P.p[P_T0W], d.U, 1), P.p[P_T0B], nullptr, a, B, d.U, d.TH, T, 1, EPI_RELU, st))) return rc;
-  if ((rc = launch_conv(a, wview_fwd(P.p[P_T2W], d.TH, 1), P.p[P_T2B], nullptr, M, B, d.TH, K2, T, 1, EPI_NONE, st))) return rc;
+  if ((rc = cconv(&ctx, 0, u, wview_fwd(P.p[P_T0W], d.U, 1), P.p[P_T0B], nullptr, a, B, d.U, d.TH, T, 1, EPI_RELU, st))) return rc;
+  if ((rc = cconv(&ctx, 0, a, wview_fwd(P.p[P_T2W], d.TH, 1), P.p[P_T2B], nullptr, M, B, d.TH, K2, T, 1, EPI_NONE, st))) return rc;
   for (int64_t b0 = 0; b0 < B; b0 += kMaxChunk) {
     int64_t nb = B - b0 < kMaxChunk ? B - b0 : kMaxChunk;
     dim3 g((unsigned)cdiv(T, 128), (unsigned)d.K, (unsigned)nb);
@@ -262,9 +266,11 @@ int layerwise_decoder_fwd(const vhmm_dims& d, const vhmm_params& P, const float*
   float* e = A.take<float>((size_t)B * d.H * T);
   float* g1 = A.take<float>((size_t)B * d.H * T);
   float* g2 = A.take<float>((size_t)B * d.H * T);
+  Tc5Ctx ctx;
+  { int rc0 = tc5_ctx_prepare(d, P, false, A, &ctx, st); if (rc0) return rc0; }
   VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "decoder_fwd: workspace %zu < %zu", ws_bytes, A.used);
   int rc;
-  if ((rc = decoder_chain(d, P, q, B, T, e, g1, g2, st))) return rc;
+  if ((rc = decoder_chain(d, P, q, B, T, e, g1, g2, st, &ctx))) return rc;
   // to_params rows [0,C) -> mu, rows [C,2C) -> logvar (VQ_VAE_HMM_fixed.py:87-90)
   if ((rc = launch_conv(g2, wview_fwd(P.p[P_DPW], d.H, 1), P.p[P_DPB], nullptr, mu, B, d.H, d.C, T, 1, EPI_NONE, st))) return rc;
   return launch_conv(g2, wview_fwd(P.p[P_DPW] + (int64_t)d.C * d.H, d.H, 1), P.p[P_DPB] + d.C, nullptr, logvar, B, d.H, d.C, T, 1, EPI_NONE, st);
