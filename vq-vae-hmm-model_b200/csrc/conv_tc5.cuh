@@ -96,26 +96,44 @@ struct ConvArgs {
   float* y;                // (B,Cout,T)
   const uint32_t* amax_x;  // device: |x| max (float bits)
   const uint32_t* amax_w;  // device: |W| max
+  uint32_t* amax_y;        // device, or null: receives |y| max (the next layer's operand scale comes for free)
   int64_t B;
   int Cin, Cout, T, epi;
   int ntt, nct;            // time tiles per sequence, out-channel tiles
   int64_t nitems;
 };
 
-// y = epi(bias + conv_KW(x, W)); requires Cin % 16 == 0, Cout % 128 == 0, T % 4 == 0, x 16-byte aligned
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(tc5::smem_u32(bar)) : "memory");
+}
+// the barrier receives one arrival when all cp.async issued so far by this thread have landed (count pre-charged: .noinc)
+__device__ __forceinline__ void cp_async_arrive(uint64_t* bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" :: "r"(tc5::smem_u32(bar)) : "memory");
+}
+
+// y = epi(bias + conv_KW(x, W)); requires Cin % 16 == 0, Cout % 128 == 0, T % 4 == 0, x 16-byte aligned.
+// Warp-specialised main loop over the K chunks (global chunk counter g, continuing across the CTA's work items):
+//   warps 1..15  load chunk g+2 (cp.async into stage (g+2) % 4, completion -> landed[stage]) and convert chunk g from its
+//                fp32 staging to the fp16 parts buffer g & 1, then arrive on full[g & 1]
+//   warp 0       waits for full[g & 1], issues the 3 KW MMAs of chunk g, commits them to empty[g & 1]
+// A parts buffer / stage is rewritten only after empty[] of the chunk that last read it; no CTA-wide barrier inside the
+// loop (the first build had two per chunk: tensor pipe 23 % active, 0.4 eligible warps per cycle).
 template <int KW>
 __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
   constexpr int PAD = KW / 2;
+  constexpr int NLD = NT - 32;                       // loader / converter threads
   using S = Sm<KW>;
   extern __shared__ __align__(1024) uint8_t sm[];
-  // one mbarrier per parts buffer: chunk k commits to bar[k & 1] and is waited for before chunk k + 2 reuses the buffer, so a
-  // waiter is never more than one phase behind (a single barrier would alias phases k and k + 2 of the same parity)
-  __shared__ __align__(8) uint64_t bar[2];
+  __shared__ __align__(8) uint64_t landed[STAGES], full[2], empty[2];
   __shared__ uint32_t tmem_sh;
   uint8_t* parts = sm + STAGES * S::STAGE;
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   for (int i = tid; i < 2 * ABYTES / 4; i += NT) reinterpret_cast<uint32_t*>(parts)[i] = 0u;
-  if (tid == 0) { tc5::mbar_init(&bar[0], 1); tc5::mbar_init(&bar[1], 1); tc5::mbar_init_fence(); }
+  if (tid == 0) {
+    for (int i = 0; i < STAGES; ++i) tc5::mbar_init(&landed[i], NLD);
+    for (int i = 0; i < 2; ++i) { tc5::mbar_init(&full[i], NLD); tc5::mbar_init(&empty[i], 1); }
+    tc5::mbar_init_fence();
+  }
   if (w == 0) tc5::tmem_alloc512(&tmem_sh);
   tc5::fence_before_sync();
   __syncthreads();
@@ -126,61 +144,24 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
   const float inv = 1.f / (sx * sw);
   const int nkc = a.Cin / KC;
   const int T = a.T;
-  uint32_t par[2] = {0u, 0u};
   constexpr uint32_t IDESC = tc5::idesc_f16(TN, 0, 0);
+  uint32_t g0 = 0;                                   // global index of this item's chunk 0
 
-  for (int64_t item = blockIdx.x; item < a.nitems; item += gridDim.x) {
+  for (int64_t item = blockIdx.x; item < a.nitems; item += gridDim.x, g0 += (uint32_t)nkc) {
     const int ct = (int)(item % a.nct);
     const int64_t bt = item / a.nct;
     const int tt = (int)(bt % a.ntt);
     const int64_t b = bt / a.ntt;
     const int t0 = tt * TM;
-    const float* xb = a.x + b * (int64_t)a.Cin * T;
-    const uint8_t* wct = a.Wg + (int64_t)ct * nkc * S::WBYTES;
-
-    auto issue_loads = [&](int kc) {
-      uint8_t* st = sm + (kc % STAGES) * S::STAGE;
-      const uint8_t* wsrc = wct + (int64_t)kc * S::WBYTES;
-      for (int i = tid; i < S::WBYTES / 16; i += NT) cp16(st + i * 16, wsrc + i * 16, 16);
-      float* xs = reinterpret_cast<float*>(st + S::WBYTES);
-      for (int i = tid; i < KC * (XW / 4); i += NT) {
-        const int c = i / (XW / 4), j = (i - c * (XW / 4)) * 4, t = t0 - 4 + j;
-        const bool ok = (t >= 0 && t < T);               // T % 4 == 0: a granule is inside or outside as a whole
-        cp16(xs + c * XP + j, xb + (int64_t)(kc * KC + c) * T + (ok ? t : 0), ok ? 16 : 0);
-      }
-    };
-    issue_loads(0);
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    if (nkc > 1) issue_loads(1);
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    for (int kc = 0; kc < nkc; ++kc) {
-      // the stage about to be refilled and the parts buffer about to be rewritten were last read by the MMAs of chunk kc-2
-      if (kc >= 2) { tc5::mbar_wait(&bar[kc & 1], par[kc & 1]); par[kc & 1] ^= 1u; }
-      if (kc + 2 < nkc) issue_loads(kc + 2);
-      asm volatile("cp.async.commit_group;" ::: "memory");
-      asm volatile("cp.async.wait_group 2;" ::: "memory");
-      __syncthreads();
-      {   // fp32 -> fp16 parts of chunk kc: item (plane, row) = 8 channels of one time step
-        const float* xs = reinterpret_cast<const float*>(sm + (kc % STAGES) * S::STAGE + S::WBYTES);
-        uint8_t* pb = parts + (kc & 1) * ABYTES;
-        for (int i = tid; i < 2 * ROWS; i += NT) {
-          const int pl = i / ROWS, r = i - pl * ROWS;
-          __align__(16) __half hh[8], mm[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) tc5::split_f16(xs[(pl * 8 + e) * XP + r + 3] * sx, hh[e], mm[e]);
-          uint8_t* p = pb + pl * PLANE + r * 16;
-          *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(hh);
-          *reinterpret_cast<uint4*>(p + APART) = *reinterpret_cast<const uint4*>(mm);
-        }
-      }
-      tc5::fence_async_smem();
-      tc5::fence_before_sync();
-      __syncthreads();
-      if (w == 0) {
+    if (w == 0) {
+      // ---- MMA issuer -------------------------------------------------------------------------------------
+      for (int kc = 0; kc < nkc; ++kc) {
+        const uint32_t g = g0 + (uint32_t)kc;
+        tc5::mbar_wait(&full[g & 1], (g >> 1) & 1u);
         tc5::fence_after_sync();
         const bool lead = tc5::elect_one();
-        const uint32_t sA = tc5::smem_u32(parts + (kc & 1) * ABYTES);
-        const uint32_t sW = tc5::smem_u32(sm + (kc % STAGES) * S::STAGE);
+        const uint32_t sA = tc5::smem_u32(parts + (g & 1) * ABYTES);
+        const uint32_t sW = tc5::smem_u32(sm + (g % STAGES) * S::STAGE);
 #pragma unroll
         for (int tau = 0; tau < KW; ++tau) {
           const int step = kc * KW + tau;
@@ -194,16 +175,63 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
             tc5::mma_f16(tmem + SMALL, am, bh, IDESC, 1u);
           }
         }
-        if (lead) tc5::commit(&bar[kc & 1]);
+        if (lead) tc5::commit(&empty[g & 1]);
         __syncwarp();
       }
+    } else {
+      // ---- loaders / converters ---------------------------------------------------------------------------
+      const int lt = tid - 32;
+      const float* xb = a.x + b * (int64_t)a.Cin * T;
+      const uint8_t* wct = a.Wg + (int64_t)ct * nkc * S::WBYTES;
+      auto issue_loads = [&](int kc) {
+        const uint32_t g = g0 + (uint32_t)kc;
+        uint8_t* st = sm + (g % STAGES) * S::STAGE;
+        const uint8_t* wsrc = wct + (int64_t)kc * S::WBYTES;
+        for (int i = lt; i < S::WBYTES / 16; i += NLD) cp16(st + i * 16, wsrc + i * 16, 16);
+        float* xs = reinterpret_cast<float*>(st + S::WBYTES);
+        for (int i = lt; i < KC * (XW / 4); i += NLD) {
+          const int c = i / (XW / 4), j = (i - c * (XW / 4)) * 4, t = t0 - 4 + j;
+          const bool ok = (t >= 0 && t < T);             // T % 4 == 0: a granule is inside or outside as a whole
+          cp16(xs + c * XP + j, xb + (int64_t)(kc * KC + c) * T + (ok ? t : 0), ok ? 16 : 0);
+        }
+        cp_async_arrive(&landed[g % STAGES]);
+      };
+      // stages of chunks 0, 1 were last read by chunks g0-4, g0-3: drained at the end of the previous item
+      issue_loads(0);
+      if (nkc > 1) issue_loads(1);
+      for (int kc = 0; kc < nkc; ++kc) {
+        const uint32_t g = g0 + (uint32_t)kc;
+        // parts buffer g & 1 and stage (g + 2) % 4 were last read by the MMAs of chunk g - 2
+        if (g >= 2) tc5::mbar_wait(&empty[g & 1], ((g - 2) >> 1) & 1u);
+        if (kc + 2 < nkc) issue_loads(kc + 2);
+        tc5::mbar_wait(&landed[g % STAGES], (g / STAGES) & 1u);
+        const float* xs = reinterpret_cast<const float*>(sm + (g % STAGES) * S::STAGE + S::WBYTES);
+        uint8_t* pb = parts + (g & 1) * ABYTES;
+        for (int i = lt; i < 2 * ROWS; i += NLD) {
+          const int pl = i / ROWS, r = i - pl * ROWS;
+          __align__(16) __half hh[8], mm[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) tc5::split_f16(xs[(pl * 8 + e) * XP + r + 3] * sx, hh[e], mm[e]);
+          uint8_t* p = pb + pl * PLANE + r * 16;
+          *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(hh);
+          *reinterpret_cast<uint4*>(p + APART) = *reinterpret_cast<const uint4*>(mm);
+        }
+        tc5::fence_async_smem();          // this thread's generic-proxy writes (parts; its cp.async of W) -> async proxy
+        mbar_arrive(&full[g & 1]);
+      }
+      // drain: the last two chunks' MMAs (idempotent waits: a completed phase answers at once)
+      for (int kc = (nkc >= 2 ? nkc - 2 : 0); kc < nkc; ++kc) {
+        const uint32_t g = g0 + (uint32_t)kc;
+        tc5::mbar_wait(&empty[g & 1], (g >> 1) & 1u);
+      }
     }
-    for (int kc = (nkc >= 2 ? nkc - 2 : 0); kc < nkc; ++kc) { tc5::mbar_wait(&bar[kc & 1], par[kc & 1]); par[kc & 1] ^= 1u; }
+    __syncthreads();                       // every MMA of the item has completed (the converters saw its commits)
     tc5::fence_after_sync();
     {   // epilogue: TMEM lane = time row; warp w reads lane quadrant w & 3, columns [32 (w >> 2), +32)
       const uint32_t lane_base = (uint32_t)(32 * (w & 3)) << 16;
       const int t = t0 + 32 * (w & 3) + lane;
       const int nsets = (nkc * KW < 3) ? nkc * KW : 3;
+      float ymax = 0.f;
 #pragma unroll 1
       for (int cgp = 0; cgp < 2; ++cgp) {
         const int col = 32 * (w >> 2) + 16 * cgp;
@@ -240,8 +268,14 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
             if (a.epi == EPI_RELU) r = fmaxf(r, 0.f);
             else if (a.epi == EPI_MASK) r = mk[e] > 0.f ? r : 0.f;
             a.y[off0 + (int64_t)e * T] = r;
+            ymax = fmaxf(ymax, fabsf(r));
           }
         }
+      }
+      if (a.amax_y) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, o));
+        if (lane == 0 && ymax > 0.f) atomicMax(a.amax_y, __float_as_uint(ymax));
       }
     }
     tc5::fence_before_sync();
@@ -294,18 +328,30 @@ static inline int conv_tc5_prepare(WView wv, int64_t n_w, int Cin, int Cout, int
   return 0;
 }
 
-static inline int launch_conv_tc5(const float* x, const Tc5Weights& W, const float* bias, const float* act, float* y,
-                                  int64_t B, int Cin, int Cout, int64_t T, int kw, int epi, cudaStream_t st) {
-  if (B <= 0 || T <= 0) return 0;
-  VHMM_CUDA_CHECK(cudaMemsetAsync(W.amax_x, 0, 4, st));
-  const int64_t nx = B * (int64_t)Cin * T;
-  int64_t blocks = cdiv(nx, 1024 * 8);
+static inline int launch_absmax(const float* p, int64_t n, uint32_t* word, cudaStream_t st) {
+  int64_t blocks = cdiv(n, 1024 * 8);
   if (blocks > 1184) blocks = 1184;
   if (blocks < 1) blocks = 1;
-  ct5::absmax_kernel<<<(unsigned)blocks, 256, 0, st>>>(x, nx, W.amax_x);
+  ct5::absmax_kernel<<<(unsigned)blocks, 256, 0, st>>>(p, n, word);
   VHMM_LAUNCH_CHECK();
+  return 0;
+}
+
+// amax_x_known: a device word that already holds |x| max (from the producer's epilogue or an earlier pass), or null;
+// amax_y: a ZEROED device word that receives |y| max, or null
+static inline int launch_conv_tc5(const float* x, const Tc5Weights& W, const float* bias, const float* act, float* y,
+                                  int64_t B, int Cin, int Cout, int64_t T, int kw, int epi, cudaStream_t st,
+                                  const uint32_t* amax_x_known = nullptr, uint32_t* amax_y = nullptr) {
+  if (B <= 0 || T <= 0) return 0;
+  const uint32_t* ax = amax_x_known;
+  if (!ax) {
+    VHMM_CUDA_CHECK(cudaMemsetAsync(W.amax_x, 0, 4, st));
+    int rc = launch_absmax(x, B * (int64_t)Cin * T, W.amax_x, st);
+    if (rc) return rc;
+    ax = W.amax_x;
+  }
   ct5::ConvArgs a{};
-  a.x = x; a.Wg = W.Wg; a.bias = bias; a.act = act; a.y = y; a.amax_x = W.amax_x; a.amax_w = W.amax_w;
+  a.x = x; a.Wg = W.Wg; a.bias = bias; a.act = act; a.y = y; a.amax_x = ax; a.amax_w = W.amax_w; a.amax_y = amax_y;
   a.B = B; a.Cin = Cin; a.Cout = Cout; a.T = (int)T; a.epi = epi;
   a.ntt = (int)cdiv(T, ct5::TM); a.nct = Cout / ct5::TN;
   a.nitems = B * a.ntt * a.nct;
@@ -549,26 +595,19 @@ static inline int64_t wgrad_tc5_scratch_floats(int Cin, int Cout, int kw, int64_
 
 // gW (layer layout, +=), gB (+=, may be null)
 static inline int launch_wgrad_tc5(const float* dy, const float* x, float* gW, float* gB, WView layout, int64_t B, int Cin,
-                                   int Cout, int64_t T, int kw, float* scratch, cudaStream_t st) {
+                                   int Cout, int64_t T, int kw, float* scratch, cudaStream_t st,
+                                   const uint32_t* amax_dy_known = nullptr, const uint32_t* amax_x_known = nullptr) {
   if (B <= 0 || T <= 0) return 0;
   const int ns = wgrad_tc5_nsplit(Cin, Cout, B, T);
   const int64_t nW = (int64_t)Cin * Cout * kw;
   uint32_t* words = reinterpret_cast<uint32_t*>(scratch + (int64_t)ns * nW);
   VHMM_CUDA_CHECK(cudaMemsetAsync(words, 0, 8, st));
-  auto amax = [&](const float* p, int64_t n, uint32_t* out) {
-    int64_t blocks = cdiv(n, 1024 * 8);
-    if (blocks > 1184) blocks = 1184;
-    if (blocks < 1) blocks = 1;
-    ct5::absmax_kernel<<<(unsigned)blocks, 256, 0, st>>>(p, n, out);
-  };
-  amax(dy, B * (int64_t)Cout * T, words);
-  VHMM_LAUNCH_CHECK();
-  amax(x, B * (int64_t)Cin * T, words + 1);
-  VHMM_LAUNCH_CHECK();
+  if (!amax_dy_known) { int rc = launch_absmax(dy, B * (int64_t)Cout * T, words, st); if (rc) return rc; }
+  if (!amax_x_known) { int rc = launch_absmax(x, B * (int64_t)Cin * T, words + 1, st); if (rc) return rc; }
   ct5::WgradArgs a{};
   a.dy = dy; a.x = x; a.part = scratch; a.part_stride = nW;
   a.w_base = layout.base; a.w_so = layout.so; a.w_sc = layout.sc; a.w_st = layout.st;
-  a.amax_dy = words; a.amax_x = words + 1;
+  a.amax_dy = amax_dy_known ? amax_dy_known : words; a.amax_x = amax_x_known ? amax_x_known : words + 1;
   a.B = B; a.Cin = Cin; a.Cout = Cout; a.T = (int)T; a.ntt = (int)cdiv(T, ct5::TM); a.nbc = Cin / ct5::WB; a.nsplit = ns;
   const unsigned grid = (unsigned)((Cout / ct5::WB) * (Cin / ct5::WB) * ns);
   if (kw == 3) {

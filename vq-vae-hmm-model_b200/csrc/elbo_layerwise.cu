@@ -51,6 +51,36 @@ struct Tc5Ctx {
   struct Entry { const float* w; int dgrad; Tc5Weights tw; };
   Entry e[16];
   int n = 0;
+  // |tensor| max words known for the CURRENT batch chunk (key = tensor pointer): filled by the tensor-core kernels' own
+  // epilogues or by one absmax pass, reused by every later consumer of the same tensor (forward, input gradient, weight
+  // gradient); reset when the chunk's buffers are rewritten
+  static constexpr int NW = 64;
+  uint32_t* pool = nullptr;
+  mutable const void* key[NW];
+  mutable int nkeys = 0;
+  int reset(cudaStream_t st) const {
+    nkeys = 0;
+    if (pool) VHMM_CUDA_CHECK(cudaMemsetAsync(pool, 0, NW * 4, st));
+    return 0;
+  }
+  uint32_t* known(const void* p) const {
+    for (int i = 0; i < nkeys; ++i) if (key[i] == p) return pool + i;
+    return nullptr;
+  }
+  uint32_t* fresh(const void* p) const {            // a zeroed word registered for tensor p (about to be produced / measured)
+    for (int i = 0; i < nkeys; ++i) if (key[i] == p) key[i] = nullptr;   // p is being rewritten: its old word is stale
+    if (!pool || nkeys >= NW) return nullptr;
+    key[nkeys] = p;
+    return pool + nkeys++;
+  }
+  // word holding |p| max, running the absmax pass if nobody produced it yet; null if the pool is exhausted
+  uint32_t* measure(const float* p, int64_t n, cudaStream_t st, int* rc) const {
+    *rc = 0;
+    if (uint32_t* k = known(p)) return k;
+    uint32_t* wd = fresh(p);
+    if (wd) *rc = launch_absmax(p, n, wd, st);
+    return wd;
+  }
   const Tc5Weights* find(const float* w, int dgrad) const {
     for (int i = 0; i < n; ++i) if (e[i].w == w && e[i].dgrad == dgrad) return &e[i].tw;
     return nullptr;
@@ -76,11 +106,16 @@ static size_t tc5_ctx_bytes(const vhmm_dims& d) {
     if (tc5_shape(L[i].Cin, L[i].Cout)) b += conv_tc5_weight_bytes(L[i].Cin, L[i].Cout, L[i].kw);
     if (L[i].need_dgrad && tc5_shape(L[i].Cout, L[i].Cin)) b += conv_tc5_weight_bytes(L[i].Cout, L[i].Cin, L[i].kw);
   }
-  return b + 256;
+  return b + 512;
 }
 static int tc5_ctx_prepare(const vhmm_dims& d, const vhmm_params& P, bool with_dgrad, Arena& A, Tc5Ctx* ctx, cudaStream_t st) {
   ctx->n = 0;
+  ctx->nkeys = 0;
+  ctx->pool = nullptr;
   if (conv_impl_mode() == 1) return 0;
+  ctx->pool = A.take<uint32_t>(Tc5Ctx::NW);
+  if (!A.ok) { ctx->pool = nullptr; return 0; }
+  { int rc0 = ctx->reset(st); if (rc0) return rc0; }
   Tc5Layer L[8];
   const int n = tc5_layers(d, L);
   for (int i = 0; i < n; ++i) {
@@ -109,15 +144,25 @@ static int tc5_ctx_prepare(const vhmm_dims& d, const vhmm_params& P, bool with_d
 static int cconv(const Tc5Ctx* ctx, int dgrad, const float* x, WView wv, const float* bias, const float* act, float* y, int64_t B,
                  int Cin, int Cout, int64_t T, int kw, int epi, cudaStream_t st) {
   const Tc5Weights* tw = ctx ? ctx->find(wv.w, dgrad) : nullptr;
-  if (tw && conv_tc5_ok(Cin, Cout, T, kw, x, y) && (!act || (((uintptr_t)act) & 15) == 0))
-    return launch_conv_tc5(x, *tw, bias, act, y, B, Cin, Cout, T, kw, epi, st);
+  if (tw && conv_tc5_ok(Cin, Cout, T, kw, x, y) && (!act || (((uintptr_t)act) & 15) == 0)) {
+    int rc = 0;
+    const uint32_t* ax = ctx->measure(x, B * (int64_t)Cin * T, st, &rc);
+    if (rc) return rc;
+    return launch_conv_tc5(x, *tw, bias, act, y, B, Cin, Cout, T, kw, epi, st, ax, ctx->fresh(y));
+  }
   VHMM_REQUIRE(conv_impl_mode() != 2 || !ctx || !tc5_shape(Cin, Cout), VHMM_E_DIMS, "conv: VHMM_CONV_TC5 selected but T %% 4 != 0 or unaligned tensors");
   return launch_conv(x, wv, bias, act, y, B, Cin, Cout, T, kw, epi, st);
 }
-static int cwgrad(const float* dy, const float* x, float* gW, float* gB, WView layout, int64_t B, int Cin, int Cout, int64_t T,
-                  int kw, float* scratch, cudaStream_t st) {
-  if (conv_impl_mode() != 1 && wgrad_tc5_ok(Cin, Cout, T, kw, dy, x))
-    return launch_wgrad_tc5(dy, x, gW, gB, layout, B, Cin, Cout, T, kw, scratch, st);
+static int cwgrad(const Tc5Ctx* ctx, const float* dy, const float* x, float* gW, float* gB, WView layout, int64_t B, int Cin, int Cout,
+                  int64_t T, int kw, float* scratch, cudaStream_t st) {
+  if (conv_impl_mode() != 1 && wgrad_tc5_ok(Cin, Cout, T, kw, dy, x)) {
+    int rc = 0;
+    const uint32_t* ady = ctx ? ctx->measure(dy, B * (int64_t)Cout * T, st, &rc) : nullptr;
+    if (rc) return rc;
+    const uint32_t* ax = ctx ? ctx->measure(x, B * (int64_t)Cin * T, st, &rc) : nullptr;
+    if (rc) return rc;
+    return launch_wgrad_tc5(dy, x, gW, gB, layout, B, Cin, Cout, T, kw, scratch, st, ady, ax);
+  }
   return launch_wgrad(dy, x, gW, gB, layout, B, Cin, Cout, T, kw, scratch, st);
 }
 
@@ -183,7 +228,7 @@ size_t layerwise_workspace_bytes(int op, const vhmm_dims& d, int64_t B, int64_t 
       return (size_t)d.K * T * (3 * (int64_t)d.H + d.K + 2 * d.C) * 4 + slack + tc5_ctx_bytes(d);
     case VHMM_OP_ELBO:
       return fixed_bytes(d, T) + (size_t)Bc * T * (s.per_step_fwd + s.per_step_bwd) * 4 +
-             (size_t)Bc * cdiv(T, 256) * 32 + slack;
+             (size_t)Bc * cdiv(T, 32) * 32 + slack;
     default:
       return 0;
   }
@@ -298,12 +343,12 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
   VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "elbo: workspace %zu too small (fixed part %zu)", ws_bytes, A.used);
   const int64_t per_step = S.per_step_fwd + (grads ? S.per_step_bwd : 0);
   const size_t left = (ws_bytes - A.used > 64 * 256) ? ws_bytes - A.used - 64 * 256 : 0;
-  int64_t Bc = (int64_t)(left / ((size_t)per_step * T * 4 + (size_t)cdiv(T, 256) * 32));
+  int64_t Bc = (int64_t)(left / ((size_t)per_step * T * 4 + (size_t)cdiv(T, 32) * 32));
   if (Bc > B) Bc = B;
   if (Bc > kMaxChunk) Bc = kMaxChunk;
   VHMM_REQUIRE(Bc >= 1, VHMM_E_WORKSPACE, "elbo: workspace %zu cannot hold one sequence (T=%lld)", ws_bytes, (long long)T);
   const size_t n = (size_t)Bc * T;
-  double* partial = A.take<double>(4 * (size_t)(Bc * cdiv(T, 256)));
+  double* partial = A.take<double>(4 * (size_t)(Bc * cdiv(T, 32)));   // wide-K loss kernel: one block per 32 steps
   float* h1 = A.take<float>(n * H);   float* h2 = A.take<float>(n * H2);
   float* lg = A.take<float>(n * K);   float* q = A.take<float>(n * K);   float* lq = A.take<float>(n * K);
   float* a = A.take<float>(n * TH);   float* M = A.take<float>(n * K2);
@@ -332,6 +377,7 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
     const float* xc = x + b0 * C * T;
     const float* uc = u + b0 * U * T;
     const int64_t* Lc = lengths + b0;
+    RC(ctx.reset(st));                       // the chunk's activation buffers are about to be rewritten
     // ---------------- forward ----------------
     RC(encoder_chain(d, P, xc, nb, T, h1, h2, lg, st, &ctx));
     {
@@ -350,25 +396,31 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
     RC(launch_conv(g2, wview_fwd(P.p[P_DPW], H, 1), P.p[P_DPB], nullptr, p, nb, H, 2 * C, T, 1, EPI_NONE, st));
     {
       dim3 g((unsigned)cdiv(T, 256), (unsigned)nb);
-      loss_seed_kernel<<<g, 256, 0, st>>>(xc, p, q, lq, M, log_pi, Lc, norms, betaf, C, K, (int)T,
-                                          partial, dp, dqp, dM);
+      int64_t nblk = (int64_t)g.x * g.y;
+      if (K <= 4) loss_seed_kernel<4><<<g, 256, 0, st>>>(xc, p, q, lq, M, log_pi, Lc, norms, betaf, C, K, (int)T, partial, dp, dqp, dM);
+      else if (K <= 8) loss_seed_kernel<8><<<g, 256, 0, st>>>(xc, p, q, lq, M, log_pi, Lc, norms, betaf, C, K, (int)T, partial, dp, dqp, dM);
+      else {
+        dim3 gr((unsigned)cdiv(T, 32), (unsigned)nb);
+        nblk = (int64_t)gr.x * gr.y;
+        loss_seed_rows_kernel<<<gr, 32 * K, 0, st>>>(xc, p, q, lq, M, log_pi, Lc, norms, betaf, C, K, (int)T, partial, dp, dqp, dM);
+      }
       VHMM_LAUNCH_CHECK();
-      sum_partials_kernel<<<1, 1024, 0, st>>>(partial, (int64_t)g.x * g.y, sums);
+      sum_partials_kernel<<<1, 1024, 0, st>>>(partial, nblk, sums);
       VHMM_LAUNCH_CHECK();
       q0_sum_kernel<<<1, 1024, 0, st>>>(q, nb, K, (int)T, qsum);
       VHMM_LAUNCH_CHECK();
     }
     if (!grads) continue;
     // ---------------- backward: decoder ----------------
-    RC(cwgrad(dp, g2, grads + off[P_DPW], grads + off[P_DPB], wview_fwd(nullptr, H, 1), nb, H, 2 * C, T, 1, scratch, st));
+    RC(cwgrad(&ctx, dp, g2, grads + off[P_DPW], grads + off[P_DPB], wview_fwd(nullptr, H, 1), nb, H, 2 * C, T, 1, scratch, st));
     RC(launch_conv(dp, wview_dgrad(P.p[P_DPW], H, 1), nullptr, g2, dg2, nb, 2 * C, H, T, 1, EPI_MASK, st));
-    RC(cwgrad(dg2, g1, grads + off[P_D2W], grads + off[P_D2B], wview_fwd(nullptr, H, 3), nb, H, H, T, 3, scratch, st));
+    RC(cwgrad(&ctx, dg2, g1, grads + off[P_D2W], grads + off[P_D2B], wview_fwd(nullptr, H, 3), nb, H, H, T, 3, scratch, st));
     RC(cconv(&ctx, 1, dg2, wview_dgrad(P.p[P_D2W], H, 3), nullptr, g1, dg1, nb, H, H, T, 3, EPI_MASK, st));
-    RC(cwgrad(dg1, e, grads + off[P_D1W], grads + off[P_D1B], wview_fwd(nullptr, H, 3), nb, H, H, T, 3, scratch, st));
+    RC(cwgrad(&ctx, dg1, e, grads + off[P_D1W], grads + off[P_D1B], wview_fwd(nullptr, H, 3), nb, H, H, T, 3, scratch, st));
     RC(cconv(&ctx, 1, dg1, wview_dgrad(P.p[P_D1W], H, 3), nullptr, nullptr, de, nb, H, H, T, 3, EPI_NONE, st));
     {
       WView embL{nullptr, 0, 1, H, 0};  // dE[k,d] stored at k*H + d  with (o=d, c=k)
-      RC(cwgrad(de, q, grads + off[P_EMB], nullptr, embL, nb, K, H, T, 1, scratch, st));
+      RC(cwgrad(&ctx, de, q, grads + off[P_EMB], nullptr, embL, nb, K, H, T, 1, scratch, st));
       WView embT{P.p[P_EMB], 0, H, 1, 0};  // dq[k,t] = sum_d E[k,d] de[d,t]: W(o=k, c=d)
       RC(launch_conv(de, embT, nullptr, nullptr, dqd, nb, H, K, T, 1, EPI_NONE, st));
     }
@@ -378,15 +430,15 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
       VHMM_LAUNCH_CHECK();
     }
     // ---------------- backward: encoder ----------------
-    RC(cwgrad(dl, h2, grads + off[P_E3W], grads + off[P_E3B], wview_fwd(nullptr, H2, 1), nb, H2, K, T, 1, scratch, st));
+    RC(cwgrad(&ctx, dl, h2, grads + off[P_E3W], grads + off[P_E3B], wview_fwd(nullptr, H2, 1), nb, H2, K, T, 1, scratch, st));
     RC(launch_conv(dl, wview_dgrad(P.p[P_E3W], H2, 1), nullptr, h2, dh2, nb, K, H2, T, 1, EPI_MASK, st));
-    RC(cwgrad(dh2, h1, grads + off[P_E2W], grads + off[P_E2B], wview_fwd(nullptr, H, 3), nb, H, H2, T, 3, scratch, st));
+    RC(cwgrad(&ctx, dh2, h1, grads + off[P_E2W], grads + off[P_E2B], wview_fwd(nullptr, H, 3), nb, H, H2, T, 3, scratch, st));
     RC(cconv(&ctx, 1, dh2, wview_dgrad(P.p[P_E2W], H, 3), nullptr, h1, dh1, nb, H2, H, T, 3, EPI_MASK, st));
-    RC(cwgrad(dh1, xc, grads + off[P_E1W], grads + off[P_E1B], wview_fwd(nullptr, C, 3), nb, C, H, T, 3, scratch, st));
+    RC(cwgrad(&ctx, dh1, xc, grads + off[P_E1W], grads + off[P_E1B], wview_fwd(nullptr, C, 3), nb, C, H, T, 3, scratch, st));
     // ---------------- backward: prior ----------------
-    RC(cwgrad(dM, a, grads + off[P_T2W], grads + off[P_T2B], wview_fwd(nullptr, TH, 1), nb, TH, K2, T, 1, scratch, st));
+    RC(cwgrad(&ctx, dM, a, grads + off[P_T2W], grads + off[P_T2B], wview_fwd(nullptr, TH, 1), nb, TH, K2, T, 1, scratch, st));
     RC(cconv(&ctx, 1, dM, wview_dgrad(P.p[P_T2W], TH, 1), nullptr, a, da, nb, K2, TH, T, 1, EPI_MASK, st));
-    RC(cwgrad(da, uc, grads + off[P_T0W], grads + off[P_T0B], wview_fwd(nullptr, U, 1), nb, U, TH, T, 1, scratch, st));
+    RC(cwgrad(&ctx, da, uc, grads + off[P_T0W], grads + off[P_T0B], wview_fwd(nullptr, U, 1), nb, U, TH, T, 1, scratch, st));
   }
 #undef RC
   finalize_prior_kernel<<<1, 32, 0, st>>>(log_pi, qsum, norms, betaf, K, sums,

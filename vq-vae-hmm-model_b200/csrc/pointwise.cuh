@@ -77,6 +77,81 @@ __global__ void log_pi_kernel(const float* __restrict__ log_prior, float* __rest
 //   logA (B,K,K,T) row-normalised                                lengths (B) int64
 // out: partial[blk*4 + {0,1,2,3}] = block sums of {nll*mask, trans term, entropy*mask, valid}
 //      dp (B,2C,T), dq_prior (B,K,T), dM (B,K,K,T)   (only when dp != null)
+// Wide-K build of loss_seed_kernel (K > 8, e.g. the scaled config's K = 32): one thread per (b, t, state s), warps along t.
+// Thread (t, s) owns ROW s of the K x K transition tile (pair term, d/dM, and the part of d/dq[s] that comes from the next
+// step's transition) and COLUMN s (the part of d/dq[s] from the transition into t: a second, L1/L2-resident read of
+// logA): no K-sized private array at all, every global access coalesced over t, fixed summation order (deterministic).
+// block = 32 * K threads (t_local = tid & 31, s = tid >> 5); grid (ceil(T/32), B); partial: 4 doubles per block.
+__global__ void __launch_bounds__(1024)
+loss_seed_rows_kernel(const float* __restrict__ x, const float* __restrict__ p, const float* __restrict__ q,
+                      const float* __restrict__ logq, const float* __restrict__ logA, const float* __restrict__ log_pi,
+                      const int64_t* __restrict__ lengths, const double* __restrict__ norms, float beta, int C, int K, int T,
+                      double* __restrict__ partial, float* __restrict__ dp, float* __restrict__ dq_prior,
+                      float* __restrict__ dM) {
+  __shared__ double red[32];
+  const int t = blockIdx.x * 32 + (threadIdx.x & 31), s = threadIdx.x >> 5;
+  const int64_t b = blockIdx.y;
+  const int64_t L = lengths[b];
+  const bool in = t < T;
+  const bool m = in && (int64_t)t < L;
+  const float aR = (float)(1.0 / norms[0]);
+  const float aP = (float)(-(double)beta / norms[1]);
+  float nll_sum = 0.f, ent = 0.f, trans = 0.f;
+  if (in) {
+    for (int c = s; c < C; c += K) {     // reconstruction (:118-120): channel c on the threads of state s = c mod K
+      const float mu = p[(b * 2 * C + c) * (int64_t)T + t];
+      const float lv = p[(b * 2 * C + C + c) * (int64_t)T + t];
+      const float xv = x[(b * C + c) * (int64_t)T + t];
+      const float ev = expf(lv);
+      const float v = fmaxf(ev, 1e-8f);
+      const float d = mu - xv;
+      const float r = d * d / v;
+      if (m) nll_sum += 0.5f * (logf(6.283185307179586f * v) + r);
+      if (dp) {
+        dp[(b * 2 * C + c) * (int64_t)T + t] = m ? aR * d / v : 0.f;
+        dp[(b * 2 * C + C + c) * (int64_t)T + t] = (m && ev >= 1e-8f) ? aR * 0.5f * (1.f - r) : 0.f;
+      }
+    }
+    const bool tm = m && t >= 1;                                   // :128
+    const bool tm_next = (t + 1 < T) && (int64_t)(t + 1) < L;
+    const float* qb = q + b * K * (int64_t)T + t;                  // q[b, k, t] = qb[k * T]
+    const int64_t os = (b * K + s) * (int64_t)T + t;
+    if (m) ent = -q[os] * logq[os];                                // :134
+    const float qps = tm ? q[os - 1] : 0.f;
+    float dqs = (t == 0) ? log_pi[s] : 0.f;                        // :123
+    const int64_t orow = ((b * K + s) * K) * (int64_t)T + t;       // logA[b, s, j, t] = logA[orow + j * T]
+    for (int j = 0; j < K; ++j) {
+      const int64_t o = orow + (int64_t)j * T;
+      if (tm) {
+        const float la = logA[o];
+        const float qcj = qb[(int64_t)j * T];
+        trans += qps * qcj * la;                                   // :127
+        if (dM) dM[o] = aP * qps * (qcj - expf(la));
+      } else if (dM) {
+        dM[o] = 0.f;
+      }
+      if (tm_next) dqs += qb[(int64_t)j * T + 1] * logA[o + 1];    // row s of the transition into t + 1
+    }
+    if (tm) {                                                      // column s of the transition into t
+      const int64_t ocol = ((b * K) * K + s) * (int64_t)T + t;     // logA[b, i, s, t] = logA[ocol + i * K * T]
+      for (int i = 0; i < K; ++i) dqs += qb[(int64_t)i * T - 1] * logA[ocol + (int64_t)i * K * T];
+    }
+    if (dq_prior) dq_prior[os] = aP * dqs;
+  }
+  const int64_t blk = (int64_t)blockIdx.y * gridDim.x + blockIdx.x;
+  double s0 = block_sum<double>((double)nll_sum, red);
+  double s1 = block_sum<double>((double)trans, red);
+  double s2 = block_sum<double>((double)ent, red);
+  double s3 = block_sum<double>((m && s == 0) ? 1.0 : 0.0, red);
+  if (threadIdx.x == 0) {
+    partial[blk * 4 + 0] = s0; partial[blk * 4 + 1] = s1;
+    partial[blk * 4 + 2] = s2; partial[blk * 4 + 3] = s3;
+  }
+}
+
+// KT: compile-time bound of K (4 / 8 / 16 / 32): the K-indexed vectors that the j loops touch stay in REGISTERS (the
+// first build indexed four KMAX-sized arrays with run-time K: local memory, 6x off the HBM time at K = 32)
+template <int KT>
 __global__ void __launch_bounds__(256)
 loss_seed_kernel(const float* __restrict__ x, const float* __restrict__ p,
                  const float* __restrict__ q, const float* __restrict__ logq,
@@ -109,34 +184,49 @@ loss_seed_kernel(const float* __restrict__ x, const float* __restrict__ p,
         dp[(b * 2 * C + C + c) * (int64_t)T + t] = (m && ev >= 1e-8f) ? aR * 0.5f * (1.f - r) : 0.f;
       }
     }
-    float qc[KMAX], qp[KMAX], qn[KMAX];
+    float qc[KT], qn[KT], dqj[KT];
     const bool tm = m && t >= 1;                        // :128 (mask is a prefix)
     const bool tm_next = (t + 1 < T) && (int64_t)(t + 1) < L;
-    for (int k = 0; k < K; ++k) {
-      const int64_t o = (b * K + k) * (int64_t)T + t;
-      qc[k] = q[o];
-      qp[k] = tm ? q[o - 1] : 0.f;
-      qn[k] = tm_next ? q[o + 1] : 0.f;
-      if (m) ent -= qc[k] * logq[o];                    // :134
-    }
-    float dq[KMAX];
-    for (int k = 0; k < K; ++k) dq[k] = (t == 0) ? log_pi[k] : 0.f;   // :123
-    for (int i = 0; i < K; ++i) {
-      for (int j = 0; j < K; ++j) {
-        const int64_t o = ((b * K + i) * K + j) * (int64_t)T + t;
-        if (tm) {
-          const float la = logA[o];
-          trans += qp[i] * qc[j] * la;                  // :127
-          dq[j] += qp[i] * la;
-          if (dM) dM[o] = aP * qp[i] * (qc[j] - expf(la));
-        } else if (dM) {
-          dM[o] = 0.f;
-        }
-        if (tm_next) dq[i] += qn[j] * logA[o + 1];
+#pragma unroll
+    for (int k = 0; k < KT; ++k) {
+      qc[k] = 0.f; qn[k] = 0.f; dqj[k] = 0.f;
+      if (k < K) {
+        const int64_t o = (b * K + k) * (int64_t)T + t;
+        qc[k] = q[o];
+        qn[k] = tm_next ? q[o + 1] : 0.f;
+        if (m) ent -= qc[k] * logq[o];                  // :134
+        dqj[k] = (t == 0) ? log_pi[k] : 0.f;            // :123
       }
     }
-    if (dq_prior)
-      for (int k = 0; k < K; ++k) dq_prior[(b * K + k) * (int64_t)T + t] = aP * dq[k];
+    for (int i = 0; i < K; ++i) {
+      const float qpi = tm ? q[(b * K + i) * (int64_t)T + t - 1] : 0.f;
+      float dqi = 0.f;                                  // the part of d/dq[i] that comes from the NEXT step's transition
+      const int64_t oi = ((b * K + i) * K) * (int64_t)T + t;
+#pragma unroll
+      for (int j = 0; j < KT; ++j) {
+        if (j < K) {
+          const int64_t o = oi + (int64_t)j * T;
+          if (tm) {
+            const float la = logA[o];
+            trans += qpi * qc[j] * la;                  // :127
+            dqj[j] += qpi * la;
+            if (dM) dM[o] = aP * qpi * (qc[j] - expf(la));
+          } else if (dM) {
+            dM[o] = 0.f;
+          }
+          if (tm_next) dqi += qn[j] * logA[o + 1];
+        }
+      }
+      if (dq_prior) dq_prior[(b * K + i) * (int64_t)T + t] = dqi;   // completed below
+    }
+    if (dq_prior) {
+#pragma unroll
+      for (int k = 0; k < KT; ++k)
+        if (k < K) {
+          float* d = dq_prior + (b * K + k) * (int64_t)T + t;
+          *d = aP * (*d + dqj[k]);
+        }
+    }
   }
   const int64_t blk = (int64_t)blockIdx.y * gridDim.x + blockIdx.x;
   double s0 = block_sum<double>((double)nll_sum, red);
