@@ -40,7 +40,7 @@ constexpr int WPLANE = 2 * TN * 16;     // rows = part*128 + o
 constexpr int XW = 136;                 // staged fp32 columns: t0-4 .. t0+131 (16-byte aligned start)
 constexpr int XP = 140;                 // pitch (floats)
 constexpr int XBYTES = KC * XP * 4;
-constexpr int STAGES = 4;
+constexpr int STAGES = 5;                // cp.async stages of the streaming kernel: chunks g+1 .. g+3 in flight
 constexpr uint32_t HH0 = 0, SMALL = 384;   // TMEM columns: three h*h sets at 0 / 128 / 256, the small terms at 384
 
 template <int KW>
@@ -111,6 +111,17 @@ __device__ __forceinline__ void cp_async_arrive(uint64_t* bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" :: "r"(tc5::smem_u32(bar)) : "memory");
 }
 
+// one arrival + `bytes` of expected transaction count (completed by the bulk copies below)
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(tc5::smem_u32(bar)), "r"(bytes) : "memory");
+}
+// TMA bulk copy (1-D, no tensor map): global -> shared, completion reported to the mbarrier as transaction bytes.  A weight
+// chunk is ONE contiguous block in the prepared image, so one instruction by one thread replaces 1536 16-byte cp.async.
+__device__ __forceinline__ void bulk_g2s(void* smem, const void* g, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"(tc5::smem_u32(smem)), "l"(g), "r"(bytes), "r"(tc5::smem_u32(bar)) : "memory");
+}
+
 // y = epi(bias + conv_KW(x, W)); requires Cin % 16 == 0, Cout % 128 == 0, T % 4 == 0, x 16-byte aligned.
 // Warp-specialised main loop over the K chunks (global chunk counter g, continuing across the CTA's work items):
 //   warps 1..15  load chunk g+2 (cp.async into stage (g+2) % 4, completion -> landed[stage]) and convert chunk g from its
@@ -130,7 +141,7 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   for (int i = tid; i < 2 * ABYTES / 4; i += NT) reinterpret_cast<uint32_t*>(parts)[i] = 0u;
   if (tid == 0) {
-    for (int i = 0; i < STAGES; ++i) tc5::mbar_init(&landed[i], NLD);
+    for (int i = 0; i < STAGES; ++i) tc5::mbar_init(&landed[i], NLD + 1);   // NLD cp.async arrivals (x) + the weight block's expect_tx
     for (int i = 0; i < 2; ++i) { tc5::mbar_init(&full[i], NLD); tc5::mbar_init(&empty[i], 1); }
     tc5::mbar_init_fence();
   }
@@ -187,7 +198,10 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
         const uint32_t g = g0 + (uint32_t)kc;
         uint8_t* st = sm + (g % STAGES) * S::STAGE;
         const uint8_t* wsrc = wct + (int64_t)kc * S::WBYTES;
-        for (int i = lt; i < S::WBYTES / 16; i += NLD) cp16(st + i * 16, wsrc + i * 16, 16);
+        if (lt == 0) {                                   // the weight chunk: one TMA bulk copy
+          mbar_expect_tx(&landed[g % STAGES], (uint32_t)S::WBYTES);
+          bulk_g2s(st, wsrc, (uint32_t)S::WBYTES, &landed[g % STAGES]);
+        }
         float* xs = reinterpret_cast<float*>(st + S::WBYTES);
         for (int i = lt; i < KC * (XW / 4); i += NLD) {
           const int c = i / (XW / 4), j = (i - c * (XW / 4)) * 4, t = t0 - 4 + j;
@@ -196,14 +210,16 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
         }
         cp_async_arrive(&landed[g % STAGES]);
       };
-      // stages of chunks 0, 1 were last read by chunks g0-4, g0-3: drained at the end of the previous item
+      // stages of chunks 0..2 were last read by chunks of the previous item: drained at its end
       issue_loads(0);
       if (nkc > 1) issue_loads(1);
+      if (nkc > 2) issue_loads(2);
       for (int kc = 0; kc < nkc; ++kc) {
         const uint32_t g = g0 + (uint32_t)kc;
-        // parts buffer g & 1 and stage (g + 2) % 4 were last read by the MMAs of chunk g - 2
+        // parts buffer g & 1 and stage (g + 3) % 5 were last read by the MMAs of chunk g - 2: ~70 KB must be in flight to
+        // cover the L2 latency at the tensor pipe's appetite of 24 KB per ~1000 cycles
         if (g >= 2) tc5::mbar_wait(&empty[g & 1], ((g - 2) >> 1) & 1u);
-        if (kc + 2 < nkc) issue_loads(kc + 2);
+        if (kc + 3 < nkc) issue_loads(kc + 3);
         tc5::mbar_wait(&landed[g % STAGES], (g / STAGES) & 1u);
         const float* xs = reinterpret_cast<const float*>(sm + (g % STAGES) * S::STAGE + S::WBYTES);
         uint8_t* pb = parts + (g & 1) * ABYTES;
@@ -287,6 +303,222 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
   if (w == 0) tc5::tmem_free512(tmem);
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Input-stationary build (Cin <= 256, several output tiles): the input tile is staged and converted to fp16 parts ONCE
+// per (sequence, time tile) and stays resident while the CTA walks the 128-channel output tiles; inside that loop only
+// weights stream (cp.async, NWS stages) and the issuer warp is bound by the tensor pipe.  The streaming kernel above
+// re-staged and re-converted the input once per output tile (8x for transition_net.2 with its 1024 outputs).
+// ---------------------------------------------------------------------------------------------------------
+constexpr int SMAX_KC = 8;                               // resident chunks: Cin <= 128
+template <int KW>
+struct SmS {
+  static constexpr int GK = (KW == 3) ? 1 : 4;           // weight chunks per stage = per TMA bulk copy (24 KB / 32 KB)
+  static constexpr int NWS = (KW == 3) ? 5 : 3;          // weight stages (~120 KB / ~100 KB in flight)
+  static constexpr int WBYTES = KW * 2 * WPLANE;         // one chunk
+  static constexpr int WREGION = NWS * GK * WBYTES;      // also the fp32 staging of the conversion phase
+  static constexpr int XROUND = WREGION / XBYTES;        // input chunks staged per conversion round
+  static constexpr int TOTAL = WREGION + SMAX_KC * ABYTES;
+};
+
+template <int KW>
+__global__ void __launch_bounds__(NT, 1) conv_tc5s_kernel(ConvArgs a) {
+  constexpr int PAD = KW / 2;
+  constexpr int NLD = NT - 32;
+  using S = SmS<KW>;
+  constexpr int NWS = S::NWS;
+  extern __shared__ __align__(1024) uint8_t sm[];
+  __shared__ __align__(8) uint64_t landed[NWS], empty[NWS], done;
+  __shared__ uint32_t tmem_sh;
+  uint8_t* parts = sm + S::WREGION;
+  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    for (int i = 0; i < NWS; ++i) { tc5::mbar_init(&landed[i], 1); tc5::mbar_init(&empty[i], 1); }
+    tc5::mbar_init(&done, 1);
+    tc5::mbar_init_fence();
+  }
+  if (w == 0) tc5::tmem_alloc512(&tmem_sh);
+  tc5::fence_before_sync();
+  __syncthreads();
+  tc5::fence_after_sync();
+  const uint32_t tmem = tmem_sh;
+  const float sx = tc5::pow2_scale(__uint_as_float(*a.amax_x));
+  const float sw = tc5::pow2_scale(__uint_as_float(*a.amax_w));
+  const float inv = 1.f / (sx * sw);
+  const int nkc = a.Cin / KC;
+  const int T = a.T;
+  constexpr uint32_t IDESC = tc5::idesc_f16(TN, 0, 0);
+#ifdef CT5_PROF
+  long long pf[6] = {0, 0, 0, 0, 0, 0}, pfl = clock64();
+#define CT5P(i) do { if (tid == 0) { long long n_ = clock64(); pf[i] += n_ - pfl; pfl = n_; } } while (0)
+#else
+#define CT5P(i)
+#endif
+  uint32_t gw = 0;      // weight chunks loaded / consumed so far by this CTA (same sequence in the loaders and the issuer)
+  uint32_t gct = 0;     // output tiles finished so far
+  const int64_t nbt = a.B * a.ntt;
+
+  constexpr int GK = S::GK;
+  const int ngr = (nkc + GK - 1) / GK;                   // weight groups per output tile
+  auto load_w = [&](int ct, int gr, uint32_t g) {        // warp 1 only: one TMA bulk copy per weight group
+    if (g >= (uint32_t)NWS) tc5::mbar_wait(&empty[g % NWS], ((g / NWS) - 1u) & 1u);
+    if (lane == 0) {
+      const int k0 = gr * GK, nk = (nkc - k0 < GK) ? nkc - k0 : GK;
+      uint8_t* st = sm + (g % NWS) * (GK * S::WBYTES);
+      const uint8_t* wsrc = a.Wg + ((int64_t)ct * nkc + k0) * S::WBYTES;
+      mbar_expect_tx(&landed[g % NWS], (uint32_t)(nk * S::WBYTES));
+      bulk_g2s(st, wsrc, (uint32_t)(nk * S::WBYTES), &landed[g % NWS]);
+    }
+    __syncwarp();
+  };
+
+  for (int64_t bt = blockIdx.x; bt < nbt; bt += gridDim.x) {
+    const int tt = (int)(bt % a.ntt);
+    const int64_t b = bt / a.ntt;
+    const int t0 = tt * TM;
+    const float* xb = a.x + b * (int64_t)a.Cin * T;
+    // ---- phase A: stage and convert the whole input tile (the weight region is free: the previous item is finished)
+    for (int c0 = 0; c0 < nkc; c0 += S::XROUND) {
+      const int nch = (nkc - c0 < S::XROUND) ? nkc - c0 : S::XROUND;
+      for (int i = tid; i < nch * KC * (XW / 4); i += NT) {
+        const int c = i / (XW / 4), j = (i - c * (XW / 4)) * 4, t = t0 - 4 + j;     // c: channel within the round
+        const bool ok = (t >= 0 && t < T);
+        cp16(reinterpret_cast<float*>(sm) + c * XP + j, xb + (int64_t)(c0 * KC + c) * T + (ok ? t : 0), ok ? 16 : 0);
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncthreads();
+      const float* xs = reinterpret_cast<const float*>(sm);
+      for (int i = tid; i < nch * 2 * ROWS; i += NT) {
+        const int ch = i / (2 * ROWS), rem = i - ch * (2 * ROWS), pl = rem / ROWS, r = rem - pl * ROWS;
+        __align__(16) __half hh[8], mm[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) tc5::split_f16(xs[(ch * KC + pl * 8 + e) * XP + r + 3] * sx, hh[e], mm[e]);
+        uint8_t* p = parts + (c0 + ch) * ABYTES + pl * PLANE + r * 16;
+        *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(hh);
+        *reinterpret_cast<uint4*>(p + APART) = *reinterpret_cast<const uint4*>(mm);
+      }
+      tc5::fence_async_smem();
+      __syncthreads();
+    }
+    CT5P(0);
+    // ---- phase B: the output tiles
+    if (w == 1) {   // first weight groups of tile 0
+      const int npre = ngr < NWS ? ngr : NWS;
+      for (int gr = 0; gr < npre; ++gr) load_w(0, gr, gw + (uint32_t)gr);
+    }
+    for (int ct = 0; ct < a.nct; ++ct) {
+      const int npre = ngr < NWS ? ngr : NWS;      // groups of this tile already requested
+      if (w == 0) {
+        for (int gr = 0; gr < ngr; ++gr) {
+          const uint32_t g = gw + (uint32_t)gr;
+          tc5::mbar_wait(&landed[g % NWS], (g / NWS) & 1u);
+          CT5P(1);
+          tc5::fence_after_sync();
+          const bool lead = tc5::elect_one();
+          const int k0 = gr * GK, nk = (nkc - k0 < GK) ? nkc - k0 : GK;
+          for (int kk = 0; kk < nk; ++kk) {
+            const int kc = k0 + kk;
+            const uint32_t sA = tc5::smem_u32(parts + kc * ABYTES);
+            const uint32_t sW = tc5::smem_u32(sm + (g % NWS) * (GK * S::WBYTES) + kk * S::WBYTES);
+#pragma unroll
+            for (int tau = 0; tau < KW; ++tau) {
+              const int step = kc * KW + tau;
+              const uint64_t ah = tc5::make_desc(sA + (tau - PAD + 1) * 16, PLANE, 128);
+              const uint64_t am = tc5::make_desc(sA + APART + (tau - PAD + 1) * 16, PLANE, 128);
+              const uint64_t bh = tc5::make_desc(sW + tau * 2 * WPLANE, WPLANE, 128);
+              const uint64_t bm = tc5::make_desc(sW + tau * 2 * WPLANE + TN * 16, WPLANE, 128);
+              if (lead) {
+                tc5::mma_f16(tmem + HH0 + 128u * (uint32_t)(step % 3), ah, bh, IDESC, step >= 3 ? 1u : 0u);
+                tc5::mma_f16(tmem + SMALL, ah, bm, IDESC, step >= 1 ? 1u : 0u);
+                tc5::mma_f16(tmem + SMALL, am, bh, IDESC, 1u);
+              }
+            }
+          }
+          if (lead) {
+            tc5::commit(&empty[g % NWS]);
+            if (gr == ngr - 1) tc5::commit(&done);
+          }
+          __syncwarp();
+          CT5P(2);
+        }
+      } else if (w == 1) {
+        for (int gr = npre; gr < ngr; ++gr) load_w(ct, gr, gw + (uint32_t)gr);
+      }
+      gw += (uint32_t)ngr;
+      tc5::mbar_wait(&done, gct & 1u);
+      CT5P(3);
+      ++gct;
+      tc5::fence_after_sync();
+      if (w == 1 && ct + 1 < a.nct) {   // the stages are free: request the next tile's first groups under the epilogue
+        for (int gr = 0; gr < npre; ++gr) load_w(ct + 1, gr, gw + (uint32_t)gr);
+      }
+      {   // epilogue: TMEM lane = time row; warp w reads lane quadrant w & 3, columns [32 (w >> 2), +32)
+        const uint32_t lane_base = (uint32_t)(32 * (w & 3)) << 16;
+        const int t = t0 + 32 * (w & 3) + lane;
+        const int nsets = (nkc * KW < 3) ? nkc * KW : 3;
+        float ymax = 0.f;
+  #pragma unroll 1
+        for (int cgp = 0; cgp < 2; ++cgp) {
+          const int col = 32 * (w >> 2) + 16 * cgp;
+          float v[16], s[16];
+          tc5::tmem_ld16(tmem + lane_base + SMALL + col, s);
+          tc5::tmem_ld16(tmem + lane_base + HH0 + col, v);
+          if (nsets > 1) {
+            float v1[16];
+            tc5::tmem_ld16(tmem + lane_base + HH0 + 128 + col, v1);
+  #pragma unroll
+            for (int e = 0; e < 16; ++e) v[e] += v1[e];
+          }
+          if (nsets > 2) {
+            float v2[16];
+            tc5::tmem_ld16(tmem + lane_base + HH0 + 256 + col, v2);
+  #pragma unroll
+            for (int e = 0; e < 16; ++e) v[e] += v2[e];
+          }
+          if (t < T) {
+            // every load (bias, ReLU mask) is issued BEFORE the first store: y, act and bias are plain pointers, so a load
+            // placed after a store would have to wait for it (possible aliasing) and the 16 columns would serialise on
+            // global-memory latency
+            const int64_t off0 = (b * a.Cout + ct * TN + col) * (int64_t)T + t;
+            float bz[16], mk[16] = {};
+  #pragma unroll
+            for (int e = 0; e < 16; ++e) bz[e] = a.bias ? __ldg(a.bias + ct * TN + col + e) : 0.f;
+            if (a.epi == EPI_MASK) {
+  #pragma unroll
+              for (int e = 0; e < 16; ++e) mk[e] = __ldg(a.act + off0 + (int64_t)e * T);
+            }
+  #pragma unroll
+            for (int e = 0; e < 16; ++e) {
+              float r = (v[e] + s[e]) * inv + bz[e];
+              if (a.epi == EPI_RELU) r = fmaxf(r, 0.f);
+              else if (a.epi == EPI_MASK) r = mk[e] > 0.f ? r : 0.f;
+              a.y[off0 + (int64_t)e * T] = r;
+              ymax = fmaxf(ymax, fabsf(r));
+            }
+          }
+        }
+        if (a.amax_y) {
+  #pragma unroll
+          for (int o = 16; o > 0; o >>= 1) ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, o));
+          if (lane == 0 && ymax > 0.f) atomicMax(a.amax_y, __float_as_uint(ymax));
+        }
+      }
+      tc5::fence_before_sync();
+      __syncthreads();
+      tc5::fence_after_sync();
+      CT5P(4);
+    }
+  }
+#ifdef CT5_PROF
+  if (tid == 0 && blockIdx.x == 0)
+    printf("conv_tc5s<%d> Cin=%d Cout=%d cycles: phaseA %lld, wait landed %lld, issue %lld, wait done %lld, epilogue %lld\n", KW, a.Cin,
+           a.Cout, pf[0], pf[1], pf[2], pf[3], pf[4]);
+#endif
+  tc5::fence_before_sync();
+  __syncthreads();
+  if (w == 0) tc5::tmem_free512(tmem);
+}
+
 }  // namespace ct5
 }  // namespace vhmm
 
@@ -356,6 +588,27 @@ static inline int launch_conv_tc5(const float* x, const Tc5Weights& W, const flo
   a.ntt = (int)cdiv(T, ct5::TM); a.nct = Cout / ct5::TN;
   a.nitems = B * a.ntt * a.nct;
   int64_t grid = device_sm_count();
+  if (a.nct >= 2 && Cin / ct5::KC <= ct5::SMAX_KC) {     // input-stationary build: convert the input tile once for all output tiles
+    const int64_t nbt = B * a.ntt;
+    if (grid > nbt) grid = nbt;
+    if (kw == 3) {
+      static PerDeviceOnce once;
+      if (once.pending()) {
+        VHMM_CUDA_CHECK(cudaFuncSetAttribute(ct5::conv_tc5s_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ct5::SmS<3>::TOTAL));
+        once.mark();
+      }
+      ct5::conv_tc5s_kernel<3><<<(unsigned)grid, ct5::NT, ct5::SmS<3>::TOTAL, st>>>(a);
+    } else {
+      static PerDeviceOnce once;
+      if (once.pending()) {
+        VHMM_CUDA_CHECK(cudaFuncSetAttribute(ct5::conv_tc5s_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ct5::SmS<1>::TOTAL));
+        once.mark();
+      }
+      ct5::conv_tc5s_kernel<1><<<(unsigned)grid, ct5::NT, ct5::SmS<1>::TOTAL, st>>>(a);
+    }
+    VHMM_LAUNCH_CHECK();
+    return 0;
+  }
   if (grid > a.nitems) grid = a.nitems;
   if (kw == 3) {
     static PerDeviceOnce once;
