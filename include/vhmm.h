@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define VHMM_VERSION 108 /* major*100 + minor */
+#define VHMM_VERSION 109 /* major*100 + minor */
 #define VHMM_NUM_PARAMS 18
 #define VHMM_PAD_STATE 255 /* Viterbi path value for t >= lengths[b] */
 
@@ -164,6 +164,12 @@ int vhmm_elbo_active_impl(const vhmm_dims* dims);
 enum { VHMM_DECODER_AUTO = 0, VHMM_DECODER_MMA = 1, VHMM_DECODER_TC5 = 2 };
 int vhmm_elbo_decoder_select(int variant);
 int vhmm_elbo_decoder_active(void);
+
+/* Input windows of the tile kernels (FUSED ELBO kernels A and B, the fused forward kernel): 0 (default) = 16-byte cp.async
+ * with zero-fill predicates, 1 = tensor-map TMA boxes (cp.async.bulk.tensor, out-of-bounds fill = the conv zero padding;
+ * needs T % 4 == 0 and 16-byte aligned tensors, else the call falls back to cp.async).  Same results bit for bit; at cfg 2
+ * the TMA build measured 0.8 % slower (85.4 vs 84.8 ms), hence the default.  Environment VHMM_TMA=1 seeds the choice. */
+int vhmm_tma_select(int on);
 
 /* Measurement hook for bench.py (roofline of the dominant kernel): while enabled, the FUSED path
  * records CUDA events on the caller's stream around its three tile kernels (up to 64 calls).

@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-5
 
 
-@pytest.fixture(autouse=True, scope="module", params=["fused", "fused-mma", "layerwise"])
+@pytest.fixture(autouse=True, scope="module", params=["fused", "fused-tma", "fused-mma", "layerwise"])
 def elbo_impl(request):
     """Every test of this module runs against all vhmm_elbo implementations (include/vhmm.h): the
     fused tile kernels with the tcgen05 decoder ("fused") and with the mma.sync decoder
@@ -21,10 +21,12 @@ def elbo_impl(request):
     import vhmm_b200.functional as Fn
     impl, _, dec = request.param.partition("-")
     Fn.elbo_select(impl)
-    Fn.elbo_decoder_select(dec or "tc5")
+    Fn.tma_select(dec == "tma")            # "fused-tma": input windows of kernels A / B / forward by tensor-map TMA boxes
+    Fn.elbo_decoder_select("mma" if dec == "mma" else "tc5")
     yield impl
     Fn.elbo_select("auto")
     Fn.elbo_decoder_select("auto")
+    Fn.tma_select(False)
 
 
 def _model(dims, params):

@@ -24,12 +24,14 @@ def _model(seed=0, ckpt=False):
 
 @pytest.mark.parametrize("B,T", [(1, 1), (2, 3), (3, 57), (2, 120), (2, 121), (5, 124), (3, 240), (2, 241), (7, 512), (2, 1000)])
 @pytest.mark.parametrize("ckpt", [False, True])
-def test_fused_forward_vs_float64_oracle(B, T, ckpt):
+@pytest.mark.parametrize("tma", [False, True])
+def test_fused_forward_vs_float64_oracle(B, T, ckpt, tma):
     """tile boundaries (T = 120, 121, 240, 241), windows shorter than the halo (T = 1, 3), T % 4 != 0 (scalar cp.async)"""
     from vhmm_b200 import functional as Fn
     from oracle import elbo as O
     m, p64 = _model(seed=B + T, ckpt=ckpt)
     assert Fn.elbo_active_impl(m._dims) == "fused"
+    Fn.tma_select(tma)      # input windows by tensor-map TMA (where T % 4 == 0) or cp.async
     g = torch.Generator().manual_seed(B * 1000 + T)
     x = torch.randn(B, 5, T, generator=g) * 1.7
     (mu64, lv64), q64 = O.forward(p64, x.double())
@@ -47,6 +49,7 @@ def test_fused_forward_vs_float64_oracle(B, T, ckpt):
     assert maxabs_rel(mu.cpu(), mu64) < TOL
     assert maxabs_rel(lv.cpu(), lv64) < TOL
     assert torch.equal(q, q2)
+    Fn.tma_select(False)
     assert torch.equal(mu, mu2) and torch.equal(lv, lv2)        # decode(q) of a probability-valued q == forward()
 
 

@@ -102,6 +102,7 @@ PROTOTYPES = {
     "vhmm_elbo_active_impl": (ctypes.c_int, [_DP]),
     "vhmm_elbo_decoder_select": (ctypes.c_int, [ctypes.c_int]),
     "vhmm_elbo_decoder_active": (ctypes.c_int, []),
+    "vhmm_tma_select": (ctypes.c_int, [ctypes.c_int]),
     "vhmm_elbo_timing": (ctypes.c_int, [ctypes.c_int]),
     "vhmm_elbo_timing_read": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int)]),
     "vhmm_conv_select": (ctypes.c_int, [ctypes.c_int]),

@@ -60,6 +60,7 @@ int fused_forward(const vhmm_dims&, const vhmm_params&, const float*, const floa
 int fused_timing_enable(int enable);
 int fused_decoder_select(int variant);
 int fused_decoder_active();
+int fused_tma_select(int on);
 int fused_timing_read(double* ms_sum, int* ncalls);
 // hmm.cu
 size_t hmm_workspace_bytes(int op, int64_t B, int64_t T, int64_t K);
@@ -263,6 +264,7 @@ int vhmm_hmm_numerics_select(int mode) {
   return hmm_numerics_select(mode);
 }
 int vhmm_elbo_decoder_active(void) { return fused_decoder_active(); }
+int vhmm_tma_select(int on) { return fused_tma_select(on); }
 
 int vhmm_elbo_timing(int enable) { return fused_timing_enable(enable); }
 

@@ -323,7 +323,6 @@ struct SmS {
 template <int KW>
 __global__ void __launch_bounds__(NT, 1) conv_tc5s_kernel(ConvArgs a) {
   constexpr int PAD = KW / 2;
-  constexpr int NLD = NT - 32;
   using S = SmS<KW>;
   constexpr int NWS = S::NWS;
   extern __shared__ __align__(1024) uint8_t sm[];

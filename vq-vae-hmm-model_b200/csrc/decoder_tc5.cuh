@@ -58,12 +58,12 @@ struct Lay {
   static constexpr int BD1 = WP + 16 * CF::PW_H;
   static constexpr int BD2 = BD1 + CF::H;
   static constexpr int BP = BD2 + CF::H;                        // [16]
-  static constexpr int QX = BP + 16;                            // rows 0..7 q, 8..15 x
+  static constexpr int QX = (BP + 16 + 31) / 32 * 32;           // rows 0..7 q, 8..15 x; 128-byte aligned (TMA destination)
   static constexpr int S = QX + 16 * PT;                        // fp32 scratch [H][PT]
   static constexpr int PB = S + CF::H * PT;                     // [16][PT]
   static constexpr int ACC = PB + 16 * PT;                      // small gradient accumulators: layout of Cfg::B_* minus B_WF
   static constexpr int NACC = CF::ACC_B - CF::B_WF;
-  static constexpr int QX1 = ACC + NACC;                        // second input buffer (prefetch of the next tile)
+  static constexpr int QX1 = (ACC + NACC + 31) / 32 * 32;       // second input buffer (prefetch of the next tile), 128-byte aligned
   static constexpr int SCR = QX1 + 16 * PT;                     // slice partials of the folded conv1 weight gradient (skinny.cuh)
   static constexpr int WFT = SCR + SkTaps<CF::K, CF::H>::FLOATS;  // [3][K][H] folded conv1, transposed for the FFMA forward
   static constexpr int FLOATS = WFT + 3 * CF::K * CF::H;
@@ -72,13 +72,13 @@ struct Lay {
 }  // namespace t5
 
 template <typename CF>
-__global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_params P) {
+__global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_params P, const __grid_constant__ TmaMaps tm) {
   constexpr int C = CF::C, H = CF::H, K = CF::K;
   static_assert(H == 64, "the tcgen05 decoder tiling is written for hidden_dim = 64");
   using L = t5::Lay<CF>;
   extern __shared__ __align__(1024) uint8_t smraw[];
   __shared__ double red[NW];
-  __shared__ __align__(8) uint64_t bar_f, bar_d, bar_w, bar_w2;
+  __shared__ __align__(8) uint64_t bar_f, bar_d, bar_w, bar_w2, bar_in[2];
   __shared__ uint32_t tmem_sh, amax_sh;
   uint8_t* W2h = smraw;                                   // fp16 weights
   uint8_t* RA = W2h + t5::W_BYTES;                         // g1 parts
@@ -107,6 +107,7 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
   for (int i = tid; i < (int)(L::BYTES / 4); i += NTH) reinterpret_cast<uint32_t*>(smraw)[i] = 0u;
   if (tid == 0) {
     tc5::mbar_init(&bar_f, 1); tc5::mbar_init(&bar_d, 1); tc5::mbar_init(&bar_w, 1); tc5::mbar_init(&bar_w2, 1);
+    tc5::mbar_init(&bar_in[0], 1); tc5::mbar_init(&bar_in[1], 1);
     tc5::mbar_init_fence();
     amax_sh = 0u;
   }
@@ -207,20 +208,47 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
   };
   TileInfo ti, tn;
   int buf = 0;
-  auto fetch = [&](const TileInfo& t_, float* dst) {
+  uint32_t par_in[2] = {0u, 0u};
+  // q and x windows of a tile: two TMA boxes issued by one thread (tensor-map TMA, zeros outside [0,T) by the bounds fill),
+  // or cp.async when the tensors do not qualify.  q beyond the dependency cone of the valid steps (t >= Leff + 6) was never
+  // written by kernel A: the cp.async path zero-fills it, the TMA path clears those columns after the box has landed.
+  auto fetch = [&](const TileInfo& t_, int which) {
+    float* dst = which ? QX1 : QX0;
+    if (cm.use_tma) {
+      if (tid == 0) {
+        tc5::fence_async_smem();
+        ::vhmm::tma::expect_tx(&bar_in[which], (uint32_t)(PT * 4 * (K + C)));
+        ::vhmm::tma::load_3d(dst, &tm.q, t_.t0 - HL, 0, (int)t_.b, &bar_in[which]);
+        ::vhmm::tma::load_3d(dst + 8 * PT, &tm.x, t_.t0 - HL, 0, (int)t_.b, &bar_in[which]);
+      }
+      return;
+    }
     const int qmax = (t_.Leff + 6 < cm.T) ? t_.Leff + 6 : cm.T;
     prefetch_rows(dst, cm.q, K, t_.b, cm.T, t_.t0, qmax);
     prefetch_rows(dst + 8 * PT, cm.x, C, t_.b, cm.T, t_.t0, cm.T);
   };
   int64_t tile = next_tile<2>(cm, blockIdx.x, ti);
-  if (tile >= 0) fetch(ti, QX0);
+  if (tile >= 0) fetch(ti, 0);
   cp_async_commit();
   int64_t nxt = (tile >= 0) ? next_tile<2>(cm, tile + gridDim.x, tn) : -1;
   while (tile >= 0) {
-    if (nxt >= 0) fetch(tn, buf ? QX0 : QX1);
+    if (nxt >= 0) fetch(tn, buf ^ 1);
     cp_async_commit();
     const TilePre pre = tile_pre(cm, nxt >= 0 ? nxt + gridDim.x : cm.ntiles);   // consumed after the tile
-    cp_async_wait_prev();
+    if (cm.use_tma) {
+      tc5::mbar_wait(&bar_in[buf], par_in[buf]); par_in[buf] ^= 1u;
+      const int qmax = (ti.Leff + 6 < cm.T) ? ti.Leff + 6 : cm.T;
+      const int j0 = qmax - (ti.t0 - HL);                        // first window column beyond the written part of q
+      if (qmax < cm.T && j0 < NC) {
+        float* qd = buf ? QX1 : QX0;
+        for (int i = tid; i < K * NC; i += NTH) {
+          const int r = i / NC, j = i - r * NC;
+          if (j >= j0) qd[r * PT + j] = 0.f;
+        }
+      }
+    } else {
+      cp_async_wait_prev();
+    }
     PROF(13);
     const float* QX = buf ? QX1 : QX0;
     const int t0 = ti.t0, T = cm.T, Lb = ti.L;

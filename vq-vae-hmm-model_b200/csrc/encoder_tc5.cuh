@@ -141,7 +141,7 @@ __device__ __forceinline__ void encoder_forward_tc5(const float* W1s, const floa
 namespace t5e {
 template <typename CF>
 struct Sz {
-  static constexpr size_t A = (size_t)OPB_A + 4 * (size_t)(CF::SM_A - 3 * CF::H2 * CF::PW_H);   // no fp32 copy of the conv2 weights
+  static constexpr size_t A = (size_t)OPB_A + 4 * (size_t)(CF::SM_A - 3 * CF::H2 * CF::PW_H) + 256;   // no fp32 copy of the conv2 weights; + 2 alignment pads (TMA)
   static constexpr size_t C = (size_t)OPB_C + 4 * (size_t)(CF::SM_C - 3 * CF::H2 * CF::PW_H);
 };
 }  // namespace t5e
@@ -150,13 +150,13 @@ struct Sz {
 // kernel A (tcgen05 build): encoder forward + prior forward/backward
 // =============================================================================================
 template <typename CF>
-__global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_params P) {
+__global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_params P, const __grid_constant__ TmaMaps tm) {
   constexpr int C = CF::C, H = CF::H, H2 = CF::H2, K = CF::K, U = CF::U, TH = CF::TH, K2 = CF::K2;
   static_assert(H == 64 && H2 == 32, "the tcgen05 encoder tiling is written for hidden_dim = 64, hidden_dim2 = 32");
   static_assert(U == 4 && TH == 128 && K2 <= 12, "the FFMA transition-MLP layers are written for u_dim = 4, trans_hidden = 128");
   extern __shared__ __align__(1024) uint8_t smraw[];
   __shared__ double red[NW];
-  __shared__ __align__(8) uint64_t bar_f;
+  __shared__ __align__(8) uint64_t bar_f, bar_in[2];
   __shared__ uint32_t tmem_sh, amax_sh;
   uint8_t* W2h = smraw;                   // fp16 conv2 weights
   uint8_t* RA = W2h + t5e::W_BYTES;       // h1 parts
@@ -171,7 +171,8 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
   float* bt0s = b3s + 16;
   float* bt2s = bt0s + TH;                // [16]
   float* lps = bt2s + 16;                 // [8]
-  float* XU0 = lps + 8;                   // rows 0..7 x, rows 8..15 u (buffer 0; buffer 1 at the end)
+  // the two input buffers are 128-byte aligned (TMA destinations): float offsets rounded up to multiples of 32
+  float* XU0 = sm + ((int)((lps + 8) - sm) + 31) / 32 * 32;   // rows 0..7 x, rows 8..15 u (buffer 0; buffer 1 at the end)
   float* R1 = XU0 + 16 * PT;               // h1 | h2, later the prior's hidden layer a
   float* H1 = R1;
   float* Ab = R1;
@@ -179,10 +180,10 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
   float* Mb = LQ + 16 * PT;               // transition logits -> log_A, row i*K+j
   float* dMb = Mb + 16 * PT;
   float* acc = dMb + 16 * PT;             // ACC_A
-  float* XU1 = acc + CF::ACC_A;
+  float* XU1 = sm + ((int)((acc + CF::ACC_A) - sm) + 31) / 32 * 32;
   float* H2b = XU1 + 16 * PT;             // h2 has its own rows: R1 holds the prior's hidden layer a by the time it is written
   for (int i = threadIdx.x; i < (int)(t5e::Sz<CF>::A / 4); i += NTH) reinterpret_cast<uint32_t*>(smraw)[i] = 0u;
-  if (threadIdx.x == 0) { tc5::mbar_init(&bar_f, 1); tc5::mbar_init_fence(); amax_sh = 0u; }
+  if (threadIdx.x == 0) { tc5::mbar_init(&bar_f, 1); tc5::mbar_init(&bar_in[0], 1); tc5::mbar_init(&bar_in[1], 1); tc5::mbar_init_fence(); amax_sh = 0u; }
   if (threadIdx.x < 32) tc5::tmem_alloc512(&tmem_sh);
   __syncthreads();
   const float sW = stage_w2e_f16<CF>(W2h, P.p[P_E2W], &amax_sh);
@@ -209,22 +210,36 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
   int ndone = 0;
   TileInfo ti, tn;
   int buf = 0;
-  auto fetch = [&](const TileInfo& t_, float* dst) {
+  uint32_t par_in[2] = {0u, 0u};
+  // the x and u windows of a tile: two TMA boxes (PT columns from t0-4, all rows, one sequence; zeros outside [0,T) by the
+  // TMA's bounds fill) issued by one thread, or the cp.async path when the tensors do not qualify (T % 4, alignment)
+  auto fetch = [&](const TileInfo& t_, int which) {
+    float* dst = which ? XU1 : XU0;
+    if (cm.use_tma) {
+      if (tid == 0) {
+        tc5::fence_async_smem();
+        ::vhmm::tma::expect_tx(&bar_in[which], (uint32_t)(PT * 4 * (C + U)));
+        ::vhmm::tma::load_3d(dst, &tm.x, t_.t0 - HL, 0, (int)t_.b, &bar_in[which]);
+        ::vhmm::tma::load_3d(dst + 8 * PT, &tm.u, t_.t0 - HL, 0, (int)t_.b, &bar_in[which]);
+      }
+      return;
+    }
     prefetch_rows(dst, cm.x, C, t_.b, cm.T, t_.t0, cm.T);
     prefetch_rows(dst + 8 * PT, cm.u, U, t_.b, cm.T, t_.t0, cm.T);
   };
   int64_t tile = next_tile<6>(cm, blockIdx.x, ti);
-  if (tile >= 0) fetch(ti, XU0);
+  if (tile >= 0) fetch(ti, 0);
   cp_async_commit();
   int64_t nxt = (tile >= 0) ? next_tile<6>(cm, tile + gridDim.x, tn) : -1;
   while (tile >= 0) {
     PROF(12);
-    if (nxt >= 0) fetch(tn, buf ? XU0 : XU1);
+    if (nxt >= 0) fetch(tn, buf ^ 1);
     cp_async_commit();
     PROF(9);
     const TilePre pre = tile_pre(cm, nxt >= 0 ? nxt + gridDim.x : cm.ntiles);   // consumed after the tile
     PROF(10);
-    cp_async_wait_prev();
+    if (cm.use_tma) { tc5::mbar_wait(&bar_in[buf], par_in[buf]); par_in[buf] ^= 1u; }
+    else cp_async_wait_prev();
     PROF(11);
     const float* XU = buf ? XU1 : XU0;
     const int t0 = ti.t0, T = cm.T, L = ti.L;
@@ -357,7 +372,7 @@ __global__ void __launch_bounds__(NTH, 1) enc_prior_tc5_kernel(Common cm, vhmm_p
 // kernel C (tcgen05 build): encoder backward (forward recomputed in the tile)
 // =============================================================================================
 template <typename CF>
-__global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_params P) {
+__global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_params P, const __grid_constant__ TmaMaps tm) {
   constexpr int C = CF::C, H = CF::H, H2 = CF::H2, K = CF::K;
   static_assert(H == 64 && H2 == 32, "the tcgen05 encoder tiling is written for hidden_dim = 64, hidden_dim2 = 32");
   static_assert(K <= 4, "the stored logits ride in rows 4..7 of the dq_dec input group");

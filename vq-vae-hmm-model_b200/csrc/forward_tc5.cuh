@@ -30,6 +30,7 @@ struct FwdArgs {
   float* q;             // (B,K,T) or null
   float* mu;            // (B,C,T) DEC
   float* logvar;        // (B,C,T) DEC
+  int use_tma;          // the input windows arrive by tensor-map TMA (T % 4 == 0, aligned base); else cp.async
 };
 
 namespace t5f {
@@ -44,7 +45,7 @@ struct Lay {
   static constexpr int BIAS = WP + 16 * CF::PW_H;                // b1 H | b2 H2 | b3 16 | bd1 H | bd2 H | bp 16
   static constexpr int NBIAS = CF::H + CF::H2 + 16 + CF::H + CF::H + 16;
   static constexpr int PADF = BIAS + NBIAS;                      // 4 floats of slack in front of the input rows (column -1 reads)
-  static constexpr int IN0 = PADF + 4;                           // [8][PT] staged input rows (x or q), buffer 0
+  static constexpr int IN0 = (PADF + 4 + 31) / 32 * 32;           // [8][PT] staged input rows (x or q), buffer 0; 128-byte aligned (TMA)
   static constexpr int IN1 = IN0 + 8 * PT;                       // buffer 1
   static constexpr int LQ = IN1 + 8 * PT;                        // [16][PT] logits -> q
   static constexpr int S = LQ + 16 * PT;                         // [H][PT] h1 (fp32), later g2
@@ -56,13 +57,13 @@ struct Lay {
 }  // namespace t5f
 
 template <typename CF, bool ENC, bool DEC>
-__global__ void __launch_bounds__(NTH, 1) forward_tc5_kernel(FwdArgs fa, vhmm_params P) {
+__global__ void __launch_bounds__(NTH, 1) forward_tc5_kernel(FwdArgs fa, vhmm_params P, const __grid_constant__ CUtensorMap tm_in) {
   constexpr int C = CF::C, H = CF::H, H2 = CF::H2, K = CF::K;
   static_assert(H == 64 && H2 == 32, "the tcgen05 tiling is written for hidden_dim = 64, hidden_dim2 = 32");
   static_assert(ENC || DEC, "nothing to do");
   using L = t5f::Lay<CF, ENC, DEC>;
   extern __shared__ __align__(1024) uint8_t smraw[];
-  __shared__ __align__(8) uint64_t bar_e, bar_d;
+  __shared__ __align__(8) uint64_t bar_e, bar_d, bar_in[2];
   __shared__ uint32_t tmem_sh, amax_sh;
   uint8_t* W2e = smraw;                                        // fp16 encoder conv2 weights (ENC)
   uint8_t* W2d = W2e + (ENC ? t5e::W_BYTES : 0);               // fp16 decoder conv2 weights (DEC)
@@ -88,7 +89,10 @@ __global__ void __launch_bounds__(NTH, 1) forward_tc5_kernel(FwdArgs fa, vhmm_pa
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
 
   for (int i = tid; i < (int)(L::BYTES / 4); i += NTH) reinterpret_cast<uint32_t*>(smraw)[i] = 0u;
-  if (tid == 0) { tc5::mbar_init(&bar_e, 1); tc5::mbar_init(&bar_d, 1); tc5::mbar_init_fence(); amax_sh = 0u; }
+  if (tid == 0) {
+    tc5::mbar_init(&bar_e, 1); tc5::mbar_init(&bar_d, 1); tc5::mbar_init(&bar_in[0], 1); tc5::mbar_init(&bar_in[1], 1);
+    tc5::mbar_init_fence(); amax_sh = 0u;
+  }
   if (w == 0) tc5::tmem_alloc512(&tmem_sh);
   __syncthreads();
   float sWe = 1.f, sWd = 1.f, sA = 1.f;
@@ -157,21 +161,31 @@ __global__ void __launch_bounds__(NTH, 1) forward_tc5_kernel(FwdArgs fa, vhmm_pa
   __syncthreads();   // everybody has read amax_sh
 
   const int T = fa.T;
-  auto fetch = [&](int64_t tile, float* dst) {
+  constexpr int IN_ROWS = ENC ? C : K;
+  uint32_t par_in[2] = {0u, 0u};
+  auto fetch = [&](int64_t tile, int which) {
+    float* dst = which ? IN1 : IN0;
     const int64_t b = tile / fa.tiles_per_seq;
     const int t0 = (int)(tile - b * fa.tiles_per_seq) * TT;
-    if (ENC) prefetch_rows(dst, fa.x, C, b, T, t0, T);
+    if (fa.use_tma) {   // one box {132 columns from t0-4, all rows, sequence b}; zeros outside [0,T) by the TMA's own bounds fill
+      if (tid == 0) {
+        tc5::fence_async_smem();                     // earlier generic-proxy accesses of the buffer vs the async-proxy write
+        ::vhmm::tma::expect_tx(&bar_in[which], (uint32_t)(PT * 4 * IN_ROWS));
+        ::vhmm::tma::load_3d(dst, &tm_in, t0 - HL, 0, (int)b, &bar_in[which]);
+      }
+    } else if (ENC) prefetch_rows(dst, fa.x, C, b, T, t0, T);
     else prefetch_rows(dst, fa.q_in, K, b, T, t0, T);
   };
   int64_t tile = blockIdx.x;
   int buf = 0;
-  if (tile < fa.ntiles) fetch(tile, IN0);
+  if (tile < fa.ntiles) fetch(tile, 0);
   cp_async_commit();
   for (; tile < fa.ntiles; tile += gridDim.x) {
     const int64_t nxt = tile + gridDim.x;
-    if (nxt < fa.ntiles) fetch(nxt, buf ? IN0 : IN1);
+    if (nxt < fa.ntiles) fetch(nxt, buf ^ 1);
     cp_async_commit();
-    cp_async_wait_prev();
+    if (fa.use_tma) { tc5::mbar_wait(&bar_in[buf], par_in[buf]); par_in[buf] ^= 1u; }
+    else cp_async_wait_prev();
     const float* IN = buf ? IN1 : IN0;
     const int64_t b = tile / fa.tiles_per_seq;
     const int t0 = (int)(tile - b * fa.tiles_per_seq) * TT;

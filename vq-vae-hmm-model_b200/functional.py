@@ -300,6 +300,11 @@ def elbo_decoder_select(variant: str = "auto"):
     check(_lib.lib().vhmm_elbo_decoder_select(code), "vhmm_elbo_decoder_select")
 
 
+def tma_select(on: bool):
+    """Input windows of the tile kernels by tensor-map TMA (True) or cp.async (False, default).  include/vhmm.h."""
+    check(_lib.lib().vhmm_tma_select(1 if on else 0), "vhmm_tma_select")
+
+
 def hmm_posterior_select(variant: str = "auto"):
     """Posterior kernels for K <= 4: "auto" (one-pass warp kernel when it applies) | "sweep"
     (forward + backward sweep, one thread per sequence).  include/vhmm.h."""
