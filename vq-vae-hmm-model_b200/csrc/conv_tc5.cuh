@@ -631,7 +631,8 @@ static inline int launch_conv_tc5(const float* x, const Tc5Weights& W, const flo
 }  // namespace vhmm
 
 // =============================================================================================================
-// weight gradient on the tensor core
+// weight gradient on the tensor core.  (Measured and dropped: converting item i+1 under the MMAs of item i with two operand-part
+// buffers and ONE fp32 staging buffer -- the exposed load latency cost more than the overlap gained: 209 vs 202 ms per cfg-5 step.)
 // =============================================================================================================
 namespace vhmm {
 namespace ct5 {
@@ -702,15 +703,17 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a) {
     float* xs = ds + WB * DY_P;
     const float* dyb = a.dy + (b * a.Cout + (int64_t)bo * WB) * T;
     const float* xb = a.x + (b * a.Cin + (int64_t)bc * WB) * T;
+    // channels beyond the tensor's own count (skinny layers padded up to the 64-channel block) are zero-filled
+    const int no = a.Cout - bo * WB, nc = a.Cin - bc * WB;
     for (int i = tid; i < WB * 32; i += WNT) {
       const int c = i >> 5, j = (i & 31) * 4, t = t0 + j;
-      const bool ok = t < T;
-      cp16(ds + c * DY_P + j, dyb + (int64_t)c * T + (ok ? t : 0), ok ? 16 : 0);
+      const bool ok = t < T && c < no;
+      cp16(ds + c * DY_P + j, dyb + (ok ? (int64_t)c * T + t : 0), ok ? 16 : 0);
     }
     for (int i = tid; i < WB * 34; i += WNT) {
       const int c = i / 34, j = (i - c * 34) * 4, t = t0 - 4 + j;
-      const bool ok = (t >= 0 && t < T);
-      cp16(xs + c * X_P + j, xb + (int64_t)c * T + (ok ? t : 0), ok ? 16 : 0);
+      const bool ok = (t >= 0 && t < T && c < nc);
+      cp16(xs + c * X_P + j, xb + (ok ? (int64_t)c * T + t : 0), ok ? 16 : 0);
     }
   };
   int64_t item = s;
@@ -798,6 +801,7 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a) {
   float* dst = a.part + (int64_t)s * a.part_stride;
   for (int i = tid; i < WB * WB * KW; i += WNT) {
     const int k = i % KW, c = (i / KW) % WB, o = i / (KW * WB);
+    if (bo * WB + o >= a.Cout || bc * WB + c >= a.Cin) continue;     // padding channels of a skinny layer
     const float v = (red[o * RP + k * 64 + c] + red[(o + 64) * RP + k * 64 + c]) * inv;
     dst[a.w_base + (int64_t)(bo * WB + o) * a.w_so + (int64_t)(bc * WB + c) * a.w_sc + (int64_t)k * a.w_st] = v;
   }
@@ -830,11 +834,13 @@ __global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict_
 }  // namespace ct5
 
 static inline bool wgrad_tc5_ok(int Cin, int Cout, int64_t T, int kw, const void* dy, const void* x) {
-  return (kw == 1 || kw == 3) && Cin % ct5::WB == 0 && Cout % ct5::WB == 0 && (T & 3) == 0 && T >= 4 &&
+  // channel counts are padded up to the 64-channel block (zero-filled): skinny layers (the embedding 256 x 32, to_logits
+  // 32 x 128, to_params 10 x 256, transition_net.0 128 x 16) still beat their FFMA build by ~3x; below 8 channels FFMA stays
+  return (kw == 1 || kw == 3) && Cin >= 8 && Cout >= 8 && (Cin >= 64 || Cout >= 64) && (T & 3) == 0 && T >= 4 &&
          (((uintptr_t)dy | (uintptr_t)x) & 15) == 0;
 }
 static inline int wgrad_tc5_nsplit(int Cin, int Cout, int64_t B, int64_t T) {
-  const int64_t blocks = (int64_t)(Cout / ct5::WB) * (Cin / ct5::WB);
+  const int64_t blocks = cdiv(Cout, ct5::WB) * cdiv(Cin, ct5::WB);
   int64_t ns = cdiv(2 * (int64_t)device_sm_count(), blocks);     // ~2 waves of CTAs: balances the (b, tile) items
   const int64_t items = B * cdiv(T, ct5::TM);
   if (ns > items) ns = items;
@@ -860,8 +866,8 @@ static inline int launch_wgrad_tc5(const float* dy, const float* x, float* gW, f
   a.dy = dy; a.x = x; a.part = scratch; a.part_stride = nW;
   a.w_base = layout.base; a.w_so = layout.so; a.w_sc = layout.sc; a.w_st = layout.st;
   a.amax_dy = amax_dy_known ? amax_dy_known : words; a.amax_x = amax_x_known ? amax_x_known : words + 1;
-  a.B = B; a.Cin = Cin; a.Cout = Cout; a.T = (int)T; a.ntt = (int)cdiv(T, ct5::TM); a.nbc = Cin / ct5::WB; a.nsplit = ns;
-  const unsigned grid = (unsigned)((Cout / ct5::WB) * (Cin / ct5::WB) * ns);
+  a.B = B; a.Cin = Cin; a.Cout = Cout; a.T = (int)T; a.ntt = (int)cdiv(T, ct5::TM); a.nbc = (int)cdiv(Cin, ct5::WB); a.nsplit = ns;
+  const unsigned grid = (unsigned)(cdiv(Cout, ct5::WB) * cdiv(Cin, ct5::WB) * ns);
   if (kw == 3) {
     static PerDeviceOnce once;
     if (once.pending()) {

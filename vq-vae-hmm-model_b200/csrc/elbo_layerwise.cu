@@ -189,8 +189,8 @@ static LayerwiseSizes layerwise_sizes(const vhmm_dims& d) {
   v = wgrad_scratch_floats(d.H, 2 * d.C, 1, BIG); m = v > m ? v : m;
   // tensor-core weight gradients keep one partial per (weight block, split): upper bound over the batch size
   auto tc5s = [&](int Cin, int Cout, int kw) {
-    if (Cin % ct5::WB || Cout % ct5::WB) return (int64_t)0;
-    const int64_t blocks = (int64_t)(Cout / ct5::WB) * (Cin / ct5::WB);
+    if (Cin < 8 || Cout < 8) return (int64_t)0;
+    const int64_t blocks = cdiv(Cout, ct5::WB) * cdiv(Cin, ct5::WB);
     return cdiv(2 * (int64_t)device_sm_count(), blocks) * ((int64_t)Cin * Cout * kw) + 64 + 32 * (int64_t)Cout;
   };
   v = tc5s(d.H, d.H2, 3); m = v > m ? v : m;
@@ -199,6 +199,8 @@ static LayerwiseSizes layerwise_sizes(const vhmm_dims& d) {
   v = tc5s(d.H2, d.K, 1); m = v > m ? v : m;
   v = tc5s(d.K, d.H, 1); m = v > m ? v : m;
   v = tc5s(d.U, d.TH, 1); m = v > m ? v : m;
+  v = tc5s(d.H, 2 * d.C, 1); m = v > m ? v : m;
+  v = tc5s(d.C, d.H, 3); m = v > m ? v : m;
   s.scratch = m;
   return s;
 }
