@@ -86,20 +86,22 @@ struct Tc5Ctx {
     return nullptr;
   }
 };
-struct Tc5Layer { int param, Cin, Cout, kw, need_dgrad; };
+struct Tc5Layer { int param, Cin, Cout, kw, need_dgrad, emb; };   // emb: the (K,H) embedding read as a 1x1 conv K -> H
 // (parameter, Cin, Cout, kw, dgrad needed) of the layers that can be GEMM-shaped at large widths
 static int tc5_layers(const vhmm_dims& d, Tc5Layer* L) {
   int n = 0;
-  L[n++] = Tc5Layer{P_E2W, d.H, d.H2, 3, 1};
-  L[n++] = Tc5Layer{P_T0W, d.U, d.TH, 1, 0};
-  L[n++] = Tc5Layer{P_T2W, d.TH, d.K * d.K, 1, 1};
-  L[n++] = Tc5Layer{P_D1W, d.H, d.H, 3, 1};
-  L[n++] = Tc5Layer{P_D2W, d.H, d.H, 3, 1};
+  L[n++] = Tc5Layer{P_E2W, d.H, d.H2, 3, 1, 0};
+  L[n++] = Tc5Layer{P_E3W, d.H2, d.K, 1, 1, 0};          // forward 128 -> 32 stays FFMA; its input gradient 32 -> 128 qualifies
+  L[n++] = Tc5Layer{P_T0W, d.U, d.TH, 1, 0, 0};
+  L[n++] = Tc5Layer{P_T2W, d.TH, d.K * d.K, 1, 1, 0};
+  L[n++] = Tc5Layer{P_EMB, d.K, d.H, 1, 0, 1};           // e = E^T q (VQ_VAE_HMM_fixed.py:83)
+  L[n++] = Tc5Layer{P_D1W, d.H, d.H, 3, 1, 0};
+  L[n++] = Tc5Layer{P_D2W, d.H, d.H, 3, 1, 0};
   return n;
 }
 static bool tc5_shape(int Cin, int Cout) { return Cin % ct5::KC == 0 && Cout % ct5::TN == 0; }
 static size_t tc5_ctx_bytes(const vhmm_dims& d) {
-  Tc5Layer L[8];
+  Tc5Layer L[12];
   const int n = tc5_layers(d, L);
   size_t b = 0;
   for (int i = 0; i < n; ++i) {
@@ -116,7 +118,7 @@ static int tc5_ctx_prepare(const vhmm_dims& d, const vhmm_params& P, bool with_d
   ctx->pool = A.take<uint32_t>(Tc5Ctx::NW);
   if (!A.ok) { ctx->pool = nullptr; return 0; }
   { int rc0 = ctx->reset(st); if (rc0) return rc0; }
-  Tc5Layer L[8];
+  Tc5Layer L[12];
   const int n = tc5_layers(d, L);
   for (int i = 0; i < n; ++i) {
     const float* w = P.p[L[i].param];
@@ -126,7 +128,8 @@ static int tc5_ctx_prepare(const vhmm_dims& d, const vhmm_params& P, bool with_d
       if (!A.ok) return 0;     // the caller reports the workspace shortfall
       Tc5Ctx::Entry& en = ctx->e[ctx->n++];
       en.w = w; en.dgrad = 0;
-      int rc = conv_tc5_prepare(wview_fwd(w, L[i].Cin, L[i].kw), nw, L[i].Cin, L[i].Cout, L[i].kw, buf, &en.tw, st);
+      const WView fv = L[i].emb ? WView{w, 0, 1, L[i].Cout, 0} : wview_fwd(w, L[i].Cin, L[i].kw);   // emb: W(o=d, c=k) = E[k*H + d]
+      int rc = conv_tc5_prepare(fv, nw, L[i].Cin, L[i].Cout, L[i].kw, buf, &en.tw, st);
       if (rc) return rc;
     }
     if (with_dgrad && L[i].need_dgrad && tc5_shape(L[i].Cout, L[i].Cin)) {
@@ -250,7 +253,7 @@ static int decoder_chain(const vhmm_dims& d, const vhmm_params& P, const float* 
                          int64_t T, float* e, float* g1, float* g2, cudaStream_t st, const Tc5Ctx* ctx = nullptr) {
   int rc;
   WView emb{P.p[P_EMB], 0, 1, d.H, 0};  // W(o=d, c=k) = E[k*H + d]   (VQ_VAE_HMM_fixed.py:83)
-  if ((rc = launch_conv(q, emb, nullptr, nullptr, e, B, d.K, d.H, T, 1, EPI_NONE, st))) return rc;
+  if ((rc = cconv(ctx, 0, q, emb, nullptr, nullptr, e, B, d.K, d.H, T, 1, EPI_NONE, st))) return rc;
   if ((rc = cconv(ctx, 0, e, wview_fwd(P.p[P_D1W], d.H, 3), P.p[P_D1B], nullptr, g1, B, d.H, d.H, T, 3, EPI_RELU, st))) return rc;
   return cconv(ctx, 0, g1, wview_fwd(P.p[P_D2W], d.H, 3), P.p[P_D2B], nullptr, g2, B, d.H, d.H, T, 3, EPI_RELU, st);
 }
@@ -433,7 +436,7 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
     }
     // ---------------- backward: encoder ----------------
     RC(cwgrad(&ctx, dl, h2, grads + off[P_E3W], grads + off[P_E3B], wview_fwd(nullptr, H2, 1), nb, H2, K, T, 1, scratch, st));
-    RC(launch_conv(dl, wview_dgrad(P.p[P_E3W], H2, 1), nullptr, h2, dh2, nb, K, H2, T, 1, EPI_MASK, st));
+    RC(cconv(&ctx, 1, dl, wview_dgrad(P.p[P_E3W], H2, 1), nullptr, h2, dh2, nb, K, H2, T, 1, EPI_MASK, st));
     RC(cwgrad(&ctx, dh2, h1, grads + off[P_E2W], grads + off[P_E2B], wview_fwd(nullptr, H, 3), nb, H, H2, T, 3, scratch, st));
     RC(cconv(&ctx, 1, dh2, wview_dgrad(P.p[P_E2W], H, 3), nullptr, h1, dh1, nb, H2, H, T, 3, EPI_MASK, st));
     RC(cwgrad(&ctx, dh1, xc, grads + off[P_E1W], grads + off[P_E1B], wview_fwd(nullptr, C, 3), nb, C, H, T, 3, scratch, st));
