@@ -407,7 +407,12 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
       else {
         dim3 gr((unsigned)cdiv(T, 32), (unsigned)nb);
         nblk = (int64_t)gr.x * gr.y;
-        loss_seed_rows_kernel<<<gr, 32 * K, 0, st>>>(xc, p, q, lq, M, log_pi, Lc, norms, betaf, C, K, (int)T, partial, dp, dqp, dM);
+        const bool al16 = ((((uintptr_t)xc | (uintptr_t)p | (uintptr_t)q | (uintptr_t)lq | (uintptr_t)M | (uintptr_t)dp | (uintptr_t)dqp |
+                              (uintptr_t)dM) & 15) == 0);
+        if ((T & 3) == 0 && al16)     // four steps per thread, 128-bit accesses
+          loss_seed_rows4_kernel<<<gr, 8 * K, 0, st>>>(xc, p, q, lq, M, log_pi, Lc, norms, betaf, C, K, (int)T, partial, dp, dqp, dM);
+        else
+          loss_seed_rows_kernel<<<gr, 32 * K, 0, st>>>(xc, p, q, lq, M, log_pi, Lc, norms, betaf, C, K, (int)T, partial, dp, dqp, dM);
       }
       VHMM_LAUNCH_CHECK();
       sum_partials_kernel<<<1, 1024, 0, st>>>(partial, nblk, sums);
