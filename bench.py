@@ -266,8 +266,8 @@ def run_stages(torch, V, Fn, model, dev, local, pk, quick=False):
         out.append(stage_line("hmm_scan (all-prefix alpha)", cfg, ms, it, ck, B * T, inb + 4 * K, pk))
         del log_A, log_b
         # ---- cfg 5 recursion shapes: K = 32 (warp-per-sequence kernels), T = 1024
-        B, T, K = 2048, 1024, 32
-        cfg = f"cfg5 recursion: B={B} T={T} K={K} (B bounded by the materialised log_A: 4,224 B/step)"
+        B, T, K = 8192, 1024, 32
+        cfg = f"cfg5 recursion: B={B} T={T} K={K} (a quarter of the cfg-5 batch: the materialised log_A is 4,224 B/step = 35 GB here)"
         log_pi, log_A, log_b = synth_hmm_inputs(torch, dev, B, T, K, 12)
         L = torch.full((B,), T, dtype=torch.int64, device=dev)
         inb = 4 * (K * K + K)
