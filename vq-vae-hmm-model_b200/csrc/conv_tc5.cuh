@@ -24,6 +24,7 @@
 #pragma once
 #include "conv_generic.cuh"
 #include "tc5.cuh"
+#include "tma.cuh"
 
 namespace vhmm {
 namespace ct5 {
@@ -631,8 +632,7 @@ static inline int launch_conv_tc5(const float* x, const Tc5Weights& W, const flo
 }  // namespace vhmm
 
 // =============================================================================================================
-// weight gradient on the tensor core.  (Measured and dropped: converting item i+1 under the MMAs of item i with two operand-part
-// buffers and ONE fp32 staging buffer -- the exposed load latency cost more than the overlap gained: 209 vs 202 ms per cfg-5 step.)
+// weight gradient on the tensor core
 // =============================================================================================================
 namespace vhmm {
 namespace ct5 {
@@ -643,9 +643,17 @@ constexpr int DY_ROWS = 128, X_ROWS = 130;   // dy row r <-> t0 + r; x row r <->
 constexpr int DY_PLANE = DY_ROWS * 16, X_PLANE = X_ROWS * 16;
 constexpr int DY_PARTS = 2 * 8 * DY_PLANE;   // [part][plane][row][8]: the m planes directly follow the h planes
 constexpr int X_PARTS = 2 * 8 * X_PLANE;
-constexpr int DY_P = 132, X_P = 140;         // fp32 staging pitches; x window = t0-4 .. t0+131
-constexpr int WSTAGE = (WB * DY_P + WB * X_P) * 4;
-constexpr int WSM_TOTAL = 2 * WSTAGE + DY_PARTS + X_PARTS;
+constexpr int DY_P = 128, X_P = 136;         // fp32 staging pitches = TMA box widths; x window = t0-4 .. t0+131
+// One buffer holds an item first as fp32 (a TMA box of dy and one of x: out-of-range columns and the padding channels of
+// a skinny layer arrive as zeros) and then, converted IN PLACE, as fp16 operand parts (an element is 4 bytes either
+// way).  Three buffers: item i feeds the MMAs, item i+1 is converted, item i+2 is in flight.
+constexpr int WDY_BYTES = WB * DY_P * 4, WX_BYTES = WB * X_P * 4;
+static_assert(WDY_BYTES >= DY_PARTS && WX_BYTES >= X_PARTS, "parts fit in their fp32 staging");
+static_assert(WDY_BYTES % 128 == 0 && WX_BYTES % 128 == 0, "TMA destinations stay 128-byte aligned");
+constexpr int WBUF = WDY_BYTES + WX_BYTES;
+constexpr int WNBUF = 3;
+constexpr int WSM_TOTAL = WNBUF * WBUF;
+static_assert(WSM_TOTAL >= 128 * (3 * 64 + 1) * 4, "final reduction tile fits");
 
 struct WgradArgs {
   const float* dy;         // (B,Cout,T)
@@ -664,16 +672,26 @@ struct WgradArgs {
 // Per item: [dy_h; dy_m] (M = 128) x [x_h; x_m] (N = 128) over K = 128 time steps per tap into TMEM (all four part
 // products at once, the m*m quadrant is ignored), then drained into per-thread fp32 registers (RN adds): the TMEM
 // accumulation chains stay 8 MMAs long, whatever the batch size.
+// Pipeline (per item i): one thread issues the two TMA boxes of item i+1, all 16 warps convert item i in place while the
+// MMAs of item i-1 run, then -- KW = 3, one TMEM accumulator set: the MMAs of i-1 are drained and those of i issued;
+// KW = 1, two sets: the MMAs of i are issued first and i-1 is drained under them.  (The first build of this kernel loaded
+// with 16-byte cp.async: 825 instructions per thread and item, half of them address arithmetic, issue-bound at IPC 2.)
 template <int KW>
-__global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a) {
+__global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a, const __grid_constant__ CUtensorMap tm_dy,
+                                                          const __grid_constant__ CUtensorMap tm_x) {
   constexpr int PAD = KW / 2;
+  constexpr int NSET = (KW == 1) ? 2 : 1;
   extern __shared__ __align__(1024) uint8_t sm[];
-  __shared__ __align__(8) uint64_t bar;
+  __shared__ __align__(8) uint64_t bar[2];
+  __shared__ __align__(8) uint64_t ld_bar[WNBUF];
   __shared__ uint32_t tmem_sh;
-  uint8_t* dyp = sm + 2 * WSTAGE;
-  uint8_t* xp = dyp + DY_PARTS;
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
-  if (tid == 0) { tc5::mbar_init(&bar, 1); tc5::mbar_init_fence(); }
+  if (tid == 0) {
+    tc5::mbar_init(&bar[0], 1); tc5::mbar_init(&bar[1], 1);
+#pragma unroll
+    for (int i = 0; i < WNBUF; ++i) tc5::mbar_init(&ld_bar[i], 1);
+    tc5::mbar_init_fence();
+  }
   if (w == 0) tc5::tmem_alloc512(&tmem_sh);
   tc5::fence_before_sync();
   __syncthreads();
@@ -684,9 +702,9 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a) {
   const int s = blockIdx.x % a.nsplit;
   const int blk = blockIdx.x / a.nsplit;
   const int bc = blk % a.nbc, bo = blk / a.nbc;
-  const int T = a.T;
   const int64_t nitems = a.B * a.ntt;
-  uint32_t par = 0;
+  uint32_t par = 0;                     // bit `set`: phase parity of bar[set]
+  uint32_t ldpar = 0;                   // bit `buf`: phase parity of ld_bar[buf]
   constexpr uint32_t IDESC = tc5::idesc_f16(128, 1, 1);
   float acc[KW][16];
 #pragma unroll
@@ -696,74 +714,89 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a) {
   const uint32_t lane_base = (uint32_t)(32 * (w & 3)) << 16;
   const int cq = w >> 2;
 
-  auto issue_loads = [&](int64_t item, int stage) {
+  auto issue_loads = [&](int64_t item, int buf) {          // thread 0 only
     const int64_t b = item / a.ntt;
     const int t0 = (int)(item - b * a.ntt) * TM;
-    float* ds = reinterpret_cast<float*>(sm + stage * WSTAGE);
-    float* xs = ds + WB * DY_P;
-    const float* dyb = a.dy + (b * a.Cout + (int64_t)bo * WB) * T;
-    const float* xb = a.x + (b * a.Cin + (int64_t)bc * WB) * T;
-    // channels beyond the tensor's own count (skinny layers padded up to the 64-channel block) are zero-filled
-    const int no = a.Cout - bo * WB, nc = a.Cin - bc * WB;
-    for (int i = tid; i < WB * 32; i += WNT) {
-      const int c = i >> 5, j = (i & 31) * 4, t = t0 + j;
-      const bool ok = t < T && c < no;
-      cp16(ds + c * DY_P + j, dyb + (ok ? (int64_t)c * T + t : 0), ok ? 16 : 0);
-    }
-    for (int i = tid; i < WB * 34; i += WNT) {
-      const int c = i / 34, j = (i - c * 34) * 4, t = t0 - 4 + j;
-      const bool ok = (t >= 0 && t < T && c < nc);
-      cp16(xs + c * X_P + j, xb + (ok ? (int64_t)c * T + t : 0), ok ? 16 : 0);
-    }
+    ::vhmm::tma::expect_tx(&ld_bar[buf], (uint32_t)WBUF);
+    ::vhmm::tma::load_3d(sm + buf * WBUF, &tm_dy, t0, bo * WB, (int)b, &ld_bar[buf]);
+    ::vhmm::tma::load_3d(sm + buf * WBUF + WDY_BYTES, &tm_x, t0 - 4, bc * WB, (int)b, &ld_bar[buf]);
   };
-  int64_t item = s;
-  if (item < nitems) issue_loads(item, 0);
-  asm volatile("cp.async.commit_group;" ::: "memory");
-  int stage = 0;
-  bool pending = false;     // MMAs of the previous item not yet drained
-  auto drain = [&]() {
-    tc5::mbar_wait(&bar, par); par ^= 1u;
+  auto drain = [&](int set) {
+    tc5::mbar_wait(&bar[set], (par >> set) & 1u); par ^= 1u << set;
     tc5::fence_after_sync();
 #pragma unroll
     for (int k = 0; k < KW; ++k) {
       float v0[16], v1[16];
-      tc5::tmem_ld16(tmem + lane_base + 128u * k + 16 * cq, v0);
-      tc5::tmem_ld16(tmem + lane_base + 128u * k + 64 + 16 * cq, v1);
+      tc5::tmem_ld16(tmem + lane_base + (uint32_t)(set * 128 * KW) + 128u * k + 16 * cq, v0);
+      tc5::tmem_ld16(tmem + lane_base + (uint32_t)(set * 128 * KW) + 128u * k + 64 + 16 * cq, v1);
 #pragma unroll
       for (int e = 0; e < 16; ++e) acc[k][e] += v0[e] + v1[e];
     }
     tc5::fence_before_sync();
   };
-  for (; item < nitems; item += a.nsplit) {
+  // x rows needed by the MMAs: KW = 3 all 130, KW = 1 rows 1..128 only
+  constexpr int XR0 = (KW == 1) ? 1 : 0, XNR = (KW == 1) ? 128 : X_ROWS;
+
+  int64_t item = s;
+  if (tid == 0 && item < nitems) issue_loads(item, 0);
+  int buf = 0;
+  int64_t n = 0;                        // items done by this CTA
+  for (; item < nitems; item += a.nsplit, ++n) {
     const int64_t nxt = item + a.nsplit;
-    if (nxt < nitems) issue_loads(nxt, stage ^ 1);
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    asm volatile("cp.async.wait_group 1;" ::: "memory");
-    if (pending) drain();          // the operand parts and the TMEM accumulators are free again
-    __syncthreads();
+    const int nbuf = (buf == WNBUF - 1) ? 0 : buf + 1;
+    // that buffer's last reader (the MMAs of item n-2) was drained by this thread in the previous iteration, and its
+    // generic-proxy accesses (conversion of item n-2) lie before several CTA barriers
+    if (tid == 0 && nxt < nitems) issue_loads(nxt, nbuf);
+    tc5::mbar_wait(&ld_bar[buf], (ldpar >> buf) & 1u); ldpar ^= 1u << buf;
+    uint8_t* dyp = sm + buf * WBUF;
+    uint8_t* xp = dyp + WDY_BYTES;
     {
-      const float* ds = reinterpret_cast<const float*>(sm + stage * WSTAGE);
-      const float* xs = ds + WB * DY_P;
-      for (int i = tid; i < 8 * DY_ROWS; i += WNT) {
+      const float* ds = reinterpret_cast<const float*>(dyp);
+      const float* xs = reinterpret_cast<const float*>(xp);
+      uint4 dh[2], dm[2], xh[3], xm[3];
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int i = tid + q * WNT;
         const int pl = i / DY_ROWS, r = i - pl * DY_ROWS;
         __align__(16) __half hh[8], mm[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) tc5::split_f16(ds[(pl * 8 + e) * DY_P + r] * sdy, hh[e], mm[e]);
-        uint8_t* p = dyp + pl * DY_PLANE + r * 16;
-        *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(hh);
-        *reinterpret_cast<uint4*>(p + 8 * DY_PLANE) = *reinterpret_cast<const uint4*>(mm);
+        dh[q] = *reinterpret_cast<const uint4*>(hh); dm[q] = *reinterpret_cast<const uint4*>(mm);
       }
-      for (int i = tid; i < 8 * X_ROWS; i += WNT) {
-        const int pl = i / X_ROWS, r = i - pl * X_ROWS;
-        __align__(16) __half hh[8], mm[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) tc5::split_f16(xs[(pl * 8 + e) * X_P + r + 3] * sx, hh[e], mm[e]);
-        uint8_t* p = xp + pl * X_PLANE + r * 16;
-        *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(hh);
-        *reinterpret_cast<uint4*>(p + 8 * X_PLANE) = *reinterpret_cast<const uint4*>(mm);
+      for (int q = 0; q < 3; ++q) {
+        const int i = tid + q * WNT;
+        if (i < 8 * XNR) {
+          const int pl = i / XNR, r = XR0 + i - pl * XNR;
+          __align__(16) __half hh[8], mm[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) tc5::split_f16(xs[(pl * 8 + e) * X_P + r + 3] * sx, hh[e], mm[e]);
+          xh[q] = *reinterpret_cast<const uint4*>(hh); xm[q] = *reinterpret_cast<const uint4*>(mm);
+        }
+      }
+      __syncthreads();                  // every fp32 value of the buffer is in registers: overwrite it with the parts
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int i = tid + q * WNT;
+        const int pl = i / DY_ROWS, r = i - pl * DY_ROWS;
+        uint8_t* p = dyp + pl * DY_PLANE + r * 16;
+        *reinterpret_cast<uint4*>(p) = dh[q];
+        *reinterpret_cast<uint4*>(p + 8 * DY_PLANE) = dm[q];
+      }
+#pragma unroll
+      for (int q = 0; q < 3; ++q) {
+        const int i = tid + q * WNT;
+        if (i < 8 * XNR) {
+          const int pl = i / XNR, r = XR0 + i - pl * XNR;
+          uint8_t* p = xp + pl * X_PLANE + r * 16;
+          *reinterpret_cast<uint4*>(p) = xh[q];
+          *reinterpret_cast<uint4*>(p + 8 * X_PLANE) = xm[q];
+        }
       }
     }
     tc5::fence_async_smem();
+    const int set = (NSET == 2) ? (int)(n & 1) : 0;
+    if (NSET == 1 && n > 0) drain(0);             // one accumulator set: it must be read before the next item overwrites it
     tc5::fence_before_sync();
     __syncthreads();
     if (w == 0) {
@@ -776,15 +809,15 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a) {
         for (int i = 0; i < 8; ++i) {
           const uint64_t da = tc5::make_desc(sD + (16 * i) * 16, 128, DY_PLANE);
           const uint64_t db = tc5::make_desc(sX + (16 * i + k - PAD + 1) * 16, 128, X_PLANE);
-          if (lead) tc5::mma_f16(tmem + 128u * k, da, db, IDESC, i ? 1u : 0u);
+          if (lead) tc5::mma_f16(tmem + (uint32_t)(set * 128 * KW) + 128u * k, da, db, IDESC, i ? 1u : 0u);
         }
-      if (lead) tc5::commit(&bar);
+      if (lead) tc5::commit(&bar[set]);
       __syncwarp();
     }
-    pending = true;
-    stage ^= 1;
+    if (NSET == 2 && n > 0) drain(set ^ 1);       // the previous item, under the MMAs just issued
+    buf = nbuf;
   }
-  if (pending) drain();
+  if (n > 0) drain((NSET == 2) ? (int)((n - 1) & 1) : 0);
   __syncthreads();
   // lanes l and l + 64 hold the h / m rows of dy for out channel l: combine through shared memory, undo the scales
   float* red = reinterpret_cast<float*>(sm);               // [128 rows][KW * 64 + 1]
@@ -837,11 +870,21 @@ static inline bool wgrad_tc5_ok(int Cin, int Cout, int64_t T, int kw, const void
   // channel counts are padded up to the 64-channel block (zero-filled): skinny layers (the embedding 256 x 32, to_logits
   // 32 x 128, to_params 10 x 256, transition_net.0 128 x 16) still beat their FFMA build by ~3x; below 8 channels FFMA stays
   return (kw == 1 || kw == 3) && Cin >= 8 && Cout >= 8 && (Cin >= 64 || Cout >= 64) && (T & 3) == 0 && T >= 4 &&
-         (((uintptr_t)dy | (uintptr_t)x) & 15) == 0;
+         (((uintptr_t)dy | (uintptr_t)x) & 15) == 0 && tma::encode_fn() != nullptr;
 }
 static inline int wgrad_tc5_nsplit(int Cin, int Cout, int64_t B, int64_t T) {
   const int64_t blocks = cdiv(Cout, ct5::WB) * cdiv(Cin, ct5::WB);
-  int64_t ns = cdiv(2 * (int64_t)device_sm_count(), blocks);     // ~2 waves of CTAs: balances the (b, tile) items
+  // one CTA per SM (the three buffers take the whole shared memory): whole waves only -- a grid of 2 waves + 8 CTAs
+  // costs 3.  Pick the wave count (1..3) that fills the machine best; ties go to fewer waves (fewer partials).
+  const int64_t sms = device_sm_count();
+  int64_t ns = 1;
+  double best = -1.0;
+  for (int64_t wv = 1; wv <= 3; ++wv) {
+    const int64_t k = (wv * sms) / blocks;
+    if (k < 1) continue;
+    const double fill = (double)(k * blocks) / (double)(wv * sms);
+    if (fill > best + 1e-9) { best = fill; ns = k; }
+  }
   const int64_t items = B * cdiv(T, ct5::TM);
   if (ns > items) ns = items;
   return (int)(ns < 1 ? 1 : ns);
@@ -868,20 +911,25 @@ static inline int launch_wgrad_tc5(const float* dy, const float* x, float* gW, f
   a.amax_dy = amax_dy_known ? amax_dy_known : words; a.amax_x = amax_x_known ? amax_x_known : words + 1;
   a.B = B; a.Cin = Cin; a.Cout = Cout; a.T = (int)T; a.ntt = (int)cdiv(T, ct5::TM); a.nbc = (int)cdiv(Cin, ct5::WB); a.nsplit = ns;
   const unsigned grid = (unsigned)(cdiv(Cout, ct5::WB) * cdiv(Cin, ct5::WB) * ns);
+  CUtensorMap tm_dy, tm_x;
+  if (!tma::make_map(&tm_dy, dy, B, Cout, T, ct5::DY_P, ct5::WB) || !tma::make_map(&tm_x, x, B, Cin, T, ct5::X_P, ct5::WB)) {
+    set_error("wgrad_tc5: cuTensorMapEncodeTiled failed (B=%lld Cin=%d Cout=%d T=%lld)", (long long)B, Cin, Cout, (long long)T);
+    return (int)cudaErrorInvalidValue;
+  }
   if (kw == 3) {
     static PerDeviceOnce once;
     if (once.pending()) {
       VHMM_CUDA_CHECK(cudaFuncSetAttribute(ct5::wgrad_tc5_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ct5::WSM_TOTAL));
       once.mark();
     }
-    ct5::wgrad_tc5_kernel<3><<<grid, ct5::WNT, ct5::WSM_TOTAL, st>>>(a);
+    ct5::wgrad_tc5_kernel<3><<<grid, ct5::WNT, ct5::WSM_TOTAL, st>>>(a, tm_dy, tm_x);
   } else {
     static PerDeviceOnce once;
     if (once.pending()) {
       VHMM_CUDA_CHECK(cudaFuncSetAttribute(ct5::wgrad_tc5_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ct5::WSM_TOTAL));
       once.mark();
     }
-    ct5::wgrad_tc5_kernel<1><<<grid, ct5::WNT, ct5::WSM_TOTAL, st>>>(a);
+    ct5::wgrad_tc5_kernel<1><<<grid, ct5::WNT, ct5::WSM_TOTAL, st>>>(a, tm_dy, tm_x);
   }
   VHMM_LAUNCH_CHECK();
   reduce_partials_kernel<<<(unsigned)cdiv(nW, 256), 256, 0, st>>>(scratch, nW, ns, nW, gW);
