@@ -655,6 +655,33 @@ constexpr int WNBUF = 3;
 constexpr int WSM_TOTAL = WNBUF * WBUF;
 static_assert(WSM_TOTAL >= 128 * (3 * 64 + 1) * 4, "final reduction tile fits");
 
+// packed fp32 pairs (Blackwell add / mul .f32x2): one issue slot for two lanes of work -- the kernel below is issue-bound
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t f2_pack(float a, float b) { f2_t r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void f2_unpack(f2_t v, float& a, float& b) { asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ f2_t f2_add(f2_t a, f2_t b) { f2_t r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2_sub(f2_t a, f2_t b) { f2_t r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2_mul(f2_t a, f2_t b) { f2_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+// eight fp32 values (scaled by s2 = {s, s}) -> their fp16 h and m parts as two 16-byte rows (same split as tc5::split_f16)
+__device__ __forceinline__ void split8(const float* v, f2_t s2, uint4& h, uint4& m) {
+  uint32_t hh[4], mm[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const f2_t xs = f2_mul(f2_pack(v[2 * e], v[2 * e + 1]), s2);
+    float x0, x1;
+    f2_unpack(xs, x0, x1);
+    const __half2 h2 = __floats2half2_rn(x0, x1);
+    const float2 hf = __half22float2(h2);
+    float r0, r1;
+    f2_unpack(f2_sub(xs, f2_pack(hf.x, hf.y)), r0, r1);
+    const __half2 m2 = __floats2half2_rn(r0, r1);
+    hh[e] = *reinterpret_cast<const uint32_t*>(&h2);
+    mm[e] = *reinterpret_cast<const uint32_t*>(&m2);
+  }
+  h = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+  m = make_uint4(mm[0], mm[1], mm[2], mm[3]);
+}
+
 struct WgradArgs {
   const float* dy;         // (B,Cout,T)
   const float* x;          // (B,Cin,T)
@@ -706,13 +733,14 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a, const __
   uint32_t par = 0;                     // bit `set`: phase parity of bar[set]
   uint32_t ldpar = 0;                   // bit `buf`: phase parity of ld_bar[buf]
   constexpr uint32_t IDESC = tc5::idesc_f16(128, 1, 1);
-  float acc[KW][16];
+  f2_t acc[KW][8];
 #pragma unroll
   for (int k = 0; k < KW; ++k)
 #pragma unroll
-    for (int e = 0; e < 16; ++e) acc[k][e] = 0.f;
+    for (int e = 0; e < 8; ++e) acc[k][e] = 0ull;          // {0.f, 0.f}
   const uint32_t lane_base = (uint32_t)(32 * (w & 3)) << 16;
   const int cq = w >> 2;
+  const f2_t sdy2 = f2_pack(sdy, sdy), sx2 = f2_pack(sx, sx);
 
   auto issue_loads = [&](int64_t item, int buf) {          // thread 0 only
     const int64_t b = item / a.ntt;
@@ -730,7 +758,8 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a, const __
       tc5::tmem_ld16(tmem + lane_base + (uint32_t)(set * 128 * KW) + 128u * k + 16 * cq, v0);
       tc5::tmem_ld16(tmem + lane_base + (uint32_t)(set * 128 * KW) + 128u * k + 64 + 16 * cq, v1);
 #pragma unroll
-      for (int e = 0; e < 16; ++e) acc[k][e] += v0[e] + v1[e];
+      for (int e = 0; e < 8; ++e)
+        acc[k][e] = f2_add(f2_add(acc[k][e], f2_pack(v0[2 * e], v0[2 * e + 1])), f2_pack(v1[2 * e], v1[2 * e + 1]));
     }
     tc5::fence_before_sync();
   };
@@ -758,20 +787,20 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a, const __
       for (int q = 0; q < 2; ++q) {
         const int i = tid + q * WNT;
         const int pl = i / DY_ROWS, r = i - pl * DY_ROWS;
-        __align__(16) __half hh[8], mm[8];
+        float v[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) tc5::split_f16(ds[(pl * 8 + e) * DY_P + r] * sdy, hh[e], mm[e]);
-        dh[q] = *reinterpret_cast<const uint4*>(hh); dm[q] = *reinterpret_cast<const uint4*>(mm);
+        for (int e = 0; e < 8; ++e) v[e] = ds[(pl * 8 + e) * DY_P + r];
+        split8(v, sdy2, dh[q], dm[q]);
       }
 #pragma unroll
       for (int q = 0; q < 3; ++q) {
         const int i = tid + q * WNT;
         if (i < 8 * XNR) {
           const int pl = i / XNR, r = XR0 + i - pl * XNR;
-          __align__(16) __half hh[8], mm[8];
+          float v[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) tc5::split_f16(xs[(pl * 8 + e) * X_P + r + 3] * sx, hh[e], mm[e]);
-          xh[q] = *reinterpret_cast<const uint4*>(hh); xm[q] = *reinterpret_cast<const uint4*>(mm);
+          for (int e = 0; e < 8; ++e) v[e] = xs[(pl * 8 + e) * X_P + r + 3];
+          split8(v, sx2, xh[q], xm[q]);
         }
       }
       __syncthreads();                  // every fp32 value of the buffer is in registers: overwrite it with the parts
@@ -827,7 +856,12 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a, const __
 #pragma unroll
     for (int k = 0; k < KW; ++k)
 #pragma unroll
-      for (int e = 0; e < 16; ++e) red[row * RP + k * 64 + 16 * cq + e] = acc[k][e];
+      for (int e = 0; e < 8; ++e) {
+        float a0, a1;
+        f2_unpack(acc[k][e], a0, a1);
+        red[row * RP + k * 64 + 16 * cq + 2 * e] = a0;
+        red[row * RP + k * 64 + 16 * cq + 2 * e + 1] = a1;
+      }
   }
   __syncthreads();
   const float inv = 1.f / (sdy * sx);
