@@ -6,6 +6,7 @@
 #include <stdlib.h>
 #include "conv_generic.cuh"
 #include "conv_tc5.cuh"
+#include "prior_tc5.cuh"
 #include "pointwise.cuh"
 
 namespace vhmm {
@@ -47,6 +48,12 @@ int conv1d_fwd(const float* x, const float* w, const float* bias, int64_t B, int
 // ---- tensor-core layer kernels inside the layer-wise path (conv_tc5.cuh) -------------------------------------
 // The weights of the layers whose shape the tcgen05 kernels take are prepared once per call (fp16 parts in the
 // kernel's chunk image): forward view and, where the input gradient is needed, the transposed tap-flipped view.
+// VHMM_PRIOR_FUSED=0 keeps the transition prior of the wide model on the layer-by-layer kernels (A/B timing, tests)
+static bool prior_fused_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("VHMM_PRIOR_FUSED"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v == 1;
+}
 struct Tc5Ctx {
   struct Entry { const float* w; int dgrad; Tc5Weights tw; };
   Entry e[16];
@@ -179,7 +186,7 @@ static LayerwiseSizes layerwise_sizes(const vhmm_dims& d) {
   LayerwiseSizes s;
   const int64_t K2 = (int64_t)d.K * d.K;
   s.per_step_fwd = d.H + d.H2 + 3 * (int64_t)d.K + d.TH + K2 + 3 * (int64_t)d.H + 2 * d.C;
-  s.per_step_bwd = 2 * d.C + d.K + K2 + 3 * (int64_t)d.H + 2 * (int64_t)d.K + d.H2 + d.H + d.TH;
+  s.per_step_bwd = 2 * d.C + d.K + K2 + 3 * (int64_t)d.H + 2 * (int64_t)d.K + d.H2 + d.H + d.TH + 2 * (int64_t)d.K;
   const int64_t BIG = 1 << 20;
   int64_t m = 0, v;
   v = wgrad_scratch_floats(d.C, d.H, 3, BIG); m = v > m ? v : m;
@@ -194,7 +201,7 @@ static LayerwiseSizes layerwise_sizes(const vhmm_dims& d) {
   auto tc5s = [&](int Cin, int Cout, int kw) {
     if (Cin < 8 || Cout < 8) return (int64_t)0;
     const int64_t blocks = cdiv(Cout, ct5::WB) * cdiv(Cin, ct5::WB);
-    return cdiv(2 * (int64_t)device_sm_count(), blocks) * ((int64_t)Cin * Cout * kw) + 64 + 32 * (int64_t)Cout;
+    return ((3 * (int64_t)device_sm_count()) / blocks + 1) * ((int64_t)Cin * Cout * kw) + 64 + 32 * (int64_t)Cout;   // >= wgrad_tc5_nsplit
   };
   v = tc5s(d.H, d.H2, 3); m = v > m ? v : m;
   v = tc5s(d.TH, d.K * d.K, 1); m = v > m ? v : m;
@@ -215,6 +222,7 @@ static size_t fixed_bytes(const vhmm_dims& d, int64_t T) {
   bytes += align_up(sizeof(double) * KMAX, 256);                       // qsum
   bytes += align_up(sizeof(float) * (size_t)s.scratch, 256);
   bytes += tc5_ctx_bytes(d);                                           // prepared tensor-core weights
+  bytes += 64 * 1024;                                                  // per-CTA partial sums of the fused prior kernel
   return bytes + 4096;
 }
 
@@ -340,6 +348,7 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
   float* log_pi = A.take<float>(KMAX);
   double* qsum = A.take<double>(KMAX);
   float* scratch = A.take<float>((size_t)S.scratch);
+  double* prior_partial = A.take<double>(64 * 1024 / sizeof(double));
   Tc5Ctx ctx;
   {
     int rc0 = tc5_ctx_prepare(d, P, grads != nullptr, A, &ctx, st);
@@ -360,8 +369,9 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
   float* e = A.take<float>(n * H);    float* g1 = A.take<float>(n * H);  float* g2 = A.take<float>(n * H);
   float* p = A.take<float>(n * 2 * C);
   float *dp = nullptr, *dqp = nullptr, *dM = nullptr, *dg2 = nullptr, *dg1 = nullptr, *de = nullptr,
-        *dqd = nullptr, *dl = nullptr, *dh2 = nullptr, *dh1 = nullptr, *da = nullptr;
+        *dqd = nullptr, *dl = nullptr, *dh2 = nullptr, *dh1 = nullptr, *da = nullptr, *dq_row = nullptr, *dq_col = nullptr;
   if (grads) {
+    dq_row = A.take<float>(n * K); dq_col = A.take<float>(n * K);
     dp = A.take<float>(n * 2 * C); dqp = A.take<float>(n * K); dM = A.take<float>(n * K2);
     dg2 = A.take<float>(n * H); dg1 = A.take<float>(n * H); de = A.take<float>(n * H);
     dqd = A.take<float>(n * K); dl = A.take<float>(n * K);
@@ -391,8 +401,23 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
       VHMM_LAUNCH_CHECK();
     }
     RC(cconv(&ctx, 0, uc, wview_fwd(P.p[P_T0W], U, 1), P.p[P_T0B], nullptr, a, nb, U, TH, T, 1, EPI_RELU, st));
-    RC(cconv(&ctx, 0, a, wview_fwd(P.p[P_T2W], TH, 1), P.p[P_T2B], nullptr, M, nb, TH, K2, T, 1, EPI_NONE, st));
-    {
+    // transition logits -> log A -> pair term and its gradients: ONE kernel when the shape allows (prior_tc5.cuh), else
+    // the layer, the row log-softmax and the loops of the loss kernel
+    const Tc5Weights* twT2 = (conv_impl_mode() != 1) ? ctx.find(P.p[P_T2W], 0) : nullptr;
+    const bool al16 = ((((uintptr_t)xc | (uintptr_t)p | (uintptr_t)q | (uintptr_t)lq | (uintptr_t)M | (uintptr_t)dp | (uintptr_t)dqp |
+                          (uintptr_t)dM) & 15) == 0);
+    const bool fused_prior = twT2 && prior_fused_enabled() && al16 && prior_tc5_ok(K, TH, T, a, q, dM) &&
+                             4 * prior_tc5_grid(nb, T) * sizeof(double) <= 64 * 1024;
+    if (fused_prior) {
+      int rcm = 0;
+      const uint32_t* ax = ctx.measure(a, nb * (int64_t)TH * T, st, &rcm);
+      RC(rcm);
+      RC(launch_prior_tc5(a, *twT2, P.p[P_T2B], q, Lc, norms, betaf, nb, TH, T, grads ? dM : nullptr, dq_row, dq_col, prior_partial,
+                          grads ? ctx.fresh(dM) : nullptr, st, ax));
+      sum_partials_kernel<<<1, 1024, 0, st>>>(prior_partial, prior_tc5_grid(nb, T), sums);
+      VHMM_LAUNCH_CHECK();
+    } else {
+      RC(cconv(&ctx, 0, a, wview_fwd(P.p[P_T2W], TH, 1), P.p[P_T2B], nullptr, M, nb, TH, K2, T, 1, EPI_NONE, st));
       dim3 g((unsigned)cdiv(T, 256), (unsigned)K, (unsigned)nb);
       row_logsoftmax_kernel<<<g, 256, 0, st>>>(M, K, (int)T);
       VHMM_LAUNCH_CHECK();
@@ -407,10 +432,9 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
       else {
         dim3 gr((unsigned)cdiv(T, 32), (unsigned)nb);
         nblk = (int64_t)gr.x * gr.y;
-        const bool al16 = ((((uintptr_t)xc | (uintptr_t)p | (uintptr_t)q | (uintptr_t)lq | (uintptr_t)M | (uintptr_t)dp | (uintptr_t)dqp |
-                              (uintptr_t)dM) & 15) == 0);
         if ((T & 3) == 0 && al16)     // four steps per thread, 128-bit accesses
-          loss_seed_rows4_kernel<<<gr, 8 * K, 0, st>>>(xc, p, q, lq, M, log_pi, Lc, norms, betaf, C, K, (int)T, partial, dp, dqp, dM);
+          loss_seed_rows4_kernel<<<gr, 8 * K, 0, st>>>(xc, p, q, lq, fused_prior ? nullptr : M, log_pi, Lc, norms, betaf, C, K, (int)T,
+                                                       partial, dp, dqp, fused_prior ? nullptr : dM);
         else
           loss_seed_rows_kernel<<<gr, 32 * K, 0, st>>>(xc, p, q, lq, M, log_pi, Lc, norms, betaf, C, K, (int)T, partial, dp, dqp, dM);
       }
@@ -436,7 +460,8 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
     }
     {
       dim3 g((unsigned)cdiv(T, 256), (unsigned)nb);
-      dlogits_kernel<<<g, 256, 0, st>>>(q, lq, dqd, dqp, Lc, norms, betaf, K, (int)T, dl);
+      dlogits_kernel<<<g, 256, 0, st>>>(q, lq, dqd, dqp, Lc, norms, betaf, K, (int)T, dl, fused_prior ? dq_row : nullptr,
+                                        fused_prior ? dq_col : nullptr);
       VHMM_LAUNCH_CHECK();
     }
     // ---------------- backward: encoder ----------------

@@ -208,9 +208,10 @@ loss_seed_rows4_kernel(const float* __restrict__ x, const float* __restrict__ p,
         dqs[e] = (t0 + e == 0) ? log_pi[s] : 0.f;        // :123
       }
     }
+    // (logA == nullptr: the pair term and its gradients come from the fused prior kernel, prior_tc5.cuh)
     const float* rowp = logA + ((b * K + s) * K) * (int64_t)T + t0;     // logA[b, s, j, t0 + e] = rowp[j * T + e]
     float* dmp = dM ? dM + ((b * K + s) * K) * (int64_t)T + t0 : nullptr;
-    for (int j = 0; j < K; ++j) {
+    for (int j = 0; logA && j < K; ++j) {
       const float4 la4 = *reinterpret_cast<const float4*>(rowp + (int64_t)j * T);
       const float4 qc4 = *reinterpret_cast<const float4*>(qb + (int64_t)j * T);
       const float la5 = more ? rowp[(int64_t)j * T + 4] : 0.f, qc5 = more ? qb[(int64_t)j * T + 4] : 0.f;
@@ -227,7 +228,7 @@ loss_seed_rows4_kernel(const float* __restrict__ x, const float* __restrict__ p,
       }
       if (dmp) *reinterpret_cast<float4*>(dmp + (int64_t)j * T) = make_float4(dm[0], dm[1], dm[2], dm[3]);
     }
-    {   // column s of the transition into t: sum_i q[i, t-1] logA[i, s, t]
+    if (logA) {   // column s of the transition into t: sum_i q[i, t-1] logA[i, s, t]
       const float* colp = logA + ((b * K) * K + s) * (int64_t)T + t0;   // logA[b, i, s, t0 + e] = colp[i * K * T + e]
       for (int i = 0; i < K; ++i) {
         const float4 la4 = *reinterpret_cast<const float4*>(colp + (int64_t)i * K * T);
@@ -388,18 +389,21 @@ __global__ void __launch_bounds__(256)
 dlogits_kernel(const float* __restrict__ q, const float* __restrict__ logq,
                const float* __restrict__ dq_dec, const float* __restrict__ dq_prior,
                const int64_t* __restrict__ lengths, const double* __restrict__ norms, float beta,
-               int K, int T, float* __restrict__ dl) {
+               int K, int T, float* __restrict__ dl, const float* __restrict__ dq_row = nullptr,
+               const float* __restrict__ dq_col = nullptr) {
   const int t = blockIdx.x * 256 + threadIdx.x;
   if (t >= T) return;
   const int64_t b = blockIdx.y;
   const bool m = (int64_t)t < lengths[b];
   const float aE = (float)((double)beta / norms[1]);   // d(-beta*E/B)/dl = +(beta/B) q (logq + H)
+  const float aP = -aE;                                // scale of the un-scaled pair-term parts of the fused prior kernel
   float qv[KMAX], lq[KMAX], dq[KMAX];
   float s = 0.f, H = 0.f;
   for (int k = 0; k < K; ++k) {
     const int64_t o = (b * K + k) * (int64_t)T + t;
     qv[k] = q[o]; lq[k] = logq[o];
     dq[k] = dq_dec[o] + dq_prior[o];
+    if (dq_row) dq[k] += aP * (dq_row[o] + dq_col[o]);
     s += qv[k] * dq[k];
     H -= qv[k] * lq[k];
   }
