@@ -685,6 +685,9 @@ __device__ __forceinline__ void split8(const float* v, f2_t s2, uint4& h, uint4&
 struct WgradArgs {
   const float* dy;         // (B,Cout,T)
   const float* x;          // (B,Cin,T)
+  const uint8_t* dy_parts; // or (kw = 1, Cout = 1024): dy already as fp16 operand parts, prior_tc5.cuh layout -- one bulk copy per
+                           // item lands [chunk (4)][part][plane (2)][row][8] in the dy region: nothing to convert; TMEM lane l <->
+                           // channel 16 (l / 32) + l % 16, part (l / 16) % 2
   float* part;             // [nsplit][part_stride] partial weight gradients in the PARAMETER's layout
   int64_t part_stride;
   int64_t w_base, w_so, w_sc, w_st;
@@ -746,7 +749,8 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a, const __
     const int64_t b = item / a.ntt;
     const int t0 = (int)(item - b * a.ntt) * TM;
     ::vhmm::tma::expect_tx(&ld_bar[buf], (uint32_t)WBUF);
-    ::vhmm::tma::load_3d(sm + buf * WBUF, &tm_dy, t0, bo * WB, (int)b, &ld_bar[buf]);
+    if (a.dy_parts) bulk_g2s(sm + buf * WBUF, a.dy_parts + (item * 64 + bo * 4) * (int64_t)8192, (uint32_t)WDY_BYTES, &ld_bar[buf]);
+    else ::vhmm::tma::load_3d(sm + buf * WBUF, &tm_dy, t0, bo * WB, (int)b, &ld_bar[buf]);
     ::vhmm::tma::load_3d(sm + buf * WBUF + WDY_BYTES, &tm_x, t0 - 4, bc * WB, (int)b, &ld_bar[buf]);
   };
   auto drain = [&](int set) {
@@ -783,8 +787,10 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a, const __
       const float* ds = reinterpret_cast<const float*>(dyp);
       const float* xs = reinterpret_cast<const float*>(xp);
       uint4 dh[2], dm[2], xh[3], xm[3];
+      const bool cdy = (a.dy_parts == nullptr);      // dy still to be converted
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
+        if (!cdy) break;
         const int i = tid + q * WNT;
         const int pl = i / DY_ROWS, r = i - pl * DY_ROWS;
         float v[8];
@@ -806,6 +812,7 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a, const __
       __syncthreads();                  // every fp32 value of the buffer is in registers: overwrite it with the parts
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
+        if (!cdy) break;
         const int i = tid + q * WNT;
         const int pl = i / DY_ROWS, r = i - pl * DY_ROWS;
         uint8_t* p = dyp + pl * DY_PLANE + r * 16;
@@ -869,7 +876,8 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a, const __
   for (int i = tid; i < WB * WB * KW; i += WNT) {
     const int k = i % KW, c = (i / KW) % WB, o = i / (KW * WB);
     if (bo * WB + o >= a.Cout || bc * WB + c >= a.Cin) continue;     // padding channels of a skinny layer
-    const float v = (red[o * RP + k * 64 + c] + red[(o + 64) * RP + k * 64 + c]) * inv;
+    const int lh = a.dy_parts ? ((o >> 4) * 32 + (o & 15)) : o, lm = a.dy_parts ? lh + 16 : o + 64;
+    const float v = (red[lh * RP + k * 64 + c] + red[lm * RP + k * 64 + c]) * inv;
     dst[a.w_base + (int64_t)(bo * WB + o) * a.w_so + (int64_t)(bc * WB + c) * a.w_sc + (int64_t)k * a.w_st] = v;
   }
   tc5::fence_before_sync();
@@ -931,7 +939,8 @@ static inline int64_t wgrad_tc5_scratch_floats(int Cin, int Cout, int kw, int64_
 // gW (layer layout, +=), gB (+=, may be null)
 static inline int launch_wgrad_tc5(const float* dy, const float* x, float* gW, float* gB, WView layout, int64_t B, int Cin,
                                    int Cout, int64_t T, int kw, float* scratch, cudaStream_t st,
-                                   const uint32_t* amax_dy_known = nullptr, const uint32_t* amax_x_known = nullptr) {
+                                   const uint32_t* amax_dy_known = nullptr, const uint32_t* amax_x_known = nullptr,
+                                   const uint8_t* dy_parts = nullptr) {
   if (B <= 0 || T <= 0) return 0;
   const int ns = wgrad_tc5_nsplit(Cin, Cout, B, T);
   const int64_t nW = (int64_t)Cin * Cout * kw;
@@ -940,12 +949,13 @@ static inline int launch_wgrad_tc5(const float* dy, const float* x, float* gW, f
   if (!amax_dy_known) { int rc = launch_absmax(dy, B * (int64_t)Cout * T, words, st); if (rc) return rc; }
   if (!amax_x_known) { int rc = launch_absmax(x, B * (int64_t)Cin * T, words + 1, st); if (rc) return rc; }
   ct5::WgradArgs a{};
-  a.dy = dy; a.x = x; a.part = scratch; a.part_stride = nW;
+  a.dy = dy; a.dy_parts = dy_parts; a.x = x; a.part = scratch; a.part_stride = nW;
   a.w_base = layout.base; a.w_so = layout.so; a.w_sc = layout.sc; a.w_st = layout.st;
   a.amax_dy = amax_dy_known ? amax_dy_known : words; a.amax_x = amax_x_known ? amax_x_known : words + 1;
   a.B = B; a.Cin = Cin; a.Cout = Cout; a.T = (int)T; a.ntt = (int)cdiv(T, ct5::TM); a.nbc = (int)cdiv(Cin, ct5::WB); a.nsplit = ns;
   const unsigned grid = (unsigned)(cdiv(Cout, ct5::WB) * cdiv(Cin, ct5::WB) * ns);
   CUtensorMap tm_dy, tm_x;
+  if (dy_parts) dy = reinterpret_cast<const float*>(dy_parts);     // (the dy map is built but never used)
   if (!tma::make_map(&tm_dy, dy, B, Cout, T, ct5::DY_P, ct5::WB) || !tma::make_map(&tm_x, x, B, Cin, T, ct5::X_P, ct5::WB)) {
     set_error("wgrad_tc5: cuTensorMapEncodeTiled failed (B=%lld Cin=%d Cout=%d T=%lld)", (long long)B, Cin, Cout, (long long)T);
     return (int)cudaErrorInvalidValue;
@@ -968,7 +978,7 @@ static inline int launch_wgrad_tc5(const float* dy, const float* x, float* gW, f
   VHMM_LAUNCH_CHECK();
   reduce_partials_kernel<<<(unsigned)cdiv(nW, 256), 256, 0, st>>>(scratch, nW, ns, nW, gW);
   VHMM_LAUNCH_CHECK();
-  if (gB) {   // (T % 4 == 0 and 16-byte alignment were checked by wgrad_tc5_ok)
+  if (gB && !dy_parts) {   // (T % 4 == 0 and 16-byte alignment were checked by wgrad_tc5_ok; operand-form dy: the caller's kernel)
     float* bpart = scratch + (int64_t)ns * nW + 64;
     int nb = B < 32 ? (int)B : 32;
     ct5::bias_grad_kernel<<<dim3((unsigned)Cout, (unsigned)nb), 256, 0, st>>>(dy, B, Cout, (int)T, nb, bpart);

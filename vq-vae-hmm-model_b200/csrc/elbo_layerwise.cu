@@ -54,6 +54,11 @@ static bool prior_fused_enabled() {
   if (v < 0) { const char* e = getenv("VHMM_PRIOR_FUSED"); v = (e && e[0] == '0') ? 0 : 1; }
   return v == 1;
 }
+static bool prior_parts_enabled() {     // VHMM_PRIOR_PARTS=0: d loss / d logits as an fp32 tensor (the consumers convert it)
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("VHMM_PRIOR_PARTS"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v == 1;
+}
 struct Tc5Ctx {
   struct Entry { const float* w; int dgrad; Tc5Weights tw; };
   Entry e[16];
@@ -408,12 +413,16 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
                           (uintptr_t)dM) & 15) == 0);
     const bool fused_prior = twT2 && prior_fused_enabled() && al16 && prior_tc5_ok(K, TH, T, a, q, dM) &&
                              4 * prior_tc5_grid(nb, T) * sizeof(double) <= 64 * 1024;
+    // d loss / d logits in operand form (fp16 parts in the dM buffer): needs both consumers on the tensor core
+    const Tc5Weights* twT2d = (conv_impl_mode() != 1) ? ctx.find(P.p[P_T2W], 1) : nullptr;
+    const bool dM_parts = fused_prior && grads && twT2d && TH == ct5::TN && prior_parts_enabled() && wgrad_tc5_ok(TH, K2, T, 1, dM, a) &&
+                          (((uintptr_t)da) & 15) == 0;
     if (fused_prior) {
       int rcm = 0;
       const uint32_t* ax = ctx.measure(a, nb * (int64_t)TH * T, st, &rcm);
       RC(rcm);
       RC(launch_prior_tc5(a, *twT2, P.p[P_T2B], q, Lc, norms, betaf, nb, TH, T, grads ? dM : nullptr, dq_row, dq_col, prior_partial,
-                          grads ? ctx.fresh(dM) : nullptr, st, ax));
+                          grads ? ctx.fresh(dM) : nullptr, st, ax, dM_parts));
       sum_partials_kernel<<<1, 1024, 0, st>>>(prior_partial, prior_tc5_grid(nb, T), sums);
       VHMM_LAUNCH_CHECK();
     } else {
@@ -471,8 +480,20 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
     RC(cconv(&ctx, 1, dh2, wview_dgrad(P.p[P_E2W], H, 3), nullptr, h1, dh1, nb, H2, H, T, 3, EPI_MASK, st));
     RC(cwgrad(&ctx, dh1, xc, grads + off[P_E1W], grads + off[P_E1B], wview_fwd(nullptr, C, 3), nb, C, H, T, 3, scratch, st));
     // ---------------- backward: prior ----------------
-    RC(cwgrad(&ctx, dM, a, grads + off[P_T2W], grads + off[P_T2B], wview_fwd(nullptr, TH, 1), nb, TH, K2, T, 1, scratch, st));
-    RC(cconv(&ctx, 1, dM, wview_dgrad(P.p[P_T2W], TH, 1), nullptr, a, da, nb, K2, TH, T, 1, EPI_MASK, st));
+    if (dM_parts) {
+      int rcm = 0;
+      const uint32_t* adM = ctx.known(dM);
+      const uint32_t* aa = ctx.measure(a, nb * (int64_t)TH * T, st, &rcm);
+      RC(rcm);
+      VHMM_REQUIRE(adM && aa, VHMM_E_WORKSPACE, "elbo: abs-max word pool exhausted");
+      const uint8_t* dMp = reinterpret_cast<const uint8_t*>(dM);
+      RC(launch_wgrad_tc5(dM, a, grads + off[P_T2W], nullptr, wview_fwd(nullptr, TH, 1), nb, TH, K2, T, 1, scratch, st, adM, aa, dMp));
+      RC(launch_bias_parts(dMp, nb, T, adM, scratch, grads + off[P_T2B], st));     // (the wgrad partials in `scratch` are consumed)
+      RC(launch_dgrad_parts_tc5(dMp, *twT2d, a, da, nb, TH, T, adM, ctx.fresh(da), st));
+    } else {
+      RC(cwgrad(&ctx, dM, a, grads + off[P_T2W], grads + off[P_T2B], wview_fwd(nullptr, TH, 1), nb, TH, K2, T, 1, scratch, st));
+      RC(cconv(&ctx, 1, dM, wview_dgrad(P.p[P_T2W], TH, 1), nullptr, a, da, nb, K2, TH, T, 1, EPI_MASK, st));
+    }
     RC(cwgrad(&ctx, da, uc, grads + off[P_T0W], grads + off[P_T0B], wview_fwd(nullptr, U, 1), nb, U, TH, T, 1, scratch, st));
   }
 #undef RC

@@ -20,6 +20,13 @@ namespace vhmm {
 namespace ct5 {
 
 constexpr int PK = 32;                                   // K of the fused prior kernel
+// d loss / d logits in OPERAND form: the two consumers (input gradient and weight gradient of transition_net.2) are GEMMs over
+// fp16 (h, m) parts; written here once, in their shared-memory image, they are fetched with bulk copies and never converted
+// (the fp32 tensor cost both consumers a conversion pass over 10^9 elements per 1024 sequences).  |dM| <= |aP| is a static
+// bound, so the scale is known before the first element exists.
+//   parts[b][time tile][chunk of 16 channels (64)][part h/m][plane of 8 channels (2)][row = step in tile (128)][8] fp16
+constexpr int PP_CHUNK = 2 * 2 * TM * 16;                // 8 KB: one chunk = the A operand of one K step of the input gradient
+constexpr int PP_TILE = (PK * PK / KC) * PP_CHUNK;       // 512 KB per (sequence, time tile)
 constexpr int PQ_P = 132;                                // q window pitch: columns t0-4 .. t0+127
 constexpr int PCOL_P = 33;                               // column-sum tile pitch
 struct SmP {
@@ -40,6 +47,7 @@ struct PriorArgs {
   const double* norms;
   float beta;
   float* dM;               // (B,K*K,T) or null (forward only)
+  uint8_t* dM_parts;       // or: d loss / d logits as fp16 operand parts (layout below), scaled by pow2_scale(|aP|)
   float* dq_row;           // (B,K,T) or null: un-scaled (the consumer multiplies by aP)
   float* dq_col;           // (B,K,T) or null
   double* partial;         // [grid][4]: slot 1 receives the CTA's pair-term sum
@@ -75,6 +83,8 @@ __global__ void __launch_bounds__(NT, 1) prior_tc5_kernel(PriorArgs a) {
   const float inv = 1.f / (sx * sw);
   const f2_t sx2 = f2_pack(sx, sx);
   const float aP = (float)(-(double)a.beta / a.norms[1]);
+  const float sM = tc5::pow2_scale(fabsf(aP));
+  const f2_t sM2 = f2_pack(sM, sM);
   if (blockIdx.x == 0 && tid == 0 && a.bound_dM) *a.bound_dM = __float_as_uint(fabsf(aP));
   const int nkc = a.Cin / KC;
   const int ngr = (nkc + GK - 1) / GK;                   // weight groups per output tile
@@ -213,19 +223,43 @@ __global__ void __launch_bounds__(NT, 1) prior_tc5_kernel(PriorArgs a) {
         const float gq = aP * qprev;
         float R = 0.f;
         float* dMp = a.dM ? a.dM + ((b * PK + irow) * (int64_t)PK) * T + t : nullptr;
+        // chunk of this thread's first 16 logits: (ct * 128 + cq * 32) / 16
+        uint8_t* dPp = a.dM_parts ? a.dM_parts + (bt * (PK * PK / KC) + ct * 8 + cq * 2) * (int64_t)PP_CHUNK + tl * 16 : nullptr;
 #pragma unroll
-        for (int j = 0; j < PK; ++j) {
-          const float la = z[j] - lsum;
-          const float qc = qs[j * PQ_P + tl + 4];
-          R = fmaf(qc, la, R);
-          colacc[j] = fmaf(qprev, la, colacc[j]);
-          if (dMp) dMp[(int64_t)j * T] = gq * (qc - __expf(z[j]) * rs);
+        for (int j8 = 0; j8 < PK / 8; ++j8) {
+          float d8[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int j = j8 * 8 + e;
+            const float la = z[j] - lsum;
+            const float qc = qs[j * PQ_P + tl + 4];
+            R = fmaf(qc, la, R);
+            colacc[j] = fmaf(qprev, la, colacc[j]);
+            d8[e] = gq * (qc - __expf(z[j]) * rs);
+            if (dMp) dMp[(int64_t)j * T] = d8[e];
+          }
+          if (dPp) {
+            uint4 h, m;
+            split8(d8, sM2, h, m);
+            uint8_t* pp = dPp + (j8 >> 1) * PP_CHUNK + (j8 & 1) * (TM * 16);     // chunk, plane; the m part follows 2 planes on
+            *reinterpret_cast<uint4*>(pp) = h;
+            *reinterpret_cast<uint4*>(pp + 2 * TM * 16) = m;
+          }
         }
         if (tm) tr = fmaf(qprev, R, tr);
         if (a.dq_row) {
           float* dr = a.dq_row + (b * PK + irow) * (int64_t)T;
           if (t >= 1) dr[t - 1] = tm ? R : 0.f;
           if (t == T - 1) dr[t] = 0.f;
+        }
+      }
+      else if (a.dM_parts) {                             // rows of the tile beyond T: zeros (0 x anything stays 0 in the consumers)
+        uint8_t* dPp = a.dM_parts + (bt * (PK * PK / KC) + ct * 8 + cq * 2) * (int64_t)PP_CHUNK + tl * 16;
+#pragma unroll
+        for (int j8 = 0; j8 < PK / 8; ++j8) {
+          uint8_t* pp = dPp + (j8 >> 1) * PP_CHUNK + (j8 & 1) * (TM * 16);
+          *reinterpret_cast<uint4*>(pp) = make_uint4(0u, 0u, 0u, 0u);
+          *reinterpret_cast<uint4*>(pp + 2 * TM * 16) = make_uint4(0u, 0u, 0u, 0u);
         }
       }
       __syncthreads();                                   // TMEM buffer ct & 1 is free for tile ct + 2
@@ -262,6 +296,175 @@ __global__ void __launch_bounds__(NT, 1) prior_tc5_kernel(PriorArgs a) {
   if (w == 0) tc5::tmem_free512(tmem);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// Input gradient of transition_net.2 from the operand-form d loss / d logits:  da[t, c] = mask(a) * sum_o dM[t, o] W[o, c].
+// No conversion anywhere: warp 1 streams (8 KB of dM parts + the 8 KB weight chunk) per K step into a ring of stages with
+// one TMA bulk copy each, warp 0 issues the three MMAs of the step, all 16 warps run the epilogue.  HBM-bound by design
+// (the 4.3 GB of dM are read once at the tensor pipe's full appetite of 16 KB per 390 cycles).
+// ---------------------------------------------------------------------------------------------------------
+constexpr int DP_NST = 8;                                // stages of 16 KB
+constexpr int DP_STAGE = PP_CHUNK + 2 * WPLANE;          // dM parts chunk | weight chunk (kw = 1)
+constexpr int DP_SMEM = DP_NST * DP_STAGE;
+struct DgradPartsArgs {
+  const uint8_t* dM_parts;
+  const uint8_t* Wg;       // prepared input-gradient view of transition_net.2 (Cin = K*K, Cout = TH <= 128: one output tile)
+  const float* act;        // (B,Cout,T): ReLU mask source
+  float* y;                // (B,Cout,T)
+  const uint32_t* amax_x;  // the |aP| word
+  const uint32_t* amax_w;
+  uint32_t* amax_y;
+  int64_t B;
+  int Cout, T, ntt;
+};
+
+__global__ void __launch_bounds__(NT, 1) dgrad_parts_tc5_kernel(DgradPartsArgs a) {
+  constexpr int NKC = PK * PK / KC;                      // 64 K steps
+  extern __shared__ __align__(1024) uint8_t sm[];
+  __shared__ __align__(8) uint64_t landed[DP_NST], empty[DP_NST], done;
+  __shared__ uint32_t tmem_sh;
+  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    for (int i = 0; i < DP_NST; ++i) { tc5::mbar_init(&landed[i], 1); tc5::mbar_init(&empty[i], 1); }
+    tc5::mbar_init(&done, 1);
+    tc5::mbar_init_fence();
+  }
+  if (w == 0) tc5::tmem_alloc512(&tmem_sh);
+  tc5::fence_before_sync();
+  __syncthreads();
+  tc5::fence_after_sync();
+  const uint32_t tmem = tmem_sh;
+  const float sx = tc5::pow2_scale(__uint_as_float(*a.amax_x));
+  const float sw = tc5::pow2_scale(__uint_as_float(*a.amax_w));
+  const float inv = 1.f / (sx * sw);
+  const int T = a.T;
+  constexpr uint32_t IDESC = tc5::idesc_f16(TN, 0, 0);
+  const int64_t nbt = a.B * a.ntt;
+  uint32_t g = 0;                                        // K steps loaded (warp 1) / issued (warp 0) so far: same sequence in both
+  uint32_t ntile = 0;
+  int pre = 0;                                           // warp 1: K steps of the current tile already requested during the previous one
+
+  for (int64_t bt = blockIdx.x; bt < nbt; bt += gridDim.x) {
+    const int tt = (int)(bt % a.ntt);
+    const int64_t b = bt / a.ntt;
+    const int t0 = tt * TM;
+    if (w == 1) {
+      auto load_steps = [&](int64_t tile, int k0, int k1) {
+        const uint8_t* src = a.dM_parts + tile * (int64_t)PP_TILE;
+        for (int kc = k0; kc < k1; ++kc, ++g) {
+          if (g >= (uint32_t)DP_NST) tc5::mbar_wait(&empty[g % DP_NST], ((g / DP_NST) - 1u) & 1u);
+          if (lane == 0) {
+            uint8_t* st = sm + (g % DP_NST) * DP_STAGE;
+            mbar_expect_tx(&landed[g % DP_NST], (uint32_t)DP_STAGE);
+            bulk_g2s(st, src + (int64_t)kc * PP_CHUNK, (uint32_t)PP_CHUNK, &landed[g % DP_NST]);
+            bulk_g2s(st + PP_CHUNK, a.Wg + (int64_t)kc * (2 * WPLANE), (uint32_t)(2 * WPLANE), &landed[g % DP_NST]);
+          }
+          __syncwarp();
+        }
+      };
+      load_steps(bt, pre, NKC);
+      // the first steps of the NEXT tile go out before this warp joins the epilogue (their stages free up as the last MMAs
+      // of this tile complete): the ring stays full across the tile boundary
+      pre = 0;
+      if (bt + gridDim.x < nbt) { load_steps(bt + gridDim.x, 0, DP_NST); pre = DP_NST; }
+    } else if (w == 0) {
+      for (int kc = 0; kc < NKC; ++kc, ++g) {
+        tc5::mbar_wait(&landed[g % DP_NST], (g / DP_NST) & 1u);
+        tc5::fence_after_sync();
+        const bool lead = tc5::elect_one();
+        const uint32_t sA = tc5::smem_u32(sm + (g % DP_NST) * DP_STAGE);
+        const uint32_t sW = sA + PP_CHUNK;
+        const uint64_t ah = tc5::make_desc(sA, TM * 16, 128);
+        const uint64_t am = tc5::make_desc(sA + 2 * TM * 16, TM * 16, 128);
+        const uint64_t bh = tc5::make_desc(sW, WPLANE, 128);
+        const uint64_t bm = tc5::make_desc(sW + TN * 16, WPLANE, 128);
+        if (lead) {
+          tc5::mma_f16(tmem + HH0 + 128u * (uint32_t)(kc % 3), ah, bh, IDESC, kc >= 3 ? 1u : 0u);
+          tc5::mma_f16(tmem + SMALL, ah, bm, IDESC, kc >= 1 ? 1u : 0u);
+          tc5::mma_f16(tmem + SMALL, am, bh, IDESC, 1u);
+          tc5::commit(&empty[g % DP_NST]);
+          if (kc == NKC - 1) tc5::commit(&done);
+        }
+        __syncwarp();
+      }
+    } else {
+      g += (uint32_t)NKC;
+    }
+    tc5::mbar_wait(&done, ntile & 1u);
+    ++ntile;
+    tc5::fence_after_sync();
+    {   // epilogue: TMEM lane = time row; warp w reads lane quadrant w & 3, columns [32 (w >> 2), +32)
+      const uint32_t lane_base = (uint32_t)(32 * (w & 3)) << 16;
+      const int t = t0 + 32 * (w & 3) + lane;
+      float ymax = 0.f;
+#pragma unroll 1
+      for (int cgp = 0; cgp < 2; ++cgp) {
+        const int col = 32 * (w >> 2) + 16 * cgp;
+        float v[16], s[16], v1[16], v2[16];
+        tc5::tmem_ld16(tmem + lane_base + SMALL + col, s);
+        tc5::tmem_ld16(tmem + lane_base + HH0 + col, v);
+        tc5::tmem_ld16(tmem + lane_base + HH0 + 128 + col, v1);
+        tc5::tmem_ld16(tmem + lane_base + HH0 + 256 + col, v2);
+#pragma unroll
+        for (int e = 0; e < 16; ++e) v[e] += v1[e] + v2[e];
+        if (t < T && col < a.Cout) {
+          const int64_t off0 = (b * a.Cout + col) * (int64_t)T + t;
+          float mk[16];
+#pragma unroll
+          for (int e = 0; e < 16; ++e) mk[e] = a.act ? __ldg(a.act + off0 + (int64_t)e * T) : 1.f;
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            const float r = mk[e] > 0.f ? (v[e] + s[e]) * inv : 0.f;
+            a.y[off0 + (int64_t)e * T] = r;
+            ymax = fmaxf(ymax, fabsf(r));
+          }
+        }
+      }
+      if (a.amax_y) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, o));
+        if (lane == 0 && ymax > 0.f) atomicMax(a.amax_y, __float_as_uint(ymax));
+      }
+    }
+    tc5::fence_before_sync();
+    __syncthreads();                                     // the accumulators are free for the next tile
+    tc5::fence_after_sync();
+  }
+  tc5::fence_before_sync();
+  __syncthreads();
+  if (w == 0) tc5::tmem_free512(tmem);
+}
+
+// bias gradient of transition_net.2 from the operand-form tensor: partial[s][o] = sum over the tiles of split s and the
+// rows of (h + m) / scale.  grid (64 chunks, nsplit), 256 threads: thread = (plane, row); 8 channels each.
+__global__ void __launch_bounds__(256) bias_parts_kernel(const uint8_t* __restrict__ parts, int64_t ntiles, int nsplit,
+                                                         const uint32_t* __restrict__ amax, float* __restrict__ partial) {
+  __shared__ float red[256 * 8];
+  const int kc = blockIdx.x, s = blockIdx.y, tid = threadIdx.x;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int64_t it = s; it < ntiles; it += nsplit) {
+    const uint4* src = reinterpret_cast<const uint4*>(parts + (it * (PK * PK / KC) + kc) * (int64_t)PP_CHUNK);
+    const uint4 h = src[tid], m = src[256 + tid];        // [part][plane][row]: tid = plane * 128 + row
+    const __half2* hh = reinterpret_cast<const __half2*>(&h);
+    const __half2* mm = reinterpret_cast<const __half2*>(&m);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 a2 = __half22float2(hh[e]), b2 = __half22float2(mm[e]);
+      acc[2 * e] += a2.x + b2.x; acc[2 * e + 1] += a2.y + b2.y;
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) red[e * 256 + tid] = acc[e];
+  __syncthreads();
+  if (tid < 16) {                                        // channel tid of the chunk: plane tid / 8, element tid % 8
+    const float* r = red + (tid & 7) * 256 + (tid >> 3) * 128;
+    float sum = 0.f;
+    for (int i = 0; i < 128; ++i) sum += r[i];
+    const float inv = 1.f / tc5::pow2_scale(__uint_as_float(*amax));
+    partial[(int64_t)s * (PK * PK) + kc * KC + tid] = sum * inv;
+  }
+}
+
 }  // namespace ct5
 
 // fused prior: usable when K == 32, the transition hidden width is a multiple of 16 up to 128, T % 4 == 0, 16-byte aligned tensors
@@ -278,7 +481,7 @@ static inline int64_t prior_tc5_grid(int64_t B, int64_t T) {
 static inline int launch_prior_tc5(const float* a, const Tc5Weights& W, const float* bias, const float* q, const int64_t* lengths,
                                    const double* norms, float beta, int64_t B, int TH, int64_t T, float* dM, float* dq_row,
                                    float* dq_col, double* partial, uint32_t* bound_dM, cudaStream_t st,
-                                   const uint32_t* amax_x_known = nullptr) {
+                                   const uint32_t* amax_x_known = nullptr, bool dM_as_parts = false) {
   if (B <= 0 || T <= 0) return 0;
   const uint32_t* ax = amax_x_known;
   if (!ax) {
@@ -289,7 +492,7 @@ static inline int launch_prior_tc5(const float* a, const Tc5Weights& W, const fl
   }
   ct5::PriorArgs p{};
   p.a = a; p.Wg = W.Wg; p.bias = bias; p.amax_x = ax; p.amax_w = W.amax_w; p.q = q; p.lengths = lengths; p.norms = norms;
-  p.beta = beta; p.dM = dM; p.dq_row = dq_row; p.dq_col = dq_col; p.partial = partial; p.bound_dM = bound_dM;
+  p.beta = beta; p.dM = dM_as_parts ? nullptr : dM; p.dM_parts = dM_as_parts ? reinterpret_cast<uint8_t*>(dM) : nullptr; p.dq_row = dq_row; p.dq_col = dq_col; p.partial = partial; p.bound_dM = bound_dM;
   p.B = B; p.Cin = TH; p.T = (int)T; p.ntt = (int)cdiv(T, ct5::TM);
   static PerDeviceOnce once;
   if (once.pending()) {
@@ -297,6 +500,35 @@ static inline int launch_prior_tc5(const float* a, const Tc5Weights& W, const fl
     once.mark();
   }
   ct5::prior_tc5_kernel<<<(unsigned)prior_tc5_grid(B, T), ct5::NT, ct5::SmP::TOTAL, st>>>(p);
+  VHMM_LAUNCH_CHECK();
+  return 0;
+}
+
+// da = mask(act) * (dM W) from the operand-form dM (TH == 128: one output tile); amax_dM: the |aP| word
+static inline int launch_dgrad_parts_tc5(const uint8_t* dM_parts, const Tc5Weights& Wd, const float* act, float* y, int64_t B, int TH,
+                                         int64_t T, const uint32_t* amax_dM, uint32_t* amax_y, cudaStream_t st) {
+  if (B <= 0 || T <= 0) return 0;
+  ct5::DgradPartsArgs a{};
+  a.dM_parts = dM_parts; a.Wg = Wd.Wg; a.act = act; a.y = y; a.amax_x = amax_dM; a.amax_w = Wd.amax_w; a.amax_y = amax_y;
+  a.B = B; a.Cout = TH; a.T = (int)T; a.ntt = (int)cdiv(T, ct5::TM);
+  static PerDeviceOnce once;
+  if (once.pending()) {
+    VHMM_CUDA_CHECK(cudaFuncSetAttribute(ct5::dgrad_parts_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ct5::DP_SMEM));
+    once.mark();
+  }
+  ct5::dgrad_parts_tc5_kernel<<<(unsigned)prior_tc5_grid(B, T), ct5::NT, ct5::DP_SMEM, st>>>(a);
+  VHMM_LAUNCH_CHECK();
+  return 0;
+}
+// gB[o] += sum_{b,t} dM[b,o,t] from the operand-form dM; bpart: 32 * K*K floats
+static inline int launch_bias_parts(const uint8_t* dM_parts, int64_t B, int64_t T, const uint32_t* amax_dM, float* bpart, float* gB,
+                                    cudaStream_t st) {
+  const int64_t ntiles = B * cdiv(T, ct5::TM);
+  const int ns = ntiles < 32 ? (int)ntiles : 32;
+  constexpr int K2 = ct5::PK * ct5::PK;
+  ct5::bias_parts_kernel<<<dim3(K2 / ct5::KC, (unsigned)ns), 256, 0, st>>>(dM_parts, ntiles, ns, amax_dM, bpart);
+  VHMM_LAUNCH_CHECK();
+  reduce_partials_kernel<<<(unsigned)cdiv(K2, 256), 256, 0, st>>>(bpart, K2, ns, K2, gB);
   VHMM_LAUNCH_CHECK();
   return 0;
 }
