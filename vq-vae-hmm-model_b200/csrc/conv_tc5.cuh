@@ -89,6 +89,33 @@ __device__ __forceinline__ void cp16(void* smem, const void* g, int bytes) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(d), "l"(g), "r"(bytes) : "memory");
 }
 
+// packed fp32 pairs (Blackwell add / mul .f32x2): one issue slot for two lanes of work -- the kernel below is issue-bound
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t f2_pack(float a, float b) { f2_t r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void f2_unpack(f2_t v, float& a, float& b) { asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ f2_t f2_add(f2_t a, f2_t b) { f2_t r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2_sub(f2_t a, f2_t b) { f2_t r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2_mul(f2_t a, f2_t b) { f2_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+// eight fp32 values (scaled by s2 = {s, s}) -> their fp16 h and m parts as two 16-byte rows (same split as tc5::split_f16)
+__device__ __forceinline__ void split8(const float* v, f2_t s2, uint4& h, uint4& m) {
+  uint32_t hh[4], mm[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const f2_t xs = f2_mul(f2_pack(v[2 * e], v[2 * e + 1]), s2);
+    float x0, x1;
+    f2_unpack(xs, x0, x1);
+    const __half2 h2 = __floats2half2_rn(x0, x1);
+    const float2 hf = __half22float2(h2);
+    float r0, r1;
+    f2_unpack(f2_sub(xs, f2_pack(hf.x, hf.y)), r0, r1);
+    const __half2 m2 = __floats2half2_rn(r0, r1);
+    hh[e] = *reinterpret_cast<const uint32_t*>(&h2);
+    mm[e] = *reinterpret_cast<const uint32_t*>(&m2);
+  }
+  h = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+  m = make_uint4(mm[0], mm[1], mm[2], mm[3]);
+}
+
 struct ConvArgs {
   const float* x;          // (B,Cin,T)
   const uint8_t* Wg;       // prepared weights
@@ -102,6 +129,7 @@ struct ConvArgs {
   int Cin, Cout, T, epi;
   int ntt, nct;            // time tiles per sequence, out-channel tiles
   int64_t nitems;
+  int use_tma;             // streaming kernel: the input chunk arrives as ONE TMA box (pitch XW) instead of 16-byte cp.async
 };
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
@@ -130,8 +158,10 @@ __device__ __forceinline__ void bulk_g2s(void* smem, const void* g, uint32_t byt
 //   warp 0       waits for full[g & 1], issues the 3 KW MMAs of chunk g, commits them to empty[g & 1]
 // A parts buffer / stage is rewritten only after empty[] of the chunk that last read it; no CTA-wide barrier inside the
 // loop (the first build had two per chunk: tensor pipe 23 % active, 0.4 eligible warps per cycle).
+// (First build: every loader thread arrived on landed[] (cp.async) and on full[] -- ~1000 mbarrier arrivals per chunk, and
+// 2.0 k cycles per chunk against 1.17 k of MMA time.  Now one TMA box per chunk and one arrival per warp.)
 template <int KW>
-__global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
+__global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a, const __grid_constant__ CUtensorMap tm_x) {
   constexpr int PAD = KW / 2;
   constexpr int NLD = NT - 32;                       // loader / converter threads
   using S = Sm<KW>;
@@ -142,8 +172,9 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   for (int i = tid; i < 2 * ABYTES / 4; i += NT) reinterpret_cast<uint32_t*>(parts)[i] = 0u;
   if (tid == 0) {
-    for (int i = 0; i < STAGES; ++i) tc5::mbar_init(&landed[i], NLD + 1);   // NLD cp.async arrivals (x) + the weight block's expect_tx
-    for (int i = 0; i < 2; ++i) { tc5::mbar_init(&full[i], NLD); tc5::mbar_init(&empty[i], 1); }
+    // cp.async build: NLD cp.async arrivals (x) + the weight block's expect_tx; TMA build: the one expect_tx
+    for (int i = 0; i < STAGES; ++i) tc5::mbar_init(&landed[i], a.use_tma ? 1 : NLD + 1);
+    for (int i = 0; i < 2; ++i) { tc5::mbar_init(&full[i], NLD / 32); tc5::mbar_init(&empty[i], 1); }
     tc5::mbar_init_fence();
   }
   if (w == 0) tc5::tmem_alloc512(&tmem_sh);
@@ -154,6 +185,7 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
   const float sx = tc5::pow2_scale(__uint_as_float(*a.amax_x));
   const float sw = tc5::pow2_scale(__uint_as_float(*a.amax_w));
   const float inv = 1.f / (sx * sw);
+  const f2_t sx2 = f2_pack(sx, sx);
   const int nkc = a.Cin / KC;
   const int T = a.T;
   constexpr uint32_t IDESC = tc5::idesc_f16(TN, 0, 0);
@@ -199,6 +231,14 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
         const uint32_t g = g0 + (uint32_t)kc;
         uint8_t* st = sm + (g % STAGES) * S::STAGE;
         const uint8_t* wsrc = wct + (int64_t)kc * S::WBYTES;
+        if (a.use_tma) {                                 // weight chunk (bulk copy) + input chunk (tensor box, zero fill outside [0,T))
+          if (lt == 0) {
+            mbar_expect_tx(&landed[g % STAGES], (uint32_t)(S::WBYTES + KC * XW * 4));
+            bulk_g2s(st, wsrc, (uint32_t)S::WBYTES, &landed[g % STAGES]);
+            ::vhmm::tma::load_3d(st + S::WBYTES, &tm_x, t0 - 4, kc * KC, (int)b, &landed[g % STAGES]);
+          }
+          return;
+        }
         if (lt == 0) {                                   // the weight chunk: one TMA bulk copy
           mbar_expect_tx(&landed[g % STAGES], (uint32_t)S::WBYTES);
           bulk_g2s(st, wsrc, (uint32_t)S::WBYTES, &landed[g % STAGES]);
@@ -224,17 +264,21 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a) {
         tc5::mbar_wait(&landed[g % STAGES], (g / STAGES) & 1u);
         const float* xs = reinterpret_cast<const float*>(sm + (g % STAGES) * S::STAGE + S::WBYTES);
         uint8_t* pb = parts + (g & 1) * ABYTES;
+        const int xp = a.use_tma ? XW : XP;
         for (int i = lt; i < 2 * ROWS; i += NLD) {
           const int pl = i / ROWS, r = i - pl * ROWS;
-          __align__(16) __half hh[8], mm[8];
+          float v[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) tc5::split_f16(xs[(pl * 8 + e) * XP + r + 3] * sx, hh[e], mm[e]);
+          for (int e = 0; e < 8; ++e) v[e] = xs[(pl * 8 + e) * xp + r + 3];
+          uint4 h, m;
+          split8(v, sx2, h, m);
           uint8_t* p = pb + pl * PLANE + r * 16;
-          *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(hh);
-          *reinterpret_cast<uint4*>(p + APART) = *reinterpret_cast<const uint4*>(mm);
+          *reinterpret_cast<uint4*>(p) = h;
+          *reinterpret_cast<uint4*>(p + APART) = m;
         }
-        tc5::fence_async_smem();          // this thread's generic-proxy writes (parts; its cp.async of W) -> async proxy
-        mbar_arrive(&full[g & 1]);
+        tc5::fence_async_smem();          // this thread's generic-proxy writes (parts) -> async proxy
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full[g & 1]);      // one arrival per loader warp
       }
       // drain: the last two chunks' MMAs (idempotent waits: a completed phase answers at once)
       for (int kc = (nkc >= 2 ? nkc - 2 : 0); kc < nkc; ++kc) {
@@ -610,20 +654,23 @@ static inline int launch_conv_tc5(const float* x, const Tc5Weights& W, const flo
     return 0;
   }
   if (grid > a.nitems) grid = a.nitems;
+  CUtensorMap tm_x;
+  a.use_tma = tma::make_map(&tm_x, x, B, Cin, T, ct5::XW, ct5::KC) ? 1 : 0;
+  if (!a.use_tma) memset(&tm_x, 0, sizeof(tm_x));
   if (kw == 3) {
     static PerDeviceOnce once;
     if (once.pending()) {
       VHMM_CUDA_CHECK(cudaFuncSetAttribute(ct5::conv_tc5_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ct5::Sm<3>::TOTAL));
       once.mark();
     }
-    ct5::conv_tc5_kernel<3><<<(unsigned)grid, ct5::NT, ct5::Sm<3>::TOTAL, st>>>(a);
+    ct5::conv_tc5_kernel<3><<<(unsigned)grid, ct5::NT, ct5::Sm<3>::TOTAL, st>>>(a, tm_x);
   } else {
     static PerDeviceOnce once;
     if (once.pending()) {
       VHMM_CUDA_CHECK(cudaFuncSetAttribute(ct5::conv_tc5_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ct5::Sm<1>::TOTAL));
       once.mark();
     }
-    ct5::conv_tc5_kernel<1><<<(unsigned)grid, ct5::NT, ct5::Sm<1>::TOTAL, st>>>(a);
+    ct5::conv_tc5_kernel<1><<<(unsigned)grid, ct5::NT, ct5::Sm<1>::TOTAL, st>>>(a, tm_x);
   }
   VHMM_LAUNCH_CHECK();
   return 0;
@@ -654,33 +701,6 @@ constexpr int WBUF = WDY_BYTES + WX_BYTES;
 constexpr int WNBUF = 3;
 constexpr int WSM_TOTAL = WNBUF * WBUF;
 static_assert(WSM_TOTAL >= 128 * (3 * 64 + 1) * 4, "final reduction tile fits");
-
-// packed fp32 pairs (Blackwell add / mul .f32x2): one issue slot for two lanes of work -- the kernel below is issue-bound
-typedef unsigned long long f2_t;
-__device__ __forceinline__ f2_t f2_pack(float a, float b) { f2_t r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
-__device__ __forceinline__ void f2_unpack(f2_t v, float& a, float& b) { asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
-__device__ __forceinline__ f2_t f2_add(f2_t a, f2_t b) { f2_t r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
-__device__ __forceinline__ f2_t f2_sub(f2_t a, f2_t b) { f2_t r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
-__device__ __forceinline__ f2_t f2_mul(f2_t a, f2_t b) { f2_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
-// eight fp32 values (scaled by s2 = {s, s}) -> their fp16 h and m parts as two 16-byte rows (same split as tc5::split_f16)
-__device__ __forceinline__ void split8(const float* v, f2_t s2, uint4& h, uint4& m) {
-  uint32_t hh[4], mm[4];
-#pragma unroll
-  for (int e = 0; e < 4; ++e) {
-    const f2_t xs = f2_mul(f2_pack(v[2 * e], v[2 * e + 1]), s2);
-    float x0, x1;
-    f2_unpack(xs, x0, x1);
-    const __half2 h2 = __floats2half2_rn(x0, x1);
-    const float2 hf = __half22float2(h2);
-    float r0, r1;
-    f2_unpack(f2_sub(xs, f2_pack(hf.x, hf.y)), r0, r1);
-    const __half2 m2 = __floats2half2_rn(r0, r1);
-    hh[e] = *reinterpret_cast<const uint32_t*>(&h2);
-    mm[e] = *reinterpret_cast<const uint32_t*>(&m2);
-  }
-  h = make_uint4(hh[0], hh[1], hh[2], hh[3]);
-  m = make_uint4(mm[0], mm[1], mm[2], mm[3]);
-}
 
 struct WgradArgs {
   const float* dy;         // (B,Cout,T)
