@@ -41,14 +41,15 @@ constexpr int WPLANE = 2 * TN * 16;     // rows = part*128 + o
 constexpr int XW = 136;                 // staged fp32 columns: t0-4 .. t0+131 (16-byte aligned start)
 constexpr int XP = 140;                 // pitch (floats)
 constexpr int XBYTES = KC * XP * 4;
-constexpr int STAGES = 5;                // cp.async stages of the streaming kernel: chunks g+1 .. g+3 in flight
+constexpr int STAGES = 6;                // load stages of the streaming kernel: chunks g+1 .. g+3 in flight
+constexpr int NPB = 3;                   // operand-parts buffers: chunk g+2 is converted while chunks g and g+1 feed the MMAs
 constexpr uint32_t HH0 = 0, SMALL = 384;   // TMEM columns: three h*h sets at 0 / 128 / 256, the small terms at 384
 
 template <int KW>
 struct Sm {
   static constexpr int WBYTES = KW * 2 * WPLANE;          // weights of one chunk: [tau][plane][256 rows][16 B]
   static constexpr int STAGE = WBYTES + XBYTES;
-  static constexpr int TOTAL = STAGES * STAGE + 2 * ABYTES;
+  static constexpr int TOTAL = STAGES * STAGE + NPB * ABYTES;
 };
 
 // |x| max of a tensor -> *out (float bits; non-negative floats order like unsigned integers).  *out zeroed by the host.
@@ -154,10 +155,13 @@ __device__ __forceinline__ void bulk_g2s(void* smem, const void* g, uint32_t byt
 // y = epi(bias + conv_KW(x, W)); requires Cin % 16 == 0, Cout % 128 == 0, T % 4 == 0, x 16-byte aligned.
 // Warp-specialised main loop over the K chunks (global chunk counter g, continuing across the CTA's work items):
 //   warps 1..15  load chunk g+2 (cp.async into stage (g+2) % 4, completion -> landed[stage]) and convert chunk g from its
-//                fp32 staging to the fp16 parts buffer g & 1, then arrive on full[g & 1]
-//   warp 0       waits for full[g & 1], issues the 3 KW MMAs of chunk g, commits them to empty[g & 1]
+//                fp32 staging to the fp16 parts buffer g % 3, then arrive on full[g % 3]
+//   warp 0       waits for full[g % 3], issues the 3 KW MMAs of chunk g, commits them to empty[g % 3]
+// (Two parts buffers left the issuer waiting ~600 cycles per chunk: from "MMAs of chunk g done" to "chunk g+2 converted"
+//  takes ~2 k cycles, more than the 1.2-1.4 k of MMA time of chunk g+1.  With three, the conversion has two chunk times.)
 // A parts buffer / stage is rewritten only after empty[] of the chunk that last read it; no CTA-wide barrier inside the
 // loop (the first build had two per chunk: tensor pipe 23 % active, 0.4 eligible warps per cycle).
+// (Measured and dropped, twice: A_h x [W_h | W_m] as one N = 256 MMA -- same kernel time as the three N = 128 MMAs.)
 // (First build: every loader thread arrived on landed[] (cp.async) and on full[] -- ~1000 mbarrier arrivals per chunk, and
 // 2.0 k cycles per chunk against 1.17 k of MMA time.  Now one TMA box per chunk and one arrival per warp.)
 template <int KW>
@@ -166,15 +170,15 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a, const __gri
   constexpr int NLD = NT - 32;                       // loader / converter threads
   using S = Sm<KW>;
   extern __shared__ __align__(1024) uint8_t sm[];
-  __shared__ __align__(8) uint64_t landed[STAGES], full[2], empty[2];
+  __shared__ __align__(8) uint64_t landed[STAGES], full[NPB], empty[NPB];
   __shared__ uint32_t tmem_sh;
   uint8_t* parts = sm + STAGES * S::STAGE;
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
-  for (int i = tid; i < 2 * ABYTES / 4; i += NT) reinterpret_cast<uint32_t*>(parts)[i] = 0u;
+  for (int i = tid; i < NPB * ABYTES / 4; i += NT) reinterpret_cast<uint32_t*>(parts)[i] = 0u;
   if (tid == 0) {
     // cp.async build: NLD cp.async arrivals (x) + the weight block's expect_tx; TMA build: the one expect_tx
     for (int i = 0; i < STAGES; ++i) tc5::mbar_init(&landed[i], a.use_tma ? 1 : NLD + 1);
-    for (int i = 0; i < 2; ++i) { tc5::mbar_init(&full[i], NLD / 32); tc5::mbar_init(&empty[i], 1); }
+    for (int i = 0; i < NPB; ++i) { tc5::mbar_init(&full[i], NLD / 32); tc5::mbar_init(&empty[i], 1); }
     tc5::mbar_init_fence();
   }
   if (w == 0) tc5::tmem_alloc512(&tmem_sh);
@@ -190,6 +194,12 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a, const __gri
   const int T = a.T;
   constexpr uint32_t IDESC = tc5::idesc_f16(TN, 0, 0);
   uint32_t g0 = 0;                                   // global index of this item's chunk 0
+#ifdef CT5_PROF
+  long long pq[4] = {0, 0, 0, 0}, pql = clock64();
+#define CT5Q(i) do { if (tid == 0) { long long n_ = clock64(); pq[i] += n_ - pql; pql = n_; } } while (0)
+#else
+#define CT5Q(i)
+#endif
 
   for (int64_t item = blockIdx.x; item < a.nitems; item += gridDim.x, g0 += (uint32_t)nkc) {
     const int ct = (int)(item % a.nct);
@@ -201,10 +211,12 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a, const __gri
       // ---- MMA issuer -------------------------------------------------------------------------------------
       for (int kc = 0; kc < nkc; ++kc) {
         const uint32_t g = g0 + (uint32_t)kc;
-        tc5::mbar_wait(&full[g & 1], (g >> 1) & 1u);
+        CT5Q(3);
+        tc5::mbar_wait(&full[g % NPB], (g / NPB) & 1u);
+        CT5Q(kc == 0 ? 0 : 1);
         tc5::fence_after_sync();
         const bool lead = tc5::elect_one();
-        const uint32_t sA = tc5::smem_u32(parts + (g & 1) * ABYTES);
+        const uint32_t sA = tc5::smem_u32(parts + (g % NPB) * ABYTES);
         const uint32_t sW = tc5::smem_u32(sm + (g % STAGES) * S::STAGE);
 #pragma unroll
         for (int tau = 0; tau < KW; ++tau) {
@@ -219,16 +231,16 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a, const __gri
             tc5::mma_f16(tmem + SMALL, am, bh, IDESC, 1u);
           }
         }
-        if (lead) tc5::commit(&empty[g & 1]);
+        if (lead) tc5::commit(&empty[g % NPB]);
         __syncwarp();
+        CT5Q(2);
       }
     } else {
       // ---- loaders / converters ---------------------------------------------------------------------------
       const int lt = tid - 32;
       const float* xb = a.x + b * (int64_t)a.Cin * T;
       const uint8_t* wct = a.Wg + (int64_t)ct * nkc * S::WBYTES;
-      auto issue_loads = [&](int kc) {
-        const uint32_t g = g0 + (uint32_t)kc;
+      auto issue_loads_at = [&](const float* xb, const uint8_t* wct, int64_t b, int t0, uint32_t g, int kc) {
         uint8_t* st = sm + (g % STAGES) * S::STAGE;
         const uint8_t* wsrc = wct + (int64_t)kc * S::WBYTES;
         if (a.use_tma) {                                 // weight chunk (bulk copy) + input chunk (tensor box, zero fill outside [0,T))
@@ -251,19 +263,22 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a, const __gri
         }
         cp_async_arrive(&landed[g % STAGES]);
       };
-      // stages of chunks 0..2 were last read by chunks of the previous item: drained at its end
-      issue_loads(0);
-      if (nkc > 1) issue_loads(1);
-      if (nkc > 2) issue_loads(2);
+      auto issue_loads = [&](int kc) { issue_loads_at(xb, wct, b, t0, g0 + (uint32_t)kc, kc); };
+      // the first three chunks of every item but the CTA's first were requested at the end of the previous item
+      if (item == (int64_t)blockIdx.x) {
+        issue_loads(0);
+        if (nkc > 1) issue_loads(1);
+        if (nkc > 2) issue_loads(2);
+      }
       for (int kc = 0; kc < nkc; ++kc) {
         const uint32_t g = g0 + (uint32_t)kc;
-        // parts buffer g & 1 and stage (g + 3) % 5 were last read by the MMAs of chunk g - 2: ~70 KB must be in flight to
+        // parts buffer g % 3 and stage (g + 3) % 6 were last read by the MMAs of chunk g - 3: ~70 KB must be in flight to
         // cover the L2 latency at the tensor pipe's appetite of 24 KB per ~1000 cycles
-        if (g >= 2) tc5::mbar_wait(&empty[g & 1], ((g - 2) >> 1) & 1u);
+        if (g >= (uint32_t)NPB) tc5::mbar_wait(&empty[g % NPB], ((g - NPB) / NPB) & 1u);
         if (kc + 3 < nkc) issue_loads(kc + 3);
         tc5::mbar_wait(&landed[g % STAGES], (g / STAGES) & 1u);
         const float* xs = reinterpret_cast<const float*>(sm + (g % STAGES) * S::STAGE + S::WBYTES);
-        uint8_t* pb = parts + (g & 1) * ABYTES;
+        uint8_t* pb = parts + (g % NPB) * ABYTES;
         const int xp = a.use_tma ? XW : XP;
         for (int i = lt; i < 2 * ROWS; i += NLD) {
           const int pl = i / ROWS, r = i - pl * ROWS;
@@ -278,12 +293,23 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a, const __gri
         }
         tc5::fence_async_smem();          // this thread's generic-proxy writes (parts) -> async proxy
         __syncwarp();
-        if (lane == 0) mbar_arrive(&full[g & 1]);      // one arrival per loader warp
+        if (lane == 0) mbar_arrive(&full[g % NPB]);    // one arrival per loader warp
       }
       // drain: the last two chunks' MMAs (idempotent waits: a completed phase answers at once)
-      for (int kc = (nkc >= 2 ? nkc - 2 : 0); kc < nkc; ++kc) {
+      for (int kc = (nkc >= NPB ? nkc - NPB : 0); kc < nkc; ++kc) {
         const uint32_t g = g0 + (uint32_t)kc;
-        tc5::mbar_wait(&empty[g & 1], (g >> 1) & 1u);
+        tc5::mbar_wait(&empty[g % NPB], (g / NPB) & 1u);
+      }
+      // every stage is free: request the next item's first chunks now, so that they land under the epilogue
+      const int64_t nitem = item + gridDim.x;
+      if (nitem < a.nitems) {
+        const int nct = (int)(nitem % a.nct);
+        const int64_t nbt = nitem / a.nct;
+        const int64_t nb = nbt / a.ntt;
+        const int nt0 = (int)(nbt % a.ntt) * TM;
+        const float* nxb = a.x + nb * (int64_t)a.Cin * T;
+        const uint8_t* nwct = a.Wg + (int64_t)nct * nkc * S::WBYTES;
+        for (int kc = 0; kc < 3 && kc < nkc; ++kc) issue_loads_at(nxb, nwct, nb, nt0, g0 + (uint32_t)(nkc + kc), kc);
       }
     }
     __syncthreads();                       // every MMA of the item has completed (the converters saw its commits)
@@ -343,6 +369,11 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a, const __gri
     __syncthreads();
     tc5::fence_after_sync();
   }
+#ifdef CT5_PROF
+  if (tid == 0 && blockIdx.x == 0)
+    printf("conv_tc5<%d> Cin=%d Cout=%d epi=%d cycles: wait first full %lld, wait full (steady) %lld, issue %lld, epilogue+sync %lld\n", KW,
+           a.Cin, a.Cout, a.epi, pq[0], pq[1], pq[2], pq[3]);
+#endif
   tc5::fence_before_sync();
   __syncthreads();
   if (w == 0) tc5::tmem_free512(tmem);
@@ -931,6 +962,7 @@ __global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict_
 static inline bool wgrad_tc5_ok(int Cin, int Cout, int64_t T, int kw, const void* dy, const void* x) {
   // channel counts are padded up to the 64-channel block (zero-filled): skinny layers (the embedding 256 x 32, to_logits
   // 32 x 128, to_params 10 x 256, transition_net.0 128 x 16) still beat their FFMA build by ~3x; below 8 channels FFMA stays
+  // (measured: encoder.conv1's 256 x 5 gradient gains nothing over its FFMA kernel)
   return (kw == 1 || kw == 3) && Cin >= 8 && Cout >= 8 && (Cin >= 64 || Cout >= 64) && (T & 3) == 0 && T >= 4 &&
          (((uintptr_t)dy | (uintptr_t)x) & 15) == 0 && tma::encode_fn() != nullptr;
 }
