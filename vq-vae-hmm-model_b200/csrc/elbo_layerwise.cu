@@ -233,7 +233,7 @@ static size_t fixed_bytes(const vhmm_dims& d, int64_t T) {
 
 size_t layerwise_workspace_bytes(int op, const vhmm_dims& d, int64_t B, int64_t T) {
   LayerwiseSizes s = layerwise_sizes(d);
-  const int64_t Bc = B < 1024 ? B : 1024;
+  const int64_t Bc = B < 2048 ? B : 2048;   // sequences per chunk of the layer-wise passes (cfg 5: ~40 GB)
   const size_t slack = 64 * 256;
   switch (op) {
     case VHMM_OP_ENCODER_FWD:
