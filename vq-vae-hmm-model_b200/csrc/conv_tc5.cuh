@@ -715,7 +715,8 @@ static inline int launch_conv_tc5(const float* x, const Tc5Weights& W, const flo
 namespace vhmm {
 namespace ct5 {
 
-constexpr int WNT = 512;                     // threads per CTA (16 warps: 4 TMEM lane quadrants x 4 column quarters)
+constexpr int WNW = 16;                      // worker warps: 4 TMEM lane quadrants x 4 column quarters
+constexpr int WNT = 32 + WNW * 32;           // threads per CTA: the issuer warp + the workers
 constexpr int WB = 64;                       // channels per weight block side (x 2 parts = MMA M / N of 128)
 constexpr int DY_ROWS = 128, X_ROWS = 130;   // dy row r <-> t0 + r; x row r <-> t0 - 1 + r
 constexpr int DY_PLANE = DY_ROWS * 16, X_PLANE = X_ROWS * 16;
@@ -753,24 +754,34 @@ struct WgradArgs {
 // Per item: [dy_h; dy_m] (M = 128) x [x_h; x_m] (N = 128) over K = 128 time steps per tap into TMEM (all four part
 // products at once, the m*m quadrant is ignored), then drained into per-thread fp32 registers (RN adds): the TMEM
 // accumulation chains stay 8 MMAs long, whatever the batch size.
-// Pipeline (per item i): one thread issues the two TMA boxes of item i+1, all 16 warps convert item i in place while the
-// MMAs of item i-1 run, then -- KW = 3, one TMEM accumulator set: the MMAs of i-1 are drained and those of i issued;
-// KW = 1, two sets: the MMAs of i are issued first and i-1 is drained under them.  (The first build of this kernel loaded
-// with 16-byte cp.async: 825 instructions per thread and item, half of them address arithmetic, issue-bound at IPC 2.)
+// Warp-specialised: 16 worker warps + 1 issuer warp (544 threads).  tcgen05.mma issue BLOCKS while the tensor pipe's queue is
+// full, so a warp that issues an item's 24 MMAs is gone for ~3.5 k cycles; as long as that warp also took part in the
+// conversion (with its CTA-wide barriers) nothing overlapped: 5.2 k cycles per item for 3.6 k of MMA time.
+//   workers, item i: thread 0 requests the two TMA boxes of item i+1; all convert item i IN PLACE (named barrier between the
+//                    reads and the writes), arrive on ready[buf]; then drain item i-1 slot by slot (mma_done[slot] ->
+//                    tcgen05.ld -> RN adds into registers -> tfree[slot])
+//   issuer, item i:  waits ready[buf], then per slot: waits tfree[slot] (the previous tenant has been read), issues the 8 MMAs,
+//                    commits to mma_done[slot]
+// A slot is one 128-column accumulator: the three taps of an item (KW = 3) or the two alternating sets (KW = 1).  With one
+// slot per tap the taps of item i+1 start as soon as the same tap of item i is drained -- the tensor pipe never waits for a
+// whole-item drain.  (The first build of this kernel loaded with 16-byte cp.async: 825 instructions per thread and item, half
+// of them address arithmetic, issue-bound at IPC 2.)
+// (17 warps: registers are granted per warp in units that leave 96 per thread -- 112 and 120 fail to launch)
 template <int KW>
 __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a, const __grid_constant__ CUtensorMap tm_dy,
                                                           const __grid_constant__ CUtensorMap tm_x) {
   constexpr int PAD = KW / 2;
-  constexpr int NSET = (KW == 1) ? 2 : 1;
+  constexpr int NSLOT = (KW == 1) ? 2 : KW;
   extern __shared__ __align__(1024) uint8_t sm[];
-  __shared__ __align__(8) uint64_t bar[2];
-  __shared__ __align__(8) uint64_t ld_bar[WNBUF];
+  __shared__ __align__(8) uint64_t mma_done[NSLOT], tfree[NSLOT];
+  __shared__ __align__(8) uint64_t ld_bar[WNBUF], ready[WNBUF];
   __shared__ uint32_t tmem_sh;
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   if (tid == 0) {
-    tc5::mbar_init(&bar[0], 1); tc5::mbar_init(&bar[1], 1);
 #pragma unroll
-    for (int i = 0; i < WNBUF; ++i) tc5::mbar_init(&ld_bar[i], 1);
+    for (int i = 0; i < NSLOT; ++i) { tc5::mbar_init(&mma_done[i], 1); tc5::mbar_init(&tfree[i], WNW); }
+#pragma unroll
+    for (int i = 0; i < WNBUF; ++i) { tc5::mbar_init(&ld_bar[i], 1); tc5::mbar_init(&ready[i], WNW); }
     tc5::mbar_init_fence();
   }
   if (w == 0) tc5::tmem_alloc512(&tmem_sh);
@@ -784,133 +795,151 @@ __global__ void __launch_bounds__(WNT, 1) wgrad_tc5_kernel(WgradArgs a, const __
   const int blk = blockIdx.x / a.nsplit;
   const int bc = blk % a.nbc, bo = blk / a.nbc;
   const int64_t nitems = a.B * a.ntt;
-  uint32_t par = 0;                     // bit `set`: phase parity of bar[set]
-  uint32_t ldpar = 0;                   // bit `buf`: phase parity of ld_bar[buf]
   constexpr uint32_t IDESC = tc5::idesc_f16(128, 1, 1);
+  const int wt = tid - 32, ww = wt >> 5;                   // worker thread / warp index (issuer warp: negative)
   f2_t acc[KW][8];
 #pragma unroll
   for (int k = 0; k < KW; ++k)
 #pragma unroll
     for (int e = 0; e < 8; ++e) acc[k][e] = 0ull;          // {0.f, 0.f}
-  const uint32_t lane_base = (uint32_t)(32 * (w & 3)) << 16;
-  const int cq = w >> 2;
-  const f2_t sdy2 = f2_pack(sdy, sdy), sx2 = f2_pack(sx, sx);
 
-  auto issue_loads = [&](int64_t item, int buf) {          // thread 0 only
-    const int64_t b = item / a.ntt;
-    const int t0 = (int)(item - b * a.ntt) * TM;
-    ::vhmm::tma::expect_tx(&ld_bar[buf], (uint32_t)WBUF);
-    if (a.dy_parts) bulk_g2s(sm + buf * WBUF, a.dy_parts + (item * 64 + bo * 4) * (int64_t)8192, (uint32_t)WDY_BYTES, &ld_bar[buf]);
-    else ::vhmm::tma::load_3d(sm + buf * WBUF, &tm_dy, t0, bo * WB, (int)b, &ld_bar[buf]);
-    ::vhmm::tma::load_3d(sm + buf * WBUF + WDY_BYTES, &tm_x, t0 - 4, bc * WB, (int)b, &ld_bar[buf]);
-  };
-  auto drain = [&](int set) {
-    tc5::mbar_wait(&bar[set], (par >> set) & 1u); par ^= 1u << set;
-    tc5::fence_after_sync();
-#pragma unroll
-    for (int k = 0; k < KW; ++k) {
-      float v0[16], v1[16];
-      tc5::tmem_ld16(tmem + lane_base + (uint32_t)(set * 128 * KW) + 128u * k + 16 * cq, v0);
-      tc5::tmem_ld16(tmem + lane_base + (uint32_t)(set * 128 * KW) + 128u * k + 64 + 16 * cq, v1);
-#pragma unroll
-      for (int e = 0; e < 8; ++e)
-        acc[k][e] = f2_add(f2_add(acc[k][e], f2_pack(v0[2 * e], v0[2 * e + 1])), f2_pack(v1[2 * e], v1[2 * e + 1]));
-    }
-    tc5::fence_before_sync();
-  };
-  // x rows needed by the MMAs: KW = 3 all 130, KW = 1 rows 1..128 only
-  constexpr int XR0 = (KW == 1) ? 1 : 0, XNR = (KW == 1) ? 128 : X_ROWS;
-
-  int64_t item = s;
-  if (tid == 0 && item < nitems) issue_loads(item, 0);
-  int buf = 0;
-  int64_t n = 0;                        // items done by this CTA
-  for (; item < nitems; item += a.nsplit, ++n) {
-    const int64_t nxt = item + a.nsplit;
-    const int nbuf = (buf == WNBUF - 1) ? 0 : buf + 1;
-    // that buffer's last reader (the MMAs of item n-2) was drained by this thread in the previous iteration, and its
-    // generic-proxy accesses (conversion of item n-2) lie before several CTA barriers
-    if (tid == 0 && nxt < nitems) issue_loads(nxt, nbuf);
-    tc5::mbar_wait(&ld_bar[buf], (ldpar >> buf) & 1u); ldpar ^= 1u << buf;
-    uint8_t* dyp = sm + buf * WBUF;
-    uint8_t* xp = dyp + WDY_BYTES;
-    {
-      const float* ds = reinterpret_cast<const float*>(dyp);
-      const float* xs = reinterpret_cast<const float*>(xp);
-      uint4 dh[2], dm[2], xh[3], xm[3];
-      const bool cdy = (a.dy_parts == nullptr);      // dy still to be converted
-#pragma unroll
-      for (int q = 0; q < 2; ++q) {
-        if (!cdy) break;
-        const int i = tid + q * WNT;
-        const int pl = i / DY_ROWS, r = i - pl * DY_ROWS;
-        float v[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) v[e] = ds[(pl * 8 + e) * DY_P + r];
-        split8(v, sdy2, dh[q], dm[q]);
-      }
-#pragma unroll
-      for (int q = 0; q < 3; ++q) {
-        const int i = tid + q * WNT;
-        if (i < 8 * XNR) {
-          const int pl = i / XNR, r = XR0 + i - pl * XNR;
-          float v[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) v[e] = xs[(pl * 8 + e) * X_P + r + 3];
-          split8(v, sx2, xh[q], xm[q]);
-        }
-      }
-      __syncthreads();                  // every fp32 value of the buffer is in registers: overwrite it with the parts
-#pragma unroll
-      for (int q = 0; q < 2; ++q) {
-        if (!cdy) break;
-        const int i = tid + q * WNT;
-        const int pl = i / DY_ROWS, r = i - pl * DY_ROWS;
-        uint8_t* p = dyp + pl * DY_PLANE + r * 16;
-        *reinterpret_cast<uint4*>(p) = dh[q];
-        *reinterpret_cast<uint4*>(p + 8 * DY_PLANE) = dm[q];
-      }
-#pragma unroll
-      for (int q = 0; q < 3; ++q) {
-        const int i = tid + q * WNT;
-        if (i < 8 * XNR) {
-          const int pl = i / XNR, r = XR0 + i - pl * XNR;
-          uint8_t* p = xp + pl * X_PLANE + r * 16;
-          *reinterpret_cast<uint4*>(p) = xh[q];
-          *reinterpret_cast<uint4*>(p + 8 * X_PLANE) = xm[q];
-        }
-      }
-    }
-    tc5::fence_async_smem();
-    const int set = (NSET == 2) ? (int)(n & 1) : 0;
-    if (NSET == 1 && n > 0) drain(0);             // one accumulator set: it must be read before the next item overwrites it
-    tc5::fence_before_sync();
-    __syncthreads();
-    if (w == 0) {
+  if (w == 0) {
+    // ---- issuer -------------------------------------------------------------------------------------------------------
+    int buf = 0;
+    uint32_t n = 0;
+    for (int64_t item = s; item < nitems; item += a.nsplit, ++n) {
+      tc5::mbar_wait(&ready[buf], (n / WNBUF) & 1u);
       tc5::fence_after_sync();
       const bool lead = tc5::elect_one();
-      const uint32_t sD = tc5::smem_u32(dyp), sX = tc5::smem_u32(xp);
+      const uint32_t sD = tc5::smem_u32(sm + buf * WBUF), sX = sD + WDY_BYTES;
 #pragma unroll
-      for (int k = 0; k < KW; ++k)
+      for (int k = 0; k < KW; ++k) {
+        const int slot = (KW == 1) ? (int)(n & 1u) : k;
+        const uint32_t use = (KW == 1) ? (n >> 1) : n;     // how often this slot has been filled before
+        if (use >= 1) { tc5::mbar_wait(&tfree[slot], (use - 1u) & 1u); tc5::fence_after_sync(); }
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const uint64_t da = tc5::make_desc(sD + (16 * i) * 16, 128, DY_PLANE);
           const uint64_t db = tc5::make_desc(sX + (16 * i + k - PAD + 1) * 16, 128, X_PLANE);
-          if (lead) tc5::mma_f16(tmem + (uint32_t)(set * 128 * KW) + 128u * k, da, db, IDESC, i ? 1u : 0u);
+          if (lead) tc5::mma_f16(tmem + 128u * (uint32_t)slot, da, db, IDESC, i ? 1u : 0u);
         }
-      if (lead) tc5::commit(&bar[set]);
-      __syncwarp();
+        if (lead) tc5::commit(&mma_done[slot]);
+        __syncwarp();
+      }
+      buf = (buf == WNBUF - 1) ? 0 : buf + 1;
     }
-    if (NSET == 2 && n > 0) drain(set ^ 1);       // the previous item, under the MMAs just issued
-    buf = nbuf;
+  } else {
+    // ---- workers ------------------------------------------------------------------------------------------------------
+    // a warp reaches the TMEM lanes 32 (w % 4) .. of its HARDWARE warp index w = ww + 1: quadrants 1,2,3,0 per column quarter
+    const uint32_t lane_base = (uint32_t)(32 * (w & 3)) << 16;
+    const int cq = ww >> 2;
+    const f2_t sdy2 = f2_pack(sdy, sdy), sx2 = f2_pack(sx, sx);
+    // x rows needed by the MMAs: KW = 3 all 130, KW = 1 rows 1..128 only
+    constexpr int XR0 = (KW == 1) ? 1 : 0, XNR = (KW == 1) ? 128 : X_ROWS;
+    constexpr int NWT = WNW * 32;
+    auto issue_loads = [&](int64_t item, int buf, uint32_t n) {          // worker thread 0 only
+      const int64_t b = item / a.ntt;
+      const int t0 = (int)(item - b * a.ntt) * TM;
+      ::vhmm::tma::expect_tx(&ld_bar[buf], (uint32_t)WBUF);
+      if (a.dy_parts) bulk_g2s(sm + buf * WBUF, a.dy_parts + (item * 64 + bo * 4) * (int64_t)8192, (uint32_t)WDY_BYTES, &ld_bar[buf]);
+      else ::vhmm::tma::load_3d(sm + buf * WBUF, &tm_dy, t0, bo * WB, (int)b, &ld_bar[buf]);
+      ::vhmm::tma::load_3d(sm + buf * WBUF + WDY_BYTES, &tm_x, t0 - 4, bc * WB, (int)b, &ld_bar[buf]);
+    };
+    auto drain_item = [&](uint32_t m) {
+#pragma unroll
+      for (int k = 0; k < KW; ++k) {
+        const int slot = (KW == 1) ? (int)(m & 1u) : k;
+        const uint32_t use = (KW == 1) ? (m >> 1) : m;
+        tc5::mbar_wait(&mma_done[slot], use & 1u);
+        tc5::fence_after_sync();
+        float v0[16], v1[16];
+        tc5::tmem_ld16(tmem + lane_base + 128u * (uint32_t)slot + 16 * cq, v0);
+        tc5::tmem_ld16(tmem + lane_base + 128u * (uint32_t)slot + 64 + 16 * cq, v1);
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          acc[k][e] = f2_add(f2_add(acc[k][e], f2_pack(v0[2 * e], v0[2 * e + 1])), f2_pack(v1[2 * e], v1[2 * e + 1]));
+        tc5::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tfree[slot]);           // one arrival per worker warp
+      }
+    };
+
+    if (wt == 0 && s < nitems) issue_loads(s, 0, 0);
+    int buf = 0;
+    uint32_t n = 0;                      // items done by this CTA
+    for (int64_t item = s; item < nitems; item += a.nsplit, ++n) {
+      const int64_t nxt = item + a.nsplit;
+      const int nbuf = (buf == WNBUF - 1) ? 0 : buf + 1;
+      // that buffer's last reader (the MMAs of item n-2) was drained by this thread in the previous iteration
+      if (wt == 0 && nxt < nitems) issue_loads(nxt, nbuf, n + 1);
+      tc5::mbar_wait(&ld_bar[buf], (n / WNBUF) & 1u);
+      uint8_t* dyp = sm + buf * WBUF;
+      uint8_t* xp = dyp + WDY_BYTES;
+      {
+        const float* ds = reinterpret_cast<const float*>(dyp);
+        const float* xs = reinterpret_cast<const float*>(xp);
+        // the dy region and the x region are converted in place one after the other (fewer live registers: 17 warps leave
+        // 96 per thread): read -> named barrier -> write, twice
+        const bool cdy = (a.dy_parts == nullptr);      // dy still to be converted
+        if (cdy) {
+          uint4 dh[2], dm[2];
+#pragma unroll
+          for (int q = 0; q < 2; ++q) {
+            const int i = wt + q * NWT;
+            const int pl = i / DY_ROWS, r = i - pl * DY_ROWS;
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = ds[(pl * 8 + e) * DY_P + r];
+            split8(v, sdy2, dh[q], dm[q]);
+          }
+          asm volatile("bar.sync 1, %0;" :: "n"(NWT) : "memory");
+#pragma unroll
+          for (int q = 0; q < 2; ++q) {
+            const int i = wt + q * NWT;
+            const int pl = i / DY_ROWS, r = i - pl * DY_ROWS;
+            uint8_t* p = dyp + pl * DY_PLANE + r * 16;
+            *reinterpret_cast<uint4*>(p) = dh[q];
+            *reinterpret_cast<uint4*>(p + 8 * DY_PLANE) = dm[q];
+          }
+        }
+        uint4 xh[3], xm[3];
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+          const int i = wt + q * NWT;
+          if (i < 8 * XNR) {
+            const int pl = i / XNR, r = XR0 + i - pl * XNR;
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = xs[(pl * 8 + e) * X_P + r + 3];
+            split8(v, sx2, xh[q], xm[q]);
+          }
+        }
+        asm volatile("bar.sync 1, %0;" :: "n"(NWT) : "memory");
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+          const int i = wt + q * NWT;
+          if (i < 8 * XNR) {
+            const int pl = i / XNR, r = XR0 + i - pl * XNR;
+            uint8_t* p = xp + pl * X_PLANE + r * 16;
+            *reinterpret_cast<uint4*>(p) = xh[q];
+            *reinterpret_cast<uint4*>(p + 8 * X_PLANE) = xm[q];
+          }
+        }
+      }
+      tc5::fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ready[buf]);
+      if (n > 0) drain_item(n - 1);        // under the MMAs of item n
+      buf = nbuf;
+    }
+    if (n > 0) drain_item(n - 1);
   }
-  if (n > 0) drain((NSET == 2) ? (int)((n - 1) & 1) : 0);
   __syncthreads();
   // lanes l and l + 64 hold the h / m rows of dy for out channel l: combine through shared memory, undo the scales
   float* red = reinterpret_cast<float*>(sm);               // [128 rows][KW * 64 + 1]
   constexpr int RP = KW * 64 + 1;
-  {
-    const int row = 32 * (w & 3) + lane;
+  if (w > 0) {
+    const int row = 32 * (w & 3) + lane, cq = ww >> 2;
 #pragma unroll
     for (int k = 0; k < KW; ++k)
 #pragma unroll
