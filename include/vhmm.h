@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define VHMM_VERSION 109 /* major*100 + minor */
+#define VHMM_VERSION 110 /* major*100 + minor */
 #define VHMM_NUM_PARAMS 18
 #define VHMM_PAD_STATE 255 /* Viterbi path value for t >= lengths[b] */
 
@@ -191,6 +191,17 @@ int vhmm_conv_select(int impl);
 size_t vhmm_conv1d_workspace_bytes(int64_t Cin, int64_t Cout, int64_t kw);
 int vhmm_conv1d_fwd(const float* x, const float* weight, const float* bias, int64_t B, int64_t Cin, int64_t Cout,
                     int64_t T, int64_t kw, int relu, float* y, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Transition prior of the LAYER-WISE path at K = 32 with a 128-wide transition_net (BASELINE.json configs[4]):
+ *   VHMM_PRIOR_FUSED   (AUTO) one kernel forms the K*K transition logits (tcgen05 GEMM), their row log-softmax, the pair term
+ *                      sum_t sum_ij q_{t-1}(i) q_t(j) log A_t(i,j) and its gradients (VQ_VAE_HMM_fixed.py:53-57, :125-131);
+ *                      d loss / d logits is written once as fp16 operand parts for the two backward GEMMs of transition_net.2
+ *   VHMM_PRIOR_FUSED_F32  the same kernel, d loss / d logits as an fp32 tensor (the backward GEMMs convert it)
+ *   VHMM_PRIOR_LAYERS  layer -> row log-softmax -> loss kernel, each a pass over the (B,K*K,T) tensor
+ * All three meet the 1e-5 parity bar (tests run each); other shapes always take LAYERS.  Environment VHMM_PRIOR_FUSED=0 /
+ * VHMM_PRIOR_PARTS=0 seed the choice. */
+enum { VHMM_PRIOR_AUTO = 0, VHMM_PRIOR_FUSED_F32 = 1, VHMM_PRIOR_LAYERS = 2 };
+int vhmm_prior_select(int mode);
 
 /* argmax regime decoding (backtesting.py:155, src/backtesting.py:107): q or logits (B,K,T) ->
  * regimes int64 (B,T), lowest index on ties. */

@@ -48,17 +48,22 @@ int conv1d_fwd(const float* x, const float* w, const float* bias, int64_t B, int
 // ---- tensor-core layer kernels inside the layer-wise path (conv_tc5.cuh) -------------------------------------
 // The weights of the layers whose shape the tcgen05 kernels take are prepared once per call (fp16 parts in the
 // kernel's chunk image): forward view and, where the input gradient is needed, the transposed tap-flipped view.
-// VHMM_PRIOR_FUSED=0 keeps the transition prior of the wide model on the layer-by-layer kernels (A/B timing, tests)
-static bool prior_fused_enabled() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("VHMM_PRIOR_FUSED"); v = (e && e[0] == '0') ? 0 : 1; }
-  return v == 1;
+// transition prior of the wide model: 0 fused kernel + operand-form gradient, 1 fused kernel + fp32 gradient, 2 layer by layer
+// (include/vhmm.h: vhmm_prior_select; environment VHMM_PRIOR_FUSED=0 / VHMM_PRIOR_PARTS=0 seed it)
+static std::atomic<int> g_prior_mode{-1};
+static int prior_mode() {
+  int m = g_prior_mode.load();
+  if (m < 0) {
+    const char* f = getenv("VHMM_PRIOR_FUSED");
+    const char* p = getenv("VHMM_PRIOR_PARTS");
+    m = (f && f[0] == '0') ? 2 : ((p && p[0] == '0') ? 1 : 0);
+    g_prior_mode = m;
+  }
+  return m;
 }
-static bool prior_parts_enabled() {     // VHMM_PRIOR_PARTS=0: d loss / d logits as an fp32 tensor (the consumers convert it)
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("VHMM_PRIOR_PARTS"); v = (e && e[0] == '0') ? 0 : 1; }
-  return v == 1;
-}
+int prior_impl_select(int mode) { g_prior_mode = mode; return 0; }
+static bool prior_fused_enabled() { return prior_mode() != 2; }
+static bool prior_parts_enabled() { return prior_mode() == 0; }
 struct Tc5Ctx {
   struct Entry { const float* w; int dgrad; Tc5Weights tw; };
   Entry e[16];

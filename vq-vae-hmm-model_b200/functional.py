@@ -300,6 +300,12 @@ def elbo_decoder_select(variant: str = "auto"):
     check(_lib.lib().vhmm_elbo_decoder_select(code), "vhmm_elbo_decoder_select")
 
 
+def prior_select(mode: str = "auto"):
+    """Transition prior of the layer-wise path at K = 32: "auto" (fused kernel, operand-form gradient) | "fused_f32" |
+    "layers" (include/vhmm.h: vhmm_prior_select)."""
+    check(_lib.lib().vhmm_prior_select({"auto": 0, "fused_f32": 1, "layers": 2}[mode]), "vhmm_prior_select")
+
+
 def tma_select(on: bool):
     """Input windows of the tile kernels by tensor-map TMA (True) or cp.async (False, default).  include/vhmm.h."""
     check(_lib.lib().vhmm_tma_select(1 if on else 0), "vhmm_tma_select")
