@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define VHMM_VERSION 110 /* major*100 + minor */
+#define VHMM_VERSION 111 /* major*100 + minor */
 #define VHMM_NUM_PARAMS 18
 #define VHMM_PAD_STATE 255 /* Viterbi path value for t >= lengths[b] */
 
@@ -202,6 +202,13 @@ int vhmm_conv1d_fwd(const float* x, const float* weight, const float* bias, int6
  * VHMM_PRIOR_PARTS=0 seed the choice. */
 enum { VHMM_PRIOR_AUTO = 0, VHMM_PRIOR_FUSED_F32 = 1, VHMM_PRIOR_LAYERS = 2 };
 int vhmm_prior_select(int mode);
+
+/* ELBO of the LAYER-WISE path with tensor-core layer kernels (K % 16 == 0, hidden_dim % 16 == 0): decoder.embeddings folded into
+ * decoder.conv1 -- e = E^T q (VQ_VAE_HMM_fixed.py:83) is linear, so conv1(e) is a K -> hidden_dim convolution of q with
+ * W'[o,k,tau] = sum_d W1[o,d,tau] E[k,d]; forward, input gradient (d loss / dq directly) and weight gradient run on the
+ * folded layer, the gradients of W1 and E follow by the chain rule.  1 (default) = on, 0 = the embedding stays a layer of its
+ * own.  Same results up to fp32 re-association; environment VHMM_EMB_FOLD=0 seeds the choice. */
+int vhmm_emb_fold_select(int on);
 
 /* argmax regime decoding (backtesting.py:155, src/backtesting.py:107): q or logits (B,K,T) ->
  * regimes int64 (B,T), lowest index on ties. */

@@ -301,8 +301,9 @@ def test_host_resident_batch_is_streamed(elbo_impl):
         assert rel_err(v.grad, g0[k]) <= 2e-6, k
 
 
-@pytest.mark.parametrize("conv,prior", [("tc5", "auto"), ("tc5", "fused_f32"), ("tc5", "layers"), ("ffma", "auto")])
-def test_scaled_config_cfg5_dims_vs_float64_oracle(conv, prior):
+@pytest.mark.parametrize("conv,prior,fold", [("tc5", "auto", True), ("tc5", "fused_f32", True), ("tc5", "layers", False),
+                                             ("tc5", "auto", False), ("ffma", "auto", True)])
+def test_scaled_config_cfg5_dims_vs_float64_oracle(conv, prior, fold):
     """BASELINE.json configs[4] dims (hidden_dim 256, hidden_dim2 128, K 32, u_dim 16) at T = 1024 on the layer-wise path with
     the tcgen05 layer kernels (conv_tc5.cuh: forward, input gradient and weight gradient of encoder.conv2, decoder.conv1/2,
     transition_net.0/2) and with the FFMA ones: loss and all 18 gradient tensors against the float64 oracle, ragged lengths.
@@ -321,6 +322,7 @@ def test_scaled_config_cfg5_dims_vs_float64_oracle(conv, prior):
     ref, _, g64 = O.loss_and_grads(p64, x.double(), u.double(), L, U, 0.7)
     Fn.conv_select(conv)
     Fn.prior_select(prior)
+    Fn.emb_fold_select(fold)        # decoder.embeddings folded into decoder.conv1 (tensor-core build only)
     try:
         loss = m.compute_loss(x.cuda(), u.cuda(), L, 0.7)
         loss.backward()
@@ -329,6 +331,7 @@ def test_scaled_config_cfg5_dims_vs_float64_oracle(conv, prior):
     finally:
         Fn.conv_select("auto")
         Fn.prior_select("auto")
+        Fn.emb_fold_select(True)
     assert abs(float(loss) - float(ref)) <= TOL * abs(float(ref)), (float(loss), float(ref))
     sd = dict(m.named_parameters())
     for k in O.PARAM_ORDER:

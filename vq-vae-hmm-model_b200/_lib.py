@@ -107,6 +107,7 @@ PROTOTYPES = {
     "vhmm_elbo_timing_read": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int)]),
     "vhmm_conv_select": (ctypes.c_int, [ctypes.c_int]),
     "vhmm_prior_select": (ctypes.c_int, [ctypes.c_int]),
+    "vhmm_emb_fold_select": (ctypes.c_int, [ctypes.c_int]),
     "vhmm_conv1d_workspace_bytes": (_SZ, [_I64, _I64, _I64]),
     "vhmm_conv1d_fwd": (ctypes.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _I64, ctypes.c_int, _P, _P, _SZ, _P]),
     "vhmm_argmax_regimes": (ctypes.c_int, [_P, _I64, _I64, _I64, _P, _P]),

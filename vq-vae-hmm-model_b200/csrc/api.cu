@@ -49,6 +49,7 @@ int layerwise_emission_table(const vhmm_dims&, const vhmm_params&, int64_t, floa
 int launch_argmax(const float* q, int64_t B, int64_t K, int64_t T, int64_t* out, cudaStream_t st);
 int conv_impl_select(int mode);
 int prior_impl_select(int mode);
+int emb_fold_select(int on);
 size_t conv1d_workspace_bytes(int Cin, int Cout, int kw);
 int conv1d_fwd(const float*, const float*, const float*, int64_t, int, int, int64_t, int, int, float*, void*, size_t, cudaStream_t);
 // elbo_fused.cu
@@ -268,6 +269,7 @@ int vhmm_prior_select(int mode) {
   ARG(mode == VHMM_PRIOR_AUTO || mode == VHMM_PRIOR_FUSED_F32 || mode == VHMM_PRIOR_LAYERS, "mode");
   return prior_impl_select(mode);
 }
+int vhmm_emb_fold_select(int on) { return emb_fold_select(on); }
 int vhmm_elbo_decoder_active(void) { return fused_decoder_active(); }
 int vhmm_tma_select(int on) { return fused_tma_select(on); }
 

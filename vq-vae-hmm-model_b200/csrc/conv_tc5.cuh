@@ -337,7 +337,7 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5_kernel(ConvArgs a, const __gri
 #pragma unroll
           for (int e = 0; e < 16; ++e) v[e] += v2[e];
         }
-        if (t < T) {
+        if (t < T && ct * TN + col < a.Cout) {      // (columns beyond Cout: zero padding rows of the weights)
           // every load (bias, ReLU mask) is issued BEFORE the first store: y, act and bias are plain pointers, so a load
           // placed after a store would have to wait for it (possible aliasing) and the 16 columns would serialise on
           // global-memory latency
@@ -550,7 +550,7 @@ __global__ void __launch_bounds__(NT, 1) conv_tc5s_kernel(ConvArgs a) {
   #pragma unroll
             for (int e = 0; e < 16; ++e) v[e] += v2[e];
           }
-          if (t < T) {
+          if (t < T && ct * TN + col < a.Cout) {
             // every load (bias, ReLU mask) is issued BEFORE the first store: y, act and bias are plain pointers, so a load
             // placed after a store would have to wait for it (possible aliasing) and the 16 columns would serialise on
             // global-memory latency
@@ -604,12 +604,15 @@ namespace vhmm {
 int conv_impl_mode();
 
 static inline bool conv_tc5_ok(int Cin, int Cout, int64_t T, int kw, const void* x, const void* y) {
-  return (kw == 1 || kw == 3) && Cin % ct5::KC == 0 && Cout % ct5::TN == 0 && (T & 3) == 0 && T >= 4 &&
+  return (kw == 1 || kw == 3) && Cin % ct5::KC == 0 && Cout % 16 == 0 && (T & 3) == 0 && T >= 4 &&
          (((uintptr_t)x | (uintptr_t)y) & 15) == 0;
 }
 // bytes of prepared weights (+ two abs-max words) for one (layer, view)
+// Cout that is not a multiple of the 128-channel output tile is padded with zero weight rows (the MMA costs the same for any
+// N <= 128); the epilogue stores the real channels only.  Needs Cout % 16 == 0 (the epilogue works in groups of 16 columns).
+static inline int conv_tc5_cout_padded(int Cout) { return (Cout + ct5::TN - 1) / ct5::TN * ct5::TN; }
 static inline size_t conv_tc5_weight_bytes(int Cin, int Cout, int kw) {
-  return align_up((size_t)Cin * Cout * kw * 4, 256) + 256;
+  return align_up((size_t)Cin * conv_tc5_cout_padded(Cout) * kw * 4, 256) + 256;
 }
 
 struct Tc5Weights {        // a weight view prepared for conv_tc5_kernel
@@ -621,9 +624,10 @@ struct Tc5Weights {        // a weight view prepared for conv_tc5_kernel
 // prepare one weight view into `buf` (conv_tc5_weight_bytes); n_w = number of floats of the underlying tensor
 static inline int conv_tc5_prepare(WView wv, int64_t n_w, int Cin, int Cout, int kw, void* buf, Tc5Weights* out, cudaStream_t st) {
   uint8_t* base = (uint8_t*)buf;
-  const size_t wb = align_up((size_t)Cin * Cout * kw * 4, 256);
+  const size_t wb = align_up((size_t)Cin * conv_tc5_cout_padded(Cout) * kw * 4, 256);
   uint32_t* words = (uint32_t*)(base + wb);
   VHMM_CUDA_CHECK(cudaMemsetAsync(words, 0, 8, st));
+  if (Cout % ct5::TN) VHMM_CUDA_CHECK(cudaMemsetAsync(base, 0, wb, st));       // the padding rows
   int64_t blocks = cdiv(n_w, 1024);
   if (blocks > 1184) blocks = 1184;
   ct5::absmax_kernel<<<(unsigned)blocks, 256, 0, st>>>(wv.w, n_w, words);
@@ -660,7 +664,7 @@ static inline int launch_conv_tc5(const float* x, const Tc5Weights& W, const flo
   ct5::ConvArgs a{};
   a.x = x; a.Wg = W.Wg; a.bias = bias; a.act = act; a.y = y; a.amax_x = ax; a.amax_w = W.amax_w; a.amax_y = amax_y;
   a.B = B; a.Cin = Cin; a.Cout = Cout; a.T = (int)T; a.epi = epi;
-  a.ntt = (int)cdiv(T, ct5::TM); a.nct = Cout / ct5::TN;
+  a.ntt = (int)cdiv(T, ct5::TM); a.nct = conv_tc5_cout_padded(Cout) / ct5::TN;
   a.nitems = B * a.ntt * a.nct;
   int64_t grid = device_sm_count();
   if (a.nct >= 2 && Cin / ct5::KC <= ct5::SMAX_KC) {     // input-stationary build: convert the input tile once for all output tiles

@@ -34,7 +34,7 @@ int conv1d_fwd(const float* x, const float* w, const float* bias, int64_t B, int
                float* y, void* ws, size_t ws_bytes, cudaStream_t st) {
   const int mode = conv_impl_mode();
   const bool ok = conv_tc5_ok(Cin, Cout, T, kw, x, y);
-  VHMM_REQUIRE(mode != 2 || ok, VHMM_E_DIMS, "conv1d: tensor-core layer kernel needs Cin %% 16 == 0, Cout %% 128 == 0, T %% 4 == 0");
+  VHMM_REQUIRE(mode != 2 || ok, VHMM_E_DIMS, "conv1d: tensor-core layer kernel needs Cin %% 16 == 0, Cout %% 16 == 0, T %% 4 == 0");
   if (mode != 1 && ok) {
     VHMM_REQUIRE(ws && ws_bytes >= conv_tc5_weight_bytes(Cin, Cout, kw), VHMM_E_WORKSPACE, "conv1d: workspace too small");
     Tc5Weights W;
@@ -186,6 +186,55 @@ static int cwgrad(const Tc5Ctx* ctx, const float* dy, const float* x, float* gW,
   return launch_wgrad(dy, x, gW, gB, layout, B, Cin, Cout, T, kw, scratch, st);
 }
 
+// ---- decoder.embeddings folded into decoder.conv1 (ELBO of the wide model) ---------------------------------------------
+// e = E^T q is linear and q is zero outside [0,T), so conv1(e) = conv(q, W') with W'[o,k,tau] = sum_d W1[o,d,tau] E[k,d]:
+// a K -> H layer instead of H -> H (8x fewer MACs at H = 256, K = 32) in the forward pass, the input gradient (which now
+// yields d loss / dq directly) and the weight gradient; the gradients of W1 and E follow from dW' by the chain rule after
+// the last batch chunk.  Exact up to fp32 re-association (the fused tile kernels do the same: DESIGN.md 4.1).
+__global__ void __launch_bounds__(256) fold_emb_kernel(const float* __restrict__ W1, const float* __restrict__ E, int H, int K,
+                                                       float* __restrict__ Wf) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= H * K * 3) return;
+  const int tau = i % 3, k = (i / 3) % K, o = i / (3 * K);
+  float acc = 0.f;
+  for (int dd = 0; dd < H; ++dd) acc = fmaf(W1[((int64_t)o * H + dd) * 3 + tau], E[(int64_t)k * H + dd], acc);
+  Wf[i] = acc;
+}
+// gW1[o,d,tau] += sum_k gWf[o,k,tau] E[k,d]
+__global__ void __launch_bounds__(256) unfold_w1_kernel(const float* __restrict__ gWf, const float* __restrict__ E, int H, int K,
+                                                        float* __restrict__ gW1) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= H * H * 3) return;
+  const int tau = i % 3, dd = (i / 3) % H, o = i / (3 * H);
+  float acc = 0.f;
+  for (int k = 0; k < K; ++k) acc = fmaf(gWf[((int64_t)o * K + k) * 3 + tau], E[(int64_t)k * H + dd], acc);
+  gW1[i] += acc;
+}
+// gE[k,d] += sum_{o,tau} gWf[o,k,tau] W1[o,d,tau]
+__global__ void __launch_bounds__(256) unfold_emb_kernel(const float* __restrict__ gWf, const float* __restrict__ W1, int H, int K,
+                                                         float* __restrict__ gE) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= K * H) return;
+  const int dd = i % H, k = i / H;
+  float acc = 0.f;
+  for (int o = 0; o < H; ++o)
+#pragma unroll
+    for (int tau = 0; tau < 3; ++tau) acc = fmaf(gWf[((int64_t)o * K + k) * 3 + tau], W1[((int64_t)o * H + dd) * 3 + tau], acc);
+  gE[i] += acc;
+}
+static std::atomic<int> g_fold_mode{-1};    // environment VHMM_EMB_FOLD=0 keeps the embedding a layer of its own
+static bool fold_enabled() {
+  int m = g_fold_mode.load();
+  if (m < 0) { const char* e = getenv("VHMM_EMB_FOLD"); m = (e && e[0] == '0') ? 0 : 1; g_fold_mode = m; }
+  return m == 1;
+}
+int emb_fold_select(int on) { g_fold_mode = on ? 1 : 0; return 0; }
+static bool fold_shape(const vhmm_dims& d) { return d.K % ct5::KC == 0 && d.H % ct5::KC == 0; }
+static size_t fold_bytes(const vhmm_dims& d) {
+  if (!fold_shape(d)) return 0;
+  return 2 * align_up((size_t)d.H * d.K * 3 * 4, 256) + conv_tc5_weight_bytes(d.K, d.H, 3) + conv_tc5_weight_bytes(d.H, d.K, 3) + 1024;
+}
+
 struct LayerwiseSizes {
   int64_t per_step_fwd;   // floats per (sequence, step) kept by the forward pass
   int64_t per_step_bwd;   // extra floats per step for the backward pass
@@ -205,6 +254,7 @@ static LayerwiseSizes layerwise_sizes(const vhmm_dims& d) {
   v = wgrad_scratch_floats(d.U, d.TH, 1, BIG); m = v > m ? v : m;
   v = wgrad_scratch_floats(d.TH, d.K * d.K, 1, BIG); m = v > m ? v : m;
   v = wgrad_scratch_floats(d.K, d.H, 1, BIG); m = v > m ? v : m;
+  v = wgrad_scratch_floats(d.K, d.H, 3, BIG); m = v > m ? v : m;      // folded embedding x conv1
   v = wgrad_scratch_floats(d.H, d.H, 3, BIG); m = v > m ? v : m;
   v = wgrad_scratch_floats(d.H, 2 * d.C, 1, BIG); m = v > m ? v : m;
   // tensor-core weight gradients keep one partial per (weight block, split): upper bound over the batch size
@@ -218,6 +268,7 @@ static LayerwiseSizes layerwise_sizes(const vhmm_dims& d) {
   v = tc5s(d.H, d.H, 3); m = v > m ? v : m;
   v = tc5s(d.H2, d.K, 1); m = v > m ? v : m;
   v = tc5s(d.K, d.H, 1); m = v > m ? v : m;
+  v = tc5s(d.K, d.H, 3); m = v > m ? v : m;
   v = tc5s(d.U, d.TH, 1); m = v > m ? v : m;
   v = tc5s(d.H, 2 * d.C, 1); m = v > m ? v : m;
   v = tc5s(d.C, d.H, 3); m = v > m ? v : m;
@@ -233,6 +284,7 @@ static size_t fixed_bytes(const vhmm_dims& d, int64_t T) {
   bytes += align_up(sizeof(float) * (size_t)s.scratch, 256);
   bytes += tc5_ctx_bytes(d);                                           // prepared tensor-core weights
   bytes += 64 * 1024;                                                  // per-CTA partial sums of the fused prior kernel
+  bytes += fold_bytes(d);                                              // folded embedding x conv1 weights, their gradient
   return bytes + 4096;
 }
 
@@ -364,6 +416,29 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
     int rc0 = tc5_ctx_prepare(d, P, grads != nullptr, A, &ctx, st);
     if (rc0) return rc0;
   }
+  // decoder.embeddings folded into decoder.conv1 (tensor-core layer kernels only)
+  float *Wf = nullptr, *gWf = nullptr;
+  const bool fold = ctx.pool && fold_enabled() && fold_shape(d) && (T & 3) == 0 && ctx.n + 2 <= 16;
+  if (fold) {
+    Wf = A.take<float>((size_t)H * K * 3);
+    gWf = A.take<float>((size_t)H * K * 3);
+    void* bf = A.take<uint8_t>(conv_tc5_weight_bytes(K, H, 3));
+    void* bd = A.take<uint8_t>(conv_tc5_weight_bytes(H, K, 3));
+    VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "elbo: workspace %zu too small (folded decoder weights)", ws_bytes);
+    fold_emb_kernel<<<(unsigned)cdiv((int64_t)H * K * 3, 256), 256, 0, st>>>(P.p[P_D1W], P.p[P_EMB], H, K, Wf);
+    VHMM_LAUNCH_CHECK();
+    VHMM_CUDA_CHECK(cudaMemsetAsync(gWf, 0, (size_t)H * K * 3 * sizeof(float), st));
+    Tc5Ctx::Entry& ef = ctx.e[ctx.n++];
+    ef.w = Wf; ef.dgrad = 0;
+    int rcf = conv_tc5_prepare(wview_fwd(Wf, K, 3), (int64_t)H * K * 3, K, H, 3, bf, &ef.tw, st);
+    if (rcf) return rcf;
+    if (grads) {
+      Tc5Ctx::Entry& ed = ctx.e[ctx.n++];
+      ed.w = Wf; ed.dgrad = 1;
+      rcf = conv_tc5_prepare(wview_dgrad(Wf, K, 3), (int64_t)H * K * 3, H, K, 3, bd, &ed.tw, st);
+      if (rcf) return rcf;
+    }
+  }
   VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "elbo: workspace %zu too small (fixed part %zu)", ws_bytes, A.used);
   const int64_t per_step = S.per_step_fwd + (grads ? S.per_step_bwd : 0);
   const size_t left = (ws_bytes - A.used > 64 * 256) ? ws_bytes - A.used - 64 * 256 : 0;
@@ -436,7 +511,12 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
       row_logsoftmax_kernel<<<g, 256, 0, st>>>(M, K, (int)T);
       VHMM_LAUNCH_CHECK();
     }
-    RC(decoder_chain(d, P, q, nb, T, e, g1, g2, st, &ctx));
+    if (fold) {
+      RC(cconv(&ctx, 0, q, wview_fwd(Wf, K, 3), P.p[P_D1B], nullptr, g1, nb, K, H, T, 3, EPI_RELU, st));
+      RC(cconv(&ctx, 0, g1, wview_fwd(P.p[P_D2W], H, 3), P.p[P_D2B], nullptr, g2, nb, H, H, T, 3, EPI_RELU, st));
+    } else {
+      RC(decoder_chain(d, P, q, nb, T, e, g1, g2, st, &ctx));
+    }
     RC(launch_conv(g2, wview_fwd(P.p[P_DPW], H, 1), P.p[P_DPB], nullptr, p, nb, H, 2 * C, T, 1, EPI_NONE, st));
     {
       dim3 g((unsigned)cdiv(T, 256), (unsigned)nb);
@@ -464,6 +544,10 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
     RC(launch_conv(dp, wview_dgrad(P.p[P_DPW], H, 1), nullptr, g2, dg2, nb, 2 * C, H, T, 1, EPI_MASK, st));
     RC(cwgrad(&ctx, dg2, g1, grads + off[P_D2W], grads + off[P_D2B], wview_fwd(nullptr, H, 3), nb, H, H, T, 3, scratch, st));
     RC(cconv(&ctx, 1, dg2, wview_dgrad(P.p[P_D2W], H, 3), nullptr, g1, dg1, nb, H, H, T, 3, EPI_MASK, st));
+    if (fold) {     // d/dW' (K -> H weight gradient) and d/dq (H -> K input gradient, zero-padded to one 128-channel tile)
+      RC(cwgrad(&ctx, dg1, q, gWf, grads + off[P_D1B], wview_fwd(nullptr, K, 3), nb, K, H, T, 3, scratch, st));
+      RC(cconv(&ctx, 1, dg1, wview_dgrad(Wf, K, 3), nullptr, nullptr, dqd, nb, H, K, T, 3, EPI_NONE, st));
+    } else {
     RC(cwgrad(&ctx, dg1, e, grads + off[P_D1W], grads + off[P_D1B], wview_fwd(nullptr, H, 3), nb, H, H, T, 3, scratch, st));
     RC(cconv(&ctx, 1, dg1, wview_dgrad(P.p[P_D1W], H, 3), nullptr, nullptr, de, nb, H, H, T, 3, EPI_NONE, st));
     {
@@ -471,6 +555,7 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
       RC(cwgrad(&ctx, de, q, grads + off[P_EMB], nullptr, embL, nb, K, H, T, 1, scratch, st));
       WView embT{P.p[P_EMB], 0, H, 1, 0};  // dq[k,t] = sum_d E[k,d] de[d,t]: W(o=k, c=d)
       RC(launch_conv(de, embT, nullptr, nullptr, dqd, nb, H, K, T, 1, EPI_NONE, st));
+    }
     }
     {
       dim3 g((unsigned)cdiv(T, 256), (unsigned)nb);
@@ -502,6 +587,12 @@ int layerwise_elbo(const vhmm_dims& d, const vhmm_params& P, const float* x, con
     RC(cwgrad(&ctx, da, uc, grads + off[P_T0W], grads + off[P_T0B], wview_fwd(nullptr, U, 1), nb, U, TH, T, 1, scratch, st));
   }
 #undef RC
+  if (fold && grads) {     // chain rule from dW' to decoder.conv1.weight and decoder.embeddings
+    unfold_w1_kernel<<<(unsigned)cdiv((int64_t)H * H * 3, 256), 256, 0, st>>>(gWf, P.p[P_EMB], H, K, grads + off[P_D1W]);
+    VHMM_LAUNCH_CHECK();
+    unfold_emb_kernel<<<(unsigned)cdiv((int64_t)K * H, 256), 256, 0, st>>>(gWf, P.p[P_D1W], H, K, grads + off[P_EMB]);
+    VHMM_LAUNCH_CHECK();
+  }
   finalize_prior_kernel<<<1, 32, 0, st>>>(log_pi, qsum, norms, betaf, K, sums,
                                           grads ? grads + off[P_LOGPRIOR] : nullptr);
   VHMM_LAUNCH_CHECK();

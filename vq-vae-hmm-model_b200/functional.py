@@ -306,6 +306,11 @@ def prior_select(mode: str = "auto"):
     check(_lib.lib().vhmm_prior_select({"auto": 0, "fused_f32": 1, "layers": 2}[mode]), "vhmm_prior_select")
 
 
+def emb_fold_select(on: bool):
+    """decoder.embeddings folded into decoder.conv1 in the layer-wise ELBO (include/vhmm.h: vhmm_emb_fold_select)."""
+    check(_lib.lib().vhmm_emb_fold_select(1 if on else 0), "vhmm_emb_fold_select")
+
+
 def tma_select(on: bool):
     """Input windows of the tile kernels by tensor-map TMA (True) or cp.async (False, default).  include/vhmm.h."""
     check(_lib.lib().vhmm_tma_select(1 if on else 0), "vhmm_tma_select")
