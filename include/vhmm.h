@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define VHMM_VERSION 111 /* major*100 + minor */
+#define VHMM_VERSION 112 /* major*100 + minor */
 #define VHMM_NUM_PARAMS 18
 #define VHMM_PAD_STATE 255 /* Viterbi path value for t >= lengths[b] */
 
@@ -342,6 +342,20 @@ int vhmm_hmm_numerics_select(int mode);
 int vhmm_viterbi(const float* log_pi, const float* log_A, const float* log_b,
                  const int64_t* lengths, int64_t B, int64_t T, int64_t K, uint8_t* path,
                  float* score, void* workspace, size_t workspace_bytes, void* stream);
+/* Allocation-free variant of vhmm_viterbi.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * results as vhmm_viterbi, bit for bit; the back-pointer scratch is a static device array of
+ * VHMM_VITERBI_STATIC_MAX_BYTES (4 MiB) inside the library, held by every GPU that loads it until exit.  Limit:
+ * B * T * (K <= 4 ? 1 : K) bytes <= VHMM_VITERBI_STATIC_MAX_BYTES (K <= 4: 4,194,304 sequence-steps per call; K = 32:
+ * 131,072) -- beyond it the call returns VHMM_E_WORKSPACE and vhmm_last_error() names the limit.  The call performs no
+ * cudaMalloc / cudaFree and calls no allocating library routine; the first call on a device resolves the array's device
+ * address (cudaGetSymbolAddress) -- a call with B == 0 does only that and may be used as set-up before a capture begins.
+ * All calls share the one array: calls that may overlap on the GPU (different streams) race on it and must be ordered by the
+ * caller; nothing in it needs clearing between calls. */
+#define VHMM_VITERBI_STATIC_MAX_BYTES (4u << 20)
+int vhmm_viterbi_static(const float* log_pi, const float* log_A, const float* log_b,
+                        const int64_t* lengths, int64_t B, int64_t T, int64_t K, uint8_t* path,
+                        float* score, void* stream);
 /* cfg 3: Viterbi path + posterior gamma from one read of the inputs. */
 int vhmm_hmm_decode(const float* log_pi, const float* log_A, const float* log_b,
                     const int64_t* lengths, int64_t B, int64_t T, int64_t K, uint8_t* path,

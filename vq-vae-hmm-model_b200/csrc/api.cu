@@ -70,6 +70,7 @@ int hmm_emission_logprob(const float*, const float*, const float*, int64_t, int6
 int hmm_forward(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, float*, float*, cudaStream_t);
 int hmm_posterior(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, float*, float*, float*, void*, size_t, cudaStream_t);
 int hmm_viterbi(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, void*, size_t, cudaStream_t);
+int hmm_viterbi_static(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, cudaStream_t);
 int hmm_decode(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, float*, void*, size_t, cudaStream_t);
 int hmm_scan(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
 int hmm_posterior_select(int mode);
@@ -376,6 +377,14 @@ int vhmm_viterbi(const float* log_pi, const float* log_A, const float* log_b, co
                  size_t workspace_bytes, void* stream) {
   HMM_ARGS_OK(); ARG(path, "path"); ARG(workspace, "workspace");
   return hmm_viterbi(log_pi, log_A, log_b, lengths, B, T, K, path, score, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int vhmm_viterbi_static(const float* log_pi, const float* log_A, const float* log_b, const int64_t* lengths,
+                        int64_t B, int64_t T, int64_t K, uint8_t* path, float* score, void* stream) {
+  if (B == 0) return hmm_viterbi_static(nullptr, nullptr, nullptr, nullptr, 0, 0, K >= 1 && K <= 32 ? K : 1, nullptr, nullptr,
+                                        (cudaStream_t)stream);     // set-up only
+  HMM_ARGS_OK(); ARG(path, "path"); ARG(B <= (int64_t)1 << 31 && T <= (int64_t)1 << 31, "B, T");
+  return hmm_viterbi_static(log_pi, log_A, log_b, lengths, B, T, K, path, score, (cudaStream_t)stream);
 }
 
 int vhmm_hmm_decode(const float* log_pi, const float* log_A, const float* log_b,

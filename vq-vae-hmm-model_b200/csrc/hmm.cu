@@ -293,6 +293,36 @@ int hmm_viterbi(const float* log_pi, const float* A, const float* Bm, const int6
   return 0;
 }
 
+// ---- allocation-free Viterbi (include/vhmm.h: vhmm_viterbi_static) ------------------------------------------------------
+// The back-pointer scratch of hmm_viterbi lives in a file-scope device array instead of a caller workspace: nothing is
+// allocated by the call (usable where cudaMalloc is off limits).  Every GPU that loads the library holds the array until
+// exit.  In HOST code the array's name is only a handle: the device address comes from cudaGetSymbolAddress, resolved once per
+// device with that device current (below), and THAT pointer goes to the kernels.  All calls share the array -- calls that
+// overlap on the GPU (two streams) race on it; nothing in it has to start at zero (every back-pointer that the back-track
+// reads was written by the same call's forward sweep).
+static __device__ __align__(256) uint8_t g_viterbi_scratch[VHMM_VITERBI_STATIC_MAX_BYTES];
+static std::atomic<void*> g_viterbi_scratch_ptr[VHMM_MAX_DEVICES];
+
+int hmm_viterbi_static(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B,
+                       int64_t T, int64_t K, uint8_t* path, float* score, cudaStream_t st) {
+  VHMM_REQUIRE(K >= 1 && K <= 32, VHMM_E_DIMS, "viterbi_static: K=%lld outside [1, 32]", (long long)K);
+  const int dev = current_device();
+  void* ptr = g_viterbi_scratch_ptr[dev].load(std::memory_order_acquire);
+  if (!ptr) {   // set-up, once per device (a call with B == 0 does only this: e.g. before a stream capture begins)
+    VHMM_CUDA_CHECK(cudaGetSymbolAddress(&ptr, g_viterbi_scratch));
+    VHMM_REQUIRE(ptr != nullptr, VHMM_E_WORKSPACE, "viterbi_static: no device address for the scratch array");
+    g_viterbi_scratch_ptr[dev].store(ptr, std::memory_order_release);
+  }
+  if (B == 0) return 0;
+  // (B, T <= 2^31 each, checked by the caller: the product below cannot overflow)
+  const uint64_t need = (uint64_t)B * (uint64_t)T * (uint64_t)psi_bytes(K);
+  VHMM_REQUIRE(need <= (uint64_t)VHMM_VITERBI_STATIC_MAX_BYTES, VHMM_E_WORKSPACE,
+               "viterbi_static: B*T*%d = %llu bytes of back-pointers exceed the static scratch of %llu bytes "
+               "(VHMM_VITERBI_STATIC_MAX_BYTES); use vhmm_viterbi with a caller workspace",
+               (int)psi_bytes(K), (unsigned long long)need, (unsigned long long)VHMM_VITERBI_STATIC_MAX_BYTES);
+  return hmm_viterbi(log_pi, A, Bm, lengths, B, T, K, path, score, ptr, (size_t)VHMM_VITERBI_STATIC_MAX_BYTES, st);
+}
+
 int hmm_decode(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B,
                int64_t T, int64_t K, uint8_t* path, float* gamma, float* loglik, void* ws, size_t ws_bytes,
                cudaStream_t st) {
