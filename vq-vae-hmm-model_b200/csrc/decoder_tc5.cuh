@@ -344,9 +344,13 @@ __global__ void __launch_bounds__(NTH, 1) decoder_tc5_kernel(Common cm, vhmm_par
     const float sB = tc5::pow2_scale(__uint_as_float(amax_sh));
     for (int i = tid; i < t5::NPL * NC; i += NTH) {   // dg2 parts -> RB (+ the tail chunk with columns >= J0+TT zeroed)
       const int pl = i / NC, j = i - pl * NC;
-      __align__(16) __half hh[8], mm[8];
+      uint4 hh[1], mm[1];
+      {
+        float v8[8];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) tc5::split_f16(S[(pl * 8 + e) * PT + j] * sB, hh[e], mm[e]);
+        for (int e = 0; e < 8; ++e) v8[e] = S[(pl * 8 + e) * PT + j];
+        tc5::split8(v8, tc5::f2_pack(sB, sB), hh[0], mm[0]);
+      }
       uint8_t* p = RB + pl * t5::PLANE + (j + 1) * 16;
       *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(hh);
       *reinterpret_cast<uint4*>(p + t5::PART) = *reinterpret_cast<const uint4*>(mm);

@@ -59,9 +59,13 @@ template <int NCH>
 __device__ __forceinline__ void act_to_parts(const float* __restrict__ A, float scale, uint8_t* dst, int part_bytes) {
   for (int i = threadIdx.x; i < (NCH / 8) * NC; i += NTH) {
     const int pl = i / NC, j = i - pl * NC;
-    __align__(16) __half hh[8], mm[8];
+    uint4 hh[1], mm[1];
+    {
+      float v8[8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) tc5::split_f16(A[(pl * 8 + e) * PT + j] * scale, hh[e], mm[e]);
+      for (int e = 0; e < 8; ++e) v8[e] = A[(pl * 8 + e) * PT + j];
+      tc5::split8(v8, tc5::f2_pack(scale, scale), hh[0], mm[0]);
+    }
     uint8_t* p = dst + pl * t5e::PLANE + (j + 1) * 16;
     *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(hh);
     *reinterpret_cast<uint4*>(p + part_bytes) = *reinterpret_cast<const uint4*>(mm);
@@ -530,9 +534,13 @@ __global__ void __launch_bounds__(NTH, 1) enc_bwd_tc5_kernel(Common cm, vhmm_par
     const float sD = tc5::pow2_scale(__uint_as_float(amax2_sh));
     for (int i = tid; i < (H2 / 8) * NC; i += NTH) {   // dh2 parts -> RB (+ the tail chunk with columns >= J0+TT zeroed)
       const int pl = i / NC, j = i - pl * NC;
-      __align__(16) __half hh[8], mm[8];
+      uint4 hh[1], mm[1];
+      {
+        float v8[8];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) tc5::split_f16(H2b[(pl * 8 + e) * PT + j] * sD, hh[e], mm[e]);
+        for (int e = 0; e < 8; ++e) v8[e] = H2b[(pl * 8 + e) * PT + j];
+        tc5::split8(v8, tc5::f2_pack(sD, sD), hh[0], mm[0]);
+      }
       uint8_t* p = RB + pl * t5e::PLANE + (j + 1) * 16;
       *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(hh);
       *reinterpret_cast<uint4*>(p + t5e::D2_PART) = *reinterpret_cast<const uint4*>(mm);

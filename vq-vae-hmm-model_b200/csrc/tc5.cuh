@@ -124,6 +124,33 @@ __device__ __forceinline__ void split_f16(float xs, __half& h, __half& m) {
   m = __float2half_rn(xs - __half2float(h));
 }
 
+// packed fp32 pairs (Blackwell add / mul .f32x2): one issue slot for two lanes of work (the conversion loops are issue-bound)
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t f2_pack(float a, float b) { f2_t r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void f2_unpack(f2_t v, float& a, float& b) { asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ f2_t f2_add(f2_t a, f2_t b) { f2_t r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2_sub(f2_t a, f2_t b) { f2_t r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2_mul(f2_t a, f2_t b) { f2_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+// eight fp32 values (scaled by s2 = {s, s}) -> their fp16 h and m parts as two 16-byte rows (same split as tc5::split_f16)
+__device__ __forceinline__ void split8(const float* v, f2_t s2, uint4& h, uint4& m) {
+  uint32_t hh[4], mm[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const f2_t xs = f2_mul(f2_pack(v[2 * e], v[2 * e + 1]), s2);
+    float x0, x1;
+    f2_unpack(xs, x0, x1);
+    const __half2 h2 = __floats2half2_rn(x0, x1);
+    const float2 hf = __half22float2(h2);
+    float r0, r1;
+    f2_unpack(f2_sub(xs, f2_pack(hf.x, hf.y)), r0, r1);
+    const __half2 m2 = __floats2half2_rn(r0, r1);
+    hh[e] = *reinterpret_cast<const uint32_t*>(&h2);
+    mm[e] = *reinterpret_cast<const uint32_t*>(&m2);
+  }
+  h = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+  m = make_uint4(mm[0], mm[1], mm[2], mm[3]);
+}
+
 // power-of-two scale that maps |x| <= bound into [2^13, 2^14) (fp16 max = 65504); 1 for bound == 0
 __device__ __forceinline__ float pow2_scale(float bound) {
   // integer form (this runs on every thread after each per-tile maximum): exponent field -> 2^(13 - e)
