@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define VHMM_VERSION 112 /* major*100 + minor */
+#define VHMM_VERSION 113 /* major*100 + minor */
 #define VHMM_NUM_PARAMS 18
 #define VHMM_PAD_STATE 255 /* Viterbi path value for t >= lengths[b] */
 
@@ -356,7 +356,14 @@ int vhmm_viterbi(const float* log_pi, const float* log_A, const float* log_b,
 int vhmm_viterbi_static(const float* log_pi, const float* log_A, const float* log_b,
                         const int64_t* lengths, int64_t B, int64_t T, int64_t K, uint8_t* path,
                         float* score, void* stream);
-/* cfg 3: Viterbi path + posterior gamma from one read of the inputs. */
+/* cfg 3: Viterbi path + posterior gamma.  Default: the Viterbi sweep, then the one-pass posterior kernel (the inputs are read
+ * twice: 109 B/step moved for 61 algorithmic).  VHMM_DECODE_ONE_KERNEL (environment VHMM_DECODE=one; K <= 4 with a sequence
+ * that fits one warp's shared memory) reads them ONCE: the one-pass posterior kernel plus a Viterbi helper warp per CTA that
+ * walks the raw log_A / log_b in shared memory before the posterior passes overwrite them.  Bit-identical paths, the same gamma
+ * -- and measured 2x SLOWER at cfg 3 (14.5 vs 7.0 ms: the serial max-plus chain competes for issue slots with the issue-bound
+ * posterior passes), hence opt-in. */
+enum { VHMM_DECODE_AUTO = 0, VHMM_DECODE_ONE_KERNEL = 1 };
+int vhmm_hmm_decode_select(int mode);
 int vhmm_hmm_decode(const float* log_pi, const float* log_A, const float* log_b,
                     const int64_t* lengths, int64_t B, int64_t T, int64_t K, uint8_t* path,
                     float* gamma, float* loglik, void* workspace, size_t workspace_bytes,

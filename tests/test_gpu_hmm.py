@@ -117,11 +117,40 @@ def test_viterbi_bit_exact(K, T, B):
     path, sc = Fn.viterbi(*d)
     assert np.array_equal(path.cpu().numpy(), path64)
     assert np.array_equal(sc.cpu().numpy(), score)
-    p2, gamma, ll = Fn.hmm_decode(*d)
-    assert np.array_equal(p2.cpu().numpy(), path64)
     g64, _, ll64 = H.posteriors(lp, la, lb, L)
-    assert np.abs(gamma.cpu().numpy() - g64).max() <= TOL
-    assert np.allclose(ll.cpu().numpy(), ll64, rtol=TOL, atol=1e-5)
+    for mode in ("auto", "one"):     # two kernels / one kernel (Viterbi helper warp inside the one-pass posterior kernel)
+        Fn.hmm_decode_select(mode)
+        try:
+            p2, gamma, ll = Fn.hmm_decode(*d)
+        finally:
+            Fn.hmm_decode_select("auto")
+        assert np.array_equal(p2.cpu().numpy(), path64), mode
+        assert np.abs(gamma.cpu().numpy() - g64).max() <= TOL, mode
+        assert np.allclose(ll.cpu().numpy(), ll64, rtol=TOL, atol=1e-5), mode
+
+
+@pytest.mark.parametrize("K,T,B", [(3, 256, 2500), (4, 100, 77), (2, 64, 9), (3, 260, 301)])
+def test_decode_one_kernel_equals_two_kernels(K, T, B):
+    """cfg-3 decode: the one-kernel build (several trips per CTA, a last trip with fewer sequences than posterior warps, rows
+    of length 0 and 1, T % 16 != 0 -> byte path stores) against the Viterbi kernel + one-pass posterior kernel: identical
+    path bytes (incl. the 0xFF padding), identical gamma and log-likelihood (the posterior arithmetic is the same code)."""
+    import vhmm_b200.functional as Fn
+    lp, la, lb, L = rand_hmm(B, T, K, seed=3 * K + T)
+    la = np.round(la * 2) / 2; lb = np.round(lb * 2) / 2; lp = np.round(lp * 2) / 2      # exact ties
+    L[1] = 0; L[2] = 1
+    d = dev(lp.astype(np.float32), la.astype(np.float32), lb.astype(np.float32), L)
+    out = {}
+    for mode in ("auto", "one"):
+        Fn.hmm_decode_select(mode)
+        try:
+            out[mode] = [t.cpu().numpy() for t in Fn.hmm_decode(*d)]
+        finally:
+            Fn.hmm_decode_select("auto")
+    assert np.array_equal(out["one"][0], out["auto"][0])
+    assert np.array_equal(out["one"][1], out["auto"][1])
+    assert np.array_equal(out["one"][2], out["auto"][2])
+    pv, _ = Fn.viterbi(*d)
+    assert np.array_equal(out["one"][0], pv.cpu().numpy())
 
 
 def test_viterbi_all_ties_lowest_index():

@@ -20,7 +20,7 @@ def test_library_exports_every_declared_symbol():
     assert declared == set(_lib.PROTOTYPES), declared ^ set(_lib.PROTOTYPES)
     for name in declared:
         assert hasattr(L, name), name
-    assert L.vhmm_version() == 112
+    assert L.vhmm_version() == 113
 
 
 def test_param_layout_matches_state_dict():

@@ -128,6 +128,7 @@ PROTOTYPES = {
     "vhmm_hmm_numerics_select": (ctypes.c_int, [ctypes.c_int]),
     "vhmm_viterbi": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _SZ, _P]),
     "vhmm_viterbi_static": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P]),
+    "vhmm_hmm_decode_select": (ctypes.c_int, [ctypes.c_int]),
     "vhmm_hmm_decode": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _SZ, _P]),
     "vhmm_hmm_scan": (ctypes.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _SZ, _P]),
 }

@@ -70,6 +70,7 @@ int hmm_emission_logprob(const float*, const float*, const float*, int64_t, int6
 int hmm_forward(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, float*, float*, cudaStream_t);
 int hmm_posterior(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, float*, float*, float*, void*, size_t, cudaStream_t);
 int hmm_viterbi(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, void*, size_t, cudaStream_t);
+int hmm_decode_select(int mode);
 int hmm_viterbi_static(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, cudaStream_t);
 int hmm_decode(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, uint8_t*, float*, float*, void*, size_t, cudaStream_t);
 int hmm_scan(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
@@ -271,6 +272,10 @@ int vhmm_prior_select(int mode) {
   return prior_impl_select(mode);
 }
 int vhmm_emb_fold_select(int on) { return emb_fold_select(on); }
+int vhmm_hmm_decode_select(int mode) {
+  ARG(mode == VHMM_DECODE_AUTO || mode == VHMM_DECODE_ONE_KERNEL, "mode");
+  return hmm_decode_select(mode);
+}
 int vhmm_elbo_decoder_active(void) { return fused_decoder_active(); }
 int vhmm_tma_select(int on) { return fused_tma_select(on); }
 

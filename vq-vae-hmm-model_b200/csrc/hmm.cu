@@ -150,6 +150,39 @@ static int launch_onepass(hw::Args a, cudaStream_t st) {
   VHMM_LAUNCH_CHECK();
   return 0;
 }
+// cfg-3 decode from ONE read of the inputs (hmm_warp.cuh, VIT): `wpb` posterior warps + the Viterbi helper warp per CTA
+// (measured SLOWER than the two kernels -- 14.5 vs 7.0 ms at cfg 3, see hmm_warp.cuh -- hence opt-in)
+static std::atomic<int> g_decode_mode{-1};   // -1: from env VHMM_DECODE (one = the single kernel), 0 two kernels, 1 one kernel
+int hmm_decode_select(int mode) { g_decode_mode = mode; return 0; }
+static bool decode_onekernel() {
+  if (g_decode_mode < 0) {
+    const char* e = getenv("VHMM_DECODE");
+    g_decode_mode = (e && e[0] == 'o') ? 1 : 0;
+  }
+  return g_decode_mode == 1;
+}
+template <int K>
+static int launch_decode_onepass(hw::Args a, cudaStream_t st) {
+  auto kern = hw::posterior_kernel<K, false, false, false, true>;
+  const size_t tp = (size_t)((a.T + 15) & ~(int64_t)15);
+  const size_t wb = (32 * (size_t)(a.SA + a.SB) + 4) * 4 + tp;       // skewed region + psi / path row
+  int wpb = (int)((110 * 1024) / wb);                                 // two CTAs per SM
+  wpb = wpb < 1 ? 1 : (wpb > 8 ? 8 : wpb);
+  const size_t smem = wb * wpb;
+  const int sms = device_sm_count();
+  VHMM_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  VHMM_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+  int per_sm = 0;
+  VHMM_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, (wpb + 1) * 32, smem));
+  if (per_sm < 1) per_sm = 1;
+  int64_t grid = (int64_t)sms * per_sm;
+  const int64_t need = cdiv(a.B, wpb);
+  if (grid > need) grid = need;
+  kern<<<(unsigned)grid, (wpb + 1) * 32, smem, st>>>(a);
+  VHMM_LAUNCH_CHECK();
+  return 0;
+}
+
 static int hmm_posterior_onepass(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths,
                                  int64_t B, int64_t T, int64_t K, float* loglik, float* gamma, float* xi,
                                  cudaStream_t st) {
@@ -330,6 +363,22 @@ int hmm_decode(const float* log_pi, const float* A, const float* Bm, const int64
   float* stash = ar.take<float>((size_t)B * T * K);
   uint8_t* psi = ar.take<uint8_t>((size_t)B * T * psi_bytes(K));
   VHMM_REQUIRE(ar.ok, VHMM_E_WORKSPACE, "hmm_decode: workspace %zu < %zu", ws_bytes, ar.used);
+  if (small_k(K) && onepass_allowed() && decode_onekernel() && onepass_fits(T, K, A, Bm, gamma, nullptr)) {
+    // ONE kernel, one read of the inputs (48 B/step read, 13 written): the one-pass posterior kernel with a Viterbi helper warp
+    hw::Args w{};
+    w.log_pi = log_pi; w.A = A; w.Bm = Bm; w.lengths = lengths; w.B = B; w.T = T;
+    w.S = 4 * (int)cdiv(T, 128);
+    w.SA = hw::pitch_odd16(w.S * (int)(K * K));
+    w.SB = hw::pitch_odd16(w.S * (int)K);
+    const uint64_t ga = (uint64_t)w.S * K * K / 4, gb = (uint64_t)w.S * K / 4;
+    w.magicA = (unsigned)(((1ull << 32) + ga - 1) / ga);
+    w.magicB = (unsigned)(((1ull << 32) + gb - 1) / gb);
+    w.loglik = loglik; w.gamma = gamma; w.xi = nullptr;
+    w.path = path; w.path_vec16 = ((T & 15) == 0) && (((uintptr_t)path & 15) == 0);
+    int rc = 0;
+    DISPATCH_K(K, (rc = launch_decode_onepass<KK>(w, st)));
+    return rc;
+  }
   if (small_k(K) && onepass_allowed() && onepass_fits(T, K, A, Bm, gamma, nullptr)) {
     // Viterbi sweep (49 B/step) + one-pass posterior (60 B/step): 109 B/step of traffic against
     // 181 B/step for the fused forward sweep + backward sweep below

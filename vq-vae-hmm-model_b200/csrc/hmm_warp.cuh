@@ -38,6 +38,8 @@ struct Args {
   float* loglik;           // (B) or null
   float* gamma;            // (B,T,K)
   float* xi;               // (B,T,K,K) or null (XI kernels only)
+  uint8_t* path;           // (B,T) Viterbi path (VIT kernels only)
+  int path_vec16;          // T % 16 == 0 and path 16-byte aligned: the path rows leave as 16-byte stores
   // SEG kernels (long sequences cut into segments of T steps; B = sequences * nseg rows, `lengths` per SEQUENCE):
   int nseg;                // segments per sequence
   float* Pmat;             // (rows, K*K) segment transfer products, scaled
@@ -181,20 +183,111 @@ __device__ __forceinline__ void warp_prefix_scan(const float* M, int ex, const f
   }
 }
 
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(nthreads) : "memory");
+}
+
+// VIT (cfg-3 decode: Viterbi path + gamma from ONE read of the inputs).  The Viterbi recursion is bit-exact max-plus in log
+// space (hmm_small.cuh: adds and strict compares in the oracle's order), so it cannot be re-associated into a scan: it is a
+// serial chain of T steps per sequence (~16 cycles each).  Run by a lane of the one-pass kernel's own warp it would use 1/32
+// of an issue slot per instruction (5.8 ms by instruction count); as a kernel of its own it reads the 48 B/step a second time
+// (3.4 ms).  Here the CTA has `wpb` posterior warps (one sequence each, as before) plus ONE helper warp whose lane s walks
+// sequence s of the CTA on the raw log_A / log_b that the posterior warp has just landed in shared memory, BEFORE pass 1
+// overwrites them with P_t (named barriers 1: inputs landed, 2: helper done reading).  The back-track and the path stores
+// run after barrier 2, under the posterior passes.  The regions of consecutive warps are skewed by 16 bytes so that the
+// helper's 16-byte loads (one region per lane) are bank-conflict free.
+// MEASURED (B = 2^20, T = 256, K = 3): 14.5 ms against 7.0 ms for the two kernels -- NOT the default.  The barriers alone
+// cost little (4.4 ms with the helper's work removed, the posterior kernel alone takes 4.0), but the helper's forward sweep
+// takes 19 us per trip instead of the ~4 us of its dependent chain: the posterior passes of the SM's other CTA are issue-bound
+// and the helper gets a third of its scheduler's slots (230 instructions per 4 steps at IPC 0.4); the back-track adds 3.7 us.
+// The Viterbi recursion needs ~2 k warp-instructions per sequence at 8 active lanes, half of the 4.5 k issue slots the SM has
+// per sequence at the posterior kernel's pace, so no arrangement of this kind gets under ~6.5 ms.
+// helper_viterbi_forward: returns the final state; psi words (one byte per step, 2 bits per target state) -> psw.
+template <int K>
+__device__ __forceinline__ int helper_viterbi_forward(const float* __restrict__ RA, const float* __restrict__ RB, int S, int SA, int SB,
+                                                       const float* __restrict__ log_pi, int n, uint32_t* __restrict__ psw) {
+  constexpr int KK = K * K;
+  float dl[K];
+#pragma unroll
+  for (int j = 0; j < K; ++j) dl[j] = 0.f;
+  for (int t = 0; t < n; t += 4) {
+    const int c = t / S, r = t - c * S;              // S % 4 == 0: the four steps lie in one chunk
+    float Av[4 * KK], Bv[4 * K];
+    lds4<KK>(RA + c * SA + r * KK, Av);
+    lds4<K>(RB + c * SB + r * K, Bv);
+    uint32_t word = 0;
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      const float* la = Av + s * KK;
+      const float* lb = Bv + s * K;
+      if (t + s < n) {
+        if (t + s == 0) {
+#pragma unroll
+          for (int j = 0; j < K; ++j) dl[j] = __fadd_rn(log_pi[j], lb[j]);
+        } else {
+          float nd[K];
+          uint32_t packed = 0;
+#pragma unroll
+          for (int j = 0; j < K; ++j) {
+            float best = __fadd_rn(dl[0], la[j]);
+            int arg = 0;
+#pragma unroll
+            for (int i = 1; i < K; ++i) {
+              const float cnd = __fadd_rn(dl[i], la[i * K + j]);
+              if (cnd > best) { best = cnd; arg = i; }
+            }
+            nd[j] = __fadd_rn(lb[j], best);
+            packed |= (uint32_t)arg << (2 * j);
+          }
+#pragma unroll
+          for (int j = 0; j < K; ++j) dl[j] = nd[j];
+          word |= packed << (8 * s);
+        }
+      }
+    }
+    psw[t >> 2] = word;
+  }
+  float best = dl[0];
+  int state = 0;
+#pragma unroll
+  for (int j = 1; j < K; ++j)
+    if (dl[j] > best) { best = dl[j]; state = j; }
+  return state;
+}
+// back-track IN PLACE: the psi bytes of a row become its path bytes (0xFF beyond the length)
+__device__ __forceinline__ void helper_backtrack(uint32_t* __restrict__ psw, int T, int n, int state) {
+  const int nw = (T + 3) >> 2;
+  for (int g = nw - 1; g >= 0; --g) {
+    const uint32_t w = (g * 4 < n) ? psw[g] : 0u;
+    uint32_t out = 0;
+#pragma unroll
+    for (int s = 3; s >= 0; --s) {
+      const int t = g * 4 + s;
+      if (t >= n) { out |= 0xFFu << (8 * s); continue; }
+      out |= (uint32_t)state << (8 * s);
+      if (t >= 1) state = (int)((w >> (8 * s + 2 * state)) & 3u);
+    }
+    psw[g] = out;
+  }
+}
+
 // LL_ONLY: forward log-likelihood only (hmm_forward without all-prefix alpha): load, pass 1 without the
 // write-back of P_t, prefix scan, log-likelihood -- no suffix scan, no sweeps, no stores.
 // SEG (with LL_ONLY): the row is one T-step segment of a longer sequence; instead of a log-likelihood the kernel
 // emits the segment's transfer-matrix product (conventions of hmm_scan.cuh: step 0 of a SEQUENCE is alpha_0, not a
 // transfer) for the per-sequence carry scan -- the time-parallel scan of hmm_scan at one-pass bandwidth.
-template <int K, bool XI, bool LL_ONLY = false, bool SEG = false>
-__global__ void __launch_bounds__(128) posterior_kernel(Args a) {
+template <int K, bool XI, bool LL_ONLY = false, bool SEG = false, bool VIT = false>
+__global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
   static_assert(!SEG || LL_ONLY, "segment products come from the log-likelihood-only pass");
+  static_assert(!VIT || (!XI && !LL_ONLY && !SEG && K <= 4), "decode: gamma + path, 2-bit back-pointers");
   constexpr int KK = K * K;
   constexpr float LOG2E = 1.4426950408889634f, LN2 = 0.6931471805599453f;
   extern __shared__ __align__(16) float smem[];
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int wpb = (blockDim.x >> 5) - (VIT ? 1 : 0);      // posterior warps (VIT: the last warp is the Viterbi helper)
   const int S = a.S, SA = a.SA, SB = a.SB;
-  float* regA = smem + (size_t)wib * 32 * (SA + SB);
+  const int REG = 32 * (SA + SB) + (VIT ? 4 : 0);         // floats per warp region (VIT: skewed by 16 bytes)
+  float* regA = smem + (size_t)wib * REG;
   float* regB = regA + 32 * SA;
   float* myA = regA + lane * SA;
   float* myB = regB + lane * SB;
@@ -207,7 +300,50 @@ __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
   for (int j = 0; j < K; ++j) pi[j] = a.log_pi[j] * LOG2E;
 
   const int64_t nwarps = (int64_t)gridDim.x * wpb;
-  for (int64_t b = (int64_t)blockIdx.x * wpb + wib; b < a.B; b += nwarps) {
+  const int TP = (int)((a.T + 15) & ~(int64_t)15);        // VIT: bytes of one psi / path row in shared memory
+  uint8_t* psi_sm = reinterpret_cast<uint8_t*>(smem + (size_t)wpb * REG);
+  // (VIT: every warp of the CTA makes the same number of trips -- the condition is on the CTA's first sequence)
+  for (int64_t b = (int64_t)blockIdx.x * wpb + wib; VIT ? (b - wib < a.B) : (b < a.B); b += nwarps) {
+    if constexpr (VIT) {
+      const int NTH = (wpb + 1) * 32;
+      if (wib == wpb) {                                   // ---- the Viterbi helper warp: lane s <-> sequence base + s
+        const int64_t base = b - wib;
+        const int64_t bs = base + lane;
+        const bool act = lane < wpb && bs < a.B;
+        int n = 0;
+        if (act) {
+          const int64_t Lh = a.lengths[bs];
+          n = (int)(Lh < 0 ? 0 : (Lh > a.T ? a.T : Lh));
+        }
+        uint32_t* psw = reinterpret_cast<uint32_t*>(psi_sm + (size_t)(act ? lane : 0) * TP);
+        const float* RA = smem + (size_t)(act ? lane : 0) * REG;
+        named_bar_sync(1, NTH);                           // the raw inputs of this trip are in shared memory
+        int state = 0;
+        if (act) state = helper_viterbi_forward<K>(RA, RA + 32 * SA, S, SA, SB, a.log_pi, n, psw);
+        named_bar_sync(2, NTH);                           // ... and may be overwritten (pass 1)
+        if (act) helper_backtrack(psw, (int)a.T, n, state);
+        __syncwarp();
+        const int nact = (int)((a.B - base < wpb) ? a.B - base : wpb);
+        if (a.path_vec16) {
+          const int gpr = (int)(a.T >> 4);                // 16-byte granules per row (T % 16 == 0: TP == T)
+          for (int i = lane; i < nact * gpr; i += 32) {
+            const int sq = i / gpr, g = i - sq * gpr;
+            const uint4 v = *reinterpret_cast<const uint4*>(psi_sm + (size_t)sq * TP + g * 16);
+            __stcs(reinterpret_cast<uint4*>(a.path + (base + sq) * a.T) + g, v);
+          }
+        } else {
+          for (int sq = 0; sq < nact; ++sq)
+            for (int i = lane; i < (int)a.T; i += 32) a.path[(base + sq) * a.T + i] = psi_sm[(size_t)sq * TP + i];
+        }
+        __syncwarp();
+        continue;
+      }
+      if (b >= a.B) {                                     // a posterior warp without a sequence on the last trip
+        named_bar_sync(1, NTH);
+        named_bar_sync(2, NTH);
+        continue;
+      }
+    }
     int64_t Ll;
     bool first = true;                               // row starts at step 0 of its sequence
     if (SEG) {
@@ -236,6 +372,11 @@ __global__ void __launch_bounds__(128) posterior_kernel(Args a) {
       hs::cp_commit();
       hs::cp_wait<0>();
       __syncwarp();
+    }
+    if constexpr (VIT) {
+      const int NTH = (wpb + 1) * 32;
+      named_bar_sync(1, NTH);            // inputs landed: the helper reads them
+      named_bar_sync(2, NTH);            // the helper is through: pass 1 may overwrite them
     }
     // ---- pass 1: P_t in place, chunk product ----------------------------------------
     float M[KK];

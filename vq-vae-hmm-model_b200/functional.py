@@ -495,6 +495,12 @@ def viterbi(log_pi, log_A, log_b, lengths=None):
     return path, score
 
 
+def hmm_decode_select(mode: str = "auto"):
+    """cfg-3 decode: "auto" (Viterbi sweep + one-pass posterior) | "one" (one kernel, inputs read once; measured slower).
+    include/vhmm.h."""
+    check(_lib.lib().vhmm_hmm_decode_select({"auto": 0, "one": 1}[mode]), "vhmm_hmm_decode_select")
+
+
 def hmm_decode(log_pi, log_A, log_b, lengths=None):
     """Viterbi path + posterior gamma + loglik from one forward sweep (cfg 3)."""
     log_pi, log_A, log_b, lengths, B, T, K = _hmm_inputs(log_pi, log_A, log_b, lengths)
