@@ -335,20 +335,20 @@ def run_train_cfg1(torch, V, dev):
 
 
 def run_cfg5(torch, V, Fn, dev, local, pk):
-    """BASELINE.json configs[4]: scaled model K=32, hidden_dim=256 (hidden_dim2=128, u_dim=16), T=1024, ELBO fwd+bwd on the
-    layer-wise path with the tcgen05 layer kernels (csrc/conv_tc5.cuh).  The layer-wise path processes the batch in chunks
-    anyway, so a B=4096 slice of the B=32768 batch measures the same per-sequence rate in a fraction of the time
-    (tools/bench_cfg5.py runs the full batch)."""
-    B, T = 4096, 1024
-    FLOP = 3872256          # SURVEY.md 8(d): algorithmic fwd+bwd FLOP per step of the scaled model
+    """BASELINE.json configs[4]: scaled model K=32, hidden_dim=256 (hidden_dim2=128, u_dim=16), B=32768, T=1024, ELBO fwd+bwd on
+    the layer-wise path with the tcgen05 layer kernels (csrc/conv_tc5.cuh, prior_tc5.cuh) at the FULL batch; the FP32-FFMA layer
+    kernels of round 1 on a B=4096 slice (the layer-wise path processes the batch in chunks of 2048 sequences anyway; at
+    0.7 s per slice the full batch would take a minute)."""
+    T = 1024
+    FLOP = 3872256          # SURVEY.md 8(d): algorithmic fwd+bwd FLOP per step of the scaled (un-folded) model
     torch.manual_seed(0)
     m = V.VAE_HMM(5, 256, 32, 128, u_dim=16).to(dev)
-    g = torch.Generator(device=dev).manual_seed(1)
-    x = torch.randn(B, 5, T, device=dev, generator=g)
-    u = torch.randn(B, 16, T, device=dev, generator=g)
-    L = torch.full((B,), T, dtype=torch.int64)
     res = {}
-    for conv in ("tc5", "ffma"):
+    for conv, B in (("tc5", 32768), ("ffma", 4096)):
+        g = torch.Generator(device=dev).manual_seed(1)
+        x = torch.randn(B, 5, T, device=dev, generator=g)
+        u = torch.randn(B, 16, T, device=dev, generator=g)
+        L = torch.full((B,), T, dtype=torch.int64)
         Fn.conv_select(conv)
         try:
             def step():
@@ -360,16 +360,18 @@ def run_cfg5(torch, V, Fn, dev, local, pk):
         finally:
             Fn.conv_select("auto")
         tf = B * T * FLOP / (ms * 1e-3) / 1e12
-        res[conv] = {"ms_per_step": ms, "iters": it, "sequence_steps_per_s": B * T / (ms * 1e-3), "achieved_tflops": tf,
+        res[conv] = {"B": B, "ms_per_step": ms, "iters": it, "sequence_steps_per_s": B * T / (ms * 1e-3), "achieved_tflops": tf,
                      "frac_of_bf16_sustained": tf / pk["bf16"], "frac_of_3pass_cap": 3 * tf / pk["bf16"],
-                     "projected_s_per_step_at_B32768": ms * 8 / 1e3, "clocks": ck}
-    del x, u, m
-    Fn.release_workspaces()
-    torch.cuda.empty_cache()
-    return {"workload": f"cfg5: VAE_HMM(5,256,K=32,128,u_dim=16) ELBO fwd+bwd, B={B} (slice of 32768) T={T}, layer-wise path",
+                     "s_per_step_at_B32768": ms * (32768 / B) / 1e3, "clocks": ck}
+        del x, u
+        Fn.release_workspaces()
+        torch.cuda.empty_cache()
+    del m
+    return {"workload": f"cfg5: VAE_HMM(5,256,K=32,128,u_dim=16) ELBO fwd+bwd, B=32768 T={T}, layer-wise path "
+                        "(tc5: the full batch; ffma: a B=4096 slice, scaled)",
             "flop_per_step": FLOP, "layer_kernels": res,
-            "note": "tc5 = tcgen05 GEMM-convolutions (2 x fp16 split, fp32 TMEM accumulators: at most 1/3 of the bf16 peak); "
-                    "ffma = the FP32 layer kernels of round 1"}
+            "note": "tc5 = tcgen05 GEMM-convolutions (2 x fp16 split, fp32 TMEM accumulators: at most 1/3 of the bf16 peak), fused "
+                    "transition-prior kernel, decoder.embeddings folded into decoder.conv1; ffma = the FP32 layer kernels of round 1"}
 
 
 def run_decode_sharded(torch, dist, V, Fn, model, dev, local, world, rank, pk):
