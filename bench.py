@@ -470,10 +470,13 @@ def main():
     uh = torch.empty(u.shape, pin_memory=True); uh.copy_(u)
     lh = lengths_cpu.pin_memory()
     beta = 1.0
+    # N > 1: every rank knows the lengths of the WHOLE batch (here: all T), so the global normalisers come from the host and
+    # the step has ONE collective (the all-reduce of [gradients || loss sums]) -- parallel.global_norms_from_lengths
+    glen = {"global_lengths": torch.full((B * world,), T, dtype=torch.int64)} if world > 1 else {}
 
     def step_resident():
         model.zero_grad(set_to_none=True)
-        loss = model.compute_loss(x, u, lengths, beta)
+        loss = model.compute_loss(x, u, lengths, beta, **glen)
         loss.backward()
         return loss
 
@@ -482,7 +485,7 @@ def main():
         # chunk by chunk underneath the kernels (functional.elbo_raw_streamed); lengths are a CPU
         # tensor exactly as the reference's collate_fn produces them
         model.zero_grad(set_to_none=True)
-        loss = model.compute_loss(xh, uh, lh, beta)
+        loss = model.compute_loss(xh, uh, lh, beta, **glen)
         loss.backward()
         return loss.item()            # D2H of the step's result, every step
 
@@ -539,7 +542,7 @@ def main():
 
         def step_strong():
             model.zero_grad(set_to_none=True)
-            ll = model.compute_loss(xs, us, ls, beta)
+            ll = model.compute_loss(xs, us, ls, beta, global_lengths=torch.full((Bs * world,), T, dtype=torch.int64))
             ll.backward()
             return ll
         for _ in range(3):

@@ -75,6 +75,13 @@ def main():
         res[f"loss_{tag}"] = loss.detach().double().cpu().numpy()
         for k, t in m.named_parameters():
             res[f"grad_{tag}:{k}"] = t.grad.detach().double().cpu().numpy()
+    # the same step with the global normalisers computed on the host from the lengths of the whole batch (one collective)
+    m.zero_grad(set_to_none=True)
+    loss = m.compute_loss(x[lo:hi].to(dev), u[lo:hi].to(dev), L[lo:hi], 0.37, global_lengths=L)
+    loss.backward()
+    res["loss_c"] = loss.detach().double().cpu().numpy()
+    for k, t in m.named_parameters():
+        res[f"grad_c:{k}"] = t.grad.detach().double().cpu().numpy()
     l2, flat = m.loss_and_flat_grads(x[lo:hi].to(dev), u[lo:hi].to(dev), L[lo:hi], 0.37)
     res["loss_flat"] = l2.double().cpu().numpy()
     res["flat"] = flat.double().cpu().numpy()

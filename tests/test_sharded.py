@@ -61,6 +61,11 @@ def _check(results, tol):
     ref, _, g = O.loss_and_grads(p64, x.double(), u.double(), L, 4, 0.37)
     flat = torch.cat([g[k].flatten() for k in O.PARAM_ORDER])
     for r in results:
+        # tag "c": global normalisers from the host (compute_loss(..., global_lengths=L)): one collective, same result as "b"
+        assert abs(float(r["loss_c"]) - float(ref)) <= tol * abs(float(ref))
+        for k in O.PARAM_ORDER:
+            assert rel_err(r[f"grad_c:{k}"], g[k]) <= tol, ("c", k)
+            assert np.array_equal(r[f"grad_c:{k}"], r[f"grad_b:{k}"]), ("c == b", k)
         assert abs(float(r["loss_flat"]) - float(ref)) <= tol * abs(float(ref))
         assert rel_err(r["flat"], flat) <= tol
     assert np.array_equal(results[0]["flat"], results[1]["flat"])               # all-reduced: bitwise equal on both ranks

@@ -119,7 +119,9 @@ class VAE_HMM(nn.Module):
     def decode(self, q):
         return Fn.decoder_fwd(self._dims, self._params(), q)
 
-    def compute_loss(self, x, u=None, lengths=None, beta=1.0):
+    def compute_loss(self, x, u=None, lengths=None, beta=1.0, global_lengths=None):
+        """VQ_VAE_HMM_fixed.py:106-137.  `global_lengths` (sharded models only, optional): the lengths of the WHOLE batch over
+        all ranks -- the global normalisers then come from the host and the step has one collective instead of two."""
         B, C, T = x.shape
         if lengths is None:
             raise ValueError('lengths required')
@@ -134,11 +136,12 @@ class VAE_HMM(nn.Module):
         norms = Fn.elbo_norms(lengths_dev, B, C, T)
         if self.shard_group is not None:
             from . import parallel
-            return parallel.sharded_elbo(self, x, u, lengths_dev, float(beta), norms, self.shard_group)
+            ng = None if global_lengths is None else parallel.global_norms_from_lengths(global_lengths, C, T, dev)
+            return parallel.sharded_elbo(self, x, u, lengths_dev, float(beta), norms, self.shard_group, ng)
         loss, _ = Fn.ElboFunction.apply(self._dims, x, u, lengths_dev, float(beta), norms, *self._params())
         return loss
 
-    def loss_and_flat_grads(self, x, u, lengths, beta=1.0):
+    def loss_and_flat_grads(self, x, u, lengths, beta=1.0, global_lengths=None):
         """compute_loss and its gradient without an autograd graph: (loss 0-d fp32 on the device,
         flat fp32 gradient buffer in state_dict order).  This is what vhmm_elbo produces in one call;
         training.FusedAdam consumes the buffer directly."""
@@ -155,7 +158,8 @@ class VAE_HMM(nn.Module):
         with torch.no_grad():
             if self.shard_group is not None:
                 from . import parallel
-                return parallel.sharded_loss_and_flat_grads(self, x, u, lengths_dev, float(beta), norms, self.shard_group)
+                ng = None if global_lengths is None else parallel.global_norms_from_lengths(global_lengths, C, T, dev)
+                return parallel.sharded_loss_and_flat_grads(self, x, u, lengths_dev, float(beta), norms, self.shard_group, ng)
             sums, grads = Fn.elbo_raw(self._dims, self._params(), x, u, lengths_dev, norms, float(beta), True)
             return Fn.loss_from_sums(sums, norms, float(beta)), grads
 

@@ -1,7 +1,8 @@
 """Batch sharding across the GPUs of one box: one process per GPU, sequences
 partitioned, parameters replicated, NO communication inside any kernel, and exactly one NCCL
-all-reduce per step over [flat gradients || loss sums] after a tiny all-reduce of the two
-normalisers.  The sharded loss equals the un-sharded loss of the concatenated batch (the
+all-reduce per step over [flat gradients || loss sums] -- after a tiny all-reduce of the two
+normalisers, unless the caller hands in the lengths of the whole batch (`global_lengths`), from which they are computed on the
+host.  The sharded loss equals the un-sharded loss of the concatenated batch (the
 reference divides the reconstruction term by the GLOBAL valid count, VQ_VAE_HMM_fixed.py:120)."""
 from __future__ import annotations
 
@@ -11,16 +12,23 @@ import torch.distributed as dist
 from . import functional as Fn
 
 
+def _global_norms(x, lengths_dev, norms_local, group, norms_global):
+    """global normalisers: given by the caller (host-side, no collective) or the all-reduced sums of valid steps * C and of
+    the batch sizes over the ranks"""
+    if norms_global is not None:
+        return norms_global.to(device=lengths_dev.device, dtype=torch.float64)
+    C = x.shape[1]
+    nv = lengths_dev.clamp(min=0, max=x.shape[2]).sum().to(torch.float64)
+    cnt = torch.stack([nv * C, norms_local[1]])
+    dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
+    return torch.stack([cnt[0].clamp(min=1.0), cnt[1]])
+
+
 class _ShardedElbo(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, model, x, u, lengths_dev, beta, norms_local, group, *params):
+    def forward(ctx, model, x, u, lengths_dev, beta, norms_local, group, norms_global, *params):
         d = model._dims
-        # global normalisers: sum of valid steps * C and of batch sizes over ranks
-        C = x.shape[1]
-        nv = lengths_dev.clamp(min=0, max=x.shape[2]).sum().to(torch.float64)
-        cnt = torch.stack([nv * C, norms_local[1]])
-        dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
-        norms = torch.stack([cnt[0].clamp(min=1.0), cnt[1]])
+        norms = _global_norms(x, lengths_dev, norms_local, group, norms_global)
         want = any(ctx.needs_input_grad)
         sums, grads = Fn.elbo_raw(d, params, x, u, lengths_dev, norms, beta, want)
         # one all-reduce: grads (fp32) followed by the sums split into hi/lo floats
@@ -44,17 +52,13 @@ class _ShardedElbo(torch.autograd.Function):
             raise Fn.VhmmError("ELBO gradients were not computed")
         flat = flat * gout.to(flat.dtype)
         outs = [flat[ctx.offsets[i]:ctx.offsets[i + 1]].view(s) for i, s in enumerate(ctx.shapes)]
-        return (None, None, None, None, None, None, None, *outs)
+        return (None, None, None, None, None, None, None, None, *outs)
 
 
-def sharded_loss_and_flat_grads(model, x, u, lengths_dev, beta, norms_local, group=None):
+def sharded_loss_and_flat_grads(model, x, u, lengths_dev, beta, norms_local, group=None, norms_global=None):
     """The exchange of _ShardedElbo without autograd: (global loss, GLOBAL flat gradient buffer)."""
     d = model._dims
-    C = x.shape[1]
-    nv = lengths_dev.clamp(min=0, max=x.shape[2]).sum().to(torch.float64)
-    cnt = torch.stack([nv * C, norms_local[1]])
-    dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
-    norms = torch.stack([cnt[0].clamp(min=1.0), cnt[1]])
+    norms = _global_norms(x, lengths_dev, norms_local, group, norms_global)
     sums, grads = Fn.elbo_raw(d, model._params(), x, u, lengths_dev, norms, beta, True)
     hi = sums.to(torch.float32)
     lo = (sums - hi.to(torch.float64)).to(torch.float32)
@@ -65,9 +69,18 @@ def sharded_loss_and_flat_grads(model, x, u, lengths_dev, beta, norms_local, gro
     return Fn.loss_from_sums(gsums, norms, beta), flat[:n]
 
 
-def sharded_elbo(model, x, u, lengths_dev, beta, norms_local, group=None):
+def sharded_elbo(model, x, u, lengths_dev, beta, norms_local, group=None, norms_global=None):
     """Global loss (identical on every rank) whose backward leaves the GLOBAL gradient in .grad."""
-    return _ShardedElbo.apply(model, x, u, lengths_dev, beta, norms_local, group, *model._params())
+    return _ShardedElbo.apply(model, x, u, lengths_dev, beta, norms_local, group, norms_global, *model._params())
+
+
+def global_norms_from_lengths(global_lengths, C, T, device):
+    """The two normalisers of the WHOLE batch (valid steps * C clamped at 1, sequences: VQ_VAE_HMM_fixed.py:120, :131) from
+    the lengths of every rank's sequences, computed on the host -- a caller that shards a batch it holds (shard_batch) knows
+    them before the split, and the step then needs ONE collective instead of two."""
+    gl = torch.as_tensor(global_lengths).to(torch.int64).cpu()
+    nv = int(gl.clamp(min=0, max=T).sum())
+    return torch.tensor([float(max(nv * C, 1)), float(gl.numel())], dtype=torch.float64, device=device)
 
 
 def shard_batch(x, u, lengths, rank, world):
