@@ -416,7 +416,7 @@ static int scan_small(hs::Args a, hs::ScanArgs sa, float* alpha, int64_t B, cuda
   VHMM_CUDA_CHECK(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TL::SMEM));
   k1<<<(unsigned)cdiv(a.nrows, HS_NT), HS_NT, TL::SMEM, st>>>(a, sa);
   VHMM_LAUNCH_CHECK();
-  hs::scan_carry_kernel<K><<<(unsigned)B, 32, 0, st>>>(a, sa);
+  hs::scan_carry_kernel<K><<<(unsigned)B, 32 * hs::CARRY_W, 0, st>>>(a, sa);
   VHMM_LAUNCH_CHECK();
   if (alpha) {
     hs::Args a3 = a;
@@ -462,7 +462,7 @@ int hmm_scan(const float* log_pi, const float* A, const float* Bm, const int64_t
     if (rc) return rc;
     hs::Args c = base_args(log_pi, A, Bm, lengths, B, T, K);
     c.nrows = B * nseg; c.rows_per_seq = (int)nseg; c.CH = (int)SEG_T;
-    DISPATCH_K(K, (hs::scan_carry_kernel<KK><<<(unsigned)B, 32, 0, st>>>(c, sa), rc = 0));
+    DISPATCH_K(K, (hs::scan_carry_kernel<KK><<<(unsigned)B, 32 * hs::CARRY_W, 0, st>>>(c, sa), rc = 0));
     VHMM_LAUNCH_CHECK();
     DISPATCH_K(K, (hs::scan_fixup_kernel<KK><<<(unsigned)B, 32, 0, st>>>(c, sa, nullptr), rc = 0));   // vanished products only
     VHMM_LAUNCH_CHECK();

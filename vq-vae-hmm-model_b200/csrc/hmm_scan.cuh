@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(NT) scan_local_kernel(Args a, ScanArgs sa) {
   const int nch = (max_n + TC - 1) / TC;
   float P[K * K];
 #pragma unroll
-  for (int i = 0; i < K * K; ++i) P[i] = (i / K == i % K) ? 1.f / K : 0.f;  // identity / K (sum 1)
+  for (int i = 0; i < K * K; ++i) P[i] = (i / K == i % K) ? 1.f : 0.f;  // the identity, exactly (chunks beyond the length keep it)
   double scale = 0.0;
   if (nch > 0) {
     stage_slab<K, TC, NT>(smem, a, row_step0, row_n, 0);
@@ -128,50 +128,113 @@ __global__ void __launch_bounds__(NT) scan_local_kernel(Args a, ScanArgs sa) {
   if (r < a.nrows) {
 #pragma unroll
     for (int i = 0; i < K * K; ++i) sa.Pmat[r * K * K + i] = P[i];
-    sa.Pscale[r] = scale + log((double)K);  // undo the 1/K of the initial identity
+    sa.Pscale[r] = scale;
   }
 }
 
-// one warp per sequence.  Lane l owns chunks [l*per, (l+1)*per).
+// P <- (P * M) * 2^-e with e = floor(log2 max entry), *scale += e ln 2.  Power-of-two normalisation is EXACT: identities (the
+// chunks beyond a sequence's length) combine without any rounding, however many threads take part in the scan -- with the
+// sum-normalised form above every combine of two identities leaves ~6e-8 in the log-scale, 2.5e-5 over 256 threads.
 template <int K>
-__global__ void __launch_bounds__(32) scan_carry_kernel(Args a, ScanArgs sa) {
+__device__ __forceinline__ void matmul_pow2(float* P, const float* M, double* scale) {
+  float R[K * K], m = 0.f;
+#pragma unroll
+  for (int i = 0; i < K; ++i)
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+      float acc = 0.f;
+#pragma unroll
+      for (int k = 0; k < K; ++k) acc = fmaf(P[i * K + k], M[k * K + j], acc);
+      R[i * K + j] = acc;
+      m = fmaxf(m, acc);
+    }
+  const unsigned bits = __float_as_uint(m) & 0x7f800000u;     // (a vanished product: bits == 0 -> zeros stay zeros, no NaN)
+  const float sc = __uint_as_float(0x7f000000u - bits);         // 2^-e
+#pragma unroll
+  for (int i = 0; i < K * K; ++i) P[i] = R[i] * sc;
+  *scale += (double)((int)(bits >> 23) - 127) * 0.6931471805599453;
+}
+
+// One CTA of CARRY_W warps per sequence; thread i owns chunks [i*per, (i+1)*per).  (The first build used ONE warp per
+// sequence: at cfg 4 -- 64 sequences, 256 chunk products each -- every lane walked 8 chunks through dependent global loads,
+// and the kernel took as long as the pass that reads the 201 MB of inputs.)
+constexpr int CARRY_W = 8;
+template <int K>
+__global__ void __launch_bounds__(32 * CARRY_W) scan_carry_kernel(Args a, ScanArgs sa) {
+  constexpr int KK = K * K;
+  constexpr int NTH = 32 * CARRY_W;
+  __shared__ float wQ[CARRY_W][KK];
+  __shared__ double wS[CARRY_W];
   const int64_t b = blockIdx.x;
-  const int lane = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int64_t L = a.lengths[b];
+  if (L <= 0) { if (tid == 0) { sa.loglik[b] = 0.f; if (sa.suspect) sa.suspect[b] = 0; } return; }   // (uniform per CTA)
   const int nck = a.rows_per_seq;
-  const int per = (nck + 31) / 32;
-  const int c_lo = min(lane * per, nck), c_hi = min(c_lo + per, nck);
+  const int per = (nck + NTH - 1) / NTH;
+  const int c_lo = min(tid * per, nck), c_hi = min(c_lo + per, nck);
   const int64_t row0 = b * nck;
-  // (1) lane-local product of this lane's chunk matrices
-  float Q[K * K];
+  // (1) thread-local product of this thread's chunk matrices
+  float Q[KK];
 #pragma unroll
-  for (int i = 0; i < K * K; ++i) Q[i] = (i / K == i % K) ? 1.f / K : 0.f;
-  double qs = log((double)K);
+  for (int i = 0; i < KK; ++i) Q[i] = (i / K == i % K) ? 1.f : 0.f;
+  double qs = 0.0;
   for (int c = c_lo; c < c_hi; ++c) {
-    float M[K * K];
+    float M[KK];
 #pragma unroll
-    for (int i = 0; i < K * K; ++i) M[i] = sa.Pmat[(row0 + c) * K * K + i];
-    matmul_norm<K>(Q, M, &qs);
+    for (int i = 0; i < KK; ++i) M[i] = sa.Pmat[(row0 + c) * KK + i];
+    matmul_pow2<K>(Q, M, &qs);
     qs += sa.Pscale[row0 + c];
   }
-  // (2) inclusive Kogge-Stone scan of (Q, qs) across lanes: X_l = Q_0 * ... * Q_l
+  // (2) inclusive Kogge-Stone scan of (Q, qs) across the lanes of a warp: X_l = Q_0 * ... * Q_l
   for (int d = 1; d < 32; d <<= 1) {
-    float Pm[K * K];
+    float Pm[KK];
 #pragma unroll
-    for (int i = 0; i < K * K; ++i) Pm[i] = __shfl_up_sync(0xffffffffu, Q[i], d);
+    for (int i = 0; i < KK; ++i) Pm[i] = __shfl_up_sync(0xffffffffu, Q[i], d);
     const double ps = __shfl_up_sync(0xffffffffu, qs, d);
     if (lane >= d) {
       double sc = ps + qs;
-      matmul_norm<K>(Pm, Q, &sc);   // Pm <- Pm * Q  (earlier factors on the left)
+      matmul_pow2<K>(Pm, Q, &sc);   // Pm <- Pm * Q  (earlier factors on the left)
 #pragma unroll
-      for (int i = 0; i < K * K; ++i) Q[i] = Pm[i];
+      for (int i = 0; i < KK; ++i) Q[i] = Pm[i];
       qs = sc;
     }
   }
-  // exclusive prefix for this lane = inclusive of lane-1
-  float X[K * K];
+  // exclusive prefix inside the warp = inclusive of lane-1
+  float X[KK];
 #pragma unroll
-  for (int i = 0; i < K * K; ++i) X[i] = __shfl_up_sync(0xffffffffu, Q[i], 1);
+  for (int i = 0; i < KK; ++i) X[i] = __shfl_up_sync(0xffffffffu, Q[i], 1);
   double xs = __shfl_up_sync(0xffffffffu, qs, 1);
+  // (2b) totals of the warps -> the product of all EARLIER warps, times the lane's exclusive prefix
+  if (lane == 31) {
+#pragma unroll
+    for (int i = 0; i < KK; ++i) wQ[w][i] = Q[i];
+    wS[w] = qs;
+  }
+  __syncthreads();
+  if (w > 0) {
+    float Wp[KK];
+#pragma unroll
+    for (int i = 0; i < KK; ++i) Wp[i] = wQ[0][i];
+    double ws = wS[0];
+    for (int k = 1; k < w; ++k) {
+      float M[KK];
+#pragma unroll
+      for (int i = 0; i < KK; ++i) M[i] = wQ[k][i];
+      ws += wS[k];
+      matmul_pow2<K>(Wp, M, &ws);
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < KK; ++i) X[i] = Wp[i];
+      xs = ws;
+    } else {
+      ws += xs;
+      matmul_pow2<K>(Wp, X, &ws);
+#pragma unroll
+      for (int i = 0; i < KK; ++i) X[i] = Wp[i];
+      xs = ws;
+    }
+  }
   // alpha_0 (normalised) and its log-scale
   float v[K];
   double ll;
@@ -186,49 +249,47 @@ __global__ void __launch_bounds__(32) scan_carry_kernel(Args a, ScanArgs sa) {
     for (int j = 0; j < K; ++j) v[j] /= cs;
     ll = (double)(logf(cs) + m);
   }
-  const int64_t L = a.lengths[b];
-  if (L <= 0) { if (lane == 0) { sa.loglik[b] = 0.f; if (sa.suspect) sa.suspect[b] = 0; } return; }
   bool vanished = false;
-  if (lane > 0) {
-    float w[K], cs = 0.f;
+  if (tid > 0) {
+    float wv[K], cs = 0.f;
 #pragma unroll
     for (int j = 0; j < K; ++j) {
       float acc = 0.f;
 #pragma unroll
       for (int i = 0; i < K; ++i) acc = fmaf(v[i], X[i * K + j], acc);
-      w[j] = acc; cs += acc;
+      wv[j] = acc; cs += acc;
     }
     vanished |= (c_lo < c_hi) && !(cs >= SCAN_VANISH);
     cs = fmaxf(cs, 1.17549435e-38f);
 #pragma unroll
-    for (int j = 0; j < K; ++j) v[j] = w[j] / cs;
+    for (int j = 0; j < K; ++j) v[j] = wv[j] / cs;
     ll += xs + (double)logf(cs);
   }
-  // (3) walk this lane's chunks: record the incoming vector, then apply the chunk product
+  // (3) walk this thread's chunks: record the incoming vector, then apply the chunk product
   for (int c = c_lo; c < c_hi; ++c) {
 #pragma unroll
     for (int j = 0; j < K; ++j) sa.vin[(row0 + c) * K + j] = v[j];
     sa.ll_in[row0 + c] = ll;
-    float w[K], cs = 0.f;
+    float wv[K], cs = 0.f;
 #pragma unroll
     for (int j = 0; j < K; ++j) {
       float acc = 0.f;
 #pragma unroll
-      for (int i = 0; i < K; ++i) acc = fmaf(v[i], sa.Pmat[(row0 + c) * K * K + i * K + j], acc);
-      w[j] = acc; cs += acc;
+      for (int i = 0; i < K; ++i) acc = fmaf(v[i], sa.Pmat[(row0 + c) * KK + i * K + j], acc);
+      wv[j] = acc; cs += acc;
     }
     // (only chunks that hold a valid transition count: beyond the length the products are identities)
     vanished |= ((int64_t)c * a.CH < L) && !(cs >= SCAN_VANISH);
     cs = fmaxf(cs, 1.17549435e-38f);
 #pragma unroll
-    for (int j = 0; j < K; ++j) v[j] = w[j] / cs;
+    for (int j = 0; j < K; ++j) v[j] = wv[j] / cs;
     ll += sa.Pscale[row0 + c] + (double)logf(cs);
   }
-  const bool any_vanished = __any_sync(0xffffffffu, vanished);
-  if (lane == 0 && sa.suspect) sa.suspect[b] = any_vanished ? 1 : 0;
-  // the lane that owns the last chunk holds the total
-  const int last_lane = (nck - 1) / per;
-  if (lane == last_lane) sa.loglik[b] = (float)ll;
+  const int any_vanished = __syncthreads_or(vanished ? 1 : 0);
+  if (tid == 0 && sa.suspect) sa.suspect[b] = any_vanished ? 1 : 0;
+  // the thread that owns the last chunk holds the total
+  const int last_tid = (nck - 1) / per;
+  if (tid == last_tid) sa.loglik[b] = (float)ll;
 }
 
 
