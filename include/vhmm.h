@@ -292,6 +292,10 @@ int vhmm_hmm_loglik_fused(const vhmm_dims* dims, const vhmm_params* params, cons
                           const float* u, const int64_t* lengths, int64_t B, int64_t T, const float* mu_tab,
                           const float* logvar_tab, float* loglik, void* workspace, size_t workspace_bytes,
                           void* stream);
+/* Conventions of the recursion stages for ragged batches (`lengths`, clamped to [0, T]): steps t >= lengths[b] are padding --
+ * alpha rows carry the last valid row unchanged, gamma / xi rows are zero, path bytes are VHMM_PAD_STATE (0xFF).  A sequence of
+ * length 0 has NO steps: loglik = 0, score = 0, every output row is padding (the CPU oracle's forward() would return
+ * logsumexp(alpha_0) for it, i.e. treats it as length 1; tests compare such rows through max(lengths, 1)). */
 /* B.2: forward recursion.  loglik (B); alpha (B,T,K) log-space or NULL. */
 int vhmm_hmm_forward(const float* log_pi, const float* log_A, const float* log_b,
                      const int64_t* lengths, int64_t B, int64_t T, int64_t K, float* loglik,
