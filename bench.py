@@ -239,7 +239,10 @@ def run_stages(torch, V, Fn, model, dev, local, pk, quick=False):
                               cfg, ms, it, ck, steps, 36, pk, flop_per_step=3328 + 90,
                               note="north-star kernel #2; nothing materialised, HBM traffic = x,u only"))
         ms, it, ck = timed_stage(torch, lambda: model.decode_regimes(x, u, L), local, mn)
-        out.append(stage_line("decode_regimes from raw x,u (front end + Viterbi + gamma)", cfg, ms, it, ck, steps, 36 + 13, pk))
+        out.append(stage_line("decode_regimes from raw x,u (front end + Viterbi + gamma)", cfg, ms, it, ck, steps, 36 + 13, pk,
+                              flop_per_step=3328 + 90,
+                              note="three kernels: the FP32-bound front end (22.6 of the ~29.5 ms, materialises log_A / log_b), the "
+                                   "Viterbi sweep and the one-pass posterior (HBM-bound, see hmm_decode below)"))
         log_pi, log_A, log_b = model.hmm_inputs(x, u)
         del x, u
         inb = 4 * (K * K + K)
