@@ -338,3 +338,30 @@ def test_scaled_config_cfg5_dims_vs_float64_oracle(conv, prior, fold):
         assert rel_err(sd[k].grad.cpu(), g64[k]) <= TOL, (conv, k, rel_err(sd[k].grad.cpu(), g64[k]))
     (mu64, lv64), q64 = O.forward(p64, x.double())
     assert maxabs_rel(q.cpu(), q64) < TOL and maxabs_rel(mu.cpu(), mu64) < TOL and maxabs_rel(lv.cpu(), lv64) < TOL
+
+
+@pytest.mark.parametrize("dims,B,T", [((5, 256, 32, 128, 16, 128), 3, 132),      # fused prior kernel with a 4-step last time tile
+                                      ((5, 256, 32, 128, 16, 128), 2, 1000),     # T % 128 != 0, % 4 == 0
+                                      ((5, 128, 16, 64, 8, 64), 5, 200),         # K = 16: folded decoder.conv1 without the fused prior
+                                      ((6, 192, 32, 64, 4, 128), 4, 260),        # hidden_dim % 64 != 0 (padded weight-gradient blocks)
+                                      ((5, 256, 32, 128, 16, 128), 4, 130)])     # T % 4 != 0: everything falls back to the FFMA layer kernels
+def test_layerwise_tensor_core_path_odd_shapes_vs_float64_oracle(dims, B, T):
+    """The tensor-core layer kernels of the layer-wise path (conv_tc5.cuh, prior_tc5.cuh) away from cfg 5's round numbers: loss and
+    all 18 gradients against the float64 oracle, ragged lengths."""
+    import vhmm_b200 as V
+    from oracle import elbo as O
+    C, H, K, H2, U, TH = dims
+    p = O.init_params(C, H, K, H2, U, TH, seed=B + T)
+    x, u, L = O.synth_batch(B, C, U, T, seed=T, ragged=True, min_len=T // 3)
+    m = V.VAE_HMM(C, H, K, H2, u_dim=U, trans_hidden=TH)
+    m.load_state_dict(p)
+    m = m.cuda()
+    p64 = {k: v.double() for k, v in p.items()}
+    ref, _, g64 = O.loss_and_grads(p64, x.double(), u.double(), L, U, 0.9)
+    loss = m.compute_loss(x.cuda(), u.cuda(), L, 0.9)
+    loss.backward()
+    assert abs(float(loss.detach()) - float(ref)) <= TOL * abs(float(ref)), (float(loss.detach()), float(ref))
+    sd = dict(m.named_parameters())
+    bad = {k: rel_err(sd[k].grad.cpu(), g64[k]) for k in O.PARAM_ORDER if rel_err(sd[k].grad.cpu(), g64[k]) > TOL}
+    assert not bad, bad
+
