@@ -460,6 +460,8 @@ def main():
     if args.scaling == "strong":
         B = B // world
 
+    # several ranks on one box: each pins itself to its GPU's NUMA node before the pinned host buffers are allocated
+    numa_node = V.parallel.bind_to_gpu_numa_node(local) if world > 1 else None
     torch.manual_seed(0)
     model = V.VAE_HMM(MODEL["C"], MODEL["H"], MODEL["K"], MODEL["H2"], u_dim=MODEL["U"]).to(dev)
     if world > 1:
@@ -610,7 +612,7 @@ def main():
                    "l2": f"inputs ({(B * T * 36) / 1e9:.2f} GB/GPU) larger than the 126 MB L2; no flush needed",
                    "elbo_impl": Fn.elbo_active_impl(model._dims), "decoder_kernel": Fn.elbo_decoder_active()},
         "e2e": {"value": e2e_value, "unit": "sequence-steps/s", "ms_per_step": ms_e2e,
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "rank0_numa_node": numa_node},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "loss": loss_val,
     }
     if strong is not None:

@@ -6,6 +6,7 @@ only -- every number is produced by libvhmm.so.  No CPU fallback: non-CUDA tenso
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Dict, Optional, Sequence, Tuple
 
 import torch
@@ -197,6 +198,19 @@ def elbo_norms(lengths_dev: torch.Tensor, B: int, C: int, T: int) -> torch.Tenso
 _stream_state = {}
 
 
+def _stream_growth() -> float:
+    e = os.environ.get("VHMM_STREAM_GROWTH")
+    if e:
+        return max(1.0, float(e))
+    try:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            return 1.4
+    except Exception:
+        pass
+    return 2.0
+
+
 def elbo_raw_streamed(d: Dims, params, x, u, lengths_dev, norms, beta: float, want_grads: bool, chunk: int = 0):
     """vhmm_elbo over a HOST-resident batch (pinned memory recommended): the batch is cut into
     chunks of sequences that are copied host->device on a side stream while the previous chunk
@@ -215,7 +229,12 @@ def elbo_raw_streamed(d: Dims, params, x, u, lengths_dev, norms, beta: float, wa
         chunk = min(chunk, B)
         sizes = [min(chunk, B - b0) for b0 in range(0, B, chunk)]
     else:
-        cap = max(1024, -(-B // 4))
+        # A chunk `growth` times the size of its predecessor arrives in time only if the copy runs `growth` times faster per
+        # byte than the kernels (14 GB/s at cfg 2).  One process per box: PCIe gives ~50 GB/s -> growth 2.  Several ranks
+        # streaming from the same host memory (torch.distributed world > 1) share its bandwidth (8 ranks: 93.6 ms per step
+        # with growth 2 against 85.2 resident) -> growth 1.4, three more chunks.  VHMM_STREAM_GROWTH overrides.
+        growth = _stream_growth()
+        cap = max(1024, -(-B // (4 if growth >= 2.0 else 6)))
         cur = max(1024, -(-B // 32))
         sizes, left, first = [], B, True
         while left > 0:
@@ -225,7 +244,7 @@ def elbo_raw_streamed(d: Dims, params, x, u, lengths_dev, norms, beta: float, wa
             if first:
                 first = False          # the first size is used twice
             else:
-                cur = min(cap, cur * 2)
+                cur = min(cap, int(cur * growth))
     big = max(sizes)
     key = (dev.index, big, C, U, T)
     st = _stream_state.get(key)

@@ -90,6 +90,37 @@ def shard_batch(x, u, lengths, rank, world):
     return x[lo:hi], u[lo:hi], lengths[lo:hi]
 
 
+def bind_to_gpu_numa_node(device_index):
+    """Pin this process to the CPU cores of the NUMA node its GPU hangs off (sysfs), BEFORE the pinned staging buffers are
+    allocated: first-touch then places them on the local node, and the host->device streams of the ranks of one box stop
+    crossing the socket interconnect.  Returns the node, or None when it cannot be determined (single
+    node, containers without sysfs, no permission) -- never raises."""
+    import os
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(device_index).pci_bus_id \
+            if hasattr(torch.cuda.get_device_properties(device_index), "pci_bus_id") else None
+        dom = getattr(torch.cuda.get_device_properties(device_index), "pci_domain_id", 0)
+        dev = getattr(torch.cuda.get_device_properties(device_index), "pci_device_id", 0)
+        if bus is None:
+            return None
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/numa_node"
+        node = int(open(path).read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = os.sched_getaffinity(0) & cpus
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return node
+    except Exception:
+        return None
+
+
 def enable_sharding(model, group=None):
     """After this, model.compute_loss() returns the global loss / leaves global gradients."""
     model.shard_group = group if group is not None else dist.group.WORLD
