@@ -786,13 +786,21 @@ __global__ void finish_kernel(const float* __restrict__ red, const double* __res
                               float* __restrict__ grads) {
   constexpr int C = CF::C, H = CF::H, H2 = CF::H2, K = CF::K, U = CF::U, TH = CF::TH, K2 = CF::K2;
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
-  if (tid == 0) {
+  if (tid < 32) {
+    // loss partials of the CTAs: lane l sums CTAs l, l + 32, ... then a fixed-order tree over the lanes (deterministic).
+    // (One thread walking all CTAs through dependent loads took 40-60 us -- a quarter of the cfg-1 training step.)
     double s[4] = {0, 0, 0, 0}, q0[K];
     for (int k = 0; k < K; ++k) q0[k] = 0.0;
-    for (int c = 0; c < ncta; ++c) {
+    for (int c = tid; c < ncta; c += 32) {
       for (int i = 0; i < 4; ++i) s[i] += loss_part[(int64_t)c * LP + i];
       for (int k = 0; k < K; ++k) q0[k] += loss_part[(int64_t)c * LP + 4 + k];
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      for (int i = 0; i < 4; ++i) s[i] += __shfl_down_sync(0xffffffffu, s[i], o);
+      for (int k = 0; k < K; ++k) q0[k] += __shfl_down_sync(0xffffffffu, q0[k], o);
+    }
+  if (tid == 0) {
     for (int i = 0; i < 4; ++i) sums[i] = s[i];
     if (grads) {   // log_prior through log_softmax (:71): g = aP*q0 - softmax * sum(aP*q0)
       const double aP = -(beta_dev ? *beta_dev : (double)beta) / norms[1];
@@ -801,6 +809,7 @@ __global__ void finish_kernel(const float* __restrict__ red, const double* __res
       constexpr int off_lp = H * C * 3 + H + H2 * H * 3 + H2 + K * H2 + K;   // offset of prior.log_prior
       for (int k = 0; k < K; ++k) grads[off_lp + k] = (float)(aP * q0[k] - exp((double)log_pi[k]) * gs);
     }
+  }
   }
   if (!grads) return;
   const float* rA = red;
