@@ -134,6 +134,7 @@ size_t hmm_param_grads_workspace_bytes(const vhmm_dims& d, int64_t B, int64_t T)
   s += align_up((size_t)Bc * T * (2 * d.TH + K2) * 4, 256) * 1 + 3 * 256;
   s += align_up((size_t)kHmmGradSlices * 2 * d.K * d.C * T * 4, 256);
   s += align_up((size_t)d.K * T * (d.K + 2 * d.C + 3 * (int64_t)d.H + 2 * d.C + 3 * (int64_t)d.H) * 4, 256) + 16 * 256;
+  s += tc5_ctx_bytes(d);          // prepared tensor-core weights (wide models)
   return s + 4096;
 }
 
@@ -155,6 +156,9 @@ int hmm_param_grads(const vhmm_dims& d, const vhmm_params& P, const float* x, co
   float* dp = A.take<float>(nk * 2 * C);
   float* e = A.take<float>(nk * H);  float* g1 = A.take<float>(nk * H);  float* g2 = A.take<float>(nk * H);
   float* dg2 = A.take<float>(nk * H); float* dg1 = A.take<float>(nk * H); float* de = A.take<float>(nk * H);
+  // tensor-core layer kernels where a layer's shape allows (transition_net of a wide model: K*K = 1024 logits)
+  Tc5Ctx ctx;
+  { int rc0 = tc5_ctx_prepare(d, P, true, A, &ctx, st); if (rc0) return rc0; }
   VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "hmm_param_grads: workspace %zu too small (fixed part %zu)", ws_bytes, A.used);
   const size_t left = ws_bytes - A.used > 4 * 256 ? ws_bytes - A.used - 4 * 256 : 0;
   int64_t Bc = (int64_t)(left / ((size_t)T * (2 * TH + K2) * 4));
@@ -173,7 +177,8 @@ int hmm_param_grads(const vhmm_dims& d, const vhmm_params& P, const float* x, co
   for (int64_t b0 = 0; b0 < B; b0 += Bc) {
     const int64_t nb = B - b0 < Bc ? B - b0 : Bc;
     const float* uc = u + b0 * U * T;
-    RC(launch_conv(uc, wview_fwd(P.p[P_T0W], U, 1), P.p[P_T0B], nullptr, a, nb, U, TH, T, 1, EPI_RELU, st));
+    RC(ctx.reset(st));                       // the chunk's buffers are about to be rewritten
+    RC(cconv(&ctx, 0, uc, wview_fwd(P.p[P_T0W], U, 1), P.p[P_T0B], nullptr, a, nb, U, TH, T, 1, EPI_RELU, st));
     {
       dim3 g((unsigned)cdiv(T, 128), (unsigned)K, (unsigned)nb);
       hg_::dM_kernel<<<g, 128, 0, st>>>(xi + b0 * T * K2, log_A + b0 * T * K2, w + b0, dM, K, (int)T);
@@ -181,9 +186,9 @@ int hmm_param_grads(const vhmm_dims& d, const vhmm_params& P, const float* x, co
     }
     // (TH x K*K weight gradient: on the tensor-core kernel where the shape allows -- 128 x 9 at the base dims, the 9 rows padded
     //  to a 64-channel block: 4.7 -> ~1 ms per 16 k sequences x 256 steps; the FFMA kernel otherwise)
-    RC(cwgrad(nullptr, dM, a, grads + off[P_T2W], grads + off[P_T2B], wview_fwd(nullptr, TH, 1), nb, TH, K2, T, 1, scratch, st));
-    RC(launch_conv(dM, wview_dgrad(P.p[P_T2W], TH, 1), nullptr, a, da, nb, K2, TH, T, 1, EPI_MASK, st));
-    RC(launch_wgrad(da, uc, grads + off[P_T0W], grads + off[P_T0B], wview_fwd(nullptr, U, 1), nb, U, TH, T, 1, scratch, st));
+    RC(cwgrad(&ctx, dM, a, grads + off[P_T2W], grads + off[P_T2B], wview_fwd(nullptr, TH, 1), nb, TH, K2, T, 1, scratch, st));
+    RC(cconv(&ctx, 1, dM, wview_dgrad(P.p[P_T2W], TH, 1), nullptr, a, da, nb, K2, TH, T, 1, EPI_MASK, st));
+    RC(cwgrad(&ctx, da, uc, grads + off[P_T0W], grads + off[P_T0B], wview_fwd(nullptr, U, 1), nb, U, TH, T, 1, scratch, st));
   }
   // ---- emission table gradient (reduction over the batch) ----
   {
