@@ -159,3 +159,21 @@ def test_import_sites_without_reference_checkout():
     body.append("assert not bad, bad")
     r = _run_import_lines(body, ROOT)
     assert r.returncode == 0 and "IMPORTS_OK" in r.stdout, r.stderr[-2000:]
+
+
+def test_round2_host_helpers():
+    """host-side helpers added in round 2: global normalisers from the whole batch's lengths (one collective per sharded
+    step), the chunk-growth rule of the streamed ELBO, NUMA binding (never raises)."""
+    import torch
+    from vhmm_b200 import parallel, functional as Fn
+    L = torch.tensor([5, 0, 12, 7, 300, -3])
+    n = parallel.global_norms_from_lengths(L, C=5, T=10, device="cpu")
+    assert n.dtype == torch.float64 and n.tolist() == [float((5 + 0 + 10 + 7 + 10 + 0) * 5), 6.0]
+    assert parallel.global_norms_from_lengths(torch.zeros(3, dtype=torch.int64), 5, 10, "cpu").tolist() == [1.0, 3.0]   # clamp(min=1)
+    assert Fn._stream_growth() == 2.0                       # single process: PCIe outruns the kernels 2x
+    os.environ["VHMM_STREAM_GROWTH"] = "1.25"
+    try:
+        assert Fn._stream_growth() == 1.25
+    finally:
+        del os.environ["VHMM_STREAM_GROWTH"]
+    assert parallel.bind_to_gpu_numa_node(0) in (None, 0, 1, 2, 3, 4, 5, 6, 7)   # no GPU here: None, and no exception
