@@ -258,6 +258,28 @@ def test_long_sequence_scan():
     a_last = torch.logsumexp(alpha[0, T - 1], dim=0)
     assert abs(float(a_last) - ll64[0]) <= 2e-5 * abs(ll64[0])
 
+@pytest.mark.parametrize("K,T", [(3, 1024), (2, 768), (4, 512)])
+def test_scan_all_prefix_alpha_by_segments(K, T):
+    """All-prefix alpha of long sequences: segment products (one-pass kernel) -> carry scan -> the one-pass kernel's alpha
+    sweep per 256-step segment from its incoming vector.  Every row of alpha against the float64 oracle, including the rows
+    carried beyond the length (lengths around the segment boundaries, 1 and 0 -- the latter reads log(1/K))."""
+    import vhmm_b200.functional as Fn
+    B = 12
+    lp, la, lb, _ = rand_hmm(B, T, K, seed=K + T)
+    L = np.array([T, T - 1, 1, 0, 255, 256, 257, 511, 512, T - 255, 300, 2], np.int64)
+    alpha64, ll64 = H.forward(lp, la, lb, np.maximum(L, 1))
+    ll, alpha = Fn.hmm_scan(*dev(lp, la, lb, L), want_alpha=True)
+    a = alpha.cpu().numpy()
+    live = L > 0
+    scale = max(1.0, np.abs(alpha64).max())
+    assert np.abs(a[live] - alpha64[live]).max() <= 2e-5 * scale
+    assert np.allclose(ll.cpu().numpy()[live], ll64[live], rtol=TOL, atol=1e-5)
+    assert np.allclose(a[~live], -np.log(K), atol=1e-6)            # a sequence of length 0 has no steps (include/vhmm.h)
+    # and the same through hmm_forward (thread-per-sequence sweep at this T): identical conventions
+    ll2, alpha2 = Fn.hmm_forward(*dev(lp, la, lb, L), want_alpha=True)
+    assert np.abs(alpha2.cpu().numpy()[live] - a[live]).max() <= 2e-5 * scale
+
+
 @pytest.mark.parametrize("K", [2, 3, 4])
 def test_scan_loglik_by_segment_products(K):
     """Log-likelihood-only scan on long sequences takes the segment-product path (one warp per 256-step segment in

@@ -130,9 +130,9 @@ static bool onepass_fits(int64_t T, int64_t K, const void* A, const void* Bm, co
   const size_t wb = 32 * (size_t)(hw::pitch_odd16(S * (int)(K * K)) + hw::pitch_odd16(S * (int)K)) * 4;
   return wb <= HW_MAX_WARP_BYTES;
 }
-template <int K, bool XI, bool LL_ONLY = false, bool SEG = false>
+template <int K, bool XI, bool LL_ONLY = false, bool SEG = false, bool ALPHA = false>
 static int launch_onepass(hw::Args a, cudaStream_t st) {
-  auto kern = hw::posterior_kernel<K, XI, LL_ONLY, SEG>;
+  auto kern = hw::posterior_kernel<K, XI, LL_ONLY, SEG, false, ALPHA>;
   const size_t wb = 32 * (size_t)(a.SA + a.SB) * 4;
   int wpb = (int)((56 * 1024) / wb);
   wpb = wpb < 1 ? 1 : (wpb > 4 ? 4 : wpb);
@@ -202,6 +202,26 @@ static int hmm_posterior_onepass(const float* log_pi, const float* A, const floa
   return rc;
 }
 
+// all-prefix log alpha by the one-pass kernel: rows of T steps (whole sequences: nseg = 1, vin = null; or segments of longer
+// sequences with the incoming vectors of the carry scan)
+static int hmm_alpha_onepass(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t rows,
+                             int64_t T, int64_t K, int nseg, const float* vin, const double* ll_in, float* loglik,
+                             float* alpha, cudaStream_t st) {
+  hw::Args a{};
+  a.log_pi = log_pi; a.A = A; a.Bm = Bm; a.lengths = lengths; a.B = rows; a.T = T;
+  a.S = 4 * (int)cdiv(T, 128);
+  a.SA = hw::pitch_odd16(a.S * (int)(K * K));
+  a.SB = hw::pitch_odd16(a.S * (int)K);
+  const uint64_t ga = (uint64_t)a.S * K * K / 4, gb = (uint64_t)a.S * K / 4;
+  a.magicA = (unsigned)(((1ull << 32) + ga - 1) / ga);
+  a.magicB = (unsigned)(((1ull << 32) + gb - 1) / gb);
+  a.loglik = loglik; a.gamma = alpha; a.xi = nullptr;
+  a.nseg = nseg; a.vin = vin; a.ll_in = ll_in;
+  int rc = 0;
+  DISPATCH_K(K, (rc = launch_onepass<KK, false, false, false, true>(a, st)));
+  return rc;
+}
+
 static hs::Args base_args(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths,
                           int64_t B, int64_t T, int64_t K) {
   hs::Args a{};
@@ -228,11 +248,20 @@ static bool wide_allowed() {
     else { constexpr int KP = 32; expr; }                            \
   } while (0)
 
+static bool alpha_onepass_enabled() {        // environment VHMM_ALPHA=sweep keeps the thread-per-row sweeps for all-prefix alpha
+  static const bool on = [] { const char* e = getenv("VHMM_ALPHA"); return !(e && e[0] == 's'); }();
+  return on;
+}
+
 int hmm_forward(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B,
                 int64_t T, int64_t K, float* loglik, float* alpha, cudaStream_t st) {
   // log-likelihood only: the time-parallel warp kernel (hmm_warp.cuh) without its sweeps
   if (!alpha && loglik && onepass_allowed() && onepass_fits(T, K, A, Bm, A, nullptr))
     return hmm_posterior_onepass(log_pi, A, Bm, lengths, B, T, K, loglik, nullptr, nullptr, st);
+  // all-prefix alpha of sequences that fit one warp's shared memory: the same kernel with its alpha sweep (inputs read once,
+  // alpha written once, time-parallel over the lanes) instead of the thread-per-sequence sweep below
+  if (alpha && onepass_allowed() && alpha_onepass_enabled() && onepass_fits(T, K, A, Bm, alpha, nullptr))
+    return hmm_alpha_onepass(log_pi, A, Bm, lengths, B, T, K, 1, nullptr, nullptr, loglik, alpha, st);
   if (small_k(K)) {
     hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
     a.loglik = loglik; a.alpha_log = alpha;
@@ -445,8 +474,8 @@ int hmm_scan(const float* log_pi, const float* A, const float* Bm, const int64_t
   // log-likelihood only, T a multiple of the segment length: segment products by the one-pass kernel (one warp per
   // 256-step segment, inputs resident in shared memory, ~HBM speed), then the per-sequence carry scan
   constexpr int64_t SEG_T = 256;
-  if (!alpha && onepass_allowed() && T % SEG_T == 0 && T >= 2 * SEG_T && B * (T / SEG_T) < (1ll << 31) &&
-      onepass_fits(SEG_T, K, A, Bm, nullptr, nullptr)) {
+  if ((!alpha || (alpha_onepass_enabled() && aligned16(alpha))) && onepass_allowed() && T % SEG_T == 0 && T >= 2 * SEG_T &&
+      B * (T / SEG_T) < (1ll << 31) && onepass_fits(SEG_T, K, A, Bm, nullptr, nullptr)) {
     const int64_t nseg = T / SEG_T;
     hw::Args w{};
     w.log_pi = log_pi; w.A = A; w.Bm = Bm; w.lengths = lengths; w.B = B * nseg; w.T = SEG_T;
@@ -464,7 +493,11 @@ int hmm_scan(const float* log_pi, const float* A, const float* Bm, const int64_t
     c.nrows = B * nseg; c.rows_per_seq = (int)nseg; c.CH = (int)SEG_T;
     DISPATCH_K(K, (hs::scan_carry_kernel<KK><<<(unsigned)B, 32 * hs::CARRY_W, 0, st>>>(c, sa), rc = 0));
     VHMM_LAUNCH_CHECK();
-    DISPATCH_K(K, (hs::scan_fixup_kernel<KK><<<(unsigned)B, 32, 0, st>>>(c, sa, nullptr), rc = 0));   // vanished products only
+    if (alpha) {   // all-prefix alpha: the segments again, each from its incoming vector (second and last read of the inputs)
+      rc = hmm_alpha_onepass(log_pi, A, Bm, lengths, B * nseg, SEG_T, K, (int)nseg, sa.vin, sa.ll_in, nullptr, alpha, st);
+      if (rc) return rc;
+    }
+    DISPATCH_K(K, (hs::scan_fixup_kernel<KK><<<(unsigned)B, 32, 0, st>>>(c, sa, alpha), rc = 0));   // vanished products only
     VHMM_LAUNCH_CHECK();
     return rc;
   }

@@ -38,6 +38,9 @@ struct Args {
   float* loglik;           // (B) or null
   float* gamma;            // (B,T,K)
   float* xi;               // (B,T,K,K) or null (XI kernels only)
+  // ALPHA kernels (all-prefix log alpha; rows = segments of T steps as in SEG; `gamma` receives the alpha rows):
+  const float* vin;        // (rows, K) incoming vector of every row (alpha before its first step, any scale), or null: one
+  const double* ll_in;     // (rows) ... and its natural-log scale            row per sequence, alpha_0 formed here
   uint8_t* path;           // (B,T) Viterbi path (VIT kernels only)
   int path_vec16;          // T % 16 == 0 and path 16-byte aligned: the path rows leave as 16-byte stores
   // SEG kernels (long sequences cut into segments of T steps; B = sequences * nseg rows, `lengths` per SEQUENCE):
@@ -276,10 +279,17 @@ __device__ __forceinline__ void helper_backtrack(uint32_t* __restrict__ psw, int
 // SEG (with LL_ONLY): the row is one T-step segment of a longer sequence; instead of a log-likelihood the kernel
 // emits the segment's transfer-matrix product (conventions of hmm_scan.cuh: step 0 of a SEQUENCE is alpha_0, not a
 // transfer) for the per-sequence carry scan -- the time-parallel scan of hmm_scan at one-pass bandwidth.
-template <int K, bool XI, bool LL_ONLY = false, bool SEG = false, bool VIT = false>
+// ALPHA: all-prefix log alpha instead of gamma (SURVEY B.2 with the optional alpha output; the fill pass of vhmm_hmm_scan):
+// rows are T-step segments of a sequence as in SEG, each with an incoming vector (vin, ll_in) from the carry scan -- or whole
+// sequences (nseg = 1, vin == null: alpha_0 is formed here).  Load, pass 1 and the prefix scan as for gamma; pass 2 tracks
+// the exact scale of alpha_hat (powers of two from the rescales + the subtracted emission maxima + ll_in) and writes
+// log alpha_t = log(alpha_hat_t) + scale_t; rows beyond the length repeat the last valid row (the convention of hs::fwd_kernel).
+template <int K, bool XI, bool LL_ONLY = false, bool SEG = false, bool VIT = false, bool ALPHA = false>
 __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
   static_assert(!SEG || LL_ONLY, "segment products come from the log-likelihood-only pass");
   static_assert(!VIT || (!XI && !LL_ONLY && !SEG && K <= 4), "decode: gamma + path, 2-bit back-pointers");
+  static_assert(!ALPHA || (!XI && !LL_ONLY && !SEG && !VIT), "alpha rows replace gamma");
+  constexpr bool ROWS = SEG || ALPHA;                      // rows are segments of sequences
   constexpr int KK = K * K;
   constexpr float LOG2E = 1.4426950408889634f, LN2 = 0.6931471805599453f;
   extern __shared__ __align__(16) float smem[];
@@ -346,11 +356,13 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
     }
     int64_t Ll;
     bool first = true;                               // row starts at step 0 of its sequence
-    if (SEG) {
+    int64_t Lseq = 0;                                // ALPHA: length of the whole sequence
+    if (ROWS) {
       const int64_t seq = b / a.nseg;
       const int seg = (int)(b - seq * a.nseg);
       first = (seg == 0);
-      Ll = a.lengths[seq] - (int64_t)seg * a.T;
+      Lseq = a.lengths[seq];
+      Ll = Lseq - (int64_t)seg * a.T;
     } else {
       Ll = a.lengths[b];
     }
@@ -384,6 +396,7 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
     for (int i = 0; i < KK; ++i) M[i] = (i / K == i % K) ? 1.f : 0.f;
     int ex = 0;
     float mbsum = 0.f;
+    float mb0 = 0.f;                                 // ALPHA without vin: the emission maximum of step 0 (scale of alpha_0)
     float v0[K];
 #pragma unroll
     for (int j = 0; j < K; ++j) v0[j] = 0.f;
@@ -398,11 +411,12 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
         if (g * 4 + s < nv) {
           const float mb = max_of<K>(lb);
           const bool is0 = (t0 + g * 4 + s == 0) && first;
-          if (!(SEG && is0)) mbsum += mb;            // (SEG: the emission of step 0 belongs to alpha_0)
+          if (!(ROWS && is0)) mbsum += mb;           // (SEG / ALPHA: the emission of step 0 belongs to alpha_0)
           float cj[K];
 #pragma unroll
           for (int j = 0; j < K; ++j) cj[j] = (lb[j] - mb) * LOG2E;
           if (is0) {
+            if (ALPHA) mb0 = mb;
 #pragma unroll
             for (int j = 0; j < K; ++j) v0[j] = ex2f(pi[j] + cj[j]);
 #pragma unroll
@@ -452,13 +466,17 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
       continue;
     }
     // ---- scan over the lanes ---------------------------------------------------------
+    if (ALPHA && a.vin) {                            // the row's incoming vector replaces alpha_0
+#pragma unroll
+      for (int j = 0; j < K; ++j) v0[j] = a.vin[b * K + j];
+    }
     float pre[K];
     int pex;
     warp_prefix_scan<K>(M, ex, v0, lane, pre, pex);
     // suffix: only the row sums (suffix product applied to the all-ones vector) are needed:
     // w_l = M_l M_{l+1} ... M_31 1.  Carry (w, Sm) with Sm the segment product.
     float suf[K];
-    if (!LL_ONLY) {
+    if (!LL_ONLY && !ALPHA) {
       float Sm[KK];
 #pragma unroll
       for (int i = 0; i < KK; ++i) Sm[i] = M[i];
@@ -523,7 +541,7 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
     }
     // log-likelihood: lane 31 holds v0 M_0 ... M_31 (scaled by 2^-pex)
     if (a.loglik) {
-      double ms = warp_sum((double)mbsum);
+      double ms = warp_sum((double)mbsum + (double)mb0);   // (mb0: ALPHA keeps the step-0 maximum apart; zero otherwise)
       if (lane == 31) {
         float s = pre[0];
 #pragma unroll
@@ -532,6 +550,99 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
       }
     }
     if (LL_ONLY) { __syncwarp(); continue; }
+    if constexpr (ALPHA) {
+      // ---- all-prefix log alpha ------------------------------------------------------------
+      // start vector of my chunk = prefix of the previous lane, true value fin * 2^E * exp(MB + LLin)
+      float fin[K];
+      int E;
+      {
+        const int pe = __shfl_up_sync(0xffffffffu, pex, 1);
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+          const float f = __shfl_up_sync(0xffffffffu, pre[j], 1);
+          fin[j] = (lane == 0) ? v0[j] : f;
+        }
+        E = (lane == 0) ? 0 : pe;
+        const float sf = pow2_rescale(fmaxf(max_of<K>(fin), 1e-37f), &E);
+#pragma unroll
+        for (int j = 0; j < K; ++j) fin[j] *= sf;
+      }
+      // emission maxima of the steps before my chunk (exclusive scan over the lanes) + the row's incoming log-scale
+      double MB = (double)mbsum;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const double o = __shfl_up_sync(0xffffffffu, MB, d);
+        if (lane >= d) MB += o;
+      }
+      MB -= (double)mbsum;
+      const double LLin = a.vin ? a.ll_in[b] : (double)__shfl_sync(0xffffffffu, mb0, 0);
+      MB += LLin;
+      float last[K];                                   // my last valid row (carried over the padding steps)
+#pragma unroll
+      for (int j = 0; j < K; ++j) last[j] = 0.f;
+      {
+        float al[K];
+#pragma unroll
+        for (int j = 0; j < K; ++j) al[j] = fin[j];
+        double mbr = 0.0;
+        for (int g = 0; g * 4 < nv; ++g) {
+          float Av[4 * KK], Bv[4 * K], Ov[4 * K];
+          lds4<KK>(myA + g * 4 * KK, Av);
+          lds4<K>(myB + g * 4 * K, Bv);
+#pragma unroll
+          for (int s = 0; s < 4; ++s) {
+            const float* P = Av + s * KK;
+            if (g * 4 + s < nv) {
+              const bool is0 = (t0 + g * 4 + s == 0) && first;
+              if (!is0) mbr += (double)max_of<K>(Bv + s * K);
+              float n[K];
+#pragma unroll
+              for (int j = 0; j < K; ++j) {
+                float acc = al[0] * P[j];
+#pragma unroll
+                for (int k = 1; k < K; ++k) acc = fmaf(al[k], P[k * K + j], acc);
+                n[j] = acc;
+              }
+              const float sc = pow2_rescale(fmaxf(max_of<K>(n), 1e-37f), &E);
+              const float off = (float)((double)E * (double)LN2 + MB + mbr);
+#pragma unroll
+              for (int j = 0; j < K; ++j) { al[j] = n[j] * sc; last[j] = logf(al[j]) + off; }
+            }
+#pragma unroll
+            for (int j = 0; j < K; ++j) Ov[s * K + j] = last[j];
+          }
+          sts4<K>(myB + g * 4 * K, Ov);
+        }
+      }
+      // padding steps (t >= L inside the row): the last valid row of the SEQUENCE -- held by the lane of step L-1, or, for a
+      // row that lies entirely beyond the length, the incoming vector itself; a sequence of length 0 reads log(1/K)
+      {
+        const int lv = (L > 0) ? (L - 1) / S : 0;
+        float fill[K];
+#pragma unroll
+        for (int j = 0; j < K; ++j) fill[j] = __shfl_sync(0xffffffffu, last[j], lv);
+        if (L == 0) {
+#pragma unroll
+          for (int j = 0; j < K; ++j)
+            fill[j] = (a.vin && Lseq > 0) ? logf(fmaxf(a.vin[b * K + j], 1e-37f)) + (float)a.ll_in[b] : -logf((float)K);
+        }
+        const int cap = max(0, min(S, T - t0));        // steps of my chunk that exist
+        for (int sidx = nv; sidx < cap; ++sidx)
+#pragma unroll
+          for (int j = 0; j < K; ++j) myB[sidx * K + j] = fill[j];
+      }
+      __syncwarp();
+      {
+        float* gG = a.gamma + b * (int64_t)T * K;
+        for (int g = lane; g < rowGB; g += 32) {
+          const int c = (int)__umulhi((unsigned)g, a.magicB);
+          const float4 v = *reinterpret_cast<const float4*>(regB + c * SB + (g - c * GB) * 4);
+          __stcs(reinterpret_cast<float4*>(gG) + g, v);
+        }
+      }
+      __syncwarp();
+      continue;
+    }
     // start vectors of my chunk
     float fin[K], bin[K];
 #pragma unroll
