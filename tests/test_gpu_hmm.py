@@ -258,6 +258,28 @@ def test_long_sequence_scan():
     a_last = torch.logsumexp(alpha[0, T - 1], dim=0)
     assert abs(float(a_last) - ll64[0]) <= 2e-5 * abs(ll64[0])
 
+@pytest.mark.parametrize("K,T", [(3, 1024), (2, 768), (4, 1280), (3, 65536)])
+def test_posterior_of_long_sequences_by_segments(K, T):
+    """gamma / xi / log-likelihood of sequences longer than one warp's shared memory: segment products -> forward and backward
+    carry scans -> the one-pass posterior kernel on 256-step rows.  Against the float64 oracle, lengths around the segment
+    boundaries, 1 and 0."""
+    import vhmm_b200.functional as Fn
+    B = 12 if T <= 2048 else 3
+    lp, la, lb, _ = rand_hmm(B, T, K, seed=2 * K + T)
+    L = np.array([T, T - 1, 1, 0, 255, 256, 257, 511, 512, T - 255, 300, 2][:B], np.int64)
+    Lo = np.maximum(L, 1)
+    g64, x64, ll64 = H.posteriors(lp, la, lb, Lo)
+    d = dev(lp, la, lb, L)
+    ll, gamma, xi = Fn.hmm_posterior(*d)
+    live = L > 0
+    assert np.allclose(ll.cpu().numpy()[live], ll64[live], rtol=TOL, atol=1e-5)
+    assert np.abs(gamma.cpu().numpy()[live] - g64[live]).max() <= TOL
+    assert np.abs(xi.cpu().numpy()[live] - x64[live]).max() <= TOL
+    assert float(gamma[~torch.from_numpy(live).cuda()].abs().max() if (~live).any() else 0.0) == 0.0     # length 0: all padding
+    ll2, gamma2, _ = Fn.hmm_posterior(*d, want_xi=False)
+    assert torch.equal(gamma2, gamma) and torch.equal(ll2, ll)
+
+
 @pytest.mark.parametrize("K,T", [(3, 1024), (2, 768), (4, 512)])
 def test_scan_all_prefix_alpha_by_segments(K, T):
     """All-prefix alpha of long sequences: segment products (one-pass kernel) -> carry scan -> the one-pass kernel's alpha

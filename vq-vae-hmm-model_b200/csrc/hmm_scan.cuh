@@ -293,6 +293,46 @@ __global__ void __launch_bounds__(32 * CARRY_W) scan_carry_kernel(Args a, ScanAr
 }
 
 
+// Backward carry over the chunk products of a sequence: bin[c] = P_{c+1} P_{c+2} ... P_{last} 1 (normalised to max 1: only
+// the direction matters, gamma and xi are normalised per step) -- beta after the last step of chunk c.  One warp per sequence;
+// the lanes fetch 32 products at a time, then the vector walks through them in reverse order by shuffles.
+template <int K>
+__global__ void __launch_bounds__(32) scan_carry_back_kernel(Args a, ScanArgs sa, float* __restrict__ bin) {
+  constexpr int KK = K * K;
+  const int64_t b = blockIdx.x;
+  const int lane = threadIdx.x;
+  const int nck = a.rows_per_seq;
+  const int64_t row0 = b * nck;
+  float r[K];
+#pragma unroll
+  for (int j = 0; j < K; ++j) r[j] = 1.f;
+  for (int base = ((nck - 1) / 32) * 32; base >= 0; base -= 32) {
+    const int c = base + lane;
+    float M[KK];
+#pragma unroll
+    for (int i = 0; i < KK; ++i) M[i] = (c < nck) ? sa.Pmat[(row0 + c) * KK + i] : ((i / K == i % K) ? 1.f : 0.f);
+    for (int l = 31; l >= 0; --l) {
+      if (base + l >= nck) continue;                     // (uniform)
+      if (lane == l) {
+#pragma unroll
+        for (int j = 0; j < K; ++j) bin[(row0 + c) * K + j] = r[j];
+      }
+      float n[K], m = 0.f;
+#pragma unroll
+      for (int i = 0; i < K; ++i) {
+        float acc = 0.f;
+#pragma unroll
+        for (int j = 0; j < K; ++j) acc = fmaf(__shfl_sync(0xffffffffu, M[i * K + j], l), r[j], acc);
+        n[i] = acc;
+        m = fmaxf(m, acc);
+      }
+      const float inv = 1.f / fmaxf(m, 1.17549435e-38f);
+#pragma unroll
+      for (int i = 0; i < K; ++i) r[i] = n[i] * inv;
+    }
+  }
+}
+
 // Sequences marked by the carry scan: per-step-normalised forward recursion (B.2), one warp per sequence.  The lanes
 // form the transfer matrices of 32 consecutive steps (coalesced loads, exps in parallel), lane 0 applies them in
 // order.  Writes loglik and, if requested, the log-space alpha rows (carried unchanged beyond the length).

@@ -41,6 +41,8 @@ struct Args {
   // ALPHA kernels (all-prefix log alpha; rows = segments of T steps as in SEG; `gamma` receives the alpha rows):
   const float* vin;        // (rows, K) incoming vector of every row (alpha before its first step, any scale), or null: one
   const double* ll_in;     // (rows) ... and its natural-log scale            row per sequence, alpha_0 formed here
+  // gamma / xi kernels on segment rows (nseg > 1: long sequences cut into T-step rows; `vin` as above):
+  const float* bin_in;     // (rows, K) beta after the row's last step (any scale), from the backward carry scan
   uint8_t* path;           // (B,T) Viterbi path (VIT kernels only)
   int path_vec16;          // T % 16 == 0 and path 16-byte aligned: the path rows leave as 16-byte stores
   // SEG kernels (long sequences cut into segments of T steps; B = sequences * nseg rows, `lengths` per SEQUENCE):
@@ -357,7 +359,7 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
     int64_t Ll;
     bool first = true;                               // row starts at step 0 of its sequence
     int64_t Lseq = 0;                                // ALPHA: length of the whole sequence
-    if (ROWS) {
+    if (ROWS || (!LL_ONLY && a.nseg > 1)) {          // (gamma / xi kernels take segment rows at run time)
       const int64_t seq = b / a.nseg;
       const int seg = (int)(b - seq * a.nseg);
       first = (seg == 0);
@@ -466,7 +468,7 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
       continue;
     }
     // ---- scan over the lanes ---------------------------------------------------------
-    if (ALPHA && a.vin) {                            // the row's incoming vector replaces alpha_0
+    if (!LL_ONLY && a.vin) {                         // the row's incoming vector replaces alpha_0
 #pragma unroll
       for (int j = 0; j < K; ++j) v0[j] = a.vin[b * K + j];
     }
@@ -481,11 +483,14 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
 #pragma unroll
       for (int i = 0; i < KK; ++i) Sm[i] = M[i];
       bool has = (lane == 31);
+      float rin[K];                                  // beta after the row's last step: ones, or the backward carry of later rows
+#pragma unroll
+      for (int j = 0; j < K; ++j) rin[j] = a.bin_in ? a.bin_in[b * K + j] : 1.f;
 #pragma unroll
       for (int i = 0; i < K; ++i) {
-        float acc = M[i * K];
+        float acc = M[i * K] * rin[0];
 #pragma unroll
-        for (int j = 1; j < K; ++j) acc += M[i * K + j];
+        for (int j = 1; j < K; ++j) acc = fmaf(M[i * K + j], rin[j], acc);
         suf[i] = acc;
       }
       const int li = lane & 7;
@@ -650,7 +655,7 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
       const float f = __shfl_up_sync(0xffffffffu, pre[j], 1);
       const float w = __shfl_down_sync(0xffffffffu, suf[j], 1);
       fin[j] = (lane == 0) ? v0[j] : f;
-      bin[j] = (lane == 31) ? 1.f : w;
+      bin[j] = (lane == 31) ? (a.bin_in ? a.bin_in[b * K + j] : 1.f) : w;
     }
     {
       const float sf = pow2_rescale(fmaxf(max_of<K>(fin), 1e-37f));
@@ -751,7 +756,7 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
             nb[i] = acc;
           }
           if (XI) {
-            if (t0 + g * 4 + s == 0) {
+            if (t0 + g * 4 + s == 0 && first) {      // (step 0 of the SEQUENCE has no incoming transition)
 #pragma unroll
               for (int i = 0; i < KK; ++i) P[i] = 0.f;
             } else {
