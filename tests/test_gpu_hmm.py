@@ -25,7 +25,8 @@ def dev(*a):
 
 
 CASES = [(2, 1, 4), (3, 1, 1), (3, 7, 9), (3, 50, 33), (3, 256, 130), (3, 257, 5), (3, 1000, 3), (4, 64, 17),
-         (5, 20, 6), (8, 31, 4), (32, 12, 3)]
+         (5, 20, 6), (8, 31, 4), (32, 12, 3),
+         (3, 1024, 5), (4, 768, 3)]     # T % 256 == 0, >= 512: the time-parallel segment paths (posterior, decode, alpha)
 
 
 @pytest.mark.parametrize("K,T,B", CASES)

@@ -469,6 +469,18 @@ int hmm_decode(const float* log_pi, const float* A, const float* Bm, const int64
     if (rc) return rc;
     return hmm_posterior_onepass(log_pi, A, Bm, lengths, B, T, K, loglik, gamma, nullptr, st);
   }
+  if (small_k(K) && onepass_allowed() && T % 256 == 0 && T >= 512 && B * (T / 256) < (1ll << 31) &&
+      onepass_fits(256, K, A, Bm, gamma, nullptr)) {
+    // long sequences: the Viterbi sweep (serial in time by nature: bit-exact max-plus) + the time-parallel posterior
+    hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
+    a.psi = psi; a.path = path; a.vec_path = ((T & 3) == 0) && (((uintptr_t)path & 3) == 0); a.score = nullptr;
+    int rc = 0;
+    DISPATCH_K(K, (rc = launch_fwd_small<KK, false, true>(a, st)));
+    if (rc) return rc;
+    DISPATCH_K(K, (rc = posterior_segments<KK>(log_pi, A, Bm, lengths, B, T, loglik, gamma, nullptr, stash,
+                                               (size_t)B * T * K * sizeof(float), st)));
+    return rc;
+  }
   if (small_k(K)) {
     // one forward sweep computes alpha_hat AND the Viterbi back-pointers from the same staged
     // inputs; the backward sweep then produces gamma.
