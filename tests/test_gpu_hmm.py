@@ -259,6 +259,28 @@ def test_long_sequence_scan():
     a_last = torch.logsumexp(alpha[0, T - 1], dim=0)
     assert abs(float(a_last) - ll64[0]) <= 2e-5 * abs(ll64[0])
 
+def test_model_loglik_of_few_long_sequences_takes_the_scan():
+    """model.hmm_log_likelihood on few long sequences (front end + time-parallel scan instead of the warp-per-sequence fused
+    kernel) equals the fused kernel and the forward recursion on the materialised inputs."""
+    import vhmm_b200 as V
+    from vhmm_b200 import functional as Fn
+    from oracle import elbo as O
+    p = O.init_params(5, 64, 3, 32, 4, 128, seed=6)
+    m = V.VAE_HMM(5, 64, 3, 32, u_dim=4)
+    m.load_state_dict(p)
+    m = m.cuda().eval()
+    x, u, L = O.synth_batch(3, 5, 4, 2048, seed=8, ragged=True, min_len=700)
+    x, u, Ld = x.cuda(), u.cuda(), L.cuda()
+    with torch.no_grad():
+        ll = m.hmm_log_likelihood(x, u, Ld)                                    # few_long -> hmm_inputs + hmm_scan
+        log_pi, log_A, log_b = m.hmm_inputs(x, u)
+        ll_fwd = Fn.hmm_forward(log_pi, log_A, log_b, Ld)
+        mu_tab, lv_tab = Fn.emission_table(m._dims, m._params(), 2048, x.device)
+        ll_fused = Fn.hmm_loglik_fused(m._dims, m._params(), log_pi, x, u, Ld, mu_tab, lv_tab)
+    assert torch.allclose(ll, ll_fwd, rtol=2e-6, atol=1e-3)
+    assert ll_fused is not None and torch.allclose(ll, ll_fused, rtol=2e-6, atol=1e-3)
+
+
 @pytest.mark.parametrize("K,T", [(3, 1024), (2, 768), (4, 1280), (3, 65536)])
 def test_posterior_of_long_sequences_by_segments(K, T):
     """gamma / xi / log-likelihood of sequences longer than one warp's shared memory: segment products -> forward and backward

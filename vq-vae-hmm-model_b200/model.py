@@ -219,13 +219,19 @@ class VAE_HMM(nn.Module):
             if lengths is not None:
                 lengths = lengths.to(device=x.device, dtype=torch.int64)
             return Fn.HmmParamLogLikFunction.apply(self._dims, x, u, lengths, *self._params())
-        if x.numel() > 0:
+        # FEW LONG sequences: the fused kernel walks a sequence with one warp, serially in time -- below ~2,400 sequences it
+        # cannot fill the machine, and at T = 65536 a warp needs milliseconds.  Front end (parallel over every (b, t)) + the
+        # time-parallel scan instead (B = 64, T = 65536: tools/loglik_long_time.py).
+        few_long = x.numel() > 0 and x.shape[2] >= 1024 and x.shape[0] < 2368
+        if x.numel() > 0 and not few_long:
             mu_tab, lv_tab = Fn.emission_table(self._dims, self._params(), x.shape[2], x.device)
             log_pi = torch.log_softmax(self.prior.log_prior.detach().float(), dim=0)
             ll = Fn.hmm_loglik_fused(self._dims, self._params(), log_pi, x, u, lengths, mu_tab, lv_tab)
             if ll is not None:
                 return ll
         log_pi, log_A, log_b = self.hmm_inputs(x, u)
+        if few_long:
+            return Fn.hmm_scan(log_pi, log_A, log_b, lengths)
         return Fn.hmm_forward(log_pi, log_A, log_b, lengths)
 
     def hmm_nll(self, x, u, lengths=None):
