@@ -266,7 +266,12 @@ def run_stages(torch, V, Fn, model, dev, local, pk, quick=False):
         out.append(stage_line("hmm_scan (log-likelihood)", cfg, ms, it, ck, B * T, inb, pk,
                               note="201 MB of inputs fit the 126 MB L2 only partly; repeated launches re-read from HBM"))
         ms, it, ck = timed_stage(torch, lambda: Fn.hmm_scan(log_pi, log_A, log_b, L, want_alpha=True), local, mn, max_iters=2000)
-        out.append(stage_line("hmm_scan (all-prefix alpha)", cfg, ms, it, ck, B * T, inb + 4 * K, pk))
+        out.append(stage_line("hmm_scan (all-prefix alpha)", cfg, ms, it, ck, B * T, inb + 4 * K, pk,
+                              note="segment products + carry scan + alpha sweep per segment: the inputs are read twice"))
+        ms, it, ck = timed_stage(torch, lambda: Fn.hmm_posterior(log_pi, log_A, log_b, L, want_xi=False), local, mn, max_iters=2000)
+        out.append(stage_line("hmm_posterior (gamma) of long sequences", cfg, ms, it, ck, B * T, inb + 4 * K, pk,
+                              note="time-parallel: segment products, forward + backward carry scans, one-pass posterior kernel on "
+                                   "256-step rows (two reads of the inputs); the thread-per-sequence sweeps took 94 ms here"))
         del log_A, log_b
         # ---- cfg 5 recursion shapes: K = 32 (warp-per-sequence kernels), T = 1024
         B, T, K = 8192, 1024, 32
