@@ -327,7 +327,8 @@ int vhmm_hmm_param_grads(const vhmm_dims* dims, const vhmm_params* params, const
  *   VHMM_POSTERIOR_SWEEP    forward sweep (alpha_hat stash) + backward sweep, one thread per
  *                           sequence: any T, 132 B/step of traffic.
  * AUTO (default) = ONEPASS when it applies; environment VHMM_POSTERIOR=sweep overrides AUTO.
- * Longer sequences with T % 256 == 0 (AUTO, vhmm_hmm_posterior): time-parallel as well -- 256-step segments: segment
+ * Longer sequences (T >= 512, T*K % 4 == 0; AUTO, vhmm_hmm_posterior / _decode / _scan): time-parallel as well -- 256-step segments
+ * (the last one of a sequence may be shorter): segment
  * products, a forward and a backward carry scan per sequence (incoming alpha / outgoing beta of every segment, the
  * log-likelihood), then the ONEPASS kernel on the segment rows; the inputs cross HBM twice.  (The sweep kernels run one
  * thread per sequence: 94 ms at B = 64, T = 65536 against 0.16 ms.) */

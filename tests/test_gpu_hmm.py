@@ -281,7 +281,7 @@ def test_model_loglik_of_few_long_sequences_takes_the_scan():
     assert ll_fused is not None and torch.allclose(ll, ll_fused, rtol=2e-6, atol=1e-3)
 
 
-@pytest.mark.parametrize("K,T", [(3, 1024), (2, 768), (4, 1280), (3, 65536)])
+@pytest.mark.parametrize("K,T", [(3, 1024), (2, 768), (4, 1280), (3, 65536), (3, 1000), (4, 777), (2, 1002), (3, 516)])
 def test_posterior_of_long_sequences_by_segments(K, T):
     """gamma / xi / log-likelihood of sequences longer than one warp's shared memory: segment products -> forward and backward
     carry scans -> the one-pass posterior kernel on 256-step rows.  Against the float64 oracle, lengths around the segment
@@ -303,7 +303,7 @@ def test_posterior_of_long_sequences_by_segments(K, T):
     assert torch.equal(gamma2, gamma) and torch.equal(ll2, ll)
 
 
-@pytest.mark.parametrize("K,T", [(3, 1024), (2, 768), (4, 512)])
+@pytest.mark.parametrize("K,T", [(3, 1024), (2, 768), (4, 512), (3, 1000), (4, 777), (2, 514)])
 def test_scan_all_prefix_alpha_by_segments(K, T):
     """All-prefix alpha of long sequences: segment products (one-pass kernel) -> carry scan -> the one-pass kernel's alpha
     sweep per 256-step segment from its incoming vector.  Every row of alpha against the float64 oracle, including the rows

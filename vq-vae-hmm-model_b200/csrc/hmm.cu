@@ -206,7 +206,7 @@ static int hmm_posterior_onepass(const float* log_pi, const float* A, const floa
 // sequences with the incoming vectors of the carry scan)
 static int hmm_alpha_onepass(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t rows,
                              int64_t T, int64_t K, int nseg, const float* vin, const double* ll_in, float* loglik,
-                             float* alpha, cudaStream_t st) {
+                             float* alpha, cudaStream_t st, int64_t seqT = 0) {
   hw::Args a{};
   a.log_pi = log_pi; a.A = A; a.Bm = Bm; a.lengths = lengths; a.B = rows; a.T = T;
   a.S = 4 * (int)cdiv(T, 128);
@@ -216,7 +216,7 @@ static int hmm_alpha_onepass(const float* log_pi, const float* A, const float* B
   a.magicA = (unsigned)(((1ull << 32) + ga - 1) / ga);
   a.magicB = (unsigned)(((1ull << 32) + gb - 1) / gb);
   a.loglik = loglik; a.gamma = alpha; a.xi = nullptr;
-  a.nseg = nseg; a.vin = vin; a.ll_in = ll_in;
+  a.nseg = nseg; a.vin = vin; a.ll_in = ll_in; a.seqT = seqT;
   int rc = 0;
   DISPATCH_K(K, (rc = launch_onepass<KK, false, false, false, true>(a, st)));
   return rc;
@@ -293,7 +293,7 @@ template <int K>
 static int posterior_segments(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B, int64_t T,
                               float* loglik, float* gamma, float* xi, void* ws, size_t ws_bytes, cudaStream_t st) {
   constexpr int64_t SEG_T = 256;
-  const int64_t nseg = T / SEG_T, rows = B * nseg;
+  const int64_t nseg = cdiv(T, SEG_T), rows = B * nseg;     // (the last row of a sequence may be shorter: Args.seqT)
   Arena ar(ws, ws_bytes);
   hs::ScanArgs sa{};
   sa.Pmat = ar.take<float>((size_t)rows * K * K);
@@ -313,7 +313,7 @@ static int posterior_segments(const float* log_pi, const float* A, const float* 
   const uint64_t ga = (uint64_t)w.S * K * K / 4, gb = (uint64_t)w.S * K / 4;
   w.magicA = (unsigned)(((1ull << 32) + ga - 1) / ga);
   w.magicB = (unsigned)(((1ull << 32) + gb - 1) / gb);
-  w.nseg = (int)nseg; w.Pmat = sa.Pmat; w.Pscale = sa.Pscale;
+  w.nseg = (int)nseg; w.seqT = T; w.Pmat = sa.Pmat; w.Pscale = sa.Pscale;
   int rc = launch_onepass<K, false, true, true>(w, st);                 // segment products
   if (rc) return rc;
   hs::Args c = base_args(log_pi, A, Bm, lengths, B, T, K);
@@ -335,8 +335,8 @@ int hmm_posterior(const float* log_pi, const float* A, const float* Bm, const in
                   cudaStream_t st) {
   if (onepass_allowed() && onepass_fits(T, K, A, Bm, gamma, xi))
     return hmm_posterior_onepass(log_pi, A, Bm, lengths, B, T, K, loglik, gamma, xi, st);
-  if (onepass_allowed() && T % 256 == 0 && T >= 512 && B * (T / 256) < (1ll << 31) && onepass_fits(256, K, A, Bm, gamma, xi) &&
-      ws_bytes >= (size_t)B * (T / 256) * (K * K + 2 * K + 6) * 4 + (size_t)B * 8 + 4096) {
+  if (onepass_allowed() && T >= 512 && ((T * K) & 3) == 0 && B * cdiv(T, 256) < (1ll << 31) && onepass_fits(256, K, A, Bm, gamma, xi) &&
+      ws_bytes >= (size_t)B * cdiv(T, 256) * (K * K + 2 * K + 6) * 4 + (size_t)B * 8 + 4096) {
     int rc = 0;
     DISPATCH_K(K, (rc = posterior_segments<KK>(log_pi, A, Bm, lengths, B, T, loglik, gamma, xi, ws, ws_bytes, st)));
     return rc;
@@ -469,7 +469,7 @@ int hmm_decode(const float* log_pi, const float* A, const float* Bm, const int64
     if (rc) return rc;
     return hmm_posterior_onepass(log_pi, A, Bm, lengths, B, T, K, loglik, gamma, nullptr, st);
   }
-  if (small_k(K) && onepass_allowed() && T % 256 == 0 && T >= 512 && B * (T / 256) < (1ll << 31) &&
+  if (small_k(K) && onepass_allowed() && T >= 512 && ((T * K) & 3) == 0 && B * cdiv(T, 256) < (1ll << 31) &&
       onepass_fits(256, K, A, Bm, gamma, nullptr)) {
     // long sequences: the Viterbi sweep (serial in time by nature: bit-exact max-plus) + the time-parallel posterior
     hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
@@ -537,9 +537,9 @@ int hmm_scan(const float* log_pi, const float* A, const float* Bm, const int64_t
   // log-likelihood only, T a multiple of the segment length: segment products by the one-pass kernel (one warp per
   // 256-step segment, inputs resident in shared memory, ~HBM speed), then the per-sequence carry scan
   constexpr int64_t SEG_T = 256;
-  if ((!alpha || (alpha_onepass_enabled() && aligned16(alpha))) && onepass_allowed() && T % SEG_T == 0 && T >= 2 * SEG_T &&
-      B * (T / SEG_T) < (1ll << 31) && onepass_fits(SEG_T, K, A, Bm, nullptr, nullptr)) {
-    const int64_t nseg = T / SEG_T;
+  if ((!alpha || (alpha_onepass_enabled() && aligned16(alpha))) && onepass_allowed() && T >= 2 * SEG_T && ((T * K) & 3) == 0 &&
+      B * cdiv(T, SEG_T) < (1ll << 31) && cdiv(T, SEG_T) <= nck && onepass_fits(SEG_T, K, A, Bm, nullptr, nullptr)) {
+    const int64_t nseg = cdiv(T, SEG_T);
     hw::Args w{};
     w.log_pi = log_pi; w.A = A; w.Bm = Bm; w.lengths = lengths; w.B = B * nseg; w.T = SEG_T;
     w.S = 4 * (int)cdiv(SEG_T, 128);
@@ -548,7 +548,7 @@ int hmm_scan(const float* log_pi, const float* A, const float* Bm, const int64_t
     const uint64_t ga = (uint64_t)w.S * K * K / 4, gb = (uint64_t)w.S * K / 4;
     w.magicA = (unsigned)(((1ull << 32) + ga - 1) / ga);
     w.magicB = (unsigned)(((1ull << 32) + gb - 1) / gb);
-    w.nseg = (int)nseg; w.Pmat = sa.Pmat; w.Pscale = sa.Pscale;
+    w.nseg = (int)nseg; w.seqT = T; w.Pmat = sa.Pmat; w.Pscale = sa.Pscale;
     int rc = 0;
     DISPATCH_K(K, (rc = launch_onepass<KK, false, true, true>(w, st)));
     if (rc) return rc;
@@ -557,7 +557,7 @@ int hmm_scan(const float* log_pi, const float* A, const float* Bm, const int64_t
     DISPATCH_K(K, (hs::scan_carry_kernel<KK><<<(unsigned)B, 32 * hs::CARRY_W, 0, st>>>(c, sa), rc = 0));
     VHMM_LAUNCH_CHECK();
     if (alpha) {   // all-prefix alpha: the segments again, each from its incoming vector (second and last read of the inputs)
-      rc = hmm_alpha_onepass(log_pi, A, Bm, lengths, B * nseg, SEG_T, K, (int)nseg, sa.vin, sa.ll_in, nullptr, alpha, st);
+      rc = hmm_alpha_onepass(log_pi, A, Bm, lengths, B * nseg, SEG_T, K, (int)nseg, sa.vin, sa.ll_in, nullptr, alpha, st, T);
       if (rc) return rc;
     }
     DISPATCH_K(K, (hs::scan_fixup_kernel<KK><<<(unsigned)B, 32, 0, st>>>(c, sa, alpha), rc = 0));   // vanished products only

@@ -43,6 +43,7 @@ struct Args {
   const double* ll_in;     // (rows) ... and its natural-log scale            row per sequence, alpha_0 formed here
   // gamma / xi kernels on segment rows (nseg > 1: long sequences cut into T-step rows; `vin` as above):
   const float* bin_in;     // (rows, K) beta after the row's last step (any scale), from the backward carry scan
+  int64_t seqT;            // segment rows: steps per SEQUENCE in memory (0: nseg * T); the last row of a sequence may be shorter
   uint8_t* path;           // (B,T) Viterbi path (VIT kernels only)
   int path_vec16;          // T % 16 == 0 and path 16-byte aligned: the path rows leave as 16-byte stores
   // SEG kernels (long sequences cut into segments of T steps; B = sequences * nseg rows, `lengths` per SEQUENCE):
@@ -306,7 +307,6 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
   const int T = (int)a.T;
   const int t0 = lane * S;
   const int GA = S * KK / 4, GB = S * K / 4;   // 16-byte granules per chunk
-  const int rowGA = T * KK / 4, rowGB = T * K / 4;
   float pi[K];
 #pragma unroll
   for (int j = 0; j < K; ++j) pi[j] = a.log_pi[j] * LOG2E;
@@ -359,21 +359,28 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
     int64_t Ll;
     bool first = true;                               // row starts at step 0 of its sequence
     int64_t Lseq = 0;                                // ALPHA: length of the whole sequence
+    int64_t step0 = b * (int64_t)T;                  // first step of the row in the (.., T_total, ..) tensors
+    int capT = T;                                    // steps of the row that exist in memory
     if (ROWS || (!LL_ONLY && a.nseg > 1)) {          // (gamma / xi kernels take segment rows at run time)
       const int64_t seq = b / a.nseg;
       const int seg = (int)(b - seq * a.nseg);
       first = (seg == 0);
       Lseq = a.lengths[seq];
       Ll = Lseq - (int64_t)seg * a.T;
+      const int64_t ST = a.seqT ? a.seqT : (int64_t)a.nseg * a.T;
+      step0 = seq * ST + (int64_t)seg * a.T;
+      const int64_t left = ST - (int64_t)seg * a.T;
+      capT = (int)(left < a.T ? left : a.T);
     } else {
       Ll = a.lengths[b];
     }
-    const int L = (int)(Ll < 0 ? 0 : (Ll > a.T ? a.T : Ll));
+    const int L = (int)(Ll < 0 ? 0 : (Ll > capT ? capT : Ll));
+    const int rowGA = capT * KK / 4, rowGB = capT * K / 4;   // 16-byte granules of the row's output (capT * K % 4 == 0)
     const int nv = max(0, min(S, L - t0));          // valid steps of my chunk
     // ---- load: granules that hold a valid step --------------------------------------
     {
-      const float* gA = a.A + b * (int64_t)T * KK;
-      const float* gB = a.Bm + b * (int64_t)T * K;
+      const float* gA = a.A + step0 * KK;
+      const float* gB = a.Bm + step0 * K;
       const int nA = (L * KK + 3) >> 2, nB = (L * K + 3) >> 2;
       for (int g = lane; g < nA; g += 32) {
         const int c = (int)__umulhi((unsigned)g, a.magicA);
@@ -631,14 +638,14 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
           for (int j = 0; j < K; ++j)
             fill[j] = (a.vin && Lseq > 0) ? logf(fmaxf(a.vin[b * K + j], 1e-37f)) + (float)a.ll_in[b] : -logf((float)K);
         }
-        const int cap = max(0, min(S, T - t0));        // steps of my chunk that exist
+        const int cap = max(0, min(S, capT - t0));     // steps of my chunk that exist
         for (int sidx = nv; sidx < cap; ++sidx)
 #pragma unroll
           for (int j = 0; j < K; ++j) myB[sidx * K + j] = fill[j];
       }
       __syncwarp();
       {
-        float* gG = a.gamma + b * (int64_t)T * K;
+        float* gG = a.gamma + step0 * K;
         for (int g = lane; g < rowGB; g += 32) {
           const int c = (int)__umulhi((unsigned)g, a.magicB);
           const float4 v = *reinterpret_cast<const float4*>(regB + c * SB + (g - c * GB) * 4);
@@ -698,7 +705,7 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
       float bh[K];
 #pragma unroll
       for (int j = 0; j < K; ++j) bh[j] = bin[j];
-      const int cap = max(0, min(S, T - t0));        // steps of my chunk that exist
+      const int cap = max(0, min(S, capT - t0));     // steps of my chunk that exist
       for (int g = (cap + 3) / 4 - 1; g >= 0; --g) {
         float Gv[4 * K];
         if (g * 4 >= nv) {
@@ -785,14 +792,14 @@ __global__ void __launch_bounds__(VIT ? 288 : 128) posterior_kernel(Args a) {
     __syncwarp();
     // ---- store: coalesced rows ------------------------------------------------------
     {
-      float* gG = a.gamma + b * (int64_t)T * K;
+      float* gG = a.gamma + step0 * K;
       for (int g = lane; g < rowGB; g += 32) {
         const int c = (int)__umulhi((unsigned)g, a.magicB);
         const float4 v = *reinterpret_cast<const float4*>(regB + c * SB + (g - c * GB) * 4);
         __stcs(reinterpret_cast<float4*>(gG) + g, v);
       }
       if (XI) {
-        float* gX = a.xi + b * (int64_t)T * KK;
+        float* gX = a.xi + step0 * KK;
         for (int g = lane; g < rowGA; g += 32) {
           const int c = (int)__umulhi((unsigned)g, a.magicA);
           const float4 v = *reinterpret_cast<const float4*>(regA + c * SA + (g - c * GA) * 4);
