@@ -477,6 +477,9 @@ def _hmm_inputs(log_pi, log_A, log_b, lengths):
 
 
 def hmm_forward(log_pi, log_A, log_b, lengths=None, want_alpha=False):
+    """vhmm_hmm_forward: the forward recursion as ONE pass (no workspace).  Sequences up to ~580 steps (K <= 4) run
+    time-parallel on one warp each; longer ones one thread per sequence -- for FEW LONG sequences use ``hmm_scan`` (same
+    results, time-parallel over 256-step segments; model.hmm_log_likelihood picks it by itself)."""
     log_pi, log_A, log_b, lengths, B, T, K = _hmm_inputs(log_pi, log_A, log_b, lengths)
     ll = torch.empty(B, device=log_b.device, dtype=torch.float32)
     alpha = torch.empty(B, T, K, device=log_b.device, dtype=torch.float32) if want_alpha else None
