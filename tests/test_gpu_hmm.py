@@ -251,7 +251,7 @@ def test_long_sequence_scan():
     lb = torch.randn(B, T, K, device="cuda", generator=g)
     lp = torch.log_softmax(torch.randn(K, device="cuda", generator=g), dim=-1)
     L = torch.tensor([T, T - 1, 40000, 129, 128, 1, 65000, 2], device="cuda")
-    ll_seq = Fn.hmm_forward(lp, la, lb, L)
+    ll_seq = Fn.hmm_forward(lp, la, lb, L, time_parallel=False)
     ll_scan, alpha = Fn.hmm_scan(lp, la, lb, L, want_alpha=True)
     assert torch.allclose(ll_seq, ll_scan, rtol=1e-6, atol=1e-2)
     _, ll64 = H.forward(lp.cpu().numpy(), la[:1].cpu().numpy(), lb[:1].cpu().numpy(), np.array([T]))
@@ -274,7 +274,7 @@ def test_model_loglik_of_few_long_sequences_takes_the_scan():
     with torch.no_grad():
         ll = m.hmm_log_likelihood(x, u, Ld)                                    # few_long -> hmm_inputs + hmm_scan
         log_pi, log_A, log_b = m.hmm_inputs(x, u)
-        ll_fwd = Fn.hmm_forward(log_pi, log_A, log_b, Ld)
+        ll_fwd = Fn.hmm_forward(log_pi, log_A, log_b, Ld, time_parallel=False)
         mu_tab, lv_tab = Fn.emission_table(m._dims, m._params(), 2048, x.device)
         ll_fused = Fn.hmm_loglik_fused(m._dims, m._params(), log_pi, x, u, Ld, mu_tab, lv_tab)
     assert torch.allclose(ll, ll_fwd, rtol=2e-6, atol=1e-3)
@@ -321,8 +321,11 @@ def test_scan_all_prefix_alpha_by_segments(K, T):
     assert np.allclose(ll.cpu().numpy()[live], ll64[live], rtol=TOL, atol=1e-5)
     assert np.allclose(a[~live], -np.log(K), atol=1e-6)            # a sequence of length 0 has no steps (include/vhmm.h)
     # and the same through hmm_forward (thread-per-sequence sweep at this T): identical conventions
-    ll2, alpha2 = Fn.hmm_forward(*dev(lp, la, lb, L), want_alpha=True)
+    ll2, alpha2 = Fn.hmm_forward(*dev(lp, la, lb, L), want_alpha=True, time_parallel=False)
     assert np.abs(alpha2.cpu().numpy()[live] - a[live]).max() <= 2e-5 * scale
+    ll3, alpha3 = Fn.hmm_forward(*dev(lp, la, lb, L), want_alpha=True)      # few long sequences: dispatched to the scan
+    if T >= 1024:
+        assert np.array_equal(alpha3.cpu().numpy(), a) and np.array_equal(ll3.cpu().numpy(), ll.cpu().numpy())
 
 
 @pytest.mark.parametrize("K", [2, 3, 4])
@@ -338,7 +341,7 @@ def test_scan_loglik_by_segment_products(K):
         lp = torch.log_softmax(torch.randn(K, device="cuda", generator=g), dim=-1)
         Ls = [T, T - 1, 1, 0, 255, 256, 257, 511, 512, 513, 700, 2][:B]
         L = torch.tensor(Ls, device="cuda")
-        ll_seq = Fn.hmm_forward(lp, la, lb, L)
+        ll_seq = Fn.hmm_forward(lp, la, lb, L, time_parallel=False)
         ll_seg = Fn.hmm_scan(lp, la, lb, L)
         ll_chk, _ = Fn.hmm_scan(lp, la, lb, L, want_alpha=True)
         assert torch.allclose(ll_seg, ll_seq, rtol=2e-6, atol=1e-3), (ll_seg, ll_seq)
@@ -513,7 +516,7 @@ def test_scan_with_structural_zeros_and_sticky_chains():
         _, ll64 = H.forward(lp, la, lb, L)
         assert np.isfinite(ll64).all()
         d = dev(lp, la, lb, L)
-        ll_seq = Fn.hmm_forward(*d).cpu().numpy()
+        ll_seq = Fn.hmm_forward(*d, time_parallel=False).cpu().numpy()
         ll_scan = Fn.hmm_scan(*d).cpu().numpy()
         ll_chk, alpha = Fn.hmm_scan(*d, want_alpha=True)
         assert np.allclose(ll_seq, ll64, rtol=TOL)
@@ -526,12 +529,12 @@ def test_scan_with_structural_zeros_and_sticky_chains():
         _, ll64b = H.forward(lp, la, lb2, L)
         d2 = dev(lp, la, lb2, L)
         ll_scan2 = Fn.hmm_scan(*d2).cpu().numpy()
-        ll_seq2 = Fn.hmm_forward(*d2).cpu().numpy()
+        ll_seq2 = Fn.hmm_forward(*d2, time_parallel=False).cpu().numpy()
         assert np.isfinite(ll_scan2).all() and np.isfinite(ll_seq2).all()
         assert np.allclose(ll_scan2[3:], ll64b[3:], rtol=TOL) and np.allclose(ll_seq2[3:], ll64b[3:], rtol=TOL)   # dense rows: fine
         Fn.hmm_numerics_select("logspace")
         try:
-            ll_log = Fn.hmm_forward(*d2).cpu().numpy()
+            ll_log = Fn.hmm_forward(*d2, time_parallel=False).cpu().numpy()
             ll_log_scan = Fn.hmm_scan(*d2).cpu().numpy()
             _, g_log, _ = Fn.hmm_posterior(*d2, want_xi=False)
             p_log, _ = Fn.viterbi(*d2)
@@ -677,3 +680,30 @@ def test_transition_probs_accessor_for_reference_consumers():
     cur = probs[:, :, -1]
     assert (cur * self_transition).sum(dim=-1, keepdim=True).shape == (6, 1)
     assert torch.bmm(cur.unsqueeze(1), A[:, -1, :, :]).shape == (6, 1, 3)
+
+
+@pytest.mark.parametrize("K,T,B", [(3, 65536, 3), (3, 1028, 12), (2, 640, 12), (4, 388, 12), (3, 64, 12), (3, 128, 12), (3, 132, 12)])
+def test_viterbi_few_long_sequences_one_warp_each(K, T, B):
+    """Fewer than 2368 sequences (T % 4 == 0, T >= 64): one warp per sequence (csrc/hmm_vitlong.cuh: bulk-copy ring, redundant
+    max-plus recursion, time-parallel back-track by map composition).  Bit-exact against the oracle with exact ties, lengths
+    around the 4-step groups and the 128-step blocks, and equal to the thread-per-sequence sweep (taken at B >= 2368)."""
+    import vhmm_b200.functional as Fn
+    lp, la, lb, L = rand_hmm(B, T, K, seed=5 * K + T)
+    la = np.round(la * 2) / 2; lb = np.round(lb * 2) / 2; lp = np.round(lp * 2) / 2
+    edge = [T, 0, 1, 2, 3, 4, 5, 127, 128, 129, T - 1, T - 4]
+    for i in range(min(B, len(edge))):
+        L[i] = min(max(edge[i], 0), T)
+    path64, score = H.viterbi(lp, la, lb, L, dtype=np.float32)
+    d = dev(lp.astype(np.float32), la.astype(np.float32), lb.astype(np.float32), L)
+    path, sc = Fn.viterbi(*d)
+    assert np.array_equal(path.cpu().numpy(), path64)
+    assert np.array_equal(sc.cpu().numpy()[L > 0], score[L > 0])
+    assert (sc.cpu().numpy()[L == 0] == 0).all()                  # include/vhmm.h: score 0 for an empty sequence
+    p2, gamma, ll = Fn.hmm_decode(*d)
+    assert np.array_equal(p2.cpu().numpy(), path64)
+    if T <= 4096:
+        copies = -(-2368 // B)
+        big = (d[0], d[1].repeat(copies, 1, 1, 1), d[2].repeat(copies, 1, 1), d[3].repeat(copies))
+        pb, sb = Fn.viterbi(*big)
+        assert bool((pb.view(copies, B, T) == path[None]).all())
+        assert bool((sb.view(copies, B) == sc[None]).all())

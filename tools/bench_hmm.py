@@ -99,7 +99,7 @@ def main():
     report("hmm_scan (all-prefix alpha)", inb + 4 * K, steps,
            timed(lambda: Fn.hmm_scan(log_pi, log_A, log_b, L, want_alpha=True)), pk, src, cfg)
     report("hmm_forward sequential (same inputs, for comparison)", inb, steps,
-           timed(lambda: Fn.hmm_forward(log_pi, log_A, log_b, L)), pk, src, cfg)
+           timed(lambda: Fn.hmm_forward(log_pi, log_A, log_b, L, time_parallel=False)), pk, src, cfg)
 
 
 if __name__ == "__main__":

@@ -5,6 +5,7 @@
 #include "hmm_wide.cuh"
 #include "hmm_scan.cuh"
 #include "hmm_warp.cuh"
+#include "hmm_vitlong.cuh"
 #include <atomic>
 #include <stdlib.h>
 
@@ -91,6 +92,28 @@ static int launch_fwd_small(const hs::Args& a, cudaStream_t st) {
   kern<<<(unsigned)cdiv(a.nrows, HS_NT), HS_NT, TL::SMEM, st>>>(a);
   VHMM_LAUNCH_CHECK();
   return 0;
+}
+
+// Viterbi of small K: few sequences (fewer than 16 warps per SM's worth) -> one warp per sequence (hmm_vitlong.cuh: the
+// thread-per-sequence sweep leaves such a batch on a handful of CTAs, 0.48 us per step); environment VHMM_VITERBI=sweep keeps
+// the sweep.  Same results bit for bit.
+static bool vit_long_enabled() {
+  static const bool on = [] { const char* e = getenv("VHMM_VITERBI"); return !(e && e[0] == 's'); }();
+  return on;
+}
+static inline bool vit_long_fits(int64_t B, int64_t T, const hs::Args& a) {
+  return vit_long_enabled() && B < 2368 && T >= 64 && (T & 3) == 0 && a.vec_in && a.vec_path && !a.ahat && !a.alpha_log;
+}
+template <int K>
+static int launch_vit_small(const hs::Args& a, cudaStream_t st) {
+  if (vit_long_fits(a.nrows, a.T, a)) {
+    auto kern = hv::vit_long_kernel<K>;
+    VHMM_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hv::Ring<K>::SMEM));
+    kern<<<(unsigned)a.nrows, 32, hv::Ring<K>::SMEM, st>>>(a);
+    VHMM_LAUNCH_CHECK();
+    return 0;
+  }
+  return launch_fwd_small<K, false, true>(a, st);
 }
 
 template <int K>
@@ -389,7 +412,7 @@ int hmm_viterbi(const float* log_pi, const float* A, const float* Bm, const int6
     hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
     a.psi = psi; a.path = path; a.vec_path = ((T & 3) == 0) && (((uintptr_t)path & 3) == 0); a.score = score;
     int rc = 0;
-    DISPATCH_K(K, (rc = launch_fwd_small<KK, false, true>(a, st)));
+    DISPATCH_K(K, (rc = launch_vit_small<KK>(a, st)));
     return rc;
   }
   VHMM_REQUIRE(K <= 32, VHMM_E_DIMS, "hmm_viterbi: K=%lld > 32", (long long)K);
@@ -465,7 +488,7 @@ int hmm_decode(const float* log_pi, const float* A, const float* Bm, const int64
     hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
     a.psi = psi; a.path = path; a.vec_path = ((T & 3) == 0) && (((uintptr_t)path & 3) == 0); a.score = nullptr;
     int rc = 0;
-    DISPATCH_K(K, (rc = launch_fwd_small<KK, false, true>(a, st)));
+    DISPATCH_K(K, (rc = launch_vit_small<KK>(a, st)));
     if (rc) return rc;
     return hmm_posterior_onepass(log_pi, A, Bm, lengths, B, T, K, loglik, gamma, nullptr, st);
   }
@@ -475,7 +498,7 @@ int hmm_decode(const float* log_pi, const float* A, const float* Bm, const int64
     hs::Args a = base_args(log_pi, A, Bm, lengths, B, T, K);
     a.psi = psi; a.path = path; a.vec_path = ((T & 3) == 0) && (((uintptr_t)path & 3) == 0); a.score = nullptr;
     int rc = 0;
-    DISPATCH_K(K, (rc = launch_fwd_small<KK, false, true>(a, st)));
+    DISPATCH_K(K, (rc = launch_vit_small<KK>(a, st)));
     if (rc) return rc;
     DISPATCH_K(K, (rc = posterior_segments<KK>(log_pi, A, Bm, lengths, B, T, loglik, gamma, nullptr, stash,
                                                (size_t)B * T * K * sizeof(float), st)));
@@ -524,6 +547,11 @@ static int scan_small(hs::Args a, hs::ScanArgs sa, float* alpha, int64_t B, cuda
 int hmm_scan(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B,
              int64_t T, int64_t K, float* loglik, float* alpha, void* ws, size_t ws_bytes, cudaStream_t st) {
   if (!small_k(K)) return hmm_forward(log_pi, A, Bm, lengths, B, T, K, loglik, alpha, st);
+  // a whole sequence fits one warp of the one-pass kernel (T up to ~580): that IS the time-parallel path, with no carry scan
+  // (B = 2^20, T = 256 through the chunk kernels below: 11.8 ms; one-pass: 2.2 ms)
+  if (onepass_allowed() && T < 512 && loglik && (!alpha || alpha_onepass_enabled()) &&
+      onepass_fits(T, K, A, Bm, alpha ? (const void*)alpha : (const void*)A, nullptr))
+    return hmm_forward(log_pi, A, Bm, lengths, B, T, K, loglik, alpha, st);
   const int64_t nck = cdiv(T, SCAN_CH);
   Arena ar(ws, ws_bytes);
   hs::ScanArgs sa{};

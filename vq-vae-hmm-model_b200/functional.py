@@ -476,10 +476,16 @@ def _hmm_inputs(log_pi, log_A, log_b, lengths):
     return log_pi, log_A, log_b, lengths, B, T, K
 
 
-def hmm_forward(log_pi, log_A, log_b, lengths=None, want_alpha=False):
+def hmm_forward(log_pi, log_A, log_b, lengths=None, want_alpha=False, time_parallel=None):
     """vhmm_hmm_forward: the forward recursion as ONE pass (no workspace).  Sequences up to ~580 steps (K <= 4) run
-    time-parallel on one warp each; longer ones one thread per sequence -- for FEW LONG sequences use ``hmm_scan`` (same
-    results, time-parallel over 256-step segments; model.hmm_log_likelihood picks it by itself)."""
+    time-parallel on one warp each; longer ones one thread per sequence -- which leaves FEW LONG sequences (T >= 1024,
+    fewer than 2368 of them: B = 64, T = 65536 takes 43 ms) on a handful of threads, so those go to ``hmm_scan`` (same
+    results and padding conventions, time-parallel over 256-step segments, 0.05 - 0.12 ms) unless ``time_parallel=False``."""
+    if time_parallel is None:
+        time_parallel = log_b.dim() == 3 and log_b.shape[1] >= 1024 and log_b.shape[0] < 2368 and log_b.shape[2] <= 4 \
+            and (log_b.shape[1] * log_b.shape[2]) % 4 == 0
+    if time_parallel:
+        return hmm_scan(log_pi, log_A, log_b, lengths, want_alpha=want_alpha)
     log_pi, log_A, log_b, lengths, B, T, K = _hmm_inputs(log_pi, log_A, log_b, lengths)
     ll = torch.empty(B, device=log_b.device, dtype=torch.float32)
     alpha = torch.empty(B, T, K, device=log_b.device, dtype=torch.float32) if want_alpha else None
