@@ -272,6 +272,11 @@ def run_stages(torch, V, Fn, model, dev, local, pk, quick=False):
         out.append(stage_line("hmm_posterior (gamma) of long sequences", cfg, ms, it, ck, B * T, inb + 4 * K, pk,
                               note="time-parallel: segment products, forward + backward carry scans, one-pass posterior kernel on "
                                    "256-step rows (two reads of the inputs); the thread-per-sequence sweeps took 94 ms here"))
+        ms, it, ck = timed_stage(torch, lambda: Fn.viterbi(log_pi, log_A, log_b, L), local, mn, max_iters=500)
+        out.append(stage_line("viterbi of long sequences", cfg, ms, it, ck, B * T, inb + 1, pk,
+                              note="bit-exact max-plus is serial in time: one warp per sequence, chain of add / 3-input max / add "
+                                   "per step, back-pointers and back-track off the chain (issue-bound at ~45 cycles per step, "
+                                   "not HBM-bound); the thread-per-sequence sweep took 31.6 ms here"))
         del log_A, log_b
         # ---- cfg 5 recursion shapes: K = 32 (warp-per-sequence kernels), T = 1024
         B, T, K = 8192, 1024, 32

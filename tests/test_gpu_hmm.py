@@ -604,7 +604,8 @@ HMM_GRAD_TOL = {"nll": 1e-5,        # the loss that is trained on: -mean_b logli
                                       ((5, 64, 3, 32, 4, 128), 5, 50),      # T % 4 != 0: Prior + emission kernels, sweep posterior
                                       ((3, 8, 4, 4, 2, 16), 7, 33),         # small dims, K = 4
                                       ((4, 16, 6, 8, 3, 32), 6, 40),        # K = 6: warp-per-sequence recursion kernels
-                                      ((5, 64, 32, 32, 16, 128), 3, 132)])  # K = 32 (cfg-5 prior): tensor-core layer kernels in the backward
+                                      ((5, 64, 32, 32, 16, 128), 3, 132),   # K = 32 (cfg-5 prior): tensor-core layer kernels in the backward
+                                      ((5, 64, 3, 32, 4, 128), 2, 1100)])   # few long sequences: scan, segment posterior, wgrad split over time slabs
 def test_hmm_nll_backward_reaches_the_18_parameters(dims, B, T):
     """model.hmm_nll(x,u,lengths).backward(): backward = gamma/xi (beta recursion) -> row log-softmax -> transition MLP
     -> emission table -> decoder on the one-hot sequences -> log_prior.  Against float64 autograd through the oracle

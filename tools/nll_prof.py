@@ -6,7 +6,8 @@ import torch
 import vhmm_b200 as V
 torch.manual_seed(0)
 m = V.VAE_HMM(5, 64, 3, 32, u_dim=4).cuda()
-B, T = int(sys.argv[1]) if len(sys.argv) > 1 else 16384, 256
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
+T = int(sys.argv[2]) if len(sys.argv) > 2 else 256
 g = torch.Generator(device="cuda").manual_seed(1)
 x = torch.randn(B, 5, T, device="cuda", generator=g); u = torch.randn(B, 4, T, device="cuda", generator=g)
 L = torch.full((B,), T, dtype=torch.int64)

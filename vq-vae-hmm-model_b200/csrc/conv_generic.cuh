@@ -184,9 +184,12 @@ wgrad_kernel(const float* __restrict__ dy, const float* __restrict__ x, float* _
   __shared__ __align__(16) float xs[WG_CT][CONV_XP];
   const int tid = threadIdx.x, cl = tid & 15, og = tid >> 4;
   const int o0 = blockIdx.x * WG_OT, c0 = blockIdx.y * WG_CT;
+  // the work units are (sequence, 128-step slab) pairs, split evenly over gridDim.z: a batch of FEW LONG sequences fills the
+  // machine like many short ones (split over the batch alone, B = 4, T = 16384 ran 4 CTAs per tile for 2.5 ms a layer)
   const int nsplit = gridDim.z, split = blockIdx.z;
-  const int64_t per = (B + nsplit - 1) / nsplit;
-  const int64_t b_lo = split * per, b_hi = (b_lo + per < B) ? b_lo + per : B;
+  const int64_t nslab = (T + WG_TT - 1) / WG_TT, units = B * nslab;
+  const int64_t per = (units + nsplit - 1) / nsplit;
+  const int64_t u_lo = split * per, u_hi = (u_lo + per < units) ? u_lo + per : units;
 
   float acc[4][KW];
   float dbs[4];
@@ -196,10 +199,12 @@ wgrad_kernel(const float* __restrict__ dy, const float* __restrict__ x, float* _
 #pragma unroll
     for (int k = 0; k < KW; ++k) acc[i][k] = 0.f;
   }
-  for (int64_t b = b_lo; b < b_hi; ++b) {
+  for (int64_t un = u_lo; un < u_hi; ++un) {
+    const int64_t b = un / nslab;
     const float* dyb = dy + b * (int64_t)Cout * T;
     const float* xb = x + b * (int64_t)Cin * T;
-    for (int t0 = 0; t0 < T; t0 += WG_TT) {
+    {
+      const int t0 = (int)(un - b * nslab) * WG_TT;
       __syncthreads();
       for (int idx = tid; idx < WG_OT * WG_TT; idx += 256) {
         int o = idx / WG_TT, j = idx - o * WG_TT;
@@ -260,15 +265,15 @@ __global__ void reduce_partials_kernel(const float* __restrict__ part, int64_t s
   out[i] = (float)((double)out[i] + s);
 }
 
-static inline int wgrad_nsplit(int Cin, int Cout, int64_t B) {
+static inline int wgrad_nsplit(int Cin, int Cout, int64_t units) {   // units = B * ceil(T / WG_TT)
   int64_t tiles = cdiv(Cout, WG_OT) * cdiv(Cin, WG_CT);
   int64_t ns = cdiv(592, tiles);
-  if (ns > B) ns = B;
+  if (ns > units) ns = units;
   if (ns < 1) ns = 1;
   return (int)ns;
 }
 
-// floats of scratch needed by launch_wgrad for one layer
+// floats of scratch needed by launch_wgrad for one layer (B: an upper bound of the work units B * ceil(T / 128))
 static inline int64_t wgrad_scratch_floats(int Cin, int Cout, int kw, int64_t B) {
   int ns = wgrad_nsplit(Cin, Cout, B);
   return (int64_t)ns * ((int64_t)Cin * Cout * kw + Cout);
@@ -279,7 +284,7 @@ static inline int launch_wgrad(const float* dy, const float* x, float* gW, float
                                int64_t B, int Cin, int Cout, int64_t T, int kw, float* scratch,
                                cudaStream_t st) {
   if (B <= 0 || T <= 0) return 0;
-  const int ns = wgrad_nsplit(Cin, Cout, B);
+  const int ns = wgrad_nsplit(Cin, Cout, B * cdiv(T, (int64_t)WG_TT));
   const int64_t nW = (int64_t)Cin * Cout * kw;
   float* partW = scratch;
   float* partB = gB ? scratch + (int64_t)ns * nW : nullptr;
