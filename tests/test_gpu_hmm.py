@@ -373,8 +373,15 @@ def test_fused_hmm_inputs_match_layerwise_and_oracle():
             log_pi, log_A, log_b = m.hmm_inputs(x.cuda(), u.cuda())
             mu_tab, lv_tab = Fn.emission_table(m._dims, m._params(), T, torch.device("cuda"))
             fused = Fn.hmm_inputs_fused(m._dims, m._params(), x.cuda(), u.cuda(), mu_tab, lv_tab)
-            _, log_A_lw = m.prior(u.cuda())
+            Fn.elbo_select("layerwise")                      # Prior.forward layer by layer (hidden layer through HBM)
+            try:
+                _, log_A_lw = m.prior(u.cuda())
+            finally:
+                Fn.elbo_select("auto")
+            lp_f, log_A_f = m.prior(u.cuda())                # base dims, T % 4 == 0: the transitions-only FFMA kernel
             log_b_lw = Fn.emission_logprob(x.cuda(), mu_tab, lv_tab)
+        assert np.abs(lp_f.cpu().numpy() - lp64.numpy()).max() <= TOL
+        assert np.abs(log_A_f.cpu().numpy() - lA64.numpy()).max() <= TOL * max(1.0, np.abs(lA64.numpy()).max())
         assert (fused is not None) == (T % 4 == 0)
         assert np.abs(log_pi.cpu().numpy() - lp64.numpy()).max() <= TOL
         assert np.abs(log_A.cpu().numpy() - lA64.numpy()).max() <= TOL * max(1.0, np.abs(lA64.numpy()).max())
@@ -664,16 +671,19 @@ def test_transition_probs_accessor_for_reference_consumers():
     import vhmm_b200 as V
     from oracle import elbo as O
     p = O.init_params(5, 64, 3, 32, 4, 128, seed=5)
-    x, u, L = O.synth_batch(6, 5, 4, 37, seed=2)
     m = V.VAE_HMM(5, 64, 3, 32, u_dim=4)
     m.load_state_dict(p)
     m = m.cuda()
-    _, lA64 = O.prior({k: v.double() for k, v in p.items()}, u.double(), 4)
-    with torch.no_grad():
-        A = m.transition_probs(u.cuda())
-        A2 = m.transition_probs(u.permute(0, 2, 1).contiguous().cuda())       # (B,T,U) layout: permute rule :64-65
-        probs = m.get_regime_probs(x.cuda(), u.cuda(), L)
-    assert A.shape == (6, 37, 3, 3) and torch.equal(A, A2)
+    for T in (40, 37):      # T % 4 == 0: the transitions-only FFMA kernel; otherwise layer by layer
+        x, u, L = O.synth_batch(6, 5, 4, T, seed=2)
+        _, lA64 = O.prior({k: v.double() for k, v in p.items()}, u.double(), 4)
+        with torch.no_grad():
+            A = m.transition_probs(u.cuda())
+            A2 = m.transition_probs(u.permute(0, 2, 1).contiguous().cuda())       # (B,T,U) layout: permute rule :64-65
+            probs = m.get_regime_probs(x.cuda(), u.cuda(), L)
+        assert A.shape == (6, T, 3, 3) and torch.equal(A, A2)
+        assert np.abs(A.cpu().numpy() - np.exp(lA64.numpy())).max() <= 1e-6
+        assert float((A.sum(-1) - 1).abs().max()) <= 1e-6
     assert np.abs(A.cpu().numpy() - np.exp(lA64.numpy())).max() <= 1e-6
     assert float((A.sum(-1) - 1).abs().max()) <= 1e-6
     # the consumer's own expressions (regime_utilities.py:46-47, loss_functions.py:134-136) on our tensors

@@ -39,7 +39,7 @@ void set_error(const char* fmt, ...) {
 // elbo_layerwise.cu
 size_t layerwise_workspace_bytes(int op, const vhmm_dims& d, int64_t B, int64_t T);
 int layerwise_encoder_fwd(const vhmm_dims&, const vhmm_params&, const float*, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t);
-int layerwise_prior_fwd(const vhmm_dims&, const vhmm_params&, const float*, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t, int as_probs);
+int layerwise_prior_fwd(const vhmm_dims&, const vhmm_params&, const float*, int64_t, int64_t, float*, float*, void*, size_t, cudaStream_t, int as_probs, bool fused_transitions);
 size_t hmm_param_grads_workspace_bytes(const vhmm_dims& d, int64_t B, int64_t T);
 int hmm_param_grads(const vhmm_dims&, const vhmm_params&, const float*, const float*, const float*, const float*, const float*,
                     const float*, const float*, const float*, int64_t, int64_t, float*, void*, size_t, cudaStream_t);
@@ -193,14 +193,16 @@ int vhmm_prior_fwd(const vhmm_dims* dims, const vhmm_params* params, const float
                    void* stream) {
   ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(u, "u");
   ARG(B > 0 && T > 0, "B,T"); ARG(log_pi && log_A, "outputs"); ARG(workspace, "workspace");
-  return layerwise_prior_fwd(*dims, *params, u, B, T, log_pi, log_A, workspace, workspace_bytes, (cudaStream_t)stream, 0);
+  return layerwise_prior_fwd(*dims, *params, u, B, T, log_pi, log_A, workspace, workspace_bytes, (cudaStream_t)stream, 0,
+                             elbo_impl_for(*dims) == VHMM_ELBO_FUSED);
 }
 
 int vhmm_transition_probs(const vhmm_dims* dims, const vhmm_params* params, const float* u, int64_t B, int64_t T,
                           float* trans_probs, void* workspace, size_t workspace_bytes, void* stream) {
   ARG(dims_ok(dims), "dims"); ARG(params_ok(params), "params"); ARG(u, "u");
   ARG(B > 0 && T > 0, "B,T"); ARG(trans_probs, "trans_probs"); ARG(workspace, "workspace");
-  return layerwise_prior_fwd(*dims, *params, u, B, T, nullptr, trans_probs, workspace, workspace_bytes, (cudaStream_t)stream, 1);
+  return layerwise_prior_fwd(*dims, *params, u, B, T, nullptr, trans_probs, workspace, workspace_bytes, (cudaStream_t)stream, 1,
+                             elbo_impl_for(*dims) == VHMM_ELBO_FUSED);
 }
 
 int vhmm_hmm_param_grads(const vhmm_dims* dims, const vhmm_params* params, const float* x, const float* u,

@@ -352,10 +352,21 @@ int layerwise_encoder_fwd(const vhmm_dims& d, const vhmm_params& P, const float*
   return 0;
 }
 
+bool hmm_transitions_supported(const vhmm_dims& d, int64_t T, const float* u, const float* out);   // hmm_inputs.cu
+int hmm_transitions(const vhmm_dims& d, const vhmm_params& P, const float* u, int64_t B, int64_t T, float* out, int as_probs,
+                    cudaStream_t st);
+
 int layerwise_prior_fwd(const vhmm_dims& d, const vhmm_params& P, const float* u, int64_t B,
                         int64_t T, float* log_pi, float* log_A, void* ws, size_t ws_bytes,
-                        cudaStream_t st, int as_probs) {
+                        cudaStream_t st, int as_probs, bool fused_transitions) {
   VHMM_REQUIRE(d.K <= KMAX, VHMM_E_DIMS, "prior_fwd: K=%d > %d", d.K, KMAX);
+  if (fused_transitions && hmm_transitions_supported(d, T, u, log_A)) {   // base dims: one FFMA kernel, no hidden layer in HBM
+    if (log_pi) {
+      log_pi_kernel<<<1, 32, 0, st>>>(P.p[P_LOGPRIOR], log_pi, d.K);
+      VHMM_LAUNCH_CHECK();
+    }
+    return hmm_transitions(d, P, u, B, T, log_A, as_probs, st);
+  }
   Arena A(ws, ws_bytes);
   const int K2 = d.K * d.K;
   float* a = A.take<float>((size_t)B * d.TH * T);

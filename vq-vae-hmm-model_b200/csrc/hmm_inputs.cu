@@ -174,6 +174,35 @@ hmm_inputs_kernel(const float* __restrict__ W0, const float* __restrict__ b0, co
   }
 }
 
+// log_A (or A = exp(log_A): PROBS) alone, from u: Prior.forward (VQ_VAE_HMM_fixed.py:59-71) and the `transition_probs` accessor
+// without the layer-wise path's hidden layer in HBM (B*TH*T floats written and read back: 1.6 ms at B = 64, T = 65536)
+template <int K, int U, int TH, bool PROBS>
+__global__ void __launch_bounds__(256)
+transitions_kernel(const float* __restrict__ W0, const float* __restrict__ b0, const float* __restrict__ W2,
+                   const float* __restrict__ b2, const float* __restrict__ u, int64_t nquads, int T, float* __restrict__ out_A) {
+  constexpr int K2 = HiCfg<K>::K2;
+  static_assert(U <= 7, "W0 row + bias are packed into 8 floats");
+  __shared__ __align__(16) float sW0[TH * 8];
+  __shared__ __align__(16) float sW2[TH * HiCfg<K>::PK2];
+  __shared__ float sb2[HiCfg<K>::PK2];
+  hi_stage_weights<K, U, TH>(W0, b0, W2, b2, sW0, sW2, sb2);
+  __syncthreads();
+  const int T4 = T >> 2;
+  for (int64_t q = (int64_t)blockIdx.x * 256 + threadIdx.x; q < nquads; q += (int64_t)gridDim.x * 256) {
+    const int64_t b = q / T4;
+    const int t = (int)(q - b * T4) * 4;
+    float out[4 * K2];
+    hi_log_A_quad<K, U, TH>(sW0, sW2, sb2, u + (b * U) * (int64_t)T + t, T, out);
+    if (PROBS) {
+#pragma unroll
+      for (int i = 0; i < 4 * K2; ++i) out[i] = expf(out[i]);
+    }
+    float4* dA = reinterpret_cast<float4*>(out_A + (b * T + t) * (int64_t)K2);
+#pragma unroll
+    for (int i = 0; i < K2; ++i) __stcs(dA + i, make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]));
+  }
+}
+
 // ---- fused transition-softmax + emission-logprob + forward recursion -----------------------------------
 // log-likelihood of every sequence straight from (x, u): one WARP per sequence, lane l owns the steps
 // [l*S, l*S+S) (S = 4 ceil(T/128)); per 4-step quad it forms log_A and log_b in registers (above), turns them
@@ -260,6 +289,24 @@ hmm_loglik_fused_kernel(const float* __restrict__ W0, const float* __restrict__ 
 
 bool hmm_inputs_supported(const vhmm_dims& d, int64_t T) {
   return d.K == 3 && d.C == 5 && d.U == 4 && d.TH == 128 && (T % 4) == 0;
+}
+
+bool hmm_transitions_supported(const vhmm_dims& d, int64_t T, const float* u, const float* out) {
+  return d.K == 3 && d.U == 4 && d.TH == 128 && (T % 4) == 0 && ((((uintptr_t)u | (uintptr_t)out) & 15) == 0);
+}
+
+int hmm_transitions(const vhmm_dims& d, const vhmm_params& P, const float* u, int64_t B, int64_t T, float* out, int as_probs,
+                    cudaStream_t st) {
+  VHMM_REQUIRE(hmm_transitions_supported(d, T, u, out), VHMM_E_DIMS, "hmm_transitions: needs K=3,U=4,TH=128, T %% 4 == 0, 16-byte aligned u / out");
+  const int64_t nquads = B * (T / 4);
+  int64_t grid = cdiv(nquads, 256);
+  if (grid > 148 * 8) grid = 148 * 8;
+  if (as_probs)
+    transitions_kernel<3, 4, 128, true><<<(unsigned)grid, 256, 0, st>>>(P.p[P_T0W], P.p[P_T0B], P.p[P_T2W], P.p[P_T2B], u, nquads, (int)T, out);
+  else
+    transitions_kernel<3, 4, 128, false><<<(unsigned)grid, 256, 0, st>>>(P.p[P_T0W], P.p[P_T0B], P.p[P_T2W], P.p[P_T2B], u, nquads, (int)T, out);
+  VHMM_LAUNCH_CHECK();
+  return 0;
 }
 
 size_t hmm_inputs_workspace_bytes(const vhmm_dims& d, int64_t T) {
