@@ -718,3 +718,29 @@ def test_viterbi_few_long_sequences_one_warp_each(K, T, B):
         pb, sb = Fn.viterbi(*big)
         assert bool((pb.view(copies, B, T) == path[None]).all())
         assert bool((sb.view(copies, B) == sc[None]).all())
+
+
+@pytest.mark.parametrize("K,T", [(32, 1024), (16, 1000), (6, 777), (7, 2048), (32, 515)])
+def test_scan_loglik_wide_k_by_segment_products(K, T):
+    """4 < K <= 32, few long sequences: vhmm_hmm_scan = segment products (one warp per 128-step segment, row-wise power-of-two
+    renormalisation) + per-sequence carry (csrc/hmm_wide_scan.cuh) against the float64 oracle and the warp-per-sequence
+    forward; lengths around the segment boundaries incl. 0 and 1; moderate and sharp emissions (rows of very different
+    weight inside a segment)."""
+    import vhmm_b200.functional as Fn
+    B = 10
+    for sharp in (False, True):
+        lp, la, lb, _ = rand_hmm(B, T, K, seed=K + T + int(sharp))
+        if sharp:
+            r = np.random.default_rng(K * T)
+            lb = (r.normal(size=(B, T, K)) * 12.0 - 20.0).astype(lb.dtype)
+        L = np.array([T, T - 1, 1, 0, 127, 128, 129, 256, 257, T // 2], np.int64)
+        _, ll64 = H.forward(lp, la, lb, np.maximum(L, 1))
+        d = dev(lp.astype(np.float32), la.astype(np.float32), lb.astype(np.float32), L)
+        ll_scan = Fn.hmm_scan(*d).cpu().numpy()
+        ll_seq = Fn.hmm_forward(*d, time_parallel=False).cpu().numpy()
+        ll_auto = Fn.hmm_forward(*d).cpu().numpy()                       # few long sequences: dispatched to the scan
+        live = L > 0
+        assert np.allclose(ll_scan[live], ll64[live], rtol=TOL, atol=1e-5), (K, T, sharp, ll_scan, ll64)
+        assert np.allclose(ll_seq[live], ll64[live], rtol=TOL, atol=1e-5)
+        assert np.array_equal(ll_auto, ll_scan)
+        assert (ll_scan[~live] == 0).all()

@@ -6,6 +6,7 @@
 #include "hmm_scan.cuh"
 #include "hmm_warp.cuh"
 #include "hmm_vitlong.cuh"
+#include "hmm_wide_scan.cuh"
 #include <atomic>
 #include <stdlib.h>
 
@@ -271,6 +272,11 @@ static bool wide_allowed() {
     else { constexpr int KP = 32; expr; }                            \
   } while (0)
 
+static bool wide_scan_enabled() {            // environment VHMM_WIDE_SCAN=off keeps the warp-per-sequence forward for K > 4
+  static const bool on = [] { const char* e = getenv("VHMM_WIDE_SCAN"); return !(e && e[0] == 'o'); }();
+  return on;
+}
+
 static bool alpha_onepass_enabled() {        // environment VHMM_ALPHA=sweep keeps the thread-per-row sweeps for all-prefix alpha
   static const bool on = [] { const char* e = getenv("VHMM_ALPHA"); return !(e && e[0] == 's'); }();
   return on;
@@ -298,7 +304,7 @@ int hmm_forward(const float* log_pi, const float* A, const float* Bm, const int6
   const int wpb = 4;
   if (wide_allowed()) {
     DISPATCH_KP(K, (hx::fwd_kernel<KP><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
-                       log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, alpha, nullptr)));
+                       log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, alpha, nullptr, nullptr)));
     VHMM_LAUNCH_CHECK();
     return 0;
   }
@@ -382,7 +388,7 @@ int hmm_posterior(const float* log_pi, const float* A, const float* Bm, const in
   const int wpb = 4;
   if (wide_allowed()) {
     DISPATCH_KP(K, (hx::fwd_kernel<KP><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
-                       log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, nullptr, stash)));
+                       log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, nullptr, stash, nullptr)));
     VHMM_LAUNCH_CHECK();
     if (xi) {
       DISPATCH_KP(K, (hx::bwd_kernel<KP, true><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
@@ -546,7 +552,30 @@ static int scan_small(hs::Args a, hs::ScanArgs sa, float* alpha, int64_t B, cuda
 
 int hmm_scan(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B,
              int64_t T, int64_t K, float* loglik, float* alpha, void* ws, size_t ws_bytes, cudaStream_t st) {
-  if (!small_k(K)) return hmm_forward(log_pi, A, Bm, lengths, B, T, K, loglik, alpha, st);
+  if (!small_k(K)) {
+    // 4 < K <= 32, log-likelihood of few long sequences: segment products + carry (hmm_wide_scan.cuh); K^3 work per step
+    // instead of K^2, but over B*T/128 warps -- it wins while the batch alone cannot fill the machine
+    if (!alpha && loglik && K > 4 && K <= 32 && wide_allowed() && wide_scan_enabled() && T >= 512 && B <= 256) {
+      const int64_t nseg = cdiv(T, (int64_t)hx::WS_SEG), rows = B * nseg;
+      Arena ar(ws, ws_bytes);
+      float* Pmat = ar.take<float>((size_t)rows * K * K);
+      int* Pex = ar.take<int>((size_t)rows * K);
+      float* mbs = ar.take<float>((size_t)rows);
+      int* suspect = ar.take<int>((size_t)B);
+      VHMM_REQUIRE(ar.ok, VHMM_E_WORKSPACE, "hmm_scan: workspace %zu < %zu", ws_bytes, ar.used);
+      DISPATCH_KP(K, (hx::seg_product_kernel<KP><<<(unsigned)cdiv(rows, hx::WS_WPB), hx::WS_WPB * 32, 0, st>>>(
+                         A, Bm, lengths, rows, (int)nseg, (int)T, (int)K, Pmat, Pex, mbs)));
+      VHMM_LAUNCH_CHECK();
+      hx::seg_carry_kernel<<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(log_pi, Bm, lengths, B, (int)nseg, (int)T, (int)K,
+                                                                              Pmat, Pex, mbs, loglik, suspect);
+      VHMM_LAUNCH_CHECK();
+      DISPATCH_KP(K, (hx::fwd_kernel<KP><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
+                         log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, nullptr, nullptr, suspect)));   // flagged only
+      VHMM_LAUNCH_CHECK();
+      return 0;
+    }
+    return hmm_forward(log_pi, A, Bm, lengths, B, T, K, loglik, alpha, st);
+  }
   // a whole sequence fits one warp of the one-pass kernel (T up to ~580): that IS the time-parallel path, with no carry scan
   // (B = 2^20, T = 256 through the chunk kernels below: 11.8 ms; one-pass: 2.2 ms)
   if (onepass_allowed() && T < 512 && loglik && (!alpha || alpha_onepass_enabled()) &&

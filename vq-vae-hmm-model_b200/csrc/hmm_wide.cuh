@@ -59,10 +59,11 @@ template <int KP>
 __global__ void __launch_bounds__(WPB * 32)      // (a 128-register cap for 16 instead of 12 warps per SM measured slower: 72.6 vs 77.6 %)
 fwd_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const float* __restrict__ Bm,
            const int64_t* __restrict__ lengths, int64_t nB, int T, int K, float* __restrict__ loglik,
-           float* __restrict__ alpha, float* __restrict__ ahat) {
+           float* __restrict__ alpha, float* __restrict__ ahat, const int* __restrict__ only) {
   const int lane = threadIdx.x & 31;
   const int64_t b = (int64_t)blockIdx.x * WPB + (threadIdx.x >> 5);
   if (b >= nB) return;
+  if (only && !only[b]) return;        // redo pass of hmm_wide_scan.cuh: flagged sequences only
   const int64_t L64 = lengths[b];
   const int L = (int)(L64 < 0 ? 0 : (L64 > T ? T : L64));
   const bool on = lane < K;
