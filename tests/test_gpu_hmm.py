@@ -744,3 +744,28 @@ def test_scan_loglik_wide_k_by_segment_products(K, T):
         assert np.allclose(ll_seq[live], ll64[live], rtol=TOL, atol=1e-5)
         assert np.array_equal(ll_auto, ll_scan)
         assert (ll_scan[~live] == 0).all()
+
+
+@pytest.mark.parametrize("K,T", [(32, 640), (16, 1000), (6, 777), (7, 1280), (32, 515)])
+def test_posterior_wide_k_of_few_long_sequences_by_rows(K, T):
+    """4 < K <= 32, few long sequences: vhmm_hmm_posterior = segment products + forward / backward carries, then the
+    warp-per-sequence forward / backward kernels on 128-step ROWS (csrc/hmm_wide_scan.cuh, hx::RowView).  gamma, xi and the
+    log-likelihood against the float64 oracle; lengths around the row boundaries incl. 0 and 1; hmm_decode's gamma too."""
+    import vhmm_b200.functional as Fn
+    B = 10
+    lp, la, lb, _ = rand_hmm(B, T, K, seed=2 * K + T)
+    L = np.array([T, T - 1, 1, 0, 127, 128, 129, 256, 257, T // 2], np.int64)
+    g64, x64, ll64 = H.posteriors(lp, la, lb, L)
+    d = dev(lp, la, lb, L)
+    ll, gamma, xi = Fn.hmm_posterior(*d, want_xi=True)
+    live = L > 0
+    assert np.allclose(ll.cpu().numpy()[live], ll64[live], rtol=TOL, atol=1e-5)
+    assert np.abs(gamma.cpu().numpy() - g64).max() <= TOL
+    assert np.abs(xi.cpu().numpy() - x64).max() <= TOL
+    ll2, gamma2, _ = Fn.hmm_posterior(*d, want_xi=False)
+    assert np.abs(gamma2.cpu().numpy() - g64).max() <= TOL
+    assert np.array_equal(ll2.cpu().numpy(), ll.cpu().numpy())
+    path, gamma3, ll3 = Fn.hmm_decode(*d)
+    assert np.abs(gamma3.cpu().numpy() - g64).max() <= TOL
+    pv, _ = Fn.viterbi(*d)
+    assert np.array_equal(path.cpu().numpy(), pv.cpu().numpy())

@@ -39,11 +39,16 @@ size_t hmm_workspace_bytes(int op, int64_t B, int64_t T, int64_t K) {
   const size_t stash = align_up((size_t)B * T * K * sizeof(float), 256);
   const size_t psi = align_up((size_t)B * T * psi_bytes(K), 256);
   const int64_t nck = cdiv(T, SCAN_CH);
+  // few long sequences at K > 4 (hmm_wide_scan.cuh): segment products, exponents, emission maxima, vin / bin per 128-step row
+  const int64_t wrows = B * cdiv(T, (int64_t)hx::WS_SEG);
+  const size_t wide_rows = (K > 4 && T >= 512 && B <= 256)
+      ? align_up((size_t)wrows * K * K * 4, 256) + 3 * align_up((size_t)wrows * K * 4, 256) + align_up((size_t)wrows * 4, 256) +
+        align_up((size_t)B * 4, 256) + 256 : 0;
   switch (op) {
     case VHMM_OP_HMM_FORWARD: return 0;
-    case VHMM_OP_HMM_POSTERIOR: return stash + 256;
+    case VHMM_OP_HMM_POSTERIOR: return stash + 256 + wide_rows;
     case VHMM_OP_VITERBI: return psi + 256;
-    case VHMM_OP_HMM_DECODE: return stash + psi + 512;
+    case VHMM_OP_HMM_DECODE: return stash + psi + 512 + wide_rows;
     case VHMM_OP_HMM_SCAN:
       return align_up((size_t)B * nck * K * K * 4, 256) + 2 * align_up((size_t)B * nck * 8, 256) +
              align_up((size_t)B * nck * K * 4, 256) + align_up((size_t)B * 4, 256) + 1024;
@@ -304,7 +309,7 @@ int hmm_forward(const float* log_pi, const float* A, const float* Bm, const int6
   const int wpb = 4;
   if (wide_allowed()) {
     DISPATCH_KP(K, (hx::fwd_kernel<KP><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
-                       log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, alpha, nullptr, nullptr)));
+                       log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, alpha, nullptr, hx::RowView{})));
     VHMM_LAUNCH_CHECK();
     return 0;
   }
@@ -386,16 +391,64 @@ int hmm_posterior(const float* log_pi, const float* A, const float* Bm, const in
   }
   VHMM_REQUIRE(K <= 32, VHMM_E_DIMS, "hmm_posterior: K=%lld > 32", (long long)K);
   const int wpb = 4;
+  if (wide_allowed() && wide_scan_enabled() && K > 4 && T >= 512 && B <= 256) {
+    // few long sequences: segment products + forward / backward carries (hmm_wide_scan.cuh), then the same forward and
+    // backward kernels on 128-step ROWS (each from its incoming alpha_hat / outgoing beta_hat) -- B*T/128 warps instead of B
+    const int64_t nseg = cdiv(T, (int64_t)hx::WS_SEG), rows = B * nseg;
+    float* Pmat = ar.take<float>((size_t)rows * K * K);
+    int* Pex = ar.take<int>((size_t)rows * K);
+    float* mbs = ar.take<float>((size_t)rows);
+    float* vin = ar.take<float>((size_t)rows * K);
+    float* bin = ar.take<float>((size_t)rows * K);
+    int* suspect = ar.take<int>((size_t)B);
+    if (ar.ok) {       // (a caller's workspace sized for the stash alone takes the warp-per-sequence kernels below)
+      DISPATCH_KP(K, (hx::seg_product_kernel<KP><<<(unsigned)cdiv(rows, hx::WS_WPB), hx::WS_WPB * 32, 0, st>>>(
+                         A, Bm, lengths, rows, (int)nseg, (int)T, (int)K, Pmat, Pex, mbs)));
+      VHMM_LAUNCH_CHECK();
+      hx::seg_carry_kernel<<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(log_pi, Bm, lengths, B, (int)nseg, (int)T, (int)K,
+                                                                              Pmat, Pex, mbs, loglik, suspect, vin);
+      VHMM_LAUNCH_CHECK();
+      hx::seg_carry_back_kernel<<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(lengths, B, (int)nseg, (int)T, (int)K, Pmat, Pex,
+                                                                                   bin, suspect);
+      VHMM_LAUNCH_CHECK();
+      const hx::RowView rv{(int)nseg, hx::WS_SEG, vin, bin, nullptr};
+      const hx::RowView redo{0, 0, nullptr, nullptr, suspect};
+      DISPATCH_KP(K, (hx::fwd_kernel<KP, true><<<(unsigned)cdiv(rows, hx::WPB), hx::WPB * 32, 0, st>>>(
+                         log_pi, A, Bm, lengths, rows, (int)T, (int)K, nullptr, nullptr, stash, rv)));
+      VHMM_LAUNCH_CHECK();
+      if (xi) {
+        DISPATCH_KP(K, (hx::bwd_kernel<KP, true, true><<<(unsigned)cdiv(rows, hx::WPB), hx::WPB * 32, 0, st>>>(
+                           A, Bm, lengths, rows, (int)T, (int)K, stash, gamma, xi, rv)));
+      } else {
+        DISPATCH_KP(K, (hx::bwd_kernel<KP, false, true><<<(unsigned)cdiv(rows, hx::WPB), hx::WPB * 32, 0, st>>>(
+                           A, Bm, lengths, rows, (int)T, (int)K, stash, gamma, nullptr, rv)));
+      }
+      VHMM_LAUNCH_CHECK();
+      // sequences whose carries vanished (flagged): the warp-per-sequence kernels again, for those only
+      DISPATCH_KP(K, (hx::fwd_kernel<KP><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
+                         log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, nullptr, stash, redo)));
+      VHMM_LAUNCH_CHECK();
+      if (xi) {
+        DISPATCH_KP(K, (hx::bwd_kernel<KP, true><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
+                           A, Bm, lengths, B, (int)T, (int)K, stash, gamma, xi, redo)));
+      } else {
+        DISPATCH_KP(K, (hx::bwd_kernel<KP, false><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
+                           A, Bm, lengths, B, (int)T, (int)K, stash, gamma, nullptr, redo)));
+      }
+      VHMM_LAUNCH_CHECK();
+      return 0;
+    }
+  }
   if (wide_allowed()) {
     DISPATCH_KP(K, (hx::fwd_kernel<KP><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
-                       log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, nullptr, stash, nullptr)));
+                       log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, nullptr, stash, hx::RowView{})));
     VHMM_LAUNCH_CHECK();
     if (xi) {
       DISPATCH_KP(K, (hx::bwd_kernel<KP, true><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
-                         A, Bm, lengths, B, (int)T, (int)K, stash, gamma, xi)));
+                         A, Bm, lengths, B, (int)T, (int)K, stash, gamma, xi, hx::RowView{})));
     } else {
       DISPATCH_KP(K, (hx::bwd_kernel<KP, false><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
-                         A, Bm, lengths, B, (int)T, (int)K, stash, gamma, nullptr)));
+                         A, Bm, lengths, B, (int)T, (int)K, stash, gamma, nullptr, hx::RowView{})));
     }
     VHMM_LAUNCH_CHECK();
     return 0;
@@ -469,8 +522,8 @@ int hmm_decode(const float* log_pi, const float* A, const float* Bm, const int64
                int64_t T, int64_t K, uint8_t* path, float* gamma, float* loglik, void* ws, size_t ws_bytes,
                cudaStream_t st) {
   Arena ar(ws, ws_bytes);
-  float* stash = ar.take<float>((size_t)B * T * K);
   uint8_t* psi = ar.take<uint8_t>((size_t)B * T * psi_bytes(K));
+  float* stash = ar.take<float>((size_t)B * T * K);      // last: the posterior's region is the stash and whatever follows it
   VHMM_REQUIRE(ar.ok, VHMM_E_WORKSPACE, "hmm_decode: workspace %zu < %zu", ws_bytes, ar.used);
   if (small_k(K) && onepass_allowed() && decode_onekernel() && onepass_fits(T, K, A, Bm, gamma, nullptr)) {
     // ONE kernel, one read of the inputs (48 B/step read, 13 written): the one-pass posterior kernel with a Viterbi helper warp
@@ -527,7 +580,7 @@ int hmm_decode(const float* log_pi, const float* A, const float* Bm, const int64
                        align_up((size_t)B * T * psi_bytes(K), 256), st);
   if (rc) return rc;
   return hmm_posterior(log_pi, A, Bm, lengths, B, T, K, loglik, gamma, nullptr, stash,
-                       align_up((size_t)B * T * K * 4, 256), st);
+                       ws_bytes - ((size_t)((char*)stash - (char*)ws)), st);
 }
 
 template <int K>
@@ -567,10 +620,10 @@ int hmm_scan(const float* log_pi, const float* A, const float* Bm, const int64_t
                          A, Bm, lengths, rows, (int)nseg, (int)T, (int)K, Pmat, Pex, mbs)));
       VHMM_LAUNCH_CHECK();
       hx::seg_carry_kernel<<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(log_pi, Bm, lengths, B, (int)nseg, (int)T, (int)K,
-                                                                              Pmat, Pex, mbs, loglik, suspect);
+                                                                              Pmat, Pex, mbs, loglik, suspect, nullptr);
       VHMM_LAUNCH_CHECK();
       DISPATCH_KP(K, (hx::fwd_kernel<KP><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
-                         log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, nullptr, nullptr, suspect)));   // flagged only
+                         log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, nullptr, nullptr, hx::RowView{0, 0, nullptr, nullptr, suspect})));   // flagged only
       VHMM_LAUNCH_CHECK();
       return 0;
     }

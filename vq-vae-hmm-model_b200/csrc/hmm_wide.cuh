@@ -55,24 +55,40 @@ __device__ __forceinline__ void load_col(const float* __restrict__ At, int K, in
 // forward: loglik (B); optional log-space alpha (B,T,K) (carried unchanged for t >= L, B.2) and/or the
 // normalised linear alpha_hat (B,T,K) (stash for bwd_kernel)
 // ---------------------------------------------------------------------------------------------------------
-template <int KP>
+// A warp's unit of work is a whole sequence (nseg <= 1) or ROW s of a sequence cut into `seg`-step rows (hmm_wide_scan.cuh:
+// few long sequences): the row starts from the normalised alpha_hat of the step before it (vin) and, in the backward kernel,
+// from the beta_hat of its last step (bin); both come from the carry kernels over the segment products.
+struct RowView {
+  int nseg, seg;
+  const float* vin;      // (rows, K) alpha_hat at the step before the row (row 0: unused)
+  const float* bin;      // (rows, K) beta_hat at the row's last valid step (last valid row: unused, ones)
+  const int* only;       // per sequence: 0 = skip (redo pass for flagged sequences), or null
+};
+
+template <int KP, bool ROWS = false>
 __global__ void __launch_bounds__(WPB * 32)      // (a 128-register cap for 16 instead of 12 warps per SM measured slower: 72.6 vs 77.6 %)
 fwd_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const float* __restrict__ Bm,
-           const int64_t* __restrict__ lengths, int64_t nB, int T, int K, float* __restrict__ loglik,
-           float* __restrict__ alpha, float* __restrict__ ahat, const int* __restrict__ only) {
+           const int64_t* __restrict__ lengths, int64_t nW, int T, int K, float* __restrict__ loglik,
+           float* __restrict__ alpha, float* __restrict__ ahat, RowView rv) {
   const int lane = threadIdx.x & 31;
-  const int64_t b = (int64_t)blockIdx.x * WPB + (threadIdx.x >> 5);
-  if (b >= nB) return;
-  if (only && !only[b]) return;        // redo pass of hmm_wide_scan.cuh: flagged sequences only
+  const int64_t w = (int64_t)blockIdx.x * WPB + (threadIdx.x >> 5);
+  if (w >= nW) return;
+  int64_t b = w;
+  int t0 = 0;
+  if (ROWS) { b = w / rv.nseg; t0 = (int)(w - b * rv.nseg) * rv.seg; }
+  if (rv.only && !rv.only[b]) return;
   const int64_t L64 = lengths[b];
-  const int L = (int)(L64 < 0 ? 0 : (L64 > T ? T : L64));
+  const int Ls = (int)(L64 < 0 ? 0 : (L64 > T ? T : L64));
+  const int L = ROWS ? max(0, min(min(rv.seg, T - t0), Ls - t0)) : Ls;    // valid steps of this row
+  const bool first = ROWS ? (t0 == 0) : true;
   const bool on = lane < K;
   const int KK = K * K;
-  const float* Ab = A + b * (int64_t)T * KK;
-  const float* Bb = Bm + b * (int64_t)T * K;
+  const int64_t s0 = b * (int64_t)T + t0;                                            // first step of the row
+  const float* Ab = A + s0 * KK;
+  const float* Bb = Bm + s0 * K;
   float v = 0.f;
   double ll = 0.0;
-  if (L > 0) {
+  if (L > 0 && first) {
     const float x = on ? log_pi[lane] + Bb[lane] : -INFINITY;
     const float m = wmax(x);
     v = on ? ex2((x - m) * LOG2E) : 0.f;
@@ -80,16 +96,19 @@ fwd_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const 
     v *= 1.f / s;
     ll = (double)m + (double)logf(s);
     if (on) {
-      if (alpha) alpha[(b * T) * K + lane] = logf(v) + (float)ll;
-      if (ahat) ahat[(b * T) * K + lane] = v;
+      if (alpha) alpha[s0 * K + lane] = logf(v) + (float)ll;
+      if (ahat) ahat[s0 * K + lane] = v;
     }
+  } else if (ROWS && L > 0) {
+    v = on ? rv.vin[w * K + lane] : 0.f;          // a later row: its step 0 is a recursion step like any other
   }
+  const int tb = first ? 1 : 0;
   float an[KP], bn = -INFINITY;
-  if (L > 1) {
-    load_col<KP>(Ab + KK, K, lane, on, an);
-    bn = on ? __ldcs(Bb + K + lane) : -INFINITY;
+  if (L > tb) {
+    load_col<KP>(Ab + (int64_t)tb * KK, K, lane, on, an);
+    bn = on ? __ldcs(Bb + (int64_t)tb * K + lane) : -INFINITY;
   }
-  for (int t = 1; t < L; ++t) {
+  for (int t = tb; t < L; ++t) {
     float ac[KP];
 #pragma unroll
     for (int i = 0; i < KP; ++i) ac[i] = an[i];
@@ -110,15 +129,16 @@ fwd_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const 
       else if ((i & 3) == 2) w2 = fmaf(vi, p, w2);
       else w3 = fmaf(vi, p, w3);
     }
-    const float w = on ? (w0 + w1) + (w2 + w3) : 0.f;
-    const float s = wsum(w);
-    v = w * (1.f / s);
+    const float wv = on ? (w0 + w1) + (w2 + w3) : 0.f;
+    const float s = wsum(wv);
+    v = wv * (1.f / s);
     ll += (double)mb + (double)logf(s);
     if (on) {
-      if (alpha) alpha[(b * T + t) * K + lane] = logf(v) + (float)ll;
-      if (ahat) ahat[(b * T + t) * K + lane] = v;
+      if (alpha) alpha[(s0 + t) * K + lane] = logf(v) + (float)ll;
+      if (ahat) ahat[(s0 + t) * K + lane] = v;
     }
   }
+  if (ROWS) return;                                // rows: alpha_hat only (log-likelihood and log alpha belong to whole sequences)
   if (lane == 0 && loglik) loglik[b] = (L > 0) ? (float)ll : 0.f;
   if (alpha && on) {
     const float carried = logf(v) + (float)ll;
@@ -129,36 +149,47 @@ fwd_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const 
 // ---------------------------------------------------------------------------------------------------------
 // backward: gamma (B,T,K) and, if XI, xi (B,T,K,K) from the alpha_hat stash (zeros for t >= L; xi[:,0] = 0)
 // ---------------------------------------------------------------------------------------------------------
-template <int KP, bool XI>
+template <int KP, bool XI, bool ROWS = false>
 __global__ void __launch_bounds__(WPB * 32)
 bwd_kernel(const float* __restrict__ A, const float* __restrict__ Bm, const int64_t* __restrict__ lengths,
-           int64_t nB, int T, int K, const float* __restrict__ ahat, float* __restrict__ gamma,
-           float* __restrict__ xi) {
+           int64_t nW, int T, int K, const float* __restrict__ ahat, float* __restrict__ gamma,
+           float* __restrict__ xi, RowView rv) {
   __shared__ float tr[WPB][KP][KP + 1];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const int64_t b = (int64_t)blockIdx.x * WPB + wib;
-  if (b >= nB) return;
+  const int64_t w = (int64_t)blockIdx.x * WPB + wib;
+  if (w >= nW) return;
+  int64_t b = w;
+  int t0 = 0;
+  if (ROWS) { b = w / rv.nseg; t0 = (int)(w - b * rv.nseg) * rv.seg; }
+  if (rv.only && !rv.only[b]) return;
   const int64_t L64 = lengths[b];
-  const int L = (int)(L64 < 0 ? 0 : (L64 > T ? T : L64));
+  const int Ls = (int)(L64 < 0 ? 0 : (L64 > T ? T : L64));
+  const int cap = ROWS ? min(rv.seg, T - t0) : T;          // steps that exist in this row
+  const int L = ROWS ? max(0, min(cap, Ls - t0)) : Ls;      // valid steps of this row
+  const bool first = ROWS ? (t0 == 0) : true;
   const bool on = lane < K;
   const int KK = K * K;
-  const float* Ab = A + b * (int64_t)T * KK;
-  const float* Bb = Bm + b * (int64_t)T * K;
-  const float* ah = ahat + b * (int64_t)T * K;
-  float* gm = gamma + b * (int64_t)T * K;
-  float* xb = XI ? xi + b * (int64_t)T * KK : nullptr;
+  const int64_t s0 = b * (int64_t)T + t0;
+  const float* Ab = A + s0 * KK;
+  const float* Bb = Bm + s0 * K;
+  const float* ah = ahat + s0 * K;                // (a later row reads ah[-1 * K ..]: the previous row's last alpha_hat)
+  float* gm = gamma + s0 * K;
+  float* xb = XI ? xi + s0 * KK : nullptr;
   // steps beyond the length (and xi of step 0): zeros
-  for (int64_t e = (int64_t)L * K + lane; e < (int64_t)T * K; e += 32) gm[e] = 0.f;
+  for (int64_t e = (int64_t)L * K + lane; e < (int64_t)cap * K; e += 32) gm[e] = 0.f;
   if (XI) {
-    for (int64_t e = (int64_t)L * KK + lane; e < (int64_t)T * KK; e += 32) xb[e] = 0.f;
-    if (L > 0) for (int e = lane; e < KK; e += 32) xb[e] = 0.f;
+    for (int64_t e = (int64_t)L * KK + lane; e < (int64_t)cap * KK; e += 32) xb[e] = 0.f;
+    if (L > 0 && first) for (int e = lane; e < KK; e += 32) xb[e] = 0.f;
   }
   if (L <= 0) return;
   float (*mytr)[KP + 1] = tr[wib];
-  float be = on ? 1.f : 0.f;                      // beta_hat_{L-1} (any positive scale: gamma / xi are normalised per step)
+  // beta_hat at the row's last valid step (any positive scale: gamma / xi are normalised per step)
+  float be = on ? 1.f : 0.f;
+  if (ROWS && t0 + L < Ls) be = on ? rv.bin[w * K + lane] : 0.f;
+  const int tb = first ? 1 : 0;                   // steps tb .. L-1 have a transition INTO them inside this row's reach
   float an[KP], bn = -INFINITY, apn = 0.f;
   float at = on ? ah[(int64_t)(L - 1) * K + lane] : 0.f;
-  if (L > 1) {
+  if (L - 1 >= tb) {
     load_col<KP>(Ab + (int64_t)(L - 1) * KK, K, lane, on, an);
     bn = on ? __ldcs(Bb + (int64_t)(L - 1) * K + lane) : -INFINITY;
     apn = on ? ah[(int64_t)(L - 2) * K + lane] : 0.f;
@@ -169,12 +200,12 @@ bwd_kernel(const float* __restrict__ A, const float* __restrict__ Bm, const int6
       const float sg = wsum(g);
       if (on) gm[(int64_t)t * K + lane] = g * (1.f / sg);
     }
-    if (t == 0) break;
+    if (t < tb) break;
     float ac[KP];
 #pragma unroll
     for (int i = 0; i < KP; ++i) ac[i] = an[i];
     const float bc = bn, ap = apn;
-    if (t >= 2) {
+    if (t - 1 >= tb) {
       load_col<KP>(Ab + (int64_t)(t - 1) * KK, K, lane, on, an);
       bn = on ? __ldcs(Bb + (int64_t)(t - 1) * K + lane) : -INFINITY;
       apn = on ? ah[(int64_t)(t - 2) * K + lane] : 0.f;
@@ -196,6 +227,7 @@ bwd_kernel(const float* __restrict__ A, const float* __restrict__ Bm, const int6
         if (on && i < K) xr[i * K + lane] = ai * q[i] * iz;
       }
     }
+    if (ROWS && t == 0) break;                     // first step of a later row: its xi only (beta of the step before is the previous row's bin)
     // row sums through shared memory: tile[i][j] = q_j[i]; lane i sums row i
     __syncwarp();
     if (lane < KP) {
@@ -203,14 +235,14 @@ bwd_kernel(const float* __restrict__ A, const float* __restrict__ Bm, const int6
       for (int i = 0; i < KP; ++i) mytr[i][lane] = q[i];
     }
     __syncwarp();
-    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    float s0a = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
     if (lane < KP) {
 #pragma unroll
       for (int j = 0; j < KP; j += 4) {
-        s0 += mytr[lane][j]; s1 += mytr[lane][j + 1]; s2 += mytr[lane][j + 2]; s3 += mytr[lane][j + 3];
+        s0a += mytr[lane][j]; s1 += mytr[lane][j + 1]; s2 += mytr[lane][j + 2]; s3 += mytr[lane][j + 3];
       }
     }
-    const float bs = on ? (s0 + s1) + (s2 + s3) : 0.f;
+    const float bs = on ? (s0a + s1) + (s2 + s3) : 0.f;
     be = bs * (1.f / wmax(bs));                    // keep beta_hat in range (power-free rescale; any positive factor)
     at = ap;
   }

@@ -1,4 +1,5 @@
-// hmm_wide_scan.cuh -- log-likelihood of FEW LONG sequences for 4 < K <= 32, parallel over time.
+// hmm_wide_scan.cuh -- log-likelihood and posteriors of FEW LONG sequences for 4 < K <= 32, parallel over time (SURVEY.md
+// Appendix B.5, B.3).
 //
 // hx::fwd_kernel (hmm_wide.cuh) walks a sequence with one warp, one step after the other, each step waiting for its own
 // K x K tile of log_A from HBM: 1.4 us per step at K = 32 whatever the batch -- 22 ms for T = 16384.  A batch of thousands of
@@ -13,6 +14,9 @@
 //                       full mantissa: the incoming vector may sit on any of them.
 //   seg_carry_kernel    one warp per sequence: alpha_0 from log_pi and log_b_0, then v <- v P_seg over the segments (rows
 //                       weighted by 2^(exponent - max), next segment's rows prefetched), log-normalisers in double.
+//   seg_carry_back_kernel  the same backwards: beta_hat at the last step of every segment.  With alpha_hat before and beta_hat
+//                       after every segment known, hx::fwd_kernel / hx::bwd_kernel run on the 128-step ROWS (hx::RowView) as if
+//                       they were sequences of their own: gamma and xi of few long sequences on B*T/128 warps.
 // K^3 instead of K^2 work per step, but over B*T/128 warps instead of B.  A carry that comes out zero or not finite (only
 // underflow inside a row: transitions below e^-87) flags the sequence, and hx::fwd_kernel redoes the flagged ones.
 #pragma once
@@ -133,7 +137,8 @@ seg_product_kernel(const float* __restrict__ A, const float* __restrict__ Bm, co
 __global__ void __launch_bounds__(WPB * 32)
 seg_carry_kernel(const float* __restrict__ log_pi, const float* __restrict__ Bm, const int64_t* __restrict__ lengths,
                  int64_t nB, int nseg, int T, int K, const float* __restrict__ Pmat, const int* __restrict__ Pex,
-                 const float* __restrict__ mbsum, float* __restrict__ loglik, int* __restrict__ suspect) {
+                 const float* __restrict__ mbsum, float* __restrict__ loglik, int* __restrict__ suspect,
+                 float* __restrict__ vin) {
   const int lane = threadIdx.x & 31;
   const int64_t b = (int64_t)blockIdx.x * WPB + (threadIdx.x >> 5);
   if (b >= nB) return;
@@ -141,7 +146,7 @@ seg_carry_kernel(const float* __restrict__ log_pi, const float* __restrict__ Bm,
   const int L = (int)(L64 < 0 ? 0 : (L64 > T ? T : L64));
   const bool on = lane < K;
   if (lane == 0) suspect[b] = 0;
-  if (L == 0) { if (lane == 0) loglik[b] = 0.f; return; }
+  if (L == 0) { if (lane == 0 && loglik) loglik[b] = 0.f; return; }
   const int KK = K * K;
   const float x = on ? log_pi[lane] + Bm[b * (int64_t)T * K + lane] : -INFINITY;
   const float m = wmax(x);
@@ -168,6 +173,7 @@ seg_carry_kernel(const float* __restrict__ log_pi, const float* __restrict__ Bm,
       for (int i = 0; i < 32; ++i) pn[i] = (on && i < K) ? Pn[i * K + lane] : 0.f;
       en = on ? Pex[(b * nseg + s + 1) * (int64_t)K + lane] : 0;
     }
+    if (vin && on) vin[(b * nseg + s) * (int64_t)K + lane] = v;      // alpha_hat at the step before segment s
     // weight of row `lane`: v * 2^ex, brought to the largest exponent among the rows that carry mass
     const int ve = (v > 0.f) ? (((__float_as_int(v) >> 23) & 0xff) - 126 + ec) : INT_MIN / 2;
     int E = ve;
@@ -190,9 +196,51 @@ seg_carry_kernel(const float* __restrict__ log_pi, const float* __restrict__ Bm,
     ll += (double)logf(sm) + (double)E * 0.6931471805599453 + (double)mbsum[b * nseg + s];
   }
   if (lane == 0) {
-    loglik[b] = (float)ll;
+    if (loglik) loglik[b] = (float)ll;
     if (bad) suspect[b] = 1;
   }
+}
+
+// beta_hat at the last valid step of every segment row, backwards: bin[last valid row] = 1, bin[s-1] = normalise(P_s bin[s]).
+// One warp per sequence, lane = state i: (P b)[i] = 2^ex[i] * sum_j Phat[i][j] b[j].
+__global__ void __launch_bounds__(WPB * 32)
+seg_carry_back_kernel(const int64_t* __restrict__ lengths, int64_t nB, int nseg, int T, int K, const float* __restrict__ Pmat,
+                      const int* __restrict__ Pex, float* __restrict__ bin, int* __restrict__ suspect) {
+  const int lane = threadIdx.x & 31;
+  const int64_t b = (int64_t)blockIdx.x * WPB + (threadIdx.x >> 5);
+  if (b >= nB) return;
+  const int64_t L64 = lengths[b];
+  const int L = (int)(L64 < 0 ? 0 : (L64 > T ? T : L64));
+  if (L == 0) return;
+  const bool on = lane < K;
+  const int KK = K * K;
+  const int ns = (L + WS_SEG - 1) / WS_SEG;
+  float be = on ? 1.f : 0.f;
+  for (int s = ns - 1; s >= 1; --s) {
+    if (on) bin[(b * nseg + s) * (int64_t)K + lane] = be;
+    const float* Ps = Pmat + (b * nseg + s) * (int64_t)KK + lane * K;     // row `lane` of the segment's product
+    float d0 = 0.f, d1 = 0.f;
+    for (int j = 0; j < K; j += 2) {
+      const float b0 = __shfl_sync(0xffffffffu, be, j), b1 = __shfl_sync(0xffffffffu, be, (j + 1) & 31);
+      if (on) {
+        d0 = fmaf(Ps[j], b0, d0);
+        if (j + 1 < K) d1 = fmaf(Ps[j + 1], b1, d1);
+      }
+    }
+    const float d = on ? d0 + d1 : 0.f;
+    const int ec = on ? Pex[(b * nseg + s) * (int64_t)K + lane] : 0;
+    const int ve = (d > 0.f) ? (((__float_as_int(d) >> 23) & 0xff) - 126 + ec) : INT_MIN / 2;
+    int E = ve;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) E = max(E, __shfl_xor_sync(0xffffffffu, E, o));
+    if (E == INT_MIN / 2) {                              // every row vanished: flag, keep something finite
+      if (lane == 0) suspect[b] = 1;
+      be = on ? 1.f : 0.f;
+      continue;
+    }
+    be = (d > 0.f) ? ldexpf(d, ec - E) : 0.f;
+  }
+  if (on) bin[(b * nseg) * (int64_t)K + lane] = be;
 }
 
 }  // namespace hx
