@@ -205,17 +205,24 @@ int hmm_param_grads(const vhmm_dims& d, const vhmm_params& P, const float* x, co
   // ---- decoder backward on the K one-hot sequences ----
   onehot_kernel<<<(unsigned)cdiv((int64_t)K * K * T, 256), 256, 0, st>>>(qh, K, (int)T);
   VHMM_LAUNCH_CHECK();
-  RC(decoder_chain(d, P, qh, K, T, e, g1, g2, st));
-  RC(launch_wgrad(dp, g2, grads + off[P_DPW], grads + off[P_DPB], wview_fwd(nullptr, H, 1), K, H, 2 * C, T, 1, scratch, st));
-  RC(launch_conv(dp, wview_dgrad(P.p[P_DPW], H, 1), nullptr, g2, dg2, K, 2 * C, H, T, 1, EPI_MASK, st));
-  RC(launch_wgrad(dg2, g1, grads + off[P_D2W], grads + off[P_D2B], wview_fwd(nullptr, H, 3), K, H, H, T, 3, scratch, st));
-  RC(launch_conv(dg2, wview_dgrad(P.p[P_D2W], H, 3), nullptr, g1, dg1, K, H, H, T, 3, EPI_MASK, st));
-  RC(launch_wgrad(dg1, e, grads + off[P_D1W], grads + off[P_D1B], wview_fwd(nullptr, H, 3), K, H, H, T, 3, scratch, st));
-  RC(launch_conv(dg1, wview_dgrad(P.p[P_D1W], H, 3), nullptr, nullptr, de, K, H, H, T, 3, EPI_NONE, st));
+  // (a long table -- few long sequences -- is real work: 3 H*H*3 layers over K*T positions forward, input gradient and weight
+  //  gradient; the tensor-core layer kernels then, as in the layer-wise ELBO.  K*T = 32 x 16384 at H = 256: 43 -> ~3 ms)
+  const Tc5Ctx* dctx = ((int64_t)K * T >= 16384 && ctx.pool) ? &ctx : nullptr;
+  if (dctx) RC(ctx.reset(st));
+  RC(decoder_chain(d, P, qh, K, T, e, g1, g2, st, dctx));
+#define WG(dy, xx, gw, gb, lay, cin, cout, kw) \
+  (dctx ? cwgrad(dctx, dy, xx, gw, gb, lay, K, cin, cout, T, kw, scratch, st) : launch_wgrad(dy, xx, gw, gb, lay, K, cin, cout, T, kw, scratch, st))
+  RC(WG(dp, g2, grads + off[P_DPW], grads + off[P_DPB], wview_fwd(nullptr, H, 1), H, 2 * C, 1));
+  RC(cconv(dctx, 1, dp, wview_dgrad(P.p[P_DPW], H, 1), nullptr, g2, dg2, K, 2 * C, H, T, 1, EPI_MASK, st));
+  RC(WG(dg2, g1, grads + off[P_D2W], grads + off[P_D2B], wview_fwd(nullptr, H, 3), H, H, 3));
+  RC(cconv(dctx, 1, dg2, wview_dgrad(P.p[P_D2W], H, 3), nullptr, g1, dg1, K, H, H, T, 3, EPI_MASK, st));
+  RC(WG(dg1, e, grads + off[P_D1W], grads + off[P_D1B], wview_fwd(nullptr, H, 3), H, H, 3));
+  RC(cconv(dctx, 1, dg1, wview_dgrad(P.p[P_D1W], H, 3), nullptr, nullptr, de, K, H, H, T, 3, EPI_NONE, st));
   {
     WView embL{nullptr, 0, 1, H, 0};
     RC(launch_wgrad(de, qh, grads + off[P_EMB], nullptr, embL, K, K, H, T, 1, scratch, st));
   }
+#undef WG
 #undef RC
   // ---- initial distribution ----
   hg_::log_prior_grad_kernel<<<1, 256, 0, st>>>(gamma, w, P.p[P_LOGPRIOR], B, K, (int)T, grads + off[P_LOGPRIOR]);
