@@ -216,19 +216,41 @@ seg_carry_back_kernel(const int64_t* __restrict__ lengths, int64_t nB, int nseg,
   const int KK = K * K;
   const int ns = (L + WS_SEG - 1) / WS_SEG;
   float be = on ? 1.f : 0.f;
+  // row `lane` of a segment's product, fetched one segment ahead of the dependent chain
+  float pn[32];
+  int en = 0;
+  auto fetch = [&](int s) {
+    const float* Ps = Pmat + (b * nseg + s) * (int64_t)KK + lane * K;
+    if ((K & 3) == 0) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (on && 4 * q < K) v = *reinterpret_cast<const float4*>(Ps + 4 * q);
+        pn[4 * q] = v.x; pn[4 * q + 1] = v.y; pn[4 * q + 2] = v.z; pn[4 * q + 3] = v.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) pn[j] = (on && j < K) ? Ps[j] : 0.f;
+    }
+    en = on ? Pex[(b * nseg + s) * (int64_t)K + lane] : 0;
+  };
+  if (ns - 1 >= 1) fetch(ns - 1);
   for (int s = ns - 1; s >= 1; --s) {
     if (on) bin[(b * nseg + s) * (int64_t)K + lane] = be;
-    const float* Ps = Pmat + (b * nseg + s) * (int64_t)KK + lane * K;     // row `lane` of the segment's product
-    float d0 = 0.f, d1 = 0.f;
-    for (int j = 0; j < K; j += 2) {
-      const float b0 = __shfl_sync(0xffffffffu, be, j), b1 = __shfl_sync(0xffffffffu, be, (j + 1) & 31);
-      if (on) {
-        d0 = fmaf(Ps[j], b0, d0);
-        if (j + 1 < K) d1 = fmaf(Ps[j + 1], b1, d1);
-      }
+    float pc[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) pc[j] = pn[j];
+    const int ec = en;
+    if (s - 1 >= 1) fetch(s - 1);
+    float d0 = 0.f, d1 = 0.f, d2 = 0.f, d3 = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      d0 = fmaf(pc[j], __shfl_sync(0xffffffffu, be, j), d0);
+      d1 = fmaf(pc[j + 1], __shfl_sync(0xffffffffu, be, j + 1), d1);
+      d2 = fmaf(pc[j + 2], __shfl_sync(0xffffffffu, be, j + 2), d2);
+      d3 = fmaf(pc[j + 3], __shfl_sync(0xffffffffu, be, j + 3), d3);
     }
-    const float d = on ? d0 + d1 : 0.f;
-    const int ec = on ? Pex[(b * nseg + s) * (int64_t)K + lane] : 0;
+    const float d = on ? (d0 + d1) + (d2 + d3) : 0.f;
     const int ve = (d > 0.f) ? (((__float_as_int(d) >> 23) & 0xff) - 126 + ec) : INT_MIN / 2;
     int E = ve;
 #pragma unroll
