@@ -461,6 +461,16 @@ int hmm_posterior(const float* log_pi, const float* A, const float* Bm, const in
   return 0;
 }
 
+template <int KP>
+static int launch_vit_ring(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B, int64_t T,
+                           int64_t K, uint8_t* psi, uint8_t* path, float* score, cudaStream_t st) {
+  auto kern = (K == KP) ? hx::vit_ring_kernel<KP, true> : hx::vit_ring_kernel<KP, false>;
+  VHMM_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hx::vit_ring_smem<KP>()));
+  kern<<<(unsigned)B, 32, hx::vit_ring_smem<KP>(), st>>>(log_pi, A, Bm, lengths, B, (int)T, (int)K, psi, path, score);
+  VHMM_LAUNCH_CHECK();
+  return 0;
+}
+
 int hmm_viterbi(const float* log_pi, const float* A, const float* Bm, const int64_t* lengths, int64_t B,
                 int64_t T, int64_t K, uint8_t* path, float* score, void* ws, size_t ws_bytes,
                 cudaStream_t st) {
@@ -476,6 +486,12 @@ int hmm_viterbi(const float* log_pi, const float* A, const float* Bm, const int6
   }
   VHMM_REQUIRE(K <= 32, VHMM_E_DIMS, "hmm_viterbi: K=%lld > 32", (long long)K);
   const int wpb = 4;
+  if (wide_allowed() && wide_scan_enabled() && (K & 3) == 0 && B <= 148 && T >= 256 && aligned16(A) && aligned16(Bm)) {
+    // few sequences: one warp per CTA, inputs through a bulk-copy ring (hx::vit_ring_kernel) -- bit-identical results
+    int rc = 0;
+    DISPATCH_KP(K, (rc = launch_vit_ring<KP>(log_pi, A, Bm, lengths, B, T, K, psi, path, score, st)));
+    return rc;
+  }
   if (wide_allowed()) {
     DISPATCH_KP(K, (hx::vit_kernel<KP><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
                        log_pi, A, Bm, lengths, B, (int)T, (int)K, psi, path, score)));

@@ -318,5 +318,142 @@ vit_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const 
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Viterbi of FEW sequences: vit_kernel above keeps ONE step of log_A in flight per warp, which a batch of thousands hides and
+// four sequences do not (1.1 us per step at K = 32: the HBM latency of the step's own tile).  Same recursion, same order of
+// operations (bit-identical paths and scores), but one warp per CTA and the inputs streamed by lane 0 into a shared-memory
+// ring with cp.async.bulk + mbarrier, 4 .. 32 steps per stage and VR_NST - 1 stages ahead of the dependent chain.  Needs K % 4 == 0
+// (every step's tile and row 16-byte aligned) and 16-byte aligned log_A / log_b.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int VR_NST = 8;                                               // stages of the ring (7 in flight)
+template <int KP> struct VitRing { static constexpr int S = KP >= 32 ? 4 : (KP >= 16 ? 16 : 32); };   // steps per stage: 9 .. 17 KB
+template <int KP>
+constexpr size_t vit_ring_smem() { return (size_t)VR_NST * VitRing<KP>::S * (KP * KP + KP) * sizeof(float); }
+
+template <int KP, bool EXACT>        // EXACT: K == KP (compile-time strides)
+__global__ void __launch_bounds__(32)
+vit_ring_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const float* __restrict__ Bm,
+                const int64_t* __restrict__ lengths, int64_t nB, int T, int K, uint8_t* __restrict__ psi,
+                uint8_t* __restrict__ path, float* __restrict__ score) {
+  constexpr int VR_S = VitRing<KP>::S;
+  extern __shared__ __align__(16) float ring[];
+  __shared__ __align__(8) uint64_t full[VR_NST];
+  __shared__ uint8_t pb[32 * KP];
+  __shared__ uint8_t ob[32];
+  __shared__ __align__(16) float dls[32];
+  const int lane = threadIdx.x;
+  const int64_t b = blockIdx.x;
+  if (b >= nB) return;
+  const int64_t L64 = lengths[b];
+  const int L = (int)(L64 < 0 ? 0 : (L64 > T ? T : L64));
+  const bool on = lane < K;
+  const int KK = K * K;
+  const float* Ab = A + b * (int64_t)T * KK;
+  const float* Bb = Bm + b * (int64_t)T * K;
+  uint8_t* ps = psi + b * (int64_t)T * K;
+  uint8_t* pr = path + b * (int64_t)T;
+  for (int t = L + lane; t < T; t += 32) pr[t] = VHMM_PAD_STATE;
+  float dl = (L > 0 && on) ? __fadd_rn(log_pi[lane], Bb[lane]) : -INFINITY;
+  const int stage_floats = VR_S * (KK + K);            // A tiles of the stage's steps, then their b rows
+  auto s32 = [](const void* p) { return (uint32_t)__cvta_generic_to_shared(p); };
+  if (lane == 0) {
+#pragma unroll
+    for (int i = 0; i < VR_NST; ++i)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(s32(&full[i])), "r"(1) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+  const int nst = (L + VR_S - 1) / VR_S;               // stage c holds steps [c*VR_S, min(L, (c+1)*VR_S))
+  auto issue = [&](int c) {
+    float* st = ring + (c % VR_NST) * stage_floats;
+    const int n = min(VR_S, L - c * VR_S);
+    const uint32_t ba = (uint32_t)n * KK * 4u, bb = (uint32_t)n * K * 4u;
+    uint64_t* bar = &full[c % VR_NST];
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(s32(bar)), "r"(ba + bb) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(s32(st)), "l"(Ab + (int64_t)c * VR_S * KK), "r"(ba), "r"(s32(bar)) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(s32(st + VR_S * KK)), "l"(Bb + (int64_t)c * VR_S * K), "r"(bb), "r"(s32(bar)) : "memory");
+  };
+  if (lane == 0)
+    for (int c = 0; c < VR_NST - 1 && c < nst; ++c) issue(c);
+  for (int c = 0; c < nst; ++c) {
+    __syncwarp();                                      // every lane is done with the stage that is refilled now
+    if (lane == 0 && c + VR_NST - 1 < nst) issue(c + VR_NST - 1);
+    {
+      const uint32_t a = s32(&full[c % VR_NST]), parity = (uint32_t)(c / VR_NST) & 1u;
+      uint32_t ok = 0;
+      for (int it = 0; it < (1 << 24) && !ok; ++it)
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+      if (!ok) __trap();
+    }
+    const float* sA = ring + (c % VR_NST) * stage_floats;
+    const float* sB = sA + VR_S * KK;
+    const int n = min(VR_S, L - c * VR_S);
+    for (int s = 0; s < n; ++s) {
+      const int t = c * VR_S + s;
+      if (t == 0) continue;                            // step 0 is the initial vector
+      // every lane needs the whole vector dl: through shared memory (one store, KP/4 broadcast 16-byte loads) instead of
+      // KP shuffles
+      dls[lane] = dl;
+      __syncwarp();
+      float dv[KP];
+#pragma unroll
+      for (int q = 0; q < KP / 4; ++q) {
+        const float4 v = reinterpret_cast<const float4*>(dls)[q];
+        dv[4 * q] = v.x; dv[4 * q + 1] = v.y; dv[4 * q + 2] = v.z; dv[4 * q + 3] = v.w;
+      }
+      __syncwarp();
+      // column `lane` of the step's tile (lanes >= K read neighbouring words of the stage: unused)
+      const int Kc = EXACT ? KP : K;
+      const float* col = sA + s * (Kc * Kc) + lane;
+      const float bc = sB[s * Kc + (on ? lane : 0)];
+      // max_i (dl[i] + a[i]) and the LOWEST i attaining it.  vit_kernel scans i upwards with a strict '>' -- a dependent chain
+      // of K compare/select pairs; here a tree of (value, index) pairs whose nodes take the right operand only when it is
+      // strictly greater: the same result (lowest index on ties), depth log2 K.
+      float cv[KP];
+      int ci[KP];
+#pragma unroll
+      for (int i = 0; i < KP; ++i) {
+        cv[i] = (EXACT || i < K) ? __fadd_rn(dv[i], col[i * Kc]) : -INFINITY;
+        ci[i] = i;
+      }
+#pragma unroll
+      for (int w = 1; w < KP; w <<= 1) {
+#pragma unroll
+        for (int i = 0; i + w < KP; i += 2 * w) {
+          const bool r = cv[i + w] > cv[i];
+          cv[i] = r ? cv[i + w] : cv[i];
+          ci[i] = r ? ci[i + w] : ci[i];
+        }
+      }
+      dl = on ? __fadd_rn(bc, cv[0]) : -INFINITY;
+      if (on) ps[(int64_t)t * K + lane] = (uint8_t)ci[0];
+    }
+  }
+  const float m = wmax(dl);
+  const unsigned ball = __ballot_sync(0xffffffffu, on && dl == m);
+  int state = ball ? __ffs(ball) - 1 : 0;             // lowest index attaining the max
+  if (lane == 0 && score) score[b] = (L > 0) ? m : 0.f;
+  __syncwarp();                                        // psi written by the lanes is visible to the warp
+  for (int hi = L - 1; hi >= 0; hi -= 32) {
+    const int lo = hi - 31 > 0 ? hi - 31 : 0;
+    const int n = hi - lo + 1;
+    for (int e = lane; e < n * K; e += 32) pb[e] = ps[(int64_t)lo * K + e];
+    __syncwarp();
+    if (lane == 0) {
+      for (int t = hi; t >= lo; --t) {
+        ob[t - lo] = (uint8_t)state;
+        if (t >= 1) state = pb[(t - lo) * K + state];
+      }
+    }
+    __syncwarp();
+    state = __shfl_sync(0xffffffffu, state, 0);
+    if (lane < n) pr[lo + lane] = ob[lane];
+    __syncwarp();
+  }
+}
+
 }  // namespace hx
 }  // namespace vhmm
