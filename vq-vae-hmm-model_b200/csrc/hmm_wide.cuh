@@ -338,7 +338,7 @@ vit_ring_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, c
   constexpr int VR_S = VitRing<KP>::S;
   extern __shared__ __align__(16) float ring[];
   __shared__ __align__(8) uint64_t full[VR_NST];
-  __shared__ uint8_t pb[32 * KP];
+  __shared__ __align__(16) uint8_t pb[32 * KP];
   __shared__ uint8_t ob[32];
   __shared__ __align__(16) float dls[32];
   const int lane = threadIdx.x;
@@ -437,10 +437,30 @@ vit_ring_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, c
   int state = ball ? __ffs(ball) - 1 : 0;             // lowest index attaining the max
   if (lane == 0 && score) score[b] = (L > 0) ? m : 0.f;
   __syncwarp();                                        // psi written by the lanes is visible to the warp
-  for (int hi = L - 1; hi >= 0; hi -= 32) {
-    const int lo = hi - 31 > 0 ? hi - 31 : 0;
+  // back-track in 32-step blocks ALIGNED to multiples of 32 steps: a block's back-pointers are 32*K contiguous bytes that the
+  // warp fetches with 16-byte loads one block AHEAD of the walk, lane 0 walks the block in shared memory
+  const bool wide_ok = (((int64_t)T * K) & 15) == 0;  // (K % 4 == 0: a block is 2 K 16-byte words, at most 64)
+  const int nv = 2 * K;
+  uint4 pre[2];
+  auto fetch = [&](int lo, int n) {                   // registers <- back-pointers of steps [lo, lo+n)
+    if (wide_ok && n == 32) {
+      const uint4* src = reinterpret_cast<const uint4*>(ps + (int64_t)lo * K);
+      if (lane < nv) pre[0] = src[lane];
+      if (32 + lane < nv) pre[1] = src[32 + lane];
+    }
+  };
+  int hi = L - 1;
+  int lo = hi >= 0 ? (hi & ~31) : 0;
+  if (hi >= 0) fetch(lo, hi - lo + 1);
+  while (hi >= 0) {
     const int n = hi - lo + 1;
-    for (int e = lane; e < n * K; e += 32) pb[e] = ps[(int64_t)lo * K + e];
+    if (wide_ok && n == 32) {
+      if (lane < nv) reinterpret_cast<uint4*>(pb)[lane] = pre[0];
+      if (32 + lane < nv) reinterpret_cast<uint4*>(pb)[32 + lane] = pre[1];
+    } else {
+      for (int e = lane; e < n * K; e += 32) pb[e] = ps[(int64_t)lo * K + e];
+    }
+    if (lo >= 32) fetch(lo - 32, 32);                 // the next block, in flight during the walk
     __syncwarp();
     if (lane == 0) {
       for (int t = hi; t >= lo; --t) {
@@ -452,6 +472,8 @@ vit_ring_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, c
     state = __shfl_sync(0xffffffffu, state, 0);
     if (lane < n) pr[lo + lane] = ob[lane];
     __syncwarp();
+    hi = lo - 1;
+    lo -= 32;
   }
 }
 
