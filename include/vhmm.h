@@ -331,7 +331,10 @@ int vhmm_hmm_param_grads(const vhmm_dims* dims, const vhmm_params* params, const
  * (the last one of a sequence may be shorter): segment
  * products, a forward and a backward carry scan per sequence (incoming alpha / outgoing beta of every segment, the
  * log-likelihood), then the ONEPASS kernel on the segment rows; the inputs cross HBM twice.  (The sweep kernels run one
- * thread per sequence: 94 ms at B = 64, T = 65536 against 0.16 ms.) */
+ * thread per sequence: 94 ms at B = 64, T = 65536 against 0.16 ms.)
+ * 4 < K <= 32 with T >= 512 and B <= 256 (few long sequences; needs the workspace vhmm_workspace_bytes reports, a smaller one
+ * takes the warp-per-sequence kernels): 128-step segment products (K x K), forward and backward carries, then the
+ * warp-per-sequence forward / backward kernels on the segment rows; environment VHMM_WIDE_SCAN=off disables it. */
 enum { VHMM_POSTERIOR_AUTO = 0, VHMM_POSTERIOR_SWEEP = 1 };
 int vhmm_hmm_posterior_select(int variant);
 /* Numerics of the sum-product recursions (vhmm_hmm_forward / _posterior / _decode / _scan and what is built on them).
@@ -347,7 +350,9 @@ int vhmm_hmm_posterior_select(int variant);
  *                           several times slower.  Viterbi is max-plus in log space in both modes (bit-exact paths). */
 enum { VHMM_NUMERICS_SCALED = 0, VHMM_NUMERICS_LOGSPACE = 1 };
 int vhmm_hmm_numerics_select(int mode);
-/* B.4: Viterbi, uint8 back-pointers, lowest-index tie-break.  path (B,T) uint8, score (B). */
+/* B.4: Viterbi, uint8 back-pointers, lowest-index tie-break.  path (B,T) uint8, score (B).  The recursion is serial in time
+ * (bit-exact max-plus); FEW sequences (K <= 4: B < 2368, T % 4 == 0; 4 < K <= 32: B <= 148, K % 4 == 0) take one warp each
+ * with the inputs streamed through a shared-memory ring -- the same paths and scores as the batch kernels. */
 int vhmm_viterbi(const float* log_pi, const float* log_A, const float* log_b,
                  const int64_t* lengths, int64_t B, int64_t T, int64_t K, uint8_t* path,
                  float* score, void* workspace, size_t workspace_bytes, void* stream);
