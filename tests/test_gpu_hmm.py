@@ -769,3 +769,24 @@ def test_posterior_wide_k_of_few_long_sequences_by_rows(K, T):
     assert np.abs(gamma3.cpu().numpy() - g64).max() <= TOL
     pv, _ = Fn.viterbi(*d)
     assert np.array_equal(path.cpu().numpy(), pv.cpu().numpy())
+
+
+@pytest.mark.parametrize("dims", [(5, 64, 3, 32, 4, 128), (4, 16, 6, 8, 3, 32)])
+def test_emission_table_of_long_sequences_repeats_its_middle_column(dims):
+    """The decoder's input for the emission table is constant over time and its receptive field is +-2 steps, so for T > 16 the
+    table is computed on 16 steps and its middle column repeated (csrc/elbo_layerwise.cu): every column, the edges included,
+    against the float64 oracle decoder on the full-length one-hot sequences."""
+    import vhmm_b200 as V
+    from vhmm_b200 import functional as Fn
+    from oracle import elbo as O
+    C, Hd, K, H2, U, TH = dims
+    p = O.init_params(C, Hd, K, H2, U, TH, seed=13)
+    m = V.VAE_HMM(C, Hd, K, H2, u_dim=U, trans_hidden=TH)
+    m.load_state_dict(p)
+    m = m.cuda()
+    p64 = {k: v.double() for k, v in p.items()}
+    for T in (16, 17, 20, 23, 301):
+        mu64, lv64 = H.emission_table(p64, T, O.decode)
+        mu, lv = Fn.emission_table(m._dims, m._params(), T, torch.device("cuda"))
+        assert np.abs(mu.cpu().numpy() - mu64.numpy()).max() <= TOL * max(1.0, float(mu64.abs().max())), T
+        assert np.abs(lv.cpu().numpy() - lv64.numpy()).max() <= TOL * max(1.0, float(lv64.abs().max())), T

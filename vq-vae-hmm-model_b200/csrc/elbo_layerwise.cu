@@ -300,7 +300,7 @@ size_t layerwise_workspace_bytes(int op, const vhmm_dims& d, int64_t B, int64_t 
     case VHMM_OP_DECODER_FWD:
       return (size_t)B * T * (3 * (int64_t)d.H) * 4 + slack + tc5_ctx_bytes(d);
     case VHMM_OP_EMISSION_TABLE:
-      return (size_t)d.K * T * (3 * (int64_t)d.H + d.K + 2 * d.C) * 4 + slack + tc5_ctx_bytes(d);
+      return (size_t)d.K * T * (3 * (int64_t)d.H + d.K + 2 * d.C) * 4 + slack + tc5_ctx_bytes(d) + 4096;
     case VHMM_OP_ELBO:
       return fixed_bytes(d, T) + (size_t)Bc * T * (s.per_step_fwd + s.per_step_bwd) * 4 +
              (size_t)Bc * cdiv(T, 32) * 32 + slack;
@@ -618,8 +618,36 @@ __global__ void onehot_kernel(float* __restrict__ q, int K, int T) {
   q[i] = (row / K == row % K) ? 1.f : 0.f;
 }
 
+// The decoder's input here is CONSTANT over time (the one-hot of state k at every step) and its receptive field is +-2 steps
+// (1x1, k=3, k=3, 1x1), so every position further than 2 steps from both ends sees the same window: the table of a long
+// sequence is the table of a 16-step one with its middle column repeated.  (K*T positions through three H x H x 3 layers
+// otherwise: 2 ms at K = 32, H = 256, T = 16384 -- most of hmm_inputs for few long sequences.)
+constexpr int kTabShort = 16, kTabEdge = 4;
+__global__ void __launch_bounds__(256) expand_table_kernel(const float* __restrict__ mu_s, const float* __restrict__ lv_s, int64_t rows,
+                                                           int T, float* __restrict__ mu, float* __restrict__ lv) {
+  const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (i >= rows * T) return;
+  const int64_t r = i / T;
+  const int t = (int)(i - r * T);
+  const int ts = t < kTabEdge ? t : (t >= T - kTabEdge ? kTabShort - (T - t) : kTabShort / 2);
+  mu[i] = mu_s[r * kTabShort + ts];
+  lv[i] = lv_s[r * kTabShort + ts];
+}
+
 int layerwise_emission_table(const vhmm_dims& d, const vhmm_params& P, int64_t T, float* mu_tab,
                              float* logvar_tab, void* ws, size_t ws_bytes, cudaStream_t st) {
+  if (T > kTabShort) {
+    Arena S(ws, ws_bytes);
+    float* mu_s = S.take<float>((size_t)d.K * d.C * kTabShort);
+    float* lv_s = S.take<float>((size_t)d.K * d.C * kTabShort);
+    VHMM_REQUIRE(S.ok, VHMM_E_WORKSPACE, "emission_table: workspace too small");
+    int rc = layerwise_emission_table(d, P, kTabShort, mu_s, lv_s, (char*)ws + S.used, ws_bytes - S.used, st);
+    if (rc) return rc;
+    const int64_t n = (int64_t)d.K * d.C * T;
+    expand_table_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(mu_s, lv_s, (int64_t)d.K * d.C, (int)T, mu_tab, logvar_tab);
+    VHMM_LAUNCH_CHECK();
+    return 0;
+  }
   Arena A(ws, ws_bytes);
   float* q = A.take<float>((size_t)d.K * d.K * T);
   VHMM_REQUIRE(A.ok, VHMM_E_WORKSPACE, "emission_table: workspace too small");
