@@ -384,9 +384,9 @@ int vhmm_hmm_decode(const float* log_pi, const float* log_A, const float* log_b,
                     void* stream);
 /* B.5: log-semiring parallel scan over T (long sequences, small batch).  loglik (B);
  * alpha (B,T,K) all-prefix forward variables or NULL.  K <= 4: 256-step segments on the one-pass warp kernel + carry
- * scan (sequences that fit one warp, T < 512, are the one-pass kernel itself).  4 < K <= 32, alpha == NULL, T >= 512,
- * B <= 256: 128-step segment products (K x K, one warp each, row-wise power-of-two scaling) + per-sequence carry;
- * otherwise the warp-per-sequence forward of vhmm_hmm_forward (same results). */
+ * scan (sequences that fit one warp, T < 512, are the one-pass kernel itself).  4 < K <= 32, T >= 512, B <= 256:
+ * 128-step segment products (K x K, one warp each, row-wise power-of-two scaling) + per-sequence carry (+ the forward
+ * kernel on the segment rows for alpha); otherwise the warp-per-sequence forward of vhmm_hmm_forward (same results). */
 int vhmm_hmm_scan(const float* log_pi, const float* log_A, const float* log_b,
                   const int64_t* lengths, int64_t B, int64_t T, int64_t K, float* loglik,
                   float* alpha, void* workspace, size_t workspace_bytes, void* stream);

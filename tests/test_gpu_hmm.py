@@ -744,6 +744,20 @@ def test_scan_loglik_wide_k_by_segment_products(K, T):
         assert np.allclose(ll_seq[live], ll64[live], rtol=TOL, atol=1e-5)
         assert np.array_equal(ll_auto, ll_scan)
         assert (ll_scan[~live] == 0).all()
+        # all-prefix log alpha: the forward kernel on the 128-step rows (incoming vector and log-scale from the carry)
+        alpha64, _ = H.forward(lp, la, lb, np.maximum(L, 1))
+        ll_a, alpha = Fn.hmm_scan(*d, want_alpha=True)
+        _, alpha_seq = Fn.hmm_forward(*d, want_alpha=True, time_parallel=False)
+        a, a_seq = alpha.cpu().numpy(), alpha_seq.cpu().numpy()
+        scale = max(1.0, np.abs(alpha64[live]).max())
+        # (scaled linear recursions: a state more than e^-87 below the step's best flushes to log 0 -- include/vhmm.h,
+        #  vhmm_hmm_numerics_select -- so the comparison takes the entries within 60 nats of each step's maximum)
+        fin = alpha64[live] > alpha64[live].max(-1, keepdims=True) - 60.0
+        assert np.abs((a[live] - alpha64[live])[fin]).max() <= 2e-5 * scale, (K, T, sharp)
+        both = np.isfinite(a_seq) & np.isfinite(a)
+        assert np.array_equal(np.isfinite(a_seq), np.isfinite(a))
+        assert np.abs(a[both] - a_seq[both]).max() <= 2e-5 * scale          # incl. the rows carried beyond the length
+        assert np.allclose(ll_a.cpu().numpy()[live], ll64[live], rtol=TOL, atol=1e-5)
 
 
 @pytest.mark.parametrize("K,T", [(32, 640), (16, 1000), (6, 777), (7, 1280), (32, 515)])

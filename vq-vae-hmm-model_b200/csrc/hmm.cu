@@ -406,13 +406,13 @@ int hmm_posterior(const float* log_pi, const float* A, const float* Bm, const in
                          A, Bm, lengths, rows, (int)nseg, (int)T, (int)K, Pmat, Pex, mbs)));
       VHMM_LAUNCH_CHECK();
       hx::seg_carry_kernel<<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(log_pi, Bm, lengths, B, (int)nseg, (int)T, (int)K,
-                                                                              Pmat, Pex, mbs, loglik, suspect, vin);
+                                                                              Pmat, Pex, mbs, loglik, suspect, vin, nullptr, nullptr);
       VHMM_LAUNCH_CHECK();
       hx::seg_carry_back_kernel<<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(lengths, B, (int)nseg, (int)T, (int)K, Pmat, Pex,
                                                                                    bin, suspect);
       VHMM_LAUNCH_CHECK();
-      const hx::RowView rv{(int)nseg, hx::WS_SEG, vin, bin, nullptr};
-      const hx::RowView redo{0, 0, nullptr, nullptr, suspect};
+      const hx::RowView rv{(int)nseg, hx::WS_SEG, vin, bin, nullptr, nullptr, nullptr};
+      const hx::RowView redo{0, 0, nullptr, nullptr, suspect, nullptr, nullptr};
       DISPATCH_KP(K, (hx::fwd_kernel<KP, true><<<(unsigned)cdiv(rows, hx::WPB), hx::WPB * 32, 0, st>>>(
                          log_pi, A, Bm, lengths, rows, (int)T, (int)K, nullptr, nullptr, stash, rv)));
       VHMM_LAUNCH_CHECK();
@@ -624,22 +624,32 @@ int hmm_scan(const float* log_pi, const float* A, const float* Bm, const int64_t
   if (!small_k(K)) {
     // 4 < K <= 32, log-likelihood of few long sequences: segment products + carry (hmm_wide_scan.cuh); K^3 work per step
     // instead of K^2, but over B*T/128 warps -- it wins while the batch alone cannot fill the machine
-    if (!alpha && loglik && K > 4 && K <= 32 && wide_allowed() && wide_scan_enabled() && T >= 512 && B <= 256) {
+    if (loglik && K > 4 && K <= 32 && wide_allowed() && wide_scan_enabled() && T >= 512 && B <= 256) {
       const int64_t nseg = cdiv(T, (int64_t)hx::WS_SEG), rows = B * nseg;
       Arena ar(ws, ws_bytes);
       float* Pmat = ar.take<float>((size_t)rows * K * K);
       int* Pex = ar.take<int>((size_t)rows * K);
       float* mbs = ar.take<float>((size_t)rows);
       int* suspect = ar.take<int>((size_t)B);
+      float* vin = alpha ? ar.take<float>((size_t)rows * K) : nullptr;
+      double* ll_in = alpha ? ar.take<double>((size_t)rows) : nullptr;
+      float* carried = alpha ? ar.take<float>((size_t)B * K) : nullptr;
       VHMM_REQUIRE(ar.ok, VHMM_E_WORKSPACE, "hmm_scan: workspace %zu < %zu", ws_bytes, ar.used);
       DISPATCH_KP(K, (hx::seg_product_kernel<KP><<<(unsigned)cdiv(rows, hx::WS_WPB), hx::WS_WPB * 32, 0, st>>>(
                          A, Bm, lengths, rows, (int)nseg, (int)T, (int)K, Pmat, Pex, mbs)));
       VHMM_LAUNCH_CHECK();
       hx::seg_carry_kernel<<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(log_pi, Bm, lengths, B, (int)nseg, (int)T, (int)K,
-                                                                              Pmat, Pex, mbs, loglik, suspect, nullptr);
+                                                                              Pmat, Pex, mbs, loglik, suspect, vin, ll_in, carried);
       VHMM_LAUNCH_CHECK();
+      if (alpha) {   // all-prefix log alpha: the forward kernel on the 128-step rows, each from its incoming vector and log-scale
+        const hx::RowView rv{(int)nseg, hx::WS_SEG, vin, nullptr, nullptr, ll_in, carried};
+        DISPATCH_KP(K, (hx::fwd_kernel<KP, true><<<(unsigned)cdiv(rows, hx::WPB), hx::WPB * 32, 0, st>>>(
+                           log_pi, A, Bm, lengths, rows, (int)T, (int)K, nullptr, alpha, nullptr, rv)));
+        VHMM_LAUNCH_CHECK();
+      }
+      const hx::RowView redo{0, 0, nullptr, nullptr, suspect, nullptr, nullptr};
       DISPATCH_KP(K, (hx::fwd_kernel<KP><<<(unsigned)cdiv(B, hx::WPB), hx::WPB * 32, 0, st>>>(
-                         log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, nullptr, nullptr, hx::RowView{0, 0, nullptr, nullptr, suspect})));   // flagged only
+                         log_pi, A, Bm, lengths, B, (int)T, (int)K, loglik, alpha, nullptr, redo)));   // flagged sequences only
       VHMM_LAUNCH_CHECK();
       return 0;
     }

@@ -63,6 +63,8 @@ struct RowView {
   const float* vin;      // (rows, K) alpha_hat at the step before the row (row 0: unused)
   const float* bin;      // (rows, K) beta_hat at the row's last valid step (last valid row: unused, ones)
   const int* only;       // per sequence: 0 = skip (redo pass for flagged sequences), or null
+  const double* ll_in;   // (rows) log-normaliser accumulated before the row   } all-prefix log alpha by rows
+  const float* carried;  // (B, K) log alpha of the sequence's last valid step  }
 };
 
 template <int KP, bool ROWS = false>
@@ -101,6 +103,7 @@ fwd_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const 
     }
   } else if (ROWS && L > 0) {
     v = on ? rv.vin[w * K + lane] : 0.f;          // a later row: its step 0 is a recursion step like any other
+    if (alpha) ll = rv.ll_in[w];
   }
   const int tb = first ? 1 : 0;
   float an[KP], bn = -INFINITY;
@@ -138,7 +141,14 @@ fwd_kernel(const float* __restrict__ log_pi, const float* __restrict__ A, const 
       if (ahat) ahat[(s0 + t) * K + lane] = v;
     }
   }
-  if (ROWS) return;                                // rows: alpha_hat only (log-likelihood and log alpha belong to whole sequences)
+  if (ROWS) {                                      // rows: steps beyond the length repeat the sequence's last valid row (B.2)
+    if (alpha && on) {
+      const float carried = rv.carried[b * K + lane];
+      const int cap = min(rv.seg, T - t0);
+      for (int t = L; t < cap; ++t) alpha[(s0 + t) * K + lane] = carried;
+    }
+    return;
+  }
   if (lane == 0 && loglik) loglik[b] = (L > 0) ? (float)ll : 0.f;
   if (alpha && on) {
     const float carried = logf(v) + (float)ll;

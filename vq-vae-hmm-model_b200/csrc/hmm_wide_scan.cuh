@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(WPB * 32)
 seg_carry_kernel(const float* __restrict__ log_pi, const float* __restrict__ Bm, const int64_t* __restrict__ lengths,
                  int64_t nB, int nseg, int T, int K, const float* __restrict__ Pmat, const int* __restrict__ Pex,
                  const float* __restrict__ mbsum, float* __restrict__ loglik, int* __restrict__ suspect,
-                 float* __restrict__ vin) {
+                 float* __restrict__ vin, double* __restrict__ ll_in, float* __restrict__ carried) {
   const int lane = threadIdx.x & 31;
   const int64_t b = (int64_t)blockIdx.x * WPB + (threadIdx.x >> 5);
   if (b >= nB) return;
@@ -146,7 +146,11 @@ seg_carry_kernel(const float* __restrict__ log_pi, const float* __restrict__ Bm,
   const int L = (int)(L64 < 0 ? 0 : (L64 > T ? T : L64));
   const bool on = lane < K;
   if (lane == 0) suspect[b] = 0;
-  if (L == 0) { if (lane == 0 && loglik) loglik[b] = 0.f; return; }
+  if (L == 0) {
+    if (lane == 0 && loglik) loglik[b] = 0.f;
+    if (carried && on) carried[b * K + lane] = logf(0.f);      // what hx::fwd_kernel carries for an empty sequence
+    return;
+  }
   const int KK = K * K;
   const float x = on ? log_pi[lane] + Bm[b * (int64_t)T * K + lane] : -INFINITY;
   const float m = wmax(x);
@@ -174,6 +178,7 @@ seg_carry_kernel(const float* __restrict__ log_pi, const float* __restrict__ Bm,
       en = on ? Pex[(b * nseg + s + 1) * (int64_t)K + lane] : 0;
     }
     if (vin && on) vin[(b * nseg + s) * (int64_t)K + lane] = v;      // alpha_hat at the step before segment s
+    if (ll_in && lane == 0) ll_in[b * nseg + s] = ll;                // ... and its log-normaliser
     // weight of row `lane`: v * 2^ex, brought to the largest exponent among the rows that carry mass
     const int ve = (v > 0.f) ? (((__float_as_int(v) >> 23) & 0xff) - 126 + ec) : INT_MIN / 2;
     int E = ve;
@@ -199,6 +204,7 @@ seg_carry_kernel(const float* __restrict__ log_pi, const float* __restrict__ Bm,
     if (loglik) loglik[b] = (float)ll;
     if (bad) suspect[b] = 1;
   }
+  if (carried && on) carried[b * K + lane] = logf(v) + (float)ll;
 }
 
 // beta_hat at the last valid step of every segment row, backwards: bin[last valid row] = 1, bin[s-1] = normalise(P_s bin[s]).

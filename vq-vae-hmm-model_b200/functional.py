@@ -484,8 +484,8 @@ def hmm_forward(log_pi, log_A, log_b, lengths=None, want_alpha=False, time_paral
     if time_parallel is None:
         time_parallel = log_b.dim() == 3 and log_b.shape[1] >= 1024 and log_b.shape[0] < 2368 and log_b.shape[2] <= 4 \
             and (log_b.shape[1] * log_b.shape[2]) % 4 == 0
-        # 4 < K <= 32: segment products + carry (csrc/hmm_wide_scan.cuh), log-likelihood only
-        time_parallel = time_parallel or (log_b.dim() == 3 and not want_alpha and 4 < log_b.shape[2] <= 32
+        # 4 < K <= 32: segment products + carry (+ the forward kernel on 128-step rows for alpha): csrc/hmm_wide_scan.cuh
+        time_parallel = time_parallel or (log_b.dim() == 3 and 4 < log_b.shape[2] <= 32
                                           and log_b.shape[1] >= 512 and log_b.shape[0] <= 256)
     if time_parallel:
         return hmm_scan(log_pi, log_A, log_b, lengths, want_alpha=want_alpha)
