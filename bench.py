@@ -293,6 +293,23 @@ def run_stages(torch, V, Fn, model, dev, local, pk, quick=False):
         del log_A, log_b
         Fn.release_workspaces()
         torch.cuda.empty_cache()
+        # ---- K = 32 on FEW LONG sequences: segment products + carries (K^3 work per step over B*T/128 warps)
+        B, T = 4, 16384
+        cfg = f"K=32 few long: B={B} T={T} K={K} (277 MB of inputs)"
+        log_pi, log_A, log_b = synth_hmm_inputs(torch, dev, B, T, K, 13)
+        L = torch.full((B,), T, dtype=torch.int64, device=dev)
+        for name, bps, fn, note in (
+                ("hmm_scan K=32 of long sequences (log-likelihood)", inb, lambda: Fn.hmm_scan(log_pi, log_A, log_b, L),
+                 "K x K segment products (one warp per 128 steps) + per-sequence carry; the warp-per-sequence forward took 18.8 ms"),
+                ("hmm_posterior K=32 of long sequences (gamma)", inb + 4 * K, lambda: Fn.hmm_posterior(log_pi, log_A, log_b, L, want_xi=False),
+                 "segment products, forward and backward carries, then the forward / backward kernels on 128-step rows (three reads of the inputs)"),
+                ("viterbi K=32 of long sequences", inb + 1, lambda: Fn.viterbi(log_pi, log_A, log_b, L),
+                 "serial in time (bit-exact max-plus): one warp per sequence, bulk-copy input ring, (value, index) tree; issue-bound")):
+            ms, it, ck = timed_stage(torch, fn, local, mn, max_iters=500)
+            out.append(stage_line(name, cfg, ms, it, ck, B * T, bps, pk, note=note))
+        del log_A, log_b
+        Fn.release_workspaces()
+        torch.cuda.empty_cache()
     return out
 
 
