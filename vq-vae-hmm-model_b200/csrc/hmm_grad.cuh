@@ -95,6 +95,39 @@ __global__ void table_reduce_kernel(const float* __restrict__ part, int nslice, 
   dp[(k * 2 * C + (int64_t)which * C) * T + ct] = (float)a;
 }
 
+// The decoder's input for the emission table is constant over time and the decoder's receptive field is +-2 steps, so every
+// forward activation (and ReLU mask) at positions 2 .. T-3 is the same, the backward is linear in dp and shift-invariant
+// there, and the parameter gradients are SUMS over t.  Hence the columns 8 .. T-9 of dp may be replaced by their sum in one
+// column: the surrogate table gradient of 25 columns
+//     [ dp[:, 0..7] | 0 0 0 0 | sum_{t=8}^{T-9} dp[:, t] | 0 0 0 0 | dp[:, T-8..T-1] ]
+// run through the decoder backward of a 25-step one-hot sequence gives the same parameter gradients (the summed column's
+// signal spreads over +-2 positions, pairs with activations +-1 further: all interior-class; the edge columns keep their
+// distance to their end).  K*25 positions instead of K*T through three H x H x 3 layers, backward and recompute.
+constexpr int kTabGradCols = 25, kTabGradEdge = 8;
+__global__ void __launch_bounds__(256) collapse_table_grad_kernel(const float* __restrict__ dp, int64_t rows, int T, float* __restrict__ dps) {
+  const int64_t r = blockIdx.x;                       // one CTA per row (k, channel)
+  if (r >= rows) return;
+  const float* src = dp + r * (int64_t)T;
+  float* dst = dps + r * kTabGradCols;
+  __shared__ double red[256];
+  double a = 0.0;
+  for (int t = kTabGradEdge + threadIdx.x; t < T - kTabGradEdge; t += 256) a += (double)src[t];
+  red[threadIdx.x] = a;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x < kTabGradCols) {
+    const int j = threadIdx.x;
+    float v = 0.f;
+    if (j < kTabGradEdge) v = src[j];
+    else if (j >= kTabGradCols - kTabGradEdge) v = src[T - kTabGradCols + j];
+    else if (j == kTabGradCols / 2) v = (float)red[0];
+    dst[j] = v;
+  }
+}
+
 // g[k] = sum_b w_b gamma[b,0,k]; grad_log_prior[k] += g[k] - softmax(log_prior)[k] sum(g).  one block of 256.
 __global__ void log_prior_grad_kernel(const float* __restrict__ gamma, const float* __restrict__ w,
                                       const float* __restrict__ log_prior, int64_t B, int K, int T,
@@ -136,6 +169,11 @@ size_t hmm_param_grads_workspace_bytes(const vhmm_dims& d, int64_t B, int64_t T)
   s += align_up((size_t)d.K * T * (d.K + 2 * d.C + 3 * (int64_t)d.H + 2 * d.C + 3 * (int64_t)d.H) * 4, 256) + 16 * 256;
   s += tc5_ctx_bytes(d);          // prepared tensor-core weights (wide models)
   return s + 4096;
+}
+
+static bool hmm_table_collapse_enabled() {   // environment VHMM_TABLE_COLLAPSE=off: the decoder backward over all K*T positions
+  static const bool on = [] { const char* e = getenv("VHMM_TABLE_COLLAPSE"); return !(e && e[0] == 'o'); }();
+  return on;
 }
 
 // grads: flat float[vhmm_param_count], OVERWRITTEN with d loss / d params for loss = sum_b w[b] loglik[b].
@@ -203,24 +241,34 @@ int hmm_param_grads(const vhmm_dims& d, const vhmm_params& P, const float* x, co
     VHMM_LAUNCH_CHECK();
   }
   // ---- decoder backward on the K one-hot sequences ----
-  onehot_kernel<<<(unsigned)cdiv((int64_t)K * K * T, 256), 256, 0, st>>>(qh, K, (int)T);
+  // a long table: its interior collapsed into one column (collapse_table_grad_kernel above): 25 steps instead of T
+  int64_t Tb = T;
+  const float* dpb = dp;
+  if (T > 64 && hmm_table_collapse_enabled()) {
+    float* dps = part;                                  // (the slices are reduced: the buffer is free; K*2C*25 <= its size)
+    hg_::collapse_table_grad_kernel<<<(unsigned)(K * 2 * C), 256, 0, st>>>(dp, (int64_t)K * 2 * C, (int)T, dps);
+    VHMM_LAUNCH_CHECK();
+    Tb = hg_::kTabGradCols;
+    dpb = dps;
+  }
+  onehot_kernel<<<(unsigned)cdiv((int64_t)K * K * Tb, 256), 256, 0, st>>>(qh, K, (int)Tb);
   VHMM_LAUNCH_CHECK();
-  // (a long table -- few long sequences -- is real work: 3 H*H*3 layers over K*T positions forward, input gradient and weight
-  //  gradient; the tensor-core layer kernels then, as in the layer-wise ELBO.  K*T = 32 x 16384 at H = 256: 43 -> ~3 ms)
-  const Tc5Ctx* dctx = ((int64_t)K * T >= 16384 && ctx.pool) ? &ctx : nullptr;
+  // (a long table that is NOT collapsed is real work: 3 H*H*3 layers over K*T positions forward, input gradient and weight
+  //  gradient; the tensor-core layer kernels then, as in the layer-wise ELBO)
+  const Tc5Ctx* dctx = ((int64_t)K * Tb >= 16384 && ctx.pool) ? &ctx : nullptr;
   if (dctx) RC(ctx.reset(st));
-  RC(decoder_chain(d, P, qh, K, T, e, g1, g2, st, dctx));
+  RC(decoder_chain(d, P, qh, K, Tb, e, g1, g2, st, dctx));
 #define WG(dy, xx, gw, gb, lay, cin, cout, kw) \
-  (dctx ? cwgrad(dctx, dy, xx, gw, gb, lay, K, cin, cout, T, kw, scratch, st) : launch_wgrad(dy, xx, gw, gb, lay, K, cin, cout, T, kw, scratch, st))
-  RC(WG(dp, g2, grads + off[P_DPW], grads + off[P_DPB], wview_fwd(nullptr, H, 1), H, 2 * C, 1));
-  RC(cconv(dctx, 1, dp, wview_dgrad(P.p[P_DPW], H, 1), nullptr, g2, dg2, K, 2 * C, H, T, 1, EPI_MASK, st));
+  (dctx ? cwgrad(dctx, dy, xx, gw, gb, lay, K, cin, cout, Tb, kw, scratch, st) : launch_wgrad(dy, xx, gw, gb, lay, K, cin, cout, Tb, kw, scratch, st))
+  RC(WG(dpb, g2, grads + off[P_DPW], grads + off[P_DPB], wview_fwd(nullptr, H, 1), H, 2 * C, 1));
+  RC(cconv(dctx, 1, dpb, wview_dgrad(P.p[P_DPW], H, 1), nullptr, g2, dg2, K, 2 * C, H, Tb, 1, EPI_MASK, st));
   RC(WG(dg2, g1, grads + off[P_D2W], grads + off[P_D2B], wview_fwd(nullptr, H, 3), H, H, 3));
-  RC(cconv(dctx, 1, dg2, wview_dgrad(P.p[P_D2W], H, 3), nullptr, g1, dg1, K, H, H, T, 3, EPI_MASK, st));
+  RC(cconv(dctx, 1, dg2, wview_dgrad(P.p[P_D2W], H, 3), nullptr, g1, dg1, K, H, H, Tb, 3, EPI_MASK, st));
   RC(WG(dg1, e, grads + off[P_D1W], grads + off[P_D1B], wview_fwd(nullptr, H, 3), H, H, 3));
-  RC(cconv(dctx, 1, dg1, wview_dgrad(P.p[P_D1W], H, 3), nullptr, nullptr, de, K, H, H, T, 3, EPI_NONE, st));
+  RC(cconv(dctx, 1, dg1, wview_dgrad(P.p[P_D1W], H, 3), nullptr, nullptr, de, K, H, H, Tb, 3, EPI_NONE, st));
   {
     WView embL{nullptr, 0, 1, H, 0};
-    RC(launch_wgrad(de, qh, grads + off[P_EMB], nullptr, embL, K, K, H, T, 1, scratch, st));
+    RC(launch_wgrad(de, qh, grads + off[P_EMB], nullptr, embL, K, K, H, Tb, 1, scratch, st));
   }
 #undef WG
 #undef RC
